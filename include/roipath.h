@@ -1,0 +1,187 @@
+/*
+ * roipath.h -- C ABI of libroipath_b200.so: the B200 (sm_100a) implementation of the
+ * RoI / NMS / mask hot path of Jittor/InstanceSegmentation-jittor.
+ *
+ * The reference has no C ABI for this path: its operators are Python callables that hand
+ * inline CUDA text to jt.code / jt.candidate.  Each entry point below names the reference
+ * interface it replaces (paths relative to the reference checkout; det/ =
+ * detectron.jittor/detectron/, yol/ = Yolact.jittor/).  INTEGRATION.md shows the ctypes
+ * binding a maintainer of the reference would add at each of those sites.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the parameter is documented "host";
+ *   - the caller owns all memory (inputs, outputs, workspaces); nothing is retained;
+ *   - `stream` is a cudaStream_t passed as void*; every call is asynchronous on it and
+ *     performs no host synchronisation;
+ *   - return value: 0 = ok, < 0 = invalid argument (RP_E_*), > 0 = a cudaError_t;
+ *   - tensors are dense, row-major, float32 unless stated; feature maps are NCHW.
+ */
+#ifndef ROIPATH_H_
+#define ROIPATH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RP_OK 0
+#define RP_E_ARG (-1)       /* null pointer / non-positive size / unsupported value */
+#define RP_E_WORKSPACE (-2) /* workspace too small */
+#define RP_E_LIMIT (-3)     /* size exceeds a documented limit */
+
+#define RP_MAX_LEVELS 8
+
+/* exported with default visibility (the library is built with -fvisibility=hidden) */
+#if defined(__GNUC__)
+#define RP_API __attribute__((visibility("default")))
+#else
+#define RP_API
+#endif
+
+/* ABI version of this header; rp_version() returns the one the library was built with. */
+#define RP_ABI_VERSION 1
+RP_API int rp_version(void);
+/* Compute capability the kernels were compiled for (100 for sm_100a). */
+RP_API int rp_built_for_sm(void);
+
+/* ------------------------------------------------------------------------------------
+ * ROIAlign (legacy / non-aligned), forward and backward.
+ * Replaces: roi_align(input, rois, output_size, spatial_scale, sampling_ratio)
+ *           det/layers/roi_align.py:298-307 (jt.code over RoIAlignForward :116-169 and
+ *           RoIAlignBackwardFeature :190-274).
+ *   feat [N,C,H,W]; rois [K,5] = (batch_idx, x1, y1, x2, y2); out [K,C,PH,PW].
+ *   sampling_ratio > 0: fixed grid; <= 0: adaptive ceil(roi/pooled) (double in forward,
+ *   float in backward, as in the reference).
+ *   mode 0 = tiled fast path (separable evaluation order, result within 1e-5 relative of
+ *   the reference); mode 1 = one thread per output in the reference's exact operand order.
+ * rp_roi_align_backward zero-fills grad_input itself (reference: cudaMemsetAsync :285).
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_roi_align_forward(const float* feat, int N, int C, int H, int W, const float* rois, int K,
+                         int PH, int PW, float spatial_scale, float sampling_ratio, float* out,
+                         int mode, void* stream);
+
+RP_API int rp_roi_align_backward(const float* dout, const float* rois, int K, int N, int C, int H, int W,
+                          int PH, int PW, float spatial_scale, float sampling_ratio,
+                          float* grad_input, int mode, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * FPN level mapping and the fused multi-level Pooler.
+ * Replaces: LevelMapper.__call__ det/modeling/poolers.py:31-43 (area with +1,
+ *           det/structures/bounding_box.py:292-304), LevelMapperwithArea.__call__ :62-73,
+ *           Pooler.execute :123-156 (per-level nonzero/gather/ROIAlign/scatter loop).
+ *   rois [K,5]; levels [K] int32 in [0,L).  One launch pools every RoI from the map of its
+ *   level and writes it to its ORIGINAL row of out [K,C,PH,PW].
+ *   feats/H/W/scales and grads are HOST arrays of length L (L <= RP_MAX_LEVELS).
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_level_map(const float* rois, int K, int k_min, int k_max, float canonical_scale,
+                 int canonical_level, float eps, int* levels, void* stream);
+
+RP_API int rp_level_map_area(const float* rois, const float* img_area, int K, int k_min, int k_max,
+                      float eps, int* levels, void* stream);
+
+RP_API int rp_pooler_forward(const float* const* feats, const int* H, const int* W, const float* scales,
+                      int L, int N, int C, const float* rois, const int* levels, int K, int PH,
+                      int PW, float sampling_ratio, float* out, int mode, void* stream);
+
+RP_API int rp_pooler_backward(const float* dout, const float* rois, const int* levels, int K,
+                       const int* H, const int* W, const float* scales, int L, int N, int C,
+                       int PH, int PW, float sampling_ratio, float* const* grads, int mode,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Greedy NMS family.
+ * Replaces: nms(dets, scores, thr) det/layers/nms.py:12-14 (-> jittor.nms),
+ *           ml_nms / _ml_nms :18-40 (jt.argsort + jt.candidate with the +1 IoU fail
+ *           condition :28-34), the keep[:max_proposals] truncation of boxlist_nms
+ *           det/structures/boxlist_ops.py:31-32, and the comparator variant of
+ *           yol/utils/cython_nms.pyx:24-74 (flags & RP_NMS_GE).
+ * A batch is B independent problems ("segments"): problem b owns rows
+ * [offsets[b], offsets[b+1]) of boxes/scores/labels (offsets: DEVICE int32 [B+1]).
+ *   boxes [n,4] xyxy; scores [n]; labels [n] float or NULL; thr compared as the reference
+ *   does ((double)iou > thr, or iou >= (float)thr with RP_NMS_GE).
+ *   keep [n] int32: for problem b, keep[offsets[b] + i], i < n_keep[b], are the kept
+ *   indices RELATIVE to offsets[b], in descending-score order (stable: equal scores keep
+ *   ascending index); n_keep [B] int32.  max_keep > 0 stops after that many.
+ *   n_total = offsets[B] and n_max = max segment length are passed by the host.
+ * flags: RP_NMS_GE               suppress when iou >= (float)thr (cython_nms.pyx:69)
+ *        RP_NMS_ASCENDING        return each keep list sorted by ascending index (:74)
+ *        RP_NMS_TIES_HIGH_FIRST  equal scores: higher index first (argsort()[::-1], :35)
+ *        RP_NMS_CYTHON           all three: the yol/utils/cython_nms.pyx contract
+ * ------------------------------------------------------------------------------------ */
+#define RP_NMS_GE 1
+#define RP_NMS_ASCENDING 2
+#define RP_NMS_TIES_HIGH_FIRST 4
+#define RP_NMS_CYTHON (RP_NMS_GE | RP_NMS_ASCENDING | RP_NMS_TIES_HIGH_FIRST)
+
+RP_API size_t rp_nms_workspace_bytes(int n_total, int n_max, int B);
+
+RP_API int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
+                   const int* offsets, int B, int n_total, int n_max, double thr, int max_keep,
+                   int flags, int* keep, int* n_keep, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Yolact: box decode, detection pre-filter, FastNMS.
+ * Replaces: decode(loc, priors) yol/layers/box_utils.py:272-316;
+ *           Detect.detect 'Slices' yol/layers/functions/detection.py:81-99;
+ *           Detect.fast_nms :139-189 and Detect.cc_fast_nms :113-137
+ *           (jaccard / intersect yol/layers/box_utils.py:31-78).
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_yolact_decode(const float* loc, const float* priors, int n, float* out, void* stream);
+
+/* Batched FastNMS.  Image b owns candidates [offsets[b], offsets[b+1]) (DEVICE int32 [B+1])
+ * of boxes [n_total,4] (relative xyxy) and coeff [n_total,D]; scores is [C, n_total]
+ * (class-major, row stride n_total).  Per image at most max_det detections, sorted by
+ * descending score, are written to row b of
+ *   out_boxes [B,max_det,4], out_coeff [B,max_det,D], out_classes [B,max_det] int32,
+ *   out_scores [B,max_det], out_index [B,max_det] int32 (candidate index relative to
+ *   offsets[b]; may be NULL), n_out [B] int32.
+ * cross_class != 0 selects cc_fast_nms (max_det is then ignored up to top_k).
+ * Limits: top_k <= 256. */
+RP_API size_t rp_fast_nms_workspace_bytes(int n_total, int n_max, int B, int C, int top_k);
+
+RP_API int rp_fast_nms_batched(const float* boxes, const float* coeff, const float* scores,
+                        const int* offsets, int B, int n_total, int n_max, int C, int D,
+                        float iou_thr, int top_k, int max_det, int second_threshold,
+                        float conf_thresh, int cross_class, float* out_boxes, float* out_coeff,
+                        int* out_classes, float* out_scores, int* out_index, int* n_out,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Prototype x coefficient mask assembly, fused with sigmoid, crop, bilinear upsample and
+ * threshold.
+ * Replaces: postprocess(...) lincomb branch yol/layers/output_utils.py:60-101 with
+ *           crop / sanitize_coordinates yol/layers/box_utils.py:333-378.
+ * Image b: proto [B,ph,pw,D] (NHWC), and detections [det_offsets[b], det_offsets[b+1])
+ * (DEVICE int32 [B+1]; or NULL with B == 1 and m_total detections) of coeff [m_total,D]
+ * and boxes [m_total,4] (relative xyxy).
+ *   out_masks [m_total,out_h,out_w] uint8 (0/1); out_boxes [m_total,4] int32 (may be NULL);
+ *   low_out [m_total,ph,pw] float (may be NULL): cropped low-resolution probabilities.
+ * Limits: D <= 64.
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_mask_assemble(const float* proto, const float* coeff, const float* boxes,
+                     const int* det_offsets, int B, int m_total, int ph, int pw, int D, int out_h,
+                     int out_w, int crop, uint8_t* out_masks, int32_t* out_boxes, float* low_out,
+                     void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Mask R-CNN mask post-processing.
+ * Replaces: MaskPostProcessor.execute det/modeling/roi_heads/mask_head/inference.py:38-45
+ *           (sigmoid + label channel select) and Masker / paste_mask_in_image :90-162,
+ *           :175-205 (pad, expand box, int32 truncation, bilinear resize, threshold, paste).
+ *   logits [K,NC,M,M], labels [K] int32 -> prob [K,M,M].
+ *   masks [n,M,M] probabilities, boxes [n,4] xyxy -> out [n,im_h,im_w] uint8 (0/1), fully
+ *   written (zero outside the box).  thresh < 0 selects the (mask*255) != 0 branch.
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_mask_select_sigmoid(const float* logits, const int* labels, int K, int NC, int M,
+                           float* out, void* stream);
+
+RP_API int rp_paste_masks(const float* masks, const float* boxes, int n, int M, int im_h, int im_w,
+                   float thresh, int padding, uint8_t* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROIPATH_H_ */

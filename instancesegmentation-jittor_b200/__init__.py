@@ -1,0 +1,20 @@
+"""b200-roi-path: the RoI / NMS / mask hot path of Jittor/InstanceSegmentation-jittor,
+hand-written for B200 (sm_100a) behind the reference's Python call signatures.
+
+Everything here calls libroipath_b200.so through ctypes (include/roipath.h); there is no
+torch-op or CPU fallback and nothing under oracle/ is ever imported.
+"""
+from . import _lib
+from ._lib import RoiPathError, lib
+from .layers import (ROIAlign, cython_nms, ml_nms, nms, nms_batched, roi_align,
+                     roi_align_backward, roi_align_forward)
+from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_in_image,
+                     paste_masks)
+from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_format,
+                      make_pooler, pooler_backward, pooler_forward)
+from .structures import (BoxList, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
+                         remove_small_boxes)
+from .yolact import (Detect, crop, decode, fast_nms_batched, mask_assemble, postprocess,
+                     sanitize_coordinates)
+
+__all__ = [n for n in dir() if not n.startswith("_")]

@@ -1,0 +1,63 @@
+// common.cuh -- small helpers shared by the kernels of libroipath_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../../include/roipath.h"
+#include "../../include/roipath_math.h"
+
+#define RP_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+#define RP_CUDA_TRY(expr)                  \
+  do {                                     \
+    cudaError_t rp_err__ = (expr);         \
+    if (rp_err__ != cudaSuccess) {         \
+      (void)cudaGetLastError();            \
+      return (int)rp_err__;                \
+    }                                      \
+  } while (0)
+
+#define RP_LAUNCH_CHECK()                  \
+  do {                                     \
+    cudaError_t rp_err__ = cudaGetLastError(); \
+    if (rp_err__ != cudaSuccess) return (int)rp_err__; \
+  } while (0)
+
+static inline int rp_env_int(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return (s && *s) ? atoi(s) : dflt;
+}
+
+static inline size_t rp_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+__device__ __forceinline__ uint32_t rp_smem_addr(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// Make this thread's generic-proxy shared-memory writes visible to the async proxy (TMA).
+__device__ __forceinline__ void rp_fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// TMA 1-D bulk store shared -> global (SASS: UBLKCP).  dst and src 16-byte aligned,
+// bytes a multiple of 16.  Issued by ONE thread; completion tracked by the bulk group.
+__device__ __forceinline__ void rp_bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(rp_smem_addr(ssrc)), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+// Wait until every committed bulk store of this thread has finished READING shared memory.
+__device__ __forceinline__ void rp_bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+__device__ __forceinline__ void rp_bulk_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// Streaming (evict-first) stores for write-once outputs.
+__device__ __forceinline__ void rp_st_cs_u32(uint32_t* p, uint32_t v) { __stcs(p, v); }

@@ -1,0 +1,655 @@
+// roi_align.cu -- ROIAlign forward/backward and the fused multi-level FPN Pooler for sm_100a.
+//
+// Reference being replaced (paths relative to the reference checkout):
+//   det/layers/roi_align.py:116-169  RoIAlignForward          (1 thread / output, 16 scalar gathers)
+//   det/layers/roi_align.py:190-274  RoIAlignBackwardFeature  (16 global atomics / output)
+//   det/modeling/poolers.py:123-156  Pooler.execute           (per-level nonzero/gather/scatter loop)
+//   det/modeling/poolers.py:31-43,62-73  LevelMapper / LevelMapperwithArea
+//
+// Design (see DESIGN.md "ROIAlign"): one CTA per RoI (x an optional channel split).  The CTA
+// builds the two 1-D sweep plans of the RoI once (roi_tile.h), then for each chunk of
+// channels
+//   phase 1  lanes along x, U1 channels per thread: one monotone sweep down the RoI's
+//            feature tile straight from global memory (coalesced row segments, every tile
+//            element read exactly once, D1*U1 loads in flight per thread) -> V[c][ph][x] in smem
+//   phase 2  thread = (c, ph) row of V: one monotone sweep along x from shared memory
+//            -> out tile [c][ph][pw] in smem
+//   store    the chunk's output is contiguous in global memory: one TMA bulk store
+//            (cp.async.bulk shared->global) issued by a single thread.
+// All RoIs of all FPN levels go through ONE launch: the level only selects the base pointer,
+// extent and scale, and every RoI writes its own output row (no nonzero / gather / scatter).
+// Backward is the exact transpose with the RoI's gradient tile accumulated privately and
+// flushed with ONE coalesced atomicAdd per tile element (instead of 16 per output element).
+#include "common.cuh"
+#include "roi_tile.h"
+
+namespace {
+
+constexpr int RT_THREADS = 256;
+constexpr int RT_U1 = 4;  // channels per thread, phase 1
+constexpr int RT_D1 = 8;  // rows in flight per thread, phase 1
+constexpr int RT_U2 = 2;  // channels per thread, phase 2
+constexpr int RT_D2 = 4;
+constexpr int RT_CC_CAP = 32;  // max channels per chunk (bounds the out tile)
+
+struct RtLevels {
+  const float* feat[RP_MAX_LEVELS];
+  float* grad[RP_MAX_LEVELS];
+  int H[RP_MAX_LEVELS];
+  int W[RP_MAX_LEVELS];
+  float scale[RP_MAX_LEVELS];
+  int L;
+};
+
+// ------------------------------------------------------------------------------------------
+// forward functors
+// ------------------------------------------------------------------------------------------
+template <int U>
+struct FwdRowLoader {  // phase 1: tile row r of U channels at this thread's column
+  const float* base;   // &feat[b][c0+q][lo0y][lo0x + x]
+  size_t cstride;      // nq * H * W
+  int W;
+  int nvalid;
+  __device__ __forceinline__ void operator()(int r, float (&v)[U]) const {
+    const float* p = base + (size_t)r * W;
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? __ldg(p + (size_t)u * cstride) : 0.f;
+  }
+};
+
+template <int U>
+struct FwdVSink {  // phase 1: V[c][bin][x]
+  float* base;     // &Vs[(q*PH)*twp + x]
+  int bstride;     // twp
+  int cstride;     // nq * PH * twp
+  int nvalid;
+  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
+    float* p = base + bin * bstride;
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) p[u * cstride] = acc[u];
+  }
+};
+
+template <int U>
+struct FwdVLoader {  // phase 2: V[c][ph][r]
+  const float* base; // &Vs[(q*PH + ph)*twp]
+  int cstride;
+  int nvalid;
+  __device__ __forceinline__ void operator()(int r, float (&v)[U]) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? base[u * cstride + r] : 0.f;
+  }
+};
+
+template <int U>
+struct FwdOutSink {  // phase 2: out tile [c][ph][bin]
+  float* base;       // &out_s[(q*PH + ph)*PW]
+  int cstride;       // nq * PH * PW
+  int nvalid;
+  float inv;         // exact 1/count or 0
+  float count;
+  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) base[u * cstride + bin] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+  }
+};
+
+__device__ __forceinline__ void rt_zero_fill(float* dst, size_t n) {
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------
+// forward kernel
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_THREADS)
+rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   float* __restrict__ out, int c_per_cta, int vs_floats, int use_bulk) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  RtAxisPlan* py = reinterpret_cast<RtAxisPlan*>(rt_smem);
+  RtAxisPlan* px = py + 1;
+  float* Vs = reinterpret_cast<float*>(rt_smem + ((2 * sizeof(RtAxisPlan) + 15) / 16) * 16);
+  float* out_s = Vs + vs_floats;
+  __shared__ int s_ok[2];
+
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x;
+  const int c_begin = blockIdx.y * c_per_cta;
+  const int c_end = min(C, c_begin + c_per_cta);
+  if (c_begin >= c_end) return;
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  float* out_k = out + ((size_t)k * C + c_begin) * P;
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) {
+    rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+    return;
+  }
+  const int H = lv.H[level], W = lv.W[level];
+  const size_t HW = (size_t)H * W;
+  const float* feat_b = lv.feat[level] + ((size_t)b * C + c_begin) * HW;
+  const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+
+  if (tid == 0) s_ok[0] = rt_build_axis_plan(py, g.sh, g.bh, PH, g.gh, H);
+  if (tid == 32) s_ok[1] = rt_build_axis_plan(px, g.sw, g.bw, PW, g.gw, W);
+  __syncthreads();
+
+  const int tiled = s_ok[0] && s_ok[1];
+  const int R = py->n, tw = px->n;
+  if (tiled && (R == 0 || tw == 0)) {  // no sample inside the map: the reference writes 0
+    rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+    return;
+  }
+  const int twp = tw | 1;  // odd row pitch: phase-2 lanes (stride twp) hit distinct banks
+  int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
+  if (cc_max > RT_CC_CAP) cc_max = RT_CC_CAP;
+  cc_max &= ~3;
+  if (cc_max < 4) {
+    // RoI too large for the tile buffers: reference-order evaluation straight from global.
+    const int total = (c_end - c_begin) * P;
+    for (int i = tid; i < total; i += RT_THREADS) {
+      const int c = i / P;
+      const int rem = i - c * P;
+      const int ph = rem / PW, pw = rem - ph * PW;
+      out_k[i] = rt_direct_output(feat_b + (size_t)c * HW, H, W, g, ph, pw);
+    }
+    return;
+  }
+
+  const int count = g.gh * g.gw;
+  const float inv = rt_exact_inv(count);
+  const float* tile0 = feat_b + (size_t)py->lo0 * W + px->lo0;
+  bool bulk_pending = false;
+
+  for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+    const int cc = min(cc_max, c_end - c_begin - c0);
+    // ---- phase 1: rows, from global -------------------------------------------------------
+    {
+      const int nq = (cc + RT_U1 - 1) / RT_U1;
+      const int items = nq * tw;
+      for (int it = tid; it < items; it += RT_THREADS) {
+        const int q = it / tw;
+        const int x = it - q * tw;
+        int nvalid = (cc - q + nq - 1) / nq;  // number of u with q + u*nq < cc
+        if (nvalid > RT_U1) nvalid = RT_U1;
+        FwdRowLoader<RT_U1> ld{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid};
+        FwdVSink<RT_U1> sink{Vs + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
+        rt_sweep_fwd<RT_U1, RT_D1>(*py, ld, sink);
+      }
+    }
+    if (bulk_pending && tid == 0) rp_bulk_wait_read();  // out_s is about to be rewritten
+    __syncthreads();
+    // ---- phase 2: columns, from shared ----------------------------------------------------
+    {
+      const int nq = (cc + RT_U2 - 1) / RT_U2;
+      const int items = nq * PH;
+      for (int it = tid; it < items; it += RT_THREADS) {
+        const int q = it / PH;
+        const int ph = it - q * PH;
+        int nvalid = (cc - q + nq - 1) / nq;
+        if (nvalid > RT_U2) nvalid = RT_U2;
+        FwdVLoader<RT_U2> ld{Vs + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
+        FwdOutSink<RT_U2> sink{out_s + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid, inv,
+                               (float)count};
+        rt_sweep_fwd<RT_U2, RT_D2>(*px, ld, sink);
+      }
+    }
+    // ---- store: the chunk is contiguous in global memory ----------------------------------
+    float* dst = out_k + (size_t)c0 * P;
+    const int nfl = cc * P;
+    const bool bulk = use_bulk && ((nfl & 3) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+    if (bulk) {
+      rp_fence_proxy_async_smem();
+      __syncthreads();
+      if (tid == 0) rp_bulk_store(dst, out_s, (uint32_t)nfl * 4u);
+      bulk_pending = true;
+    } else {
+      __syncthreads();
+      for (int i = tid; i < nfl; i += RT_THREADS) dst[i] = out_s[i];
+      bulk_pending = false;
+    }
+  }
+  if (bulk_pending && tid == 0) rp_bulk_wait_all();
+}
+
+// mode 1: one thread per output element, reference operand order (bit-exact vs the oracle).
+__global__ void __launch_bounds__(256)
+rt_pool_fwd_exact_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                         const int* __restrict__ levels, size_t total, int PH, int PW,
+                         float sampling_ratio, float* __restrict__ out) {
+  const int P = PH * PW;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int pw = (int)(i % PW);
+    const int ph = (int)((i / PW) % PH);
+    const int c = (int)((i / P) % C);
+    const int k = (int)(i / ((size_t)P * C));
+    const float* roi = rois + (size_t)k * 5;
+    const int level = levels ? levels[k] : 0;
+    const int b = (int)roi[0];
+    if (level < 0 || level >= lv.L || b < 0 || b >= N) {
+      out[i] = 0.f;
+      continue;
+    }
+    const int H = lv.H[level], W = lv.W[level];
+    const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+    out[i] = rt_direct_output(lv.feat[level] + ((size_t)b * C + c) * H * W, H, W, g, ph, pw);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward functors
+// ------------------------------------------------------------------------------------------
+template <int U>
+struct BwdDoutSource {  // phase A: dout tile [c][ph][bin=pw] in smem
+  const float* base;    // &d_s[(q*PH + ph)*PW]
+  int cstride;
+  int nvalid;
+  __device__ __forceinline__ void operator()(int bin, float (&g)[U]) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u) g[u] = (u < nvalid) ? base[u * cstride + bin] : 0.f;
+  }
+};
+
+template <int U>
+struct BwdHEmit {  // phase A: Hs[c][ph][x]
+  float* base;     // &Hs[(q*PH + ph)*twp]
+  int cstride;
+  int nvalid;
+  __device__ __forceinline__ void operator()(int r, const float (&v)[U]) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) base[u * cstride + r] = v[u];
+  }
+};
+
+template <int U>
+struct BwdHSource {  // phase B: Hs[c][bin=ph][x]
+  const float* base; // &Hs[(q*PH)*twp + x]
+  int bstride;       // twp
+  int cstride;
+  int nvalid;
+  __device__ __forceinline__ void operator()(int bin, float (&g)[U]) const {
+    const float* p = base + bin * bstride;
+#pragma unroll
+    for (int u = 0; u < U; ++u) g[u] = (u < nvalid) ? p[u * cstride] : 0.f;
+  }
+};
+
+template <int U>
+struct BwdGradEmit {  // phase B: one atomicAdd per tile element, lanes along x (coalesced RED)
+  float* base;        // &grad[b][c0+q][lo0y][lo0x + x]
+  size_t cstride;
+  int W;
+  int nvalid;
+  float inv;
+  float count;
+  __device__ __forceinline__ void operator()(int r, const float (&v)[U]) const {
+    float* p = base + (size_t)r * W;
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) {
+        const float val = (inv != 0.f) ? v[u] * inv : v[u] / count;
+        if (val != 0.f) atomicAdd(p + (size_t)u * cstride, val);
+      }
+  }
+};
+
+// Reference-order backward for one output element (det/layers/roi_align.py:62-111,:236-272).
+__device__ __forceinline__ void rt_direct_backward(float* plane, int H, int W, const RtGeom& g,
+                                                   int ph, int pw, float top) {
+  const float count = (float)(g.gh * g.gw);
+  for (int iy = 0; iy < g.gh; ++iy) {
+    int ylo, yhi;
+    float hy, ly;
+    const int vy = rt_axis_tap(g.sh, g.bh, ph, iy, g.gh, H, &ylo, &yhi, &hy, &ly);
+    for (int ix = 0; ix < g.gw; ++ix) {
+      int xlo, xhi;
+      float hx, lx;
+      const int vx = rt_axis_tap(g.sw, g.bw, pw, ix, g.gw, W, &xlo, &xhi, &hx, &lx);
+      if (!(vy && vx)) continue;
+      const float w1 = hy * hx, w2 = hy * lx, w3 = ly * hx, w4 = ly * lx;
+      atomicAdd(plane + ylo * W + xlo, top * w1 / count);
+      atomicAdd(plane + ylo * W + xhi, top * w2 / count);
+      atomicAdd(plane + yhi * W + xlo, top * w3 / count);
+      atomicAdd(plane + yhi * W + xhi, top * w4 / count);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward kernel (transpose of the forward sweeps)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_THREADS)
+rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   const float* __restrict__ dout, int c_per_cta, int vs_floats) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  RtAxisPlan* py = reinterpret_cast<RtAxisPlan*>(rt_smem);
+  RtAxisPlan* px = py + 1;
+  float* Hs = reinterpret_cast<float*>(rt_smem + ((2 * sizeof(RtAxisPlan) + 15) / 16) * 16);
+  float* d_s = Hs + vs_floats;
+  __shared__ int s_ok[2];
+
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x;
+  const int c_begin = blockIdx.y * c_per_cta;
+  const int c_end = min(C, c_begin + c_per_cta);
+  if (c_begin >= c_end) return;
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) return;
+  const int H = lv.H[level], W = lv.W[level];
+  const size_t HW = (size_t)H * W;
+  float* grad_b = lv.grad[level] + ((size_t)b * C + c_begin) * HW;
+  const float* dout_k = dout + ((size_t)k * C + c_begin) * P;
+  const RtGeom g = rt_geom_bwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+
+  if (tid == 0) s_ok[0] = rt_build_axis_plan(py, g.sh, g.bh, PH, g.gh, H);
+  if (tid == 32) s_ok[1] = rt_build_axis_plan(px, g.sw, g.bw, PW, g.gw, W);
+  __syncthreads();
+
+  const int tiled = s_ok[0] && s_ok[1];
+  const int R = py->n, tw = px->n;
+  if (tiled && (R == 0 || tw == 0)) return;
+  const int twp = tw | 1;
+  int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
+  if (cc_max > RT_CC_CAP) cc_max = RT_CC_CAP;
+  cc_max &= ~3;
+  if (cc_max < 4) {
+    const int total = (c_end - c_begin) * P;
+    for (int i = tid; i < total; i += RT_THREADS) {
+      const int c = i / P;
+      const int rem = i - c * P;
+      const int ph = rem / PW, pw = rem - ph * PW;
+      rt_direct_backward(grad_b + (size_t)c * HW, H, W, g, ph, pw, dout_k[i]);
+    }
+    return;
+  }
+
+  const int count = g.gh * g.gw;
+  const float inv = rt_exact_inv(count);
+  float* tile0 = grad_b + (size_t)py->lo0 * W + px->lo0;
+
+  for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+    const int cc = min(cc_max, c_end - c_begin - c0);
+    // ---- stage the chunk's dout (contiguous) --------------------------------------------
+    {
+      const float* src = dout_k + (size_t)c0 * P;
+      const int nfl = cc * P;
+      for (int i = tid; i < nfl; i += RT_THREADS) d_s[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    // ---- phase A: transpose of the column sweep: dout[c][ph][:] -> Hs[c][ph][x] ------------
+    {
+      const int nq = (cc + RT_U2 - 1) / RT_U2;
+      const int items = nq * PH;
+      for (int it = tid; it < items; it += RT_THREADS) {
+        const int q = it / PH;
+        const int ph = it - q * PH;
+        int nvalid = (cc - q + nq - 1) / nq;
+        if (nvalid > RT_U2) nvalid = RT_U2;
+        BwdDoutSource<RT_U2> src{d_s + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid};
+        BwdHEmit<RT_U2> emit{Hs + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
+        rt_sweep_bwd<RT_U2>(*px, src, emit);
+      }
+    }
+    __syncthreads();
+    // ---- phase B: transpose of the row sweep: Hs[c][:][x] -> grad tile, one RED / element ---
+    {
+      const int nq = (cc + RT_U1 - 1) / RT_U1;
+      const int items = nq * tw;
+      for (int it = tid; it < items; it += RT_THREADS) {
+        const int q = it / tw;
+        const int x = it - q * tw;
+        int nvalid = (cc - q + nq - 1) / nq;
+        if (nvalid > RT_U1) nvalid = RT_U1;
+        BwdHSource<RT_U1> src{Hs + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
+        BwdGradEmit<RT_U1> emit{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid,
+                                inv, (float)count};
+        rt_sweep_bwd<RT_U1>(*py, src, emit);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// mode 1: the reference's own scheme (one thread per output element, 4 atomics per sample).
+__global__ void __launch_bounds__(256)
+rt_pool_bwd_exact_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                         const int* __restrict__ levels, size_t total, int PH, int PW,
+                         float sampling_ratio, const float* __restrict__ dout) {
+  const int P = PH * PW;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int pw = (int)(i % PW);
+    const int ph = (int)((i / PW) % PH);
+    const int c = (int)((i / P) % C);
+    const int k = (int)(i / ((size_t)P * C));
+    const float* roi = rois + (size_t)k * 5;
+    const int level = levels ? levels[k] : 0;
+    const int b = (int)roi[0];
+    if (level < 0 || level >= lv.L || b < 0 || b >= N) continue;
+    const int H = lv.H[level], W = lv.W[level];
+    const RtGeom g = rt_geom_bwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+    rt_direct_backward(lv.grad[level] + ((size_t)b * C + c) * H * W, H, W, g, ph, pw, dout[i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// level mapping
+// ------------------------------------------------------------------------------------------
+__global__ void rt_level_map_kernel(const float* __restrict__ rois, int K, int k_min, int k_max,
+                                    float s0, int lvl0, float eps, int* __restrict__ levels) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const float* b = rois + (size_t)k * 5 + 1;
+  levels[k] = rp_fpn_level(b[0], b[1], b[2], b[3], k_min, k_max, s0, lvl0, eps);
+}
+
+__global__ void rt_level_map_area_kernel(const float* __restrict__ rois,
+                                         const float* __restrict__ img_area, int K, int k_min,
+                                         int k_max, float eps, int* __restrict__ levels) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const float* b = rois + (size_t)k * 5 + 1;
+  levels[k] = rp_fpn_level_area(b[0], b[1], b[2], b[3], img_area[k], k_min, k_max, eps);
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+struct RtLaunch {
+  int csplit, c_per_cta, vs_floats;
+  size_t smem;
+};
+
+RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
+  RtLaunch l;
+  // V buffer: enough for RT_CC_CAP channels of a 27-wide tile at 14 bins; tunable for ncu runs.
+  l.vs_floats = rp_env_int("RP_ROI_VS_FLOATS", 8192);
+  const int min_vs = PH * 3 * 4;  // at least 4 channels of a 2-wide tile
+  if (l.vs_floats < min_vs) l.vs_floats = min_vs;
+  // enough CTAs for ~4 waves of 3 resident CTAs per SM; otherwise one CTA per RoI
+  const int want = 4 * 3 * RP_NUM_SMS;
+  int csplit = 1;
+  if (K < want) csplit = (want + K - 1) / K;
+  const int max_split = (C + 31) / 32;
+  if (csplit > max_split) csplit = max_split;
+  if (csplit < 1) csplit = 1;
+  int cpc = (C + csplit - 1) / csplit;
+  cpc = (cpc + 3) & ~3;
+  l.c_per_cta = cpc;
+  l.csplit = (C + cpc - 1) / cpc;
+  l.smem = rp_align_up(2 * sizeof(RtAxisPlan), 16) + sizeof(float) * (size_t)l.vs_floats +
+           sizeof(float) * (size_t)RT_CC_CAP * PH * PW;
+  return l;
+}
+
+int rt_fill_levels(RtLevels* lv, const float* const* feats, float* const* grads, const int* H,
+                   const int* W, const float* scales, int L) {
+  if (L < 1 || L > RP_MAX_LEVELS || !H || !W || !scales) return RP_E_ARG;
+  lv->L = L;
+  for (int l = 0; l < RP_MAX_LEVELS; ++l) {
+    lv->feat[l] = nullptr;
+    lv->grad[l] = nullptr;
+    lv->H[l] = lv->W[l] = 0;
+    lv->scale[l] = 0.f;
+  }
+  for (int l = 0; l < L; ++l) {
+    if (H[l] < 1 || W[l] < 1) return RP_E_ARG;
+    if (feats) {
+      if (!feats[l]) return RP_E_ARG;
+      lv->feat[l] = feats[l];
+    }
+    if (grads) {
+      if (!grads[l]) return RP_E_ARG;
+      lv->grad[l] = grads[l];
+    }
+    lv->H[l] = H[l];
+    lv->W[l] = W[l];
+    lv->scale[l] = scales[l];
+  }
+  return RP_OK;
+}
+
+int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K,
+               int PH, int PW, float sampling_ratio, float* out, int mode, cudaStream_t st) {
+  if (K == 0) return RP_OK;
+  if (!rois || !out || N < 1 || C < 1 || K < 0 || PH < 1 || PW < 1) return RP_E_ARG;
+  if ((size_t)PH * PW > 4096) return RP_E_LIMIT;
+  if (mode == 1) {
+    const size_t total = (size_t)K * C * PH * PW;
+    size_t blocks = (total + 255) / 256;
+    if (blocks > (size_t)RP_NUM_SMS * 32) blocks = (size_t)RP_NUM_SMS * 32;
+    rt_pool_fwd_exact_kernel<<<(unsigned)blocks, 256, 0, st>>>(lv, N, C, rois, levels, total, PH,
+                                                               PW, sampling_ratio, out);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
+  if (mode != 0) return RP_E_ARG;
+  const RtLaunch l = rt_plan_launch(K, C, PH, PW);
+  if (l.smem > 227 * 1024) return RP_E_LIMIT;
+  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)l.smem));
+  const int use_bulk = rp_env_int("RP_ROI_BULK_STORE", 1);
+  dim3 grid((unsigned)K, (unsigned)l.csplit);
+  rt_pool_fwd_kernel<<<grid, RT_THREADS, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                       sampling_ratio, out, l.c_per_cta,
+                                                       l.vs_floats, use_bulk);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K,
+                int PH, int PW, float sampling_ratio, const float* dout, int mode,
+                cudaStream_t st) {
+  for (int l = 0; l < lv.L; ++l)
+    RP_CUDA_TRY(cudaMemsetAsync(lv.grad[l], 0, sizeof(float) * (size_t)N * C * lv.H[l] * lv.W[l], st));
+  if (K == 0) return RP_OK;
+  if (!rois || !dout || N < 1 || C < 1 || K < 0 || PH < 1 || PW < 1) return RP_E_ARG;
+  if ((size_t)PH * PW > 4096) return RP_E_LIMIT;
+  if (mode == 1) {
+    const size_t total = (size_t)K * C * PH * PW;
+    size_t blocks = (total + 255) / 256;
+    if (blocks > (size_t)RP_NUM_SMS * 32) blocks = (size_t)RP_NUM_SMS * 32;
+    rt_pool_bwd_exact_kernel<<<(unsigned)blocks, 256, 0, st>>>(lv, N, C, rois, levels, total, PH,
+                                                               PW, sampling_ratio, dout);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
+  if (mode != 0) return RP_E_ARG;
+  const RtLaunch l = rt_plan_launch(K, C, PH, PW);
+  if (l.smem > 227 * 1024) return RP_E_LIMIT;
+  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)l.smem));
+  dim3 grid((unsigned)K, (unsigned)l.csplit);
+  rt_pool_bwd_kernel<<<grid, RT_THREADS, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                       sampling_ratio, dout, l.c_per_cta,
+                                                       l.vs_floats);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+int rp_roi_align_forward(const float* feat, int N, int C, int H, int W, const float* rois, int K,
+                         int PH, int PW, float spatial_scale, float sampling_ratio, float* out,
+                         int mode, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!feat) return RP_E_ARG;
+  RtLevels lv;
+  const float* feats[1] = {feat};
+  int rc = rt_fill_levels(&lv, feats, nullptr, &H, &W, &spatial_scale, 1);
+  if (rc) return rc;
+  return rt_forward(lv, N, C, rois, nullptr, K, PH, PW, sampling_ratio, out, mode,
+                    (cudaStream_t)stream);
+}
+
+int rp_roi_align_backward(const float* dout, const float* rois, int K, int N, int C, int H, int W,
+                          int PH, int PW, float spatial_scale, float sampling_ratio,
+                          float* grad_input, int mode, void* stream) {
+  if (!grad_input || N < 1 || C < 1) return RP_E_ARG;
+  RtLevels lv;
+  float* grads[1] = {grad_input};
+  int rc = rt_fill_levels(&lv, nullptr, grads, &H, &W, &spatial_scale, 1);
+  if (rc) return rc;
+  return rt_backward(lv, N, C, rois, nullptr, K, PH, PW, sampling_ratio, dout, mode,
+                     (cudaStream_t)stream);
+}
+
+int rp_level_map(const float* rois, int K, int k_min, int k_max, float canonical_scale,
+                 int canonical_level, float eps, int* levels, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!rois || !levels || K < 0 || k_max < k_min) return RP_E_ARG;
+  rt_level_map_kernel<<<(K + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      rois, K, k_min, k_max, canonical_scale, canonical_level, eps, levels);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_level_map_area(const float* rois, const float* img_area, int K, int k_min, int k_max,
+                      float eps, int* levels, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!rois || !img_area || !levels || K < 0 || k_max < k_min) return RP_E_ARG;
+  rt_level_map_area_kernel<<<(K + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      rois, img_area, K, k_min, k_max, eps, levels);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_pooler_forward(const float* const* feats, const int* H, const int* W, const float* scales,
+                      int L, int N, int C, const float* rois, const int* levels, int K, int PH,
+                      int PW, float sampling_ratio, float* out, int mode, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!feats || (L > 1 && !levels)) return RP_E_ARG;
+  RtLevels lv;
+  int rc = rt_fill_levels(&lv, feats, nullptr, H, W, scales, L);
+  if (rc) return rc;
+  return rt_forward(lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, mode,
+                    (cudaStream_t)stream);
+}
+
+int rp_pooler_backward(const float* dout, const float* rois, const int* levels, int K,
+                       const int* H, const int* W, const float* scales, int L, int N, int C,
+                       int PH, int PW, float sampling_ratio, float* const* grads, int mode,
+                       void* stream) {
+  if (!grads || N < 1 || C < 1 || (L > 1 && K > 0 && !levels)) return RP_E_ARG;
+  RtLevels lv;
+  int rc = rt_fill_levels(&lv, nullptr, grads, H, W, scales, L);
+  if (rc) return rc;
+  return rt_backward(lv, N, C, rois, levels, K, PH, PW, sampling_ratio, dout, mode,
+                     (cudaStream_t)stream);
+}
+
+}  // extern "C"

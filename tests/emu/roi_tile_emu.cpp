@@ -1,0 +1,271 @@
+// roi_tile_emu.cpp -- HOST emulation of the tiled ROIAlign kernels (test infrastructure).
+//
+// Runs the same roi_tile.h code the CUDA kernels run (plans + sweeps), with the CTA's thread
+// loops executed serially and each __syncthreads() replaced by finishing the loop.  It lets
+// the CPU test-suite check the tiled algorithm (item mapping, channel chunking, plan
+// construction, forward and transposed sweeps) against the oracle without a GPU.
+// The chunk / item arithmetic below mirrors rt_pool_fwd_kernel / rt_pool_bwd_kernel in
+// instancesegmentation-jittor_b200/csrc/roi_align.cu line for line.
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../../instancesegmentation-jittor_b200/csrc/roi_tile.h"
+
+namespace {
+constexpr int U1 = 4, D1 = 8, U2 = 2, D2 = 4, CC_CAP = 32;
+
+template <int U>
+struct RowLoader {
+  const float* base;
+  size_t cstride;
+  int W, nvalid;
+  void operator()(int r, float (&v)[U]) const {
+    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? base[(size_t)r * W + (size_t)u * cstride] : 0.f;
+  }
+};
+template <int U>
+struct VSink {
+  float* base;
+  int bstride, cstride, nvalid;
+  void operator()(int bin, const float (&acc)[U]) const {
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) base[bin * bstride + u * cstride] = acc[u];
+  }
+};
+template <int U>
+struct VLoader {
+  const float* base;
+  int cstride, nvalid;
+  void operator()(int r, float (&v)[U]) const {
+    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? base[u * cstride + r] : 0.f;
+  }
+};
+template <int U>
+struct OutSink {
+  float* base;
+  int cstride, nvalid;
+  float inv, count;
+  void operator()(int bin, const float (&acc)[U]) const {
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) base[u * cstride + bin] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+  }
+};
+template <int U>
+struct DoutSource {
+  const float* base;
+  int cstride, nvalid;
+  void operator()(int bin, float (&g)[U]) const {
+    for (int u = 0; u < U; ++u) g[u] = (u < nvalid) ? base[u * cstride + bin] : 0.f;
+  }
+};
+template <int U>
+struct HEmit {
+  float* base;
+  int cstride, nvalid;
+  void operator()(int r, const float (&v)[U]) const {
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) base[u * cstride + r] = v[u];
+  }
+};
+template <int U>
+struct HSource {
+  const float* base;
+  int bstride, cstride, nvalid;
+  void operator()(int bin, float (&g)[U]) const {
+    for (int u = 0; u < U; ++u) g[u] = (u < nvalid) ? base[bin * bstride + u * cstride] : 0.f;
+  }
+};
+template <int U>
+struct GradEmit {
+  float* base;
+  size_t cstride;
+  int W, nvalid;
+  float inv, count;
+  void operator()(int r, const float (&v)[U]) const {
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) {
+        const float val = (inv != 0.f) ? v[u] * inv : v[u] / count;
+        if (val != 0.f) base[(size_t)r * W + (size_t)u * cstride] += val;
+      }
+  }
+};
+}  // namespace
+
+extern "C" {
+
+// levels == NULL: single level.  feats/H/W/scales are arrays of length L.
+__attribute__((visibility("default"))) int emu_pooler_forward(
+    const float* const* feats, const int* Hs, const int* Ws, const float* scales, int L, int N,
+    int C, const float* rois, const int* levels, int K, int PH, int PW, float sampling_ratio,
+    float* out, int vs_floats, int c_per_cta) {
+  const int P = PH * PW;
+  int n_direct = 0;
+  std::vector<float> Vs(vs_floats), out_s((size_t)CC_CAP * P);
+  for (int k = 0; k < K; ++k) {
+    for (int c_begin = 0; c_begin < C; c_begin += c_per_cta) {
+      const int c_end = std::min(C, c_begin + c_per_cta);
+      const float* roi = rois + (size_t)k * 5;
+      const int level = levels ? levels[k] : 0;
+      const int b = (int)roi[0];
+      float* out_k = out + ((size_t)k * C + c_begin) * P;
+      if (level < 0 || level >= L || b < 0 || b >= N) {
+        std::fill(out_k, out_k + (size_t)(c_end - c_begin) * P, 0.f);
+        continue;
+      }
+      const int H = Hs[level], W = Ws[level];
+      const size_t HW = (size_t)H * W;
+      const float* feat_b = feats[level] + ((size_t)b * C + c_begin) * HW;
+      const RtGeom g = rt_geom_fwd(roi, scales[level], sampling_ratio, PH, PW);
+      RtAxisPlan py, px;
+      const int ok0 = rt_build_axis_plan(&py, g.sh, g.bh, PH, g.gh, H);
+      const int ok1 = rt_build_axis_plan(&px, g.sw, g.bw, PW, g.gw, W);
+      const int tiled = ok0 && ok1;
+      const int R = py.n, tw = px.n;
+      if (tiled && (R == 0 || tw == 0)) {
+        std::fill(out_k, out_k + (size_t)(c_end - c_begin) * P, 0.f);
+        continue;
+      }
+      const int twp = tw | 1;
+      int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
+      if (cc_max > CC_CAP) cc_max = CC_CAP;
+      cc_max &= ~3;
+      if (cc_max < 4) {
+        ++n_direct;
+        const int total = (c_end - c_begin) * P;
+        for (int i = 0; i < total; ++i) {
+          const int c = i / P, rem = i - c * P, ph = rem / PW, pw = rem - ph * PW;
+          out_k[i] = rt_direct_output(feat_b + (size_t)c * HW, H, W, g, ph, pw);
+        }
+        continue;
+      }
+      const int count = g.gh * g.gw;
+      const float inv = rt_exact_inv(count);
+      const float* tile0 = feat_b + (size_t)py.lo0 * W + px.lo0;
+      for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+        const int cc = std::min(cc_max, c_end - c_begin - c0);
+        std::fill(Vs.begin(), Vs.end(), 1e30f);  // poison: unwritten V must never be read
+        {
+          const int nq = (cc + U1 - 1) / U1, items = nq * tw;
+          for (int it = 0; it < items; ++it) {
+            const int q = it / tw, x = it - q * tw;
+            int nvalid = (cc - q + nq - 1) / nq;
+            if (nvalid > U1) nvalid = U1;
+            RowLoader<U1> ld{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid};
+            VSink<U1> sink{Vs.data() + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
+            rt_sweep_fwd<U1, D1>(py, ld, sink);
+          }
+        }
+        std::fill(out_s.begin(), out_s.end(), 1e30f);
+        {
+          const int nq = (cc + U2 - 1) / U2, items = nq * PH;
+          for (int it = 0; it < items; ++it) {
+            const int q = it / PH, ph = it - q * PH;
+            int nvalid = (cc - q + nq - 1) / nq;
+            if (nvalid > U2) nvalid = U2;
+            VLoader<U2> ld{Vs.data() + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
+            OutSink<U2> sink{out_s.data() + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid, inv,
+                             (float)count};
+            rt_sweep_fwd<U2, D2>(px, ld, sink);
+          }
+        }
+        std::memcpy(out_k + (size_t)c0 * P, out_s.data(), sizeof(float) * (size_t)cc * P);
+      }
+    }
+  }
+  return n_direct;
+}
+
+// grads[l] must be zero-filled by the caller.
+__attribute__((visibility("default"))) int emu_pooler_backward(
+    const float* dout, const float* rois, const int* levels, int K, const int* Hs, const int* Ws,
+    const float* scales, int L, int N, int C, int PH, int PW, float sampling_ratio,
+    float* const* grads, int vs_floats, int c_per_cta) {
+  const int P = PH * PW;
+  int n_direct = 0;
+  std::vector<float> Hbuf(vs_floats), d_s((size_t)CC_CAP * P);
+  for (int k = 0; k < K; ++k) {
+    for (int c_begin = 0; c_begin < C; c_begin += c_per_cta) {
+      const int c_end = std::min(C, c_begin + c_per_cta);
+      const float* roi = rois + (size_t)k * 5;
+      const int level = levels ? levels[k] : 0;
+      const int b = (int)roi[0];
+      if (level < 0 || level >= L || b < 0 || b >= N) continue;
+      const int H = Hs[level], W = Ws[level];
+      const size_t HW = (size_t)H * W;
+      float* grad_b = grads[level] + ((size_t)b * C + c_begin) * HW;
+      const float* dout_k = dout + ((size_t)k * C + c_begin) * P;
+      const RtGeom g = rt_geom_bwd(roi, scales[level], sampling_ratio, PH, PW);
+      RtAxisPlan py, px;
+      const int ok0 = rt_build_axis_plan(&py, g.sh, g.bh, PH, g.gh, H);
+      const int ok1 = rt_build_axis_plan(&px, g.sw, g.bw, PW, g.gw, W);
+      const int tiled = ok0 && ok1;
+      const int R = py.n, tw = px.n;
+      if (tiled && (R == 0 || tw == 0)) continue;
+      const int twp = tw | 1;
+      int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
+      if (cc_max > CC_CAP) cc_max = CC_CAP;
+      cc_max &= ~3;
+      const int count = g.gh * g.gw;
+      if (cc_max < 4) {
+        ++n_direct;
+        const int total = (c_end - c_begin) * P;
+        for (int i = 0; i < total; ++i) {
+          const int c = i / P, rem = i - c * P, ph = rem / PW, pw = rem - ph * PW;
+          float* plane = grad_b + (size_t)c * HW;
+          const float top = dout_k[i];
+          for (int iy = 0; iy < g.gh; ++iy) {
+            int ylo, yhi;
+            float hy, ly;
+            const int vy = rt_axis_tap(g.sh, g.bh, ph, iy, g.gh, H, &ylo, &yhi, &hy, &ly);
+            for (int ix = 0; ix < g.gw; ++ix) {
+              int xlo, xhi;
+              float hx, lx;
+              const int vx = rt_axis_tap(g.sw, g.bw, pw, ix, g.gw, W, &xlo, &xhi, &hx, &lx);
+              if (!(vy && vx)) continue;
+              plane[ylo * W + xlo] += top * (hy * hx) / (float)count;
+              plane[ylo * W + xhi] += top * (hy * lx) / (float)count;
+              plane[yhi * W + xlo] += top * (ly * hx) / (float)count;
+              plane[yhi * W + xhi] += top * (ly * lx) / (float)count;
+            }
+          }
+        }
+        continue;
+      }
+      const float inv = rt_exact_inv(count);
+      float* tile0 = grad_b + (size_t)py.lo0 * W + px.lo0;
+      for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+        const int cc = std::min(cc_max, c_end - c_begin - c0);
+        std::memcpy(d_s.data(), dout_k + (size_t)c0 * P, sizeof(float) * (size_t)cc * P);
+        std::fill(Hbuf.begin(), Hbuf.end(), 1e30f);
+        {
+          const int nq = (cc + U2 - 1) / U2, items = nq * PH;
+          for (int it = 0; it < items; ++it) {
+            const int q = it / PH, ph = it - q * PH;
+            int nvalid = (cc - q + nq - 1) / nq;
+            if (nvalid > U2) nvalid = U2;
+            DoutSource<U2> src{d_s.data() + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid};
+            HEmit<U2> emit{Hbuf.data() + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
+            rt_sweep_bwd<U2>(px, src, emit);
+          }
+        }
+        {
+          const int nq = (cc + U1 - 1) / U1, items = nq * tw;
+          for (int it = 0; it < items; ++it) {
+            const int q = it / tw, x = it - q * tw;
+            int nvalid = (cc - q + nq - 1) / nq;
+            if (nvalid > U1) nvalid = U1;
+            HSource<U1> src{Hbuf.data() + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
+            GradEmit<U1> emit{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid, inv,
+                              (float)count};
+            rt_sweep_bwd<U1>(py, src, emit);
+          }
+        }
+      }
+    }
+  }
+  return n_direct;
+}
+
+}  // extern "C"
