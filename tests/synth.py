@@ -1,0 +1,126 @@
+"""Seeded synthetic inputs of SURVEY.md 8(d), shared by the tests, smoke() and bench.py.
+numpy only (no torch, no oracle) so that every consumer sees bit-identical inputs."""
+import numpy as np
+
+FPN_SCALES = (0.25, 0.125, 0.0625, 0.03125)
+IMG_W, IMG_H = 1333, 800
+PAD_W, PAD_H = 1344, 800  # SIZE_DIVISIBILITY 32
+
+
+def fpn_shapes(n_images, channels=256, pad_w=PAD_W, pad_h=PAD_H):
+    return [(n_images, channels, int(round(pad_h * s)), int(round(pad_w * s))) for s in FPN_SCALES]
+
+
+def fpn_features(n_images, channels=256, seed=1234, pad_w=PAD_W, pad_h=PAD_H):
+    out = []
+    for lvl, shp in enumerate(fpn_shapes(n_images, channels, pad_w, pad_h)):
+        rng = np.random.default_rng(seed + lvl)
+        out.append(rng.standard_normal(shp, dtype=np.float32))
+    return out
+
+
+ADVERSARIAL_BOXES = np.array([
+    [50.0, 50.0, 50.0, 50.0],        # zero size
+    [5.0, 5.0, 6.0, 6.0],            # 1 px
+    [0.0, 0.0, IMG_W - 1, IMG_H - 1],  # full image
+    [1200.0, 700.0, 1332.0, 799.0],  # hugging the corner
+], np.float32)
+
+
+def proposals(n, seed, img_w=IMG_W, img_h=IMG_H, smin=16.0, smax=800.0, adversarial=True):
+    """sqrt(area) log-uniform in [smin,smax], aspect in {1/2,1,2}*U(0.8,1.25), centres uniform,
+    clipped to [0,W-1]x[0,H-1] (bounding_box.py:270-273)."""
+    rng = np.random.default_rng(seed)
+    s = np.exp(rng.uniform(np.log(smin), np.log(smax), n))
+    ar = rng.choice([0.5, 1.0, 2.0], n) * rng.uniform(0.8, 1.25, n)
+    w = s * np.sqrt(ar)
+    h = s / np.sqrt(ar)
+    cx = rng.uniform(0, img_w, n)
+    cy = rng.uniform(0, img_h, n)
+    b = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], 1)
+    b[:, 0::2] = np.clip(b[:, 0::2], 0, img_w - 1)
+    b[:, 1::2] = np.clip(b[:, 1::2], 0, img_h - 1)
+    b = b.astype(np.float32)
+    if adversarial and n >= 8:
+        b[-4:] = ADVERSARIAL_BOXES
+    return b
+
+
+def rois_for_images(n_images, per_image, seed=4321, **kw):
+    """[n_images*per_image, 5] = (image, x1,y1,x2,y2), image-major."""
+    rows = []
+    for i in range(n_images):
+        b = proposals(per_image, seed + i, **kw)
+        rows.append(np.concatenate([np.full((per_image, 1), i, np.float32), b], 1))
+    return np.concatenate(rows, 0).astype(np.float32)
+
+
+def nms_boxes(n, seed, img_w=IMG_W, img_h=IMG_H, clusters=256, tie_heavy=False):
+    """Clustered boxes (realistic 70-95% suppression) and scores (SURVEY.md 8(d) cfg 2)."""
+    rng = np.random.default_rng(seed)
+    centres = rng.uniform(0, 1, (clusters, 2)) * [img_w, img_h]
+    which = rng.integers(0, clusters, n)
+    c = centres[which] + rng.normal(0, 12.0, (n, 2))
+    # sizes are a property of the cluster (objects), jittered per box
+    cs = np.exp(rng.uniform(np.log(16), np.log(512), clusters))
+    car = rng.choice([0.5, 1.0, 2.0], clusters)
+    s = cs[which] * rng.uniform(0.8, 1.25, n)
+    ar = car[which] * rng.uniform(0.8, 1.25, n)
+    w = s * np.sqrt(ar)
+    h = s / np.sqrt(ar)
+    b = np.stack([c[:, 0] - w / 2, c[:, 1] - h / 2, c[:, 0] + w / 2, c[:, 1] + h / 2], 1)
+    b[:, 0::2] = np.clip(b[:, 0::2], 0, img_w - 1)
+    b[:, 1::2] = np.clip(b[:, 1::2], 0, img_h - 1)
+    scores = rng.permutation(np.linspace(0.01, 0.99, n)).astype(np.float32)
+    if tie_heavy:
+        scores = (np.floor(scores * 256) / 256).astype(np.float32)
+    labels = rng.integers(1, 81, n).astype(np.float32)
+    return b.astype(np.float32), scores, labels
+
+
+def yolact_priors(max_size=550):
+    """Prior boxes exactly as Yolact.jittor/yolact.py:198-238 for yolact_resnet50
+    (conv sizes 69,35,18,9,5; scales 24..384; aspect ratios [1,1/2,2]; square anchors)."""
+    out = []
+    for conv, scale in zip((69, 35, 18, 9, 5), (24, 48, 96, 192, 384)):
+        for j in range(conv):
+            for i in range(conv):
+                x = (i + 0.5) / conv
+                y = (j + 0.5) / conv
+                for ar in (1, 0.5, 2):
+                    ar = np.sqrt(ar)
+                    w = scale * ar / max_size
+                    h = w  # use_square_anchors
+                    out.append([x, y, w, h])
+    return np.asarray(out, np.float32)
+
+
+def yolact_image(seed, priors, num_classes=81, mask_dim=32, proto_hw=138, hot_frac=0.02):
+    """One image of Yolact head outputs (SURVEY.md 8(d) cfg 4)."""
+    rng = np.random.default_rng(seed)
+    P = priors.shape[0]
+    loc = rng.normal(0, 0.5, (P, 4)).astype(np.float32)
+    logits = rng.standard_normal((P, num_classes)).astype(np.float32)
+    logits[:, 0] += 6.0
+    hot = rng.random(P) < hot_frac
+    cls = rng.integers(1, num_classes, P)
+    logits[hot, cls[hot]] += 8.0
+    e = np.exp(logits - logits.max(1, keepdims=True))
+    conf = (e / e.sum(1, keepdims=True)).astype(np.float32)
+    mask = np.tanh(rng.standard_normal((P, mask_dim))).astype(np.float32)
+    proto = np.maximum(rng.standard_normal((proto_hw, proto_hw, mask_dim)), 0).astype(np.float32)
+    return loc, conf, mask, proto
+
+
+def paste_inputs(n, seed, M=28, img_w=IMG_W, img_h=IMG_H):
+    """Mask probabilities (smoothed) and fractional boxes (SURVEY.md 8(d) cfg 5)."""
+    rng = np.random.default_rng(seed)
+    raw = rng.normal(0, 2.0, (n, M + 2, M + 2))
+    sm = sum(raw[:, dy:dy + M, dx:dx + M] for dy in range(3) for dx in range(3)) / 9.0
+    masks = (1.0 / (1.0 + np.exp(-sm))).astype(np.float32)
+    b = proposals(n, seed + 17, img_w, img_h, smin=24.0, smax=600.0, adversarial=False)
+    b = b + rng.uniform(0, 1, b.shape).astype(np.float32) * 0.9
+    if n >= 8:
+        b[-4:] = np.array([[-30.5, -20.25, 100.75, 90.5], [700.2, 400.1, 700.9, 400.6],
+                           [0, 0, img_w - 1, img_h - 1], [1300.5, 780.5, 1400.0, 850.0]], np.float32)
+    return masks, b.astype(np.float32)

@@ -1,0 +1,78 @@
+"""CPU checks of the drop-in boundary: the C-ABI library builds for sm_100a, loads without a
+GPU, exports exactly the symbols include/roipath.h declares, and the host layer refuses to
+run without CUDA tensors (no CPU fallback)."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+import roipath_b200 as rp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "roipath.h")
+
+
+def _declared():
+    text = open(HEADER).read()
+    return sorted(set(re.findall(r"^RP_API\s+\w+\s+(rp_\w+)\s*\(", text, flags=re.M)))
+
+
+def test_header_declares_the_whole_path():
+    names = _declared()
+    for must in ("rp_roi_align_forward", "rp_roi_align_backward", "rp_pooler_forward",
+                 "rp_pooler_backward", "rp_level_map", "rp_nms_batched", "rp_fast_nms_batched",
+                 "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    L = rp.lib()
+    path = rp.package._lib.LIB_PATH
+    out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (rp_\w+)", out))
+    assert exported == set(_declared())
+    assert set(rp.package._lib.SIGNATURES) == set(_declared())
+    assert L.rp_version() == 1
+    assert L.rp_built_for_sm() == 100
+
+
+def test_library_holds_sm100a_code_and_tma_bulk_store():
+    path = rp.package._lib.LIB_PATH
+    out = subprocess.run(["cuobjdump", "-lelf", path], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+    sass = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True).stdout
+    assert "UBLKCP" in sass  # cp.async.bulk shared->global in the ROIAlign forward kernel
+
+
+def test_argument_errors_need_no_gpu():
+    L = rp.lib()
+    # null pointers / bad sizes are rejected before any CUDA call
+    assert L.rp_roi_align_forward(None, 1, 1, 4, 4, None, 3, 7, 7, 1.0, 2.0, None, 0, None) == -1
+    assert L.rp_nms_batched(None, None, None, None, 0, 0, 0, 0.5, -1, 0, None, None, None, 0, None) == -1
+    assert L.rp_mask_assemble(None, None, None, None, 1, 5, 138, 138, 32, 550, 550, 1, None, None,
+                              None, None) == -1
+    assert L.rp_paste_masks(None, None, 3, 28, 800, 1333, 0.5, 1, None, None) == -1
+    assert L.rp_nms_workspace_bytes(160000, 20000, 8) > 8 * 20000 * 313 * 8
+    assert L.rp_fast_nms_workspace_bytes(500, 500, 1, 80, 200) > 0
+
+
+def test_no_cpu_fallback():
+    x = torch.zeros(1, 4, 8, 8)
+    rois = torch.tensor([[0, 0, 0, 4, 4.0]])
+    with pytest.raises(rp.RoiPathError):
+        rp.roi_align(x, rois, (7, 7), 1.0, 2)
+    with pytest.raises(rp.RoiPathError):
+        rp.nms(torch.zeros(3, 4), torch.zeros(3), 0.5)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "instancesegmentation-jittor_b200")
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(root, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+                assert "libroipath_oracle" not in text and "roipath_oracle.c" not in text, f
