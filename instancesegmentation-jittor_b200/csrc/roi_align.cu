@@ -41,78 +41,127 @@ struct RtLevels {
   int L;
 };
 
-// ------------------------------------------------------------------------------------------
-// forward functors
-// ------------------------------------------------------------------------------------------
-template <int U>
-struct FwdRowLoader {  // phase 1: tile row r of U channels at this thread's column
-  const float* base;   // &feat[b][c0+q][lo0y][lo0x + x]
-  size_t cstride;      // nq * H * W
-  int W;
-  int nvalid;
-  __device__ __forceinline__ void operator()(int r, float (&v)[U]) const {
-    const float* p = base + (size_t)r * W;
-#pragma unroll
-    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? __ldg(p + (size_t)u * cstride) : 0.f;
-  }
-};
-
-template <int U>
-struct FwdVSink {  // phase 1: V[c][bin][x]
-  float* base;     // &Vs[(q*PH)*twp + x]
-  int bstride;     // twp
-  int cstride;     // nq * PH * twp
-  int nvalid;
-  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
-    float* p = base + bin * bstride;
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (u < nvalid) p[u * cstride] = acc[u];
-  }
-};
-
-template <int U>
-struct FwdVLoader {  // phase 2: V[c][ph][r]
-  const float* base; // &Vs[(q*PH + ph)*twp]
-  int cstride;
-  int nvalid;
-  __device__ __forceinline__ void operator()(int r, float (&v)[U]) const {
-#pragma unroll
-    for (int u = 0; u < U; ++u) v[u] = (u < nvalid) ? base[u * cstride + r] : 0.f;
-  }
-};
-
-template <int U>
-struct FwdOutSink {  // phase 2: out tile [c][ph][bin]
-  float* base;       // &out_s[(q*PH + ph)*PW]
-  int cstride;       // nq * PH * PW
-  int nvalid;
-  float inv;         // exact 1/count or 0
-  float count;
-  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (u < nvalid) base[u * cstride + bin] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
-  }
-};
-
 __device__ __forceinline__ void rt_zero_fill(float* dst, size_t n) {
   for (size_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = 0.f;
 }
 
 // ------------------------------------------------------------------------------------------
-// forward kernel
+// forward kernel (v2): cp.async-staged raw tile, one thread per (output column, U channels)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RT_THREADS)
+// Per RoI the CTA builds a y-plan in shared memory: one float4 per y-sample
+//   (w_lo, w_hi, rows to advance before this sample, -) ,
+// every thread keeps the x taps of ITS output column in registers.  For each chunk of channels
+//   stage    the RoI's feature tile [cc][R][twa] is copied global -> shared with cp.async
+//            (16-byte copies when the map's rows are 16-byte aligned, 4-byte otherwise)
+//   compute  thread (pw, U channels) walks the tile rows once, top to bottom: per row it forms
+//            the horizontally interpolated value T(row) of its column (2*G taps), and the
+//            y-samples consume the rolling pair (T(row), T(row+1)); a finished bin is scaled
+//            and written straight to global memory (lanes = consecutive pw: 4*PW-byte runs).
+constexpr int RT2_THREADS = 256;
+constexpr int RT2_GMAX = 4;      // x taps kept in registers up to this sampling grid
+constexpr int RT2_CC_CAP = 64;   // channels per chunk upper bound
+
+__device__ __forceinline__ void rt_cp_async16(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void rt_cp_async4(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void rt_cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+// Copy rows [0, nrows) x [0, ncol) elements of EB bytes: row r of channel c starts at
+// gsrc + c*g_cstride + r*g_rstride (elements of 4 bytes), lands at sdst + c*s_cstride + r*s_rstride.
+// Lanes are packed (row-in-group, column) so that narrow tiles still use every lane.
+template <int VEC>
+__device__ __forceinline__ void rt_stage_tile(float* sdst, const float* gsrc, int cc, int R,
+                                              int ncol, size_t g_cstride, int g_rstride,
+                                              int s_cstride, int s_rstride) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int rows_per_iter = ncol >= 32 ? 1 : 32 / ncol;
+  const int lrow = ncol >= 32 ? 0 : lane / ncol;
+  const int lcol = ncol >= 32 ? lane : lane - lrow * ncol;
+  const bool lane_on = ncol >= 32 ? true : (lrow < rows_per_iter);
+  const int total = cc * R;
+  const int step = nwarps * rows_per_iter;
+  int row = warp * rows_per_iter + lrow;  // flat (c, y)
+  int c = row / R, y = row - c * R;
+  const int step_c = step / R, step_y = step - step_c * R;
+  for (; row < total; row += step) {
+    if (lane_on) {
+      const float* g = gsrc + (size_t)c * g_cstride + (size_t)y * g_rstride;
+      float* s = sdst + c * s_cstride + y * s_rstride;
+      for (int q = lcol; q < ncol; q += 32) {
+        if (VEC == 4)
+          rt_cp_async16(s + q * 4, g + q * 4);
+        else
+          rt_cp_async4(s + q, g + q);
+      }
+    }
+    c += step_c;
+    y += step_y;
+    if (y >= R) {
+      y -= R;
+      ++c;
+    }
+  }
+}
+
+// global sink of a finished bin: out[c][bin][pw], streaming store
+template <int U>
+struct FwdGlobalSink {
+  float* optr;     // &out[k][c0 + q][0][pw]
+  size_t cstride;  // nq * PH * PW
+  int PW, nvalid;
+  float inv, count;
+  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) {
+        const float v = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+        __stcs(optr + (size_t)u * cstride + bin * PW, v);
+      }
+  }
+};
+
+template <int G, int U>
+__device__ __forceinline__ void rt_fwd_compute(const float* __restrict__ tile,
+                                               const RtYSample* __restrict__ ytab,
+                                               const RtW* __restrict__ xw_s,
+                                               const short* __restrict__ xo_s, int S, int gy,
+                                               int gx, int R, int twa, int chp, int cc, int PH,
+                                               int PW, float inv, float count,
+                                               float* __restrict__ out_c0) {
+  // items: (channel group q, pw); channels of a group: q + u*nq
+  const int nq = (cc + U - 1) / U;
+  const int items = nq * PW;
+  const int P = PH * PW;
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {
+    const int q = it / PW;
+    const int pw = it - q * PW;
+    int nvalid = (cc - q + nq - 1) / nq;
+    if (nvalid > U) nvalid = U;
+    FwdGlobalSink<U> sink{out_c0 + (size_t)q * P + pw, (size_t)nq * P, PW, nvalid, inv, count};
+    rt_fwd_item<G, U>(tile, ytab, xw_s, xo_s, S, gy, gx, R, twa, chp, q, nq, nvalid, pw, sink);
+  }
+}
+
+template <int U>
+__global__ void __launch_bounds__(RT2_THREADS)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int vs_floats, int use_bulk) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
-  RtAxisPlan* py = reinterpret_cast<RtAxisPlan*>(rt_smem);
-  RtAxisPlan* px = py + 1;
-  float* Vs = reinterpret_cast<float*>(rt_smem + ((2 * sizeof(RtAxisPlan) + 15) / 16) * 16);
-  float* out_s = Vs + vs_floats;
-  __shared__ int s_ok[2];
+  // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | ylo[RT_SMAX] | tile[tile_floats]
+  RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
+  RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
+  short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
+  short* ylo_s = xo_s + RT_SMAX;
+  float* tile = reinterpret_cast<float*>(ylo_s + RT_SMAX);
+  __shared__ int s_ext[4];  // y: min lo, max hi ; x: min lo, max hi
 
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
@@ -132,25 +181,58 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const size_t HW = (size_t)H * W;
   const float* feat_b = lv.feat[level] + ((size_t)b * C + c_begin) * HW;
   const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+  const int SY = PH * g.gh, SX = PW * g.gw;
+  const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0;
 
-  if (tid == 0) s_ok[0] = rt_build_axis_plan(py, g.sh, g.bh, PH, g.gh, H);
-  if (tid == 32) s_ok[1] = rt_build_axis_plan(px, g.sw, g.bw, PW, g.gw, W);
+  // ---- plans: taps of every y- and x-sample in parallel, extents by shared atomics ----------
+  if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
   __syncthreads();
-
-  const int tiled = s_ok[0] && s_ok[1];
-  const int R = py->n, tw = px->n;
-  if (tiled && (R == 0 || tw == 0)) {  // no sample inside the map: the reference writes 0
+  if (fits) {
+    for (int s = tid; s < SY + SX; s += RT2_THREADS) {
+      const bool isy = s < SY;
+      const int t = isy ? s : s - SY;
+      const int grid = isy ? g.gh : g.gw;
+      const int p = t / grid, i = t - p * grid;
+      int lo = 0, hi = 0;
+      float wlo = 0.f, whi = 0.f;
+      const int ok = isy ? rt_axis_tap(g.sh, g.bh, p, i, grid, H, &lo, &hi, &wlo, &whi)
+                         : rt_axis_tap(g.sw, g.bw, p, i, grid, W, &lo, &hi, &wlo, &whi);
+      if (ok) {
+        atomicMin(&s_ext[isy ? 0 : 2], lo);
+        atomicMax(&s_ext[isy ? 1 : 3], hi);
+      }
+      if (isy) {
+        ytab[t].wlo = wlo;
+        ytab[t].whi = whi;
+        ylo_s[t] = ok ? (short)lo : (short)-1;
+      } else {
+        xw_s[t].lo = wlo;
+        xw_s[t].hi = whi;
+        xo_s[t] = ok ? (short)lo : (short)-1;
+      }
+    }
+  }
+  __syncthreads();
+  const int y0 = s_ext[0], y1 = s_ext[1], x0 = s_ext[2], x1 = s_ext[3];
+  const bool empty = fits && (y1 < 0 || x1 < 0);  // no sample inside the map on some axis
+  if (empty) {
     rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
     return;
   }
-  const int twp = tw | 1;  // odd row pitch: phase-2 lanes (stride twp) hit distinct banks
-  int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
-  if (cc_max > RT_CC_CAP) cc_max = RT_CC_CAP;
-  cc_max &= ~3;
-  if (cc_max < 4) {
-    // RoI too large for the tile buffers: reference-order evaluation straight from global.
+  const int R = y1 - y0 + 1, tw = x1 - x0 + 1;
+  // 16-byte staging needs 16-byte aligned rows: W % 4 == 0 and an aligned base pointer
+  const bool vec = ((W & 3) == 0) && ((reinterpret_cast<uintptr_t>(lv.feat[level]) & 15) == 0);
+  const int xa0 = vec ? (x0 & ~3) : x0;
+  const int ncol = vec ? (((x1 >> 2) - (xa0 >> 2)) + 1) : tw;  // 16-byte or 4-byte columns
+  const int twa = vec ? ncol * 4 : (tw + 1);  // +1: the hi tap of a clamped sample reads x+1
+  const int chp = R * twa + (vec ? 4 : 1);    // channel pitch (the slack keeps x+1 in bounds)
+  int cc_max = fits ? tile_floats / chp : 0;
+  if (cc_max > RT2_CC_CAP) cc_max = RT2_CC_CAP;
+  if (cc_max >= U) cc_max = cc_max / U * U;
+  if (cc_max < 1 || R > 4096) {
+    // RoI too large for the tile buffer: reference-order evaluation straight from global.
     const int total = (c_end - c_begin) * P;
-    for (int i = tid; i < total; i += RT_THREADS) {
+    for (int i = tid; i < total; i += RT2_THREADS) {
       const int c = i / P;
       const int rem = i - c * P;
       const int ph = rem / PW, pw = rem - ph * PW;
@@ -158,61 +240,44 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     return;
   }
+  // finish the plans: y advance counts (serial over <= RT_SMAX samples), x offsets in the tile
+  if (tid == 0) rt_finish_yplan(ytab, ylo_s, SY, y0);
+  for (int t = tid; t < SX; t += RT2_THREADS) {
+    const int lo = xo_s[t];
+    xo_s[t] = (short)(lo >= 0 ? lo - xa0 : 0);
+  }
+  // cells the staging never writes but a zero-weight "x+1" tap may read: keep them finite
+  if (vec) {
+    for (int i = tid; i < cc_max * 4; i += RT2_THREADS) tile[(i >> 2) * chp + R * twa + (i & 3)] = 0.f;
+  } else {
+    for (int i = tid; i < cc_max * R; i += RT2_THREADS) {
+      const int c = i / R, y = i - c * R;
+      tile[c * chp + y * twa + tw] = 0.f;
+    }
+    for (int c = tid; c < cc_max; c += RT2_THREADS) tile[c * chp + R * twa] = 0.f;
+  }
+  __syncthreads();
 
   const int count = g.gh * g.gw;
   const float inv = rt_exact_inv(count);
-  const float* tile0 = feat_b + (size_t)py->lo0 * W + px->lo0;
-  bool bulk_pending = false;
+  const float* src0 = feat_b + (size_t)y0 * W + xa0;
 
   for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
     const int cc = min(cc_max, c_end - c_begin - c0);
-    // ---- phase 1: rows, from global -------------------------------------------------------
-    {
-      const int nq = (cc + RT_U1 - 1) / RT_U1;
-      const int items = nq * tw;
-      for (int it = tid; it < items; it += RT_THREADS) {
-        const int q = it / tw;
-        const int x = it - q * tw;
-        int nvalid = (cc - q + nq - 1) / nq;  // number of u with q + u*nq < cc
-        if (nvalid > RT_U1) nvalid = RT_U1;
-        FwdRowLoader<RT_U1> ld{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid};
-        FwdVSink<RT_U1> sink{Vs + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
-        rt_sweep_fwd<RT_U1, RT_D1>(*py, ld, sink);
-      }
-    }
-    if (bulk_pending && tid == 0) rp_bulk_wait_read();  // out_s is about to be rewritten
+    if (vec)
+      rt_stage_tile<4>(tile, src0 + (size_t)c0 * HW, cc, R, ncol, HW, W, chp, twa);
+    else
+      rt_stage_tile<1>(tile, src0 + (size_t)c0 * HW, cc, R, ncol, HW, W, chp, twa);
+    rt_cp_async_wait_all();
     __syncthreads();
-    // ---- phase 2: columns, from shared ----------------------------------------------------
-    {
-      const int nq = (cc + RT_U2 - 1) / RT_U2;
-      const int items = nq * PH;
-      for (int it = tid; it < items; it += RT_THREADS) {
-        const int q = it / PH;
-        const int ph = it - q * PH;
-        int nvalid = (cc - q + nq - 1) / nq;
-        if (nvalid > RT_U2) nvalid = RT_U2;
-        FwdVLoader<RT_U2> ld{Vs + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
-        FwdOutSink<RT_U2> sink{out_s + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid, inv,
-                               (float)count};
-        rt_sweep_fwd<RT_U2, RT_D2>(*px, ld, sink);
-      }
+    float* out_c0 = out_k + (size_t)c0 * P;
+    switch (g.gw <= RT2_GMAX ? g.gw : 0) {
+      case 1: rt_fwd_compute<1, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+      case 2: rt_fwd_compute<2, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+      default: rt_fwd_compute<0, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
     }
-    // ---- store: the chunk is contiguous in global memory ----------------------------------
-    float* dst = out_k + (size_t)c0 * P;
-    const int nfl = cc * P;
-    const bool bulk = use_bulk && ((nfl & 3) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
-    if (bulk) {
-      rp_fence_proxy_async_smem();
-      __syncthreads();
-      if (tid == 0) rp_bulk_store(dst, out_s, (uint32_t)nfl * 4u);
-      bulk_pending = true;
-    } else {
-      __syncthreads();
-      for (int i = tid; i < nfl; i += RT_THREADS) dst[i] = out_s[i];
-      bulk_pending = false;
-    }
+    __syncthreads();  // the tile is overwritten by the next chunk
   }
-  if (bulk_pending && tid == 0) rp_bulk_wait_all();
 }
 
 // mode 1: one thread per output element, reference operand order (bit-exact vs the oracle).
@@ -465,18 +530,22 @@ __global__ void rt_level_map_area_kernel(const float* __restrict__ rois,
 // host side
 // ------------------------------------------------------------------------------------------
 struct RtLaunch {
-  int csplit, c_per_cta, vs_floats;
-  size_t smem;
+  int csplit, c_per_cta, vs_floats, tile_floats, U;
+  size_t smem, smem_fwd;
 };
 
 RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   RtLaunch l;
-  // V buffer: enough for RT_CC_CAP channels of a 27-wide tile at 14 bins; tunable for ncu runs.
-  l.vs_floats = rp_env_int("RP_ROI_VS_FLOATS", 8192);
+  // backward: H buffer, enough for RT_CC_CAP channels of a 27-wide tile at 14 bins
+  l.vs_floats = rp_env_int("RP_ROI_VS_FLOATS", 8192) & ~3;
   const int min_vs = PH * 3 * 4;  // at least 4 channels of a 2-wide tile
   if (l.vs_floats < min_vs) l.vs_floats = min_vs;
-  // enough CTAs for ~4 waves of 3 resident CTAs per SM; otherwise one CTA per RoI
-  const int want = 4 * 3 * RP_NUM_SMS;
+  // forward: raw feature tile buffer (48 KB => 4 resident CTAs per SM)
+  l.tile_floats = rp_env_int("RP_ROI_TILE_FLOATS", 12288) & ~3;
+  if (l.tile_floats < 256) l.tile_floats = 256;
+  l.U = rp_env_int("RP_ROI_U", 2);
+  // enough CTAs for ~3 waves of 4 resident CTAs per SM; otherwise one CTA per RoI
+  const int want = 3 * 4 * RP_NUM_SMS;
   int csplit = 1;
   if (K < want) csplit = (want + K - 1) / K;
   const int max_split = (C + 31) / 32;
@@ -488,7 +557,22 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   l.csplit = (C + cpc - 1) / cpc;
   l.smem = rp_align_up(2 * sizeof(RtAxisPlan), 16) + sizeof(float) * (size_t)l.vs_floats +
            sizeof(float) * (size_t)RT_CC_CAP * PH * PW;
+  l.smem_fwd = sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + 2 * sizeof(short) * RT_SMAX +
+               sizeof(float) * (size_t)l.tile_floats;
   return l;
+}
+
+template <int U>
+int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
+                  const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
+                  cudaStream_t st) {
+  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_fwd_kernel<U>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l.smem_fwd));
+  dim3 grid((unsigned)K, (unsigned)l.csplit);
+  rt_pool_fwd_kernel<U><<<grid, RT2_THREADS, l.smem_fwd, st>>>(
+      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
 }
 
 int rt_fill_levels(RtLevels* lv, const float* const* feats, float* const* grads, const int* H,
@@ -534,16 +618,12 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   if (mode != 0) return RP_E_ARG;
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
-  if (l.smem > 227 * 1024) return RP_E_LIMIT;
-  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)l.smem));
-  const int use_bulk = rp_env_int("RP_ROI_BULK_STORE", 1);
-  dim3 grid((unsigned)K, (unsigned)l.csplit);
-  rt_pool_fwd_kernel<<<grid, RT_THREADS, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
-                                                       sampling_ratio, out, l.c_per_cta,
-                                                       l.vs_floats, use_bulk);
-  RP_LAUNCH_CHECK();
-  return RP_OK;
+  if (l.smem_fwd > 227 * 1024) return RP_E_LIMIT;
+  switch (l.U) {
+    case 1: return rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
+    case 4: return rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
+    default: return rt_launch_fwd<2>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
+  }
 }
 
 int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K,

@@ -273,6 +273,114 @@ RT_HD void rt_sweep_bwd(const RtAxisPlan& p, Source& src, Emit& emit) {
   }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Forward, v2: column walk over a raw tile held in shared memory.
+ * y-plan: one entry per y-sample: weights of the (row, row+1) pair and the number of tile rows
+ * to advance before the sample (monotone => the tile is walked once, top to bottom).
+ * ------------------------------------------------------------------------------------------ */
+struct __attribute__((aligned(16))) RtYSample {
+  float wlo, whi;
+  int adv;
+  int pad;
+};
+
+/* Finish a y-plan serially: ylo[s] = lo row of sample s (or -1 when out of range), y0 = the
+ * smallest lo.  (The kernel fills wlo/whi/ylo in parallel and calls this on one thread.) */
+RT_HD void rt_finish_yplan(RtYSample* ytab, const short* ylo, int S, int y0) {
+  int cur = 0;
+  for (int s = 0; s < S; ++s) {
+    const int lo = ylo[s];
+    int adv = 0;
+    if (lo >= 0) {
+      adv = (lo - y0) - cur;
+      cur = lo - y0;
+    }
+    ytab[s].adv = adv;
+  }
+}
+
+/* One item = (output column pw, U channels q + u*nq) of one channel chunk.
+ *   tile [cc][R rows][twa] with channel pitch chp; xw/xo: weights and tile-relative lo column
+ *   of the x-samples (pw*gx + i); the hi tap is column lo+1 (weight 0 where it was clamped).
+ *   sink(bin, acc) receives each finished output bin (unscaled sum over the gy*gx samples). */
+template <int G, int U, class Sink>
+RT_HD void rt_fwd_item(const float* tile, const RtYSample* ytab, const RtW* xw, const short* xo_t,
+                       int S, int gy, int gx, int R, int twa, int chp, int q, int nq, int nvalid,
+                       int pw, Sink& sink) {
+  float hx[G > 0 ? G : 1], lx[G > 0 ? G : 1];
+  int xo[G > 0 ? G : 1];
+  if (G > 0) {
+#pragma unroll
+    for (int i = 0; i < G; ++i) {
+      const RtW w = xw[pw * G + i];
+      hx[i] = w.lo;
+      lx[i] = w.hi;
+      xo[i] = xo_t[pw * G + i];
+    }
+  }
+  const float* base[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) base[u] = tile + (u < nvalid ? (q + u * nq) : q) * chp;
+
+  auto rowT = [&](int row, float(&T)[U]) {
+    if (row < R) {
+      const int ro = row * twa;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float* p = base[u] + ro;
+        float t = 0.f;
+        if (G > 0) {
+#pragma unroll
+          for (int i = 0; i < G; ++i) {
+            t = fmaf(hx[i], p[xo[i]], t);
+            t = fmaf(lx[i], p[xo[i] + 1], t);
+          }
+        } else {
+          for (int i = 0; i < gx; ++i) {
+            const RtW w = xw[pw * gx + i];
+            const int o = xo_t[pw * gx + i];
+            t = fmaf(w.lo, p[o], t);
+            t = fmaf(w.hi, p[o + 1], t);
+          }
+        }
+        T[u] = t;
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) T[u] = 0.f;
+    }
+  };
+
+  float Tlo[U], Thi[U], acc[U];
+  rowT(0, Tlo);
+  rowT(1, Thi);
+#pragma unroll
+  for (int u = 0; u < U; ++u) acc[u] = 0.f;
+  int row = 0, cnt = 0, bin = 0;
+  for (int s = 0; s < S; ++s) {
+    const RtYSample e = ytab[s];
+    if (e.adv == 1) {
+      ++row;
+#pragma unroll
+      for (int u = 0; u < U; ++u) Tlo[u] = Thi[u];
+      rowT(row + 1, Thi);
+    } else if (e.adv > 1) {
+      row += e.adv;
+      rowT(row, Tlo);
+      rowT(row + 1, Thi);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) acc[u] = fmaf(e.whi, Thi[u], fmaf(e.wlo, Tlo[u], acc[u]));
+    if (++cnt == gy) {
+      sink(bin, acc);
+#pragma unroll
+      for (int u = 0; u < U; ++u) acc[u] = 0.f;
+      cnt = 0;
+      ++bin;
+    }
+  }
+}
+
 /* 1/count when that is exact (count a power of two), else 0 => divide. */
 RT_HD float rt_exact_inv(int count) {
   return (count > 0 && (count & (count - 1)) == 0) ? 1.0f / (float)count : 0.0f;

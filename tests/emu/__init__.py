@@ -36,8 +36,8 @@ def _levels_args(arrs, scales):
     return L, ptr, Hs, Ws, sc
 
 
-def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, vs_floats=8192,
-                   c_per_cta=None):
+def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, vs_floats=12288,
+                   c_per_cta=None, U=2):
     feats = [np.ascontiguousarray(f, np.float32) for f in feats]
     rois = np.ascontiguousarray(rois, np.float32)
     L, ptr, Hs, Ws, sc = _levels_args(feats, scales)
@@ -51,7 +51,7 @@ def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, vs_
         lv = levels.ctypes.data_as(_i32p)
     nd = lib().emu_pooler_forward(ptr, Hs, Ws, sc, L, N, C, rois.ctypes.data_as(_f32p), lv, K, PH,
                                   PW, ctypes.c_float(sampling_ratio), out.ctypes.data_as(_f32p),
-                                  int(vs_floats), int(c_per_cta or C))
+                                  int(vs_floats), int(c_per_cta or C), int(U))
     return out, nd
 
 

@@ -8,6 +8,7 @@
 // instancesegmentation-jittor_b200/csrc/roi_align.cu line for line.
 #include <algorithm>
 #include <cstdint>
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -93,16 +94,46 @@ struct GradEmit {
 };
 }  // namespace
 
-extern "C" {
+template <int U>
+struct EmuOutSink {
+  float* optr;
+  size_t cstride;
+  int PW, nvalid;
+  float inv, count;
+  void operator()(int bin, const float (&acc)[U]) const {
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) optr[(size_t)u * cstride + bin * PW] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+  }
+};
+
+template <int G, int U>
+static void emu_fwd_compute(const float* tile, const RtYSample* ytab, const RtW* xw,
+                            const short* xo, int S, int gy, int gx, int R, int twa, int chp, int cc,
+                            int PH, int PW, float inv, float count, float* out_c0) {
+  const int nq = (cc + U - 1) / U, items = nq * PW, P = PH * PW;
+  for (int it = 0; it < items; ++it) {
+    const int q = it / PW, pw = it - q * PW;
+    int nvalid = (cc - q + nq - 1) / nq;
+    if (nvalid > U) nvalid = U;
+    EmuOutSink<U> sink{out_c0 + (size_t)q * P + pw, (size_t)nq * P, PW, nvalid, inv, count};
+    rt_fwd_item<G, U>(tile, ytab, xw, xo, S, gy, gx, R, twa, chp, q, nq, nvalid, pw, sink);
+  }
+}
 
 // levels == NULL: single level.  feats/H/W/scales are arrays of length L.
-__attribute__((visibility("default"))) int emu_pooler_forward(
-    const float* const* feats, const int* Hs, const int* Ws, const float* scales, int L, int N,
-    int C, const float* rois, const int* levels, int K, int PH, int PW, float sampling_ratio,
-    float* out, int vs_floats, int c_per_cta) {
+// Mirrors rt_pool_fwd_kernel<U> (v2): vs_floats = tile buffer size in floats.
+template <int U>
+static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const int* Ws,
+                                const float* scales, int L, int N, int C, const float* rois,
+                                const int* levels, int K, int PH, int PW, float sampling_ratio,
+                                float* out, int tile_floats, int c_per_cta) {
   const int P = PH * PW;
+  const int CC_CAP = 64;
   int n_direct = 0;
-  std::vector<float> Vs(vs_floats), out_s((size_t)CC_CAP * P);
+  std::vector<float> tile(tile_floats);
+  std::vector<RtYSample> ytab(RT_SMAX);
+  std::vector<RtW> xw(RT_SMAX);
+  std::vector<short> xo(RT_SMAX), ylo(RT_SMAX);
   for (int k = 0; k < K; ++k) {
     for (int c_begin = 0; c_begin < C; c_begin += c_per_cta) {
       const int c_end = std::min(C, c_begin + c_per_cta);
@@ -118,20 +149,49 @@ __attribute__((visibility("default"))) int emu_pooler_forward(
       const size_t HW = (size_t)H * W;
       const float* feat_b = feats[level] + ((size_t)b * C + c_begin) * HW;
       const RtGeom g = rt_geom_fwd(roi, scales[level], sampling_ratio, PH, PW);
-      RtAxisPlan py, px;
-      const int ok0 = rt_build_axis_plan(&py, g.sh, g.bh, PH, g.gh, H);
-      const int ok1 = rt_build_axis_plan(&px, g.sw, g.bw, PW, g.gw, W);
-      const int tiled = ok0 && ok1;
-      const int R = py.n, tw = px.n;
-      if (tiled && (R == 0 || tw == 0)) {
+      const int SY = PH * g.gh, SX = PW * g.gw;
+      const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0;
+      int ext[4] = {0x7fffffff, -1, 0x7fffffff, -1};
+      if (fits) {
+        for (int s = 0; s < SY + SX; ++s) {
+          const bool isy = s < SY;
+          const int t = isy ? s : s - SY;
+          const int grid = isy ? g.gh : g.gw;
+          const int p = t / grid, i = t - p * grid;
+          int lo = 0, hi = 0;
+          float wlo = 0.f, whi = 0.f;
+          const int ok = isy ? rt_axis_tap(g.sh, g.bh, p, i, grid, H, &lo, &hi, &wlo, &whi)
+                             : rt_axis_tap(g.sw, g.bw, p, i, grid, W, &lo, &hi, &wlo, &whi);
+          if (ok) {
+            ext[isy ? 0 : 2] = std::min(ext[isy ? 0 : 2], lo);
+            ext[isy ? 1 : 3] = std::max(ext[isy ? 1 : 3], hi);
+          }
+          if (isy) {
+            ytab[t].wlo = wlo;
+            ytab[t].whi = whi;
+            ylo[t] = ok ? (short)lo : (short)-1;
+          } else {
+            xw[t].lo = wlo;
+            xw[t].hi = whi;
+            xo[t] = ok ? (short)lo : (short)-1;
+          }
+        }
+      }
+      const int y0 = ext[0], y1 = ext[1], x0 = ext[2], x1 = ext[3];
+      if (fits && (y1 < 0 || x1 < 0)) {
         std::fill(out_k, out_k + (size_t)(c_end - c_begin) * P, 0.f);
         continue;
       }
-      const int twp = tw | 1;
-      int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
+      const int R = y1 - y0 + 1, tw = x1 - x0 + 1;
+      const bool vec = (W & 3) == 0;
+      const int xa0 = vec ? (x0 & ~3) : x0;
+      const int ncol = vec ? (((x1 >> 2) - (xa0 >> 2)) + 1) : tw;
+      const int twa = vec ? ncol * 4 : (tw + 1);
+      const int chp = R * twa + (vec ? 4 : 1);
+      int cc_max = fits ? tile_floats / chp : 0;
       if (cc_max > CC_CAP) cc_max = CC_CAP;
-      cc_max &= ~3;
-      if (cc_max < 4) {
+      if (cc_max >= U) cc_max = cc_max / U * U;
+      if (cc_max < 1 || R > 4096) {
         ++n_direct;
         const int total = (c_end - c_begin) * P;
         for (int i = 0; i < total; ++i) {
@@ -140,42 +200,49 @@ __attribute__((visibility("default"))) int emu_pooler_forward(
         }
         continue;
       }
+      rt_finish_yplan(ytab.data(), ylo.data(), SY, y0);
+      for (int t = 0; t < SX; ++t) xo[t] = (short)(xo[t] >= 0 ? xo[t] - xa0 : 0);
+      std::fill(tile.begin(), tile.end(), NAN);  // poison: anything read must have been written
+      if (vec) {
+        for (int i = 0; i < cc_max * 4; ++i) tile[(i >> 2) * chp + R * twa + (i & 3)] = 0.f;
+      } else {
+        for (int i = 0; i < cc_max * R; ++i) tile[(i / R) * chp + (i % R) * twa + tw] = 0.f;
+        for (int c = 0; c < cc_max; ++c) tile[c * chp + R * twa] = 0.f;
+      }
       const int count = g.gh * g.gw;
       const float inv = rt_exact_inv(count);
-      const float* tile0 = feat_b + (size_t)py.lo0 * W + px.lo0;
+      const float* src0 = feat_b + (size_t)y0 * W + xa0;
+      const int ncol_el = vec ? ncol * 4 : ncol;
       for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
         const int cc = std::min(cc_max, c_end - c_begin - c0);
-        std::fill(Vs.begin(), Vs.end(), 1e30f);  // poison: unwritten V must never be read
-        {
-          const int nq = (cc + U1 - 1) / U1, items = nq * tw;
-          for (int it = 0; it < items; ++it) {
-            const int q = it / tw, x = it - q * tw;
-            int nvalid = (cc - q + nq - 1) / nq;
-            if (nvalid > U1) nvalid = U1;
-            RowLoader<U1> ld{tile0 + (size_t)(c0 + q) * HW + x, (size_t)nq * HW, W, nvalid};
-            VSink<U1> sink{Vs.data() + (size_t)q * PH * twp + x, twp, nq * PH * twp, nvalid};
-            rt_sweep_fwd<U1, D1>(py, ld, sink);
-          }
+        for (int c = 0; c < cc; ++c)
+          for (int y = 0; y < R; ++y)
+            std::memcpy(&tile[c * chp + y * twa], src0 + (size_t)(c0 + c) * HW + (size_t)y * W,
+                        sizeof(float) * ncol_el);
+        float* out_c0 = out_k + (size_t)c0 * P;
+        switch (g.gw <= 4 ? g.gw : 0) {
+          case 1: emu_fwd_compute<1, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+          case 2: emu_fwd_compute<2, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+          default: emu_fwd_compute<0, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
         }
-        std::fill(out_s.begin(), out_s.end(), 1e30f);
-        {
-          const int nq = (cc + U2 - 1) / U2, items = nq * PH;
-          for (int it = 0; it < items; ++it) {
-            const int q = it / PH, ph = it - q * PH;
-            int nvalid = (cc - q + nq - 1) / nq;
-            if (nvalid > U2) nvalid = U2;
-            VLoader<U2> ld{Vs.data() + (size_t)(q * PH + ph) * twp, nq * PH * twp, nvalid};
-            OutSink<U2> sink{out_s.data() + (size_t)(q * PH + ph) * PW, nq * PH * PW, nvalid, inv,
-                             (float)count};
-            rt_sweep_fwd<U2, D2>(px, ld, sink);
-          }
-        }
-        std::memcpy(out_k + (size_t)c0 * P, out_s.data(), sizeof(float) * (size_t)cc * P);
       }
     }
   }
   return n_direct;
 }
+
+extern "C" __attribute__((visibility("default"))) int emu_pooler_forward(
+    const float* const* feats, const int* Hs, const int* Ws, const float* scales, int L, int N,
+    int C, const float* rois, const int* levels, int K, int PH, int PW, float sampling_ratio,
+    float* out, int tile_floats, int c_per_cta, int U) {
+  switch (U) {
+    case 1: return emu_pooler_forward_t<1>(feats, Hs, Ws, scales, L, N, C, rois, levels, K, PH, PW, sampling_ratio, out, tile_floats, c_per_cta);
+    case 4: return emu_pooler_forward_t<4>(feats, Hs, Ws, scales, L, N, C, rois, levels, K, PH, PW, sampling_ratio, out, tile_floats, c_per_cta);
+    default: return emu_pooler_forward_t<2>(feats, Hs, Ws, scales, L, N, C, rois, levels, K, PH, PW, sampling_ratio, out, tile_floats, c_per_cta);
+  }
+}
+
+extern "C" {
 
 // grads[l] must be zero-filled by the caller.
 __attribute__((visibility("default"))) int emu_pooler_backward(

@@ -39,12 +39,12 @@ def test_library_exports_every_declared_symbol():
     assert L.rp_built_for_sm() == 100
 
 
-def test_library_holds_sm100a_code_and_tma_bulk_store():
+def test_library_holds_sm100a_code_and_async_copies():
     path = rp.package._lib.LIB_PATH
     out = subprocess.run(["cuobjdump", "-lelf", path], capture_output=True, text=True).stdout
     assert "sm_100a" in out
     sass = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True).stdout
-    assert "UBLKCP" in sass  # cp.async.bulk shared->global in the ROIAlign forward kernel
+    assert "LDGSTS" in sass  # cp.async global->shared tile staging in the ROIAlign forward kernel
 
 
 def test_argument_errors_need_no_gpu():
