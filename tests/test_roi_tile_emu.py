@@ -44,7 +44,7 @@ def test_direct_path_is_bit_exact():
     feat = rng.standard_normal((1, 8, 50, 84)).astype(np.float32)
     rois = _rois(rng, 40, 1)
     a = oracle.roi_align_forward(feat, rois, (7, 7), 1 / 16, 2)
-    b, nd = emu.pooler_forward([feat], [1 / 16], rois, None, (7, 7), 2, vs_floats=8, c_per_cta=8)
+    b, nd = emu.pooler_forward([feat], [1 / 16], rois, None, (7, 7), 2, vs_floats=2, c_per_cta=8)
     assert nd == 40 - 1  # everything but the RoI that lies entirely outside the map
     np.testing.assert_array_equal(a, b)
 
