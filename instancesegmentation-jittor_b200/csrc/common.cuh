@@ -59,5 +59,40 @@ __device__ __forceinline__ void rp_bulk_wait_all() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// ---- mbarrier + TMA 1-D bulk load global -> shared (SASS: UBLKCP) -------------------------
+__device__ __forceinline__ void rp_mbar_init(uint64_t* bar, uint32_t arrivals) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rp_smem_addr(bar)), "r"(arrivals)
+               : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// One arrival that also announces `bytes` of asynchronous copies to wait for in this phase.
+__device__ __forceinline__ void rp_mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rp_smem_addr(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void rp_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "RP_MBAR_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra RP_MBAR_DONE;\n"
+      "bra RP_MBAR_WAIT;\n"
+      "RP_MBAR_DONE:\n"
+      "}\n" ::"r"(rp_smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+// dst / src 16-byte aligned, bytes a multiple of 16; completion is counted on `bar`.
+__device__ __forceinline__ void rp_bulk_load(void* sdst, const void* gsrc, uint32_t bytes,
+                                             uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          rp_smem_addr(sdst)),
+      "l"(gsrc), "r"(bytes), "r"(rp_smem_addr(bar))
+      : "memory");
+}
+
 // Streaming (evict-first) stores for write-once outputs.
 __device__ __forceinline__ void rp_st_cs_u32(uint32_t* p, uint32_t v) { __stcs(p, v); }

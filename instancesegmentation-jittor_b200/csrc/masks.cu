@@ -171,6 +171,73 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
   }
 }
 
+// Fallback for resize ratios whose per-tile prototype footprint does not fit shared memory
+// (down-sampling, which Yolact only meets for images smaller than the 138x138 prototypes):
+// one thread per 4 output pixels, the four low-resolution taps of each pixel recomputed from
+// global memory.  Same operations per mask bit as the tiled kernel => same bits.
+__device__ __forceinline__ float ma_low_value(const float* __restrict__ proto_b,
+                                              const float* __restrict__ cf, int y, int x, int pw,
+                                              int D, int crop, float cx1, float cx2, float cy1,
+                                              float cy2) {
+  const bool in = !crop || (((float)x >= cx1) && ((float)x < cx2) && ((float)y >= cy1) &&
+                            ((float)y < cy2));
+  if (!in) return 0.f;
+  const float* p = proto_b + ((size_t)y * pw + x) * D;
+  float acc = 0.f;
+  for (int k = 0; k < D; ++k) acc = fmaf(__ldg(p + k), __ldg(cf + k), acc);
+  return rp_sigmoidf(acc);
+}
+
+__global__ void __launch_bounds__(256)
+mask_assemble_direct_kernel(const float* __restrict__ proto, const float* __restrict__ coeff,
+                            const float* __restrict__ boxes, const int* __restrict__ det_offsets,
+                            int B, int m_total, int ph, int pw, int D, int out_h, int out_w,
+                            int crop, uint8_t* __restrict__ out_masks) {
+  const int groups = (out_w + 3) >> 2;
+  const size_t per_det = (size_t)groups * out_h;
+  const size_t total = per_det * m_total;
+  const float sy = (float)ph / (float)out_h, sx = (float)pw / (float)out_w;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i / per_det);
+    const size_t rem = i - (size_t)j * per_det;
+    const int Y = (int)(rem / groups);
+    const int X = (int)(rem - (size_t)Y * groups) * 4;
+    int b = 0;
+    if (det_offsets) {
+      int lo = 0, hi = B - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (det_offsets[mid] <= j)
+          lo = mid;
+        else
+          hi = mid - 1;
+      }
+      b = lo;
+    }
+    const float* proto_b = proto + (size_t)b * ph * pw * D;
+    const float* cf = coeff + (size_t)j * D;
+    const float* bxj = boxes + (size_t)j * 4;
+    float cx1, cx2, cy1, cy2;
+    mk_sanitize(bxj[0], bxj[2], pw, 1, &cx1, &cx2);
+    mk_sanitize(bxj[1], bxj[3], ph, 1, &cy1, &cy2);
+    const MkTap yt = mk_tap(Y, sy, ph);
+    uint32_t packed = 0;
+    for (int q = 0; q < 4 && X + q < out_w; ++q) {
+      const MkTap xt = mk_tap(X + q, sx, pw);
+      const float v00 = ma_low_value(proto_b, cf, yt.i0, xt.i0, pw, D, crop, cx1, cx2, cy1, cy2);
+      const float v01 = ma_low_value(proto_b, cf, yt.i0, xt.i1, pw, D, crop, cx1, cx2, cy1, cy2);
+      const float v10 = ma_low_value(proto_b, cf, yt.i1, xt.i0, pw, D, crop, cx1, cx2, cy1, cy2);
+      const float v11 = ma_low_value(proto_b, cf, yt.i1, xt.i1, pw, D, crop, cx1, cx2, cy1, cy2);
+      const float top = xt.w0 * v00 + xt.w1 * v01;
+      const float bot = xt.w0 * v10 + xt.w1 * v11;
+      const float val = yt.w0 * top + yt.w1 * bot;
+      if (val > 0.5f) packed |= (1u << (8 * q));
+    }
+    mk_store4(out_masks + ((size_t)j * out_h + Y) * out_w + X, packed, out_w - X);
+  }
+}
+
 // boxes -> absolute int32 (yol/layers/output_utils.py:99-101) and optional low-res output
 __global__ void mask_boxes_kernel(const float* __restrict__ boxes, int m, int out_h, int out_w,
                                   int32_t* __restrict__ out_boxes) {
@@ -335,17 +402,25 @@ int rp_mask_assemble(const float* proto, const float* coeff, const float* boxes,
   if (fc > pw) fc = pw;
   const size_t pix = (size_t)fr * fc;
   const size_t smem = sizeof(float) * ((size_t)D * (pix | 1) + ((pix + 3) & ~(size_t)3) + MA_DMAX);
-  if (smem > 200 * 1024) return RP_E_LIMIT;  // extreme down-sampling ratios are out of scope
-  if (smem > 48 * 1024)
-    RP_CUDA_TRY(cudaFuncSetAttribute(mask_assemble_kernel,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int tiles_x = (out_w + MA_TW - 1) / MA_TW, tiles_y = (out_h + MA_TH - 1) / MA_TH;
   if (B > 65535) return RP_E_LIMIT;
-  dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)B);
-  mask_assemble_kernel<<<grid, MA_THREADS, smem, st>>>(proto, coeff, boxes, det_offsets, m_total,
-                                                       ph, pw, D, out_h, out_w, crop, tiles_x, fr,
-                                                       fc, out_masks);
-  RP_LAUNCH_CHECK();
+  if (smem > 200 * 1024) {
+    const size_t total = (size_t)((out_w + 3) >> 2) * out_h * m_total;
+    size_t blocks = (total + 255) / 256;
+    if (blocks > (size_t)RP_NUM_SMS * 64) blocks = (size_t)RP_NUM_SMS * 64;
+    mask_assemble_direct_kernel<<<(unsigned)blocks, 256, 0, st>>>(
+        proto, coeff, boxes, det_offsets, B, m_total, ph, pw, D, out_h, out_w, crop, out_masks);
+    RP_LAUNCH_CHECK();
+  } else {
+    if (smem > 48 * 1024)
+      RP_CUDA_TRY(cudaFuncSetAttribute(mask_assemble_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int tiles_x = (out_w + MA_TW - 1) / MA_TW, tiles_y = (out_h + MA_TH - 1) / MA_TH;
+    dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)B);
+    mask_assemble_kernel<<<grid, MA_THREADS, smem, st>>>(proto, coeff, boxes, det_offsets, m_total,
+                                                         ph, pw, D, out_h, out_w, crop, tiles_x,
+                                                         fr, fc, out_masks);
+    RP_LAUNCH_CHECK();
+  }
   if (out_boxes) {
     mask_boxes_kernel<<<(m_total + 127) / 128, 128, 0, st>>>(boxes, m_total, out_h, out_w,
                                                              out_boxes);

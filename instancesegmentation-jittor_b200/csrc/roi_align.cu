@@ -46,135 +46,84 @@ __device__ __forceinline__ void rt_zero_fill(float* dst, size_t n) {
 }
 
 // ------------------------------------------------------------------------------------------
-// forward kernel (v2): cp.async-staged raw tile, one thread per (output column, U channels)
+// forward kernel (v3): TMA-staged raw tile, one thread per (output column, U channels, segment)
 // ------------------------------------------------------------------------------------------
-// Per RoI the CTA builds a y-plan in shared memory: one float4 per y-sample
-//   (w_lo, w_hi, rows to advance before this sample, -) ,
-// every thread keeps the x taps of ITS output column in registers.  For each chunk of channels
-//   stage    the RoI's feature tile [cc][R][twa] is copied global -> shared with cp.async
-//            (16-byte copies when the map's rows are 16-byte aligned, 4-byte otherwise)
-//   compute  thread (pw, U channels) walks the tile rows once, top to bottom: per row it forms
-//            the horizontally interpolated value T(row) of its column (2*G taps), and the
-//            y-samples consume the rolling pair (T(row), T(row+1)); a finished bin is scaled
-//            and written straight to global memory (lanes = consecutive pw: 4*PW-byte runs).
-constexpr int RT2_THREADS = 256;
-constexpr int RT2_GMAX = 4;      // x taps kept in registers up to this sampling grid
-constexpr int RT2_CC_CAP = 64;   // channels per chunk upper bound
+// Per RoI the CTA builds, in parallel, the y-sample table (weights + tile row, one 16-byte
+// entry per sample) and the x-sample table in shared memory.  Then, per chunk of channels:
+//   stage    the RoI's feature tile [cc][R][twa] goes global -> shared.  When the map's rows
+//            are 16-byte aligned every tile row is ONE TMA bulk copy (cp.async.bulk, SASS
+//            UBLKCP) whose completion is counted on an mbarrier; otherwise 4-byte cp.async.
+//   compute  roi_tile.h rt_fwd_item: thread (pw, U channels, segment of output rows) walks the
+//            tile rows once; finished bins are scaled and streamed to global memory
+//            (lanes = consecutive pw: 4*PW-byte runs per channel).
+// The CTA has PW * gpb compute threads (gpb a power of two), so the item count per chunk,
+// gpb = ncg channel groups x nseg segments, always fills the CTA: a large tile (few channels
+// fit) is cut into more segments instead of idling threads.
+constexpr int RT3_MAX_THREADS = 256;
 
-__device__ __forceinline__ void rt_cp_async16(void* sdst, const void* gsrc) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
-               : "memory");
-}
 __device__ __forceinline__ void rt_cp_async4(void* sdst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void rt_cp_async8(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
                : "memory");
 }
 __device__ __forceinline__ void rt_cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
-
-// Copy rows [0, nrows) x [0, ncol) elements of EB bytes: row r of channel c starts at
-// gsrc + c*g_cstride + r*g_rstride (elements of 4 bytes), lands at sdst + c*s_cstride + r*s_rstride.
-// Lanes are packed (row-in-group, column) so that narrow tiles still use every lane.
-template <int VEC>
-__device__ __forceinline__ void rt_stage_tile(float* sdst, const float* gsrc, int cc, int R,
-                                              int ncol, size_t g_cstride, int g_rstride,
-                                              int s_cstride, int s_rstride) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int rows_per_iter = ncol >= 32 ? 1 : 32 / ncol;
-  const int lrow = ncol >= 32 ? 0 : lane / ncol;
-  const int lcol = ncol >= 32 ? lane : lane - lrow * ncol;
-  const bool lane_on = ncol >= 32 ? true : (lrow < rows_per_iter);
-  const int total = cc * R;
-  const int step = nwarps * rows_per_iter;
-  int row = warp * rows_per_iter + lrow;  // flat (c, y)
-  int c = row / R, y = row - c * R;
-  const int step_c = step / R, step_y = step - step_c * R;
-  for (; row < total; row += step) {
-    if (lane_on) {
-      const float* g = gsrc + (size_t)c * g_cstride + (size_t)y * g_rstride;
-      float* s = sdst + c * s_cstride + y * s_rstride;
-      for (int q = lcol; q < ncol; q += 32) {
-        if (VEC == 4)
-          rt_cp_async16(s + q * 4, g + q * 4);
-        else
-          rt_cp_async4(s + q, g + q);
-      }
-    }
-    c += step_c;
-    y += step_y;
-    if (y >= R) {
-      y -= R;
-      ++c;
-    }
-  }
+// exact floor(j / d) for j * d < 2^32, with m = rt_magic(d)
+__device__ __forceinline__ uint32_t rt_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
+__device__ __forceinline__ uint32_t rt_div(uint32_t j, uint32_t d, uint32_t m) {
+  return d == 1 ? j : __umulhi(j, m);
 }
 
-// global sink of a finished bin: out[c][bin][pw], streaming store
+// global sink of the finished bins of one item: out[c_u][bin][pw], streaming stores
 template <int U>
 struct FwdGlobalSink {
-  float* optr;     // &out[k][c0 + q][0][pw]
-  size_t cstride;  // nq * PH * PW
+  float* optr;     // &out[k][c of channel 0][b0][pw], advanced by PW per bin
+  size_t cstride;  // ncg * PH * PW
   int PW, nvalid;
   float inv, count;
-  __device__ __forceinline__ void operator()(int bin, const float (&acc)[U]) const {
+  __device__ __forceinline__ void operator()(int, const float (&acc)[U]) {
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (u < nvalid) {
         const float v = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
-        __stcs(optr + (size_t)u * cstride + bin * PW, v);
+        __stcs(optr + (size_t)u * cstride, v);
       }
+    optr += PW;
   }
 };
 
-template <int G, int U>
-__device__ __forceinline__ void rt_fwd_compute(const float* __restrict__ tile,
-                                               const RtYSample* __restrict__ ytab,
-                                               const RtW* __restrict__ xw_s,
-                                               const short* __restrict__ xo_s, int S, int gy,
-                                               int gx, int R, int twa, int chp, int cc, int PH,
-                                               int PW, float inv, float count,
-                                               float* __restrict__ out_c0) {
-  // items: (channel group q, pw); channels of a group: q + u*nq
-  const int nq = (cc + U - 1) / U;
-  const int items = nq * PW;
-  const int P = PH * PW;
-  for (int it = threadIdx.x; it < items; it += blockDim.x) {
-    const int q = it / PW;
-    const int pw = it - q * PW;
-    int nvalid = (cc - q + nq - 1) / nq;
-    if (nvalid > U) nvalid = U;
-    FwdGlobalSink<U> sink{out_c0 + (size_t)q * P + pw, (size_t)nq * P, PW, nvalid, inv, count};
-    rt_fwd_item<G, U>(tile, ytab, xw_s, xo_s, S, gy, gx, R, twa, chp, q, nq, nvalid, pw, sink);
-  }
-}
-
 template <int U>
-__global__ void __launch_bounds__(RT2_THREADS)
+__global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
-  // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | ylo[RT_SMAX] | tile[tile_floats]
+  // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
   RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
   short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
-  short* ylo_s = xo_s + RT_SMAX;
-  float* tile = reinterpret_cast<float*>(ylo_s + RT_SMAX);
-  __shared__ int s_ext[4];  // y: min lo, max hi ; x: min lo, max hi
+  float* tile = reinterpret_cast<float*>(xo_s + RT_SMAX);
+  __shared__ int s_ext[4];  // y: min lo, max lo ; x: min lo, max lo
+  __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x;
+  const int nthreads = blockDim.x;
   const int k = blockIdx.x;
   const int c_begin = blockIdx.y * c_per_cta;
   const int c_end = min(C, c_begin + c_per_cta);
   if (c_begin >= c_end) return;
+  const int nch = c_end - c_begin;
   const int P = PH * PW;
   const float* roi = rois + (size_t)k * 5;
   const int level = levels ? levels[k] : 0;
   const int b = (int)roi[0];
   float* out_k = out + ((size_t)k * C + c_begin) * P;
   if (level < 0 || level >= lv.L || b < 0 || b >= N) {
-    rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+    rt_zero_fill(out_k, (size_t)nch * P);
     return;
   }
   const int H = lv.H[level], W = lv.W[level];
@@ -182,57 +131,58 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const float* feat_b = lv.feat[level] + ((size_t)b * C + c_begin) * HW;
   const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
   const int SY = PH * g.gh, SX = PW * g.gw;
-  const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0;
+  const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0 && H >= 2 && W >= 2;
 
-  // ---- plans: taps of every y- and x-sample in parallel, extents by shared atomics ----------
+  // ---- tables: taps of every y- and x-sample in parallel, extents by shared atomics ---------
   if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
+  if (tid == 0) rp_mbar_init(&s_bar, 1);
   __syncthreads();
   if (fits) {
-    for (int s = tid; s < SY + SX; s += RT2_THREADS) {
+    for (int s = tid; s < SY + SX; s += nthreads) {
       const bool isy = s < SY;
       const int t = isy ? s : s - SY;
       const int grid = isy ? g.gh : g.gw;
       const int p = t / grid, i = t - p * grid;
-      int lo = 0, hi = 0;
+      int lo = 0;
       float wlo = 0.f, whi = 0.f;
-      const int ok = isy ? rt_axis_tap(g.sh, g.bh, p, i, grid, H, &lo, &hi, &wlo, &whi)
-                         : rt_axis_tap(g.sw, g.bw, p, i, grid, W, &lo, &hi, &wlo, &whi);
+      const int ok = isy ? rt_axis_tap_pair(g.sh, g.bh, p, i, grid, H, &lo, &wlo, &whi)
+                         : rt_axis_tap_pair(g.sw, g.bw, p, i, grid, W, &lo, &wlo, &whi);
       if (ok) {
         atomicMin(&s_ext[isy ? 0 : 2], lo);
-        atomicMax(&s_ext[isy ? 1 : 3], hi);
+        atomicMax(&s_ext[isy ? 1 : 3], lo);
       }
       if (isy) {
         ytab[t].wlo = wlo;
         ytab[t].whi = whi;
-        ylo_s[t] = ok ? (short)lo : (short)-1;
+        ytab[t].row = lo;
       } else {
         xw_s[t].lo = wlo;
         xw_s[t].hi = whi;
-        xo_s[t] = ok ? (short)lo : (short)-1;
+        xo_s[t] = (short)lo;
       }
     }
   }
   __syncthreads();
-  const int y0 = s_ext[0], y1 = s_ext[1], x0 = s_ext[2], x1 = s_ext[3];
-  const bool empty = fits && (y1 < 0 || x1 < 0);  // no sample inside the map on some axis
-  if (empty) {
-    rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+  const int y0 = s_ext[0], yl = s_ext[1], x0 = s_ext[2], xl = s_ext[3];
+  if (fits && (yl < 0 || xl < 0)) {  // no sample inside the map on some axis
+    rt_zero_fill(out_k, (size_t)nch * P);
     return;
   }
-  const int R = y1 - y0 + 1, tw = x1 - x0 + 1;
-  // 16-byte staging needs 16-byte aligned rows: W % 4 == 0 and an aligned base pointer
-  const bool vec = ((W & 3) == 0) && ((reinterpret_cast<uintptr_t>(lv.feat[level]) & 15) == 0);
-  const int xa0 = vec ? (x0 & ~3) : x0;
-  const int ncol = vec ? (((x1 >> 2) - (xa0 >> 2)) + 1) : tw;  // 16-byte or 4-byte columns
-  const int twa = vec ? ncol * 4 : (tw + 1);  // +1: the hi tap of a clamped sample reads x+1
-  const int chp = R * twa + (vec ? 4 : 1);    // channel pitch (the slack keeps x+1 in bounds)
-  int cc_max = fits ? tile_floats / chp : 0;
-  if (cc_max > RT2_CC_CAP) cc_max = RT2_CC_CAP;
-  if (cc_max >= U) cc_max = cc_max / U * U;
-  if (cc_max < 1 || R > 4096) {
-    // RoI too large for the tile buffer: reference-order evaluation straight from global.
-    const int total = (c_end - c_begin) * P;
-    for (int i = tid; i < total; i += RT2_THREADS) {
+  const int R = yl - y0 + 2, tw = xl - x0 + 2;  // the hi tap of every sample is lo + 1
+  // staging width: TMA rows need 16-byte aligned row starts (W % 4 == 0, aligned base pointer);
+  // maps with even W are staged with 8-byte cp.async, anything else with 4-byte cp.async
+  const uintptr_t base_addr = reinterpret_cast<uintptr_t>(lv.feat[level]);
+  const int vecw = (((W & 3) == 0) && ((base_addr & 15) == 0)) ? 4
+                   : (((W & 1) == 0) && ((base_addr & 7) == 0)) ? 2 : 1;
+  const int xa0 = x0 & ~(vecw - 1);
+  const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
+  RtTilePlan tp;
+  tp.cc = 0;
+  if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, U, nch, PH);
+  if (tp.cc < 1) {
+    // RoI too large for the tile buffer (or a degenerate map): reference-order evaluation
+    const int total = nch * P;
+    for (int i = tid; i < total; i += nthreads) {
       const int c = i / P;
       const int rem = i - c * P;
       const int ph = rem / PW, pw = rem - ph * PW;
@@ -240,41 +190,86 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     return;
   }
-  // finish the plans: y advance counts (serial over <= RT_SMAX samples), x offsets in the tile
-  if (tid == 0) rt_finish_yplan(ytab, ylo_s, SY, y0);
-  for (int t = tid; t < SX; t += RT2_THREADS) {
-    const int lo = xo_s[t];
-    xo_s[t] = (short)(lo >= 0 ? lo - xa0 : 0);
-  }
-  // cells the staging never writes but a zero-weight "x+1" tap may read: keep them finite
-  if (vec) {
-    for (int i = tid; i < cc_max * 4; i += RT2_THREADS) tile[(i >> 2) * chp + R * twa + (i & 3)] = 0.f;
-  } else {
-    for (int i = tid; i < cc_max * R; i += RT2_THREADS) {
-      const int c = i / R, y = i - c * R;
-      tile[c * chp + y * twa + tw] = 0.f;
+  // tile-relative rows / columns; out-of-range samples (zero weights) park on the nearest one
+  for (int s = tid; s < SY + SX; s += nthreads) {
+    if (s < SY) {
+      const int lo = ytab[s].row;
+      ytab[s].row = lo >= 0 ? lo - y0 : (lo == -1 ? 0 : yl - y0);
+    } else {
+      const int t = s - SY;
+      const int lo = xo_s[t];
+      xo_s[t] = (short)(lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0));
     }
-    for (int c = tid; c < cc_max; c += RT2_THREADS) tile[c * chp + R * twa] = 0.f;
   }
   __syncthreads();
 
+  // ---- this thread's item: (pw, channel group cg, segment seg) -------------------------------
+  const int chp = tp.chp;
+  const bool active = tid < PW * gpb;
+  const int grp = tid / PW;
+  const int pw = tid - grp * PW;
+  const int cg = grp & (tp.ncg - 1);
+  const int seg = grp / tp.ncg;
+  const int b0 = active ? seg * PH / tp.nseg : 0;
+  const int b1 = active ? (seg + 1) * PH / tp.nseg : 0;
   const int count = g.gh * g.gw;
   const float inv = rt_exact_inv(count);
   const float* src0 = feat_b + (size_t)y0 * W + xa0;
+  const uint32_t magicR = rt_magic((uint32_t)R), magicT = rt_magic((uint32_t)twa);
+  uint32_t phase = 0;
 
-  for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
-    const int cc = min(cc_max, c_end - c_begin - c0);
-    if (vec)
-      rt_stage_tile<4>(tile, src0 + (size_t)c0 * HW, cc, R, ncol, HW, W, chp, twa);
-    else
-      rt_stage_tile<1>(tile, src0 + (size_t)c0 * HW, cc, R, ncol, HW, W, chp, twa);
-    rt_cp_async_wait_all();
-    __syncthreads();
-    float* out_c0 = out_k + (size_t)c0 * P;
-    switch (g.gw <= RT2_GMAX ? g.gw : 0) {
-      case 1: rt_fwd_compute<1, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
-      case 2: rt_fwd_compute<2, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
-      default: rt_fwd_compute<0, U>(tile, ytab, xw_s, xo_s, SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+  for (int c0 = 0; c0 < nch; c0 += tp.cc) {
+    const int cc = min(tp.cc, nch - c0);
+    const float* src = src0 + (size_t)c0 * HW;
+    const int rows = cc * R;
+    if (vecw == 4) {
+      if (tid == 0) rp_mbar_arrive_expect_tx(&s_bar, (uint32_t)(rows * twa) * 4u);
+      for (int j = tid; j < rows; j += nthreads) {
+        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
+        const int y = j - c * R;
+        rp_bulk_load(tile + c * chp + y * twa, src + (size_t)c * HW + (size_t)y * W,
+                     (uint32_t)twa * 4u, &s_bar);
+      }
+      rp_mbar_wait(&s_bar, phase);
+      phase ^= 1u;
+    } else if (vecw == 2) {
+      const int hw = twa >> 1, total = rows * hw;
+      const uint32_t magicH = rt_magic((uint32_t)hw);
+      for (int e = tid; e < total; e += nthreads) {
+        const int j = (int)rt_div((uint32_t)e, (uint32_t)hw, magicH);
+        const int x = (e - j * hw) * 2;
+        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
+        const int y = j - c * R;
+        rt_cp_async8(tile + c * chp + y * twa + x, src + (size_t)c * HW + (size_t)y * W + x);
+      }
+      rt_cp_async_wait_all();
+      __syncthreads();
+    } else {
+      const int total = rows * twa;
+      for (int e = tid; e < total; e += nthreads) {
+        const int j = (int)rt_div((uint32_t)e, (uint32_t)twa, magicT);
+        const int x = e - j * twa;
+        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
+        const int y = j - c * R;
+        rt_cp_async4(tile + c * chp + y * twa + x, src + (size_t)c * HW + (size_t)y * W + x);
+      }
+      rt_cp_async_wait_all();
+      __syncthreads();
+    }
+    if (b0 < b1) {
+      int nvalid = (cc - cg + tp.ncg - 1) / tp.ncg;
+      if (nvalid > U) nvalid = U;
+      if (nvalid > 0) {
+        FwdGlobalSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, (size_t)tp.ncg * P, PW,
+                              nvalid, inv, (float)count};
+        const float* tile_g = tile + cg * chp;
+        const int ustride = tp.ncg * chp;
+        switch (g.gw <= 2 ? g.gw : 0) {
+          case 1: rt_fwd_item<1, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
+          case 2: rt_fwd_item<2, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
+          default: rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
+        }
+      }
     }
     __syncthreads();  // the tile is overwritten by the next chunk
   }
@@ -531,6 +526,7 @@ __global__ void rt_level_map_area_kernel(const float* __restrict__ rois,
 // ------------------------------------------------------------------------------------------
 struct RtLaunch {
   int csplit, c_per_cta, vs_floats, tile_floats, U;
+  int gpb, threads_fwd;  // forward: thread groups (of PW threads) per CTA, CTA size
   size_t smem, smem_fwd;
 };
 
@@ -544,20 +540,21 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   l.tile_floats = rp_env_int("RP_ROI_TILE_FLOATS", 12288) & ~3;
   if (l.tile_floats < 256) l.tile_floats = 256;
   l.U = rp_env_int("RP_ROI_U", 2);
-  // enough CTAs for ~3 waves of 4 resident CTAs per SM; otherwise one CTA per RoI
-  const int want = 3 * 4 * RP_NUM_SMS;
-  int csplit = 1;
-  if (K < want) csplit = (want + K - 1) / K;
-  const int max_split = (C + 31) / 32;
-  if (csplit > max_split) csplit = max_split;
-  if (csplit < 1) csplit = 1;
-  int cpc = (C + csplit - 1) / csplit;
+  // forward CTA: gpb groups of PW threads, gpb the largest power of two that fits 256 threads
+  l.gpb = 1;
+  while (PW * l.gpb * 2 <= RT3_MAX_THREADS) l.gpb *= 2;
+  l.threads_fwd = (PW * l.gpb + 31) / 32 * 32;
+  // channel split: the slow grid dimension walks channel slices, so that the feature planes
+  // of one slice (C/csplit of every image) are what competes for L2 at any one time
+  int cpc = rp_env_int("RP_ROI_CPC", 64);
+  if (cpc < 4) cpc = 4;
+  if (cpc > C) cpc = C;
   cpc = (cpc + 3) & ~3;
   l.c_per_cta = cpc;
   l.csplit = (C + cpc - 1) / cpc;
   l.smem = rp_align_up(2 * sizeof(RtAxisPlan), 16) + sizeof(float) * (size_t)l.vs_floats +
            sizeof(float) * (size_t)RT_CC_CAP * PH * PW;
-  l.smem_fwd = sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + 2 * sizeof(short) * RT_SMAX +
+  l.smem_fwd = sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX +
                sizeof(float) * (size_t)l.tile_floats;
   return l;
 }
@@ -569,8 +566,8 @@ int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const flo
   RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_fwd_kernel<U>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l.smem_fwd));
   dim3 grid((unsigned)K, (unsigned)l.csplit);
-  rt_pool_fwd_kernel<U><<<grid, RT2_THREADS, l.smem_fwd, st>>>(
-      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats);
+  rt_pool_fwd_kernel<U><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
+      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }
@@ -607,7 +604,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   if (K == 0) return RP_OK;
   if (!rois || !out || N < 1 || C < 1 || K < 0 || PH < 1 || PW < 1) return RP_E_ARG;
   if ((size_t)PH * PW > 4096) return RP_E_LIMIT;
-  if (mode == 1) {
+  if (mode == 1 || (mode == 0 && PW > RT3_MAX_THREADS)) {
     const size_t total = (size_t)K * C * PH * PW;
     size_t blocks = (total + 255) / 256;
     if (blocks > (size_t)RP_NUM_SMS * 32) blocks = (size_t)RP_NUM_SMS * 32;

@@ -180,61 +180,6 @@ RT_HD int rt_build_axis_plan(RtAxisPlan* p, float start, float bin, int pooled, 
   return 1;
 }
 
-/* Forward sweep along one axis.
- *   ld(r, v)      loads tile row r (0 <= r < p.n) into v[0..U)
- *   sink(b, acc)  receives the finished bin b
- * Rows are fetched D ahead through a statically indexed register ring, so D*U loads are in
- * flight per thread; every branch depends only on the plan (uniform across the CTA). */
-template <int U, int D, class Loader, class Sink>
-RT_HD void rt_sweep_fwd(const RtAxisPlan& p, Loader& ld, Sink& sink) {
-  float v[D][U];
-  float acc[U];
-#pragma unroll
-  for (int u = 0; u < U; ++u) acc[u] = 0.f;
-  const int n = p.n;
-  const int g = p.g;
-#pragma unroll
-  for (int j = 0; j < D; ++j) {
-    if (j < n) {
-      ld(j, v[j]);
-    } else {
-#pragma unroll
-      for (int u = 0; u < U; ++u) v[j][u] = 0.f;
-    }
-  }
-  int cnt = 0, bin = 0;
-  for (int r = 0; r < n; r += D) {
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-      const int rr = r + j;
-      if (rr < n) {
-        const int jn = (j + 1) % D;
-        const uint32_t rg = p.rng[rr];
-        const int sb = (int)(rg & 0xffffu), se = (int)(rg >> 16);
-        for (int s = sb; s < se; ++s) {
-          const RtW w = p.w[s];
-#pragma unroll
-          for (int u = 0; u < U; ++u) acc[u] = fmaf(w.hi, v[jn][u], fmaf(w.lo, v[j][u], acc[u]));
-          if (++cnt == g) {
-            sink(bin, acc);
-#pragma unroll
-            for (int u = 0; u < U; ++u) acc[u] = 0.f;
-            cnt = 0;
-            ++bin;
-          }
-        }
-        const int nr = rr + D;
-        if (nr < n) {
-          ld(nr, v[j]);
-        } else {
-#pragma unroll
-          for (int u = 0; u < U; ++u) v[j][u] = 0.f;
-        }
-      }
-    }
-  }
-}
-
 /* Transposed sweep (backward): bins are read, tile rows are produced.
  *   src(b, g)     loads the gradient of bin b into g[0..U)
  *   emit(r, val)  receives the finished gradient of tile row r (each row exactly once)
@@ -274,39 +219,99 @@ RT_HD void rt_sweep_bwd(const RtAxisPlan& p, Source& src, Emit& emit) {
 }
 
 /* ------------------------------------------------------------------------------------------
- * Forward, v2: column walk over a raw tile held in shared memory.
- * y-plan: one entry per y-sample: weights of the (row, row+1) pair and the number of tile rows
- * to advance before the sample (monotone => the tile is walked once, top to bottom).
+ * Forward (v3): column walk over a raw feature tile held in shared memory.
+ *
+ * The CTA of one RoI stages the RoI's feature tile [cc channels][R rows][twa columns] and
+ * every thread owns one ITEM = (output column pw, U channels, a contiguous range of output
+ * rows [b0,b1) = "segment").  The item walks the tile rows of its segment once, top to bottom:
+ * per row it forms the horizontally interpolated value T(row) of its column (2 taps per
+ * x-sample, x taps in registers), and the y-samples consume the rolling pair
+ * (T(row), T(row+1)).  Segments exist so that RoIs with large tiles (few channels fit in
+ * shared memory) still give every thread of the CTA an item.
  * ------------------------------------------------------------------------------------------ */
+
+/* A tap pair that never reads outside [0, extent): the reference's border clamp
+ * (hi = lo = extent-1, weight of hi = 0, roi_align.py:33-45) is re-expressed on the pair
+ * (extent-2, extent-1) with weights (0, 1) -- the same value, and lo+1 is always valid.
+ * Needs extent >= 2.  Returns 0 for an out-of-range sample (zero weights, lo = -1 / -2). */
+RT_HD int rt_axis_tap_pair(float start, float bin, int p, int i, int grid, int extent, int* lo,
+                           float* wlo, float* whi) {
+  int l = 0, h = 0;
+  float a = 0.f, b = 0.f;
+  const int ok = rt_axis_tap(start, bin, p, i, grid, extent, &l, &h, &a, &b);
+  if (ok && h == l) { /* clamped at the far border: a = 1, b = 0 on (l, l) */
+    l = l - 1;
+    b = a;
+    a = 0.f;
+  }
+  if (!ok) { /* -1: before the map, -2: past it (the caller parks it on the nearest tile row) */
+    const float v = start + (float)p * bin + ((float)i + .5f) * bin / (float)grid;
+    l = (v < -1.0f) ? -1 : -2;
+  }
+  *lo = l;
+  *wlo = a;
+  *whi = b;
+  return ok;
+}
+
 struct __attribute__((aligned(16))) RtYSample {
-  float wlo, whi;
-  int adv;
+  float wlo, whi; /* weights of tile rows (row, row + 1) */
+  int row;        /* tile-relative row of the lo tap; monotone in the sample index */
   int pad;
 };
 
-/* Finish a y-plan serially: ylo[s] = lo row of sample s (or -1 when out of range), y0 = the
- * smallest lo.  (The kernel fills wlo/whi/ylo in parallel and calls this on one thread.) */
-RT_HD void rt_finish_yplan(RtYSample* ytab, const short* ylo, int S, int y0) {
-  int cur = 0;
-  for (int s = 0; s < S; ++s) {
-    const int lo = ylo[s];
-    int adv = 0;
-    if (lo >= 0) {
-      adv = (lo - y0) - cur;
-      cur = lo - y0;
-    }
-    ytab[s].adv = adv;
-  }
+/* How one RoI's work is cut into chunks and items (all CTA-uniform). */
+struct RtTilePlan {
+  int R, twa, chp; /* tile rows, row pitch (floats), channel pitch (floats) */
+  int nseg, ncg;   /* segments per column, channel groups per chunk: nseg * ncg == gpb */
+  int cc;          /* channels staged per chunk (<= ncg * U) ; 0 => direct path */
+};
+
+RT_HD int rt_pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
 }
 
-/* One item = (output column pw, U channels q + u*nq) of one channel chunk.
- *   tile [cc][R rows][twa] with channel pitch chp; xw/xo: weights and tile-relative lo column
- *   of the x-samples (pw*gx + i); the hi tap is column lo+1 (weight 0 where it was clamped).
- *   sink(bin, acc) receives each finished output bin (unscaled sum over the gy*gx samples). */
+/* gpb = thread groups per CTA (a power of two; each group = PW threads), U = channels per
+ * thread, c_cta = channels this CTA must produce, tile_floats = shared-memory tile budget. */
+RT_HD RtTilePlan rt_plan_tile(int R, int twa, int tile_floats, int gpb, int U, int c_cta, int PH) {
+  RtTilePlan t;
+  t.R = R;
+  t.twa = twa;
+  /* channel pitch: == 16 (mod 32) floats so that the 2-3 channel groups a warp spans start
+   * 16 banks apart; stays a multiple of 4 (16-byte rows) when twa is one */
+  int chp = R * twa;
+  if (twa % 4 == 0) {
+    chp += (48 - (chp & 31)) & 31;
+    if (chp > tile_floats) chp = R * twa;
+  }
+  t.chp = chp;
+  const int cc_fit = chp > 0 ? tile_floats / chp : 0;
+  if (cc_fit < 1) {
+    t.nseg = t.ncg = 1;
+    t.cc = 0;
+    return t;
+  }
+  const int seg_cap = rt_pow2_ceil(PH) < gpb ? rt_pow2_ceil(PH) : gpb;
+  const int c_need = (c_cta + U - 1) / U * U;
+  const int c_lim = cc_fit < c_need ? cc_fit : c_need;
+  int nseg = 1;
+  while (nseg < seg_cap && (gpb / nseg) * U > c_lim) nseg <<= 1;
+  t.nseg = nseg;
+  t.ncg = gpb / nseg;
+  t.cc = t.ncg * U < cc_fit ? t.ncg * U : cc_fit;
+  return t;
+}
+
+/* One item.  tile_g = tile + cg * chp (channel u of the item lives at tile_g + u * ustride,
+ * channels >= nvalid alias channel 0 and are not emitted).  xw / xo_t: weights and
+ * tile-relative lo column of the x-samples; ytab: the y-samples.  sink(bin, acc) receives the
+ * unscaled sum over the gy*gx samples of output row `bin`, for bin = b0 .. b1-1 in order. */
 template <int G, int U, class Sink>
-RT_HD void rt_fwd_item(const float* tile, const RtYSample* ytab, const RtW* xw, const short* xo_t,
-                       int S, int gy, int gx, int R, int twa, int chp, int q, int nq, int nvalid,
-                       int pw, Sink& sink) {
+RT_HD void rt_fwd_item(const float* tile_g, int ustride, int nvalid, const RtYSample* ytab,
+                       const RtW* xw, const short* xo_t, int gy, int gx, int twa, int pw, int b0,
+                       int b1, Sink& sink) {
   float hx[G > 0 ? G : 1], lx[G > 0 ? G : 1];
   int xo[G > 0 ? G : 1];
   if (G > 0) {
@@ -320,64 +325,58 @@ RT_HD void rt_fwd_item(const float* tile, const RtYSample* ytab, const RtW* xw, 
   }
   const float* base[U];
 #pragma unroll
-  for (int u = 0; u < U; ++u) base[u] = tile + (u < nvalid ? (q + u * nq) : q) * chp;
+  for (int u = 0; u < U; ++u) base[u] = tile_g + (u < nvalid ? u * ustride : 0);
 
   auto rowT = [&](int row, float(&T)[U]) {
-    if (row < R) {
-      const int ro = row * twa;
+    const int ro = row * twa;
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const float* p = base[u] + ro;
-        float t = 0.f;
-        if (G > 0) {
+    for (int u = 0; u < U; ++u) {
+      const float* p = base[u] + ro;
+      float t = 0.f;
+      if (G > 0) {
 #pragma unroll
-          for (int i = 0; i < G; ++i) {
-            t = fmaf(hx[i], p[xo[i]], t);
-            t = fmaf(lx[i], p[xo[i] + 1], t);
-          }
-        } else {
-          for (int i = 0; i < gx; ++i) {
-            const RtW w = xw[pw * gx + i];
-            const int o = xo_t[pw * gx + i];
-            t = fmaf(w.lo, p[o], t);
-            t = fmaf(w.hi, p[o + 1], t);
-          }
+        for (int i = 0; i < G; ++i) {
+          t = fmaf(hx[i], p[xo[i]], t);
+          t = fmaf(lx[i], p[xo[i] + 1], t);
         }
-        T[u] = t;
+      } else {
+        for (int i = 0; i < gx; ++i) {
+          const RtW w = xw[pw * gx + i];
+          const int o = xo_t[pw * gx + i];
+          t = fmaf(w.lo, p[o], t);
+          t = fmaf(w.hi, p[o + 1], t);
+        }
       }
-    } else {
-#pragma unroll
-      for (int u = 0; u < U; ++u) T[u] = 0.f;
+      T[u] = t;
     }
   };
 
+  if (b0 >= b1) return;
   float Tlo[U], Thi[U], acc[U];
-  rowT(0, Tlo);
-  rowT(1, Thi);
+  int s = b0 * gy;
+  int row = ytab[s].row;
+  rowT(row, Tlo);
+  rowT(row + 1, Thi);
+  for (int bin = b0; bin < b1; ++bin) {
 #pragma unroll
-  for (int u = 0; u < U; ++u) acc[u] = 0.f;
-  int row = 0, cnt = 0, bin = 0;
-  for (int s = 0; s < S; ++s) {
-    const RtYSample e = ytab[s];
-    if (e.adv == 1) {
-      ++row;
+    for (int u = 0; u < U; ++u) acc[u] = 0.f;
+    for (int i = 0; i < gy; ++i, ++s) {
+      const RtYSample e = ytab[s];
+      const int d = e.row - row;
+      if (d != 0) {
+        row = e.row;
+        if (d == 1) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) Tlo[u] = Thi[u];
-      rowT(row + 1, Thi);
-    } else if (e.adv > 1) {
-      row += e.adv;
-      rowT(row, Tlo);
-      rowT(row + 1, Thi);
+          for (int u = 0; u < U; ++u) Tlo[u] = Thi[u];
+        } else {
+          rowT(row, Tlo);
+        }
+        rowT(row + 1, Thi);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) acc[u] = fmaf(e.whi, Thi[u], fmaf(e.wlo, Tlo[u], acc[u]));
     }
-#pragma unroll
-    for (int u = 0; u < U; ++u) acc[u] = fmaf(e.whi, Thi[u], fmaf(e.wlo, Tlo[u], acc[u]));
-    if (++cnt == gy) {
-      sink(bin, acc);
-#pragma unroll
-      for (int u = 0; u < U; ++u) acc[u] = 0.f;
-      cnt = 0;
-      ++bin;
-    }
+    sink(bin, acc);
   }
 }
 

@@ -194,7 +194,7 @@ class Detect(object):
         idx = torch.cat(idx_lst)
         classes = torch.cat(cls_lst)
         sc = torch.cat(scr_lst)
-        sc, idx2 = sc.sort(0, descending=True, stable=True)
+        sc, idx2 = sc.sort(dim=0, descending=True, stable=True)
         idx2 = idx2[: self.max_num_detections]
         sc = sc[: self.max_num_detections]
         idx = idx[idx2]

@@ -100,49 +100,38 @@ struct EmuOutSink {
   size_t cstride;
   int PW, nvalid;
   float inv, count;
-  void operator()(int bin, const float (&acc)[U]) const {
+  void operator()(int, const float (&acc)[U]) {
     for (int u = 0; u < U; ++u)
-      if (u < nvalid) optr[(size_t)u * cstride + bin * PW] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+      if (u < nvalid) optr[(size_t)u * cstride] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+    optr += PW;
   }
 };
 
-template <int G, int U>
-static void emu_fwd_compute(const float* tile, const RtYSample* ytab, const RtW* xw,
-                            const short* xo, int S, int gy, int gx, int R, int twa, int chp, int cc,
-                            int PH, int PW, float inv, float count, float* out_c0) {
-  const int nq = (cc + U - 1) / U, items = nq * PW, P = PH * PW;
-  for (int it = 0; it < items; ++it) {
-    const int q = it / PW, pw = it - q * PW;
-    int nvalid = (cc - q + nq - 1) / nq;
-    if (nvalid > U) nvalid = U;
-    EmuOutSink<U> sink{out_c0 + (size_t)q * P + pw, (size_t)nq * P, PW, nvalid, inv, count};
-    rt_fwd_item<G, U>(tile, ytab, xw, xo, S, gy, gx, R, twa, chp, q, nq, nvalid, pw, sink);
-  }
-}
-
 // levels == NULL: single level.  feats/H/W/scales are arrays of length L.
-// Mirrors rt_pool_fwd_kernel<U> (v2): vs_floats = tile buffer size in floats.
+// Mirrors rt_pool_fwd_kernel<U> (v3); the CTA's threads run serially.
 template <int U>
 static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const int* Ws,
                                 const float* scales, int L, int N, int C, const float* rois,
                                 const int* levels, int K, int PH, int PW, float sampling_ratio,
                                 float* out, int tile_floats, int c_per_cta) {
   const int P = PH * PW;
-  const int CC_CAP = 64;
   int n_direct = 0;
+  int gpb = 1;
+  while (PW * gpb * 2 <= 256) gpb *= 2;
   std::vector<float> tile(tile_floats);
   std::vector<RtYSample> ytab(RT_SMAX);
   std::vector<RtW> xw(RT_SMAX);
-  std::vector<short> xo(RT_SMAX), ylo(RT_SMAX);
+  std::vector<short> xo(RT_SMAX);
   for (int k = 0; k < K; ++k) {
     for (int c_begin = 0; c_begin < C; c_begin += c_per_cta) {
       const int c_end = std::min(C, c_begin + c_per_cta);
+      const int nch = c_end - c_begin;
       const float* roi = rois + (size_t)k * 5;
       const int level = levels ? levels[k] : 0;
       const int b = (int)roi[0];
       float* out_k = out + ((size_t)k * C + c_begin) * P;
       if (level < 0 || level >= L || b < 0 || b >= N) {
-        std::fill(out_k, out_k + (size_t)(c_end - c_begin) * P, 0.f);
+        std::fill(out_k, out_k + (size_t)nch * P, 0.f);
         continue;
       }
       const int H = Hs[level], W = Ws[level];
@@ -150,7 +139,7 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
       const float* feat_b = feats[level] + ((size_t)b * C + c_begin) * HW;
       const RtGeom g = rt_geom_fwd(roi, scales[level], sampling_ratio, PH, PW);
       const int SY = PH * g.gh, SX = PW * g.gw;
-      const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0;
+      const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0 && H >= 2 && W >= 2;
       int ext[4] = {0x7fffffff, -1, 0x7fffffff, -1};
       if (fits) {
         for (int s = 0; s < SY + SX; ++s) {
@@ -158,72 +147,84 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
           const int t = isy ? s : s - SY;
           const int grid = isy ? g.gh : g.gw;
           const int p = t / grid, i = t - p * grid;
-          int lo = 0, hi = 0;
+          int lo = 0;
           float wlo = 0.f, whi = 0.f;
-          const int ok = isy ? rt_axis_tap(g.sh, g.bh, p, i, grid, H, &lo, &hi, &wlo, &whi)
-                             : rt_axis_tap(g.sw, g.bw, p, i, grid, W, &lo, &hi, &wlo, &whi);
+          const int ok = isy ? rt_axis_tap_pair(g.sh, g.bh, p, i, grid, H, &lo, &wlo, &whi)
+                             : rt_axis_tap_pair(g.sw, g.bw, p, i, grid, W, &lo, &wlo, &whi);
           if (ok) {
             ext[isy ? 0 : 2] = std::min(ext[isy ? 0 : 2], lo);
-            ext[isy ? 1 : 3] = std::max(ext[isy ? 1 : 3], hi);
+            ext[isy ? 1 : 3] = std::max(ext[isy ? 1 : 3], lo);
           }
           if (isy) {
             ytab[t].wlo = wlo;
             ytab[t].whi = whi;
-            ylo[t] = ok ? (short)lo : (short)-1;
+            ytab[t].row = lo;
           } else {
             xw[t].lo = wlo;
             xw[t].hi = whi;
-            xo[t] = ok ? (short)lo : (short)-1;
+            xo[t] = (short)lo;
           }
         }
       }
-      const int y0 = ext[0], y1 = ext[1], x0 = ext[2], x1 = ext[3];
-      if (fits && (y1 < 0 || x1 < 0)) {
-        std::fill(out_k, out_k + (size_t)(c_end - c_begin) * P, 0.f);
+      const int y0 = ext[0], yl = ext[1], x0 = ext[2], xl = ext[3];
+      if (fits && (yl < 0 || xl < 0)) {
+        std::fill(out_k, out_k + (size_t)nch * P, 0.f);
         continue;
       }
-      const int R = y1 - y0 + 1, tw = x1 - x0 + 1;
-      const bool vec = (W & 3) == 0;
-      const int xa0 = vec ? (x0 & ~3) : x0;
-      const int ncol = vec ? (((x1 >> 2) - (xa0 >> 2)) + 1) : tw;
-      const int twa = vec ? ncol * 4 : (tw + 1);
-      const int chp = R * twa + (vec ? 4 : 1);
-      int cc_max = fits ? tile_floats / chp : 0;
-      if (cc_max > CC_CAP) cc_max = CC_CAP;
-      if (cc_max >= U) cc_max = cc_max / U * U;
-      if (cc_max < 1 || R > 4096) {
+      const int R = yl - y0 + 2;
+      const int vecw = (W & 3) == 0 ? 4 : ((W & 1) == 0 ? 2 : 1);
+      const int xa0 = x0 & ~(vecw - 1);
+      const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
+      RtTilePlan tp;
+      tp.cc = 0;
+      if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, U, nch, PH);
+      if (tp.cc < 1) {
         ++n_direct;
-        const int total = (c_end - c_begin) * P;
+        const int total = nch * P;
         for (int i = 0; i < total; ++i) {
           const int c = i / P, rem = i - c * P, ph = rem / PW, pw = rem - ph * PW;
           out_k[i] = rt_direct_output(feat_b + (size_t)c * HW, H, W, g, ph, pw);
         }
         continue;
       }
-      rt_finish_yplan(ytab.data(), ylo.data(), SY, y0);
-      for (int t = 0; t < SX; ++t) xo[t] = (short)(xo[t] >= 0 ? xo[t] - xa0 : 0);
-      std::fill(tile.begin(), tile.end(), NAN);  // poison: anything read must have been written
-      if (vec) {
-        for (int i = 0; i < cc_max * 4; ++i) tile[(i >> 2) * chp + R * twa + (i & 3)] = 0.f;
-      } else {
-        for (int i = 0; i < cc_max * R; ++i) tile[(i / R) * chp + (i % R) * twa + tw] = 0.f;
-        for (int c = 0; c < cc_max; ++c) tile[c * chp + R * twa] = 0.f;
+      for (int s = 0; s < SY + SX; ++s) {
+        if (s < SY) {
+          const int lo = ytab[s].row;
+          ytab[s].row = lo >= 0 ? lo - y0 : (lo == -1 ? 0 : yl - y0);
+        } else {
+          const int t = s - SY;
+          const int lo = xo[t];
+          xo[t] = (short)(lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0));
+        }
       }
+      const int chp = tp.chp;
       const int count = g.gh * g.gw;
       const float inv = rt_exact_inv(count);
       const float* src0 = feat_b + (size_t)y0 * W + xa0;
-      const int ncol_el = vec ? ncol * 4 : ncol;
-      for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
-        const int cc = std::min(cc_max, c_end - c_begin - c0);
+      for (int c0 = 0; c0 < nch; c0 += tp.cc) {
+        const int cc = std::min(tp.cc, nch - c0);
+        std::fill(tile.begin(), tile.end(), NAN);  // poison: anything read must have been staged
         for (int c = 0; c < cc; ++c)
           for (int y = 0; y < R; ++y)
             std::memcpy(&tile[c * chp + y * twa], src0 + (size_t)(c0 + c) * HW + (size_t)y * W,
-                        sizeof(float) * ncol_el);
-        float* out_c0 = out_k + (size_t)c0 * P;
-        switch (g.gw <= 4 ? g.gw : 0) {
-          case 1: emu_fwd_compute<1, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
-          case 2: emu_fwd_compute<2, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
-          default: emu_fwd_compute<0, U>(tile.data(), ytab.data(), xw.data(), xo.data(), SY, g.gh, g.gw, R, twa, chp, cc, PH, PW, inv, (float)count, out_c0); break;
+                        sizeof(float) * twa);
+        for (int tid = 0; tid < PW * gpb; ++tid) {
+          const int grp = tid / PW, pw = tid - grp * PW;
+          const int cg = grp & (tp.ncg - 1), seg = grp / tp.ncg;
+          const int b0 = seg * PH / tp.nseg, b1 = (seg + 1) * PH / tp.nseg;
+          if (b0 >= b1) continue;
+          int nvalid = (cc - cg + tp.ncg - 1) / tp.ncg;
+          if (nvalid > U) nvalid = U;
+          if (nvalid <= 0) continue;
+          EmuOutSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, (size_t)tp.ncg * P, PW,
+                             nvalid, inv, (float)count};
+          const float* tile_g = tile.data() + cg * chp;
+          const int ustride = tp.ncg * chp;
+          switch (g.gw <= 2 ? g.gw : 0) {
+            case 1: rt_fwd_item<1, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
+            case 2: rt_fwd_item<2, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
+            default: rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
+          }
         }
       }
     }
