@@ -27,9 +27,7 @@ namespace {
 
 constexpr int RT_THREADS = 256;
 constexpr int RT_U1 = 4;  // channels per thread, phase 1
-constexpr int RT_D1 = 8;  // rows in flight per thread, phase 1
 constexpr int RT_U2 = 2;  // channels per thread, phase 2
-constexpr int RT_D2 = 4;
 constexpr int RT_CC_CAP = 32;  // max channels per chunk (bounds the out tile)
 
 struct RtLevels {
@@ -61,6 +59,10 @@ __device__ __forceinline__ void rt_zero_fill(float* dst, size_t n) {
 // fit) is cut into more segments instead of idling threads.
 constexpr int RT3_MAX_THREADS = 256;
 
+__device__ __forceinline__ void rt_cp_async16(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
+               : "memory");
+}
 __device__ __forceinline__ void rt_cp_async4(void* sdst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(rp_smem_addr(sdst)), "l"(gsrc)
                : "memory");
@@ -78,19 +80,45 @@ __device__ __forceinline__ uint32_t rt_div(uint32_t j, uint32_t d, uint32_t m) {
   return d == 1 ? j : __umulhi(j, m);
 }
 
+// Stage cc channels of a [R rows][vw columns of VEC floats] tile: warp w owns channels w, w+nw, ...
+// and its lanes walk the channel's columns row-major (coalesced row segments; one magic
+// division per copy, no per-copy channel arithmetic).  Shared rows are contiguous (pitch
+// vw * VEC), channel pitch chp.
+template <int VEC>
+__device__ __forceinline__ void rt_stage_tile(float* tile, const float* __restrict__ src, int cc,
+                                              int R, int vw, uint32_t magicV, int W, size_t HW,
+                                              int chp) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int per_ch = R * vw;
+  for (int c = warp; c < cc; c += nw) {
+    const float* g = src + (size_t)c * HW;
+    float* s = tile + c * chp;
+    for (int i = lane; i < per_ch; i += 32) {
+      const int y = (int)rt_div((uint32_t)i, (uint32_t)vw, magicV);
+      const int q = i - y * vw;
+      const float* gp = g + (y * W + q * VEC);
+      if (VEC == 4)
+        rt_cp_async16(s + i * 4, gp);
+      else if (VEC == 2)
+        rt_cp_async8(s + i * 2, gp);
+      else
+        rt_cp_async4(s + i, gp);
+    }
+  }
+}
+
 // global sink of the finished bins of one item: out[c_u][bin][pw], streaming stores
 template <int U>
 struct FwdGlobalSink {
   float* optr;     // &out[k][c of channel 0][b0][pw], advanced by PW per bin
-  size_t cstride;  // ncg * PH * PW
+  int cstride;     // ncg * PH * PW
   int PW, nvalid;
-  float inv, count;
+  float inv;  // 1 / (gy * gx): within 1 ulp of the reference's division
   __device__ __forceinline__ void operator()(int, const float (&acc)[U]) {
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (u < nvalid) {
-        const float v = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
-        __stcs(optr + (size_t)u * cstride, v);
+        __stcs(optr + u * cstride, acc[u] * inv);
       }
     optr += PW;
   }
@@ -100,7 +128,7 @@ template <int U>
 __global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
@@ -108,7 +136,6 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
   float* tile = reinterpret_cast<float*>(xo_s + RT_SMAX);
   __shared__ int s_ext[4];  // y: min lo, max lo ; x: min lo, max lo
-  __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x;
   const int nthreads = blockDim.x;
@@ -135,7 +162,6 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 
   // ---- tables: taps of every y- and x-sample in parallel, extents by shared atomics ---------
   if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
-  if (tid == 0) rp_mbar_init(&s_bar, 1);
   __syncthreads();
   if (fits) {
     for (int s = tid; s < SY + SX; s += nthreads) {
@@ -155,6 +181,7 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
         ytab[t].wlo = wlo;
         ytab[t].whi = whi;
         ytab[t].row = lo;
+        ytab[t].flags = (i == grid - 1) ? RT_F_EMIT : 0;
       } else {
         xw_s[t].lo = wlo;
         xw_s[t].hi = whi;
@@ -168,7 +195,7 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     rt_zero_fill(out_k, (size_t)nch * P);
     return;
   }
-  const int R = yl - y0 + 2, tw = xl - x0 + 2;  // the hi tap of every sample is lo + 1
+  const int R = yl - y0 + 2;  // the hi tap of every sample is lo + 1
   // staging width: TMA rows need 16-byte aligned row starts (W % 4 == 0, aligned base pointer);
   // maps with even W are staged with 8-byte cp.async, anything else with 4-byte cp.async
   const uintptr_t base_addr = reinterpret_cast<uintptr_t>(lv.feat[level]);
@@ -178,7 +205,7 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
   RtTilePlan tp;
   tp.cc = 0;
-  if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, U, nch, PH);
+  if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, gw, U, nch, PH);
   if (tp.cc < 1) {
     // RoI too large for the tile buffer (or a degenerate map): reference-order evaluation
     const int total = nch * P;
@@ -202,73 +229,53 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
   }
   __syncthreads();
+  // how the live row pair moves before each y-sample (rows are final now)
+  for (int s = tid; s < SY; s += nthreads) {
+    const int cur = ytab[s].row;
+    const int prev = s ? ytab[s - 1].row : cur;
+    ytab[s].flags = rt_ysample_flags(cur, prev, ytab[s].flags & RT_F_EMIT);
+  }
+  __syncthreads();
 
   // ---- this thread's item: (pw, channel group cg, segment seg) -------------------------------
   const int chp = tp.chp;
-  const bool active = tid < PW * gpb;
-  const int grp = tid / PW;
-  const int pw = tid - grp * PW;
+  const int grp = tid / gw;
+  const int pw = tid - grp * gw;
+  const bool active = (grp < gpb) && (pw < PW);
+  const int ncg_shift = 31 - __clz(tp.ncg);
   const int cg = grp & (tp.ncg - 1);
-  const int seg = grp / tp.ncg;
+  const int seg = grp >> ncg_shift;
   const int b0 = active ? seg * PH / tp.nseg : 0;
   const int b1 = active ? (seg + 1) * PH / tp.nseg : 0;
   const int count = g.gh * g.gw;
-  const float inv = rt_exact_inv(count);
+  const float inv = 1.0f / (float)count;
   const float* src0 = feat_b + (size_t)y0 * W + xa0;
-  const uint32_t magicR = rt_magic((uint32_t)R), magicT = rt_magic((uint32_t)twa);
-  uint32_t phase = 0;
+  const int vw = twa / vecw;  // staging columns (of vecw floats) per tile row
+  const uint32_t magicV = rt_magic((uint32_t)vw);
 
   for (int c0 = 0; c0 < nch; c0 += tp.cc) {
     const int cc = min(tp.cc, nch - c0);
     const float* src = src0 + (size_t)c0 * HW;
-    const int rows = cc * R;
-    if (vecw == 4) {
-      if (tid == 0) rp_mbar_arrive_expect_tx(&s_bar, (uint32_t)(rows * twa) * 4u);
-      for (int j = tid; j < rows; j += nthreads) {
-        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
-        const int y = j - c * R;
-        rp_bulk_load(tile + c * chp + y * twa, src + (size_t)c * HW + (size_t)y * W,
-                     (uint32_t)twa * 4u, &s_bar);
-      }
-      rp_mbar_wait(&s_bar, phase);
-      phase ^= 1u;
-    } else if (vecw == 2) {
-      const int hw = twa >> 1, total = rows * hw;
-      const uint32_t magicH = rt_magic((uint32_t)hw);
-      for (int e = tid; e < total; e += nthreads) {
-        const int j = (int)rt_div((uint32_t)e, (uint32_t)hw, magicH);
-        const int x = (e - j * hw) * 2;
-        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
-        const int y = j - c * R;
-        rt_cp_async8(tile + c * chp + y * twa + x, src + (size_t)c * HW + (size_t)y * W + x);
-      }
-      rt_cp_async_wait_all();
-      __syncthreads();
-    } else {
-      const int total = rows * twa;
-      for (int e = tid; e < total; e += nthreads) {
-        const int j = (int)rt_div((uint32_t)e, (uint32_t)twa, magicT);
-        const int x = e - j * twa;
-        const int c = (int)rt_div((uint32_t)j, (uint32_t)R, magicR);
-        const int y = j - c * R;
-        rt_cp_async4(tile + c * chp + y * twa + x, src + (size_t)c * HW + (size_t)y * W + x);
-      }
-      rt_cp_async_wait_all();
-      __syncthreads();
-    }
+    if (vecw == 4)
+      rt_stage_tile<4>(tile, src, cc, R, vw, magicV, W, HW, chp);
+    else if (vecw == 2)
+      rt_stage_tile<2>(tile, src, cc, R, vw, magicV, W, HW, chp);
+    else
+      rt_stage_tile<1>(tile, src, cc, R, vw, magicV, W, HW, chp);
+    rt_cp_async_wait_all();
+    __syncthreads();
     if (b0 < b1) {
-      int nvalid = (cc - cg + tp.ncg - 1) / tp.ncg;
+      int nvalid = (cc - cg + tp.ncg - 1) >> ncg_shift;
       if (nvalid > U) nvalid = U;
       if (nvalid > 0) {
-        FwdGlobalSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, (size_t)tp.ncg * P, PW,
-                              nvalid, inv, (float)count};
+        FwdGlobalSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW,
+                              nvalid, inv};
         const float* tile_g = tile + cg * chp;
         const int ustride = tp.ncg * chp;
-        switch (g.gw <= 2 ? g.gw : 0) {
-          case 1: rt_fwd_item<1, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
-          case 2: rt_fwd_item<2, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
-          default: rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink); break;
-        }
+        if (g.gw == 2)
+          rt_fwd_item_fsm<U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, twa, pw, b0, b1, sink);
+        else
+          rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink);
       }
     }
     __syncthreads();  // the tile is overwritten by the next chunk
@@ -526,7 +533,7 @@ __global__ void rt_level_map_area_kernel(const float* __restrict__ rois,
 // ------------------------------------------------------------------------------------------
 struct RtLaunch {
   int csplit, c_per_cta, vs_floats, tile_floats, U;
-  int gpb, threads_fwd;  // forward: thread groups (of PW threads) per CTA, CTA size
+  int gpb, gw, threads_fwd;  // forward: thread groups per CTA, lanes per group (>= PW), CTA size
   size_t smem, smem_fwd;
 };
 
@@ -540,10 +547,17 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   l.tile_floats = rp_env_int("RP_ROI_TILE_FLOATS", 12288) & ~3;
   if (l.tile_floats < 256) l.tile_floats = 256;
   l.U = rp_env_int("RP_ROI_U", 2);
-  // forward CTA: gpb groups of PW threads, gpb the largest power of two that fits 256 threads
+  // forward CTA: gpb groups of gw lanes; gw = PW rounded up to a power of two when that is < 32
+  // (whole groups per warp => the groups of a warp can be kept on disjoint banks), gpb the
+  // largest power of two that fits 256 threads
+  l.gw = PW;
+  if (PW < 32) {
+    l.gw = 1;
+    while (l.gw < PW) l.gw *= 2;
+  }
   l.gpb = 1;
-  while (PW * l.gpb * 2 <= RT3_MAX_THREADS) l.gpb *= 2;
-  l.threads_fwd = (PW * l.gpb + 31) / 32 * 32;
+  while (l.gw * l.gpb * 2 <= RT3_MAX_THREADS) l.gpb *= 2;
+  l.threads_fwd = (l.gw * l.gpb + 31) / 32 * 32;
   // channel split: the slow grid dimension walks channel slices, so that the feature planes
   // of one slice (C/csplit of every image) are what competes for L2 at any one time
   int cpc = rp_env_int("RP_ROI_CPC", 64);
@@ -567,7 +581,7 @@ int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const flo
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l.smem_fwd));
   dim3 grid((unsigned)K, (unsigned)l.csplit);
   rt_pool_fwd_kernel<U><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb);
+      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

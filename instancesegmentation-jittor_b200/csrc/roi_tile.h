@@ -257,7 +257,7 @@ RT_HD int rt_axis_tap_pair(float start, float bin, int p, int i, int grid, int e
 struct __attribute__((aligned(16))) RtYSample {
   float wlo, whi; /* weights of tile rows (row, row + 1) */
   int row;        /* tile-relative row of the lo tap; monotone in the sample index */
-  int pad;
+  int flags;      /* RT_F_EMIT on the last y-sample of an output row, RT_F_ADV / RT_F_JUMP */
 };
 
 /* How one RoI's work is cut into chunks and items (all CTA-uniform). */
@@ -273,17 +273,20 @@ RT_HD int rt_pow2_ceil(int v) {
   return p;
 }
 
-/* gpb = thread groups per CTA (a power of two; each group = PW threads), U = channels per
- * thread, c_cta = channels this CTA must produce, tile_floats = shared-memory tile budget. */
-RT_HD RtTilePlan rt_plan_tile(int R, int twa, int tile_floats, int gpb, int U, int c_cta, int PH) {
+/* gpb = thread groups per CTA (a power of two; each group = gw >= PW lanes, gw a power of two
+ * when it is < 32), U = channels per thread, c_cta = channels this CTA must produce,
+ * tile_floats = shared-memory tile budget. */
+RT_HD RtTilePlan rt_plan_tile(int R, int twa, int tile_floats, int gpb, int gw, int U, int c_cta,
+                              int PH) {
   RtTilePlan t;
   t.R = R;
   t.twa = twa;
-  /* channel pitch: == 16 (mod 32) floats so that the 2-3 channel groups a warp spans start
-   * 16 banks apart; stays a multiple of 4 (16-byte rows) when twa is one */
+  /* channel pitch == gw (mod 32) floats: the 32/gw channel groups that share a warp start gw
+   * banks apart, so their loads do not collide (exactly when the tile is <= gw wide); stays a
+   * multiple of 4 (16-byte rows) when twa is one */
   int chp = R * twa;
-  if (twa % 4 == 0) {
-    chp += (48 - (chp & 31)) & 31;
+  if (gw >= 4 && gw < 32 && (twa & 3) == 0) {
+    chp += (gw - chp) & 31;
     if (chp > tile_floats) chp = R * twa;
   }
   t.chp = chp;
@@ -378,6 +381,117 @@ RT_HD void rt_fwd_item(const float* tile_g, int ustride, int nvalid, const RtYSa
     }
     sink(bin, acc);
   }
+}
+
+/* The same item for gx == 2 (x taps in registers, any gy), written for the instruction count.
+ * Each y-sample record carries flags that say how the live row pair moves before the sample
+ * (CTA-uniform, so every branch below is uniform):
+ *   RT_F_ADV   advance by exactly one row: ONE new x-interpolated row is computed.  The two
+ *              live rows sit in two register sets whose roles alternate, so the walk is a
+ *              two-state machine (which set is the lo row) and nothing is ever moved;
+ *   RT_F_JUMP  advance by d >= 2 rows: both rows are recomputed, (d - 2) is in flags >> 8;
+ *   RT_F_EMIT  the sample is the last of its output row.
+ * Identical arithmetic, operation for operation, to rt_fwd_item<2, U>. */
+#define RT_F_ADV 1
+#define RT_F_EMIT 2
+#define RT_F_JUMP 4
+
+/* flags of sample s from its own row, the previous sample's row and the emit bit */
+RT_HD int rt_ysample_flags(int row, int prev_row, int emit) {
+  const int d = row - prev_row;
+  int f = emit ? RT_F_EMIT : 0;
+  if (d == 1) f |= RT_F_ADV;
+  if (d >= 2) f |= RT_F_JUMP | ((d - 2) << 8);
+  return f;
+}
+
+template <int U, class Sink>
+RT_HD void rt_fwd_item_fsm(const float* tile_g, int ustride, int nvalid, const RtYSample* ytab,
+                           const RtW* xw, const short* xo_t, int gy, int twa, int pw, int b0,
+                           int b1, Sink& sink) {
+  if (b0 >= b1) return;
+  const RtW w0 = xw[pw * 2], w1 = xw[pw * 2 + 1];
+  const int xo0 = xo_t[pw * 2], xo1 = xo_t[pw * 2 + 1];
+  const RtYSample* st = ytab + b0 * gy;
+  int bins_left = b1 - b0;
+  /* the first sample of a segment: its row pair is computed from scratch, flags ignored */
+  const int r0 = st->row;
+  const float* p0[U];
+  const float* p1[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const float* b = tile_g + (u < nvalid ? u * ustride : 0) + r0 * twa;
+    p0[u] = b + xo0;
+    p1[u] = b + xo1;
+  }
+  float Ta[U], Tb[U], acc[U];
+#define RT_XROW(T)                                                                              \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                               \
+    T[u] = fmaf(w1.hi, p1[u][1],                                                                \
+                fmaf(w1.lo, p1[u][0], fmaf(w0.hi, p0[u][1], fmaf(w0.lo, p0[u][0], 0.f))));      \
+    p0[u] += twa;                                                                               \
+    p1[u] += twa;                                                                               \
+  }
+#define RT_JUMP(LO, HI)                                                                         \
+  {                                                                                             \
+    const int skip = (e.flags >> 8) * twa;                                                       \
+    _Pragma("unroll") for (int u = 0; u < U; ++u) {                                             \
+      p0[u] += skip;                                                                            \
+      p1[u] += skip;                                                                            \
+    }                                                                                           \
+    RT_XROW(LO)                                                                                 \
+    RT_XROW(HI)                                                                                 \
+  }
+#define RT_YFMA(LO, HI)                                                                         \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) acc[u] =                                        \
+      fmaf(e.whi, HI[u], fmaf(e.wlo, LO[u], acc[u]));
+#define RT_EMIT()                                                                               \
+  if (e.flags & RT_F_EMIT) {                                                                     \
+    sink(0, acc);                                                                               \
+    _Pragma("unroll") for (int u = 0; u < U; ++u) acc[u] = 0.f;                                 \
+    if (--bins_left == 0) return;                                                               \
+  }
+  RT_XROW(Ta)
+  RT_XROW(Tb)
+#pragma unroll
+  for (int u = 0; u < U; ++u) acc[u] = 0.f;
+  {
+    const RtYSample e = *st++;
+    RT_YFMA(Ta, Tb)
+    RT_EMIT()
+  }
+  for (;;) {
+    /* state A: Ta = lo row, Tb = hi row */
+    for (;;) {
+      const RtYSample e = *st++;
+      if (e.flags & RT_F_ADV) {
+        RT_XROW(Ta) /* Ta becomes the new hi row */
+        RT_YFMA(Tb, Ta)
+        RT_EMIT()
+        break;
+      }
+      if (e.flags & RT_F_JUMP) RT_JUMP(Ta, Tb)
+      RT_YFMA(Ta, Tb)
+      RT_EMIT()
+    }
+    /* state B: Tb = lo row, Ta = hi row */
+    for (;;) {
+      const RtYSample e = *st++;
+      if (e.flags & RT_F_ADV) {
+        RT_XROW(Tb)
+        RT_YFMA(Ta, Tb)
+        RT_EMIT()
+        break;
+      }
+      if (e.flags & RT_F_JUMP) RT_JUMP(Tb, Ta)
+      RT_YFMA(Tb, Ta)
+      RT_EMIT()
+    }
+  }
+#undef RT_XROW
+#undef RT_JUMP
+#undef RT_YFMA
+#undef RT_EMIT
 }
 
 /* 1/count when that is exact (count a power of two), else 0 => divide. */

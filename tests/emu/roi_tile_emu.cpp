@@ -99,10 +99,10 @@ struct EmuOutSink {
   float* optr;
   size_t cstride;
   int PW, nvalid;
-  float inv, count;
+  float inv;
   void operator()(int, const float (&acc)[U]) {
     for (int u = 0; u < U; ++u)
-      if (u < nvalid) optr[(size_t)u * cstride] = (inv != 0.f) ? acc[u] * inv : acc[u] / count;
+      if (u < nvalid) optr[(size_t)u * cstride] = acc[u] * inv;
     optr += PW;
   }
 };
@@ -116,8 +116,13 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
                                 float* out, int tile_floats, int c_per_cta) {
   const int P = PH * PW;
   int n_direct = 0;
+  int gw = PW;
+  if (PW < 32) {
+    gw = 1;
+    while (gw < PW) gw *= 2;
+  }
   int gpb = 1;
-  while (PW * gpb * 2 <= 256) gpb *= 2;
+  while (gw * gpb * 2 <= 256) gpb *= 2;
   std::vector<float> tile(tile_floats);
   std::vector<RtYSample> ytab(RT_SMAX);
   std::vector<RtW> xw(RT_SMAX);
@@ -159,6 +164,7 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
             ytab[t].wlo = wlo;
             ytab[t].whi = whi;
             ytab[t].row = lo;
+            ytab[t].flags = (i == grid - 1) ? RT_F_EMIT : 0;
           } else {
             xw[t].lo = wlo;
             xw[t].hi = whi;
@@ -177,7 +183,7 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
       const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
       RtTilePlan tp;
       tp.cc = 0;
-      if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, U, nch, PH);
+      if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, gw, U, nch, PH);
       if (tp.cc < 1) {
         ++n_direct;
         const int total = nch * P;
@@ -197,9 +203,15 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
           xo[t] = (short)(lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0));
         }
       }
+      {
+        std::vector<int> fl(SY);
+        for (int s = 0; s < SY; ++s)
+          fl[s] = rt_ysample_flags(ytab[s].row, s ? ytab[s - 1].row : ytab[s].row, ytab[s].flags & RT_F_EMIT);
+        for (int s = 0; s < SY; ++s) ytab[s].flags = fl[s];
+      }
       const int chp = tp.chp;
       const int count = g.gh * g.gw;
-      const float inv = rt_exact_inv(count);
+      const float inv = 1.0f / (float)count;
       const float* src0 = feat_b + (size_t)y0 * W + xa0;
       for (int c0 = 0; c0 < nch; c0 += tp.cc) {
         const int cc = std::min(tp.cc, nch - c0);
@@ -208,8 +220,9 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
           for (int y = 0; y < R; ++y)
             std::memcpy(&tile[c * chp + y * twa], src0 + (size_t)(c0 + c) * HW + (size_t)y * W,
                         sizeof(float) * twa);
-        for (int tid = 0; tid < PW * gpb; ++tid) {
-          const int grp = tid / PW, pw = tid - grp * PW;
+        for (int tid = 0; tid < gw * gpb; ++tid) {
+          const int grp = tid / gw, pw = tid - grp * gw;
+          if (pw >= PW) continue;
           const int cg = grp & (tp.ncg - 1), seg = grp / tp.ncg;
           const int b0 = seg * PH / tp.nseg, b1 = (seg + 1) * PH / tp.nseg;
           if (b0 >= b1) continue;
@@ -217,14 +230,13 @@ static int emu_pooler_forward_t(const float* const* feats, const int* Hs, const 
           if (nvalid > U) nvalid = U;
           if (nvalid <= 0) continue;
           EmuOutSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, (size_t)tp.ncg * P, PW,
-                             nvalid, inv, (float)count};
+                             nvalid, inv};
           const float* tile_g = tile.data() + cg * chp;
           const int ustride = tp.ncg * chp;
-          switch (g.gw <= 2 ? g.gw : 0) {
-            case 1: rt_fwd_item<1, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
-            case 2: rt_fwd_item<2, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
-            default: rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink); break;
-          }
+          if (g.gw == 2)
+            rt_fwd_item_fsm<U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, twa, pw, b0, b1, sink);
+          else
+            rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab.data(), xw.data(), xo.data(), g.gh, g.gw, twa, pw, b0, b1, sink);
         }
       }
     }
