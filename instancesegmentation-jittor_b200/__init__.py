@@ -8,6 +8,7 @@ from . import _lib
 from ._lib import RoiPathError, lib
 from .layers import (ROIAlign, cython_nms, ml_nms, nms, nms_batched, roi_align,
                      roi_align_backward, roi_align_forward)
+from . import parallel
 from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_in_image,
                      paste_masks)
 from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_format,
