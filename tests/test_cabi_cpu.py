@@ -55,7 +55,9 @@ def test_argument_errors_need_no_gpu():
     assert L.rp_mask_assemble(None, None, None, None, 1, 5, 138, 138, 32, 550, 550, 1, None, None,
                               None, None) == -1
     assert L.rp_paste_masks(None, None, 3, 28, 800, 1333, 0.5, 1, None, None) == -1
-    assert L.rp_nms_workspace_bytes(160000, 20000, 8) > 8 * 20000 * 313 * 8
+    # banded NMS: the workspace is O(n), no n x n/64 bit matrix (400 MB at 8 x 20k boxes)
+    ws = L.rp_nms_workspace_bytes(160000, 20000, 8)
+    assert 160000 * 40 < ws < 64 * 1024 * 1024
     assert L.rp_fast_nms_workspace_bytes(500, 500, 1, 80, 200) > 0
 
 
