@@ -96,8 +96,10 @@ constexpr int NMS_BAND_MAX = 1024;
 template <bool GE>
 __device__ __forceinline__ bool nms_pair(const NmsBox& a, float aarea, const NmsBox& q, float qarea,
                                          float t_cmp, float t_lo) {
-  const float iw = rp_fmaxf(0.0f, (rp_fminf(a.x2, q.x2) - rp_fmaxf(a.x1, q.x1)) + 1.0f);
-  const float ih = rp_fmaxf(0.0f, (rp_fminf(a.y2, q.y2) - rp_fmaxf(a.y1, q.y1)) + 1.0f);
+  // fminf/fmaxf (one FMNMX each) instead of the oracle's compare-and-select: the two differ
+  // only in the sign of a zero result (which the +1 absorbs) and for NaN coordinates.
+  const float iw = fmaxf(0.0f, (fminf(a.x2, q.x2) - fmaxf(a.x1, q.x1)) + 1.0f);
+  const float ih = fmaxf(0.0f, (fminf(a.y2, q.y2) - fmaxf(a.y1, q.y1)) + 1.0f);
   const float inter = ih * iw;
   const float uni = (aarea + qarea) - inter;
   // exact filter: fl(inter/uni) > t (or >= t) is impossible when inter < t_lo*uni with
@@ -105,6 +107,12 @@ __device__ __forceinline__ bool nms_pair(const NmsBox& a, float aarea, const Nms
   if (inter < t_lo * uni) return false;
   const float iou = inter / uni;
   return GE ? (iou >= t_cmp) : (iou > t_cmp);
+}
+
+__device__ __forceinline__ uint64_t nms_warp_or64(uint64_t v) {
+  const uint32_t lo = __reduce_or_sync(0xffffffffu, (uint32_t)v);
+  const uint32_t hi = __reduce_or_sync(0xffffffffu, (uint32_t)(v >> 32));
+  return ((uint64_t)hi << 32) | lo;
 }
 
 struct NmsBand {
@@ -115,7 +123,6 @@ struct NmsBand {
   const int* sorted_vals;
   uint64_t* removed;      // [B][wmax]
   uint64_t* D;            // [B][BR][bw]  diagonal block of the current band (upper triangle)
-  uint64_t* DT;           // [B][BR]      per box: lower-ranked... higher-SCORED boxes of its chunk that overlap it
   NmsBox* kbox;           // [B][BR]      boxes the current band kept
   float* karea;
   float* klabel;
@@ -158,24 +165,16 @@ __device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int ban
   if (LABELS) alabel = p.slabel[off + row];
   int ncol = n - (base + cb * 64);
   ncol = ncol > 64 ? 64 : ncol;
-  uint64_t up = 0, low = 0;
+  uint64_t up = 0;
   const NmsBox* cbx = cbox + j * 64;
   const float* car = carea + j * 64;
   const float* clb = clabel + j * 64;
-  const bool diag = (cb == rb);
-  for (int c = 0; c < ncol; ++c) {
-    if (diag && c == r) continue;
+  for (int c = (cb == rb) ? r + 1 : 0; c < ncol; ++c) {  // strict upper triangle
     bool sup = nms_pair<GE>(a, aarea, cbx[c], car[c], p.t_cmp, p.t_lo);
     if (LABELS) sup = sup && (alabel == clb[c]);
-    if (sup) {
-      if (diag && c < r)
-        low |= (1ull << c);
-      else
-        up |= (1ull << c);
-    }
+    if (sup) up |= (1ull << c);
   }
   p.D[((size_t)seg * p.BR + rrow) * p.bw + cb] = up;
-  if (diag) p.DT[(size_t)seg * p.BR + rrow] = low;
 }
 
 template <bool GE, bool LABELS>
@@ -242,8 +241,7 @@ nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __rest
                    uint8_t* __restrict__ flags) {
   extern __shared__ __align__(16) uint64_t nr_smem[];
   uint64_t* Ds = nr_smem;               // [BR][bw]
-  uint64_t* DTs = Ds + p.BR * p.bw;     // [BR]
-  uint64_t* rem = DTs + p.BR;           // [bw]
+  uint64_t* rem = Ds + p.BR * p.bw;     // [bw]
   uint64_t* keptm = rem + p.bw;         // [bw]
   int* cbase = reinterpret_cast<int*>(keptm + p.bw);  // [bw + 1]
   const int seg = blockIdx.x;
@@ -258,9 +256,15 @@ nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __rest
   const int chunks = (rows + 63) >> 6;
   {
     const uint64_t* Dg = p.D + (size_t)seg * p.BR * p.bw;
-    for (int i = tid; i < rows * p.bw; i += blockDim.x) Ds[i] = Dg[i];
-    const uint64_t* DTg = p.DT + (size_t)seg * p.BR;
-    for (int i = tid; i < rows; i += blockDim.x) DTs[i] = DTg[i];
+    if ((p.bw & 1) == 0) {  // 16-byte copies (rows * bw is even, both bases 16-byte aligned)
+      const uint4* g4 = reinterpret_cast<const uint4*>(Dg);
+      uint4* s4 = reinterpret_cast<uint4*>(Ds);
+      const int n4 = (rows * p.bw) >> 1;
+#pragma unroll 8
+      for (int i = tid; i < n4; i += blockDim.x) s4[i] = g4[i];
+    } else {
+      for (int i = tid; i < rows * p.bw; i += blockDim.x) Ds[i] = Dg[i];
+    }
     if (tid < p.bw) {
       rem[tid] = p.removed[(size_t)seg * p.wmax + band * p.bw + tid];
       keptm[tid] = 0ull;
@@ -274,20 +278,22 @@ nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __rest
     for (int c = 0; c < chunks; ++c) {
       const int nrow = min(64, rows - c * 64);
       const uint64_t valid = (nrow == 64) ? ~0ull : ((1ull << nrow) - 1ull);
+      // Greedy rule as a warp-parallel fixpoint.  Lane l holds the diagonal-block rows of boxes
+      // l and l+32 (bits = the lower-scored boxes of the chunk each one overlaps).  A box is
+      // suppressed once a KEPT higher-scored box overlaps it, and kept once no undecided
+      // higher-scored box overlaps it; the lowest undecided box is always decided, and chains
+      // of overlapping boxes inside 64 ranks are short.
       uint64_t undec = ~rem[c] & valid;
       uint64_t kept = 0ull;
-      const uint64_t cm0 = (l < nrow) ? DTs[c * 64 + l] : 0ull;
-      const uint64_t cm1 = (l + 32 < nrow) ? DTs[c * 64 + 32 + l] : 0ull;
-      // parallel fixpoint of the greedy rule: a box is suppressed once a kept higher-scored
-      // box overlaps it, kept once every overlapping higher-scored box is decided and not kept
+      const uint64_t r0 = (l < nrow) ? Ds[(c * 64 + l) * p.bw + c] : 0ull;
+      const uint64_t r1 = (l + 32 < nrow) ? Ds[(c * 64 + 32 + l) * p.bw + c] : 0ull;
       while (undec) {
-        const bool u0 = (undec >> l) & 1ull, u1 = (undec >> (l + 32)) & 1ull;
-        const bool s0 = u0 && (cm0 & kept), s1 = u1 && (cm1 & kept);
-        const bool k0 = u0 && !s0 && !(cm0 & undec), k1 = u1 && !s1 && !(cm1 & undec);
-        const uint64_t nk = (uint64_t)__ballot_sync(0xffffffffu, k0) |
-                            ((uint64_t)__ballot_sync(0xffffffffu, k1) << 32);
-        const uint64_t ns = (uint64_t)__ballot_sync(0xffffffffu, s0) |
-                            ((uint64_t)__ballot_sync(0xffffffffu, s1) << 32);
+        const uint64_t ks = (((kept >> l) & 1ull) ? r0 : 0ull) | (((kept >> (l + 32)) & 1ull) ? r1 : 0ull);
+        const uint64_t us = (((undec >> l) & 1ull) ? r0 : 0ull) | (((undec >> (l + 32)) & 1ull) ? r1 : 0ull);
+        const uint64_t sup = nms_warp_or64(ks);  // overlapped by a kept box
+        const uint64_t pot = nms_warp_or64(us);  // overlapped by an undecided box
+        const uint64_t ns = undec & sup;
+        const uint64_t nk = undec & ~sup & ~pot;
         kept |= nk;
         undec &= ~(nk | ns);
       }
@@ -303,17 +309,16 @@ nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __rest
       }
       count += __popcll(kept);
       if (stop) break;
-      // removed bits of the later chunks of this band
-      const int w = c + 1 + l;
-      if (w < chunks) {
-        uint64_t acc = rem[w];
-        uint64_t k = kept;
-        while (k) {
-          const int i = __ffsll((long long)k) - 1;
-          k &= k - 1;
-          acc |= Ds[(c * 64 + i) * p.bw + w];
+      // removed bits of the later chunks of this band: OR of the kept rows, word by word
+      {
+        const bool k0 = (kept >> l) & 1ull, k1 = (kept >> (l + 32)) & 1ull;
+        const uint64_t* d0 = Ds + (c * 64 + l) * p.bw;
+        const uint64_t* d1 = Ds + (c * 64 + 32 + l) * p.bw;
+        for (int w = c + 1; w < chunks; ++w) {
+          const uint64_t v = (k0 ? d0[w] : 0ull) | (k1 ? d1[w] : 0ull);
+          const uint64_t o = nms_warp_or64(v);
+          if (l == 0) rem[w] |= o;
         }
-        rem[w] = acc;
       }
       __syncwarp();
     }
@@ -396,7 +401,7 @@ struct NmsWorkspace {
   int *count, *done, *kcount;
   char* zero_begin;
   size_t zero_bytes;
-  uint64_t *D, *DT;
+  uint64_t* D;
   NmsBox* kbox;
   float *karea, *klabel;
   int BR, bw, wmax;
@@ -443,7 +448,6 @@ NmsWorkspace nms_carve(void* base, int n_total, int n_max, int B) {
   w.zero_begin = base ? (char*)base + z0 : nullptr;
   w.zero_bytes = o - z0;
   w.D = (uint64_t*)take(nb * (size_t)w.BR * w.bw * 8);
-  w.DT = (uint64_t*)take(nb * (size_t)w.BR * 8);
   w.kbox = (NmsBox*)take(nb * (size_t)w.BR * sizeof(NmsBox));
   w.karea = (float*)take(nb * (size_t)w.BR * 4);
   w.klabel = (float*)take(nb * (size_t)w.BR * 4);
@@ -457,7 +461,7 @@ int nms_run_bands(const NmsBand& p, int B, int n_max, int max_keep, int ascendin
   const int bands = (n_max + p.BR - 1) / p.BR;
   const int groups = (p.bw + 3) / 4;
   const int ndiag = p.bw * groups;
-  const size_t smem = sizeof(uint64_t) * ((size_t)p.BR * p.bw + p.BR + 2 * (size_t)p.bw) +
+  const size_t smem = sizeof(uint64_t) * ((size_t)p.BR * p.bw + 2 * (size_t)p.bw) +
                       sizeof(int) * ((size_t)p.bw + 2);
   RP_CUDA_TRY(cudaFuncSetAttribute(nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
@@ -534,7 +538,6 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
   p.sorted_vals = w.vals_out;
   p.removed = w.removed;
   p.D = w.D;
-  p.DT = w.DT;
   p.kbox = w.kbox;
   p.karea = w.karea;
   p.klabel = w.klabel;
