@@ -124,12 +124,14 @@ struct FwdGlobalSink {
   }
 };
 
+// The v3 evaluation of one (RoI, channel slice) by the whole CTA; any CTA size that is a multiple
+// of gw.  Also the fallback of the banded kernel below for RoIs without a band form.
 template <int U>
-__global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
-rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
-                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
-  extern __shared__ __align__(16) unsigned char rt_smem[];
+__device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const RtLevels& lv, int N,
+                                                int C, const float* __restrict__ rois,
+                                                const int* __restrict__ levels, int PH, int PW,
+                                                float sampling_ratio, float* __restrict__ out,
+                                                int c_per_cta, int tile_floats, int gpb, int gw) {
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
   RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
@@ -279,6 +281,227 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
       }
     }
     __syncthreads();  // the tile is overwritten by the next chunk
+  }
+}
+
+constexpr int RT3_TABLE_BYTES =
+    sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX;
+
+template <int U>
+__global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
+rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  rt3_roi_forward<U>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
+                     tile_floats, gpb, gw);
+}
+
+// ------------------------------------------------------------------------------------------
+// forward kernel (v4, banded): see roi_tile.h "Forward (v4)".  CTA = one RoI x one channel
+// slice, RB_THREADS threads, 5 CTAs per SM.  Per chunk of cc channels:
+//   stage   the RoI's tile [cc][R rows][nq 16-byte strips] global -> shared with cp.async
+//           (issued right after the previous chunk's y-pass, so it overlaps the x-pass);
+//   y-pass  one thread per (channel, strip, segment): rb_ywalk reads the strip once and writes
+//           V[c][ph][4 columns] (16-byte shared stores);
+//   x-pass  thread = (pw, row slot): 4 shared loads + 4 FMA per output, thread t writes float t
+//           of the chunk's contiguous output block (128-byte lines per warp, streaming).
+// RoIs without a band form (bins wider than 4 feature pixels at sampling 2, adaptive sampling
+// of large RoIs, maps smaller than 4x4) are evaluated by the v3 body with the same CTA.
+// ------------------------------------------------------------------------------------------
+constexpr int RB_THREADS = 128;
+
+// Warp w stages channels w, w + nw, ...: its lanes form rpw = 32 / vpr rows of vpr staging
+// vectors (VEC floats each) and step down the tile rpw rows at a time -- one cp.async, one
+// 64-bit and one 32-bit add per copy; no division inside the loop.
+template <int VEC>
+__device__ __forceinline__ void rb_stage_tile(float* tile, const float* __restrict__ src, int cc,
+                                              int R, int nq, int W, size_t HW, int chp, int wlim) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int vpr = (4 / VEC) * nq;  // staging vectors per tile row
+  int rpw = 32 / vpr;
+  if (rpw < 1) rpw = 1;
+  const int vrow = rpw == 1 ? 0 : lane / vpr;
+  const int v0 = lane - vrow * vpr;
+  if (vrow >= rpw) return;
+  const uint32_t tile_s = rp_smem_addr(tile);
+  for (int c = warp; c < cc; c += nw) {
+    for (int v = v0; v < vpr; v += 32) {  // one trip unless the row has more than 32 vectors
+      const int col = v * VEC;
+      const float* gp = src + (size_t)c * HW + (size_t)vrow * W + col;
+      uint32_t sp = tile_s + 4u * (uint32_t)(c * chp + vrow * 4 * nq + col);
+      const size_t gstep = (size_t)rpw * W;
+      const uint32_t sstep = 16u * (uint32_t)(rpw * nq);
+      if (VEC == 4 || col < wlim) {
+        for (int y = vrow; y < R; y += rpw) {
+          if (VEC == 4)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sp), "l"(gp) : "memory");
+          else if (VEC == 2)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sp), "l"(gp) : "memory");
+          else
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sp), "l"(gp) : "memory");
+          gp += gstep;
+          sp += sstep;
+        }
+      } else {  // columns past the end of the map row: never weighted, but keep them finite
+        for (int y = vrow; y < R; y += rpw) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sp + 4u * e), "f"(0.f) : "memory");
+          sp += sstep;
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(RB_THREADS, 5)
+rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  __shared__ RbPlan plan;
+  __shared__ int s_fin[2];
+
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x;
+  const int c_begin = blockIdx.y * c_per_cta;
+  const int c_end = min(C, c_begin + c_per_cta);
+  if (c_begin >= c_end) return;
+  const int nch = c_end - c_begin;
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  float* out_k = out + ((size_t)k * C + c_begin) * P;
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) {
+    rt_zero_fill(out_k, (size_t)nch * P);
+    return;
+  }
+  const int H = lv.H[level], W = lv.W[level];
+  const size_t HW = (size_t)H * W;
+  const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+
+  // ---- band plan of the RoI (CTA-uniform) ----------------------------------------------------
+  int ok = rb_axis_candidate(g.bh, g.gh, PH, H) && rb_axis_candidate(g.bw, g.gw, PW, W);
+  if (ok) {
+    if (tid < PH)
+      ok = rb_build_bin(&plan.ay, tid, g.sh, g.bh, g.gh, H);
+    else if (tid >= 32 && tid < 32 + PW)
+      ok = rb_build_bin(&plan.ax, tid - 32, g.sw, g.bw, g.gw, W);
+  }
+  ok = __syncthreads_and(ok);
+  if (ok) {
+    if (tid == 0) s_fin[0] = rb_finish_axis(&plan.ay, PH);
+    if (tid == 32) s_fin[1] = rb_finish_axis(&plan.ax, PW);
+    __syncthreads();
+    ok = s_fin[0] && s_fin[1];
+  }
+  int cc = 0, nseg = 1, nq = 0, vp = 0, chp4 = 0, xa0 = 0, vecw = 1, R = 0, y0 = 0;
+  if (ok) {
+    y0 = plan.ay.lo0;
+    R = plan.ay.ext;
+    const int x0 = plan.ax.lo0, xe = x0 + plan.ax.ext;
+    const uintptr_t base_addr = reinterpret_cast<uintptr_t>(lv.feat[level]);
+    vecw = (((W & 3) == 0) && ((base_addr & 15) == 0)) ? 4
+           : (((W & 1) == 0) && ((base_addr & 7) == 0)) ? 2 : 1;
+    xa0 = x0 & ~(vecw - 1);
+    nq = (xe - xa0 + 3) >> 2;
+    {                                       // V row pitch: vpu 16-byte units, vpu >= nq, vpu mod 8 in
+      int vpu = nq;                         // {3, 5}: the two V rows an x-pass warp reads sit 12 or
+      while ((vpu & 7) != 3 && (vpu & 7) != 5) ++vpu;  // 20 banks apart
+      vp = 4 * vpu;
+    }
+    chp4 = R * nq + ((nq - R * nq) & 7);    // channel pitch in 16-byte units, == nq (mod 8): the
+                                            // strips of consecutive channels continue the banks
+    rb_plan_chunk(smem_floats, 4 * chp4 + PH * vp, nq, nch, PH, RB_THREADS, &cc, &nseg);
+    ok = cc >= 1;
+  }
+  if (!ok) {
+    rt3_roi_forward<2>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
+                       (smem_floats * 4 - RT3_TABLE_BYTES) / 4, gpb, gw);
+    return;
+  }
+  if (tid == 0) rb_plan_segments(&plan, PH, nseg);
+  __syncthreads();
+  {
+    const int count = g.gh * g.gw;
+    if (tid < 32) rb_plan_bin(&plan, tid, PH, PW, nseg, plan.ax.lo0 - xa0, 1.0f / (float)count);
+    const int nword = RB_MAXE / 4 + 1;
+    if (tid >= 32 && tid < 32 + nword) {
+      for (int s = 0; s < nseg; ++s)
+        if ((tid - 32) * 4 < plan.seg_rows[s] + 4) rb_plan_mword(&plan, s, tid - 32);
+    }
+  }
+  __syncthreads();
+
+  float* tile = reinterpret_cast<float*>(rt_smem);
+  const int chp = 4 * chp4;
+  float* V = tile + cc * chp;
+  const float* src0 = lv.feat[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
+  const int wlim = W - xa0;
+  // x-pass mapping: groups of xg lanes (16 when PW <= 16, so a warp holds two whole V rows)
+  const int xg = PW <= 16 ? 16 : PW;
+  const int nslots = RB_THREADS / xg;
+  const int pw = tid % xg, slot = tid / xg;
+  const bool xactive = pw < PW && slot < nslots;
+  // 3-tap x bands (every RoI narrower than 28 feature pixels): skip the 4th load
+  const int tap3 = __syncthreads_and(tid >= PW || plan.xw[tid].w == 0.f);
+  auto stage = [&](int c0, int ccur) {
+    const float* src = src0 + (size_t)c0 * HW;
+    if (vecw == 4)
+      rb_stage_tile<4>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+    else if (vecw == 2)
+      rb_stage_tile<2>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+    else
+      rb_stage_tile<1>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  stage(0, min(cc, nch));
+  for (int c0 = 0; c0 < nch; c0 += cc) {
+    const int ccur = min(cc, nch - c0);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();  // tile(c0) has landed; every thread is done with V of the previous chunk
+    // ---- y-pass ------------------------------------------------------------------------------
+    {
+      const int per_seg = ccur * nq;
+      const int total = per_seg * nseg;
+      const RbF4* tile4 = reinterpret_cast<const RbF4*>(tile);
+      for (int s = tid; s < total; s += RB_THREADS) {
+        const int seg = s >= per_seg ? 1 : 0;
+        const int rem = s - seg * per_seg;
+        const int c = rem / nq, q = rem - c * nq;
+        const int b0 = plan.seg_b0[seg];
+        rb_ywalk(tile4 + c * chp4 + plan.seg_r0[seg] * nq + q, nq, plan.seg_rows[seg], plan.mw[seg],
+                 plan.wrot + b0, V + (c * PH + b0) * vp + 4 * q, vp);
+      }
+    }
+    __syncthreads();  // V complete, tile free
+    if (c0 + cc < nch) stage(c0 + cc, min(cc, nch - c0 - cc));
+    // ---- x-pass ------------------------------------------------------------------------------
+    if (xactive) {
+      const RbF4 w = plan.xw[pw];
+      const float* v = V + slot * vp + plan.xo[pw];
+      float* o = out_k + (size_t)c0 * P + slot * PW + pw;
+      const int nrow = ccur * PH;
+      const int vstep = nslots * vp, ostep = nslots * PW;
+      if (tap3) {
+#pragma unroll 2
+        for (int r = slot; r < nrow; r += nslots) {
+          __stcs(o, fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0])));
+          v += vstep;
+          o += ostep;
+        }
+      } else {
+#pragma unroll 2
+        for (int r = slot; r < nrow; r += nslots) {
+          __stcs(o, fmaf(w.w, v[3], fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0]))));
+          v += vstep;
+          o += ostep;
+        }
+      }
+    }
   }
 }
 
@@ -629,6 +852,27 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   if (mode != 0) return RP_E_ARG;
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
+  if (rp_env_int("RP_ROI_IMPL", 3) == 4 && PW <= RB_THREADS) {
+    // banded kernel; RoIs without a band form run the v3 body inside the same CTA
+    int gw = PW, gpb = 1;
+    if (PW < 32) {
+      gw = 1;
+      while (gw < PW) gw *= 2;
+    }
+    while (gw * gpb * 2 <= RB_THREADS) gpb *= 2;
+    int kb = rp_env_int("RP_ROI_BAND_SMEM_KB", 40);
+    if (kb < 16) kb = 16;
+    if (kb > 200) kb = 200;
+    const int smem = kb * 1024;
+    RP_CUDA_TRY(cudaFuncSetAttribute(rb_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem));
+    dim3 grid((unsigned)K, (unsigned)l.csplit);
+    rb_pool_fwd_kernel<<<grid, RB_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                       sampling_ratio, out, l.c_per_cta, smem / 4,
+                                                       gpb, gw);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
   if (l.smem_fwd > 227 * 1024) return RP_E_LIMIT;
   switch (l.U) {
     case 1: return rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);

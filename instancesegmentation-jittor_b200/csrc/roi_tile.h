@@ -494,6 +494,231 @@ RT_HD void rt_fwd_item_fsm(const float* tile_g, int ustride, int nvalid, const R
 #undef RT_EMIT
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Forward (v4, "banded"): every output bin of an axis reads a BAND of at most 4 consecutive
+ * tile rows (columns).  With `grid` samples per bin spaced bin/grid apart, the lo taps of a bin
+ * span ceil((grid-1)*bin/grid) rows and every sample adds its hi tap, so the band form exists
+ * whenever (grid-1)*bin/grid <= 2 -- e.g. sampling_ratio 2 with bins up to 4 feature pixels
+ * (RoIs up to 56 pixels on their FPN level at 14 bins; the FPN level mapping keeps them below
+ * 45).  The per-sample weights of a bin are MERGED per row: out = sum_j w[j] * F[start + j],
+ * which differs from the reference's per-sample order only by reassociation (~1e-7 relative).
+ *
+ * The two passes are then
+ *   y-pass  thread = one 4-column strip of one channel: it reads its strip top to bottom ONCE
+ *           (16-byte shared loads, a 4-deep register ring: row r lives in slot r & 3) and, as
+ *           soon as row start+3 of a bin has arrived, forms V[bin][4 columns] with the bin's
+ *           weights rotated to the ring (static register names, no moves, uniform branches);
+ *   x-pass  thread = output column pw: out[ph][pw] = sum_j xw[pw][j] * V[ph][xo[pw] + j],
+ *           consecutive threads write consecutive output floats.
+ * Everything below is CTA-uniform data built once per RoI.
+ * ------------------------------------------------------------------------------------------ */
+#define RB_MAXP 32 /* pooled bins per axis */
+#define RB_MAXG 8  /* samples per bin per axis */
+#define RB_MAXE 96 /* tile rows / columns */
+#define RB_MAXSEG 2
+
+struct __attribute__((aligned(16))) RbF4 {
+  float x, y, z, w;
+};
+
+struct RbAxis {
+  int lo0; /* feature row / column of tile row / column 0 */
+  int ext; /* tile extent: last band start + 4 */
+  int start[RB_MAXP]; /* band start per bin: absolute (-1 = no sample in range) until
+                         rb_finish_axis, tile-relative afterwards; non-decreasing */
+  RbF4 w[RB_MAXP];    /* merged weights of rows start .. start+3 */
+};
+
+/* Cheap necessary condition, evaluated identically by every thread. */
+RT_HD int rb_axis_candidate(float bin, int grid, int pooled, int extent) {
+  if (grid < 1 || grid > RB_MAXG || pooled < 1 || pooled > RB_MAXP || extent < 4) return 0;
+  return (float)(grid - 1) * bin / (float)grid <= 2.0f;
+}
+
+/* One bin (independent of the other bins).  Returns 0 when the bin's taps do not fit a band. */
+RT_HD int rb_build_bin(RbAxis* a, int b, float start, float bin, int grid, int extent) {
+  int first = 0x7fffffff, last = -1;
+  for (int i = 0; i < grid; ++i) {
+    int lo, hi;
+    float wlo, whi;
+    if (rt_axis_tap(start, bin, b, i, grid, extent, &lo, &hi, &wlo, &whi)) {
+      first = lo < first ? lo : first;
+      last = hi > last ? hi : last;
+    }
+  }
+  float w0 = 0.f, w1 = 0.f, w2 = 0.f, w3 = 0.f;
+  int st = -1, ok = 1;
+  if (last >= 0) {
+    st = first <= extent - 4 ? first : extent - 4;
+    if (last - st > 3) {
+      ok = 0;
+    } else {
+      for (int i = 0; i < grid; ++i) {
+        int lo, hi;
+        float wlo, whi;
+        if (rt_axis_tap(start, bin, b, i, grid, extent, &lo, &hi, &wlo, &whi)) {
+          const int jl = lo - st, jh = hi - st;
+          w0 += (jl == 0 ? wlo : 0.f) + (jh == 0 ? whi : 0.f);
+          w1 += (jl == 1 ? wlo : 0.f) + (jh == 1 ? whi : 0.f);
+          w2 += (jl == 2 ? wlo : 0.f) + (jh == 2 ? whi : 0.f);
+          w3 += (jl == 3 ? wlo : 0.f) + (jh == 3 ? whi : 0.f);
+        }
+      }
+    }
+  }
+  a->start[b] = st;
+  a->w[b].x = w0;
+  a->w[b].y = w1;
+  a->w[b].z = w2;
+  a->w[b].w = w3;
+  return ok;
+}
+
+/* Serial pass over the bins: bins without a sample ride on a neighbour's band (zero weights),
+ * starts become tile-relative.  Returns 0 when the tile is too large. */
+RT_HD int rb_finish_axis(RbAxis* a, int n) {
+  int prev = -1;
+  for (int b = 0; b < n; ++b)
+    if (a->start[b] >= 0) {
+      prev = a->start[b];
+      break;
+    }
+  if (prev < 0) prev = 0; /* nothing in range: all weights are zero, any band will do */
+  for (int b = 0; b < n; ++b) {
+    if (a->start[b] < 0)
+      a->start[b] = prev;
+    else
+      prev = a->start[b];
+  }
+  a->lo0 = a->start[0];
+  a->ext = a->start[n - 1] + 4 - a->lo0;
+  for (int b = 0; b < n; ++b) a->start[b] -= a->lo0;
+  return a->ext <= RB_MAXE;
+}
+
+/* CTA-uniform plan of one RoI. */
+struct RbPlan {
+  RbAxis ay, ax;
+  RbF4 wrot[RB_MAXP];                     /* y weights rotated to the ring of the bin's segment */
+  RbF4 xw[RB_MAXP];                       /* x weights times 1/(gy*gx) */
+  int xo[RB_MAXP];                        /* first V column of the band of pw */
+  uint32_t mw[RB_MAXSEG][RB_MAXE / 4 + 1]; /* byte k of word i: bins completed by row 4i+k */
+  int seg_b0[RB_MAXSEG + 1];              /* bins of segment s: seg_b0[s] .. seg_b0[s+1]-1 */
+  int seg_r0[RB_MAXSEG];                  /* first tile row of the segment */
+  int seg_rows[RB_MAXSEG];                /* rows the segment walks */
+};
+
+RT_HD void rb_plan_segments(RbPlan* p, int PH, int nseg) {
+  for (int s = 0; s <= nseg; ++s) p->seg_b0[s] = s * PH / nseg;
+  for (int s = 0; s < nseg; ++s) {
+    p->seg_r0[s] = p->ay.start[p->seg_b0[s]];
+    p->seg_rows[s] = p->ay.start[p->seg_b0[s + 1] - 1] + 4 - p->seg_r0[s];
+  }
+}
+
+/* Per-bin derived data; b < max(PH, PW).  xoff = tile column of feature column ax.lo0. */
+RT_HD void rb_plan_bin(RbPlan* p, int b, int PH, int PW, int nseg, int xoff, float inv) {
+  if (b < PH) {
+    int s = 0;
+    while (s + 1 < nseg && b >= p->seg_b0[s + 1]) ++s;
+    const int rot = (p->ay.start[b] - p->seg_r0[s]) & 3; /* ring slot of the band's first row */
+    const RbF4 w = p->ay.w[b];
+    RbF4 r;
+    r.x = rot == 0 ? w.x : (rot == 1 ? w.w : (rot == 2 ? w.z : w.y));
+    r.y = rot == 0 ? w.y : (rot == 1 ? w.x : (rot == 2 ? w.w : w.z));
+    r.z = rot == 0 ? w.z : (rot == 1 ? w.y : (rot == 2 ? w.x : w.w));
+    r.w = rot == 0 ? w.w : (rot == 1 ? w.z : (rot == 2 ? w.y : w.x));
+    p->wrot[b] = r;
+  }
+  if (b < PW) {
+    const RbF4 w = p->ax.w[b];
+    RbF4 r;
+    r.x = w.x * inv;
+    r.y = w.y * inv;
+    r.z = w.z * inv;
+    r.w = w.w * inv;
+    p->xw[b] = r;
+    p->xo[b] = p->ax.start[b] + xoff;
+  }
+}
+
+/* Word i of segment s: how many bins complete at rows 4i .. 4i+3 of the segment. */
+RT_HD void rb_plan_mword(RbPlan* p, int s, int i) {
+  uint32_t m = 0;
+  for (int b = p->seg_b0[s]; b < p->seg_b0[s + 1]; ++b) {
+    const int r = p->ay.start[b] - p->seg_r0[s] + 3;
+    if ((r >> 2) == i) m += 1u << (8 * (r & 3));
+  }
+  p->mw[s][i] = m;
+}
+
+/* y-pass of one strip: rows = the segment's rows of this strip (pitch nq RbF4), wr / v start at
+ * the segment's first bin; V rows are vp floats apart. */
+RT_HD void rb_ywalk(const RbF4* rows, int nq, int nrows, const uint32_t* mw, const RbF4* wr,
+                    float* v, int vp) {
+  RbF4 W0, W1, W2, W3;
+  W0.x = W0.y = W0.z = W0.w = 0.f;
+  W1 = W0;
+  W2 = W0;
+  W3 = W0;
+#define RB_BINS(cnt)                                                                             \
+  for (uint32_t m_ = (cnt); m_ != 0; --m_) {                                                    \
+    const RbF4 w_ = *wr++;                                                                      \
+    RbF4 a_;                                                                                    \
+    a_.x = fmaf(w_.w, W3.x, fmaf(w_.z, W2.x, fmaf(w_.y, W1.x, w_.x * W0.x)));                   \
+    a_.y = fmaf(w_.w, W3.y, fmaf(w_.z, W2.y, fmaf(w_.y, W1.y, w_.x * W0.y)));                   \
+    a_.z = fmaf(w_.w, W3.z, fmaf(w_.z, W2.z, fmaf(w_.y, W1.z, w_.x * W0.z)));                   \
+    a_.w = fmaf(w_.w, W3.w, fmaf(w_.z, W2.w, fmaf(w_.y, W1.w, w_.x * W0.w)));                   \
+    *reinterpret_cast<RbF4*>(v) = a_;                                                           \
+    v += vp;                                                                                    \
+  }
+  for (int r = 0; r < nrows; r += 4) {
+    const uint32_t m = mw[r >> 2];
+    W0 = rows[0];
+    RB_BINS(m & 0xffu)
+    if (r + 1 < nrows) W1 = rows[nq];
+    RB_BINS((m >> 8) & 0xffu)
+    if (r + 2 < nrows) W2 = rows[2 * nq];
+    RB_BINS((m >> 16) & 0xffu)
+    if (r + 3 < nrows) W3 = rows[3 * nq];
+    RB_BINS(m >> 24)
+    rows += 4 * nq;
+  }
+#undef RB_BINS
+}
+
+/* Channels per chunk and y segments for one RoI (CTA-uniform).  per_ch = shared-memory floats
+ * one channel needs (tile + V), nq = strips per channel, nt = threads. */
+RT_HD void rb_plan_chunk(int budget_floats, int per_ch, int nq, int nch, int PH, int nt, int* cc_out,
+                         int* nseg_out) {
+  int cc_fit = per_ch > 0 ? budget_floats / per_ch : 0;
+  if (cc_fit > nch) cc_fit = nch;
+  int best_cc = cc_fit, best_seg = 1;
+  float best = -1.f;
+  for (int nseg = 1; nseg <= RB_MAXSEG && nseg <= PH; ++nseg) {
+    if (cc_fit < 1) break;
+    const int per = nq * nseg;
+    int rounds = cc_fit * per / nt;
+    if (rounds < 1) rounds = 1;
+    int cc = rounds * nt / per;
+    if (cc > cc_fit) cc = cc_fit;
+    if (cc < 1) cc = 1;
+    /* even chunks over the CTA's channels */
+    const int nchunk = (nch + cc - 1) / cc;
+    cc = (nch + nchunk - 1) / nchunk;
+    const int items = cc * per;
+    const float util = (float)items / (float)((items + nt - 1) / nt * nt);
+    const float score = util * (nseg == 1 ? 1.0f : 0.88f); /* a second segment re-reads 3 rows */
+    if (score > best) {
+      best = score;
+      best_cc = cc;
+      best_seg = nseg;
+    }
+  }
+  *cc_out = best_cc;
+  *nseg_out = best_seg;
+}
+
 /* 1/count when that is exact (count a power of two), else 0 => divide. */
 RT_HD float rt_exact_inv(int count) {
   return (count > 0 && (count & (count - 1)) == 0) ? 1.0f / (float)count : 0.0f;

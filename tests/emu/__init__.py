@@ -55,6 +55,27 @@ def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, vs_
     return out, nd
 
 
+def band_forward(feats, scales, rois, levels, output_size, sampling_ratio, smem_floats=10240,
+                 c_per_cta=None, nthreads=128):
+    """The banded (v4) forward kernel emulated on the host; returns (out, number of
+    (RoI, channel slice) pairs that had no band form)."""
+    feats = [np.ascontiguousarray(f, np.float32) for f in feats]
+    rois = np.ascontiguousarray(rois, np.float32)
+    L, ptr, Hs, Ws, sc = _levels_args(feats, scales)
+    N, C = feats[0].shape[:2]
+    K = rois.shape[0]
+    PH, PW = output_size
+    out = np.full((K, C, PH, PW), 7e30, np.float32)
+    lv = None
+    if levels is not None:
+        levels = np.ascontiguousarray(levels, np.int32)
+        lv = levels.ctypes.data_as(_i32p)
+    nf = lib().emu_band_forward(ptr, Hs, Ws, sc, L, N, C, rois.ctypes.data_as(_f32p), lv, K, PH, PW,
+                                ctypes.c_float(sampling_ratio), out.ctypes.data_as(_f32p),
+                                int(smem_floats), int(c_per_cta or C), int(nthreads))
+    return out, nf
+
+
 def pooler_backward(dout, feat_shapes, scales, rois, levels, sampling_ratio, vs_floats=8192,
                     c_per_cta=None):
     dout = np.ascontiguousarray(dout, np.float32)

@@ -255,6 +255,116 @@ extern "C" __attribute__((visibility("default"))) int emu_pooler_forward(
   }
 }
 
+// Mirrors rb_pool_fwd_kernel (v4, banded): the same plan functions, chunking, strip walk and
+// x-pass; the CTA's threads run serially.  Returns the number of (RoI, slice) pairs without a
+// band form (evaluated in the reference's order here; by the v3 body on the GPU).
+extern "C" __attribute__((visibility("default"))) int emu_band_forward(
+    const float* const* feats, const int* Hs, const int* Ws, const float* scales, int L, int N,
+    int C, const float* rois, const int* levels, int K, int PH, int PW, float sampling_ratio,
+    float* out, int smem_floats, int c_per_cta, int nthreads) {
+  const int P = PH * PW;
+  int n_fallback = 0;
+  std::vector<float> smem((size_t)smem_floats + 4);
+  float* base = smem.data();
+  while (reinterpret_cast<uintptr_t>(base) & 15) ++base;
+  for (int k = 0; k < K; ++k) {
+    for (int c_begin = 0; c_begin < C; c_begin += c_per_cta) {
+      const int c_end = std::min(C, c_begin + c_per_cta);
+      const int nch = c_end - c_begin;
+      const float* roi = rois + (size_t)k * 5;
+      const int level = levels ? levels[k] : 0;
+      const int b = (int)roi[0];
+      float* out_k = out + ((size_t)k * C + c_begin) * P;
+      if (level < 0 || level >= L || b < 0 || b >= N) {
+        std::fill(out_k, out_k + (size_t)nch * P, 0.f);
+        continue;
+      }
+      const int H = Hs[level], W = Ws[level];
+      const size_t HW = (size_t)H * W;
+      const RtGeom g = rt_geom_fwd(roi, scales[level], sampling_ratio, PH, PW);
+      static RbPlan plan;
+      int ok = rb_axis_candidate(g.bh, g.gh, PH, H) && rb_axis_candidate(g.bw, g.gw, PW, W);
+      if (ok) {
+        for (int t = 0; t < PH; ++t) ok &= rb_build_bin(&plan.ay, t, g.sh, g.bh, g.gh, H);
+        for (int t = 0; t < PW; ++t) ok &= rb_build_bin(&plan.ax, t, g.sw, g.bw, g.gw, W);
+      }
+      if (ok) ok = rb_finish_axis(&plan.ay, PH) & rb_finish_axis(&plan.ax, PW);
+      int cc = 0, nseg = 1, nq = 0, vp = 0, chp4 = 0, xa0 = 0, vecw = 1, R = 0, y0 = 0;
+      if (ok) {
+        y0 = plan.ay.lo0;
+        R = plan.ay.ext;
+        const int x0 = plan.ax.lo0, xe = x0 + plan.ax.ext;
+        vecw = (W & 3) == 0 ? 4 : ((W & 1) == 0 ? 2 : 1);
+        xa0 = x0 & ~(vecw - 1);
+        nq = (xe - xa0 + 3) >> 2;
+        {
+          int vpu = nq;
+          while ((vpu & 7) != 3 && (vpu & 7) != 5) ++vpu;
+          vp = 4 * vpu;
+        }
+        chp4 = R * nq + ((nq - R * nq) & 7);
+        rb_plan_chunk(smem_floats, 4 * chp4 + PH * vp, nq, nch, PH, nthreads, &cc, &nseg);
+        ok = cc >= 1;
+      }
+      if (!ok) {
+        ++n_fallback;
+        const float* feat_b = feats[level] + ((size_t)b * C + c_begin) * HW;
+        for (int i = 0; i < nch * P; ++i) {
+          const int c = i / P, rem = i - c * P, ph = rem / PW, pw = rem - ph * PW;
+          out_k[i] = rt_direct_output(feat_b + (size_t)c * HW, H, W, g, ph, pw);
+        }
+        continue;
+      }
+      rb_plan_segments(&plan, PH, nseg);
+      for (int t = 0; t < 32; ++t)
+        rb_plan_bin(&plan, t, PH, PW, nseg, plan.ax.lo0 - xa0, 1.0f / (float)(g.gh * g.gw));
+      for (int sgm = 0; sgm < nseg; ++sgm)
+        for (int i = 0; i * 4 < plan.seg_rows[sgm] + 4; ++i) rb_plan_mword(&plan, sgm, i);
+      float* tile = base;
+      const int chp = 4 * chp4;
+      float* V = tile + cc * chp;
+      const float* src0 = feats[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
+      const int wlim = W - xa0;
+      const int xg = PW <= 16 ? 16 : PW;
+      const int nslots = nthreads / xg;
+      int tap3 = 1;
+      for (int t = 0; t < PW; ++t) tap3 &= plan.xw[t].w == 0.f;
+      for (int c0 = 0; c0 < nch; c0 += cc) {
+        const int ccur = std::min(cc, nch - c0);
+        std::fill(base, base + smem_floats, NAN);  // poison: anything read must have been written
+        for (int c = 0; c < ccur; ++c)
+          for (int y = 0; y < R; ++y)
+            for (int col = 0; col < 4 * nq; ++col)
+              tile[c * chp + y * 4 * nq + col] =
+                  col < wlim ? src0[(size_t)(c0 + c) * HW + (size_t)y * W + col] : 0.f;
+        const int per_seg = ccur * nq, total = per_seg * nseg;
+        for (int sidx = 0; sidx < total; ++sidx) {
+          const int seg = sidx >= per_seg ? 1 : 0;
+          const int rem = sidx - seg * per_seg;
+          const int c = rem / nq, q = rem - c * nq;
+          const int b0 = plan.seg_b0[seg];
+          rb_ywalk(reinterpret_cast<const RbF4*>(tile) + c * chp4 + plan.seg_r0[seg] * nq + q, nq,
+                   plan.seg_rows[seg], plan.mw[seg], plan.wrot + b0, V + (c * PH + b0) * vp + 4 * q, vp);
+        }
+        for (int tid = 0; tid < nthreads; ++tid) {
+          const int pw = tid % xg, slot = tid / xg;
+          if (!(pw < PW && slot < nslots)) continue;
+          const RbF4 w = plan.xw[pw];
+          const float* v = V + slot * vp + plan.xo[pw];
+          float* o = out_k + (size_t)c0 * P + slot * PW + pw;
+          for (int r = slot; r < ccur * PH; r += nslots) {
+            *o = tap3 ? fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0]))
+                      : fmaf(w.w, v[3], fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0])));
+            v += nslots * vp;
+            o += nslots * PW;
+          }
+        }
+      }
+    }
+  }
+  return n_fallback;
+}
+
 extern "C" {
 
 // grads[l] must be zero-filled by the caller.

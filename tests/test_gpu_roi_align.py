@@ -164,3 +164,32 @@ def test_full_size_properties():
     lhs = float((o1.double() * d.double()).sum())
     rhs = float(sum((a.double() * b.double()).sum() for a, b in zip(f1, grads)))
     assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), abs(rhs), 1.0) * 10
+
+
+@pytest.mark.parametrize("impl", ["3", "4"])
+@pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
+def test_forward_kernel_variants(impl, P, sr, monkeypatch):
+    """Both forward kernels (RP_ROI_IMPL=3: column walk; =4: banded, v3 body as its fallback)
+    against the oracle, on aligned (W % 4 == 0), 8-byte (W = 42) and odd-width maps."""
+    monkeypatch.setenv("RP_ROI_IMPL", impl)
+    rng = np.random.default_rng(11)
+    for (H, W), C, cpc in [((50, 84), 37, "16"), ((25, 42), 8, "64"), ((13, 19), 5, "64"), ((3, 9), 4, "64")]:
+        monkeypatch.setenv("RP_ROI_CPC", cpc)
+        feat = rng.standard_normal((2, C, H, W)).astype(np.float32)
+        rois = _rois(rng, 90, 2)
+        rois[:, 1:] *= np.float32(W * 16 / 1344)
+        exp = oracle.roi_align_forward(feat, rois, P, 1 / 16, sr)
+        out = rp.roi_align(T(feat), T(rois), P, 1 / 16, sr).cpu().numpy()
+        _close(out, exp)
+
+
+def test_banded_pooler_multi_level(monkeypatch):
+    monkeypatch.setenv("RP_ROI_IMPL", "4")
+    N, C = 2, 24
+    feats = synth.fpn_features(N, C)
+    rois = synth.rois_for_images(N, 200)
+    lv = oracle.level_map(rois[:, 1:], 2, 5)
+    for P in [(14, 14), (7, 7)]:
+        exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, P, 2)
+        out = rp.pooler_forward([T(f) for f in feats], synth.FPN_SCALES, T(rois), T(lv), P, 2)
+        _close(out.cpu().numpy(), exp)

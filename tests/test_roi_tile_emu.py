@@ -83,3 +83,50 @@ def test_linearity_and_constant_preservation():
     ones = np.full((N, C, 50, 84), 3.0, np.float32)
     oc, _ = emu.pooler_forward([ones], [1 / 16], rois, None, (7, 7), 2)
     np.testing.assert_allclose(oc, 3.0, rtol=1e-6)
+
+
+# ---- banded (v4) forward: same plan / walk code as rb_pool_fwd_kernel -----------------------------
+@pytest.mark.parametrize("P,sr", [((7, 7), 2), ((14, 14), 2), ((14, 14), 0), ((3, 5), 3), ((14, 14), 1),
+                                  ((28, 28), 2)])
+def test_band_forward_single_level(P, sr):
+    rng = np.random.default_rng(5)
+    N, C = 2, 21
+    feat = rng.standard_normal((N, C, 50, 84)).astype(np.float32)
+    rois = _rois(rng, 120, N)
+    a = oracle.roi_align_forward(feat, rois, P, 1 / 16, sr)
+    for smem, cpc, nt in [(10240, None, 128), (2600, 8, 128), (1200, 5, 64)]:
+        b, nf = emu.band_forward([feat], [1 / 16], rois, None, P, sr, smem, cpc, nt)
+        _close(b, a)
+        assert nf < 120 * (1 if cpc is None else -(-C // cpc))  # the band path is exercised
+
+
+def test_band_forward_multi_level_and_odd_maps():
+    rng = np.random.default_rng(6)
+    N, C = 2, 16
+    shapes = [(N, C, 200, 336), (N, C, 100, 168), (N, C, 50, 84), (N, C, 25, 42)]
+    feats = [rng.standard_normal(s).astype(np.float32) for s in shapes]
+    rois = synth.rois_for_images(N, 150)
+    levels = oracle.level_map(rois[:, 1:], 2, 5)
+    a = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, levels, (14, 14), 2)
+    b, nf = emu.band_forward(feats, synth.FPN_SCALES, rois, levels, (14, 14), 2)
+    assert nf == 0  # every FPN-mapped RoI has a band form at 14 bins, sampling 2
+    _close(b, a)
+    # maps whose rows are not 16-byte aligned (8- and 4-byte staging) and tiny maps (fallback)
+    for H, W in [(25, 42), (13, 19), (4, 4), (3, 9)]:
+        f = rng.standard_normal((1, 6, H, W)).astype(np.float32)
+        r = _rois(rng, 60, 1)
+        r[:, 1:] *= np.float32(W * 16 / 1344)
+        a = oracle.roi_align_forward(f, r, (7, 7), 1 / 16, 2)
+        b, _ = emu.band_forward([f], [1 / 16], r, None, (7, 7), 2)
+        _close(b, a)
+
+
+def test_band_plan_properties():
+    # merged weights of a bin sum to the number of in-range samples; band starts are monotone
+    import ctypes
+    rng = np.random.default_rng(7)
+    f = np.ones((1, 4, 50, 84), np.float32)
+    rois = _rois(rng, 200, 1)
+    out, _ = emu.band_forward([f], [1 / 16], rois, None, (14, 14), 2)
+    ref = oracle.roi_align_forward(f, rois, (14, 14), 1 / 16, 2)
+    np.testing.assert_allclose(out, ref, rtol=2e-6, atol=2e-6)
