@@ -311,56 +311,85 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 // ------------------------------------------------------------------------------------------
 constexpr int RB_THREADS = 128;
 
-// Warp w stages channels w, w + nw, ...: its lanes form rpw = 32 / vpr rows of vpr staging
-// vectors (VEC floats each) and step down the tile rpw rows at a time -- one cp.async, one
-// 64-bit and one 32-bit add per copy; no division inside the loop.
-template <int VEC>
-__device__ __forceinline__ void rb_stage_tile(float* tile, const float* __restrict__ src, int cc,
-                                              int R, int nq, int W, size_t HW, int chp, int wlim) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const int vpr = (4 / VEC) * nq;  // staging vectors per tile row
+// Per-thread staging constants of one RoI (computed once, used for every chunk): the lanes of a
+// warp form rpw = 32 / vpr rows of vpr staging vectors (VEC floats each) and step down the tile
+// rpw rows at a time; warp w stages channels w, w + nw, ...  One cp.async, one 64-bit and one
+// 32-bit add per copy; no division inside the chunk loop.
+struct RbStageLane {
+  int active;     // this lane copies (lanes past rpw * vpr idle)
+  int vrow;       // first tile row of the lane
+  int rpw;        // rows per warp step
+  int zero;       // the lane's columns lie past the end of the map row: store zeros instead
+  size_t goff;    // vrow * W + col
+  uint32_t soff;  // byte offset of (vrow, col) inside a channel's tile
+};
+
+__device__ __forceinline__ RbStageLane rb_stage_lane(int vec, int nq, int W, int wlim) {
+  RbStageLane l;
+  const int lane = threadIdx.x & 31;
+  const int vpr = (4 / vec) * nq;
   int rpw = 32 / vpr;
-  if (rpw < 1) rpw = 1;
-  const int vrow = rpw == 1 ? 0 : lane / vpr;
-  const int v0 = lane - vrow * vpr;
-  if (vrow >= rpw) return;
-  const uint32_t tile_s = rp_smem_addr(tile);
-  for (int c = warp; c < cc; c += nw) {
-    for (int v = v0; v < vpr; v += 32) {  // one trip unless the row has more than 32 vectors
-      const int col = v * VEC;
-      const float* gp = src + (size_t)c * HW + (size_t)vrow * W + col;
-      uint32_t sp = tile_s + 4u * (uint32_t)(c * chp + vrow * 4 * nq + col);
-      const size_t gstep = (size_t)rpw * W;
-      const uint32_t sstep = 16u * (uint32_t)(rpw * nq);
-      if (VEC == 4 || col < wlim) {
-        for (int y = vrow; y < R; y += rpw) {
-          if (VEC == 4)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sp), "l"(gp) : "memory");
-          else if (VEC == 2)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sp), "l"(gp) : "memory");
-          else
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sp), "l"(gp) : "memory");
-          gp += gstep;
-          sp += sstep;
-        }
-      } else {  // columns past the end of the map row: never weighted, but keep them finite
-        for (int y = vrow; y < R; y += rpw) {
+  if (rpw < 1) rpw = 1;  // rows wider than 32 vectors (vec < 4 only): not on the band path
+  l.rpw = rpw;
+  l.vrow = lane / vpr;
+  const int col = (lane - l.vrow * vpr) * vec;
+  l.active = l.vrow < rpw;
+  l.zero = col >= wlim;
+  l.goff = (size_t)l.vrow * W + col;
+  l.soff = 4u * (uint32_t)(l.vrow * 4 * nq + col);
+  return l;
+}
+
+template <int VEC>
+__device__ __forceinline__ void rb_stage_tile(uint32_t tile_s, const float* __restrict__ src, int cc,
+                                              int R, int nq, int W, size_t HW, int chp,
+                                              const RbStageLane& l) {
+  if (!l.active) return;
+  const int warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const size_t gstep = (size_t)l.rpw * W;
+  const uint32_t sstep = 16u * (uint32_t)(l.rpw * nq);
+  const float* gc = src + (size_t)warp * HW + l.goff;
+  uint32_t sc = tile_s + 4u * (uint32_t)(warp * chp) + l.soff;
+  const size_t gcs = (size_t)nw * HW;
+  const uint32_t scs = 4u * (uint32_t)(nw * chp);
+  for (int c = warp; c < cc; c += nw, gc += gcs, sc += scs) {
+    const float* gp = gc;
+    uint32_t sp = sc;
+    if (VEC == 4 || !l.zero) {
+      for (int y = l.vrow; y < R; y += l.rpw) {
+        if (VEC == 4)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sp), "l"(gp) : "memory");
+        else if (VEC == 2)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sp), "l"(gp) : "memory");
+        else
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sp), "l"(gp) : "memory");
+        gp += gstep;
+        sp += sstep;
+      }
+    } else {  // columns past the end of the map row: never weighted, but keep them finite
+      for (int y = l.vrow; y < R; y += l.rpw) {
 #pragma unroll
-          for (int e = 0; e < VEC; ++e)
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sp + 4u * e), "f"(0.f) : "memory");
-          sp += sstep;
-        }
+        for (int e = 0; e < VEC; ++e)
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(sp + 4u * e), "f"(0.f) : "memory");
+        sp += sstep;
       }
     }
   }
 }
 
-__global__ void __launch_bounds__(RB_THREADS, 5)
+// CTA-uniform launch geometry of one RoI, written by thread 0.
+struct RbGeo {
+  int ok, cc, nseg, nq, vp, chp4, xa0, vecw;
+};
+
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
 rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
                    float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   __shared__ RbPlan plan;
+  __shared__ RbGeo geo;
   __shared__ int s_fin[2];
 
   const int tid = threadIdx.x;
@@ -395,35 +424,43 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     if (tid == 0) s_fin[0] = rb_finish_axis(&plan.ay, PH);
     if (tid == 32) s_fin[1] = rb_finish_axis(&plan.ax, PW);
     __syncthreads();
-    ok = s_fin[0] && s_fin[1];
-  }
-  int cc = 0, nseg = 1, nq = 0, vp = 0, chp4 = 0, xa0 = 0, vecw = 1, R = 0, y0 = 0;
-  if (ok) {
-    y0 = plan.ay.lo0;
-    R = plan.ay.ext;
-    const int x0 = plan.ax.lo0, xe = x0 + plan.ax.ext;
-    const uintptr_t base_addr = reinterpret_cast<uintptr_t>(lv.feat[level]);
-    vecw = (((W & 3) == 0) && ((base_addr & 15) == 0)) ? 4
-           : (((W & 1) == 0) && ((base_addr & 7) == 0)) ? 2 : 1;
-    xa0 = x0 & ~(vecw - 1);
-    nq = (xe - xa0 + 3) >> 2;
-    {                                       // V row pitch: vpu 16-byte units, vpu >= nq, vpu mod 8 in
-      int vpu = nq;                         // {3, 5}: the two V rows an x-pass warp reads sit 12 or
-      while ((vpu & 7) != 3 && (vpu & 7) != 5) ++vpu;  // 20 banks apart
-      vp = 4 * vpu;
+    if (tid == 0) {
+      RbGeo ge;
+      ge.ok = s_fin[0] && s_fin[1];
+      ge.cc = 0;
+      ge.nseg = 1;
+      const int x0 = plan.ax.lo0, xe = x0 + plan.ax.ext, R = plan.ay.ext;
+      const uintptr_t base_addr = reinterpret_cast<uintptr_t>(lv.feat[level]);
+      ge.vecw = (((W & 3) == 0) && ((base_addr & 15) == 0)) ? 4
+                : (((W & 1) == 0) && ((base_addr & 7) == 0)) ? 2 : 1;
+      ge.xa0 = x0 & ~(ge.vecw - 1);
+      ge.nq = (xe - ge.xa0 + 3) >> 2;
+      int vpu = ge.nq;  // V row pitch: vpu 16-byte units, vpu >= nq, vpu mod 8 in {3, 5}: the two
+      while ((vpu & 7) != 3 && (vpu & 7) != 5) ++vpu;  // V rows of an x-pass warp sit 12 / 20 banks apart
+      ge.vp = 4 * vpu;
+      // channel pitch in 16-byte units, == nq (mod 8): the strips of consecutive channels
+      // continue the banks
+      ge.chp4 = R * ge.nq + ((ge.nq - R * ge.nq) & 7);
+      if (ge.ok && (4 / ge.vecw) * ge.nq <= 32) {
+        rb_plan_chunk(smem_floats, 4 * ge.chp4 + PH * ge.vp, ge.nq, nch, PH, NT, &ge.cc,
+                      &ge.nseg);
+        ge.ok = ge.cc >= 1;
+      } else {
+        ge.ok = 0;
+      }
+      if (ge.ok) rb_plan_segments(&plan, PH, ge.nseg);
+      geo = ge;
     }
-    chp4 = R * nq + ((nq - R * nq) & 7);    // channel pitch in 16-byte units, == nq (mod 8): the
-                                            // strips of consecutive channels continue the banks
-    rb_plan_chunk(smem_floats, 4 * chp4 + PH * vp, nq, nch, PH, RB_THREADS, &cc, &nseg);
-    ok = cc >= 1;
+    __syncthreads();
+    ok = geo.ok;
   }
   if (!ok) {
     rt3_roi_forward<2>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
                        (smem_floats * 4 - RT3_TABLE_BYTES) / 4, gpb, gw);
     return;
   }
-  if (tid == 0) rb_plan_segments(&plan, PH, nseg);
-  __syncthreads();
+  const int cc = geo.cc, nseg = geo.nseg, nq = geo.nq, vp = geo.vp, chp4 = geo.chp4;
+  const int xa0 = geo.xa0, vecw = geo.vecw, R = plan.ay.ext, y0 = plan.ay.lo0;
   {
     const int count = g.gh * g.gw;
     if (tid < 32) rb_plan_bin(&plan, tid, PH, PW, nseg, plan.ax.lo0 - xa0, 1.0f / (float)count);
@@ -434,69 +471,85 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
   }
   __syncthreads();
+  // 3-tap x bands (every RoI narrower than 28 feature pixels): skip the 4th load
+  const int tap3 = __syncthreads_and(tid >= PW || plan.xw[tid].w == 0.f);
 
   float* tile = reinterpret_cast<float*>(rt_smem);
+  const uint32_t tile_s = rp_smem_addr(tile);
   const int chp = 4 * chp4;
   float* V = tile + cc * chp;
   const float* src0 = lv.feat[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
-  const int wlim = W - xa0;
+  const RbStageLane sl = rb_stage_lane(vecw, nq, W, W - xa0);
   // x-pass mapping: groups of xg lanes (16 when PW <= 16, so a warp holds two whole V rows)
   const int xg = PW <= 16 ? 16 : PW;
-  const int nslots = RB_THREADS / xg;
+  const int nslots = NT / xg;
   const int pw = tid % xg, slot = tid / xg;
   const bool xactive = pw < PW && slot < nslots;
-  // 3-tap x bands (every RoI narrower than 28 feature pixels): skip the 4th load
-  const int tap3 = __syncthreads_and(tid >= PW || plan.xw[tid].w == 0.f);
+  const RbF4 xw = plan.xw[xactive ? pw : 0];
+  const int xo = plan.xo[xactive ? pw : 0];
+  // y-pass mapping: strip s = (segment, channel, 4-column strip) in units of the FULL chunk, so
+  // the decode is done once; channels past the end of a short last chunk are skipped
+  const int per_seg = cc * nq, nstrip = per_seg * nseg;
+  int ys_c = 0, ys_rows = 0, ys_toff = 0, ys_voff = 0, ys_b0 = 0, ys_seg = 0;
+  if (tid < nstrip) {
+    ys_seg = tid >= per_seg ? 1 : 0;
+    const int rem = tid - ys_seg * per_seg;
+    ys_c = rem / nq;
+    const int q = rem - ys_c * nq;
+    ys_b0 = plan.seg_b0[ys_seg];
+    ys_rows = plan.seg_rows[ys_seg];
+    ys_toff = ys_c * chp4 + plan.seg_r0[ys_seg] * nq + q;
+    ys_voff = (ys_c * PH + ys_b0) * vp + 4 * q;
+  }
+
   auto stage = [&](int c0, int ccur) {
     const float* src = src0 + (size_t)c0 * HW;
     if (vecw == 4)
-      rb_stage_tile<4>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+      rb_stage_tile<4>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
     else if (vecw == 2)
-      rb_stage_tile<2>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+      rb_stage_tile<2>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
     else
-      rb_stage_tile<1>(tile, src, ccur, R, nq, W, HW, chp, wlim);
+      rb_stage_tile<1>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
+  const RbF4* tile4 = reinterpret_cast<const RbF4*>(tile);
   stage(0, min(cc, nch));
   for (int c0 = 0; c0 < nch; c0 += cc) {
     const int ccur = min(cc, nch - c0);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();  // tile(c0) has landed; every thread is done with V of the previous chunk
     // ---- y-pass ------------------------------------------------------------------------------
-    {
-      const int per_seg = ccur * nq;
-      const int total = per_seg * nseg;
-      const RbF4* tile4 = reinterpret_cast<const RbF4*>(tile);
-      for (int s = tid; s < total; s += RB_THREADS) {
-        const int seg = s >= per_seg ? 1 : 0;
-        const int rem = s - seg * per_seg;
-        const int c = rem / nq, q = rem - c * nq;
-        const int b0 = plan.seg_b0[seg];
+    if (tid < nstrip && ys_c < ccur)
+      rb_ywalk(tile4 + ys_toff, nq, ys_rows, plan.mw[ys_seg], plan.wrot + ys_b0, V + ys_voff, vp);
+    for (int s = tid + NT; s < nstrip; s += NT) {  // more strips than threads
+      const int seg = s >= per_seg ? 1 : 0;
+      const int rem = s - seg * per_seg;
+      const int c = rem / nq, q = rem - c * nq;
+      const int b0 = plan.seg_b0[seg];
+      if (c < ccur)
         rb_ywalk(tile4 + c * chp4 + plan.seg_r0[seg] * nq + q, nq, plan.seg_rows[seg], plan.mw[seg],
                  plan.wrot + b0, V + (c * PH + b0) * vp + 4 * q, vp);
-      }
     }
     __syncthreads();  // V complete, tile free
     if (c0 + cc < nch) stage(c0 + cc, min(cc, nch - c0 - cc));
     // ---- x-pass ------------------------------------------------------------------------------
     if (xactive) {
-      const RbF4 w = plan.xw[pw];
-      const float* v = V + slot * vp + plan.xo[pw];
+      const float* v = V + slot * vp + xo;
       float* o = out_k + (size_t)c0 * P + slot * PW + pw;
       const int nrow = ccur * PH;
       const int vstep = nslots * vp, ostep = nslots * PW;
       if (tap3) {
 #pragma unroll 2
         for (int r = slot; r < nrow; r += nslots) {
-          __stcs(o, fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0])));
+          __stcs(o, fmaf(xw.z, v[2], fmaf(xw.y, v[1], xw.x * v[0])));
           v += vstep;
           o += ostep;
         }
       } else {
 #pragma unroll 2
         for (int r = slot; r < nrow; r += nslots) {
-          __stcs(o, fmaf(w.w, v[3], fmaf(w.z, v[2], fmaf(w.y, v[1], w.x * v[0]))));
+          __stcs(o, fmaf(xw.w, v[3], fmaf(xw.z, v[2], fmaf(xw.y, v[1], xw.x * v[0]))));
           v += vstep;
           o += ostep;
         }
@@ -852,24 +905,37 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   if (mode != 0) return RP_E_ARG;
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
-  if (rp_env_int("RP_ROI_IMPL", 3) == 4 && PW <= RB_THREADS) {
+  if (rp_env_int("RP_ROI_IMPL", 3) == 4 && PW <= 128) {
     // banded kernel; RoIs without a band form run the v3 body inside the same CTA
+    const int cfg = rp_env_int("RP_ROI_BAND_CFG", 0);  // 0: 128 thr x5, 1: 128 x8, 2: 256 x4, 3: 256 x3
+    const int nt = cfg >= 2 ? 256 : 128;
     int gw = PW, gpb = 1;
     if (PW < 32) {
       gw = 1;
       while (gw < PW) gw *= 2;
     }
-    while (gw * gpb * 2 <= RB_THREADS) gpb *= 2;
-    int kb = rp_env_int("RP_ROI_BAND_SMEM_KB", 40);
+    while (gw * gpb * 2 <= nt) gpb *= 2;
+    static const int dflt_kb[4] = {40, 24, 52, 70};
+    int kb = rp_env_int("RP_ROI_BAND_SMEM_KB", dflt_kb[cfg & 3]);
     if (kb < 16) kb = 16;
     if (kb > 200) kb = 200;
     const int smem = kb * 1024;
-    RP_CUDA_TRY(cudaFuncSetAttribute(rb_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     smem));
     dim3 grid((unsigned)K, (unsigned)l.csplit);
-    rb_pool_fwd_kernel<<<grid, RB_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
-                                                       sampling_ratio, out, l.c_per_cta, smem / 4,
-                                                       gpb, gw);
+#define RB_LAUNCH(NT_, MB_)                                                                      \
+  do {                                                                                           \
+    RP_CUDA_TRY(cudaFuncSetAttribute(rb_pool_fwd_kernel<NT_, MB_>,                               \
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem));        \
+    rb_pool_fwd_kernel<NT_, MB_><<<grid, NT_, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,     \
+                                                          sampling_ratio, out, l.c_per_cta,      \
+                                                          smem / 4, gpb, gw);                    \
+  } while (0)
+    switch (cfg & 3) {
+      case 1: RB_LAUNCH(128, 8); break;
+      case 2: RB_LAUNCH(256, 4); break;
+      case 3: RB_LAUNCH(256, 3); break;
+      default: RB_LAUNCH(128, 5); break;
+    }
+#undef RB_LAUNCH
     RP_LAUNCH_CHECK();
     return RP_OK;
   }

@@ -303,8 +303,12 @@ extern "C" __attribute__((visibility("default"))) int emu_band_forward(
           vp = 4 * vpu;
         }
         chp4 = R * nq + ((nq - R * nq) & 7);
-        rb_plan_chunk(smem_floats, 4 * chp4 + PH * vp, nq, nch, PH, nthreads, &cc, &nseg);
-        ok = cc >= 1;
+        if ((4 / vecw) * nq <= 32) {
+          rb_plan_chunk(smem_floats, 4 * chp4 + PH * vp, nq, nch, PH, nthreads, &cc, &nseg);
+          ok = cc >= 1;
+        } else {
+          ok = 0;
+        }
       }
       if (!ok) {
         ++n_fallback;

@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--res", type=int, default=14)
     ap.add_argument("--kb", default="32,40,56")
     ap.add_argument("--cpc", default="64,128,256")
+    ap.add_argument("--cfg", default="0")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     shapes = synth.fpn_shapes(a.images, 256)
@@ -52,14 +53,15 @@ def main():
     ref = out.clone()
     print("v3 default: %.3f ms  %.2f M RoIs/s" % (ms, K / ms / 1e3), flush=True)
     os.environ["RP_ROI_IMPL"] = "4"
-    for kb, cpc in itertools.product(a.kb.split(","), a.cpc.split(",")):
+    for cfg, kb, cpc in itertools.product(a.cfg.split(","), a.kb.split(","), a.cpc.split(",")):
+        os.environ["RP_ROI_BAND_CFG"] = cfg
         os.environ["RP_ROI_BAND_SMEM_KB"] = kb
         os.environ["RP_ROI_CPC"] = cpc
         out.fill_(7e30)
         ms = run("v4")
         err = float(((out - ref).abs() / (ref.abs() + 1)).max())
-        print("v4 kb=%s cpc=%s : %.3f ms  %.2f M RoIs/s  out-only %.0f GB/s  max rel diff vs v3 %.2e"
-              % (kb, cpc, ms, K / ms / 1e3, out.numel() * 4 / ms / 1e6, err), flush=True)
+        print("v4 cfg=%s kb=%s cpc=%s : %.3f ms  %.2f M RoIs/s  out-only %.0f GB/s  max rel diff vs v3 %.2e"
+              % (cfg, kb, cpc, ms, K / ms / 1e3, out.numel() * 4 / ms / 1e6, err), flush=True)
 
 
 if __name__ == "__main__":
