@@ -52,7 +52,7 @@ def build(force=False, verbose=False):
     for s in srcs:
         o = os.path.join(HERE, "build", os.path.basename(s) + ".o")
         objs.append(o)
-        cmd = [NVCC] + FLAGS + ["-c", s, "-o", o]
+        cmd = [NVCC] + FLAGS + os.environ.get("RP_EXTRA_NVCC", "").split() + ["-c", s, "-o", o]
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     log = []
     for s, p in procs:

@@ -96,3 +96,30 @@ __device__ __forceinline__ void rp_bulk_load(void* sdst, const void* gsrc, uint3
 
 // Streaming (evict-first) stores for write-once outputs.
 __device__ __forceinline__ void rp_st_cs_u32(uint32_t* p, uint32_t v) { __stcs(p, v); }
+
+// ---- TMA tensor load (cp.async.bulk.tensor, SASS UTMALDG): one 3-D box global -> shared --------
+// dst 128-byte aligned; completion (box bytes, out-of-bounds parts included) counted on `bar`.
+__device__ __forceinline__ void rp_tma_load_3d(void* sdst, const void* tmap, int x, int y, int z,
+                                               uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(rp_smem_addr(sdst)),
+      "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(rp_smem_addr(bar))
+      : "memory");
+}
+// Bounded wait: traps instead of hanging the GPU if the expected bytes never arrive.
+__device__ __forceinline__ void rp_mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(rp_smem_addr(bar)), "r"(parity)
+        : "memory");
+    if (spin > (1u << 24)) __trap();
+  }
+}

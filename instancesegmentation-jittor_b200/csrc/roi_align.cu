@@ -20,6 +20,10 @@
 // extent and scale, and every RoI writes its own output row (no nonzero / gather / scatter).
 // Backward is the exact transpose with the RoI's gradient tile accumulated privately and
 // flushed with ONE coalesced atomicAdd per tile element (instead of 16 per output element).
+#include <cuda.h>  // CUtensorMap types only; the encoder is fetched through the runtime
+
+#include <mutex>
+
 #include "common.cuh"
 #include "roi_tile.h"
 
@@ -103,6 +107,72 @@ __device__ __forceinline__ void rt_stage_tile(float* tile, const float* __restri
         rt_cp_async8(s + i * 2, gp);
       else
         rt_cp_async4(s + i, gp);
+    }
+  }
+}
+
+// Per-thread staging constants of one RoI (computed once, used for every chunk): the lanes of a
+// warp form rpw = 32 / vpr rows of vpr staging vectors (VEC floats each) and step down the tile
+// rpw rows at a time; warp w stages channels w, w + nw, ...  One cp.async, one 64-bit and one
+// 32-bit add per copy; no division inside the chunk loop.
+struct RbStageLane {
+  int active;     // this lane copies (lanes past rpw * vpr idle)
+  int vrow;       // first tile row of the lane
+  int rpw;        // rows per warp step
+  int zero;       // the lane's columns lie past the end of the map row: store zeros instead
+  size_t goff;    // vrow * W + col
+  uint32_t soff;  // byte offset of (vrow, col) inside a channel's tile
+};
+
+// vpr staging vectors of `vec` floats per tile row; tile rows are rpitch floats apart
+__device__ __forceinline__ RbStageLane rb_stage_lane(int vec, int vpr, int rpitch, int W, int wlim) {
+  RbStageLane l;
+  const int lane = threadIdx.x & 31;
+  int rpw = 32 / vpr;
+  if (rpw < 1) rpw = 1;  // rows wider than 32 vectors (vec < 4 only): not on the band path
+  l.rpw = rpw;
+  l.vrow = lane / vpr;
+  const int col = (lane - l.vrow * vpr) * vec;
+  l.active = l.vrow < rpw;
+  l.zero = col >= wlim;
+  l.goff = (size_t)l.vrow * W + col;
+  l.soff = 4u * (uint32_t)(l.vrow * rpitch + col);
+  return l;
+}
+
+template <int VEC>
+__device__ __forceinline__ void rb_stage_tile(uint32_t tile_s, const float* __restrict__ src, int cc,
+                                              int R, int rpitch, int W, size_t HW, int chp,
+                                              const RbStageLane& l) {
+  if (!l.active) return;
+  const int warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const size_t gstep = (size_t)l.rpw * W;
+  const uint32_t sstep = 4u * (uint32_t)(l.rpw * rpitch);
+  const float* gc = src + (size_t)warp * HW + l.goff;
+  uint32_t sc = tile_s + 4u * (uint32_t)(warp * chp) + l.soff;
+  const size_t gcs = (size_t)nw * HW;
+  const uint32_t scs = 4u * (uint32_t)(nw * chp);
+  for (int c = warp; c < cc; c += nw, gc += gcs, sc += scs) {
+    const float* gp = gc;
+    uint32_t sp = sc;
+    if (VEC == 4 || !l.zero) {
+      for (int y = l.vrow; y < R; y += l.rpw) {
+        if (VEC == 4)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sp), "l"(gp) : "memory");
+        else if (VEC == 2)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sp), "l"(gp) : "memory");
+        else
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sp), "l"(gp) : "memory");
+        gp += gstep;
+        sp += sstep;
+      }
+    } else {  // columns past the end of the map row: never weighted, but keep them finite
+      for (int y = l.vrow; y < R; y += l.rpw) {
+#pragma unroll
+        for (int e = 0; e < VEC; ++e)
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(sp + 4u * e), "f"(0.f) : "memory");
+        sp += sstep;
+      }
     }
   }
 }
@@ -252,13 +322,23 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   const int count = g.gh * g.gw;
   const float inv = 1.0f / (float)count;
   const float* src0 = feat_b + (size_t)y0 * W + xa0;
-  const int vw = twa / vecw;  // staging columns (of vecw floats) per tile row
+  const int vw = twa / vecw;  // staging vectors (of vecw floats) per tile row
+  const bool lane_stage = vw <= 32;  // lanes form whole rows: no division per copy
   const uint32_t magicV = rt_magic((uint32_t)vw);
+  const RbStageLane sl = rb_stage_lane(vecw, vw, twa, W, 0x7fffffff);
+  const uint32_t tile_s = rp_smem_addr(tile);
 
   for (int c0 = 0; c0 < nch; c0 += tp.cc) {
     const int cc = min(tp.cc, nch - c0);
     const float* src = src0 + (size_t)c0 * HW;
-    if (vecw == 4)
+    if (lane_stage) {
+      if (vecw == 4)
+        rb_stage_tile<4>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+      else if (vecw == 2)
+        rb_stage_tile<2>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+      else
+        rb_stage_tile<1>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+    } else if (vecw == 4)
       rt_stage_tile<4>(tile, src, cc, R, vw, magicV, W, HW, chp);
     else if (vecw == 2)
       rt_stage_tile<2>(tile, src, cc, R, vw, magicV, W, HW, chp);
@@ -311,86 +391,38 @@ rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 // ------------------------------------------------------------------------------------------
 constexpr int RB_THREADS = 128;
 
-// Per-thread staging constants of one RoI (computed once, used for every chunk): the lanes of a
-// warp form rpw = 32 / vpr rows of vpr staging vectors (VEC floats each) and step down the tile
-// rpw rows at a time; warp w stages channels w, w + nw, ...  One cp.async, one 64-bit and one
-// 32-bit add per copy; no division inside the chunk loop.
-struct RbStageLane {
-  int active;     // this lane copies (lanes past rpw * vpr idle)
-  int vrow;       // first tile row of the lane
-  int rpw;        // rows per warp step
-  int zero;       // the lane's columns lie past the end of the map row: store zeros instead
-  size_t goff;    // vrow * W + col
-  uint32_t soff;  // byte offset of (vrow, col) inside a channel's tile
-};
-
-__device__ __forceinline__ RbStageLane rb_stage_lane(int vec, int nq, int W, int wlim) {
-  RbStageLane l;
-  const int lane = threadIdx.x & 31;
-  const int vpr = (4 / vec) * nq;
-  int rpw = 32 / vpr;
-  if (rpw < 1) rpw = 1;  // rows wider than 32 vectors (vec < 4 only): not on the band path
-  l.rpw = rpw;
-  l.vrow = lane / vpr;
-  const int col = (lane - l.vrow * vpr) * vec;
-  l.active = l.vrow < rpw;
-  l.zero = col >= wlim;
-  l.goff = (size_t)l.vrow * W + col;
-  l.soff = 4u * (uint32_t)(l.vrow * 4 * nq + col);
-  return l;
-}
-
-template <int VEC>
-__device__ __forceinline__ void rb_stage_tile(uint32_t tile_s, const float* __restrict__ src, int cc,
-                                              int R, int nq, int W, size_t HW, int chp,
-                                              const RbStageLane& l) {
-  if (!l.active) return;
-  const int warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const size_t gstep = (size_t)l.rpw * W;
-  const uint32_t sstep = 16u * (uint32_t)(l.rpw * nq);
-  const float* gc = src + (size_t)warp * HW + l.goff;
-  uint32_t sc = tile_s + 4u * (uint32_t)(warp * chp) + l.soff;
-  const size_t gcs = (size_t)nw * HW;
-  const uint32_t scs = 4u * (uint32_t)(nw * chp);
-  for (int c = warp; c < cc; c += nw, gc += gcs, sc += scs) {
-    const float* gp = gc;
-    uint32_t sp = sc;
-    if (VEC == 4 || !l.zero) {
-      for (int y = l.vrow; y < R; y += l.rpw) {
-        if (VEC == 4)
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sp), "l"(gp) : "memory");
-        else if (VEC == 2)
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sp), "l"(gp) : "memory");
-        else
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sp), "l"(gp) : "memory");
-        gp += gstep;
-        sp += sstep;
-      }
-    } else {  // columns past the end of the map row: never weighted, but keep them finite
-      for (int y = l.vrow; y < R; y += l.rpw) {
-#pragma unroll
-        for (int e = 0; e < VEC; ++e)
-          asm volatile("st.shared.f32 [%0], %1;" ::"r"(sp + 4u * e), "f"(0.f) : "memory");
-        sp += sstep;
-      }
-    }
-  }
-}
-
 // CTA-uniform launch geometry of one RoI, written by thread 0.
 struct RbGeo {
   int ok, cc, nseg, nq, vp, chp4, xa0, vecw;
+  int tma;        // tile staged by TMA boxes: layout [segment][row][channel][4nq]
+  int segoff4[RB_MAXSEG];  // first 16-byte unit of each segment's rows (TMA layout)
+  int rows_total;
+};
+
+// TMA descriptors of the feature maps: per level one 3-D tensor (W, H, N*C planes) and one
+// descriptor per box width 4*nq floats (nq = 1..16), box = (4nq, 1 row, RB_BOXC planes).  A box
+// lands in shared memory as [RB_BOXC][4nq]: consecutive channels' strips are contiguous, so the
+// strip loads of a warp are one conflict-free 512-byte run.  Levels whose rows are not 16-byte
+// multiples (W % 4 != 0) cannot be TMA tensors and keep the cp.async path.
+constexpr int RB_TMA_LEVELS = 5;
+constexpr int RB_TMA_NQ = 16;
+constexpr int RB_BOXC = 8;
+struct RbMaps {
+  CUtensorMap m[RB_TMA_LEVELS][RB_TMA_NQ];
+  int ok[RB_TMA_LEVELS];
 };
 
 template <int NT, int MINB>
 __global__ void __launch_bounds__(NT, MINB)
 rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw) {
-  extern __shared__ __align__(16) unsigned char rt_smem[];
+                   float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw,
+                   const __grid_constant__ RbMaps maps) {
+  extern __shared__ __align__(128) unsigned char rt_smem[];
   __shared__ RbPlan plan;
   __shared__ RbGeo geo;
   __shared__ int s_fin[2];
+  __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
@@ -410,6 +442,7 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int H = lv.H[level], W = lv.W[level];
   const size_t HW = (size_t)H * W;
   const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+  if (tid == 0) rp_mbar_init(&s_bar, 1);
 
   // ---- band plan of the RoI (CTA-uniform) ----------------------------------------------------
   int ok = rb_axis_candidate(g.bh, g.gh, PH, H) && rb_axis_candidate(g.bw, g.gw, PW, W);
@@ -441,14 +474,47 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
       // channel pitch in 16-byte units, == nq (mod 8): the strips of consecutive channels
       // continue the banks
       ge.chp4 = R * ge.nq + ((ge.nq - R * ge.nq) & 7);
-      if (ge.ok && (4 / ge.vecw) * ge.nq <= 32) {
-        rb_plan_chunk(smem_floats, 4 * ge.chp4 + PH * ge.vp, ge.nq, nch, PH, NT, &ge.cc,
-                      &ge.nseg);
-        ge.ok = ge.cc >= 1;
-      } else {
-        ge.ok = 0;
+      ge.tma = 0;
+      ge.segoff4[0] = ge.segoff4[1] = 0;
+      ge.rows_total = R;
+      if (ge.ok && level < RB_TMA_LEVELS && maps.ok[level]) {
+        // TMA staging: the innermost box coordinate must be a multiple of 16 bytes (measured:
+        // unaligned x raises an illegal-instruction fault), so the tile starts at x0 & ~3
+        const int nq_t = (xe - (x0 & ~3) + 3) >> 2;
+        if (nq_t <= RB_TMA_NQ) {
+          int vpu_t = nq_t;
+          while ((vpu_t & 7) != 3 && (vpu_t & 7) != 5) ++vpu_t;
+          int cc_t = 0, nseg_t = 1;
+          rb_plan_chunk(smem_floats, (R + 4) * 4 * nq_t + PH * 4 * vpu_t, nq_t, nch, PH, NT, &cc_t,
+                        &nseg_t, RB_BOXC);
+          if (cc_t >= RB_BOXC) {
+            ge.tma = 1;
+            ge.xa0 = x0 & ~3;
+            ge.nq = nq_t;
+            ge.vp = 4 * vpu_t;
+            ge.cc = cc_t;
+            ge.nseg = nseg_t;
+          }
+        }
       }
-      if (ge.ok) rb_plan_segments(&plan, PH, ge.nseg);
+      if (ge.tma) {
+        rb_plan_segments(&plan, PH, ge.nseg);
+        int acc = 0;
+        for (int sg = 0; sg < ge.nseg; ++sg) {
+          ge.segoff4[sg] = acc * ge.cc * ge.nq;
+          acc += plan.seg_rows[sg];
+        }
+        ge.rows_total = acc;
+      } else {
+        if (ge.ok && (4 / ge.vecw) * ge.nq <= 32) {
+          rb_plan_chunk(smem_floats, 4 * ge.chp4 + PH * ge.vp, ge.nq, nch, PH, NT, &ge.cc,
+                        &ge.nseg);
+          ge.ok = ge.cc >= 1;
+        } else {
+          ge.ok = 0;
+        }
+        if (ge.ok) rb_plan_segments(&plan, PH, ge.nseg);
+      }
       geo = ge;
     }
     __syncthreads();
@@ -474,12 +540,16 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   // 3-tap x bands (every RoI narrower than 28 feature pixels): skip the 4th load
   const int tap3 = __syncthreads_and(tid >= PW || plan.xw[tid].w == 0.f);
 
-  float* tile = reinterpret_cast<float*>(rt_smem);
+  // TMA boxes need a 128-byte aligned destination; the dynamic window itself is only 16-byte
+  // aligned, so the tile starts at the next 128-byte boundary (the launch adds the slack)
+  float* tile = reinterpret_cast<float*>(rt_smem + ((128u - (rp_smem_addr(rt_smem) & 127u)) & 127u));
   const uint32_t tile_s = rp_smem_addr(tile);
   const int chp = 4 * chp4;
-  float* V = tile + cc * chp;
+  const int tma = geo.tma;
+  const int rp4 = tma ? cc * nq : nq;  // tile row pitch in 16-byte units
+  float* V = tile + (tma ? geo.rows_total * cc * 4 * nq : cc * chp);
   const float* src0 = lv.feat[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
-  const RbStageLane sl = rb_stage_lane(vecw, nq, W, W - xa0);
+  const RbStageLane sl = rb_stage_lane(vecw, (4 / vecw) * nq, 4 * nq, W, W - xa0);
   // x-pass mapping: groups of xg lanes (16 when PW <= 16, so a warp holds two whole V rows)
   const int xg = PW <= 16 ? 16 : PW;
   const int nslots = NT / xg;
@@ -498,18 +568,40 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     const int q = rem - ys_c * nq;
     ys_b0 = plan.seg_b0[ys_seg];
     ys_rows = plan.seg_rows[ys_seg];
-    ys_toff = ys_c * chp4 + plan.seg_r0[ys_seg] * nq + q;
+    ys_toff = tma ? geo.segoff4[ys_seg] + ys_c * nq + q : ys_c * chp4 + plan.seg_r0[ys_seg] * nq + q;
     ys_voff = (ys_c * PH + ys_b0) * vp + 4 * q;
   }
 
+  // TMA staging constants: box i = (tile row i / ng, channel group i % ng)
+  const int ng = cc / RB_BOXC;
+  const int nbox = geo.rows_total * ng;
+  const int plane0 = b * C + c_begin;
+  const int x0t = xa0;
+  const int seg1_at = nseg > 1 ? plan.seg_rows[0] : 0x7fffffff;
+  const int yseg0 = y0 + plan.seg_r0[0];
+  const int yseg1 = nseg > 1 ? y0 + plan.seg_r0[1] - plan.seg_rows[0] : 0;
+  const void* tmap = tma ? (const void*)&maps.m[level][nq - 1] : nullptr;
   auto stage = [&](int c0, int ccur) {
+    if (tma) {
+      if (tid < 32) {
+        if (tid == 0) rp_mbar_arrive_expect_tx(&s_bar, (uint32_t)nbox * (uint32_t)(RB_BOXC * 16 * nq));
+        __syncwarp();
+        for (int i = tid; i < nbox; i += 32) {
+          const int ri = i / ng, gi = i - ri * ng;
+          const int y = ri < seg1_at ? yseg0 + ri : yseg1 + ri;
+          rp_tma_load_3d(tile + (size_t)(ri * cc + gi * RB_BOXC) * 4 * nq, tmap, x0t, y,
+                         plane0 + c0 + gi * RB_BOXC, &s_bar);
+        }
+      }
+      return;
+    }
     const float* src = src0 + (size_t)c0 * HW;
     if (vecw == 4)
-      rb_stage_tile<4>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
+      rb_stage_tile<4>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     else if (vecw == 2)
-      rb_stage_tile<2>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
+      rb_stage_tile<2>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     else
-      rb_stage_tile<1>(tile_s, src, ccur, R, nq, W, HW, chp, sl);
+      rb_stage_tile<1>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
@@ -517,19 +609,23 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   stage(0, min(cc, nch));
   for (int c0 = 0; c0 < nch; c0 += cc) {
     const int ccur = min(cc, nch - c0);
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (tma)
+      rp_mbar_wait_bounded(&s_bar, (uint32_t)(c0 / cc) & 1u);
+    else
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();  // tile(c0) has landed; every thread is done with V of the previous chunk
     // ---- y-pass ------------------------------------------------------------------------------
     if (tid < nstrip && ys_c < ccur)
-      rb_ywalk(tile4 + ys_toff, nq, ys_rows, plan.mw[ys_seg], plan.wrot + ys_b0, V + ys_voff, vp);
+      rb_ywalk(tile4 + ys_toff, rp4, ys_rows, plan.mw[ys_seg], plan.wrot + ys_b0, V + ys_voff, vp);
     for (int s = tid + NT; s < nstrip; s += NT) {  // more strips than threads
       const int seg = s >= per_seg ? 1 : 0;
       const int rem = s - seg * per_seg;
       const int c = rem / nq, q = rem - c * nq;
       const int b0 = plan.seg_b0[seg];
       if (c < ccur)
-        rb_ywalk(tile4 + c * chp4 + plan.seg_r0[seg] * nq + q, nq, plan.seg_rows[seg], plan.mw[seg],
-                 plan.wrot + b0, V + (c * PH + b0) * vp + 4 * q, vp);
+        rb_ywalk(tile4 + (tma ? geo.segoff4[seg] + c * nq + q : c * chp4 + plan.seg_r0[seg] * nq + q),
+                 rp4, plan.seg_rows[seg], plan.mw[seg], plan.wrot + b0, V + (c * PH + b0) * vp + 4 * q,
+                 vp);
     }
     __syncthreads();  // V complete, tile free
     if (c0 + cc < nch) stage(c0 + cc, min(cc, nch - c0 - cc));
@@ -849,6 +945,79 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   return l;
 }
 
+// ---- TMA descriptors: encoded on the host once per (base pointer, planes, H, W), cached ---------
+typedef CUresult (*rb_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                 CUtensorMapFloatOOBfill);
+
+rb_encode_fn rb_encoder() {
+  static rb_encode_fn fn = []() -> rb_encode_fn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    return reinterpret_cast<rb_encode_fn>(p);
+  }();
+  return fn;
+}
+
+struct RbMapEntry {
+  const float* ptr;
+  long long planes;
+  int H, W, ok;
+  CUtensorMap m[RB_TMA_NQ];
+};
+
+// Fills maps->m[l] / ok[l] for level l; a small cache keeps repeated calls free of encoding.
+void rb_level_maps(RbMaps* maps, int l, const float* ptr, long long planes, int H, int W) {
+  static std::mutex mu;
+  static RbMapEntry cache[16];
+  static int next = 0;
+  maps->ok[l] = 0;
+  if (!ptr || (W & 3) || (reinterpret_cast<uintptr_t>(ptr) & 15) || planes < RB_BOXC ||
+      planes > 0x7fffffffLL)
+    return;
+  rb_encode_fn enc = rb_encoder();
+  if (!enc) return;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < 16; ++i) {
+    const RbMapEntry& e = cache[i];
+    if (e.ptr == ptr && e.planes == planes && e.H == H && e.W == W) {
+      if (e.ok) {
+        memcpy(maps->m[l], e.m, sizeof(e.m));
+        maps->ok[l] = 1;
+      }
+      return;
+    }
+  }
+  RbMapEntry& e = cache[next];
+  next = (next + 1) & 15;
+  e.ptr = ptr;
+  e.planes = planes;
+  e.H = H;
+  e.W = W;
+  e.ok = 1;
+  const cuuint64_t gdim[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+  const cuuint64_t gstride[2] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  for (int nq = 1; nq <= RB_TMA_NQ && e.ok; ++nq) {
+    const cuuint32_t box[3] = {(cuuint32_t)(4 * nq), 1, (cuuint32_t)RB_BOXC};
+    const CUresult r = enc(&e.m[nq - 1], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr),
+                           gdim, gstride, box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) e.ok = 0;
+  }
+  if (e.ok) {
+    memcpy(maps->m[l], e.m, sizeof(e.m));
+    maps->ok[l] = 1;
+  }
+}
+
 template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
@@ -921,13 +1090,18 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     if (kb > 200) kb = 200;
     const int smem = kb * 1024;
     dim3 grid((unsigned)K, (unsigned)l.csplit);
+    RbMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    if (rp_env_int("RP_ROI_TMA", 0))  // opt-in: single-buffered TMA staging measured slower (2.44 vs 2.29 ms)
+      for (int i = 0; i < lv.L && i < RB_TMA_LEVELS; ++i)
+        rb_level_maps(&maps, i, lv.feat[i], (long long)N * C, lv.H[i], lv.W[i]);
 #define RB_LAUNCH(NT_, MB_)                                                                      \
   do {                                                                                           \
     RP_CUDA_TRY(cudaFuncSetAttribute(rb_pool_fwd_kernel<NT_, MB_>,                               \
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));        \
     rb_pool_fwd_kernel<NT_, MB_><<<grid, NT_, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,     \
                                                           sampling_ratio, out, l.c_per_cta,      \
-                                                          smem / 4, gpb, gw);                    \
+                                                          (smem - 128) / 4, gpb, gw, maps);      \
   } while (0)
     switch (cfg & 3) {
       case 1: RB_LAUNCH(128, 8); break;

@@ -652,9 +652,9 @@ RT_HD void rb_plan_mword(RbPlan* p, int s, int i) {
   p->mw[s][i] = m;
 }
 
-/* y-pass of one strip: rows = the segment's rows of this strip (pitch nq RbF4), wr / v start at
+/* y-pass of one strip: rows = the segment's rows of this strip (pitch rp4 RbF4), wr / v start at
  * the segment's first bin; V rows are vp floats apart. */
-RT_HD void rb_ywalk(const RbF4* rows, int nq, int nrows, const uint32_t* mw, const RbF4* wr,
+RT_HD void rb_ywalk(const RbF4* rows, int rp4, int nrows, const uint32_t* mw, const RbF4* wr,
                     float* v, int vp) {
   RbF4 W0, W1, W2, W3;
   W0.x = W0.y = W0.z = W0.w = 0.f;
@@ -676,13 +676,13 @@ RT_HD void rb_ywalk(const RbF4* rows, int nq, int nrows, const uint32_t* mw, con
     const uint32_t m = mw[r >> 2];
     W0 = rows[0];
     RB_BINS(m & 0xffu)
-    if (r + 1 < nrows) W1 = rows[nq];
+    if (r + 1 < nrows) W1 = rows[rp4];
     RB_BINS((m >> 8) & 0xffu)
-    if (r + 2 < nrows) W2 = rows[2 * nq];
+    if (r + 2 < nrows) W2 = rows[2 * rp4];
     RB_BINS((m >> 16) & 0xffu)
-    if (r + 3 < nrows) W3 = rows[3 * nq];
+    if (r + 3 < nrows) W3 = rows[3 * rp4];
     RB_BINS(m >> 24)
-    rows += 4 * nq;
+    rows += 4 * rp4;
   }
 #undef RB_BINS
 }
@@ -690,8 +690,33 @@ RT_HD void rb_ywalk(const RbF4* rows, int nq, int nrows, const uint32_t* mw, con
 /* Channels per chunk and y segments for one RoI (CTA-uniform).  per_ch = shared-memory floats
  * one channel needs (tile + V), nq = strips per channel, nt = threads. */
 RT_HD void rb_plan_chunk(int budget_floats, int per_ch, int nq, int nch, int PH, int nt, int* cc_out,
-                         int* nseg_out) {
+                         int* nseg_out, int cmul = 1) {
   int cc_fit = per_ch > 0 ? budget_floats / per_ch : 0;
+  if (cmul > 1) { /* chunks of whole channel groups (TMA boxes); the last one may run past nch */
+    cc_fit = cc_fit / cmul * cmul;
+    const int nch_up = (nch + cmul - 1) / cmul * cmul;
+    if (cc_fit > nch_up) cc_fit = nch_up;
+    int best_cc = 0, best_seg = 1;
+    float best = -1.f;
+    for (int nseg = 1; nseg <= RB_MAXSEG && nseg <= PH; ++nseg) {
+      for (int cc = cmul; cc <= cc_fit; cc += cmul) {
+        const int items = cc * nq * nseg;
+        const int nchunk = (nch + cc - 1) / cc;
+        /* thread utilisation of a full chunk x how well the chunks cover nch */
+        const float util = (float)items / (float)((items + nt - 1) / nt * nt);
+        const float cover = (float)nch / (float)(nchunk * cc);
+        const float score = util * cover * (nseg == 1 ? 1.0f : 0.88f) * (1.0f - 0.25f / (float)cc);
+        if (score > best) {
+          best = score;
+          best_cc = cc;
+          best_seg = nseg;
+        }
+      }
+    }
+    *cc_out = best_cc;
+    *nseg_out = best_seg;
+    return;
+  }
   if (cc_fit > nch) cc_fit = nch;
   int best_cc = cc_fit, best_seg = 1;
   float best = -1.f;
