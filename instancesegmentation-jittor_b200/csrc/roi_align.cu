@@ -932,7 +932,7 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   l.threads_fwd = (l.gw * l.gpb + 31) / 32 * 32;
   // channel split: the slow grid dimension walks channel slices, so that the feature planes
   // of one slice (C/csplit of every image) are what competes for L2 at any one time
-  int cpc = rp_env_int("RP_ROI_CPC", 64);
+  int cpc = rp_env_int("RP_ROI_CPC", 128);
   if (cpc < 4) cpc = 4;
   if (cpc > C) cpc = C;
   cpc = (cpc + 3) & ~3;

@@ -180,6 +180,79 @@ class Pooler(torch.nn.Module):
 
     execute = forward
 
+    def execute_host(self, x_host, boxes_host, out_host=None, device=None):
+        """The same pooling for HOST-resident inputs, pipelined image by image.
+
+        x_host: list of per-level CPU tensors [N,C,H_l,W_l] (pinned for asynchronous copies);
+        boxes_host: list of N CPU tensors [k_i,4] (xyxy); out_host: optional pinned CPU tensor
+        [sum k_i, C, R, R].  Three streams overlap the host->device copy of image i+1, the
+        pooling launch of image i and the device->host copy of image i-1 (images are independent
+        on this path), with two device staging buffers per direction.  Forward
+        only; returns out_host after the last copy has finished."""
+        if not isinstance(self.map_levels, LevelMapper):
+            raise ValueError("execute_host supports the MASKRCNN level mapping only")
+        dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        L = len(self.scales)
+        feats = list(x_host)[:L]
+        N, C = int(feats[0].shape[0]), int(feats[0].shape[1])
+        PH, PW = (self.output_size if isinstance(self.output_size, (tuple, list))
+                  else (self.output_size, self.output_size))
+        counts = [int(b.shape[0]) for b in boxes_host]
+        K, kmax = sum(counts), max(counts + [1])
+        if out_host is None:
+            out_host = torch.empty((K, C, PH, PW), dtype=_F32).pin_memory()
+        key = (str(dev), tuple(tuple(f.shape[1:]) for f in feats), kmax, PH, PW)
+        st = getattr(self, "_host_pipe", None)
+        if st is None or st["key"] != key:
+            st = {"key": key,
+                  "feat": [[torch.empty((1,) + tuple(f.shape[1:]), dtype=_F32, device=dev) for f in feats]
+                           for _ in range(2)],
+                  "rois": [torch.zeros((kmax, 5), dtype=_F32, device=dev) for _ in range(2)],
+                  "out": [torch.empty((kmax, C, PH, PW), dtype=_F32, device=dev) for _ in range(2)],
+                  "s_in": torch.cuda.Stream(dev), "s_run": torch.cuda.Stream(dev),
+                  "s_out": torch.cuda.Stream(dev)}
+            self._host_pipe = st
+        s_in, s_run, s_out = st["s_in"], st["s_run"], st["s_out"]
+        cur = torch.cuda.current_stream(dev)
+        for s in (s_in, s_run, s_out):
+            s.wait_stream(cur)
+        ev_in = [None, None]
+        ev_run = [None, None]
+        ev_out = [None, None]
+        row = 0
+        for i in range(N):
+            b = i & 1
+            k = counts[i]
+            with torch.cuda.stream(s_in):
+                if ev_run[b] is not None:
+                    s_in.wait_event(ev_run[b])  # the staging maps of slot b have been consumed
+                for l in range(L):
+                    st["feat"][b][l].copy_(feats[l][i:i + 1], non_blocking=True)
+                if k:
+                    st["rois"][b][:k, 1:].copy_(boxes_host[i], non_blocking=True)
+                ev_in[b] = s_in.record_event()
+            with torch.cuda.stream(s_run):
+                s_run.wait_event(ev_in[b])
+                if ev_out[b] is not None:
+                    s_run.wait_event(ev_out[b])  # the staging output of slot b has been copied out
+                if k:
+                    rois = st["rois"][b][:k]
+                    levels = (self.map_levels.map_rois(rois) if L > 1
+                              else torch.zeros((k,), dtype=_I32, device=dev))
+                    pooler_forward(st["feat"][b], self.scales, rois, levels, (PH, PW),
+                                   self.sampling_ratio, out=st["out"][b][:k])
+                ev_run[b] = s_run.record_event()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_run[b])
+                if k:
+                    out_host[row:row + k].copy_(st["out"][b][:k], non_blocking=True)
+                ev_out[b] = s_out.record_event()
+            row += k
+        for s in (s_in, s_run, s_out):
+            cur.wait_stream(s)
+        s_out.synchronize()
+        return out_host
+
 
 def make_pooler(resolution, scales, sampling_ratio):
     """poolers.py:159-168 without the yacs cfg object (not installed here): pass

@@ -193,3 +193,24 @@ def test_banded_pooler_multi_level(monkeypatch):
         exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, P, 2)
         out = rp.pooler_forward([T(f) for f in feats], synth.FPN_SCALES, T(rois), T(lv), P, 2)
         _close(out.cpu().numpy(), exp)
+
+
+def test_pooler_execute_host_pipeline():
+    """Host-buffer entry (three-stream pipeline over images) == the resident-tensor call."""
+    N, C = 5, 8
+    feats = synth.fpn_features(N, C)
+    rois = synth.rois_for_images(N, 40)
+    pooler = rp.Pooler((7, 7), synth.FPN_SCALES, 2)
+    h_feats = [torch.from_numpy(f).pin_memory() for f in feats]
+    h_rois = torch.from_numpy(rois)
+    boxes_host = [h_rois[h_rois[:, 0] == i][:, 1:].contiguous() for i in range(N)]
+    boxes_host[2] = boxes_host[2][:0]  # an image without proposals
+    out = pooler.execute_host(h_feats, boxes_host)
+    bl = [rp.BoxList(b.to(DEV), (synth.IMG_W, synth.IMG_H)) for b in boxes_host]
+    with torch.no_grad():
+        ref = pooler([f.to(DEV) for f in h_feats], bl)
+    assert out.shape == ref.shape
+    np.testing.assert_array_equal(out.numpy(), ref.cpu().numpy())
+    # second call reuses the staging buffers
+    out2 = pooler.execute_host(h_feats, boxes_host)
+    np.testing.assert_array_equal(out2.numpy(), ref.cpu().numpy())
