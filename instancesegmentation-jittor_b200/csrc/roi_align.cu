@@ -416,13 +416,13 @@ template <int NT, int MINB>
 __global__ void __launch_bounds__(NT, MINB)
 rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw,
+                   float* __restrict__ out, int c_per_cta, int smem_floats, int gpb, int gw, int nbuf,
                    const __grid_constant__ RbMaps maps) {
   extern __shared__ __align__(128) unsigned char rt_smem[];
   __shared__ RbPlan plan;
   __shared__ RbGeo geo;
   __shared__ int s_fin[2];
-  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ __align__(8) uint64_t s_bar[2];
 
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
@@ -442,7 +442,10 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int H = lv.H[level], W = lv.W[level];
   const size_t HW = (size_t)H * W;
   const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
-  if (tid == 0) rp_mbar_init(&s_bar, 1);
+  if (tid == 0) {
+    rp_mbar_init(&s_bar[0], 1);
+    rp_mbar_init(&s_bar[1], 1);
+  }
 
   // ---- band plan of the RoI (CTA-uniform) ----------------------------------------------------
   int ok = rb_axis_candidate(g.bh, g.gh, PH, H) && rb_axis_candidate(g.bw, g.gw, PW, W);
@@ -485,8 +488,8 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           int vpu_t = nq_t;
           while ((vpu_t & 7) != 3 && (vpu_t & 7) != 5) ++vpu_t;
           int cc_t = 0, nseg_t = 1;
-          rb_plan_chunk(smem_floats, (R + 4) * 4 * nq_t + PH * 4 * vpu_t, nq_t, nch, PH, NT, &cc_t,
-                        &nseg_t, RB_BOXC);
+          rb_plan_chunk(smem_floats, nbuf * (R + 4) * 4 * nq_t + PH * 4 * vpu_t, nq_t, nch, PH, NT,
+                        &cc_t, &nseg_t, RB_BOXC);
           if (cc_t >= RB_BOXC) {
             ge.tma = 1;
             ge.xa0 = x0 & ~3;
@@ -507,7 +510,7 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
         ge.rows_total = acc;
       } else {
         if (ge.ok && (4 / ge.vecw) * ge.nq <= 32) {
-          rb_plan_chunk(smem_floats, 4 * ge.chp4 + PH * ge.vp, ge.nq, nch, PH, NT, &ge.cc,
+          rb_plan_chunk(smem_floats, nbuf * 4 * ge.chp4 + PH * ge.vp, ge.nq, nch, PH, NT, &ge.cc,
                         &ge.nseg);
           ge.ok = ge.cc >= 1;
         } else {
@@ -547,7 +550,8 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int chp = 4 * chp4;
   const int tma = geo.tma;
   const int rp4 = tma ? cc * nq : nq;  // tile row pitch in 16-byte units
-  float* V = tile + (tma ? geo.rows_total * cc * 4 * nq : cc * chp);
+  const int tsz = tma ? geo.rows_total * cc * 4 * nq : cc * chp;  // floats per tile buffer
+  float* V = tile + nbuf * tsz;
   const float* src0 = lv.feat[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
   const RbStageLane sl = rb_stage_lane(vecw, (4 / vecw) * nq, 4 * nq, W, W - xa0);
   // x-pass mapping: groups of xg lanes (16 when PW <= 16, so a warp holds two whole V rows)
@@ -581,40 +585,52 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int yseg0 = y0 + plan.seg_r0[0];
   const int yseg1 = nseg > 1 ? y0 + plan.seg_r0[1] - plan.seg_rows[0] : 0;
   const void* tmap = tma ? (const void*)&maps.m[level][nq - 1] : nullptr;
-  auto stage = [&](int c0, int ccur) {
+  auto stage = [&](int c0, int ccur, int buf) {
     if (tma) {
       if (tid < 32) {
-        if (tid == 0) rp_mbar_arrive_expect_tx(&s_bar, (uint32_t)nbox * (uint32_t)(RB_BOXC * 16 * nq));
+        uint64_t* bar = &s_bar[buf];
+        if (tid == 0) rp_mbar_arrive_expect_tx(bar, (uint32_t)nbox * (uint32_t)(RB_BOXC * 16 * nq));
         __syncwarp();
+        float* dst = tile + buf * tsz;
         for (int i = tid; i < nbox; i += 32) {
           const int ri = i / ng, gi = i - ri * ng;
           const int y = ri < seg1_at ? yseg0 + ri : yseg1 + ri;
-          rp_tma_load_3d(tile + (size_t)(ri * cc + gi * RB_BOXC) * 4 * nq, tmap, x0t, y,
-                         plane0 + c0 + gi * RB_BOXC, &s_bar);
+          rp_tma_load_3d(dst + (size_t)(ri * cc + gi * RB_BOXC) * 4 * nq, tmap, x0t, y,
+                         plane0 + c0 + gi * RB_BOXC, bar);
         }
       }
       return;
     }
     const float* src = src0 + (size_t)c0 * HW;
+    const uint32_t dst_s = tile_s + 4u * (uint32_t)(buf * tsz);
     if (vecw == 4)
-      rb_stage_tile<4>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
+      rb_stage_tile<4>(dst_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     else if (vecw == 2)
-      rb_stage_tile<2>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
+      rb_stage_tile<2>(dst_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     else
-      rb_stage_tile<1>(tile_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
+      rb_stage_tile<1>(dst_s, src, ccur, R, 4 * nq, W, HW, chp, sl);
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
-  const RbF4* tile4 = reinterpret_cast<const RbF4*>(tile);
-  stage(0, min(cc, nch));
-  for (int c0 = 0; c0 < nch; c0 += cc) {
+  const int tsz4 = tsz / 4;
+  stage(0, min(cc, nch), 0);
+  for (int c0 = 0, j = 0; c0 < nch; c0 += cc, ++j) {
     const int ccur = min(cc, nch - c0);
-    if (tma)
-      rp_mbar_wait_bounded(&s_bar, (uint32_t)(c0 / cc) & 1u);
-    else
+    const bool more = c0 + cc < nch;
+    const int buf = nbuf == 2 ? (j & 1) : 0;
+    // double-buffered: the next chunk's copies are in flight during this chunk's y- and x-pass
+    // (its buffer was last read by the y-pass before the previous chunk's second barrier)
+    if (nbuf == 2 && more) stage(c0 + cc, min(cc, nch - c0 - cc), buf ^ 1);
+    if (tma) {
+      rp_mbar_wait_bounded(&s_bar[buf], (uint32_t)(nbuf == 2 ? (j >> 1) : j) & 1u);
+    } else if (nbuf == 2 && more) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
     __syncthreads();  // tile(c0) has landed; every thread is done with V of the previous chunk
     // ---- y-pass ------------------------------------------------------------------------------
+    const RbF4* tile4 = reinterpret_cast<const RbF4*>(tile) + buf * tsz4;
     if (tid < nstrip && ys_c < ccur)
       rb_ywalk(tile4 + ys_toff, rp4, ys_rows, plan.mw[ys_seg], plan.wrot + ys_b0, V + ys_voff, vp);
     for (int s = tid + NT; s < nstrip; s += NT) {  // more strips than threads
@@ -628,7 +644,7 @@ rb_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                  vp);
     }
     __syncthreads();  // V complete, tile free
-    if (c0 + cc < nch) stage(c0 + cc, min(cc, nch - c0 - cc));
+    if (nbuf == 1 && more) stage(c0 + cc, min(cc, nch - c0 - cc), 0);
     // ---- x-pass ------------------------------------------------------------------------------
     if (xactive) {
       const float* v = V + slot * vp + xo;
@@ -1089,6 +1105,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     if (kb < 16) kb = 16;
     if (kb > 200) kb = 200;
     const int smem = kb * 1024;
+    const int nbuf = rp_env_int("RP_ROI_BAND_NBUF", 1) == 2 ? 2 : 1;  // double buffering measured slower (smaller chunks)
     dim3 grid((unsigned)K, (unsigned)l.csplit);
     RbMaps maps;
     memset(&maps, 0, sizeof(maps));
@@ -1101,7 +1118,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));        \
     rb_pool_fwd_kernel<NT_, MB_><<<grid, NT_, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,     \
                                                           sampling_ratio, out, l.c_per_cta,      \
-                                                          (smem - 128) / 4, gpb, gw, maps);      \
+                                                          (smem - 128) / 4, gpb, gw, nbuf, maps); \
   } while (0)
     switch (cfg & 3) {
       case 1: RB_LAUNCH(128, 8); break;

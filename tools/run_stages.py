@@ -1,0 +1,94 @@
+"""Run every other stage of the path once or twice at its BASELINE configuration (GPU box; used
+under ncu for per-kernel captures, and plain for a timing table).
+
+    python tools/run_stages.py [reps]
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import roipath_b200 as rp  # noqa: E402
+from tests import synth  # noqa: E402
+
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+dev = torch.device("cuda", 0)
+T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def timed(name, fn, nbytes=None):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    print("%-44s %8.3f ms%s" % (name, ms, ("  %7.0f GB/s" % (nbytes / ms / 1e6)) if nbytes else ""), flush=True)
+
+
+# Pooler backward, train configuration: 16 images x 512 RoIs at 7x7 (box head), 256 channels
+N = 16
+shapes = synth.fpn_shapes(N, 256)
+rois = T(synth.rois_for_images(N, 512))
+levels = rp.LevelMapper(2, 5).map_rois(rois)
+for res in (7, 14):
+    k = rois.shape[0] if res == 7 else 2048
+    d = torch.randn((k, 256, res, res), device=dev)
+    grad_bytes = sum(int(np.prod(s)) for s in shapes) * 4
+    timed("pooler bwd %dx%d, %d RoIs" % (res, res, k),
+          lambda: rp.pooler_backward(d, rois[:k], levels[:k], shapes, synth.FPN_SCALES, 2),
+          d.numel() * 4 + grad_bytes)
+    del d
+
+# greedy NMS, 8 images x 20k boxes
+B, n = 8, 20000
+bs, ss = zip(*[synth.nms_boxes(n, 7 + i)[:2] for i in range(B)])
+boxes, scores = T(np.concatenate(bs)), T(np.concatenate(ss))
+offs = T((np.arange(B + 1) * n).astype(np.int32))
+timed("nms 8 x 20000, thr 0.7", lambda: rp.nms_batched(boxes, scores, offs, 0.7, n_max=n))
+
+# Yolact post, batch 64
+priors = synth.yolact_priors()
+B = 64
+base = []
+for i in range(4):
+    loc, conf, mask, proto = synth.yolact_image(100 + i, priors)
+    bx = rp.decode(T(loc), T(priors)).cpu().numpy()
+    fg = np.ascontiguousarray(conf[:, 1:].T)
+    kp = np.nonzero(fg.max(0) > np.float32(0.05))[0]
+    base.append((bx[kp], mask[kp], np.ascontiguousarray(fg[:, kp]), proto))
+cands = [base[i % 4] for i in range(B)]
+offs_np = np.concatenate([[0], np.cumsum([c[0].shape[0] for c in cands])]).astype(np.int32)
+yb, yc = T(np.concatenate([c[0] for c in cands])), T(np.concatenate([c[1] for c in cands]))
+ys = T(np.concatenate([c[2] for c in cands], 1))
+yp = T(np.stack([c[3] for c in cands]))
+yo = T(offs_np)
+masks_buf = torch.empty((B * 100, 550, 550), dtype=torch.uint8, device=dev)
+slot_off = T((np.arange(B + 1) * 100).astype(np.int32))
+res = {}
+
+
+def fnms():
+    res["r"] = rp.fast_nms_batched(yb, yc, ys, yo, 0.5, 200, 100, n_max=int(np.diff(offs_np).max()))
+
+
+timed("fast_nms batch 64", fnms)
+r = res["r"]
+timed("mask_assemble batch 64, 550x550",
+      lambda: rp.mask_assemble(yp, r["mask"].reshape(B * 100, -1), r["box"].reshape(B * 100, 4), 550, 550,
+                               True, det_offsets=slot_off, out=masks_buf),
+      B * (138 * 138 * 32 * 4) + B * 100 * 550 * 550)
+del masks_buf, yp
+
+# paste-back, 100 instances at 1333x800
+pm, pb = synth.paste_inputs(100, 200)
+pmt, pbt = T(pm), T(pb)
+pout = torch.empty((100, 800, 1333), dtype=torch.uint8, device=dev)
+timed("paste_masks 100 x 800x1333", lambda: rp.paste_masks(pmt, pbt, 800, 1333, out=pout),
+      100 * 28 * 28 * 4 + 100 * 800 * 1333)

@@ -24,6 +24,8 @@ def main():
     ap.add_argument("--kb", default="32,40,56")
     ap.add_argument("--cpc", default="64,128,256")
     ap.add_argument("--cfg", default="0")
+    ap.add_argument("--nbuf", default="2")
+    ap.add_argument("--tma", default="0")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     shapes = synth.fpn_shapes(a.images, 256)
@@ -53,15 +55,18 @@ def main():
     ref = out.clone()
     print("v3 default: %.3f ms  %.2f M RoIs/s" % (ms, K / ms / 1e3), flush=True)
     os.environ["RP_ROI_IMPL"] = "4"
-    for cfg, kb, cpc in itertools.product(a.cfg.split(","), a.kb.split(","), a.cpc.split(",")):
+    for tma, nbuf, cfg, kb, cpc in itertools.product(a.tma.split(","), a.nbuf.split(","), a.cfg.split(","),
+                                                     a.kb.split(","), a.cpc.split(",")):
+        os.environ["RP_ROI_TMA"] = tma
+        os.environ["RP_ROI_BAND_NBUF"] = nbuf
         os.environ["RP_ROI_BAND_CFG"] = cfg
         os.environ["RP_ROI_BAND_SMEM_KB"] = kb
         os.environ["RP_ROI_CPC"] = cpc
         out.fill_(7e30)
         ms = run("v4")
         err = float(((out - ref).abs() / (ref.abs() + 1)).max())
-        print("v4 cfg=%s kb=%s cpc=%s : %.3f ms  %.2f M RoIs/s  out-only %.0f GB/s  max rel diff vs v3 %.2e"
-              % (cfg, kb, cpc, ms, K / ms / 1e3, out.numel() * 4 / ms / 1e6, err), flush=True)
+        print("v4 tma=%s nbuf=%s cfg=%s kb=%s cpc=%s : %.3f ms  %.2f M RoIs/s  out-only %.0f GB/s  max rel diff vs v3 %.2e"
+              % (tma, nbuf, cfg, kb, cpc, ms, K / ms / 1e3, out.numel() * 4 / ms / 1e6, err), flush=True)
 
 
 if __name__ == "__main__":
