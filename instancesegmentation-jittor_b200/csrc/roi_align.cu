@@ -781,7 +781,7 @@ __device__ __forceinline__ void rt_direct_backward(float* plane, int H, int W, c
 __global__ void __launch_bounds__(RT_THREADS)
 rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   const float* __restrict__ dout, int c_per_cta, int vs_floats) {
+                   const float* __restrict__ dout, int c_per_cta, int vs_floats, int cc_cap) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   RtAxisPlan* py = reinterpret_cast<RtAxisPlan*>(rt_smem);
   RtAxisPlan* px = py + 1;
@@ -814,11 +814,11 @@ rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   if (tiled && (R == 0 || tw == 0)) return;
   const int twp = tw | 1;
   int cc_max = tiled ? (vs_floats / (PH * twp)) : 0;
-  if (cc_max > RT_CC_CAP) cc_max = RT_CC_CAP;
+  if (cc_max > cc_cap) cc_max = cc_cap;
   cc_max &= ~3;
   if (cc_max < 4) {
     const int total = (c_end - c_begin) * P;
-    for (int i = tid; i < total; i += RT_THREADS) {
+    for (int i = tid; i < total; i += blockDim.x) {
       const int c = i / P;
       const int rem = i - c * P;
       const int ph = rem / PW, pw = rem - ph * PW;
@@ -837,14 +837,14 @@ rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     {
       const float* src = dout_k + (size_t)c0 * P;
       const int nfl = cc * P;
-      for (int i = tid; i < nfl; i += RT_THREADS) d_s[i] = __ldg(src + i);
+      for (int i = tid; i < nfl; i += blockDim.x) d_s[i] = __ldg(src + i);
     }
     __syncthreads();
     // ---- phase A: transpose of the column sweep: dout[c][ph][:] -> Hs[c][ph][x] ------------
     {
       const int nq = (cc + RT_U2 - 1) / RT_U2;
       const int items = nq * PH;
-      for (int it = tid; it < items; it += RT_THREADS) {
+      for (int it = tid; it < items; it += blockDim.x) {
         const int q = it / PH;
         const int ph = it - q * PH;
         int nvalid = (cc - q + nq - 1) / nq;
@@ -859,7 +859,7 @@ rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     {
       const int nq = (cc + RT_U1 - 1) / RT_U1;
       const int items = nq * tw;
-      for (int it = tid; it < items; it += RT_THREADS) {
+      for (int it = tid; it < items; it += blockDim.x) {
         const int q = it / tw;
         const int x = it - q * tw;
         int nvalid = (cc - q + nq - 1) / nq;
@@ -920,7 +920,7 @@ __global__ void rt_level_map_area_kernel(const float* __restrict__ rois,
 // host side
 // ------------------------------------------------------------------------------------------
 struct RtLaunch {
-  int csplit, c_per_cta, vs_floats, tile_floats, U;
+  int csplit, c_per_cta, vs_floats, tile_floats, U, bwd_cc, bwd_threads;
   int gpb, gw, threads_fwd;  // forward: thread groups per CTA, lanes per group (>= PW), CTA size
   size_t smem, smem_fwd;
 };
@@ -928,7 +928,10 @@ struct RtLaunch {
 RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   RtLaunch l;
   // backward: H buffer, enough for RT_CC_CAP channels of a 27-wide tile at 14 bins
-  l.vs_floats = rp_env_int("RP_ROI_VS_FLOATS", 8192) & ~3;
+  // measured (tools/sweep_bwd.py, 16 images x 512 RoIs): 7x7 is fastest with 128 threads and a 16 KB
+  // H buffer (2.12 vs 2.68 ms), 14x14 with 256 threads and 16 channels per chunk (1.59 vs 1.69 ms)
+  const bool small_bins = PH * PW <= 64;
+  l.vs_floats = rp_env_int("RP_ROI_VS_FLOATS", small_bins ? 4096 : 8192) & ~3;
   const int min_vs = PH * 3 * 4;  // at least 4 channels of a 2-wide tile
   if (l.vs_floats < min_vs) l.vs_floats = min_vs;
   // forward: raw feature tile buffer (48 KB => 4 resident CTAs per SM)
@@ -954,8 +957,16 @@ RtLaunch rt_plan_launch(int K, int C, int PH, int PW) {
   cpc = (cpc + 3) & ~3;
   l.c_per_cta = cpc;
   l.csplit = (C + cpc - 1) / cpc;
+  l.bwd_cc = rp_env_int("RP_ROI_BWD_CC", small_bins ? RT_CC_CAP : 16);
+  if (l.bwd_cc < 4) l.bwd_cc = 4;
+  if (l.bwd_cc > RT_CC_CAP) l.bwd_cc = RT_CC_CAP;
+  l.bwd_cc &= ~3;
+  l.bwd_threads = rp_env_int("RP_ROI_BWD_THREADS", small_bins ? 128 : RT_THREADS);
+  if (l.bwd_threads < 64) l.bwd_threads = 64;
+  if (l.bwd_threads > RT_THREADS) l.bwd_threads = RT_THREADS;
+  l.bwd_threads &= ~31;
   l.smem = rp_align_up(2 * sizeof(RtAxisPlan), 16) + sizeof(float) * (size_t)l.vs_floats +
-           sizeof(float) * (size_t)RT_CC_CAP * PH * PW;
+           sizeof(float) * (size_t)l.bwd_cc * PH * PW;
   l.smem_fwd = sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX +
                sizeof(float) * (size_t)l.tile_floats;
   return l;
@@ -1161,9 +1172,9 @@ int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* 
   RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)l.smem));
   dim3 grid((unsigned)K, (unsigned)l.csplit);
-  rt_pool_bwd_kernel<<<grid, RT_THREADS, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
-                                                       sampling_ratio, dout, l.c_per_cta,
-                                                       l.vs_floats);
+  rt_pool_bwd_kernel<<<grid, l.bwd_threads, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                          sampling_ratio, dout, l.c_per_cta,
+                                                          l.vs_floats, l.bwd_cc);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }
