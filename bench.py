@@ -251,6 +251,18 @@ def extras(rp, torch, dev):
         return float(np.median(ts))
 
     T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    # --- Pooler backward, train shape of BASELINE configs[2]: 16 images x 512 RoIs (7x7, box head)
+    #     and 2048 positives (14x14, mask head); bytes = dout read + every level gradient written
+    shapes = synth.fpn_shapes(IMAGES_PER_GPU, CHANNELS)
+    rois_b = T(synth.rois_for_images(IMAGES_PER_GPU, 512))
+    lv_b = rp.LevelMapper(2, 5).map_rois(rois_b)
+    grad_bytes = sum(int(np.prod(sh)) for sh in shapes) * 4
+    for res, k in ((7, int(rois_b.shape[0])), (14, 2048)):
+        d = torch.randn((k, CHANNELS, res, res), device=dev)
+        ms = med(lambda: rp.pooler_backward(d, rois_b[:k], lv_b[:k], shapes, synth.FPN_SCALES, SAMPLING), n=5)
+        out["pooler_bwd_%dx%d_ms" % (res, res)] = ms
+        out["pooler_bwd_%dx%d_gbs" % (res, res)] = (d.numel() * 4 + grad_bytes) / (ms * 1e-3) / 1e9
+        del d
     # --- NMS sweep, batch 8 (BASELINE configs[1]); thr 0.7
     for n in (2000, 5000, 10000, 20000):
         B = 8

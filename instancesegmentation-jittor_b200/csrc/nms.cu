@@ -12,13 +12,15 @@
 //   2. sort    ONE stable LSD radix sort over the whole batch (cub::DeviceRadixSort) -- the
 //              stable descending score order of jt.argsort; ties keep ascending index
 //   3. gather  boxes (+area, +label) into rank order
-//   4. mask    upper-triangular suppression bit matrix in 64x64 tiles: lanes = 32 consecutive
-//              rows, the 64 column boxes of the tile broadcast from shared memory.  The IoU
+//   4. bands   ranks are processed in bands of <= 1024 boxes (see "Banded greedy NMS" below):
+//              per band one `resolve` launch (greedy inside the band from its diagonal bit block,
+//              warp fixpoint on REDUX OR reductions) and one GPU-wide `suppress` launch (every
+//              later, still alive box against the boxes the band kept; early exit).  The IoU
 //              test is exact: a pair is rejected without a division when inter < t_lo * union
 //              (t_lo just below the threshold), everything else takes the IEEE division.
-//   5. scan    one CTA per problem walks the ranks in 64-box chunks: a single thread resolves
-//              the chunk against its 64x64 diagonal block, all threads OR the kept rows into
-//              the removed bitmap; stops at max_keep.
+//              No n x n/64 bit matrix exists; workspace is O(n).
+//   5. finish  ordered compaction of the kept flags: keep indices in descending-score order (or
+//              ascending index for the cython variant), n_keep, truncation at max_keep.
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
