@@ -380,6 +380,86 @@ paste_masks_kernel(const float* __restrict__ masks, const float* __restrict__ bo
   }
 }
 
+// Flat variant: the instance plane [im_h * im_w] is written as 16-byte words regardless of the
+// row length (1333-byte rows make 3 rows in 4 unaligned for word stores in the band kernel above).
+// CTA = (PF_CHUNK bytes of the plane, instance).  Chunks whose rows miss the pasted box -- most of
+// them: a box covers a few percent of the image -- are a pure streaming zero fill; the others
+// evaluate the same per-pixel arithmetic as paste_masks_kernel.  Needs a 16-byte aligned output
+// and im_h * im_w % 16 == 0.
+constexpr int PF_CHUNK = 16384;
+
+__global__ void __launch_bounds__(PM_THREADS)
+paste_masks_flat_kernel(const float* __restrict__ masks, const float* __restrict__ boxes, int M,
+                        int im_h, int im_w, float thresh, int padding, float scale,
+                        uint8_t* __restrict__ out) {
+  __shared__ float pad_s[PM_MAXP * PM_MAXP];
+  const int tid = threadIdx.x;
+  const int i = blockIdx.y;
+  const int P = M + 2 * padding;
+  const float* b = boxes + (size_t)i * 4;
+  float w_half = (b[2] - b[0]) * .5f;
+  float h_half = (b[3] - b[1]) * .5f;
+  const float x_c = (b[2] + b[0]) * .5f;
+  const float y_c = (b[3] + b[1]) * .5f;
+  w_half *= scale;
+  h_half *= scale;
+  const int bx0 = (int)(x_c - w_half), bx1 = (int)(x_c + w_half);
+  const int by0 = (int)(y_c - h_half), by1 = (int)(y_c + h_half);
+  int w = bx1 - bx0 + 1, h = by1 - by0 + 1;
+  if (w < 1) w = 1;
+  if (h < 1) h = 1;
+  const int x_0 = max(bx0, 0), x_1 = min(min(bx1 + 1, im_w), bx0 + w);
+  const int y_0 = max(by0, 0), y_1 = min(min(by1 + 1, im_h), by0 + h);
+  const int plane = im_h * im_w;
+  const int f0 = blockIdx.x * PF_CHUNK;
+  const int f1 = min(plane, f0 + PF_CHUNK);
+  uint8_t* out_i = out + (size_t)i * plane;
+  const int Yfirst = f0 / im_w, Ylast = (f1 - 1) / im_w;
+  const bool touches = (Yfirst < y_1) && (Ylast >= y_0) && (x_0 < x_1);
+  if (!touches) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) __stcs(reinterpret_cast<uint4*>(out_i + f), z);
+    return;
+  }
+  for (int t = tid; t < P * P; t += PM_THREADS) {
+    const int py = t / P, px = t - py * P;
+    const int my = py - padding, mx = px - padding;
+    pad_s[t] = (my >= 0 && my < M && mx >= 0 && mx < M) ? __ldg(masks + ((size_t)i * M + my) * M + mx) : 0.f;
+  }
+  __syncthreads();
+  const float sy = (float)P / (float)h, sx = (float)P / (float)w;
+  for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) {
+    int Y = f / im_w;
+    int X = f - Y * im_w;
+    uint32_t word[4] = {0u, 0u, 0u, 0u};
+    // rows of this 16-byte group: Y (and Y + 1 when the group wraps)
+    if ((Y < y_1 && Y >= y_0 && X < x_1 && X + 15 >= x_0) || (X + 15 >= im_w && Y + 1 < y_1 && Y + 1 >= y_0)) {
+      MkTap yt = mk_tap(Y - by0, sy, P);
+      bool row_in = Y >= y_0 && Y < y_1;
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        if (row_in && X >= x_0 && X < x_1) {
+          const MkTap xt = mk_tap(X - bx0, sx, P);
+          const float* r0 = pad_s + yt.i0 * P;
+          const float* r1 = pad_s + yt.i1 * P;
+          const float top = xt.w0 * r0[xt.i0] + xt.w1 * r0[xt.i1];
+          const float bot = xt.w0 * r1[xt.i0] + xt.w1 * r1[xt.i1];
+          const float v = yt.w0 * top + yt.w1 * bot;
+          const bool on = (thresh >= 0.f) ? (v > thresh) : ((v * 255.0f) != 0.0f);
+          if (on) word[q >> 2] |= 1u << (8 * (q & 3));
+        }
+        if (++X == im_w) {
+          X = 0;
+          ++Y;
+          row_in = Y >= y_0 && Y < y_1;
+          if (row_in) yt = mk_tap(Y - by0, sy, P);
+        }
+      }
+    }
+    __stcs(reinterpret_cast<uint4*>(out_i + f), make_uint4(word[0], word[1], word[2], word[3]));
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -455,6 +535,15 @@ int rp_paste_masks(const float* masks, const float* boxes, int n, int M, int im_
   if (P > PM_MAXP) return RP_E_LIMIT;
   if (n > 65535) return RP_E_LIMIT;
   const float scale = (float)((double)P / (double)M);
+  const long long plane = (long long)im_h * im_w;
+  if ((plane & 15) == 0 && im_w >= 16 && plane < 0x7fff0000LL && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+      rp_env_int("RP_PASTE_FLAT", 1)) {
+    dim3 grid((unsigned)((plane + PF_CHUNK - 1) / PF_CHUNK), (unsigned)n);
+    paste_masks_flat_kernel<<<grid, PM_THREADS, 0, (cudaStream_t)stream>>>(masks, boxes, M, im_h, im_w,
+                                                                            thresh, padding, scale, out);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
   dim3 grid((unsigned)((im_h + PM_ROWS - 1) / PM_ROWS), (unsigned)n);
   paste_masks_kernel<<<grid, PM_THREADS, 0, (cudaStream_t)stream>>>(masks, boxes, M, im_h, im_w,
                                                                      thresh, padding, scale, out);

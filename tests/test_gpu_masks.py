@@ -27,7 +27,7 @@ def test_mask_select_sigmoid_bit_exact():
     np.testing.assert_array_equal(got[:, 0], oracle.mask_select_sigmoid(logits, labels))
 
 
-@pytest.mark.parametrize("hw", [(800, 1333), (427, 641)])
+@pytest.mark.parametrize("hw", [(800, 1333), (427, 641), (64, 48), (33, 16), (600, 1000)])
 @pytest.mark.parametrize("thresh", [0.5, -1.0])
 def test_paste_bit_exact(hw, thresh):
     h, w = hw
