@@ -81,7 +81,7 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
                      const float* __restrict__ boxes, const int* __restrict__ det_offsets,
                      int m_total, int ph, int pw, int D, int out_h, int out_w, int crop,
                      int tiles_x, int fp_rows_max, int fp_cols_max,
-                     uint8_t* __restrict__ out_masks) {
+                     uint8_t* __restrict__ out_masks, int prefilled) {
   extern __shared__ __align__(16) float ma_smem[];
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
@@ -96,6 +96,19 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
   const MkTap ty0 = mk_tap(Y0, sy, ph), ty1 = mk_tap(Y1, sy, ph);
   const MkTap tx0 = mk_tap(X0, sx, pw), tx1 = mk_tap(X1, sx, pw);
   const int fy0 = ty0.i0, fy1 = ty1.i1, fx0 = tx0.i0, fx1 = tx1.i1;
+  if (prefilled && crop) {
+    // the output was zero-filled by the caller: a tile no detection's crop box reaches has
+    // nothing to write and does not even stage the prototypes
+    int any = 0;
+    for (int j = j0 + tid; j < j1; j += MA_THREADS) {
+      const float* bxj = boxes + (size_t)j * 4;
+      float cx1, cx2, cy1, cy2;
+      mk_sanitize(bxj[0], bxj[2], pw, 1, &cx1, &cx2);
+      mk_sanitize(bxj[1], bxj[3], ph, 1, &cy1, &cy2);
+      any |= !(!((float)fx1 >= cx1) || !((float)fx0 < cx2) || !((float)fy1 >= cy1) || !((float)fy0 < cy2));
+    }
+    if (!__syncthreads_or(any)) return;
+  }
   const int frows = fy1 - fy0 + 1, fcols = fx1 - fx0 + 1;
   const int npix = frows * fcols;
   const int pixp = (fp_rows_max * fp_cols_max) | 1;  // odd pitch: conflict-free k-major staging
@@ -148,6 +161,7 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
       }
       __syncthreads();
     }
+    if (empty && prefilled) continue;  // zeros are already there
 #pragma unroll
     for (int ry = 0; ry < 4; ++ry) {
       const int Y = Y0 + tyq * 4 + ry;
@@ -496,9 +510,15 @@ int rp_mask_assemble(const float* proto, const float* coeff, const float* boxes,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles_x = (out_w + MA_TW - 1) / MA_TW, tiles_y = (out_h + MA_TH - 1) / MA_TH;
     dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)B);
+    // With cropping most (detection, tile) pairs lie outside the crop box: zero-fill the whole
+    // output at memset speed first and let the kernel write only the tiles a box reaches (row
+    // lengths such as 550 make half of the tile rows unaligned for word stores otherwise).
+    const int prefill = crop && rp_env_int("RP_MASK_PREFILL", 1);
+    if (prefill)
+      RP_CUDA_TRY(cudaMemsetAsync(out_masks, 0, (size_t)m_total * out_h * out_w, st));
     mask_assemble_kernel<<<grid, MA_THREADS, smem, st>>>(proto, coeff, boxes, det_offsets, m_total,
                                                          ph, pw, D, out_h, out_w, crop, tiles_x,
-                                                         fr, fc, out_masks);
+                                                         fr, fc, out_masks, prefill);
     RP_LAUNCH_CHECK();
   }
   if (out_boxes) {
