@@ -155,6 +155,158 @@ fn_class_kernel(const float* __restrict__ boxes, const float* __restrict__ score
   cand_src[o] = src;
 }
 
+// ------------------------------------------------------------------------------------------
+// Fused top-k selection + FastNMS of one (class, image): replaces keys + batch-wide radix sort +
+// fn_class_kernel (the sort of all C * n scores was 60 % of FastNMS).  The CTA
+//   1. loads the class's n scores as order-reversed keys (shared-memory cache for n <= FN_CACHE),
+//   2. finds the top_k-th smallest key T by a 4-pass byte-wise radix select (256-bin shared
+//      histogram, block scan over the bins),
+//   3. collects every key < T and, in ascending candidate order, the first (top_k - #less) keys
+//      == T  -- exactly the first top_k entries of a stable descending sort,
+//   4. bitonic-sorts the <= 256 (key, candidate) pairs, and
+//   5. continues as fn_class_kernel: boxes to shared memory, column max of triu(IoU), keep.
+// ------------------------------------------------------------------------------------------
+constexpr int FN_CACHE = 6144;
+
+__device__ __forceinline__ int fn_block_excl_scan(int v, int* warp_sums, int* total) {
+  // exclusive scan of one int per thread over FN_MAX_TOPK (256) threads
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += t;
+  }
+  if (lane == 31) warp_sums[wid] = inc;
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < FN_MAX_TOPK / 32; ++w) {
+    const int sw = warp_sums[w];
+    if (w < wid) base += sw;
+    tot += sw;
+  }
+  __syncthreads();
+  *total = tot;
+  return base + inc - v;
+}
+
+__global__ void __launch_bounds__(FN_MAX_TOPK)
+fn_class_select_kernel(const float* __restrict__ boxes, const float* __restrict__ scores,
+                       const int* __restrict__ offsets, int C, int n_total, int top_k, float iou_thr,
+                       int second_threshold, float conf_thresh, uint64_t* __restrict__ keys2,
+                       int* __restrict__ vals2, float* __restrict__ cand_score,
+                       int* __restrict__ cand_src) {
+  __shared__ uint32_t kc[FN_CACHE];
+  __shared__ int hist[256];
+  __shared__ int wsum[FN_MAX_TOPK / 32];
+  __shared__ unsigned long long sel[FN_MAX_TOPK];
+  __shared__ float4 bx[FN_MAX_TOPK];
+  __shared__ float ar[FN_MAX_TOPK];
+  __shared__ int s_bin, s_kk, s_cnt;
+  const int c = blockIdx.x, b = blockIdx.y;
+  const int off = offsets[b];
+  const int n = offsets[b + 1] - off;
+  const int k = min(n, top_k);
+  const int tid = threadIdx.x;
+  const float* sc_c = scores + (size_t)c * n_total + off;
+  const bool cached = n <= FN_CACHE;
+  if (cached)
+    for (int j = tid; j < n; j += FN_MAX_TOPK) kc[j] = fn_desc_bits(sc_c[j]);
+  sel[tid] = ~0ull;
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+  auto key_at = [&](int j) -> uint32_t { return cached ? kc[j] : fn_desc_bits(sc_c[j]); };
+
+  if (n <= top_k) {
+    for (int j = tid; j < n; j += FN_MAX_TOPK) sel[j] = ((unsigned long long)key_at(j) << 32) | (uint32_t)j;
+  } else {
+    // ---- radix select: T = the k-th smallest key, kk = how many keys == T belong to the top k
+    uint32_t prefix = 0, mask = 0;
+    int kk = k;
+    for (int pass = 3; pass >= 0; --pass) {
+      hist[tid] = 0;
+      __syncthreads();
+      const int sh = 8 * pass;
+      for (int j = tid; j < n; j += FN_MAX_TOPK) {
+        const uint32_t key = key_at(j);
+        if ((key & mask) == prefix) atomicAdd(&hist[(key >> sh) & 255u], 1);
+      }
+      __syncthreads();
+      const int h = hist[tid];
+      int tot;
+      const int ex = fn_block_excl_scan(h, wsum, &tot);
+      if (ex < kk && kk <= ex + h) {
+        s_bin = tid;
+        s_kk = kk - ex;
+      }
+      __syncthreads();
+      prefix |= (uint32_t)s_bin << sh;
+      mask |= 255u << sh;
+      kk = s_kk;
+      __syncthreads();
+    }
+    const uint32_t T = prefix;
+    const int n_less = k - kk;
+    // ---- collect: all keys < T (any order), then the first kk keys == T in candidate order
+    int eq_base = 0;
+    for (int j0 = 0; j0 < n; j0 += FN_MAX_TOPK) {
+      const int j = j0 + tid;
+      uint32_t key = 0xffffffffu;
+      bool lt = false, eq = false;
+      if (j < n) {
+        key = key_at(j);
+        lt = key < T;
+        eq = key == T;
+      }
+      if (lt) sel[atomicAdd(&s_cnt, 1)] = ((unsigned long long)key << 32) | (uint32_t)j;
+      int tot;
+      const int ex = fn_block_excl_scan(eq ? 1 : 0, wsum, &tot);
+      if (eq && eq_base + ex < kk) sel[n_less + eq_base + ex] = ((unsigned long long)key << 32) | (uint32_t)j;
+      eq_base += tot;
+    }
+  }
+  __syncthreads();
+  // ---- bitonic sort of the 256 (key, candidate) pairs, ascending = descending score, stable
+  for (int size = 2; size <= FN_MAX_TOPK; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const int partner = tid ^ stride;
+      if (partner > tid) {
+        const unsigned long long a = sel[tid], d = sel[partner];
+        const bool up = (tid & size) == 0;
+        if ((a > d) == up) {
+          sel[tid] = d;
+          sel[partner] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // ---- FastNMS on the sorted top k (as fn_class_kernel)
+  const int r = tid;
+  int src = 0;
+  float sc = 0.f;
+  if (r < k) {
+    src = (int)(uint32_t)(sel[r] & 0xffffffffull);
+    const float4 p = *reinterpret_cast<const float4*>(boxes + (size_t)(off + src) * 4);
+    bx[r] = p;
+    ar[r] = rp_area_rel(p.x, p.y, p.z, p.w);
+    sc = sc_c[src];
+  }
+  __syncthreads();
+  if (r >= top_k) return;
+  bool keep = false;
+  if (r < k) {
+    keep = fn_keep_rank(bx, ar, r, iou_thr);
+    if (second_threshold) keep = keep && (sc > conf_thresh);
+  }
+  const size_t o = ((size_t)b * C + c) * top_k + r;
+  keys2[o] = ((uint64_t)(uint32_t)b << 32) | (uint64_t)fn_desc_bits(keep ? sc : -INFINITY);
+  vals2[o] = c * top_k + r;
+  cand_score[o] = keep ? sc : -INFINITY;
+  cand_src[o] = src;
+}
+
 // grid B; emits the first max_det kept candidates of the image.
 __global__ void fn_emit_kernel(const float* __restrict__ boxes, const float* __restrict__ coeff,
                                const int* __restrict__ offsets, const int* __restrict__ sorted_vals2,
@@ -349,18 +501,26 @@ int rp_fast_nms_batched(const float* boxes, const float* coeff, const float* sco
     RP_LAUNCH_CHECK();
     return RP_OK;
   }
-  const size_t n1 = (size_t)C * n_total;
-  fn_keys_kernel<<<(unsigned)((n1 + T - 1) / T), T, 0, st>>>(scores, offsets, B, C, n_total,
-                                                            w.keys_in, w.vals_in);
-  RP_LAUNCH_CHECK();
-  RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
-                                              w.vals_in, w.vals_out, (int)n1, 0,
-                                              32 + fn_bits((size_t)B * C), st));
   if (B > 65535) return RP_E_LIMIT;
-  fn_class_kernel<<<dim3((unsigned)C, (unsigned)B), FN_MAX_TOPK, 0, st>>>(
-      boxes, scores, offsets, w.vals_out, C, n_total, top_k, iou_thr, second_threshold,
-      conf_thresh, w.keys2_in, w.vals2_in, w.cand_score, w.cand_src);
-  RP_LAUNCH_CHECK();
+  if (rp_env_int("RP_FASTNMS_SELECT", 1)) {
+    // fused per-(class, image) top-k selection + FastNMS: no batch-wide sort of the C * n scores
+    fn_class_select_kernel<<<dim3((unsigned)C, (unsigned)B), FN_MAX_TOPK, 0, st>>>(
+        boxes, scores, offsets, C, n_total, top_k, iou_thr, second_threshold, conf_thresh, w.keys2_in,
+        w.vals2_in, w.cand_score, w.cand_src);
+    RP_LAUNCH_CHECK();
+  } else {
+    const size_t n1 = (size_t)C * n_total;
+    fn_keys_kernel<<<(unsigned)((n1 + T - 1) / T), T, 0, st>>>(scores, offsets, B, C, n_total,
+                                                              w.keys_in, w.vals_in);
+    RP_LAUNCH_CHECK();
+    RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
+                                                w.vals_in, w.vals_out, (int)n1, 0,
+                                                32 + fn_bits((size_t)B * C), st));
+    fn_class_kernel<<<dim3((unsigned)C, (unsigned)B), FN_MAX_TOPK, 0, st>>>(
+        boxes, scores, offsets, w.vals_out, C, n_total, top_k, iou_thr, second_threshold,
+        conf_thresh, w.keys2_in, w.vals2_in, w.cand_score, w.cand_src);
+    RP_LAUNCH_CHECK();
+  }
   const size_t n2 = (size_t)B * C * top_k;
   RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys2_in, w.keys2_out,
                                               w.vals2_in, w.vals2_out, (int)n2, 0,

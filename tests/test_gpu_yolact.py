@@ -196,3 +196,32 @@ def test_full_size_batch64_properties(priors):
     a = masks[:cnt[0]].sum(dtype=torch.int64)
     b4 = masks[det_off[4]: det_off[5]].sum(dtype=torch.int64)
     assert int(a) == int(b4) and int(a) > 0
+
+
+@pytest.mark.parametrize("n,levels", [(700, 16), (3000, 1024), (7000, 64), (260, 4)])
+def test_fast_nms_select_ties_large(n, levels):
+    """The fused top-k selection (radix select + ordered tie pick + bitonic sort) must equal the
+    first top_k entries of a stable descending sort: heavy ties, n above top_k, n above the
+    shared-memory key cache (7000), two images of different sizes in one launch."""
+    rng = np.random.default_rng(n)
+    C, D = 6, 8
+    sizes = [n, max(201, n // 3)]
+    cands = []
+    for m in sizes:
+        ctr = rng.uniform(0.1, 0.9, (m, 2)).astype(np.float32)
+        wh = rng.uniform(0.02, 0.3, (m, 2)).astype(np.float32)
+        boxes = np.concatenate([ctr - wh / 2, ctr + wh / 2], 1).astype(np.float32)
+        coeff = rng.standard_normal((m, D)).astype(np.float32)
+        scores = (np.floor(rng.uniform(0, 1, (C, m)) * levels) / levels).astype(np.float32)
+        scores[0, : m // 2] = 0.0  # a class where more than half of the candidates tie at zero
+        cands.append((boxes, coeff, scores))
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    r = rp.fast_nms_batched(T(np.concatenate([c[0] for c in cands])), T(np.concatenate([c[1] for c in cands])),
+                            T(np.concatenate([c[2] for c in cands], 1)), T(offs), 0.5, 200, 100)
+    cnt = r["count"].cpu().numpy()
+    for i, c in enumerate(cands):
+        o = oracle.fast_nms(c[0], c[1], c[2], 0.5, 200, 100)
+        assert cnt[i] == len(o[3])
+        np.testing.assert_array_equal(r["score"][i, :cnt[i]].cpu().numpy(), o[3])
+        np.testing.assert_array_equal(r["class"][i, :cnt[i]].cpu().numpy(), o[2])
+        np.testing.assert_array_equal(r["index"][i, :cnt[i]].cpu().numpy(), o[4])
