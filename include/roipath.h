@@ -104,7 +104,9 @@ RP_API int rp_pooler_backward(const float* dout, const float* rois, const int* l
  *   keep [n] int32: for problem b, keep[offsets[b] + i], i < n_keep[b], are the kept
  *   indices RELATIVE to offsets[b], in descending-score order (stable: equal scores keep
  *   ascending index); n_keep [B] int32.  max_keep > 0 stops after that many.
- *   n_total = offsets[B] and n_max = max segment length are passed by the host.
+ *   n_total >= offsets[B] and n_max >= max segment length are passed by the host; both may
+ *   be upper bounds (rows in [offsets[B], n_total) must be readable and are ignored), so a
+ *   producer with device-side counts (rp_rpn_pre_nms) chains without a host read.
  * flags: RP_NMS_GE               suppress when iou >= (float)thr (cython_nms.pyx:69)
  *        RP_NMS_ASCENDING        return each keep list sorted by ascending index (:74)
  *        RP_NMS_TIES_HIGH_FIRST  equal scores: higher index first (argsort()[::-1], :35)
@@ -180,6 +182,36 @@ RP_API int rp_mask_select_sigmoid(const float* logits, const int* labels, int K,
 
 RP_API int rp_paste_masks(const float* masks, const float* boxes, int n, int M, int im_h, int im_w,
                    float thresh, int padding, uint8_t* out, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * RPN proposal stage in front of the NMS (the caller of rp_nms_batched).
+ * Replaces: BoxCoder.decode det/modeling/box_coder.py:53-94 (rp_box_decode), and in
+ *           RPNPostProcessor.forward_for_single_feature_map det/modeling/rpn/inference.py:83-117
+ *           everything before boxlist_nms: permute_and_flatten (rpn/utils.py:10-15), sigmoid,
+ *           topk(pre_nms_top_n, sorted), the regression / anchor gathers, decode,
+ *           clip_to_image(remove_empty=False) bounding_box.py:263-277 and remove_small_boxes
+ *           boxlist_ops.py:64-76.
+ * rp_box_decode: rel_codes [n,4K] (K codes per reference box, the 0::4 .. 3::4 strides of
+ *   :73-76), boxes [n,4] xyxy (all 16-byte aligned) -> out [n,4K].
+ * rp_rpn_pre_nms, one FPN level, N images:
+ *   objectness [N,A,H,W]; box_regression [N,4A,H,W]; anchors [N,H*W*A,4] in the reference's
+ *   flattened (h,w,a) order; im_wh [N,2] float (width, height of each image).
+ *   k = min(pre_nms_top_n, A*H*W) candidates per image, descending sigmoid score, equal
+ *   scores by ascending flattened index.
+ *   out_offsets [N+1] DEVICE int32: image b owns rows [out_offsets[b], out_offsets[b+1]) of
+ *   out_boxes [N*k,4], out_scores [N*k], out_index [N*k] (flattened anchor index; may be
+ *   NULL), in rank order with the small boxes removed -- the layout rp_nms_batched reads.
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_box_decode(const float* rel_codes, const float* boxes, int n, int K, float wx,
+                  float wy, float ww, float wh, float bbox_xform_clip, float* out, void* stream);
+
+RP_API size_t rp_rpn_pre_nms_workspace_bytes(int N, int A, int H, int W, int k);
+
+RP_API int rp_rpn_pre_nms(const float* objectness, const float* box_regression, const float* anchors,
+                   const float* im_wh, int N, int A, int H, int W, int pre_nms_top_n,
+                   float min_size, float wx, float wy, float ww, float wh, float bbox_xform_clip,
+                   float* out_boxes, float* out_scores, int* out_index, int* out_offsets,
+                   void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -39,6 +39,10 @@ SIGNATURES = {
     "rp_mask_assemble": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "rp_mask_select_sigmoid": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "rp_paste_masks": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _vp]),
+    "rp_box_decode": (_i, [_vp, _vp, _i, _i, _f, _f, _f, _f, _f, _vp, _vp]),
+    "rp_rpn_pre_nms_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "rp_rpn_pre_nms": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _f, _f, _f,
+                            _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
 }
 
 _lib = None

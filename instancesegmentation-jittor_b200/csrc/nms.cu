@@ -54,6 +54,13 @@ __global__ void nms_keys_kernel(const float* __restrict__ scores, const int* __r
                                 uint64_t* __restrict__ keys, int* __restrict__ vals) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n_total) return;
+  if (p >= offsets[B]) {
+    // n_total may be an upper bound of offsets[B] (a device-side count the host never reads,
+    // e.g. the output of rp_rpn_pre_nms): the slack rows sort behind the last problem
+    keys[p] = ((uint64_t)(uint32_t)B << 32);
+    vals[p] = p;
+    return;
+  }
   const int b = nms_find_segment(offsets, B, p);
   // With ties_high_first the segment is fed to the stable sort in reversed element order, so
   // equal scores come out with the HIGHER index first (argsort()[::-1] of cython_nms.pyx:35).
@@ -522,7 +529,7 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
                                     (flags & RP_NMS_TIES_HIGH_FIRST) ? 1 : 0, w.keys_in, w.vals_in);
   RP_LAUNCH_CHECK();
   int seg_bits = 1;
-  while ((1 << seg_bits) < B) ++seg_bits;
+  while ((1 << seg_bits) < B + 1) ++seg_bits;  // B problems + the slack id B
   RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
                                               w.vals_in, w.vals_out, n_total, 0, 32 + seg_bits,
                                               st));

@@ -218,6 +218,40 @@ def argsort_desc(key):
     return order
 
 
+# --------------------------------------------------------------------------- RPN
+def box_decode(rel_codes, boxes, weights=(1.0, 1.0, 1.0, 1.0), clip=float(np.log(1000.0 / 16))):
+    rel_codes, cp = _f(rel_codes)
+    boxes, bp = _f(boxes)
+    n, K = rel_codes.shape[0], rel_codes.shape[1] // 4
+    out = np.zeros_like(rel_codes)
+    cf = ctypes.c_float
+    lib().orc_box_decode(cp, bp, n, K, cf(weights[0]), cf(weights[1]), cf(weights[2]),
+                         cf(weights[3]), cf(clip), out.ctypes.data_as(_f32p))
+    return out
+
+
+def rpn_pre_nms(objectness, box_regression, anchors, im_wh, pre_nms_top_n, min_size,
+                weights=(1.0, 1.0, 1.0, 1.0), clip=float(np.log(1000.0 / 16))):
+    """Per image lists of (boxes [m,4], scores [m], index [m]) in rank order."""
+    objectness, op = _f(objectness)
+    box_regression, rp = _f(box_regression)
+    anchors, ap = _f(anchors)
+    im_wh, wp = _f(im_wh)
+    N, A, H, W = objectness.shape
+    k = min(int(pre_nms_top_n), A * H * W)
+    boxes = np.zeros((N, k, 4), np.float32)
+    scores = np.zeros((N, k), np.float32)
+    index = np.zeros((N, k), np.int32)
+    counts = np.zeros((N,), np.int32)
+    cf = ctypes.c_float
+    lib().orc_rpn_pre_nms(op, rp, ap, wp, N, A, H, W, int(pre_nms_top_n), cf(min_size),
+                          cf(weights[0]), cf(weights[1]), cf(weights[2]), cf(weights[3]), cf(clip),
+                          boxes.ctypes.data_as(_f32p), scores.ctypes.data_as(_f32p),
+                          index.ctypes.data_as(_i32p), counts.ctypes.data_as(_i32p))
+    return [(boxes[b, :counts[b]].copy(), scores[b, :counts[b]].copy(), index[b, :counts[b]].copy())
+            for b in range(N)]
+
+
 # --------------------------------------------------------------------------- Yolact
 def yolact_decode(loc, priors):
     loc, lp = _f(loc)

@@ -18,6 +18,10 @@
  *   - orc_nms: pinned against the golden vectors of
  *     detectron.jittor/tests/test_nms.py:11-58,60-217 (keep sets).
  *   - orc_cython_nms: pinned against the reference's cython_nms.pyx compiled here.
+ *   - orc_box_decode: pinned against the known-answer vectors of
+ *     detectron.jittor/tests/test_box_coder.py (tests/golden/box_coder_kat.npz, atol 1e-4).
+ *   - orc_rpn_pre_nms: the decode inside is pinned as above; the sort's tie order, the clip and
+ *     the small-box test follow the source text (PARITY UNPINNED for those).
  *   - everything else (ml_nms label term, FastNMS, jaccard, crop, assembly, bilinear
  *     resize, paste-back, level mapping): PARITY UNPINNED -- the reference holds no
  *     known-answer test and Jittor is not installable; the restatement follows the
@@ -793,6 +797,97 @@ ORC_API void orc_paste_masks(const float* masks, const float* boxes, int n, int 
     }
     free(pad);
   }
+}
+
+/* ------------------------------------------------------------------------- */
+/* RPN proposal stage in front of the NMS                                     */
+/* ------------------------------------------------------------------------- */
+
+/* det/modeling/box_coder.py:53-94 BoxCoder.decode.  rel_codes [n,4K], boxes [n,4], out [n,4K].
+ * TO_REMOVE = 1 (:65-67); d* = code / weight (:72-75); dw, dh clamped from above (:77-78);
+ * centre and size (:80-83); x2 / y2 carry the "- 1" (:90-93).  exp is rp_expf, the function the
+ * CUDA side shares (pinned against the reference's known-answer test at atol 1e-4 and against
+ * libm in tests/test_oracle_golden.py). */
+ORC_API void orc_box_decode(const float* rel_codes, const float* boxes, int n, int K, float wx,
+                            float wy, float ww, float wh, float clip, float* out) {
+  for (int i = 0; i < n; ++i) {
+    const float* b = boxes + (size_t)i * 4;
+    const float widths = b[2] - b[0] + 1.0f;
+    const float heights = b[3] - b[1] + 1.0f;
+    const float ctr_x = b[0] + 0.5f * widths;
+    const float ctr_y = b[1] + 0.5f * heights;
+    for (int c = 0; c < K; ++c) {
+      const float* d = rel_codes + ((size_t)i * K + c) * 4;
+      float* o = out + ((size_t)i * K + c) * 4;
+      const float dx = d[0] / wx, dy = d[1] / wy;
+      float dw = d[2] / ww, dh = d[3] / wh;
+      if (dw > clip) dw = clip;
+      if (dh > clip) dh = clip;
+      const float pcx = dx * widths + ctr_x;
+      const float pcy = dy * heights + ctr_y;
+      const float pw = rp_expf(dw) * widths;
+      const float ph = rp_expf(dh) * heights;
+      o[0] = pcx - 0.5f * pw;
+      o[1] = pcy - 0.5f * ph;
+      o[2] = pcx + 0.5f * pw - 1.0f;
+      o[3] = pcy + 0.5f * ph - 1.0f;
+    }
+  }
+}
+
+/* det/modeling/rpn/inference.py:83-111, one level, up to (not including) boxlist_nms:
+ *   permute_and_flatten (rpn/utils.py:10-15): element e = (h*W + w)*A + a of image b is
+ *   objectness[b][a][h][w] and box_regression[b][4a .. 4a+3][h][w];
+ *   sigmoid (:89); topk(pre_nms_top_n, sorted=True) (:95-96) -- restated as a stable
+ *   descending sort, equal scores by ascending e (tie order is this repo's choice, PARITY
+ *   UNPINNED for ties); gathers (:100-104); decode (:106-108);
+ *   clip_to_image(remove_empty=False) det/structures/bounding_box.py:263-277: clamp to
+ *   [0, w-1] x [0, h-1]; remove_small_boxes det/structures/boxlist_ops.py:64-76: keep when
+ *   x2-x1+1 >= min_size and y2-y1+1 >= min_size.
+ * anchors [N, H*W*A, 4]; im_wh [N,2] (width, height).  Outputs are padded per image:
+ * out_boxes [N,k,4], out_scores [N,k], out_index [N,k], counts [N]; k = min(top_n, A*H*W). */
+ORC_API void orc_rpn_pre_nms(const float* objectness, const float* box_regression,
+                             const float* anchors, const float* im_wh, int N, int A, int H, int W,
+                             int pre_nms_top_n, float min_size, float wx, float wy, float ww,
+                             float wh, float clip, float* out_boxes, float* out_scores,
+                             int* out_index, int* counts) {
+  const int HW = H * W;
+  const int per = A * HW;
+  const int k = pre_nms_top_n < per ? pre_nms_top_n : per;
+  float* flat = (float*)malloc(sizeof(float) * (size_t)per);
+  int* order = (int*)malloc(sizeof(int) * (size_t)per);
+  for (int b = 0; b < N; ++b) {
+    const float* obj = objectness + (size_t)b * per;
+    const float* reg = box_regression + (size_t)b * per * 4;
+    const float* anc = anchors + (size_t)b * per * 4;
+    for (int hw = 0; hw < HW; ++hw)
+      for (int a = 0; a < A; ++a) flat[hw * A + a] = rp_sigmoidf(obj[(size_t)a * HW + hw]);
+    orc_argsort_desc(flat, per, order);
+    int m = 0;
+    for (int j = 0; j < k; ++j) {
+      const int e = order[j];
+      const int hw = e / A, a = e % A;
+      float code[4], box[4];
+      for (int c = 0; c < 4; ++c) code[c] = reg[((size_t)a * 4 + c) * HW + hw];
+      orc_box_decode(code, anc + (size_t)e * 4, 1, 1, wx, wy, ww, wh, clip, box);
+      const float xmax = im_wh[2 * b] - 1.0f, ymax = im_wh[2 * b + 1] - 1.0f;
+      box[0] = fminf(fmaxf(box[0], 0.0f), xmax);
+      box[1] = fminf(fmaxf(box[1], 0.0f), ymax);
+      box[2] = fminf(fmaxf(box[2], 0.0f), xmax);
+      box[3] = fminf(fmaxf(box[3], 0.0f), ymax);
+      const float ws = box[2] - box[0] + 1.0f, hs = box[3] - box[1] + 1.0f;
+      if (ws >= min_size && hs >= min_size) {
+        const size_t o = (size_t)b * k + m;
+        memcpy(out_boxes + o * 4, box, sizeof(box));
+        out_scores[o] = flat[e];
+        out_index[o] = e;
+        ++m;
+      }
+    }
+    counts[b] = m;
+  }
+  free(flat);
+  free(order);
 }
 
 /* ------------------------------------------------------------------------- */

@@ -10,6 +10,9 @@ Run in the BUILD container (needs /root/reference); the GPU box only reads the .
                         compiled as C++ by oracle/build.py (oracle/_ref/libroialign_ref.so).
   cython_nms_ref.npz -- inputs + keeps of the reference's Yolact.jittor/utils/cython_nms.pyx
                         compiled here (oracle/_ref/cython_nms_ref*.so).
+  box_coder_kat.npz  -- the reference's known-answer vectors for BoxCoder.decode, parsed out of
+                        detectron.jittor/tests/test_box_coder.py:11-108 (5 boxes, 5 deltas,
+                        5 expected boxes, assert_allclose atol 1e-4).
 """
 import ast
 import os
@@ -54,6 +57,14 @@ def make_nms_kat():
              keep5=np.array([[1, 3, -1, -1, -1], [1, 3, -1, -1, -1], [1, 3, -1, -1, -1],
                              [1, 2, 3, 4, -1], [0, 1, 2, 3, 4]], np.int64),
              boxes53=boxes53, scores53=scores53, keep53=gt53)
+
+
+def make_box_coder_kat():
+    lits = _np_array_literals(os.path.join(REF, "detectron.jittor/tests/test_box_coder.py"))
+    assert len(lits) == 3 and all(len(l) == 20 for l in lits)
+    bbox, deltas, gt = (np.asarray(l, np.float32).reshape(-1, 4) for l in lits)  # source order
+    np.savez(os.path.join(HERE, "box_coder_kat.npz"), bbox=bbox, deltas=deltas, gt_bbox=gt,
+             atol=np.float32(1e-4))
 
 
 def make_roi_align_ref():
@@ -103,6 +114,7 @@ def make_cython_nms_ref():
 
 if __name__ == "__main__":
     make_nms_kat()
+    make_box_coder_kat()
     make_roi_align_ref()
     make_cython_nms_ref()
     for f in sorted(os.listdir(HERE)):

@@ -124,3 +124,32 @@ def paste_inputs(n, seed, M=28, img_w=IMG_W, img_h=IMG_H):
         b[-4:] = np.array([[-30.5, -20.25, 100.75, 90.5], [700.2, 400.1, 700.9, 400.6],
                            [0, 0, img_w - 1, img_h - 1], [1300.5, 780.5, 1400.0, 850.0]], np.float32)
     return masks, b.astype(np.float32)
+
+
+def rpn_level(n_images, A, H, W, stride, seed, size=None, ties=False, img_w=IMG_W, img_h=IMG_H):
+    """One FPN level of RPN head outputs + its anchors.
+    anchors [n_images, H*W*A, 4] in the reference's (h, w, a) order: A aspect ratios
+    (0.5, 1, 2, ...) of a `size`-pixel box (legacy +1/-1 corners) centred on each stride cell;
+    objectness [N,A,H,W] logits (quantised to 1/4 when ties=True: many equal scores);
+    box_regression [N,4A,H,W] with a few dw/dh above bbox_xform_clip and a few collapsing boxes."""
+    rng = np.random.default_rng(seed)
+    size = float(size if size is not None else stride * 8)
+    ratios = np.array([0.5, 1.0, 2.0, 0.25, 4.0][:A] if A <= 5 else np.linspace(0.25, 4, A))
+    ws = np.round(np.sqrt(size * size / ratios))
+    hs = np.round(ws * ratios)
+    cell = np.stack([-(ws - 1) / 2, -(hs - 1) / 2, (ws - 1) / 2, (hs - 1) / 2], 1) + (stride - 1) / 2
+    sy, sx = np.meshgrid(np.arange(H) * stride, np.arange(W) * stride, indexing="ij")
+    shifts = np.stack([sx, sy, sx, sy], -1).reshape(-1, 1, 4)
+    anchors = (shifts + cell[None]).reshape(-1, 4).astype(np.float32)
+    anchors = np.broadcast_to(anchors, (n_images,) + anchors.shape).copy()
+    obj = rng.standard_normal((n_images, A, H, W)).astype(np.float32) * 2.0 - 1.0
+    if ties:
+        obj = np.round(obj * 4.0) / 4.0
+    reg = (rng.standard_normal((n_images, 4 * A, H, W)) * 0.4).astype(np.float32)
+    flat = reg.reshape(-1)
+    hot = rng.choice(flat.size, max(4, flat.size // 200), replace=False)
+    flat[hot] = rng.choice([5.0, 4.2, -6.0, -9.0], hot.size).astype(np.float32)
+    im_wh = np.tile(np.array([[img_w, img_h]], np.float32), (n_images, 1))
+    if n_images > 1:
+        im_wh[1] = (int(img_w * 0.75), int(img_h * 0.9))  # images of a batch differ in size
+    return anchors, obj.astype(np.float32), reg, im_wh

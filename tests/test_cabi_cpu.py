@@ -24,7 +24,8 @@ def test_header_declares_the_whole_path():
     names = _declared()
     for must in ("rp_roi_align_forward", "rp_roi_align_backward", "rp_pooler_forward",
                  "rp_pooler_backward", "rp_level_map", "rp_nms_batched", "rp_fast_nms_batched",
-                 "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode"):
+                 "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode",
+                 "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes"):
         assert must in names
 
 
@@ -59,6 +60,14 @@ def test_argument_errors_need_no_gpu():
     ws = L.rp_nms_workspace_bytes(160000, 20000, 8)
     assert 160000 * 40 < ws < 64 * 1024 * 1024
     assert L.rp_fast_nms_workspace_bytes(500, 500, 1, 80, 200) > 0
+    assert L.rp_box_decode(None, None, 3, 1, 1.0, 1.0, 1.0, 1.0, 4.0, None, None) == -1
+    assert L.rp_box_decode(None, None, 0, 1, 1.0, 1.0, 1.0, 1.0, 4.0, None, None) == 0
+    assert L.rp_rpn_pre_nms(None, None, None, None, 1, 3, 4, 4, 10, 0.0, 1.0, 1.0, 1.0, 1.0, 4.0,
+                            None, None, None, None, None, 0, None) == -1
+    # RPN proposal stage: O(N*A*H*W) sort buffers + O(N*k) slots
+    ws = L.rp_rpn_pre_nms_workspace_bytes(2, 3, 200, 336, 2000)
+    assert 2 * 3 * 200 * 336 * 24 < ws < 32 * 1024 * 1024
+    assert L.rp_rpn_pre_nms_workspace_bytes(0, 3, 4, 4, 10) == 0
 
 
 def test_no_cpu_fallback():

@@ -1,0 +1,147 @@
+"""GPU parity of the RPN proposal stage (BoxCoder.decode, sigmoid + top-k + gather + decode +
+clip + small-box removal, chained into the batched NMS) against the oracle: boxes, scores and
+indices bit-exact, including the tie order of equal scores."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import roipath_b200 as rp
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def test_box_decode_reference_kat(golden_dir):
+    # detectron.jittor/tests/test_box_coder.py:11-108
+    k = np.load(os.path.join(golden_dir, "box_coder_kat.npz"))
+    coder = rp.BoxCoder(weights=(1.0, 1.0, 1.0, 1.0))
+    out = coder.decode(T(k["deltas"]), T(k["bbox"])).cpu().numpy()
+    np.testing.assert_allclose(out, k["gt_bbox"], atol=float(k["atol"]))
+    np.testing.assert_array_equal(out, oracle.box_decode(k["deltas"], k["bbox"]))
+
+
+@pytest.mark.parametrize("n,K", [(1, 1), (255, 1), (1000, 81), (4097, 2)])
+def test_box_decode_matches_oracle(n, K):
+    rng = np.random.default_rng(n + K)
+    x1 = rng.uniform(0, 900, n); y1 = rng.uniform(0, 600, n)
+    boxes = np.stack([x1, y1, x1 + rng.uniform(0, 400, n), y1 + rng.uniform(0, 300, n)], 1).astype(np.float32)
+    codes = (rng.standard_normal((n, 4 * K)) * 2.0).astype(np.float32)
+    codes[::7, 2] = 50.0
+    w = (10.0, 10.0, 5.0, 5.0)
+    out = rp.BoxCoder(w).decode(T(codes), T(boxes)).cpu().numpy()
+    np.testing.assert_array_equal(out, oracle.box_decode(codes, boxes, w))
+    assert rp.box_decode(T(codes[:0]), T(boxes[:0])).shape == (0, 4 * K)
+
+
+CASES = [  # N, A, H, W, stride, top_n, min_size, ties
+    (1, 3, 5, 7, 64, 1000, 0.0, False),       # fewer anchors than top_n
+    (2, 3, 25, 42, 32, 1000, 0.0, False),
+    (2, 3, 50, 84, 16, 1000, 8.0, True),
+    (3, 3, 100, 168, 8, 2000, 4.0, True),
+    (2, 1, 13, 9, 16, 50, 16.0, True),
+    (2, 5, 31, 17, 16, 257, 2.0, False),      # A not 3, k not a multiple of the CTA width
+    (1, 3, 200, 336, 4, 6000, 0.0, False),    # the P2 level of a 800 x 1344 image, training top_n 2000+
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_pre_nms_matches_oracle(case):
+    N, A, H, W, stride, top_n, min_size, ties = case
+    anchors, obj, reg, im_wh = synth.rpn_level(N, A, H, W, stride, seed=H * W + A, ties=ties)
+    boxes, scores, index, offsets, k = rp.rpn_pre_nms(T(obj), T(reg), T(anchors), T(im_wh), top_n, min_size)
+    assert k == min(top_n, A * H * W)
+    off = offsets.cpu().numpy()
+    ref = oracle.rpn_pre_nms(obj, reg, anchors, im_wh, top_n, min_size)
+    assert off[0] == 0
+    bx, sc, ix = boxes.cpu().numpy(), scores.cpu().numpy(), index.cpu().numpy()
+    for b in range(N):
+        rb, rs, ri = ref[b]
+        assert off[b + 1] - off[b] == len(ri)
+        sl = slice(off[b], off[b + 1])
+        np.testing.assert_array_equal(ix[sl], ri)
+        np.testing.assert_array_equal(sc[sl], rs)
+        np.testing.assert_array_equal(bx[sl], rb)
+    if min_size > 0:
+        assert off[N] < N * k  # the filter removed something: the packed layout is exercised
+
+
+def _anchor_lists(anchors, im_wh):
+    return [rp.BoxList(T(anchors[b]), (int(im_wh[b, 0]), int(im_wh[b, 1])), mode="xyxy")
+            for b in range(anchors.shape[0])]
+
+
+def _oracle_level(obj, reg, anchors, im_wh, top_n, min_size, thr, post):
+    out = []
+    for rb, rs, _ in oracle.rpn_pre_nms(obj, reg, anchors, im_wh, top_n, min_size):
+        keep = oracle.nms(rb, rs, thr, max_keep=post) if len(rb) else np.zeros((0,), np.int32)
+        out.append((rb[keep], rs[keep]))
+    return out
+
+
+@pytest.mark.parametrize("ties", [False, True])
+def test_single_feature_map_matches_oracle(ties):
+    N, A, H, W, stride = 3, 3, 50, 84, 16
+    anchors, obj, reg, im_wh = synth.rpn_level(N, A, H, W, stride, seed=11, ties=ties)
+    post = rp.RPNPostProcessor(pre_nms_top_n=2000, post_nms_top_n=300, nms_thresh=0.7, min_size=4)
+    res = post.forward_for_single_feature_map(_anchor_lists(anchors, im_wh), T(obj), T(reg))
+    ref = _oracle_level(obj, reg, anchors, im_wh, 2000, 4.0, 0.7, 300)
+    assert len(res) == N
+    for b in range(N):
+        assert res[b].size == (int(im_wh[b, 0]), int(im_wh[b, 1])) and res[b].mode == "xyxy"
+        np.testing.assert_array_equal(res[b].bbox.cpu().numpy(), ref[b][0])
+        np.testing.assert_array_equal(res[b].get_field("objectness").cpu().numpy(), ref[b][1])
+        assert len(res[b]) <= 300
+
+
+def test_all_levels_matches_oracle():
+    # execute(): 5 FPN levels, image-major anchor lists, test-time per-image top-k over levels
+    N, A = 2, 3
+    shapes = [(200, 336, 4), (100, 168, 8), (50, 84, 16), (25, 42, 32), (13, 21, 64)]
+    levels = [synth.rpn_level(N, A, H, W, s, seed=100 + s) for H, W, s in shapes]
+    im_wh = levels[0][3]
+    anchors = [[rp.BoxList(T(lv[0][b]), (int(im_wh[b, 0]), int(im_wh[b, 1]))) for lv in levels]
+               for b in range(N)]
+    post = rp.RPNPostProcessor(pre_nms_top_n=1000, post_nms_top_n=1000, nms_thresh=0.7, min_size=0,
+                               fpn_post_nms_top_n=1000)
+    post.eval()
+    res = post(anchors, [T(lv[1]) for lv in levels], [T(lv[2]) for lv in levels])
+    per_level = [_oracle_level(lv[1], lv[2], lv[0], lv[3], 1000, 0.0, 0.7, 1000) for lv in levels]
+    for b in range(N):
+        rb = np.concatenate([pl[b][0] for pl in per_level], 0)
+        rs = np.concatenate([pl[b][1] for pl in per_level], 0)
+        order = np.argsort(-rs, kind="stable")[:1000]
+        np.testing.assert_array_equal(res[b].bbox.cpu().numpy(), rb[order])
+        np.testing.assert_array_equal(res[b].get_field("objectness").cpu().numpy(), rs[order])
+
+
+def test_training_mode_adds_gt_and_selects_per_batch():
+    N, A, H, W, stride = 2, 3, 25, 42, 32
+    lv = [synth.rpn_level(N, A, H, W, stride, seed=5), synth.rpn_level(N, A, 13, 21, 64, seed=6)]
+    im_wh = lv[0][3]
+    sizes = [(int(im_wh[b, 0]), int(im_wh[b, 1])) for b in range(N)]
+    anchors = [[rp.BoxList(T(l[0][b]), sizes[b]) for l in lv] for b in range(N)]
+    targets = [rp.BoxList(T(synth.proposals(3, 50 + b, adversarial=False)), sizes[b]) for b in range(N)]
+    post = rp.RPNPostProcessor(2000, 2000, 0.7, 0, fpn_post_nms_top_n=500, fpn_post_nms_per_batch=True)
+    post.train()
+    res = post(anchors, [T(l[1]) for l in lv], [T(l[2]) for l in lv], targets)
+    assert sum(len(r) for r in res) == 500 + 3 * N
+    for b in range(N):
+        obj = res[b].get_field("objectness").cpu().numpy()
+        assert np.all(obj[-3:] == 1.0)
+        np.testing.assert_array_equal(res[b].bbox[-3:].cpu().numpy(), targets[b].bbox.cpu().numpy())
+
+
+def test_errors_are_loud():
+    anchors, obj, reg, im_wh = synth.rpn_level(1, 3, 5, 7, 64, seed=1)
+    with pytest.raises(ValueError):
+        rp.rpn_pre_nms(T(obj), T(reg[:, :8]), T(anchors), T(im_wh), 100, 0)
+    with pytest.raises(Exception):
+        rp.rpn_pre_nms(obj, reg, anchors, im_wh, 100, 0)  # numpy / CPU input: no fallback
