@@ -319,6 +319,25 @@ def extras(rp, torch, dev):
     ms_p = med(lambda: rp.paste_masks(pmt, pbt, 800, 1333, out=pout))
     out["paste_ms_per_image_100inst"] = ms_p
     out["paste_gbs"] = (100 * 28 * 28 * 4 + 100 * 800 * 1333) / (ms_p * 1e-3) / 1e9
+    # --- RPN proposal stage: 5 FPN levels of 8 images at 800 x 1344, test
+    #     configuration (pre/post/fpn top-n 1000, thr 0.7): pre-NMS + NMS + per-image selection,
+    #     device part (no host read) and the whole RPNPostProcessor.execute (BoxLists out)
+    N, A = 8, 3
+    lv = [synth.rpn_level(N, A, H, W, st, seed=100 + st)
+          for H, W, st in ((200, 336, 4), (100, 168, 8), (50, 84, 16), (25, 42, 32), (13, 21, 64))]
+    im_wh = lv[0][3]
+    anchors = [[rp.BoxList(T(l[0][b]), (int(im_wh[b, 0]), int(im_wh[b, 1]))) for l in lv] for b in range(N)]
+    objs, regs, ancs, wh = [T(l[1]) for l in lv], [T(l[2]) for l in lv], [T(l[0]) for l in lv], T(im_wh)
+    post = rp.RPNPostProcessor(1000, 1000, 0.7, 0, fpn_post_nms_top_n=1000)
+    post.eval()
+
+    def rpn_device():
+        bx, sc, _, off, ks = rp.rpn_pre_nms_levels(objs, regs, ancs, wh, 1000, 0.0)
+        keep, nk = rp.nms_batched(bx, sc, off, 0.7, max_keep=1000, n_max=max(ks))
+        rp.rpn_select_levels(bx, sc, off, keep, nk, len(lv), N, 1000)
+
+    out["rpn_post_device_ms_per_batch8"] = med(rpn_device)
+    out["rpn_post_execute_ms_per_batch8"] = med(lambda: post(anchors, objs, regs))
     return out
 
 

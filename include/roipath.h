@@ -201,17 +201,45 @@ RP_API int rp_paste_masks(const float* masks, const float* boxes, int n, int M, 
  *   out_offsets [N+1] DEVICE int32: image b owns rows [out_offsets[b], out_offsets[b+1]) of
  *   out_boxes [N*k,4], out_scores [N*k], out_index [N*k] (flattened anchor index; may be
  *   NULL), in rank order with the small boxes removed -- the layout rp_nms_batched reads.
+ * rp_rpn_pre_nms_levels: the same for L <= RP_MAX_LEVELS levels in ONE set of launches (one
+ *   sort for the whole batch).  objectness / box_regression / anchors / A / H / W are HOST
+ *   arrays of length L.  Problem s = l*N + b (level-major) owns rows
+ *   [out_offsets[s], out_offsets[s+1]); out_offsets [L*N+1]; outputs hold
+ *   sum_l N*k_l rows, k_l = min(pre_nms_top_n, A_l*H_l*W_l).
+ * rp_rpn_select_levels: RPNPostProcessor.select_over_all_levels, test-time branch
+ *   inference.py:175-183: per image, the top_n best of the boxes its L problems kept
+ *   (offsets / keep / n_keep as returned by rp_nms_batched for the L*N problems above),
+ *   descending score, equal scores in (level, keep rank) order = the cat_boxlist order :143-144.
+ *   n_cap = rows of boxes / scores / keep.  out_boxes [N*top_n,4], out_scores [N*top_n]: image
+ *   b owns rows [b*top_n, b*top_n + out_count[b]).
  * ------------------------------------------------------------------------------------ */
 RP_API int rp_box_decode(const float* rel_codes, const float* boxes, int n, int K, float wx,
                   float wy, float ww, float wh, float bbox_xform_clip, float* out, void* stream);
 
-RP_API size_t rp_rpn_pre_nms_workspace_bytes(int N, int A, int H, int W, int k);
+RP_API size_t rp_rpn_pre_nms_workspace_bytes(int N, int A, int H, int W, int pre_nms_top_n);
 
 RP_API int rp_rpn_pre_nms(const float* objectness, const float* box_regression, const float* anchors,
                    const float* im_wh, int N, int A, int H, int W, int pre_nms_top_n,
                    float min_size, float wx, float wy, float ww, float wh, float bbox_xform_clip,
                    float* out_boxes, float* out_scores, int* out_index, int* out_offsets,
                    void* workspace, size_t workspace_bytes, void* stream);
+
+RP_API size_t rp_rpn_pre_nms_levels_workspace_bytes(int L, int N, const int* A, const int* H,
+                                             const int* W, int pre_nms_top_n);
+
+RP_API int rp_rpn_pre_nms_levels(const float* const* objectness, const float* const* box_regression,
+                          const float* const* anchors, const int* A, const int* H, const int* W,
+                          int L, const float* im_wh, int N, int pre_nms_top_n, float min_size,
+                          float wx, float wy, float ww, float wh, float bbox_xform_clip,
+                          float* out_boxes, float* out_scores, int* out_index, int* out_offsets,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+RP_API size_t rp_rpn_select_workspace_bytes(int n_cap, int L, int N);
+
+RP_API int rp_rpn_select_levels(const float* boxes, const float* scores, const int* offsets,
+                         const int* keep, const int* n_keep, int L, int N, int n_cap, int top_n,
+                         float* out_boxes, float* out_scores, int* out_count, void* workspace,
+                         size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

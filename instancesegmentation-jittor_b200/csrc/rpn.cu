@@ -69,25 +69,46 @@ __global__ void rpn_box_decode_kernel(const float* __restrict__ codes, const flo
   *reinterpret_cast<float4*>(out + i * 4) = rpn_decode_one(a, d, wx, wy, ww, wh, clip);
 }
 
-// element e of image b in the reference's flattened order is (h, w, a) = (e / (W*A), ., e % A);
+
+// ---- all FPN levels of a batch in one set of launches --------------------------------------
+// Problem ("segment") s = l * N + b is level l of image b.  Level l holds per_l = A_l*H_l*W_l
+// anchors per image and keeps k_l = min(pre_nms_top_n, per_l) of them.  Elements of all segments
+// live in one array (segment s at elem_base[l] + b*per_l), their candidate slots in another
+// (segment s at slot_base[l] + b*k_l).
+struct RpnLevels {
+  const float* obj[RP_MAX_LEVELS];
+  const float* reg[RP_MAX_LEVELS];
+  const float* anc[RP_MAX_LEVELS];
+  int A[RP_MAX_LEVELS], HW[RP_MAX_LEVELS], k[RP_MAX_LEVELS];
+  int elem_base[RP_MAX_LEVELS + 1];  // prefix of N * per_l
+  int slot_base[RP_MAX_LEVELS + 1];  // prefix of N * k_l
+  int L, N;
+};
+
+// element e of a segment in the reference's flattened order is (h, w, a) = (e / (W*A), ., e % A);
 // its logit lives at objectness[b][a][h][w].
-__global__ void rpn_keys_kernel(const float* __restrict__ objectness, int N, int A, int HW,
-                                uint64_t* __restrict__ keys, int* __restrict__ vals) {
-  const size_t per = (size_t)A * HW;
-  const size_t f = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= per * N) return;
-  // threads walk the NCHW tensor (coalesced reads); the key goes to the element's flattened slot
-  const int b = (int)(f / per);
-  const size_t r = f - (size_t)b * per;
-  const int a = (int)(r / HW);
-  const int hw = (int)(r - (size_t)a * HW);
+__global__ void rpn_keys_kernel(const __grid_constant__ RpnLevels lv, uint64_t* __restrict__ keys,
+                                int* __restrict__ vals) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= lv.elem_base[lv.L]) return;
+  int l = 0;
+  while (l + 1 < lv.L && f >= lv.elem_base[l + 1]) ++l;
+  // threads walk each NCHW tensor (coalesced reads); the key goes to the element's flattened slot
+  const int A = lv.A[l], HW = lv.HW[l];
+  const int per = A * HW;
+  const int r0 = f - lv.elem_base[l];
+  const int b = r0 / per;
+  const int r = r0 - b * per;
+  const int a = r / HW;
+  const int hw = r - a * HW;
   const int e = hw * A + a;
-  const float s = rp_sigmoidf(objectness[f]);
-  const size_t o = (size_t)b * per + e;
-  keys[o] = ((uint64_t)(uint32_t)b << 32) | (uint64_t)rpn_desc_bits(s);
+  const float s = rp_sigmoidf(lv.obj[l][r0]);
+  const int o = lv.elem_base[l] + b * per + e;
+  keys[o] = ((uint64_t)(uint32_t)(l * lv.N + b) << 32) | (uint64_t)rpn_desc_bits(s);
   vals[o] = e;
 }
 
+template <int T>
 __device__ __forceinline__ int rpn_block_excl_scan(int v, int* warp_sums, int* total) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int inc = v;
@@ -100,7 +121,7 @@ __device__ __forceinline__ int rpn_block_excl_scan(int v, int* warp_sums, int* t
   __syncthreads();
   int base = 0, tot = 0;
 #pragma unroll
-  for (int w = 0; w < RPN_THREADS / 32; ++w) {
+  for (int w = 0; w < T / 32; ++w) {
     const int sw = warp_sums[w];
     if (w < wid) base += sw;
     tot += sw;
@@ -110,21 +131,24 @@ __device__ __forceinline__ int rpn_block_excl_scan(int v, int* warp_sums, int* t
   return base + inc - v;
 }
 
-// One CTA per image: ranks 0..k-1 in order -> padded slots [b*k + j], count[b].
+// One CTA per segment: ranks 0..k-1 in order -> the segment's slots, counts[s].
 __global__ void __launch_bounds__(RPN_THREADS)
-rpn_decode_kernel(const float* __restrict__ objectness, const float* __restrict__ regression,
-                  const float* __restrict__ anchors, const float* __restrict__ im_wh,
-                  const int* __restrict__ sorted_vals, int A, int HW, int k, float min_size,
-                  float wx, float wy, float ww, float wh, float clip, float* __restrict__ pad_boxes,
+rpn_decode_kernel(const __grid_constant__ RpnLevels lv, const float* __restrict__ im_wh,
+                  const int* __restrict__ sorted_vals, float min_size, float wx, float wy, float ww,
+                  float wh, float clip, float* __restrict__ pad_boxes,
                   float* __restrict__ pad_scores, int* __restrict__ pad_index,
                   int* __restrict__ counts) {
   __shared__ int wsum[RPN_THREADS / 32];
-  const int b = blockIdx.x;
+  const int s = blockIdx.x;
+  const int l = s / lv.N, b = s - l * lv.N;
+  const int A = lv.A[l], HW = lv.HW[l], k = lv.k[l];
   const size_t per = (size_t)A * HW;
   const float im_w = im_wh[2 * b], im_h = im_wh[2 * b + 1];
-  const float* obj_b = objectness + (size_t)b * per;
-  const float* reg_b = regression + (size_t)b * per * 4;
-  const float* anc_b = anchors + (size_t)b * per * 4;
+  const float* obj_b = lv.obj[l] + (size_t)b * per;
+  const float* reg_b = lv.reg[l] + (size_t)b * per * 4;
+  const float* anc_b = lv.anc[l] + (size_t)b * per * 4;
+  const int* vals_s = sorted_vals + lv.elem_base[l] + (size_t)b * per;
+  const size_t slot0 = (size_t)lv.slot_base[l] + (size_t)b * k;
   int base = 0;
   for (int j0 = 0; j0 < k; j0 += RPN_THREADS) {
     const int j = j0 + threadIdx.x;
@@ -132,7 +156,7 @@ rpn_decode_kernel(const float* __restrict__ objectness, const float* __restrict_
     float4 bx = make_float4(0.f, 0.f, 0.f, 0.f);
     float sc = 0.f;
     if (j < k) {
-      e = sorted_vals[(size_t)b * per + j];
+      e = vals_s[j];
       const int hw = e / A, a = e - hw * A;
       sc = rp_sigmoidf(obj_b[(size_t)a * HW + hw]);
       float4 d;  // box_regression[b][a*4 + c][h][w]
@@ -152,41 +176,131 @@ rpn_decode_kernel(const float* __restrict__ objectness, const float* __restrict_
       ok = (ws >= min_size) && (hs >= min_size);
     }
     int tot;
-    const int ex = rpn_block_excl_scan(ok, wsum, &tot);
+    const int ex = rpn_block_excl_scan<RPN_THREADS>(ok, wsum, &tot);
     if (ok) {
-      const size_t o = (size_t)b * k + base + ex;
+      const size_t o = slot0 + base + ex;
       *reinterpret_cast<float4*>(pad_boxes + o * 4) = bx;
       pad_scores[o] = sc;
       pad_index[o] = e;
     }
     base += tot;
   }
-  if (threadIdx.x == 0) counts[b] = base;
+  if (threadIdx.x == 0) counts[s] = base;
 }
 
-__global__ void rpn_offsets_kernel(const int* __restrict__ counts, int N, int* __restrict__ offsets) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) {
-    int acc = 0;
-    for (int b = 0; b < N; ++b) {
-      offsets[b] = acc;
-      acc += counts[b];
-    }
-    offsets[N] = acc;
+// offsets[0..S] = exclusive scan of counts[0..S) (one CTA; S = L*N is small)
+__global__ void __launch_bounds__(RPN_THREADS)
+rpn_offsets_kernel(const int* __restrict__ counts, int S, int* __restrict__ offsets) {
+  __shared__ int wsum[RPN_THREADS / 32];
+  int base = 0;
+  for (int s0 = 0; s0 < S; s0 += RPN_THREADS) {
+    const int s = s0 + threadIdx.x;
+    const int v = s < S ? counts[s] : 0;
+    int tot;
+    const int ex = rpn_block_excl_scan<RPN_THREADS>(v, wsum, &tot);
+    if (s < S) offsets[s] = base + ex;
+    base += tot;
   }
+  if (threadIdx.x == 0) offsets[S] = base;
 }
 
-__global__ void rpn_pack_kernel(const float* __restrict__ pad_boxes, const float* __restrict__ pad_scores,
+__global__ void rpn_pack_kernel(const __grid_constant__ RpnLevels lv,
+                                const float* __restrict__ pad_boxes,
+                                const float* __restrict__ pad_scores,
                                 const int* __restrict__ pad_index, const int* __restrict__ offsets,
-                                int k, float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                float* __restrict__ out_boxes, float* __restrict__ out_scores,
                                 int* __restrict__ out_index) {
+  const int s = blockIdx.y;
+  const int l = s / lv.N, b = s - l * lv.N;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int off = offsets[s], cnt = offsets[s + 1] - off;
+  if (j >= cnt) return;
+  const size_t src = (size_t)lv.slot_base[l] + (size_t)b * lv.k[l] + j, o = (size_t)off + j;
+  *reinterpret_cast<float4*>(out_boxes + o * 4) =
+      *reinterpret_cast<const float4*>(pad_boxes + src * 4);
+  out_scores[o] = pad_scores[src];
+  if (out_index) out_index[o] = pad_index[src];
+}
+
+// ---- per-image top-k over the levels' NMS survivors (inference.py:175-183) ------------------
+// seg_pos[s]: where segment s = (l, b) starts in the image-major concatenation
+// (cat_boxlist over levels, inference.py:143-144); img_off[b]: where image b starts.
+__global__ void __launch_bounds__(RPN_THREADS)
+rpn_sel_scan_kernel(const int* __restrict__ n_keep, int L, int N, int* __restrict__ img_off,
+                    int* __restrict__ seg_pos) {
+  __shared__ int wsum[RPN_THREADS / 32];
+  int base = 0;
+  for (int b0 = 0; b0 < N; b0 += RPN_THREADS) {
+    const int b = b0 + threadIdx.x;
+    int v = 0;
+    if (b < N)
+      for (int l = 0; l < L; ++l) v += n_keep[l * N + b];
+    int tot;
+    const int ex = rpn_block_excl_scan<RPN_THREADS>(v, wsum, &tot);
+    if (b < N) {
+      int p = base + ex;
+      img_off[b] = p;
+      for (int l = 0; l < L; ++l) {
+        seg_pos[l * N + b] = p;
+        p += n_keep[l * N + b];
+      }
+    }
+    base += tot;
+  }
+  if (threadIdx.x == 0) img_off[N] = base;
+}
+
+__global__ void rpn_sel_keys_kernel(const float* __restrict__ scores, const int* __restrict__ offsets,
+                                    const int* __restrict__ keep, const int* __restrict__ img_off,
+                                    const int* __restrict__ seg_pos, int L, int N, int n_cap,
+                                    uint64_t* __restrict__ keys, int* __restrict__ vals) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_cap) return;
+  if (p >= img_off[N]) {  // slack behind the last image
+    keys[p] = (uint64_t)(uint32_t)N << 32;
+    vals[p] = 0;
+    return;
+  }
+  int lo = 0, hi = N - 1;  // largest b with img_off[b] <= p
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (img_off[mid] <= p)
+      lo = mid;
+    else
+      hi = mid - 1;
+  }
+  const int b = lo;
+  int l = 0;  // last level whose start is <= p (empty levels share a start: take the last)
+  for (int q = 1; q < L; ++q)
+    if (seg_pos[q * N + b] <= p) l = q;
+  const int s = l * N + b;
+  const int src = offsets[s] + keep[offsets[s] + (p - seg_pos[s])];
+  keys[p] = ((uint64_t)(uint32_t)b << 32) | (uint64_t)rpn_desc_bits(scores[src]);
+  vals[p] = src;
+}
+
+__global__ void rpn_sel_emit_kernel(const float* __restrict__ boxes, const float* __restrict__ scores,
+                                    const int* __restrict__ img_off, const int* __restrict__ sorted_vals,
+                                    int top_n, float* __restrict__ out_boxes,
+                                    float* __restrict__ out_scores, int* __restrict__ out_count) {
   const int b = blockIdx.y;
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  const int off = offsets[b], cnt = offsets[b + 1] - off;
+  const int off = img_off[b];
+  int cnt = img_off[b + 1] - off;
+  if (cnt > top_n) cnt = top_n;
+  if (j == 0) out_count[b] = cnt;
   if (j >= cnt) return;
-  const size_t s = (size_t)b * k + j, o = (size_t)off + j;
-  *reinterpret_cast<float4*>(out_boxes + o * 4) = *reinterpret_cast<const float4*>(pad_boxes + s * 4);
-  out_scores[o] = pad_scores[s];
-  if (out_index) out_index[o] = pad_index[s];
+  const int src = sorted_vals[off + j];
+  const size_t o = (size_t)b * top_n + j;
+  *reinterpret_cast<float4*>(out_boxes + o * 4) = *reinterpret_cast<const float4*>(boxes + (size_t)src * 4);
+  out_scores[o] = scores[src];
+}
+
+size_t rpn_cub_bytes(size_t n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs((void*)nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                  (const int*)nullptr, (int*)nullptr, (int)n);
+  return bytes;
 }
 
 struct RpnWorkspace {
@@ -198,14 +312,7 @@ struct RpnWorkspace {
   size_t cub_bytes, total;
 };
 
-size_t rpn_cub_bytes(size_t n) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs((void*)nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                  (const int*)nullptr, (int*)nullptr, (int)n);
-  return bytes;
-}
-
-RpnWorkspace rpn_carve(void* base, size_t n_total, int N, int k) {
+RpnWorkspace rpn_carve(void* base, size_t n_elems, size_t n_slots, int S) {
   RpnWorkspace w;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -213,24 +320,76 @@ RpnWorkspace rpn_carve(void* base, size_t n_total, int N, int k) {
     off += rp_align_up(bytes, 256);
     return p;
   };
-  w.keys_in = (uint64_t*)take(8 * n_total);
-  w.keys_out = (uint64_t*)take(8 * n_total);
-  w.vals_in = (int*)take(4 * n_total);
-  w.vals_out = (int*)take(4 * n_total);
-  w.pad_boxes = (float*)take(16 * (size_t)N * k);
-  w.pad_scores = (float*)take(4 * (size_t)N * k);
-  w.pad_index = (int*)take(4 * (size_t)N * k);
-  w.counts = (int*)take(4 * (size_t)N);
-  w.cub_bytes = rpn_cub_bytes(n_total);
+  w.keys_in = (uint64_t*)take(8 * n_elems);
+  w.keys_out = (uint64_t*)take(8 * n_elems);
+  w.vals_in = (int*)take(4 * n_elems);
+  w.vals_out = (int*)take(4 * n_elems);
+  w.pad_boxes = (float*)take(16 * n_slots);
+  w.pad_scores = (float*)take(4 * n_slots);
+  w.pad_index = (int*)take(4 * n_slots);
+  w.counts = (int*)take(4 * (size_t)S);
+  w.cub_bytes = rpn_cub_bytes(n_elems);
   w.cub_temp = take(w.cub_bytes);
   w.total = off;
   return w;
 }
 
-int rpn_bits(size_t v) {
+struct RpnSelWorkspace {
+  uint64_t *keys_in, *keys_out;
+  int *vals_in, *vals_out, *img_off, *seg_pos;
+  void* cub_temp;
+  size_t cub_bytes, total;
+};
+
+RpnSelWorkspace rpn_sel_carve(void* base, size_t n_cap, int L, int N) {
+  RpnSelWorkspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (void*)((char*)base + off) : nullptr;
+    off += rp_align_up(bytes, 256);
+    return p;
+  };
+  w.keys_in = (uint64_t*)take(8 * n_cap);
+  w.keys_out = (uint64_t*)take(8 * n_cap);
+  w.vals_in = (int*)take(4 * n_cap);
+  w.vals_out = (int*)take(4 * n_cap);
+  w.img_off = (int*)take(4 * (size_t)(N + 1));
+  w.seg_pos = (int*)take(4 * (size_t)L * N);
+  w.cub_bytes = rpn_cub_bytes(n_cap);
+  w.cub_temp = take(w.cub_bytes);
+  w.total = off;
+  return w;
+}
+
+int rpn_bits(size_t v) {  // bits needed for ids 0 .. v-1
   int b = 1;
-  while (b < 32 && ((size_t)1 << b) < v) ++b;
+  while (b < 31 && ((size_t)1 << b) < v) ++b;
   return b;
+}
+
+// sizes of a set of levels; returns 0 when an argument is out of range
+int rpn_fill_levels(RpnLevels& lv, int L, int N, const int* A, const int* H, const int* W,
+                    int pre_nms_top_n) {
+  if (L < 1 || L > RP_MAX_LEVELS || N < 1 || !A || !H || !W || pre_nms_top_n < 1) return 0;
+  lv.L = L;
+  lv.N = N;
+  size_t eb = 0, sb = 0;
+  for (int l = 0; l < L; ++l) {
+    if (A[l] < 1 || H[l] < 1 || W[l] < 1) return 0;
+    const size_t per = (size_t)A[l] * H[l] * W[l];
+    const size_t k = (size_t)pre_nms_top_n < per ? (size_t)pre_nms_top_n : per;
+    lv.A[l] = A[l];
+    lv.HW[l] = H[l] * W[l];
+    lv.k[l] = (int)k;
+    lv.elem_base[l] = (int)eb;
+    lv.slot_base[l] = (int)sb;
+    eb += per * N;
+    sb += k * N;
+    if (eb > 0x7fffffffull) return -1;
+  }
+  lv.elem_base[L] = (int)eb;
+  lv.slot_base[L] = (int)sb;
+  return 1;
 }
 
 }  // namespace
@@ -251,9 +410,60 @@ int rp_box_decode(const float* rel_codes, const float* boxes, int n, int K, floa
   return RP_OK;
 }
 
-size_t rp_rpn_pre_nms_workspace_bytes(int N, int A, int H, int W, int k) {
-  if (N < 1 || A < 1 || H < 1 || W < 1 || k < 1) return 0;
-  return rpn_carve(nullptr, (size_t)N * A * H * W, N, k).total;
+size_t rp_rpn_pre_nms_levels_workspace_bytes(int L, int N, const int* A, const int* H, const int* W,
+                                             int pre_nms_top_n) {
+  RpnLevels lv;
+  if (rpn_fill_levels(lv, L, N, A, H, W, pre_nms_top_n) != 1) return 0;
+  return rpn_carve(nullptr, (size_t)lv.elem_base[L], (size_t)lv.slot_base[L], L * N).total;
+}
+
+int rp_rpn_pre_nms_levels(const float* const* objectness, const float* const* box_regression,
+                          const float* const* anchors, const int* A, const int* H, const int* W,
+                          int L, const float* im_wh, int N, int pre_nms_top_n, float min_size,
+                          float wx, float wy, float ww, float wh, float bbox_xform_clip,
+                          float* out_boxes, float* out_scores, int* out_index, int* out_offsets,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  RpnLevels lv;
+  const int ok = rpn_fill_levels(lv, L, N, A, H, W, pre_nms_top_n);
+  if (ok == 0) return RP_E_ARG;
+  if (ok < 0) return RP_E_LIMIT;
+  if (!objectness || !box_regression || !anchors || !im_wh || !out_boxes || !out_scores ||
+      !out_offsets || !workspace)
+    return RP_E_ARG;
+  if ((reinterpret_cast<uintptr_t>(out_boxes) & 15) != 0) return RP_E_ARG;
+  int kmax = 0;
+  for (int l = 0; l < L; ++l) {
+    if (!objectness[l] || !box_regression[l] || !anchors[l]) return RP_E_ARG;
+    if ((reinterpret_cast<uintptr_t>(anchors[l]) & 15) != 0) return RP_E_ARG;
+    lv.obj[l] = objectness[l];
+    lv.reg[l] = box_regression[l];
+    lv.anc[l] = anchors[l];
+    if (lv.k[l] > kmax) kmax = lv.k[l];
+  }
+  const int S = L * N;
+  if (S > 65535) return RP_E_LIMIT;
+  const int n_elems = lv.elem_base[L];
+  RpnWorkspace w = rpn_carve(workspace, (size_t)n_elems, (size_t)lv.slot_base[L], S);
+  if (w.total > workspace_bytes) return RP_E_WORKSPACE;
+  rpn_keys_kernel<<<(unsigned)((n_elems + 255) / 256), 256, 0, st>>>(lv, w.keys_in, w.vals_in);
+  RP_LAUNCH_CHECK();
+  RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out, w.vals_in,
+                                              w.vals_out, n_elems, 0, 32 + rpn_bits((size_t)S), st));
+  rpn_decode_kernel<<<S, RPN_THREADS, 0, st>>>(lv, im_wh, w.vals_out, min_size, wx, wy, ww, wh,
+                                               bbox_xform_clip, w.pad_boxes, w.pad_scores,
+                                               w.pad_index, w.counts);
+  RP_LAUNCH_CHECK();
+  rpn_offsets_kernel<<<1, RPN_THREADS, 0, st>>>(w.counts, S, out_offsets);
+  RP_LAUNCH_CHECK();
+  rpn_pack_kernel<<<dim3((unsigned)((kmax + 255) / 256), (unsigned)S), 256, 0, st>>>(
+      lv, w.pad_boxes, w.pad_scores, w.pad_index, out_offsets, out_boxes, out_scores, out_index);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+size_t rp_rpn_pre_nms_workspace_bytes(int N, int A, int H, int W, int pre_nms_top_n) {
+  return rp_rpn_pre_nms_levels_workspace_bytes(1, N, &A, &H, &W, pre_nms_top_n);
 }
 
 int rp_rpn_pre_nms(const float* objectness, const float* box_regression, const float* anchors,
@@ -261,33 +471,38 @@ int rp_rpn_pre_nms(const float* objectness, const float* box_regression, const f
                    float wx, float wy, float ww, float wh, float bbox_xform_clip, float* out_boxes,
                    float* out_scores, int* out_index, int* out_offsets, void* workspace,
                    size_t workspace_bytes, void* stream) {
+  return rp_rpn_pre_nms_levels(&objectness, &box_regression, &anchors, &A, &H, &W, 1, im_wh, N,
+                               pre_nms_top_n, min_size, wx, wy, ww, wh, bbox_xform_clip, out_boxes,
+                               out_scores, out_index, out_offsets, workspace, workspace_bytes, stream);
+}
+
+size_t rp_rpn_select_workspace_bytes(int n_cap, int L, int N) {
+  if (n_cap < 1 || L < 1 || N < 1) return 0;
+  return rpn_sel_carve(nullptr, (size_t)n_cap, L, N).total;
+}
+
+int rp_rpn_select_levels(const float* boxes, const float* scores, const int* offsets, const int* keep,
+                         const int* n_keep, int L, int N, int n_cap, int top_n, float* out_boxes,
+                         float* out_scores, int* out_count, void* workspace, size_t workspace_bytes,
+                         void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  if (N < 1 || A < 1 || H < 1 || W < 1 || pre_nms_top_n < 1) return RP_E_ARG;
-  if (!objectness || !box_regression || !anchors || !im_wh || !out_boxes || !out_scores ||
-      !out_offsets || !workspace)
+  if (L < 1 || N < 1 || n_cap < 1 || top_n < 1 || N > 65535) return RP_E_ARG;
+  if (!boxes || !scores || !offsets || !keep || !n_keep || !out_boxes || !out_scores || !out_count ||
+      !workspace)
     return RP_E_ARG;
-  if (((reinterpret_cast<uintptr_t>(anchors) | reinterpret_cast<uintptr_t>(out_boxes)) & 15) != 0)
+  if (((reinterpret_cast<uintptr_t>(boxes) | reinterpret_cast<uintptr_t>(out_boxes)) & 15) != 0)
     return RP_E_ARG;
-  const size_t per = (size_t)A * H * W;
-  const size_t n_total = per * N;
-  if (n_total > 0x7fffffffull) return RP_E_LIMIT;
-  const int k = (int)((size_t)pre_nms_top_n < per ? (size_t)pre_nms_top_n : per);
-  RpnWorkspace w = rpn_carve(workspace, n_total, N, k);
+  RpnSelWorkspace w = rpn_sel_carve(workspace, (size_t)n_cap, L, N);
   if (w.total > workspace_bytes) return RP_E_WORKSPACE;
-  rpn_keys_kernel<<<(unsigned)((n_total + 255) / 256), 256, 0, st>>>(objectness, N, A, H * W, w.keys_in,
-                                                                    w.vals_in);
+  rpn_sel_scan_kernel<<<1, RPN_THREADS, 0, st>>>(n_keep, L, N, w.img_off, w.seg_pos);
+  RP_LAUNCH_CHECK();
+  rpn_sel_keys_kernel<<<(unsigned)((n_cap + 255) / 256), 256, 0, st>>>(
+      scores, offsets, keep, w.img_off, w.seg_pos, L, N, n_cap, w.keys_in, w.vals_in);
   RP_LAUNCH_CHECK();
   RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out, w.vals_in,
-                                              w.vals_out, (int)n_total, 0, 32 + rpn_bits((size_t)N), st));
-  rpn_decode_kernel<<<N, RPN_THREADS, 0, st>>>(objectness, box_regression, anchors, im_wh, w.vals_out, A,
-                                               H * W, k, min_size, wx, wy, ww, wh, bbox_xform_clip,
-                                               w.pad_boxes, w.pad_scores, w.pad_index, w.counts);
-  RP_LAUNCH_CHECK();
-  rpn_offsets_kernel<<<1, 32, 0, st>>>(w.counts, N, out_offsets);
-  RP_LAUNCH_CHECK();
-  if (N > 65535) return RP_E_LIMIT;
-  rpn_pack_kernel<<<dim3((unsigned)((k + 255) / 256), (unsigned)N), 256, 0, st>>>(
-      w.pad_boxes, w.pad_scores, w.pad_index, out_offsets, k, out_boxes, out_scores, out_index);
+                                              w.vals_out, n_cap, 0, 32 + rpn_bits((size_t)N + 1), st));
+  rpn_sel_emit_kernel<<<dim3((unsigned)((top_n + 255) / 256), (unsigned)N), 256, 0, st>>>(
+      boxes, scores, w.img_off, w.vals_out, top_n, out_boxes, out_scores, out_count);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

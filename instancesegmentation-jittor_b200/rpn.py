@@ -5,10 +5,11 @@ detectron.jittor/detectron/modeling/rpn/inference.py (RPNPostProcessor: __init__
 add_gt_proposals :55-74, forward_for_single_feature_map :76-125, execute :127-155,
 select_over_all_levels :157-188, make_rpn_postprocessor :191-213) with the same names,
 arguments and results.  Where the reference runs permute / sigmoid / topk / two gathers /
-decode and then a per-image python loop of clip, remove_small_boxes and boxlist_nms, this
-module makes ONE rp_rpn_pre_nms call and ONE rp_nms_batched call per level for the whole
-batch, chained through device-side offsets, and reads the keep counts of ALL levels back in
-a single host copy.
+decode per level and then a per-image python loop of clip, remove_small_boxes and
+boxlist_nms, this module makes ONE rp_rpn_pre_nms_levels call (all levels, all images, one
+sort), ONE rp_nms_batched call over the L*N problems and, at test time, ONE
+rp_rpn_select_levels call, chained through device-side offsets; the host reads one small
+vector of counts back at the end.
 """
 import ctypes
 import math
@@ -108,8 +109,82 @@ def rpn_pre_nms(objectness, box_regression, anchors, im_wh, pre_nms_top_n, min_s
     return boxes, scores, index, offsets, k
 
 
+def rpn_pre_nms_levels(objectness, box_regression, anchors, im_wh, pre_nms_top_n, min_size,
+                       weights=(1.0, 1.0, 1.0, 1.0), bbox_xform_clip=math.log(1000.0 / 16)):
+    """All FPN levels of a batch in one set of launches (one sort for everything).
+
+    objectness / box_regression / anchors: lists over levels of [N,A_l,H_l,W_l] /
+    [N,4A_l,H_l,W_l] / [N,H_l*W_l*A_l,4].  Returns (boxes, scores, index, offsets [L*N+1], ks):
+    problem s = l*N + b owns rows offsets[s]:offsets[s+1]; ks[l] = min(top_n, A_l*H_l*W_l).
+    """
+    L = len(objectness)
+    if L < 1 or L > _lib.RP_MAX_LEVELS or len(box_regression) != L or len(anchors) != L:
+        raise ValueError("between 1 and %d levels, one tensor of each kind per level" % _lib.RP_MAX_LEVELS)
+    objectness = [_lib.as_f32(o, "objectness") for o in objectness]
+    box_regression = [_lib.as_f32(r, "box_regression") for r in box_regression]
+    anchors = [_lib.as_f32(a, "anchors") for a in anchors]
+    im_wh = _lib.as_f32(im_wh, "im_wh")
+    N = int(objectness[0].shape[0])
+    As, Hs, Ws, ks = [], [], [], []
+    for o, r, a in zip(objectness, box_regression, anchors):
+        if o.ndim != 4 or int(o.shape[0]) != N:
+            raise ValueError("objectness should be [N,A,H,W] with the same N on every level")
+        _, A, H, W = (int(v) for v in o.shape)
+        if tuple(r.shape) != (N, 4 * A, H, W):
+            raise ValueError("box_regression should be [%d,%d,%d,%d], got %s"
+                             % (N, 4 * A, H, W, tuple(r.shape)))
+        if a.numel() != N * A * H * W * 4:
+            raise ValueError("anchors should be [%d,%d,4], got %s" % (N, A * H * W, tuple(a.shape)))
+        As.append(A), Hs.append(H), Ws.append(W), ks.append(min(int(pre_nms_top_n), A * H * W))
+    if im_wh.numel() != 2 * N:
+        raise ValueError("im_wh should be [%d,2]" % N)
+    dev = objectness[0].device
+    cap = N * sum(ks)
+    boxes = torch.empty((cap, 4), dtype=_F32, device=dev)
+    scores = torch.empty((cap,), dtype=_F32, device=dev)
+    index = torch.empty((cap,), dtype=_I32, device=dev)
+    offsets = torch.empty((L * N + 1,), dtype=_I32, device=dev)
+    arr_i = lambda v: (ctypes.c_int * L)(*v)
+    arr_p = lambda ts: (ctypes.c_void_p * L)(*[_lib.dptr(t, _F32).value for t in ts])
+    cA, cH, cW = arr_i(As), arr_i(Hs), arr_i(Ws)
+    lib = _lib.lib()
+    nbytes = lib.rp_rpn_pre_nms_levels_workspace_bytes(L, N, cA, cH, cW, int(pre_nms_top_n))
+    ws = _lib.workspace(nbytes, dev, "rpn")
+    wx, wy, ww, wh = (float(w) for w in weights)
+    rc = lib.rp_rpn_pre_nms_levels(
+        arr_p(objectness), arr_p(box_regression), arr_p(anchors), cA, cH, cW, L,
+        _lib.dptr(im_wh, _F32), N, int(pre_nms_top_n), float(min_size), wx, wy, ww, wh,
+        float(bbox_xform_clip), _lib.dptr(boxes, _F32), _lib.dptr(scores, _F32),
+        _lib.dptr(index, _I32), _lib.dptr(offsets, _I32), ctypes.c_void_p(ws.data_ptr()),
+        ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "rp_rpn_pre_nms_levels")
+    return boxes, scores, index, offsets, ks
+
+
+def rpn_select_levels(boxes, scores, offsets, keep, n_keep, L, N, top_n):
+    """Per image, the top_n best of the boxes its L problems kept (inference.py:175-183).
+    Returns (out_boxes [N,top_n,4], out_scores [N,top_n], out_count [N] int32); no host sync."""
+    dev = boxes.device
+    cap = int(boxes.shape[0])
+    out_boxes = torch.empty((N, int(top_n), 4), dtype=_F32, device=dev)
+    out_scores = torch.empty((N, int(top_n)), dtype=_F32, device=dev)
+    out_count = torch.empty((N,), dtype=_I32, device=dev)
+    lib = _lib.lib()
+    nbytes = lib.rp_rpn_select_workspace_bytes(cap, L, N)
+    ws = _lib.workspace(nbytes, dev, "rpn_select")
+    rc = lib.rp_rpn_select_levels(
+        _lib.dptr(boxes, _F32), _lib.dptr(scores, _F32), _lib.dptr(offsets, _I32),
+        _lib.dptr(keep, _I32), _lib.dptr(n_keep, _I32), L, N, cap, int(top_n),
+        _lib.dptr(out_boxes, _F32), _lib.dptr(out_scores, _F32), _lib.dptr(out_count, _I32),
+        ctypes.c_void_p(ws.data_ptr()), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "rp_rpn_select_levels")
+    return out_boxes, out_scores, out_count
+
+
 class RPNPostProcessor(torch.nn.Module):
-    """rpn/inference.py:15-188."""
+    """rpn/inference.py:15-188.  Device work for the whole batch and all levels: one
+    rp_rpn_pre_nms_levels, one rp_nms_batched over the L*N problems and (test time) one
+    rp_rpn_select_levels; the host reads N (or L*N) counts back ONCE to slice BoxLists."""
 
     def __init__(self, pre_nms_top_n, post_nms_top_n, nms_thresh, min_size, box_coder=None,
                  fpn_post_nms_top_n=None, fpn_post_nms_per_batch=True):
@@ -125,6 +200,7 @@ class RPNPostProcessor(torch.nn.Module):
             fpn_post_nms_top_n = post_nms_top_n
         self.fpn_post_nms_top_n = fpn_post_nms_top_n
         self.fpn_post_nms_per_batch = fpn_post_nms_per_batch
+        self._anchor_cache = {}
 
     def is_training(self):
         return self.training
@@ -135,84 +211,86 @@ class RPNPostProcessor(torch.nn.Module):
             g.add_field("objectness", torch.ones(len(g), dtype=_F32, device=g.bbox.device))
         return [cat_boxlist((p, g)) for p, g in zip(proposals, gt_boxes)]
 
-    # ---- device part of one level: nothing here waits for the GPU
-    def _level_launch(self, anchors, objectness, box_regression):
-        N = int(objectness.shape[0])
-        dev = objectness.device
-        if isinstance(anchors, torch.Tensor):
-            raise TypeError("anchors: list[BoxList] (one per image), as in the reference")
-        image_shapes = [a.size for a in anchors]
-        if len(image_shapes) != N:
-            raise ValueError("%d anchor lists for %d images" % (len(image_shapes), N))
-        concat = torch.stack([a.bbox for a in anchors], dim=0).to(_F32).contiguous()
-        im_wh = torch.tensor([[float(s[0]), float(s[1])] for s in image_shapes], dtype=_F32).to(
+    def _stack_anchors(self, anchors):
+        """list[BoxList] of one level -> [N, H*W*A, 4].  Anchors depend only on the padded batch
+        shape, so the stacked tensor is reused while the per-image tensors stay the same objects."""
+        key = tuple((a.bbox.data_ptr(), int(a.bbox.shape[0])) for a in anchors)
+        hit = self._anchor_cache.get(key)
+        if hit is None:
+            if len(self._anchor_cache) > 64:
+                self._anchor_cache.clear()
+            hit = torch.stack([a.bbox for a in anchors], dim=0).to(_F32).contiguous()
+            self._anchor_cache[key] = hit
+        return hit
+
+    # ---- device part: nothing here waits for the GPU
+    def _launch(self, anchors_by_level, objectness, box_regression):
+        L, N = len(objectness), int(objectness[0].shape[0])
+        dev = objectness[0].device
+        shapes = [a.size for a in anchors_by_level[0]]
+        if len(shapes) != N:
+            raise ValueError("%d anchor lists for %d images" % (len(shapes), N))
+        stacked = [self._stack_anchors(a) for a in anchors_by_level]
+        im_wh = torch.tensor([[float(s[0]), float(s[1])] for s in shapes], dtype=_F32).to(
             dev, non_blocking=True)
         bc = self.box_coder
-        boxes, scores, index, offsets, k = rpn_pre_nms(
-            objectness, box_regression, concat, im_wh, self.pre_nms_top_n, self.min_size,
+        boxes, scores, index, offsets, ks = rpn_pre_nms_levels(
+            objectness, box_regression, stacked, im_wh, self.pre_nms_top_n, self.min_size,
             bc.weights, bc.bbox_xform_clip)
-        if self.nms_thresh > 0:
+        keep = n_keep = None
+        if self.nms_thresh > 0:  # boxlist_nms returns its input otherwise (boxlist_ops.py:24-25)
             keep, n_keep = layers.nms_batched(
                 boxes, scores, offsets, self.nms_thresh, None,
-                max_keep=self.post_nms_top_n if self.post_nms_top_n > 0 else -1, n_max=k)
-        else:  # boxlist_nms returns its input when nms_thresh <= 0 (boxlist_ops.py:24-25)
-            keep, n_keep = None, None
+                max_keep=self.post_nms_top_n if self.post_nms_top_n > 0 else -1, n_max=max(ks))
         return dict(boxes=boxes, scores=scores, offsets=offsets, keep=keep, n_keep=n_keep,
-                    shapes=image_shapes, N=N)
+                    shapes=shapes, N=N, L=L)
 
     @staticmethod
-    def _level_collect(lv, offsets_h, n_keep_h):
-        out = []
-        for b in range(lv["N"]):
-            o0, o1 = int(offsets_h[b]), int(offsets_h[b + 1])
-            if lv["keep"] is None:
-                sel = slice(o0, o1)
-                bx, sc = lv["boxes"][sel], lv["scores"][sel]
-            else:
-                idx = lv["keep"][o0: o0 + int(n_keep_h[b])].long() + o0
-                bx, sc = lv["boxes"][idx], lv["scores"][idx]
-            bl = BoxList(bx, lv["shapes"][b], mode="xyxy")
-            bl.add_field("objectness", sc)
-            out.append(bl)
-        return out
-
-    @staticmethod
-    def _read_back(levels):
-        """ONE device->host copy for the offsets and keep counts of every level."""
-        parts = []
-        for lv in levels:
-            parts.append(lv["offsets"])
-            if lv["n_keep"] is not None:
-                parts.append(lv["n_keep"])
+    def _collect(st):
+        """One device->host copy (offsets + keep counts), then BoxLists per (level, image)."""
+        parts = [st["offsets"]] + ([st["n_keep"]] if st["n_keep"] is not None else [])
         host = torch.cat(parts).cpu().tolist()
-        out, p = [], 0
-        for lv in levels:
-            N = lv["N"]
-            off = host[p: p + N + 1]
-            p += N + 1
-            nk = None
-            if lv["n_keep"] is not None:
-                nk = host[p: p + N]
-                p += N
-            out.append((off, nk))
+        S = st["L"] * st["N"]
+        off, nk = host[:S + 1], host[S + 1:]
+        out = []
+        for l in range(st["L"]):
+            row = []
+            for b in range(st["N"]):
+                s = l * st["N"] + b
+                if st["keep"] is None:
+                    bx, sc = st["boxes"][off[s]: off[s + 1]], st["scores"][off[s]: off[s + 1]]
+                else:
+                    idx = st["keep"][off[s]: off[s] + nk[s]].long() + off[s]
+                    bx, sc = st["boxes"][idx], st["scores"][idx]
+                bl = BoxList(bx, st["shapes"][b], mode="xyxy")
+                bl.add_field("objectness", sc)
+                row.append(bl)
+            out.append(row)
         return out
 
     def forward_for_single_feature_map(self, anchors, objectness, box_regression):
         """anchors: list[BoxList]; objectness [N,A,H,W]; box_regression [N,4A,H,W]."""
-        lv = self._level_launch(anchors, objectness, box_regression)
-        (off, nk), = self._read_back([lv])
-        return self._level_collect(lv, off, nk)
+        st = self._launch([list(anchors)], [objectness], [box_regression])
+        return self._collect(st)[0]
 
     def forward(self, anchors, objectness, box_regression, targets=None):
         """anchors: list[list[BoxList]] (image-major); objectness, box_regression: list per level."""
         num_levels = len(objectness)
-        anchors = list(zip(*anchors))
-        levels = [self._level_launch(a, o, b) for a, o, b in zip(anchors, objectness, box_regression)]
-        sampled = [self._level_collect(lv, off, nk)
-                   for lv, (off, nk) in zip(levels, self._read_back(levels))]
-        boxlists = [cat_boxlist(bl) for bl in zip(*sampled)]
-        if num_levels > 1:
-            boxlists = self.select_over_all_levels(boxlists)
+        st = self._launch(list(zip(*anchors)), list(objectness), list(box_regression))
+        per_batch = self.is_training() and self.fpn_post_nms_per_batch
+        if num_levels > 1 and not per_batch and st["keep"] is not None:
+            ob, osc, cnt = rpn_select_levels(st["boxes"], st["scores"], st["offsets"], st["keep"],
+                                             st["n_keep"], st["L"], st["N"], self.fpn_post_nms_top_n)
+            boxlists = []
+            for b, c in enumerate(cnt.cpu().tolist()):  # the one host read of the stage
+                bl = BoxList(ob[b, :c], st["shapes"][b], mode="xyxy")
+                bl.add_field("objectness", osc[b, :c])
+                boxlists.append(bl)
+        else:
+            sampled = self._collect(st)
+            boxlists = [cat_boxlist(bl) for bl in zip(*sampled)]
+            if num_levels > 1:
+                boxlists = self.select_over_all_levels(boxlists)
         if self.is_training() and targets is not None:
             boxlists = self.add_gt_proposals(boxlists, targets)
         return boxlists
@@ -220,8 +298,8 @@ class RPNPostProcessor(torch.nn.Module):
     execute = forward
 
     def select_over_all_levels(self, boxlists):
-        """inference.py:157-188 (top-k of the concatenated objectness; stable: equal scores keep
-        the lower index)."""
+        """inference.py:157-188 on BoxLists (the training per-batch branch, and the fallback of the
+        test-time branch).  Stable: equal scores keep the lower index."""
         num_images = len(boxlists)
         if self.is_training() and self.fpn_post_nms_per_batch:
             objectness = torch.cat([b.get_field("objectness") for b in boxlists], dim=0)

@@ -73,6 +73,46 @@ def test_pre_nms_matches_oracle(case):
         assert off[N] < N * k  # the filter removed something: the packed layout is exercised
 
 
+def test_pre_nms_levels_matches_oracle():
+    N, A = 3, 3
+    shapes = [(50, 84, 16), (25, 42, 32), (13, 21, 64), (2, 3, 128)]
+    lv = [synth.rpn_level(N, A, H, W, s, seed=40 + s, ties=(s == 32)) for H, W, s in shapes]
+    im_wh = lv[0][3]
+    boxes, scores, index, offsets, ks = rp.rpn_pre_nms_levels(
+        [T(l[1]) for l in lv], [T(l[2]) for l in lv], [T(l[0]) for l in lv], T(im_wh), 600, 6.0)
+    assert ks == [600, 600, 600, 18]
+    off = offsets.cpu().numpy()
+    bx, sc, ix = boxes.cpu().numpy(), scores.cpu().numpy(), index.cpu().numpy()
+    assert bx.shape[0] == N * sum(ks) and off[0] == 0
+    for l, lvl in enumerate(lv):
+        ref = oracle.rpn_pre_nms(lvl[1], lvl[2], lvl[0], im_wh, 600, 6.0)
+        for b in range(N):
+            sl = slice(off[l * N + b], off[l * N + b + 1])
+            np.testing.assert_array_equal(ix[sl], ref[b][2])
+            np.testing.assert_array_equal(sc[sl], ref[b][1])
+            np.testing.assert_array_equal(bx[sl], ref[b][0])
+
+
+def test_select_levels_matches_host_branch():
+    # rp_rpn_select_levels against the BoxList form of inference.py:175-183, tie-heavy scores
+    N, A = 3, 3
+    shapes = [(25, 42, 32), (13, 21, 64), (7, 11, 128)]
+    lv = [synth.rpn_level(N, A, H, W, s, seed=60 + s, ties=True) for H, W, s in shapes]
+    im_wh = lv[0][3]
+    anchors = [[rp.BoxList(T(l[0][b]), (int(im_wh[b, 0]), int(im_wh[b, 1]))) for l in lv] for b in range(N)]
+    objs, regs = [T(l[1]) for l in lv], [T(l[2]) for l in lv]
+    for top in (50, 400, 5000):
+        post = rp.RPNPostProcessor(1000, 300, 0.7, 0, fpn_post_nms_top_n=top)
+        post.eval()
+        fused = post(anchors, objs, regs)
+        st = post._launch(list(zip(*anchors)), objs, regs)
+        host = post.select_over_all_levels([rp.cat_boxlist(bl) for bl in zip(*post._collect(st))])
+        for f, h in zip(fused, host):
+            np.testing.assert_array_equal(f.bbox.cpu().numpy(), h.bbox.cpu().numpy())
+            np.testing.assert_array_equal(f.get_field("objectness").cpu().numpy(),
+                                          h.get_field("objectness").cpu().numpy())
+
+
 def _anchor_lists(anchors, im_wh):
     return [rp.BoxList(T(anchors[b]), (int(im_wh[b, 0]), int(im_wh[b, 1])), mode="xyxy")
             for b in range(anchors.shape[0])]

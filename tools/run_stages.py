@@ -92,3 +92,34 @@ pmt, pbt = T(pm), T(pb)
 pout = torch.empty((100, 800, 1333), dtype=torch.uint8, device=dev)
 timed("paste_masks 100 x 800x1333", lambda: rp.paste_masks(pmt, pbt, 800, 1333, out=pout),
       100 * 28 * 28 * 4 + 100 * 800 * 1333)
+
+# RPN proposal stage, 5 FPN levels of an 800 x 1344 batch, test configuration
+# (PRE_NMS_TOP_N_TEST 1000, POST_NMS_TOP_N_TEST 1000, FPN_POST_NMS_TOP_N_TEST 1000, thr 0.7)
+N, A = 8, 3
+shapes5 = [(200, 336, 4), (100, 168, 8), (50, 84, 16), (25, 42, 32), (13, 21, 64)]
+lv = [synth.rpn_level(N, A, H, W, s, seed=100 + s) for H, W, s in shapes5]
+im_wh = lv[0][3]
+anchors = [[rp.BoxList(T(l[0][b]), (int(im_wh[b, 0]), int(im_wh[b, 1]))) for l in lv] for b in range(N)]
+objs, regs = [T(l[1]) for l in lv], [T(l[2]) for l in lv]
+anc_t = [T(l[0]) for l in lv]
+wh_t = T(im_wh)
+head_bytes = sum(l[1].nbytes + l[2].nbytes + l[0].nbytes for l in lv)
+for top_n in (1000, 2000):
+    post = rp.RPNPostProcessor(top_n, top_n, 0.7, 0, fpn_post_nms_top_n=top_n)
+    post.eval()
+
+    def device_part():
+        bx, sc, ix, off, ks = rp.rpn_pre_nms_levels(objs, regs, anc_t, wh_t, top_n, 0.0)
+        keep, nk = rp.nms_batched(bx, sc, off, 0.7, max_keep=top_n, n_max=max(ks))
+        rp.rpn_select_levels(bx, sc, off, keep, nk, len(lv), N, top_n)
+
+    def per_level():
+        for a, o, r in zip(anc_t, objs, regs):
+            bx, sc, ix, off, k = rp.rpn_pre_nms(o, r, a, wh_t, top_n, 0.0)
+            rp.nms_batched(bx, sc, off, 0.7, max_keep=top_n, n_max=k)
+
+    timed("rpn pre-NMS 5 levels x %d images, top %d" % (N, top_n),
+          lambda: rp.rpn_pre_nms_levels(objs, regs, anc_t, wh_t, top_n, 0.0), head_bytes)
+    timed("rpn pre-NMS + NMS, one call per level", per_level)
+    timed("rpn pre-NMS + NMS + select, all levels fused", device_part)
+    timed("RPNPostProcessor.execute (BoxLists out)", lambda: post(anchors, objs, regs))
