@@ -338,6 +338,12 @@ def extras(rp, torch, dev):
 
     out["rpn_post_device_ms_per_batch8"] = med(rpn_device)
     out["rpn_post_execute_ms_per_batch8"] = med(lambda: post(anchors, objs, regs))
+    # --- box-head post-processor: 8 images x 1000 proposals x 81 classes
+    lg, reg, pr, counts, bwh = synth.box_head_batch(8, 1000, seed=3)
+    lgt, regt, prt, bwht = T(lg), T(reg), T(pr), T(bwh)
+    boffs = T(np.concatenate([[0], np.cumsum(counts)]).astype(np.int32))
+    out["box_post_device_ms_per_batch8"] = med(
+        lambda: rp.box_post(lgt, regt, prt, boffs, bwht, 1000, 0.05, 0.5, 100))
     return out
 
 

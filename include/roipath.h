@@ -241,6 +241,37 @@ RP_API int rp_rpn_select_levels(const float* boxes, const float* scores, const i
                          float* out_boxes, float* out_scores, int* out_count, void* workspace,
                          size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Box-head post-processor (the caller of the per-class NMS).
+ * Replaces: PostProcessor.execute det/modeling/roi_heads/box_head/inference.py:45-90 (softmax,
+ *           class-wise BoxCoder.decode, clip_to_image) and filter_results :112-195 (per class
+ *           j >= 1: score > score_thresh, boxlist_nms; cat over classes; when more than
+ *           detections_per_img survive, keep those with score >= the detections_per_img-th
+ *           largest score -- jt.kthvalue :180-187, ties all kept).
+ *   class_logits [R,C]; box_regression [R,reg_cols] (reg_cols = 4C, or any multiple of 4 with
+ *   cls_agnostic != 0: the LAST four columns are used for every class, :66-67,71-72);
+ *   proposals [R,4] xyxy; image b owns rows [row_offsets[b], row_offsets[b+1]) (DEVICE int32
+ *   [N+1]); r_max >= the largest image's row count; im_wh [N,2] float (width, height).
+ *   cand_cap bounds the number of (row, class) pairs above the threshold that are processed
+ *   (R*(C-1) is always enough); n_cand [1] DEVICE receives the real number -- a caller that
+ *   passed a smaller cap compares and repeats the call when n_cand > cand_cap.
+ *   prob_out [R,C] softmax probabilities (may be NULL).
+ *   Image b's detections are rows [b*out_cap, b*out_cap + min(out_count[b], out_cap)) of
+ *   out_boxes [N*out_cap,4], out_scores, out_labels (int32 class), out_rows (int32 proposal
+ *   row relative to row_offsets[b]; may be NULL), class-major, descending score inside a
+ *   class; out_count[b] is the full count (it can exceed detections_per_img on ties).
+ * Limits: nms_thresh > 0; N*(C-1) <= 65535.
+ * ------------------------------------------------------------------------------------ */
+RP_API size_t rp_box_post_workspace_bytes(int R, int C, int N, int r_max, int cand_cap);
+
+RP_API int rp_box_post(const float* class_logits, const float* box_regression, const float* proposals,
+                const int* row_offsets, const float* im_wh, int R, int C, int N, int r_max,
+                int reg_cols, int cls_agnostic, float score_thresh, double nms_thresh,
+                int detections_per_img, float wx, float wy, float ww, float wh,
+                float bbox_xform_clip, int cand_cap, float* prob_out, float* out_boxes,
+                float* out_scores, int* out_labels, int* out_rows, int* out_count, int out_cap,
+                int* n_cand, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

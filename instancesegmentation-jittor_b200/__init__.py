@@ -13,6 +13,7 @@ from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_
                      paste_masks)
 from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_format,
                       make_pooler, pooler_backward, pooler_forward)
+from .box_head import PostProcessor, box_post, make_roi_box_post_processor
 from .rpn import (BoxCoder, RPNPostProcessor, box_decode, make_rpn_postprocessor, rpn_pre_nms,
                   rpn_pre_nms_levels, rpn_select_levels)
 from .structures import (BoxList, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,

@@ -252,6 +252,37 @@ def rpn_pre_nms(objectness, box_regression, anchors, im_wh, pre_nms_top_n, min_s
             for b in range(N)]
 
 
+# --------------------------------------------------------------------------- box head
+def softmax_rows(x):
+    x, xp = _f(x)
+    out = np.zeros_like(x)
+    lib().orc_softmax_rows(xp, x.shape[0], x.shape[1], out.ctypes.data_as(_f32p))
+    return out
+
+
+def box_post_image(logits, reg, props, im_wh, score_thresh=0.05, nms_thresh=0.5, dets=100,
+                   weights=(10.0, 10.0, 5.0, 5.0), clip=float(np.log(1000.0 / 16)),
+                   cls_agnostic=False):
+    """One image of PostProcessor.execute + filter_results -> (boxes, scores, labels, rows)."""
+    logits, lp = _f(logits)
+    reg, rp_ = _f(reg)
+    props, pp = _f(props)
+    n, C = logits.shape
+    cap = max(n * (C - 1), 1)
+    ob = np.zeros((cap, 4), np.float32)
+    osc = np.zeros((cap,), np.float32)
+    ol = np.zeros((cap,), np.int32)
+    orow = np.zeros((cap,), np.int32)
+    cf = ctypes.c_float
+    fn = lib().orc_box_post_image
+    fn.restype = ctypes.c_int
+    m = fn(lp, rp_, pp, n, C, reg.shape[1], int(bool(cls_agnostic)), cf(im_wh[0]), cf(im_wh[1]),
+           cf(score_thresh), ctypes.c_double(nms_thresh), int(dets), cf(weights[0]), cf(weights[1]),
+           cf(weights[2]), cf(weights[3]), cf(clip), ob.ctypes.data_as(_f32p),
+           osc.ctypes.data_as(_f32p), ol.ctypes.data_as(_i32p), orow.ctypes.data_as(_i32p))
+    return ob[:m].copy(), osc[:m].copy(), ol[:m].copy(), orow[:m].copy()
+
+
 # --------------------------------------------------------------------------- Yolact
 def yolact_decode(loc, priors):
     loc, lp = _f(loc)

@@ -22,6 +22,8 @@
  *     detectron.jittor/tests/test_box_coder.py (tests/golden/box_coder_kat.npz, atol 1e-4).
  *   - orc_rpn_pre_nms: the decode inside is pinned as above; the sort's tie order, the clip and
  *     the small-box test follow the source text (PARITY UNPINNED for those).
+ *   - orc_box_post_image / orc_softmax_rows: PARITY UNPINNED (no known-answer test in the
+ *     reference); the decode and the NMS inside are the pinned functions above.
  *   - everything else (ml_nms label term, FastNMS, jaccard, crop, assembly, bilinear
  *     resize, paste-back, level mapping): PARITY UNPINNED -- the reference holds no
  *     known-answer test and Jittor is not installable; the restatement follows the
@@ -888,6 +890,111 @@ ORC_API void orc_rpn_pre_nms(const float* objectness, const float* box_regressio
   }
   free(flat);
   free(order);
+}
+
+/* ------------------------------------------------------------------------- */
+/* Box-head post-processor                                                    */
+/* ------------------------------------------------------------------------- */
+
+/* nn.softmax(class_logits, -1) det/modeling/roi_heads/box_head/inference.py:58, restated as
+ * exp(x - max) / sum with the sum taken in class order (PARITY UNPINNED: Jittor's reduction
+ * order is not visible in the reference tree). */
+ORC_API void orc_softmax_rows(const float* x, int R, int C, float* out) {
+  for (int i = 0; i < R; ++i) {
+    const float* r = x + (size_t)i * C;
+    float* o = out + (size_t)i * C;
+    float m = r[0];
+    for (int c = 1; c < C; ++c) m = fmaxf(m, r[c]);
+    float sum = 0.0f;
+    for (int c = 0; c < C; ++c) {
+      o[c] = rp_expf(r[c] - m);
+      sum += o[c];
+    }
+    for (int c = 0; c < C; ++c) o[c] = o[c] / sum;
+  }
+}
+
+static int orc_cmp_float_asc(const void* a, const void* b) {
+  const float x = *(const float*)a, y = *(const float*)b;
+  return (x > y) - (x < y);
+}
+
+/* One image of PostProcessor.execute + filter_results, inference.py:45-90,112-195.
+ *   logits [n,C], reg [n,reg_cols], props [n,4]; softmax (:58); decode of every class's codes
+ *   with the proposal (:68-70; cls_agnostic: the last four columns for every class :66-67,
+ *   71-72); clip_to_image(remove_empty=False) (:80); per class j = 1..C-1 (:126-168):
+ *   inds = nonzero(scores[:,j] > score_thresh) in ascending row order, boxlist_nms(thr)
+ *   -> kept in descending score order, labels = j; cat over classes (:170); when
+ *   number_of_detections > detections_per_img > 0 (:178): image_thresh =
+ *   kthvalue(scores, n - dets + 1) = the dets-th largest score, keep = scores >= image_thresh in
+ *   their order (:180-187).
+ * The score threshold is compared in float32 (PARITY UNPINNED).
+ * Outputs sized n*(C-1): out_boxes [.,4], out_scores, out_labels, out_rows; returns the count. */
+ORC_API int orc_box_post_image(const float* logits, const float* reg, const float* props, int n, int C,
+                               int reg_cols, int cls_agnostic, float im_w, float im_h,
+                               float score_thresh, double nms_thresh, int dets, float wx, float wy,
+                               float ww, float wh, float clip, float* out_boxes, float* out_scores,
+                               int* out_labels, int* out_rows) {
+  if (n <= 0) return 0;
+  float* prob = (float*)malloc(sizeof(float) * (size_t)n * C);
+  float* cb = (float*)malloc(sizeof(float) * 4 * (size_t)n);
+  float* cs = (float*)malloc(sizeof(float) * (size_t)n);
+  int* crow = (int*)malloc(sizeof(int) * (size_t)n);
+  int* keep = (int*)malloc(sizeof(int) * (size_t)n);
+  orc_softmax_rows(logits, n, C, prob);
+  int m = 0;
+  for (int j = 1; j < C; ++j) {
+    int nc = 0;
+    for (int i = 0; i < n; ++i) {
+      const float p = prob[(size_t)i * C + j];
+      if (!(p > score_thresh)) continue;
+      const float* code = reg + (size_t)i * reg_cols + (cls_agnostic ? reg_cols - 4 : 4 * j);
+      float* b = cb + (size_t)nc * 4;
+      orc_box_decode(code, props + (size_t)i * 4, 1, 1, wx, wy, ww, wh, clip, b);
+      b[0] = fminf(fmaxf(b[0], 0.0f), im_w - 1.0f);
+      b[1] = fminf(fmaxf(b[1], 0.0f), im_h - 1.0f);
+      b[2] = fminf(fmaxf(b[2], 0.0f), im_w - 1.0f);
+      b[3] = fminf(fmaxf(b[3], 0.0f), im_h - 1.0f);
+      cs[nc] = p;
+      crow[nc] = i;
+      ++nc;
+    }
+    if (nc == 0) continue;
+    const int nk = orc_nms(cb, cs, nc, nms_thresh, NULL, -1, keep);
+    for (int q = 0; q < nk; ++q) {
+      memcpy(out_boxes + (size_t)m * 4, cb + (size_t)keep[q] * 4, sizeof(float) * 4);
+      out_scores[m] = cs[keep[q]];
+      out_labels[m] = j;
+      out_rows[m] = crow[keep[q]];
+      ++m;
+    }
+  }
+  if (dets > 0 && m > dets) {
+    float* sorted = (float*)malloc(sizeof(float) * (size_t)m);
+    memcpy(sorted, out_scores, sizeof(float) * (size_t)m);
+    qsort(sorted, (size_t)m, sizeof(float), orc_cmp_float_asc);
+    const float image_thresh = sorted[m - dets]; /* kthvalue(k = m - dets + 1), 1-based */
+    free(sorted);
+    int w = 0;
+    for (int q = 0; q < m; ++q) {
+      if (out_scores[q] >= image_thresh) {
+        if (w != q) {
+          memmove(out_boxes + (size_t)w * 4, out_boxes + (size_t)q * 4, sizeof(float) * 4);
+          out_scores[w] = out_scores[q];
+          out_labels[w] = out_labels[q];
+          out_rows[w] = out_rows[q];
+        }
+        ++w;
+      }
+    }
+    m = w;
+  }
+  free(prob);
+  free(cb);
+  free(cs);
+  free(crow);
+  free(keep);
+  return m;
 }
 
 /* ------------------------------------------------------------------------- */

@@ -153,3 +153,50 @@ def rpn_level(n_images, A, H, W, stride, seed, size=None, ties=False, img_w=IMG_
     if n_images > 1:
         im_wh[1] = (int(img_w * 0.75), int(img_h * 0.9))  # images of a batch differ in size
     return anchors, obj.astype(np.float32), reg, im_wh
+
+
+def box_head_batch(n_images, per_image, num_classes=81, seed=0, ties=False, objects=12,
+                   img_w=IMG_W, img_h=IMG_H):
+    """Box-head outputs for a batch: per image `objects` ground-truth-like
+    boxes with a class each; 70 % of the proposals are jittered copies of them (high logit on the
+    object's class -> real per-class suppression), the rest are background.  ties=True draws the
+    foreground logit rows from a pool of 16 rows: many EQUAL scores on different boxes, which
+    exercises the sort's tie order and the kthvalue cut.
+    Returns logits [R,C], regression [R,4C], proposals [R,4], per-image counts, im_wh [N,2]."""
+    rng = np.random.default_rng(seed)
+    C = num_classes
+    counts = [per_image if i % 2 == 0 else max(1, per_image - 37) for i in range(n_images)]
+    pool = rng.standard_normal((16, C)).astype(np.float32)
+    pool[:, 0] = rng.uniform(0, 2, 16)
+    logits, props = [], []
+    for b, n in enumerate(counts):
+        obj = proposals(objects, seed * 131 + b, img_w, img_h, smin=40.0, smax=500.0, adversarial=False)
+        cls = rng.integers(1, C, objects)
+        lg = rng.standard_normal((n, C)).astype(np.float32)
+        lg[:, 0] += 6.0
+        pr = proposals(n, seed * 977 + b, img_w, img_h, adversarial=False)
+        fg = rng.random(n) < 0.7
+        which = rng.integers(0, objects, n)
+        for i in np.nonzero(fg)[0]:
+            o = obj[which[i]]
+            w, h = o[2] - o[0], o[3] - o[1]
+            pr[i] = o + rng.normal(0, 0.08, 4) * np.array([w, h, w, h])
+            if ties:
+                lg[i] = pool[rng.integers(0, 16)]
+                lg[i, cls[which[i]]] = 4.0
+            else:
+                lg[i, 0] = rng.uniform(0, 3)
+                lg[i, cls[which[i]]] = rng.uniform(2, 6)
+                lg[i, rng.integers(1, C)] += rng.uniform(0, 4)  # a second plausible class
+        pr[:, 0::2] = np.clip(np.sort(pr[:, 0::2], 1), 0, img_w - 1)
+        pr[:, 1::2] = np.clip(np.sort(pr[:, 1::2], 1), 0, img_h - 1)
+        logits.append(lg)
+        props.append(pr.astype(np.float32))
+    logits = np.concatenate(logits).astype(np.float32)
+    props = np.concatenate(props).astype(np.float32)
+    reg = (rng.standard_normal((logits.shape[0], 4 * C)) * 1.5).astype(np.float32)
+    reg[::97, 2::4] = 30.0  # dw above the clamp
+    im_wh = np.tile(np.array([[img_w, img_h]], np.float32), (n_images, 1))
+    if n_images > 1:
+        im_wh[1] = (int(img_w * 0.75), int(img_h * 0.9))
+    return logits, reg, props, counts, im_wh

@@ -25,7 +25,8 @@ def test_header_declares_the_whole_path():
     for must in ("rp_roi_align_forward", "rp_roi_align_backward", "rp_pooler_forward",
                  "rp_pooler_backward", "rp_level_map", "rp_nms_batched", "rp_fast_nms_batched",
                  "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode",
-                 "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes"):
+                 "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes",
+                 "rp_rpn_pre_nms_levels", "rp_rpn_select_levels", "rp_box_post"):
         assert must in names
 
 
@@ -68,6 +69,17 @@ def test_argument_errors_need_no_gpu():
     ws = L.rp_rpn_pre_nms_workspace_bytes(2, 3, 200, 336, 2000)
     assert 2 * 3 * 200 * 336 * 24 < ws < 32 * 1024 * 1024
     assert L.rp_rpn_pre_nms_workspace_bytes(0, 3, 4, 4, 10) == 0
+    A3 = (ctypes.c_int * 2)(3, 3)
+    H2 = (ctypes.c_int * 2)(50, 25)
+    W2 = (ctypes.c_int * 2)(84, 42)
+    assert L.rp_rpn_pre_nms_levels_workspace_bytes(2, 4, A3, H2, W2, 1000) > 4 * 3 * (50 * 84 + 25 * 42) * 24
+    assert L.rp_rpn_pre_nms_levels_workspace_bytes(9, 4, A3, H2, W2, 1000) == 0  # > RP_MAX_LEVELS
+    assert L.rp_rpn_select_levels(None, None, None, None, None, 5, 8, 1000, 100, None, None, None,
+                                  None, 0, None) == -1
+    assert L.rp_box_post_workspace_bytes(8000, 81, 8, 1000, 8000 * 80) > 8000 * 80 * 28
+    assert L.rp_box_post(None, None, None, None, None, 10, 81, 1, 10, 324, 0, 0.05, 0.5, 100, 10.0,
+                         10.0, 5.0, 5.0, 4.0, 800, None, None, None, None, None, None, 200, None,
+                         None, 0, None) == -1
 
 
 def test_no_cpu_fallback():

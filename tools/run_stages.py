@@ -123,3 +123,16 @@ for top_n in (1000, 2000):
     timed("rpn pre-NMS + NMS, one call per level", per_level)
     timed("rpn pre-NMS + NMS + select, all levels fused", device_part)
     timed("RPNPostProcessor.execute (BoxLists out)", lambda: post(anchors, objs, regs))
+
+# box-head post-processor, 8 images x 1000 proposals, 81 classes (thr 0.05, NMS 0.5, 100 per image)
+lg, reg, pr, counts, wh = synth.box_head_batch(8, 1000, seed=3)
+lgt, regt, prt, wht = T(lg), T(reg), T(pr), T(wh)
+offs_bh = T(np.concatenate([[0], np.cumsum(counts)]).astype(np.int32))
+bls, o = [], 0
+for b, n in enumerate(counts):
+    bls.append(rp.BoxList(prt[o:o + n], (int(wh[b, 0]), int(wh[b, 1]))))
+    o += n
+bh = rp.PostProcessor(0.05, 0.5, 100)
+timed("box post device part, 8 x 1000 x 81", lambda: rp.box_post(lgt, regt, prt, offs_bh, wht, 1000, 0.05, 0.5, 100),
+      lg.nbytes + reg.nbytes + pr.nbytes)
+timed("PostProcessor.execute (BoxLists out)", lambda: bh((lgt, regt), bls))
