@@ -312,6 +312,17 @@ def extras(rp, torch, dev):
     out["mask_assemble_ms_per_batch64"] = ms_a
     out["mask_assemble_gbs"] = (B * (138 * 138 * 32 * 4 + 100 * 32 * 4 + 1600) + B * 100 * 550 * 550) / (ms_a * 1e-3) / 1e9
     del masks_buf, yp
+    # --- Yolact Detect pre-stage from the raw head outputs, batch 64:
+    #     decode + class-max + conf filter + gathers over the 399 MB conf tensor
+    raw = [synth.yolact_image(100 + i, priors) for i in range(4)]
+    loc64 = T(np.stack([raw[i % 4][0] for i in range(B)]))
+    conf64 = T(np.stack([raw[i % 4][1] for i in range(B)]))
+    mask64 = T(np.stack([raw[i % 4][2] for i in range(B)]))
+    pri_t = T(priors)
+    ms_f = med(lambda: rp.detect_prefilter(loc64, conf64, mask64, pri_t, 0.05), n=5, warm=2)
+    out["yolact_prefilter_ms_per_batch64"] = ms_f
+    out["yolact_prefilter_gbs"] = (conf64.numel() + loc64.numel()) * 4 / (ms_f * 1e-3) / 1e9
+    del loc64, conf64, mask64
     # --- paste-back, 100 instances at 1333x800 (BASELINE configs[4], one image per launch)
     pm, pb = synth.paste_inputs(100, 200)
     pmt, pbt = T(pm), T(pb)

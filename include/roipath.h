@@ -142,6 +142,25 @@ RP_API int rp_yolact_decode(const float* loc, const float* priors, int n, float*
  *   offsets[b]; may be NULL), n_out [B] int32.
  * cross_class != 0 selects cc_fast_nms (max_det is then ignored up to top_k).
  * Limits: top_k <= 256. */
+/* Detect pre-stage for a whole batch: Detect.__call__ / detect 'Slices'
+ * yol/layers/functions/detection.py:64-98 -- decode (box_utils.py:272-316), class-max over the
+ * foreground classes, conf_scores > conf_thresh, and the gathers of boxes / mask coefficients /
+ * scores, without the boolean-mask synchronisation.
+ *   loc [B,P,4]; conf [B,P,NC] (class 0 = background); mask [B,P,D]; priors [P,4].
+ *   Kept priors of image b, in prior order, are rows [out_offsets[b], out_offsets[b+1]) of
+ *   out_boxes [cand_cap,4], out_coeff [cand_cap,D], out_prior [cand_cap] (prior index) and
+ *   COLUMNS of out_scores [NC-1, cand_cap] (row c = class c+1) -- exactly the
+ *   (boxes, coeff, scores, offsets, n_total = cand_cap, C = NC-1) inputs of rp_fast_nms_batched.
+ *   out_offsets [B+1] DEVICE int32; n_cand [1] DEVICE: the real number of kept priors; when it
+ *   exceeds cand_cap the run was truncated and the caller repeats it with more room. */
+RP_API size_t rp_yolact_prefilter_workspace_bytes(int B, int P, int cand_cap);
+
+RP_API int rp_yolact_prefilter(const float* loc, const float* conf, const float* mask,
+                        const float* priors, int B, int P, int NC, int D, float conf_thresh,
+                        int cand_cap, float* out_boxes, float* out_coeff, float* out_scores,
+                        int* out_prior, int* out_offsets, int* n_cand, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
 RP_API size_t rp_fast_nms_workspace_bytes(int n_total, int n_max, int B, int C, int top_k);
 
 RP_API int rp_fast_nms_batched(const float* boxes, const float* coeff, const float* scores,

@@ -18,7 +18,7 @@ from .rpn import (BoxCoder, RPNPostProcessor, box_decode, make_rpn_postprocessor
                   rpn_pre_nms_levels, rpn_select_levels)
 from .structures import (BoxList, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
                          remove_small_boxes)
-from .yolact import (Detect, crop, decode, fast_nms_batched, mask_assemble, postprocess,
+from .yolact import (Detect, crop, decode, detect_prefilter, fast_nms_batched, mask_assemble, postprocess,
                      sanitize_coordinates)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

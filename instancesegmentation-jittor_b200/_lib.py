@@ -46,6 +46,9 @@ SIGNATURES = {
     "rp_rpn_pre_nms_levels_workspace_bytes": (_sz, [_i, _i, _vp, _vp, _vp, _i]),
     "rp_rpn_pre_nms_levels": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _f, _f, _f, _f, _f,
                                    _f, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "rp_yolact_prefilter_workspace_bytes": (_sz, [_i, _i, _i]),
+    "rp_yolact_prefilter": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _vp, _vp, _vp, _vp,
+                                 _vp, _vp, _sz, _vp]),
     "rp_box_post_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rp_box_post": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _d, _i, _f, _f, _f, _f,
                          _f, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _sz, _vp]),

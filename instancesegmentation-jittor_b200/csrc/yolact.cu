@@ -72,6 +72,11 @@ __global__ void fn_keys_kernel(const float* __restrict__ scores, const int* __re
   if (f >= (size_t)C * n_total) return;
   const int c = (int)(f / n_total);
   const int j = (int)(f - (size_t)c * n_total);
+  if (j >= offsets[B]) {  // n_total may be an upper bound: slack sorts behind every problem
+    keys[f] = (uint64_t)(uint32_t)(B * C) << 32;
+    vals[f] = 0;
+    return;
+  }
   const int b = fn_find_segment(offsets, B, j);
   keys[f] = ((uint64_t)(uint32_t)(b * C + c) << 32) | (uint64_t)fn_desc_bits(scores[f]);
   vals[f] = j - offsets[b];
@@ -84,6 +89,11 @@ __global__ void fn_cc_keys_kernel(const float* __restrict__ scores, const int* _
                                   int* __restrict__ cls_out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n_total) return;
+  if (j >= offsets[B]) {  // n_total may be an upper bound (rp_yolact_prefilter's cand_cap)
+    keys[j] = (uint64_t)(uint32_t)B << 32;
+    vals[j] = 0;
+    return;
+  }
   float best = scores[j];
   int bc = 0;
   for (int c = 1; c < C; ++c) {
@@ -415,7 +425,10 @@ FnWorkspace fn_carve(void* base, int n_total, int B, int C, int top_k) {
     o = rp_align_up(o + bytes, 256);
     return base ? (void*)((char*)base + at) : (void*)nullptr;
   };
-  const size_t n1 = (size_t)C * (size_t)(n_total > 0 ? n_total : 1);
+  // the batch-wide sort arrays hold C * n_total keys only on the legacy sort path; the default
+  // (fused select) path sorts nothing of that size, the cross-class path sorts n_total keys
+  const size_t nt = (size_t)(n_total > 0 ? n_total : 1);
+  const size_t n1 = rp_env_int("RP_FASTNMS_SELECT", 1) ? nt : (size_t)C * nt;
   const size_t n2 = (size_t)B * C * top_k;
   w.keys_in = (uint64_t*)take(n1 * 8);
   w.keys_out = (uint64_t*)take(n1 * 8);
@@ -442,9 +455,198 @@ int fn_bits(size_t v) {
   return b;
 }
 
+
+// ---- Detect pre-stage (detection.py:64-98) for a whole batch ---------------------------------
+// decode + class-max over the foreground classes + "> conf_thresh" + ordered compaction of the
+// kept priors, with the [C, n] score layout FastNMS reads.  A chunk is YP_CHUNK consecutive
+// priors of one image.
+constexpr int YP_CHUNK = 256;
+
+// pass A: flags[b*P + p] = max_c conf[b][p][1 + c] > thr; chunk_count[b*nchunks + chunk].
+// The chunk's conf rows are one contiguous run of YP_CHUNK*NC floats: it is streamed into shared
+// memory with 16-byte loads (all of them in flight at once), then thread t takes the maximum of row
+// t (row stride NC: conflict-free when NC is odd, 2-way at worst otherwise).
+__global__ void __launch_bounds__(YP_CHUNK)
+yp_flag_kernel(const float* __restrict__ conf, int P, int NC, float thr,
+               uint8_t* __restrict__ flags, int* __restrict__ chunk_count) {
+  extern __shared__ __align__(16) float yp_rows[];
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int p0 = chunk * YP_CHUNK;
+  const int rows = min(YP_CHUNK, P - p0);
+  const float* src = conf + ((size_t)b * P + p0) * NC;
+  const int nfl = rows * NC;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const int nv = nfl >> 2;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* d4 = reinterpret_cast<float4*>(yp_rows);
+#pragma unroll 8
+    for (int i = threadIdx.x; i < nv; i += YP_CHUNK) d4[i] = __ldcs(s4 + i);
+    for (int i = (nv << 2) + threadIdx.x; i < nfl; i += YP_CHUNK) yp_rows[i] = src[i];
+  } else {
+    for (int i = threadIdx.x; i < nfl; i += YP_CHUNK) yp_rows[i] = src[i];
+  }
+  __syncthreads();
+  int f = 0;
+  if (threadIdx.x < rows) {
+    const float* row = yp_rows + threadIdx.x * NC;
+    float m = -INFINITY;
+    for (int c = 1; c < NC; ++c) m = fmaxf(m, row[c]);
+    f = m > thr;
+    flags[(size_t)b * P + p0 + threadIdx.x] = (uint8_t)f;
+  }
+  const int cnt = __syncthreads_count(f);
+  if (threadIdx.x == 0) chunk_count[b * gridDim.x + chunk] = cnt;
+}
+
+// pass B: exclusive scan over the B*nchunks counts (image-major); offsets[b] = image starts,
+// everything clamped to cand_cap; n_cand = the unclamped total.  Thread t owns a contiguous run.
+__global__ void __launch_bounds__(FN_MAX_TOPK)
+yp_scan_kernel(const int* __restrict__ chunk_count, int B, int nchunks, int cand_cap,
+               int* __restrict__ chunk_off, int* __restrict__ offsets, int* __restrict__ n_cand) {
+  __shared__ int wsum[FN_MAX_TOPK / 32];
+  const int S = B * nchunks;
+  const int run = (S + FN_MAX_TOPK - 1) / FN_MAX_TOPK;
+  const int s0 = threadIdx.x * run, s1 = min(S, s0 + run);
+  int sum = 0;
+  for (int s = s0; s < s1; ++s) sum += chunk_count[s];
+  int tot;
+  int acc = fn_block_excl_scan(sum, wsum, &tot);
+  for (int s = s0; s < s1; ++s) {
+    const int o = min(acc, cand_cap);
+    chunk_off[s] = o;
+    if (s % nchunks == 0) offsets[s / nchunks] = o;
+    acc += chunk_count[s];
+  }
+  if (threadIdx.x == 0) {
+    offsets[B] = min(tot, cand_cap);
+    *n_cand = tot;
+  }
+}
+
+// pass C: thread per prior -> its slot; decoded box, prior index and image of the slot
+__global__ void __launch_bounds__(YP_CHUNK)
+yp_index_kernel(const float* __restrict__ loc, const float* __restrict__ priors,
+                const uint8_t* __restrict__ flags, const int* __restrict__ chunk_off, int P,
+                int cand_cap, float* __restrict__ out_boxes, int* __restrict__ slot_prior,
+                int* __restrict__ slot_img) {
+  __shared__ int wsum[YP_CHUNK / 32];
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int p = chunk * YP_CHUNK + threadIdx.x;
+  const int f = (p < P) ? (int)flags[(size_t)b * P + p] : 0;
+  int tot;
+  const int ex = fn_block_excl_scan(f, wsum, &tot);
+  const int dst = chunk_off[b * gridDim.x + chunk] + ex;
+  if (f && dst < cand_cap) {  // a clamped run drops the tail (the caller repeats with more room)
+    const float4 l = *reinterpret_cast<const float4*>(loc + ((size_t)b * P + p) * 4);
+    const float4 pr = *reinterpret_cast<const float4*>(priors + (size_t)p * 4);
+    // decode(), box_utils.py:272-316 -- same operation order as yolact_decode_kernel
+    const float cx = pr.x + l.x * 0.1f * pr.z;
+    const float cy = pr.y + l.y * 0.1f * pr.w;
+    const float w = pr.z * rp_expf(l.z * 0.2f);
+    const float h = pr.w * rp_expf(l.w * 0.2f);
+    const float x1 = cx - w / 2.0f;
+    const float y1 = cy - h / 2.0f;
+    *reinterpret_cast<float4*>(out_boxes + (size_t)dst * 4) = make_float4(x1, y1, w + x1, h + y1);
+    slot_prior[dst] = p;
+    slot_img[dst] = b;
+  }
+}
+
+// pass D: 32 consecutive slots per CTA.  Each warp copies whole rows (coefficients straight
+// through, conf rows into shared memory); the scores then leave transposed with the slots along
+// the lanes, i.e. as full 128-byte lines of out_scores [NC-1, cand_cap].
+constexpr int YP_GROUP = 32;
+__global__ void __launch_bounds__(YP_CHUNK)
+yp_gather_kernel(const float* __restrict__ conf, const float* __restrict__ mask,
+                 const int* __restrict__ offsets, const int* __restrict__ slot_prior,
+                 const int* __restrict__ slot_img, int B, int P, int NC, int D, int cand_cap,
+                 float* __restrict__ out_coeff, float* __restrict__ out_scores) {
+  extern __shared__ __align__(16) float yp_kept[];  // [YP_GROUP][NC]
+  const int total = offsets[B];
+  const int d0 = blockIdx.x * YP_GROUP;
+  if (d0 >= total) return;
+  const int cnt = min(YP_GROUP, total - d0);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int e = wid; e < cnt; e += YP_CHUNK / 32) {
+    const size_t row = (size_t)slot_img[d0 + e] * P + slot_prior[d0 + e];
+    const float* mrow = mask + row * D;
+    for (int d = lane; d < D; d += 32) out_coeff[(size_t)(d0 + e) * D + d] = mrow[d];
+    const float* crow = conf + row * NC;
+    for (int c = lane; c < NC; c += 32) yp_kept[e * NC + c] = crow[c];
+  }
+  __syncthreads();
+  if (lane < cnt)
+    for (int c = 1 + wid; c < NC; c += YP_CHUNK / 32)
+      out_scores[(size_t)(c - 1) * cand_cap + d0 + lane] = yp_kept[lane * NC + c];
+}
+
+struct YpWorkspace {
+  uint8_t* flags;
+  int *chunk_count, *chunk_off, *slot_img;
+  size_t total;
+};
+
+YpWorkspace yp_carve(void* base, int B, int P, int cand_cap) {
+  YpWorkspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (void*)((char*)base + off) : nullptr;
+    off += rp_align_up(bytes, 256);
+    return p;
+  };
+  const int nchunks = (P + YP_CHUNK - 1) / YP_CHUNK;
+  w.flags = (uint8_t*)take((size_t)B * P);
+  w.chunk_count = (int*)take(4 * (size_t)B * nchunks);
+  w.chunk_off = (int*)take(4 * (size_t)B * nchunks);
+  w.slot_img = (int*)take(4 * (size_t)cand_cap);
+  w.total = off;
+  return w;
+}
+
 }  // namespace
 
 extern "C" {
+
+size_t rp_yolact_prefilter_workspace_bytes(int B, int P, int cand_cap) {
+  if (B < 1 || P < 1 || cand_cap < 1) return 0;
+  return yp_carve(nullptr, B, P, cand_cap).total;
+}
+
+int rp_yolact_prefilter(const float* loc, const float* conf, const float* mask, const float* priors,
+                        int B, int P, int NC, int D, float conf_thresh, int cand_cap,
+                        float* out_boxes, float* out_coeff, float* out_scores, int* out_prior,
+                        int* out_offsets, int* n_cand, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (B < 1 || P < 1 || NC < 2 || D < 1 || cand_cap < 1 || B > 65535) return RP_E_ARG;
+  if (!loc || !conf || !mask || !priors || !out_boxes || !out_coeff || !out_scores || !out_prior ||
+      !out_offsets || !n_cand || !workspace)
+    return RP_E_ARG;
+  if (((reinterpret_cast<uintptr_t>(loc) | reinterpret_cast<uintptr_t>(priors) |
+        reinterpret_cast<uintptr_t>(out_boxes)) & 15) != 0)
+    return RP_E_ARG;
+  YpWorkspace w = yp_carve(workspace, B, P, cand_cap);
+  if (w.total > workspace_bytes) return RP_E_WORKSPACE;
+  const int nchunks = (P + YP_CHUNK - 1) / YP_CHUNK;
+  const dim3 grid((unsigned)nchunks, (unsigned)B);
+  const size_t flag_smem = (size_t)YP_CHUNK * NC * sizeof(float);
+  if (flag_smem > 200 * 1024) return RP_E_LIMIT;  // NC <= 200 classes
+  RP_CUDA_TRY(cudaFuncSetAttribute(yp_flag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)flag_smem));
+  yp_flag_kernel<<<grid, YP_CHUNK, flag_smem, st>>>(conf, P, NC, conf_thresh, w.flags, w.chunk_count);
+  RP_LAUNCH_CHECK();
+  yp_scan_kernel<<<1, FN_MAX_TOPK, 0, st>>>(w.chunk_count, B, nchunks, cand_cap, w.chunk_off,
+                                            out_offsets, n_cand);
+  RP_LAUNCH_CHECK();
+  yp_index_kernel<<<grid, YP_CHUNK, 0, st>>>(loc, priors, w.flags, w.chunk_off, P, cand_cap, out_boxes,
+                                             out_prior, w.slot_img);
+  RP_LAUNCH_CHECK();
+  yp_gather_kernel<<<(cand_cap + YP_GROUP - 1) / YP_GROUP, YP_CHUNK,
+                     (size_t)YP_GROUP * NC * sizeof(float), st>>>(
+      conf, mask, out_offsets, out_prior, w.slot_img, B, P, NC, D, cand_cap, out_coeff, out_scores);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
 
 int rp_yolact_decode(const float* loc, const float* priors, int n, float* out, void* stream) {
   if (n == 0) return RP_OK;
@@ -494,7 +696,7 @@ int rp_fast_nms_batched(const float* boxes, const float* coeff, const float* sco
     RP_LAUNCH_CHECK();
     RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
                                                 w.vals_in, w.vals_out, n_total, 0,
-                                                32 + fn_bits((size_t)B), st));
+                                                32 + fn_bits((size_t)B + 1), st));
     fn_cc_kernel<<<B, FN_MAX_TOPK, 0, st>>>(boxes, coeff, offsets, w.vals_out, w.best, w.cls, D,
                                             top_k, max_det, iou_thr, out_boxes, out_coeff,
                                             out_classes, out_scores, out_index, n_out);
@@ -515,7 +717,7 @@ int rp_fast_nms_batched(const float* boxes, const float* coeff, const float* sco
     RP_LAUNCH_CHECK();
     RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
                                                 w.vals_in, w.vals_out, (int)n1, 0,
-                                                32 + fn_bits((size_t)B * C), st));
+                                                32 + fn_bits((size_t)B * C + 1), st));
     fn_class_kernel<<<dim3((unsigned)C, (unsigned)B), FN_MAX_TOPK, 0, st>>>(
         boxes, scores, offsets, w.vals_out, C, n_total, top_k, iou_thr, second_threshold,
         conf_thresh, w.keys2_in, w.vals2_in, w.cand_score, w.cand_src);

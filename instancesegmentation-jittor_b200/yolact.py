@@ -82,6 +82,41 @@ def fast_nms_batched(boxes, coeff, scores, offsets, iou_threshold=0.5, top_k=200
     return {"box": ob, "mask": oc, "class": ocl, "score": osc, "index": oi, "count": cnt}
 
 
+def detect_prefilter(loc, conf, mask, priors, conf_thresh, cand_cap=None):
+    """Detect pre-stage for a whole batch (detection.py:64-98) in three launches: decode,
+    class-max over the foreground classes, `> conf_thresh`, ordered gathers.  No host sync.
+
+    loc [B,P,4], conf [B,P,NC], mask [B,P,D], priors [P,4].  Returns a dict of device tensors:
+    box [cap,4], mask [cap,D], score [NC-1,cap], prior [cap] int32, offsets [B+1] int32,
+    n_cand [1] int32 (the real number of kept priors: > cap means the run was truncated).
+    """
+    loc = _lib.as_f32(loc, "loc")
+    conf = _lib.as_f32(conf, "conf")
+    mask = _lib.as_f32(mask, "mask")
+    priors = _lib.as_f32(priors, "priors")
+    B, P = int(loc.shape[0]), int(loc.shape[1])
+    NC, D = int(conf.shape[-1]), int(mask.shape[-1])
+    if conf.numel() != B * P * NC or mask.numel() != B * P * D or priors.numel() != P * 4:
+        raise ValueError("loc [B,P,4], conf [B,P,NC], mask [B,P,D], priors [P,4]")
+    dev = loc.device
+    cap = int(cand_cap) if cand_cap else B * min(P, 4096)
+    out = dict(box=torch.empty((cap, 4), dtype=_F32, device=dev),
+               mask=torch.empty((cap, D), dtype=_F32, device=dev),
+               score=torch.empty((NC - 1, cap), dtype=_F32, device=dev),
+               prior=torch.empty((cap,), dtype=_I32, device=dev),
+               offsets=torch.empty((B + 1,), dtype=_I32, device=dev),
+               n_cand=torch.empty((1,), dtype=_I32, device=dev), cap=cap)
+    L = _lib.lib()
+    ws = _lib.workspace(L.rp_yolact_prefilter_workspace_bytes(B, P, cap), dev, "yolact_prefilter")
+    rc = L.rp_yolact_prefilter(
+        _lib.dptr(loc, _F32), _lib.dptr(conf, _F32), _lib.dptr(mask, _F32), _lib.dptr(priors, _F32),
+        B, P, NC, D, float(conf_thresh), cap, _lib.dptr(out["box"]), _lib.dptr(out["mask"]),
+        _lib.dptr(out["score"]), _lib.dptr(out["prior"]), _lib.dptr(out["offsets"]),
+        _lib.dptr(out["n_cand"]), ctypes.c_void_p(ws.data_ptr()), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "rp_yolact_prefilter")
+    return out
+
+
 class Detect(object):
     """Drop-in for layers.functions.detection.Detect (detection.py:11-237)."""
 
@@ -110,12 +145,43 @@ class Detect(object):
         out = []
         batch_size = loc_data.shape[0]
         num_priors = prior_data.shape[0]
+        if self.use_fast_nms:
+            return self._call_batched(loc_data, conf_data, mask_data, prior_data, proto_data, net)
         conf_preds = conf_data.view(batch_size, num_priors, self.num_classes).transpose(2, 1)
         for batch_idx in range(batch_size):
             decoded_boxes = decode(loc_data[batch_idx], prior_data)
             result = self.detect(batch_idx, conf_preds, decoded_boxes, mask_data)
             if result is not None and proto_data is not None:
                 result["proto"] = proto_data[batch_idx]
+            out.append({"detection": result, "net": net})
+        return out
+
+    def _call_batched(self, loc_data, conf_data, mask_data, prior_data, proto_data, net):
+        """The FastNMS branches for the whole batch: rp_yolact_prefilter -> rp_fast_nms_batched
+        chained through device-side offsets; ONE host read (counts) for all images."""
+        B, P = int(loc_data.shape[0]), int(prior_data.shape[0])
+        conf = conf_data.reshape(B, P, self.num_classes)
+        cap = None
+        while True:
+            pre = detect_prefilter(loc_data, conf, mask_data, prior_data, self.conf_thresh, cap)
+            r = fast_nms_batched(pre["box"], pre["mask"], pre["score"], pre["offsets"],
+                                 self.nms_thresh, self.top_k, self.max_num_detections, False,
+                                 self.conf_thresh, self.use_cross_class_nms, n_max=min(P, pre["cap"]))
+            host = torch.cat([r["count"], pre["n_cand"], pre["offsets"]]).cpu().tolist()
+            counts, n_cand, offs = host[:B], host[B], host[B + 1:]
+            if n_cand <= pre["cap"]:
+                break
+            cap = n_cand  # more candidates than slots: repeat once with exact room
+        out = []
+        for b in range(B):
+            m = counts[b]
+            if offs[b + 1] - offs[b] == 0:  # detection.py:92-93: no candidate -> None
+                result = None
+            else:
+                result = {"box": r["box"][b, :m], "mask": r["mask"][b, :m],
+                          "class": r["class"][b, :m].long(), "score": r["score"][b, :m]}
+                if proto_data is not None:
+                    result["proto"] = proto_data[b]
             out.append({"detection": result, "net": net})
         return out
 

@@ -26,7 +26,8 @@ def test_header_declares_the_whole_path():
                  "rp_pooler_backward", "rp_level_map", "rp_nms_batched", "rp_fast_nms_batched",
                  "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode",
                  "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes",
-                 "rp_rpn_pre_nms_levels", "rp_rpn_select_levels", "rp_box_post"):
+                 "rp_rpn_pre_nms_levels", "rp_rpn_select_levels", "rp_box_post",
+                 "rp_yolact_prefilter"):
         assert must in names
 
 
@@ -76,6 +77,9 @@ def test_argument_errors_need_no_gpu():
     assert L.rp_rpn_pre_nms_levels_workspace_bytes(9, 4, A3, H2, W2, 1000) == 0  # > RP_MAX_LEVELS
     assert L.rp_rpn_select_levels(None, None, None, None, None, 5, 8, 1000, 100, None, None, None,
                                   None, 0, None) == -1
+    assert L.rp_yolact_prefilter_workspace_bytes(64, 19248, 65536) >= 64 * 19248 + 4 * 65536
+    assert L.rp_yolact_prefilter(None, None, None, None, 64, 19248, 81, 32, 0.05, 65536, None, None,
+                                 None, None, None, None, None, 0, None) == -1
     assert L.rp_box_post_workspace_bytes(8000, 81, 8, 1000, 8000 * 80) > 8000 * 80 * 28
     assert L.rp_box_post(None, None, None, None, None, 10, 81, 1, 10, 324, 0, 0.05, 0.5, 100, 10.0,
                          10.0, 5.0, 5.0, 4.0, 800, None, None, None, None, None, None, 200, None,

@@ -225,3 +225,86 @@ def test_fast_nms_select_ties_large(n, levels):
         np.testing.assert_array_equal(r["score"][i, :cnt[i]].cpu().numpy(), o[3])
         np.testing.assert_array_equal(r["class"][i, :cnt[i]].cpu().numpy(), o[2])
         np.testing.assert_array_equal(r["index"][i, :cnt[i]].cpu().numpy(), o[4])
+
+
+def _batch(priors, seeds):
+    imgs = [synth.yolact_image(s, priors) for s in seeds]
+    return imgs, {"loc": T(np.stack([i[0] for i in imgs])), "conf": T(np.stack([i[1] for i in imgs])),
+                  "mask": T(np.stack([i[2] for i in imgs])), "priors": T(priors),
+                  "proto": T(np.stack([i[3] for i in imgs]))}
+
+
+def test_detect_prefilter_matches_oracle(priors):
+    imgs, pred = _batch(priors, [500, 501, 502])
+    conf = pred["conf"].clone()
+    conf[1, :, 1:] = 0.0  # image 1 has no candidate at all
+    for cap in (None, 3000):  # 3000 < the number of candidates: truncated run, n_cand reports it
+        r = rp.detect_prefilter(pred["loc"], conf, pred["mask"], pred["priors"], 0.05, cap)
+        off = r["offsets"].cpu().numpy()
+        n_cand = int(r["n_cand"].item())
+        total = 0
+        for b, (loc, cf, mask, _) in enumerate(imgs):
+            fg = np.ascontiguousarray(cf[:, 1:].T) if b != 1 else np.zeros((80, priors.shape[0]), np.float32)
+            keep = oracle.detect_filter(fg, 0.05)
+            total += len(keep)
+            lo, hi = off[b], off[b + 1]
+            if cap is None:
+                assert hi - lo == len(keep)
+            keep = keep[: hi - lo]
+            np.testing.assert_array_equal(r["prior"][lo:hi].cpu().numpy(), keep)
+            np.testing.assert_array_equal(r["box"][lo:hi].cpu().numpy(), oracle.yolact_decode(loc, priors)[keep])
+            np.testing.assert_array_equal(r["mask"][lo:hi].cpu().numpy(), mask[keep])
+            np.testing.assert_array_equal(r["score"][:, lo:hi].cpu().numpy(), fg[:, keep])
+        assert n_cand == total and off[0] == 0
+        if cap is not None:
+            assert n_cand > cap and off[-1] == cap
+
+
+@pytest.mark.parametrize("cross_class", [False, True])
+def test_detect_batched_matches_oracle(priors, cross_class):
+    imgs, pred = _batch(priors, [510, 511, 512, 513, 514])
+    pred["conf"][3, :, 1:] = 0.0
+    det = rp.Detect(81, 0, 200, 0.05, 0.5)
+    det.use_fast_nms = True
+    det.use_cross_class_nms = cross_class
+    out = det(pred, None)
+    assert out[3]["detection"] is None
+    for b, (loc, cf, mask, _) in enumerate(imgs):
+        if b == 3:
+            continue
+        fg = np.ascontiguousarray(cf[:, 1:].T)
+        keep = oracle.detect_filter(fg, 0.05)
+        bx = oracle.yolact_decode(loc, priors)[keep]
+        sc = np.ascontiguousarray(fg[:, keep])
+        if cross_class:
+            ob, oc, ocl, osc, _ = oracle.cc_fast_nms(bx, mask[keep], sc, 0.5, 200)
+        else:
+            ob, oc, ocl, osc, _ = oracle.fast_nms(bx, mask[keep], sc, 0.5, 200, 100)
+        d = out[b]["detection"]
+        np.testing.assert_array_equal(d["class"].cpu().numpy(), ocl)
+        np.testing.assert_array_equal(d["score"].cpu().numpy(), osc)
+        np.testing.assert_array_equal(d["box"].cpu().numpy(), ob)
+        np.testing.assert_array_equal(d["mask"].cpu().numpy(), oc)
+
+
+def test_detect_batched_repeats_when_the_candidate_slots_overflow(priors, monkeypatch):
+    imgs, pred = _batch(priors, [520, 521])
+    calls = []
+    real = rp.package.yolact.detect_prefilter
+
+    def small_first(loc, conf, mask, pri, thr, cap=None):
+        calls.append(cap)
+        return real(loc, conf, mask, pri, thr, cap if cap else 300)
+
+    monkeypatch.setattr(rp.package.yolact, "detect_prefilter", small_first)
+    det = rp.Detect(81, 0, 200, 0.05, 0.5)
+    det.use_fast_nms = True
+    out = det(pred, None)
+    assert len(calls) == 2 and calls[0] is None and calls[1] > 300
+    loc, cf, mask, _ = imgs[1]
+    fg = np.ascontiguousarray(cf[:, 1:].T)
+    keep = oracle.detect_filter(fg, 0.05)
+    ob, oc, ocl, osc, _ = oracle.fast_nms(oracle.yolact_decode(loc, priors)[keep], mask[keep],
+                                          np.ascontiguousarray(fg[:, keep]), 0.5, 200, 100)
+    np.testing.assert_array_equal(out[1]["detection"]["score"].cpu().numpy(), osc)
+    np.testing.assert_array_equal(out[1]["detection"]["box"].cpu().numpy(), ob)

@@ -136,3 +136,18 @@ bh = rp.PostProcessor(0.05, 0.5, 100)
 timed("box post device part, 8 x 1000 x 81", lambda: rp.box_post(lgt, regt, prt, offs_bh, wht, 1000, 0.05, 0.5, 100),
       lg.nbytes + reg.nbytes + pr.nbytes)
 timed("PostProcessor.execute (BoxLists out)", lambda: bh((lgt, regt), bls))
+
+# Yolact Detect for the batch from the raw head outputs: prefilter (decode + class-max + conf
+# filter + gathers over the 399 MB conf tensor) -> FastNMS, batch 64
+B = 64
+imgs = [synth.yolact_image(100 + i, priors) for i in range(4)]
+loc64 = T(np.stack([imgs[i % 4][0] for i in range(B)]))
+conf64 = T(np.stack([imgs[i % 4][1] for i in range(B)]))
+mask64 = T(np.stack([imgs[i % 4][2] for i in range(B)]))
+pri_t = T(priors)
+timed("yolact prefilter batch 64 (19248 priors x 81)",
+      lambda: rp.detect_prefilter(loc64, conf64, mask64, pri_t, 0.05), conf64.numel() * 4 + loc64.numel() * 4)
+det = rp.Detect(81, 0, 200, 0.05, 0.5)
+det.use_fast_nms = True
+pred = {"loc": loc64, "conf": conf64, "mask": mask64, "priors": pri_t}
+timed("Detect.__call__ batch 64 (prefilter + FastNMS, dicts out)", lambda: det(pred, None))
