@@ -291,6 +291,34 @@ RP_API int rp_box_post(const float* class_logits, const float* box_regression, c
                 float* out_scores, int* out_labels, int* out_rows, int* out_count, int out_cap,
                 int* n_cand, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Other RoI-family operators.
+ * rp_boxlist_iou: boxlist_iou det/structures/boxlist_ops.py:79-116 -- boxes1 [N,4], boxes2 [M,4]
+ *   xyxy (16-byte aligned) -> out [N,M] = inter / (area1 + area2 - inter), TO_REMOVE = 1.
+ * rp_roi_pool_forward / _backward: roi_pool det/layers/roi_pool.py:16-88,101-148 -- feat
+ *   [N,C,H,W], rois [K,5] -> out [K,C,PH,PW] (max, 0 for an empty bin) and argmax [K,C,PH,PW]
+ *   int32 (offset inside the plane, -1 when nothing was pooled); the backward zero-fills
+ *   grad_input [N,C,H,W] (:143) and adds dout at the argmax positions.
+ * rp_mask_prob: mask_prob_cuda det/layers/mask_prob.py:9-103 (EmbedMask) -- embed_pixel
+ *   [num_pixel,dim], embed_center [num_center,dim], sigma_center [num_center], boxes
+ *   [num_center,4] int32 (x1,y1,x2,y2, end exclusive), box_areas [num_center] int32 ->
+ *   probs [num_center,num_pixel] = exp(-|e_p - e_c|^2 * sigma) inside each centre's box, 0
+ *   elsewhere (the launch zero-fills, :60).  Limits: dim <= 128, num_center <= 65535.
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_boxlist_iou(const float* boxes1, int N, const float* boxes2, int M, float* out,
+                   void* stream);
+
+RP_API int rp_roi_pool_forward(const float* feat, int N, int C, int H, int W, const float* rois, int K,
+                        int PH, int PW, float spatial_scale, float* out, int* argmax,
+                        void* stream);
+
+RP_API int rp_roi_pool_backward(const float* dout, const float* rois, const int* argmax, int K, int N,
+                         int C, int H, int W, int PH, int PW, float* grad_input, void* stream);
+
+RP_API int rp_mask_prob(const float* embed_pixel, const float* embed_center, const float* sigma_center,
+                 const int* boxes, const int* box_areas, int num_pixel, int num_center, int dim,
+                 int mask_width, float* probs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,7 +6,8 @@ torch-op or CPU fallback and nothing under oracle/ is ever imported.
 """
 from . import _lib
 from ._lib import RoiPathError, lib
-from .layers import (ROIAlign, cython_nms, ml_nms, nms, nms_batched, roi_align,
+from .layers import (ROIAlign, ROIPool, cython_nms, mask_prob_cuda, ml_nms, nms, nms_batched, roi_align,
+                     roi_pool,
                      roi_align_backward, roi_align_forward)
 from . import parallel
 from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_in_image,
@@ -16,7 +17,7 @@ from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_f
 from .box_head import PostProcessor, box_post, make_roi_box_post_processor
 from .rpn import (BoxCoder, RPNPostProcessor, box_decode, make_rpn_postprocessor, rpn_pre_nms,
                   rpn_pre_nms_levels, rpn_select_levels)
-from .structures import (BoxList, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
+from .structures import (BoxList, boxlist_iou, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
                          remove_small_boxes)
 from .yolact import (Detect, crop, decode, detect_prefilter, fast_nms_batched, mask_assemble, postprocess,
                      sanitize_coordinates)

@@ -1,0 +1,178 @@
+// roi_misc.cu -- the other RoI-family kernels of SURVEY.md 8(f) rank 4, sm_100a:
+//   boxlist_iou   det/structures/boxlist_ops.py:79-116   N x M IoU (+1) for the training Matcher
+//   ROIPool       det/layers/roi_pool.py:16-88 (forward, argmax), :101-148 (backward)
+//   mask_prob     det/layers/mask_prob.py:9-57            EmbedMask pixel/centre margin probability
+#include "common.cuh"
+
+namespace {
+
+// ---- boxlist_iou: CTA = 32 x 8 tile of the [N, M] matrix, rows' boxes and areas in registers -----
+__global__ void __launch_bounds__(256)
+iou_matrix_kernel(const float* __restrict__ a, int N, const float* __restrict__ b, int M,
+                  float* __restrict__ out) {
+  const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int i0 = (blockIdx.y * 8 + (threadIdx.x >> 5)) * 4;
+  if (j >= M) return;
+  const float4 q = *reinterpret_cast<const float4*>(b + (size_t)j * 4);
+  const float area2 = (q.z - q.x + 1.0f) * (q.w - q.y + 1.0f);  // BoxList.area(), TO_REMOVE = 1
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int i = i0 + r;
+    if (i >= N) return;
+    const float4 p = *reinterpret_cast<const float4*>(a + (size_t)i * 4);
+    const float area1 = (p.z - p.x + 1.0f) * (p.w - p.y + 1.0f);
+    const float w = fmaxf(fminf(p.z, q.z) - fmaxf(p.x, q.x) + 1.0f, 0.0f);  // :106-111
+    const float h = fmaxf(fminf(p.w, q.w) - fmaxf(p.y, q.y) + 1.0f, 0.0f);
+    const float inter = w * h;
+    __stcs(out + (size_t)i * M + j, inter / (area1 + area2 - inter));  // :114
+  }
+}
+
+// ---- ROIPool ------------------------------------------------------------------------------
+// One thread per output element, index order (n, c, ph, pw) as the reference: neighbouring lanes
+// read neighbouring bins of one plane.  round() is C round (half away from zero), the bin maths
+// is float as in the kernel text (roi_pool.py:44-69).
+__global__ void __launch_bounds__(256)
+roi_pool_fwd_kernel(const float* __restrict__ feat, const float* __restrict__ rois, size_t total,
+                    int C, int H, int W, int PH, int PW, float scale, float* __restrict__ out,
+                    int* __restrict__ argmax) {
+  const size_t index = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (index >= total) return;
+  const int pw = (int)(index % PW);
+  const int ph = (int)((index / PW) % PH);
+  const int c = (int)((index / PW / PH) % C);
+  const int n = (int)(index / PW / PH / C);
+  const float* r = rois + (size_t)n * 5;
+  const int bi = (int)r[0];
+  const int sw = (int)roundf(r[1] * scale), sh = (int)roundf(r[2] * scale);
+  const int ew = (int)roundf(r[3] * scale), eh = (int)roundf(r[4] * scale);
+  const int rw = max(ew - sw + 1, 1), rh = max(eh - sh + 1, 1);
+  const float bh = (float)(1.0 * rh / PH), bw = (float)(1.0 * rw / PW);  // double quotient, :55-56
+  int hs = (int)floorf(ph * bh), ws = (int)floorf(pw * bw);
+  int he = (int)ceilf((ph + 1) * bh), we = (int)ceilf((pw + 1) * bw);
+  hs = min(max(hs + sh, 0), H);
+  he = min(max(he + sh, 0), H);
+  ws = min(max(ws + sw, 0), W);
+  we = min(max(we + sw, 0), W);
+  const bool empty = (he <= hs) || (we <= ws);
+  float maxval = empty ? 0.0f : -99999999.0f;
+  int maxidx = -1;
+  const float* plane = feat + ((size_t)bi * C + c) * H * W;
+  for (int h = hs; h < he; ++h)
+    for (int w = ws; w < we; ++w) {
+      const float v = plane[h * W + w];
+      if (v > maxval) {
+        maxval = v;
+        maxidx = h * W + w;
+      }
+    }
+  out[index] = maxval;
+  argmax[index] = maxidx;
+}
+
+__global__ void __launch_bounds__(256)
+roi_pool_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ rois,
+                    const int* __restrict__ argmax, size_t total, int C, int H, int W, int PH, int PW,
+                    float* __restrict__ grad) {
+  const size_t index = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (index >= total) return;
+  const int c = (int)((index / PW / PH) % C);
+  const int n = (int)(index / PW / PH / C);
+  const int a = argmax[index];
+  if (a < 0) return;
+  const int bi = (int)rois[(size_t)n * 5];
+  atomicAdd(grad + ((size_t)bi * C + c) * H * W + a, dout[index]);
+}
+
+// ---- EmbedMask mask_prob --------------------------------------------------------------------
+// CTA = (slice of the box's pixels, centre): no per-thread linear search for the centre
+// (mask_prob.py:25-32); the centre's embedding sits in shared memory.
+constexpr int MP_MAXDIM = 128;
+__global__ void __launch_bounds__(256)
+mask_prob_kernel(const float* __restrict__ embed_pixel, const float* __restrict__ embed_center,
+                 const float* __restrict__ sigma_center, const int* __restrict__ boxes,
+                 const int* __restrict__ box_areas, int num_pixel, int mask_width, int dim,
+                 float* __restrict__ probs) {
+  __shared__ float ec[MP_MAXDIM];
+  const int n = blockIdx.y;
+  for (int d = threadIdx.x; d < dim; d += blockDim.x) ec[d] = embed_center[(size_t)n * dim + d];
+  __syncthreads();
+  const int area = box_areas[n];
+  const int x1 = boxes[4 * n], y1 = boxes[4 * n + 1];
+  const int bw = boxes[4 * n + 2] - x1;
+  if (bw <= 0) return;
+  const float sg = sigma_center[n];
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < area; q += gridDim.x * blockDim.x) {
+    const int x = q % bw + x1, y = q / bw + y1;
+    const int pid = y * mask_width + x;
+    if (pid < 0 || pid >= num_pixel) continue;
+    const float* ep = embed_pixel + (size_t)pid * dim;
+    float norm2 = 0.0f;
+    for (int d = 0; d < dim; ++d) {
+      const float t = ep[d] - ec[d];
+      norm2 = norm2 + t * t;
+    }
+    probs[(size_t)n * num_pixel + pid] = rp_expf(-norm2 * sg);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int rp_boxlist_iou(const float* boxes1, int N, const float* boxes2, int M, float* out, void* stream) {
+  if (N == 0 || M == 0) return RP_OK;
+  if (!boxes1 || !boxes2 || !out || N < 0 || M < 0) return RP_E_ARG;
+  if (((reinterpret_cast<uintptr_t>(boxes1) | reinterpret_cast<uintptr_t>(boxes2)) & 15) != 0)
+    return RP_E_ARG;
+  const dim3 grid((unsigned)((M + 31) / 32), (unsigned)((N + 31) / 32));
+  if (grid.y > 65535) return RP_E_LIMIT;
+  iou_matrix_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(boxes1, N, boxes2, M, out);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_roi_pool_forward(const float* feat, int N, int C, int H, int W, const float* rois, int K, int PH,
+                        int PW, float spatial_scale, float* out, int* argmax, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!feat || !rois || !out || !argmax || N < 1 || C < 1 || H < 1 || W < 1 || K < 0 || PH < 1 ||
+      PW < 1)
+    return RP_E_ARG;
+  if ((size_t)H * W > 0x7fffffffull) return RP_E_LIMIT;
+  const size_t total = (size_t)K * C * PH * PW;
+  roi_pool_fwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      feat, rois, total, C, H, W, PH, PW, spatial_scale, out, argmax);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_roi_pool_backward(const float* dout, const float* rois, const int* argmax, int K, int N, int C,
+                         int H, int W, int PH, int PW, float* grad_input, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!grad_input || N < 1 || C < 1 || H < 1 || W < 1 || K < 0 || PH < 1 || PW < 1) return RP_E_ARG;
+  RP_CUDA_TRY(cudaMemsetAsync(grad_input, 0, sizeof(float) * (size_t)N * C * H * W, st));  // :143
+  if (K == 0) return RP_OK;
+  if (!dout || !rois || !argmax) return RP_E_ARG;
+  const size_t total = (size_t)K * C * PH * PW;
+  roi_pool_bwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dout, rois, argmax, total, C, H,
+                                                                       W, PH, PW, grad_input);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_mask_prob(const float* embed_pixel, const float* embed_center, const float* sigma_center,
+                 const int* boxes, const int* box_areas, int num_pixel, int num_center, int dim,
+                 int mask_width, float* probs, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (num_pixel < 0 || num_center < 0 || dim < 1 || mask_width < 1) return RP_E_ARG;
+  if (dim > MP_MAXDIM || num_center > 65535) return RP_E_LIMIT;
+  if ((size_t)num_pixel * num_center == 0) return RP_OK;
+  if (!embed_pixel || !embed_center || !sigma_center || !boxes || !box_areas || !probs) return RP_E_ARG;
+  RP_CUDA_TRY(cudaMemsetAsync(probs, 0, sizeof(float) * (size_t)num_pixel * num_center, st));  // :60
+  mask_prob_kernel<<<dim3(32, (unsigned)num_center), 256, 0, st>>>(
+      embed_pixel, embed_center, sigma_center, boxes, box_areas, num_pixel, mask_width, dim, probs);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+}  // extern "C"

@@ -153,3 +153,86 @@ def cython_nms(dets, thresh):
     dets = _lib.as_f32(dets, "dets")
     return _nms_single(dets[:, :4].contiguous(), dets[:, 4].contiguous(), None, thresh,
                        flags=_lib.RP_NMS_CYTHON)
+
+
+# ------------------------------------------------------------------------------- ROIPool
+class _ROIPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, input, rois, output_size, spatial_scale):
+        input = _lib.as_f32(input, "input")
+        rois = _lib.as_f32(rois, "rois")
+        PH, PW = _pair(output_size)
+        N, C, H, W = (int(v) for v in input.shape)
+        K = int(rois.shape[0])
+        out = torch.zeros((K, C, PH, PW), dtype=_F32, device=input.device)
+        arg = torch.zeros((K, C, PH, PW), dtype=_I32, device=input.device)
+        rc = _lib.lib().rp_roi_pool_forward(
+            _lib.dptr(input, _F32, "input"), N, C, H, W, _lib.dptr(rois, _F32, "rois"), K, PH, PW,
+            float(spatial_scale), _lib.dptr(out), _lib.dptr(arg), _lib.stream_ptr(input.device))
+        _lib.check(rc, "rp_roi_pool_forward")
+        ctx.save_for_backward(rois, arg)
+        ctx.shape = (N, C, H, W)
+        ctx.mark_non_differentiable(arg)
+        return out, arg
+
+    @staticmethod
+    def backward(ctx, dout, _darg):
+        rois, arg = ctx.saved_tensors
+        N, C, H, W = ctx.shape
+        K, _, PH, PW = (int(v) for v in arg.shape)
+        dout = _lib.as_f32(dout, "dout")
+        grad = torch.empty((N, C, H, W), dtype=_F32, device=dout.device)
+        rc = _lib.lib().rp_roi_pool_backward(
+            _lib.dptr(dout, _F32), _lib.dptr(rois, _F32), _lib.dptr(arg, _I32), K, N, C, H, W, PH, PW,
+            _lib.dptr(grad), _lib.stream_ptr(dout.device))
+        _lib.check(rc, "rp_roi_pool_backward")
+        return grad, None, None, None
+
+
+def roi_pool(input, rois, output_size, spatial_scale, return_argmax=False):
+    """Drop-in for detectron.layers.roi_pool (roi_pool.py:154-162)."""
+    out, arg = _ROIPoolFn.apply(input, rois, output_size, spatial_scale)
+    return (out, arg) if return_argmax else out
+
+
+class ROIPool(torch.nn.Module):
+    """roi_pool.py:166-183."""
+
+    def __init__(self, output_size, spatial_scale):
+        super().__init__()
+        self.output_size = output_size
+        self.spatial_scale = spatial_scale
+
+    def forward(self, input, rois):
+        return roi_pool(input, rois, self.output_size, self.spatial_scale)
+
+    execute = forward
+
+    def __repr__(self):
+        return "%s(output_size=%s, spatial_scale=%s)" % (self.__class__.__name__, self.output_size,
+                                                         self.spatial_scale)
+
+
+# ------------------------------------------------------------------------------- EmbedMask
+def mask_prob_cuda(embed_pixel, embed_center, sigma_center, boxes, box_areas, area_sum, mask_width):
+    """Drop-in for detectron.layers.mask_prob.mask_prob_cuda (mask_prob.py:84-103): probs
+    [num_center, num_pixel] (the reference declares the shape transposed but indexes it this way,
+    :56).  area_sum is accepted for signature parity; the launch does not need it."""
+    assert embed_pixel.ndim == 2, "embed_pixel should be MxDim"
+    assert embed_center.ndim == 2, "embed_center should be NxDim"
+    assert sigma_center.ndim == 1, "sigma_center should be N"
+    assert embed_pixel.shape[1] == embed_center.shape[1], "Dim should the same"
+    assert embed_center.shape[0] == sigma_center.shape[0], "center number should be the same"
+    assert embed_center.shape[0] == boxes.shape[0], "center number and box number should be the same"
+    M, N = int(embed_pixel.shape[0]), int(embed_center.shape[0])
+    embed_pixel = _lib.as_f32(embed_pixel, "embed_pixel")
+    if M * N == 0:
+        return torch.empty((0,), dtype=_F32, device=embed_pixel.device)
+    out = torch.empty((N, M), dtype=_F32, device=embed_pixel.device)
+    rc = _lib.lib().rp_mask_prob(
+        _lib.dptr(embed_pixel, _F32), _lib.dptr(_lib.as_f32(embed_center, "embed_center"), _F32),
+        _lib.dptr(_lib.as_f32(sigma_center, "sigma_center"), _F32),
+        _lib.dptr(boxes.to(_I32).contiguous(), _I32), _lib.dptr(box_areas.to(_I32).contiguous(), _I32),
+        M, N, int(embed_pixel.shape[1]), int(mask_width), _lib.dptr(out), _lib.stream_ptr(out.device))
+    _lib.check(rc, "rp_mask_prob")
+    return out

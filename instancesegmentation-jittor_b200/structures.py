@@ -9,7 +9,7 @@ CUDA tensors.
 """
 import torch
 
-from . import layers
+from . import _lib, layers
 
 TO_REMOVE = 1
 
@@ -185,6 +185,20 @@ def remove_small_boxes(boxlist, min_size):
     xywh = boxlist.convert("xywh").bbox
     keep = (xywh[:, 2] >= min_size) & (xywh[:, 3] >= min_size)
     return boxlist[keep]
+
+
+def boxlist_iou(boxlist1, boxlist2):
+    """boxlist_ops.py:79-116: [N,M] IoU with the legacy +1 (one launch, no [N,M,2] temporaries)."""
+    if boxlist1.size != boxlist2.size:
+        raise RuntimeError("boxlists should have same image size, got {}, {}".format(boxlist1, boxlist2))
+    b1 = _lib.as_f32(boxlist1.convert("xyxy").bbox, "boxlist1")
+    b2 = _lib.as_f32(boxlist2.convert("xyxy").bbox, "boxlist2")
+    N, M = int(b1.shape[0]), int(b2.shape[0])
+    out = torch.empty((N, M), dtype=torch.float32, device=b1.device)
+    rc = _lib.lib().rp_boxlist_iou(_lib.dptr(b1), N, _lib.dptr(b2), M, _lib.dptr(out),
+                                   _lib.stream_ptr(b1.device))
+    _lib.check(rc, "rp_boxlist_iou")
+    return out
 
 
 def cat_boxlist(bboxes):

@@ -283,6 +283,51 @@ def box_post_image(logits, reg, props, im_wh, score_thresh=0.05, nms_thresh=0.5,
     return ob[:m].copy(), osc[:m].copy(), ol[:m].copy(), orow[:m].copy()
 
 
+# --------------------------------------------------------------------------- other RoI ops
+def boxlist_iou(a, b):
+    a, ap = _f(a)
+    b, bp = _f(b)
+    out = np.zeros((a.shape[0], b.shape[0]), np.float32)
+    lib().orc_boxlist_iou(ap, a.shape[0], bp, b.shape[0], out.ctypes.data_as(_f32p))
+    return out
+
+
+def roi_pool_forward(feat, rois, output_size, spatial_scale):
+    feat, fp = _f(feat)
+    rois, rp_ = _f(rois)
+    N, C, H, W = feat.shape
+    PH, PW = output_size if isinstance(output_size, (tuple, list)) else (output_size, output_size)
+    K = rois.shape[0]
+    out = np.zeros((K, C, PH, PW), np.float32)
+    arg = np.zeros((K, C, PH, PW), np.int32)
+    lib().orc_roi_pool_forward(fp, N, C, H, W, rp_, K, PH, PW, ctypes.c_float(spatial_scale),
+                               out.ctypes.data_as(_f32p), arg.ctypes.data_as(_i32p))
+    return out, arg
+
+
+def roi_pool_backward(dout, rois, argmax, feat_shape):
+    dout, dp = _f(dout)
+    rois, rp_ = _f(rois)
+    argmax, ap = _i(argmax)
+    N, C, H, W = feat_shape
+    K, _, PH, PW = dout.shape
+    grad = np.zeros((N, C, H, W), np.float32)
+    lib().orc_roi_pool_backward(dp, rp_, ap, K, N, C, H, W, PH, PW, grad.ctypes.data_as(_f32p))
+    return grad
+
+
+def mask_prob(embed_pixel, embed_center, sigma_center, boxes, box_areas, mask_width):
+    ep, epp = _f(embed_pixel)
+    ec, ecp = _f(embed_center)
+    sg, sgp = _f(sigma_center)
+    bx, bxp = _i(boxes)
+    ar, arp = _i(box_areas)
+    out = np.zeros((ec.shape[0], ep.shape[0]), np.float32)
+    lib().orc_mask_prob(epp, ecp, sgp, bxp, arp, ep.shape[0], ec.shape[0], ep.shape[1],
+                        int(mask_width), out.ctypes.data_as(_f32p))
+    return out
+
+
 # --------------------------------------------------------------------------- Yolact
 def yolact_decode(loc, priors):
     loc, lp = _f(loc)

@@ -998,6 +998,106 @@ ORC_API int orc_box_post_image(const float* logits, const float* reg, const floa
 }
 
 /* ------------------------------------------------------------------------- */
+/* Other RoI-family operators                                                 */
+/* ------------------------------------------------------------------------- */
+
+/* det/structures/boxlist_ops.py:79-116 boxlist_iou: area with TO_REMOVE = 1
+ * (bounding_box.py:292-304), wh = clamp(rb - lt + 1, 0), iou = inter / (a1 + a2 - inter). */
+ORC_API void orc_boxlist_iou(const float* a, int N, const float* b, int M, float* out) {
+  for (int i = 0; i < N; ++i) {
+    const float* p = a + (size_t)i * 4;
+    const float area1 = (p[2] - p[0] + 1.0f) * (p[3] - p[1] + 1.0f);
+    for (int j = 0; j < M; ++j) {
+      const float* q = b + (size_t)j * 4;
+      const float area2 = (q[2] - q[0] + 1.0f) * (q[3] - q[1] + 1.0f);
+      const float w = fmaxf(fminf(p[2], q[2]) - fmaxf(p[0], q[0]) + 1.0f, 0.0f);
+      const float h = fmaxf(fminf(p[3], q[3]) - fmaxf(p[1], q[1]) + 1.0f, 0.0f);
+      const float inter = w * h;
+      out[(size_t)i * M + j] = inter / (area1 + area2 - inter);
+    }
+  }
+}
+
+/* det/layers/roi_pool.py:16-88 RoIPoolForwardKernel: round() of the scaled corners, malformed
+ * RoIs forced to 1x1, bin size = (float)(1.0 * extent / pooled) (a double quotient, :55-56),
+ * floor / ceil bin edges clipped to the map, empty bin -> 0 / -1, otherwise the first maximum
+ * in (h, w) scan order above -99999999. */
+ORC_API void orc_roi_pool_forward(const float* feat, int N, int C, int H, int W, const float* rois,
+                                  int K, int PH, int PW, float scale, float* out, int* argmax) {
+  (void)N;
+  for (int n = 0; n < K; ++n) {
+    const float* r = rois + (size_t)n * 5;
+    const int bi = (int)r[0];
+    const int sw = (int)roundf(r[1] * scale), sh = (int)roundf(r[2] * scale);
+    const int ew = (int)roundf(r[3] * scale), eh = (int)roundf(r[4] * scale);
+    const int rw = ew - sw + 1 > 1 ? ew - sw + 1 : 1, rh = eh - sh + 1 > 1 ? eh - sh + 1 : 1;
+    const float bh = (float)(1.0 * rh / PH), bw = (float)(1.0 * rw / PW);
+    for (int c = 0; c < C; ++c) {
+      const float* plane = feat + ((size_t)bi * C + c) * H * W;
+      for (int ph = 0; ph < PH; ++ph)
+        for (int pw = 0; pw < PW; ++pw) {
+          int hs = (int)floorf(ph * bh), ws = (int)floorf(pw * bw);
+          int he = (int)ceilf((ph + 1) * bh), we = (int)ceilf((pw + 1) * bw);
+          hs = hs + sh < 0 ? 0 : (hs + sh > H ? H : hs + sh);
+          he = he + sh < 0 ? 0 : (he + sh > H ? H : he + sh);
+          ws = ws + sw < 0 ? 0 : (ws + sw > W ? W : ws + sw);
+          we = we + sw < 0 ? 0 : (we + sw > W ? W : we + sw);
+          const int empty = (he <= hs) || (we <= ws);
+          float maxval = empty ? 0.0f : -99999999.0f;
+          int maxidx = -1;
+          for (int h = hs; h < he; ++h)
+            for (int w = ws; w < we; ++w)
+              if (plane[h * W + w] > maxval) {
+                maxval = plane[h * W + w];
+                maxidx = h * W + w;
+              }
+          const size_t o = (((size_t)n * C + c) * PH + ph) * PW + pw;
+          out[o] = maxval;
+          argmax[o] = maxidx;
+        }
+    }
+  }
+}
+
+/* det/layers/roi_pool.py:101-148 RoIPoolBackwardKernel (sequential accumulation order). */
+ORC_API void orc_roi_pool_backward(const float* dout, const float* rois, const int* argmax, int K,
+                                   int N, int C, int H, int W, int PH, int PW, float* grad) {
+  memset(grad, 0, sizeof(float) * (size_t)N * C * H * W);
+  for (int n = 0; n < K; ++n) {
+    const int bi = (int)rois[(size_t)n * 5];
+    for (int c = 0; c < C; ++c)
+      for (int q = 0; q < PH * PW; ++q) {
+        const size_t o = ((size_t)n * C + c) * PH * PW + q;
+        if (argmax[o] != -1) grad[((size_t)bi * C + c) * H * W + argmax[o]] += dout[o];
+      }
+  }
+}
+
+/* det/layers/mask_prob.py:9-57 MaskProbForward: for centre n, its first box_areas[n] pixels in
+ * row-major order of the box (x1,y1,x2,y2 end exclusive): p = exp(-sum_d (e_p - e_c)^2 * sigma);
+ * the sum in dimension order, uncontracted; exp is rp_expf (PARITY UNPINNED: the reference's
+ * expf / FMA contraction are nvcc's). */
+ORC_API void orc_mask_prob(const float* ep, const float* ec, const float* sigma, const int* boxes,
+                           const int* areas, int num_pixel, int num_center, int dim, int mask_width,
+                           float* probs) {
+  memset(probs, 0, sizeof(float) * (size_t)num_pixel * num_center);
+  for (int n = 0; n < num_center; ++n) {
+    const int x1 = boxes[4 * n], y1 = boxes[4 * n + 1], bw = boxes[4 * n + 2] - x1;
+    if (bw <= 0) continue;
+    for (int q = 0; q < areas[n]; ++q) {
+      const int pid = (q / bw + y1) * mask_width + (q % bw + x1);
+      if (pid < 0 || pid >= num_pixel) continue;
+      float norm2 = 0.0f;
+      for (int d = 0; d < dim; ++d) {
+        const float t = ep[(size_t)pid * dim + d] - ec[(size_t)n * dim + d];
+        norm2 = norm2 + t * t;
+      }
+      probs[(size_t)n * num_pixel + pid] = rp_expf(-norm2 * sigma[n]);
+    }
+  }
+}
+
+/* ------------------------------------------------------------------------- */
 /* helpers exported for tests                                                 */
 /* ------------------------------------------------------------------------- */
 ORC_API float orc_expf(float x) { return rp_expf(x); }

@@ -200,3 +200,21 @@ def box_head_batch(n_images, per_image, num_classes=81, seed=0, ties=False, obje
     if n_images > 1:
         im_wh[1] = (int(img_w * 0.75), int(img_h * 0.9))
     return logits, reg, props, counts, im_wh
+
+
+def embed_mask_inputs(n_center, h, w, dim, seed=0):
+    """EmbedMask mask_prob inputs: pixel embeddings [h*w, dim], centre
+    embeddings, sigmas, int boxes (end exclusive, inside the map) and their areas."""
+    rng = np.random.default_rng(seed)
+    ep = rng.standard_normal((h * w, dim)).astype(np.float32)
+    ec = rng.standard_normal((n_center, dim)).astype(np.float32)
+    sg = rng.uniform(0.05, 2.0, n_center).astype(np.float32)
+    x1 = rng.integers(0, w - 2, n_center)
+    y1 = rng.integers(0, h - 2, n_center)
+    x2 = np.minimum(x1 + rng.integers(1, w, n_center), w)
+    y2 = np.minimum(y1 + rng.integers(1, h, n_center), h)
+    bx = np.stack([x1, y1, x2, y2], 1).astype(np.int32)
+    if n_center > 2:
+        bx[-1] = (0, 0, w, h)
+    areas = ((bx[:, 2] - bx[:, 0]) * (bx[:, 3] - bx[:, 1])).astype(np.int32)
+    return ep, ec, sg, bx, areas, w

@@ -27,7 +27,8 @@ def test_header_declares_the_whole_path():
                  "rp_mask_assemble", "rp_paste_masks", "rp_mask_select_sigmoid", "rp_yolact_decode",
                  "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes",
                  "rp_rpn_pre_nms_levels", "rp_rpn_select_levels", "rp_box_post",
-                 "rp_yolact_prefilter"):
+                 "rp_yolact_prefilter", "rp_boxlist_iou", "rp_roi_pool_forward", "rp_roi_pool_backward",
+                 "rp_mask_prob"):
         assert must in names
 
 
@@ -80,6 +81,10 @@ def test_argument_errors_need_no_gpu():
     assert L.rp_yolact_prefilter_workspace_bytes(64, 19248, 65536) >= 64 * 19248 + 4 * 65536
     assert L.rp_yolact_prefilter(None, None, None, None, 64, 19248, 81, 32, 0.05, 65536, None, None,
                                  None, None, None, None, None, 0, None) == -1
+    assert L.rp_boxlist_iou(None, 5, None, 5, None, None) == -1
+    assert L.rp_boxlist_iou(None, 0, None, 5, None, None) == 0
+    assert L.rp_roi_pool_forward(None, 1, 1, 4, 4, None, 3, 7, 7, 1.0, None, None, None) == -1
+    assert L.rp_mask_prob(None, None, None, None, None, 100, 3, 200, 10, None, None) == -3  # dim > 128
     assert L.rp_box_post_workspace_bytes(8000, 81, 8, 1000, 8000 * 80) > 8000 * 80 * 28
     assert L.rp_box_post(None, None, None, None, None, 10, 81, 1, 10, 324, 0, 0.05, 0.5, 100, 10.0,
                          10.0, 5.0, 5.0, 4.0, 800, None, None, None, None, None, None, 200, None,

@@ -1,0 +1,56 @@
+"""GPU parity of the other RoI-family operators (ROIPool fwd/bwd, boxlist_iou, EmbedMask
+mask_prob) against the oracle: bit-exact except the atomically accumulated ROIPool gradient."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import roipath_b200 as rp
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+@pytest.mark.parametrize("size,scale,shape", [(7, 0.0625, (2, 16, 50, 84)), ((3, 5), 0.125, (2, 3, 100, 168)),
+                                               (14, 0.25, (1, 4, 200, 336)), (2, 0.03125, (3, 8, 25, 42))])
+def test_roi_pool_matches_oracle(size, scale, shape):
+    rng = np.random.default_rng(shape[2])
+    feat = rng.standard_normal(shape).astype(np.float32)
+    rois = synth.rois_for_images(shape[0], 100, seed=3)
+    rois[5, 1:] = (-50.0, -40.0, -20.0, -10.0)   # entirely outside: empty bins -> 0 / -1
+    rois[6, 1:] = (300.0, 200.0, 100.0, 50.0)    # malformed: forced to 1x1
+    f = T(feat).requires_grad_(True)
+    out, arg = rp.roi_pool(f, T(rois), size, scale, return_argmax=True)
+    o_ref, a_ref = oracle.roi_pool_forward(feat, rois, size, scale)
+    np.testing.assert_array_equal(arg.cpu().numpy(), a_ref)
+    np.testing.assert_array_equal(out.detach().cpu().numpy(), o_ref)
+    g = rng.standard_normal(o_ref.shape).astype(np.float32)
+    out.backward(T(g))
+    g_ref = oracle.roi_pool_backward(g, rois, a_ref, shape)
+    np.testing.assert_allclose(f.grad.cpu().numpy(), g_ref, rtol=1e-5, atol=1e-5)
+    mod = rp.ROIPool(size, scale)
+    np.testing.assert_array_equal(mod(T(feat), T(rois)).cpu().numpy(), o_ref)
+    assert rp.roi_pool(T(feat), T(rois[:0]), size, scale).shape[0] == 0
+
+
+@pytest.mark.parametrize("n,m", [(1, 1), (37, 5), (2000, 33), (513, 1000)])
+def test_boxlist_iou_matches_oracle(n, m):
+    a, b = synth.proposals(n, n, adversarial=n >= 8), synth.proposals(m, m + 1, adversarial=False)
+    A, B = rp.BoxList(T(a), (synth.IMG_W, synth.IMG_H)), rp.BoxList(T(b), (synth.IMG_W, synth.IMG_H))
+    np.testing.assert_array_equal(rp.boxlist_iou(A, B).cpu().numpy(), oracle.boxlist_iou(a, b))
+    with pytest.raises(RuntimeError):
+        rp.boxlist_iou(A, rp.BoxList(T(b), (10, 10)))
+    assert rp.boxlist_iou(A, rp.BoxList(T(b[:0]), (synth.IMG_W, synth.IMG_H))).shape == (n, 0)
+
+
+@pytest.mark.parametrize("n_center,h,w,dim", [(1, 8, 8, 4), (6, 40, 56, 8), (40, 100, 136, 32)])
+def test_mask_prob_matches_oracle(n_center, h, w, dim):
+    ep, ec, sg, bx, ar, mw = synth.embed_mask_inputs(n_center, h, w, dim, seed=dim)
+    got = rp.mask_prob_cuda(T(ep), T(ec), T(sg), T(bx), T(ar), int(ar.sum()), mw)
+    np.testing.assert_array_equal(got.cpu().numpy(), oracle.mask_prob(ep, ec, sg, bx, ar, mw))
+    assert rp.mask_prob_cuda(T(ep), T(ec[:0]), T(sg[:0]), T(bx[:0]), T(ar[:0]), 0, mw).numel() == 0
