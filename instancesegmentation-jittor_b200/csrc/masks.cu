@@ -72,11 +72,14 @@ __device__ __forceinline__ void mk_store4(uint8_t* p, uint32_t packed, int n_val
 constexpr int MA_THREADS = 256;
 constexpr int MA_TW = 128;  // output tile width  (32 threads x 4 pixels)
 constexpr int MA_TH = 32;   // output tile height (8 thread rows x 4 rows)
+#ifndef MA_MINB
+#define MA_MINB 4  // resident CTAs per SM asked of the register allocator
+#endif
 constexpr int MA_DMAX = 64;
 
 // CTA = (output tile, image).  The tile's prototype footprint is staged once, k-major, in
 // shared memory and reused by every detection of the image.
-__global__ void __launch_bounds__(MA_THREADS)
+__global__ void __launch_bounds__(MA_THREADS, MA_MINB)
 mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ coeff,
                      const float* __restrict__ boxes, const int* __restrict__ det_offsets,
                      int m_total, int ph, int pw, int D, int out_h, int out_w, int crop,
@@ -154,7 +157,19 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
         float v = 0.f;
         if (in) {
           float acc = 0.f;
-          for (int k = 0; k < D; ++k) acc = fmaf(proto_s[(size_t)k * pixp + pix], coef_s[k], acc);
+          if ((D & 3) == 0) {  // four coefficients per (broadcast) shared load; same k order
+            const float* pp = proto_s + pix;
+#pragma unroll 2
+            for (int k = 0; k < D; k += 4) {
+              const float4 c4 = *reinterpret_cast<const float4*>(coef_s + k);
+              acc = fmaf(pp[(size_t)k * pixp], c4.x, acc);
+              acc = fmaf(pp[(size_t)(k + 1) * pixp], c4.y, acc);
+              acc = fmaf(pp[(size_t)(k + 2) * pixp], c4.z, acc);
+              acc = fmaf(pp[(size_t)(k + 3) * pixp], c4.w, acc);
+            }
+          } else {
+            for (int k = 0; k < D; ++k) acc = fmaf(proto_s[(size_t)k * pixp + pix], coef_s[k], acc);
+          }
           v = rp_sigmoidf(acc);
         }
         low_s[pix] = v;
