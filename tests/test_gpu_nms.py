@@ -125,3 +125,22 @@ def test_full_size_20k_batch8():
             if mk < 0:                                # idempotence: NMS of the survivors keeps all
                 k2 = rp.nms(T(bs[i][k]), T(ss[i][k]), 0.7).cpu().numpy()
                 np.testing.assert_array_equal(k2, np.arange(len(k)))
+
+
+def test_n_total_and_n_max_may_be_upper_bounds():
+    # a producer with device-side counts (rp_rpn_pre_nms) hands over padded arrays: rows past
+    # offsets[B] must be ignored, whatever they hold
+    B, n = 3, 700
+    bs, ss = zip(*[synth.nms_boxes(n - 50 * i, 40 + i, tie_heavy=True)[:2] for i in range(B)])
+    lens = [b.shape[0] for b in bs]
+    boxes, scores = np.concatenate(bs), np.concatenate(ss)
+    pad = 900
+    boxes_p = np.concatenate([boxes, np.full((pad, 4), 1e9, np.float32)])
+    scores_p = np.concatenate([scores, np.full((pad,), 7.0, np.float32)])  # higher than any real score
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    keep, n_keep = rp.nms_batched(T(boxes_p), T(scores_p), T(offs), 0.5, n_max=1024)
+    keep, n_keep = keep.cpu().numpy(), n_keep.cpu().numpy()
+    for i in range(B):
+        ref = oracle.nms(bs[i], ss[i], 0.5)
+        assert n_keep[i] == len(ref)
+        np.testing.assert_array_equal(keep[offs[i]: offs[i] + n_keep[i]], ref)
