@@ -69,6 +69,15 @@ def test_ties_beyond_the_slack_slots():
     _check(res, lg, reg, pr, counts, wh, dets=10)
 
 
+def test_candidate_slots_overflow_is_repeated():
+    # threshold 0: every (row, class) pair is a candidate, far more than the first-try slots
+    lg, reg, pr, counts, wh = synth.box_head_batch(2, 700, num_classes=21, seed=5)
+    post = rp.PostProcessor(0.0, 0.5, 100)
+    post.cand_slots_per_row = 1
+    res = post((T(lg), T(reg)), _boxlists(pr, counts, wh))
+    _check(res, lg, reg, pr, counts, wh, score_thresh=0.0)
+
+
 def test_cls_agnostic_regression():
     lg, reg, pr, counts, wh = synth.box_head_batch(2, 300, num_classes=21, seed=6)
     reg = np.ascontiguousarray(reg[:, :8])  # [R, 2*4]: background + one shared box
