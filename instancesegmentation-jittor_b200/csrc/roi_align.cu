@@ -748,7 +748,13 @@ struct BwdGradEmit {  // phase B: one atomicAdd per tile element, lanes along x 
     for (int u = 0; u < U; ++u)
       if (u < nvalid) {
         const float val = (inv != 0.f) ? v[u] * inv : v[u] / count;
+#if defined(RT_BWD_ABLATE_STORE)  // timing ablation only (wrong results): plain store instead of RED
+        if (val != 0.f) p[(size_t)u * cstride] = val;
+#elif defined(RT_BWD_ABLATE_NOFLUSH)  // timing ablation only: no global traffic at all
+        if (val == 123.456f) p[(size_t)u * cstride] = val;
+#else
         if (val != 0.f) atomicAdd(p + (size_t)u * cstride, val);
+#endif
       }
   }
 };
