@@ -782,13 +782,282 @@ __device__ __forceinline__ void rt_direct_backward(float* plane, int H, int W, c
 }
 
 // ------------------------------------------------------------------------------------------
+// backward kernel, gather form (default).  Per axis every pooled bin touches a short run of
+// consecutive tile rows / columns (at most RG_TAPS) with merged weights; first and last touched
+// rows are non-decreasing in the bin index, so the bins that touch one tile row are a contiguous
+// range.  Per chunk of channels:
+//   stage    dout[c][ph][pw] (contiguous) -> shared
+//   phase A  thread = (ph, x), RG_U channels: H[c][ph][x] = sum_{pw covering x} wx * dout
+//   phase B  thread = (y, x),  RG_U channels: g = sum_{ph covering y} wy * H[c][ph][x];
+//            one RED per tile element, lanes along x
+// Every tile element is produced exactly once and the weights / ranges are fetched once for
+// RG_U channels.  RoIs without a band form are left to the sweep kernel below (second launch).
+// ------------------------------------------------------------------------------------------
+constexpr int RG_U = 8;
+constexpr int RG_TAPS = 8;  // tile rows / columns one bin may touch (merged taps)
+
+struct RgAxis {
+  int lo0;             // feature row / column of tile row / column 0
+  int ext;             // tile extent
+  int start[RB_MAXP];  // first touched row of the bin: absolute until rg_finish_axis, then
+                       // tile-relative; non-decreasing (bins without a sample: len 0)
+  int len[RB_MAXP];    // touched rows: start .. start + len - 1, at most RG_TAPS
+  float w[RB_MAXP][RG_TAPS];  // merged weights of those rows
+};
+
+struct RgAxes {
+  RgAxis ay, ax;
+  int covy[RB_MAXE], covx[RB_MAXE];  // first | last << 8 covering bin of a tile row / column
+};
+
+// One bin (independent of the others).  0 when its taps span more than RG_TAPS rows.
+__device__ __forceinline__ int rg_build_bin(RgAxis* a, int b, float start, float bin, int grid,
+                                            int extent) {
+  int first = 0x7fffffff, last = -1;
+  for (int i = 0; i < grid; ++i) {
+    int lo, hi;
+    float wlo, whi;
+    if (rt_axis_tap(start, bin, b, i, grid, extent, &lo, &hi, &wlo, &whi)) {
+      first = lo < first ? lo : first;
+      last = hi > last ? hi : last;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < RG_TAPS; ++j) a->w[b][j] = 0.f;
+  if (last < 0) {
+    a->start[b] = -1;
+    a->len[b] = 0;
+    return 1;
+  }
+  a->start[b] = first;
+  a->len[b] = last - first + 1;
+  if (last - first + 1 > RG_TAPS) return 0;
+  for (int i = 0; i < grid; ++i) {
+    int lo, hi;
+    float wlo, whi;
+    if (rt_axis_tap(start, bin, b, i, grid, extent, &lo, &hi, &wlo, &whi)) {
+      a->w[b][lo - first] += wlo;  // only this thread touches row b of w
+      a->w[b][hi - first] += whi;
+    }
+  }
+  return 1;
+}
+
+// Serial pass: empty bins take a neighbour's start (they cover nothing), starts become
+// tile-relative.  0 when the tile is too large.
+__device__ __forceinline__ int rg_finish_axis(RgAxis* a, int n) {
+  int prev = -1, end = 0;
+  for (int b = 0; b < n; ++b)
+    if (a->start[b] >= 0) {
+      prev = a->start[b];
+      break;
+    }
+  if (prev < 0) prev = 0;  // nothing in range
+  const int lo0 = prev;
+  for (int b = 0; b < n; ++b) {
+    if (a->start[b] < 0)
+      a->start[b] = prev;
+    else
+      prev = a->start[b];
+    const int e = a->start[b] + a->len[b];
+    end = e > end ? e : end;
+    a->start[b] -= lo0;
+  }
+  a->lo0 = lo0;
+  a->ext = end > lo0 ? end - lo0 : 0;
+  return a->ext <= RB_MAXE;
+}
+
+// CTA-uniform (blockDim.x >= 64): builds the merged-tap axes of the RoI; 1 when both exist.
+__device__ __forceinline__ int rg_build_axes(RgAxes* pl, int* fin, const RtGeom& g, int PH, int PW,
+                                             int H, int W) {
+  if (g.gh < 1 || g.gh > RB_MAXG || g.gw < 1 || g.gw > RB_MAXG || PH > RB_MAXP || PW > RB_MAXP)
+    return 0;
+  const int tid = threadIdx.x;
+  int ok = 1;
+  if (tid < PH)
+    ok = rg_build_bin(&pl->ay, tid, g.sh, g.bh, g.gh, H);
+  else if (tid >= 32 && tid < 32 + PW)
+    ok = rg_build_bin(&pl->ax, tid - 32, g.sw, g.bw, g.gw, W);
+  if (!__syncthreads_and(ok)) return 0;
+  if (tid == 0) fin[0] = rg_finish_axis(&pl->ay, PH);
+  if (tid == 32) fin[1] = rg_finish_axis(&pl->ax, PW);
+  __syncthreads();
+  return fin[0] && fin[1];
+}
+
+__global__ void __launch_bounds__(RT_THREADS)
+rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   const float* __restrict__ dout, int c_per_cta, int buf_floats, int cc_cap) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  RgAxes* pl = reinterpret_cast<RgAxes*>(rt_smem);
+  float* d_s = reinterpret_cast<float*>(rt_smem + ((sizeof(RgAxes) + 15) / 16) * 16);
+  __shared__ int fin[2];
+
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x;
+  const int c_begin = blockIdx.y * c_per_cta;
+  const int c_end = min(C, c_begin + c_per_cta);
+  if (c_begin >= c_end) return;
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) return;
+  const int H = lv.H[level], W = lv.W[level];
+  const size_t HW = (size_t)H * W;
+  const RtGeom g = rt_geom_bwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+  if (!rg_build_axes(pl, fin, g, PH, PW, H, W)) return;  // the sweep kernel owns this RoI
+
+  const int exty = pl->ay.ext, extx = pl->ax.ext;
+  if (exty == 0 || extx == 0) return;  // no sample inside the map: the gradient is zero
+  const int xp = extx | 1;
+  int cc_max = buf_floats / (P + PH * xp);
+  if (cc_max > cc_cap) cc_max = cc_cap;
+  cc_max &= ~3;
+  if (cc_max < 4) {  // tile too large for the buffer: reference-order scatter (rare)
+    const float* dk = dout + ((size_t)k * C + c_begin) * P;
+    float* gb = lv.grad[level] + ((size_t)b * C + c_begin) * HW;
+    const int total = (c_end - c_begin) * P;
+    for (int i = tid; i < total; i += blockDim.x) {
+      const int c = i / P;
+      const int rem = i - c * P;
+      const int ph = rem / PW, pw = rem - ph * PW;
+      rt_direct_backward(gb + (size_t)c * HW, H, W, g, ph, pw, dk[i]);
+    }
+    return;
+  }
+  // covering bin ranges of every tile row / column
+  for (int i = tid; i < exty + extx; i += blockDim.x) {
+    const bool isy = i < exty;
+    const RgAxis* a = isy ? &pl->ay : &pl->ax;
+    const int e = isy ? i : i - exty, n = isy ? PH : PW;
+    int fb = n, lb = -1;
+    for (int p = 0; p < n; ++p) {
+      const int st = a->start[p];
+      if (st <= e && e < st + a->len[p]) {
+        if (fb == n) fb = p;
+        lb = p;
+      }
+    }
+    (isy ? pl->covy : pl->covx)[e] = fb | (lb << 8);
+  }
+  const int count = g.gh * g.gw;
+  const float inv = rt_exact_inv(count);
+  const float fcount = (float)count;
+  const float* wyf = &pl->ay.w[0][0];
+  const float* wxf = &pl->ax.w[0][0];
+  float* tile0 = lv.grad[level] + ((size_t)b * C + c_begin) * HW + (size_t)pl->ay.lo0 * W + pl->ax.lo0;
+  const float* dout_k = dout + ((size_t)k * C + c_begin) * P;
+  const int nA = PH * extx, nB = exty * extx;
+  const uint32_t mx = rt_magic((uint32_t)extx);
+
+  for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+    const int cc = min(cc_max, c_end - c_begin - c0);
+    float* Hs = d_s + (size_t)cc * P;  // [cc][PH][xp]
+    {
+      const float* src = dout_k + (size_t)c0 * P;
+      const int nfl = cc * P;
+      if (((reinterpret_cast<uintptr_t>(src) & 15) == 0) && (nfl & 3) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(d_s);
+        for (int i = tid; i < (nfl >> 2); i += blockDim.x) d4[i] = __ldg(s4 + i);
+      } else {
+        for (int i = tid; i < nfl; i += blockDim.x) d_s[i] = __ldg(src + i);
+      }
+    }
+    __syncthreads();  // also orders the cov arrays before their first use
+    const int ngrp = (cc + RG_U - 1) / RG_U;
+    const int hstride = PH * xp;  // channel pitch of Hs
+    // ---- phase A ---------------------------------------------------------------------------
+    for (int grp = 0; grp < ngrp; ++grp) {
+      const int cb = grp * RG_U;
+      const int nvalid = min(RG_U, cc - cb);
+      for (int rem = tid; rem < nA; rem += blockDim.x) {
+        const int ph = (int)rt_div((uint32_t)rem, (uint32_t)extx, mx);
+        const int x = rem - ph * extx;
+        const int cv = pl->covx[x];
+        const int fb = cv & 255, lb = cv >> 8;
+        float acc[RG_U];
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
+        const float* dp = d_s + cb * P + ph * PW;
+        if (nvalid == RG_U) {
+          for (int p = fb; p <= lb; ++p) {
+            const float w = wxf[p * RG_TAPS + (x - pl->ax.start[p])];
+            const float* dq = dp + p;
+#pragma unroll
+            for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, dq[u * P], acc[u]);
+          }
+        } else {
+          for (int p = fb; p <= lb; ++p) {
+            const float w = wxf[p * RG_TAPS + (x - pl->ax.start[p])];
+#pragma unroll
+            for (int u = 0; u < RG_U; ++u)
+              if (u < nvalid) acc[u] = fmaf(w, dp[u * P + p], acc[u]);
+          }
+        }
+        float* hp = Hs + cb * hstride + ph * xp + x;
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u)
+          if (u < nvalid) hp[u * hstride] = acc[u];
+      }
+    }
+    __syncthreads();
+    // ---- phase B ---------------------------------------------------------------------------
+    for (int grp = 0; grp < ngrp; ++grp) {
+      const int cb = grp * RG_U;
+      const int nvalid = min(RG_U, cc - cb);
+      float* gbase = tile0 + (size_t)(c0 + cb) * HW;
+      for (int rem = tid; rem < nB; rem += blockDim.x) {
+        const int y = (int)rt_div((uint32_t)rem, (uint32_t)extx, mx);
+        const int x = rem - y * extx;
+        const int cv = pl->covy[y];
+        const int fb = cv & 255, lb = cv >> 8;
+        float acc[RG_U];
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
+        const float* hp = Hs + cb * hstride + x;
+        if (nvalid == RG_U) {
+          for (int q = fb; q <= lb; ++q) {
+            const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
+            const float* hq = hp + q * xp;
+#pragma unroll
+            for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, hq[u * hstride], acc[u]);
+          }
+        } else {
+          for (int q = fb; q <= lb; ++q) {
+            const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
+#pragma unroll
+            for (int u = 0; u < RG_U; ++u)
+              if (u < nvalid) acc[u] = fmaf(w, hp[u * hstride + q * xp], acc[u]);
+          }
+        }
+        float* gp = gbase + (size_t)y * W + x;
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u)
+          if (u < nvalid) {
+            const float val = (inv != 0.f) ? acc[u] * inv : acc[u] / fcount;
+            if (val != 0.f) atomicAdd(gp + (size_t)u * HW, val);
+          }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // backward kernel (transpose of the forward sweeps)
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(RT_THREADS)
 rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   const float* __restrict__ dout, int c_per_cta, int vs_floats, int cc_cap) {
+                   const float* __restrict__ dout, int c_per_cta, int vs_floats, int cc_cap,
+                   int skip_banded) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
+  __shared__ RgAxes rg_axes_s;
+  __shared__ int rg_fin[2];
   RtAxisPlan* py = reinterpret_cast<RtAxisPlan*>(rt_smem);
   RtAxisPlan* px = py + 1;
   float* Hs = reinterpret_cast<float*>(rt_smem + ((2 * sizeof(RtAxisPlan) + 15) / 16) * 16);
@@ -810,6 +1079,8 @@ rt_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   float* grad_b = lv.grad[level] + ((size_t)b * C + c_begin) * HW;
   const float* dout_k = dout + ((size_t)k * C + c_begin) * P;
   const RtGeom g = rt_geom_bwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+  // second launch of the default path: only the RoIs the gather kernel returned from
+  if (skip_banded && rg_build_axes(&rg_axes_s, rg_fin, g, PH, PW, H, W)) return;
 
   if (tid == 0) s_ok[0] = rt_build_axis_plan(py, g.sh, g.bh, PH, g.gh, H);
   if (tid == 32) s_ok[1] = rt_build_axis_plan(px, g.sw, g.bw, PW, g.gw, W);
@@ -1175,12 +1446,29 @@ int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* 
   if (mode != 0) return RP_E_ARG;
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
   if (l.smem > 227 * 1024) return RP_E_LIMIT;
+  dim3 grid((unsigned)K, (unsigned)l.csplit);
+  const int gather = rp_env_int("RP_ROI_BWD_IMPL", 2) == 2 && PH <= RB_MAXP && PW <= RB_MAXP;
+  if (gather) {
+    int gthreads = rp_env_int("RP_ROI_BWD_G_THREADS", 256) & ~31;
+    if (gthreads < 64) gthreads = 64;
+    if (gthreads > RT_THREADS) gthreads = RT_THREADS;
+    int gfloats = rp_env_int("RP_ROI_BWD_G_FLOATS", 8192) & ~3;
+    if (gfloats < 1024) gfloats = 1024;
+    int gcc = rp_env_int("RP_ROI_BWD_G_CC", 32) & ~3;
+    if (gcc < 4) gcc = 4;
+    const size_t gsmem = rp_align_up(sizeof(RgAxes), 16) + sizeof(float) * (size_t)gfloats;
+    if (gsmem > 227 * 1024) return RP_E_LIMIT;
+    RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)gsmem));
+    rg_pool_bwd_kernel<<<grid, gthreads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
+                                                      dout, l.c_per_cta, gfloats, gcc);
+    RP_LAUNCH_CHECK();
+  }
   RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)l.smem));
-  dim3 grid((unsigned)K, (unsigned)l.csplit);
   rt_pool_bwd_kernel<<<grid, l.bwd_threads, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
                                                           sampling_ratio, dout, l.c_per_cta,
-                                                          l.vs_floats, l.bwd_cc);
+                                                          l.vs_floats, l.bwd_cc, gather);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }
