@@ -793,7 +793,10 @@ __device__ __forceinline__ void rt_direct_backward(float* plane, int H, int W, c
 // Every tile element is produced exactly once and the weights / ranges are fetched once for
 // RG_U channels.  RoIs without a band form are left to the sweep kernel below (second launch).
 // ------------------------------------------------------------------------------------------
-constexpr int RG_U = 8;
+#ifndef RG_UCH
+#define RG_UCH 8
+#endif
+constexpr int RG_U = RG_UCH;  // channels per thread
 constexpr int RG_TAPS = 8;  // tile rows / columns one bin may touch (merged taps)
 
 struct RgAxis {
@@ -886,10 +889,14 @@ __device__ __forceinline__ int rg_build_axes(RgAxes* pl, int* fin, const RtGeom&
   return fin[0] && fin[1];
 }
 
-__global__ void __launch_bounds__(RT_THREADS)
+#ifndef RG_MINB
+#define RG_MINB 4  // resident 256-thread CTAs per SM asked of the register allocator (<= 64 registers)
+#endif
+__global__ void __launch_bounds__(RT_THREADS, RG_MINB)
 rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   const float* __restrict__ dout, int c_per_cta, int buf_floats, int cc_cap) {
+                   const float* __restrict__ dout, int c_per_cta, int buf_floats, int cc_cap,
+                   int direct_fallback) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   RgAxes* pl = reinterpret_cast<RgAxes*>(rt_smem);
   float* d_s = reinterpret_cast<float*>(rt_smem + ((sizeof(RgAxes) + 15) / 16) * 16);
@@ -908,15 +915,20 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int H = lv.H[level], W = lv.W[level];
   const size_t HW = (size_t)H * W;
   const RtGeom g = rt_geom_bwd(roi, lv.scale[level], sampling_ratio, PH, PW);
-  if (!rg_build_axes(pl, fin, g, PH, PW, H, W)) return;  // the sweep kernel owns this RoI
-
-  const int exty = pl->ay.ext, extx = pl->ax.ext;
-  if (exty == 0 || extx == 0) return;  // no sample inside the map: the gradient is zero
-  const int xp = extx | 1;
-  int cc_max = buf_floats / (P + PH * xp);
-  if (cc_max > cc_cap) cc_max = cc_cap;
-  cc_max &= ~3;
-  if (cc_max < 4) {  // tile too large for the buffer: reference-order scatter (rare)
+  const int banded = rg_build_axes(pl, fin, g, PH, PW, H, W);
+  if (!banded && !direct_fallback) return;  // the sweep kernel (second launch) owns this RoI
+  int cc_max = 0, exty = 0, extx = 0;
+  if (banded) {
+    exty = pl->ay.ext;
+    extx = pl->ax.ext;
+    if (exty == 0 || extx == 0) return;  // no sample inside the map: the gradient is zero
+    cc_max = buf_floats / (P + PH * (extx | 1));
+    if (cc_max > cc_cap) cc_max = cc_cap;
+    cc_max &= ~3;
+  }
+  if (cc_max < 4) {
+    // no short-tap form (one-launch configuration) or tile too large for the buffer: rare,
+    // reference-order scatter by the whole CTA
     const float* dk = dout + ((size_t)k * C + c_begin) * P;
     float* gb = lv.grad[level] + ((size_t)b * C + c_begin) * HW;
     const int total = (c_end - c_begin) * P;
@@ -928,6 +940,7 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     return;
   }
+  const int xp = extx | 1;
   // covering bin ranges of every tile row / column
   for (int i = tid; i < exty + extx; i += blockDim.x) {
     const bool isy = i < exty;
@@ -1460,9 +1473,14 @@ int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* 
     if (gsmem > 227 * 1024) return RP_E_LIMIT;
     RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)gsmem));
+    // with a fixed sampling grid <= RB_MAXG only bins wider than ~6 feature pixels lack a short-tap
+    // form: too rare for a second launch, the gather kernel scatters them in reference order itself
+    const int one_launch = sampling_ratio > 0 && (int)sampling_ratio <= RB_MAXG &&
+                           rp_env_int("RP_ROI_BWD_SWEEP_FALLBACK", 0) == 0;
     rg_pool_bwd_kernel<<<grid, gthreads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
-                                                      dout, l.c_per_cta, gfloats, gcc);
+                                                      dout, l.c_per_cta, gfloats, gcc, one_launch);
     RP_LAUNCH_CHECK();
+    if (one_launch) return RP_OK;
   }
   RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)l.smem));
