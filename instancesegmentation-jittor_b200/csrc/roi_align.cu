@@ -1012,9 +1012,14 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           }
         }
         float* hp = Hs + cb * hstride + ph * xp + x;
+        if (nvalid == RG_U) {
 #pragma unroll
-        for (int u = 0; u < RG_U; ++u)
-          if (u < nvalid) hp[u * hstride] = acc[u];
+          for (int u = 0; u < RG_U; ++u) hp[u * hstride] = acc[u];
+        } else {
+#pragma unroll
+          for (int u = 0; u < RG_U; ++u)
+            if (u < nvalid) hp[u * hstride] = acc[u];
+        }
       }
     }
     __syncthreads();
@@ -1047,13 +1052,21 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
               if (u < nvalid) acc[u] = fmaf(w, hp[u * hstride + q * xp], acc[u]);
           }
         }
+        if (fb > lb) continue;  // a tile row no bin touches carries no gradient
         float* gp = gbase + (size_t)y * W + x;
+        // one RED per tile element, unconditionally: a per-element "!= 0" test costs a divergent
+        // branch each, and zeros only arise from zero dout here
+        if (nvalid == RG_U && inv != 0.f) {
 #pragma unroll
-        for (int u = 0; u < RG_U; ++u)
-          if (u < nvalid) {
-            const float val = (inv != 0.f) ? acc[u] * inv : acc[u] / fcount;
-            if (val != 0.f) atomicAdd(gp + (size_t)u * HW, val);
+          for (int u = 0; u < RG_U; ++u) {
+            atomicAdd(gp, acc[u] * inv);
+            gp += HW;
           }
+        } else {
+#pragma unroll
+          for (int u = 0; u < RG_U; ++u)
+            if (u < nvalid) atomicAdd(gp + (size_t)u * HW, (inv != 0.f) ? acc[u] * inv : acc[u] / fcount);
+        }
       }
     }
     __syncthreads();

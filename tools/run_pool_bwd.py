@@ -21,7 +21,7 @@ grad_bytes = sum(int(np.prod(s)) for s in shapes) * 4
 for res, k in ((7, int(rois.shape[0])), (14, 2048)):
     d = torch.randn((k, 256, res, res), device=dev)
     fn = lambda: rp.pooler_backward(d, rois[:k], levels[:k], shapes, synth.FPN_SCALES, 2)
-    for _ in range(2):
+    for _ in range(10):  # the first launches after start-up run at ramping clocks
         fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
