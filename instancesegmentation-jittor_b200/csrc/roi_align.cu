@@ -922,11 +922,11 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     exty = pl->ay.ext;
     extx = pl->ax.ext;
     if (exty == 0 || extx == 0) return;  // no sample inside the map: the gradient is zero
-    cc_max = buf_floats / (P + PH * (extx | 1));
+    cc_max = (buf_floats - 4) / (P + PH * extx);  // whole groups of RG_U channels (H is group-padded)
     if (cc_max > cc_cap) cc_max = cc_cap;
-    cc_max &= ~3;
+    cc_max &= ~(RG_U - 1);
   }
-  if (cc_max < 4) {
+  if (cc_max < RG_U) {
     // no short-tap form (one-launch configuration) or tile too large for the buffer: rare,
     // reference-order scatter by the whole CTA
     const float* dk = dout + ((size_t)k * C + c_begin) * P;
@@ -940,7 +940,6 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     return;
   }
-  const int xp = extx | 1;
   // covering bin ranges of every tile row / column
   for (int i = tid; i < exty + extx; i += blockDim.x) {
     const bool isy = i < exty;
@@ -968,7 +967,7 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 
   for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
     const int cc = min(cc_max, c_end - c_begin - c0);
-    float* Hs = d_s + (size_t)cc * P;  // [cc][PH][xp]
+    float* Hs = d_s + ((cc_max * P + 3) & ~3);  // [group][PH][extx][RG_U]: a thread's channels are 32 bytes
     {
       const float* src = dout_k + (size_t)c0 * P;
       const int nfl = cc * P;
@@ -982,7 +981,7 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     __syncthreads();  // also orders the cov arrays before their first use
     const int ngrp = (cc + RG_U - 1) / RG_U;
-    const int hstride = PH * xp;  // channel pitch of Hs
+    const int hgroup = PH * extx * RG_U;  // group pitch of Hs
     // ---- phase A ---------------------------------------------------------------------------
     for (int grp = 0; grp < ngrp; ++grp) {
       const int cb = grp * RG_U;
@@ -1011,15 +1010,11 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
               if (u < nvalid) acc[u] = fmaf(w, dp[u * P + p], acc[u]);
           }
         }
-        float* hp = Hs + cb * hstride + ph * xp + x;
-        if (nvalid == RG_U) {
+        // channels past nvalid hold zeros: the group is stored whole (two 16-byte stores)
+        float4* hp = reinterpret_cast<float4*>(Hs + grp * hgroup + (ph * extx + x) * RG_U);
 #pragma unroll
-          for (int u = 0; u < RG_U; ++u) hp[u * hstride] = acc[u];
-        } else {
-#pragma unroll
-          for (int u = 0; u < RG_U; ++u)
-            if (u < nvalid) hp[u * hstride] = acc[u];
-        }
+        for (int v = 0; v < RG_U / 4; ++v)
+          hp[v] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
       }
     }
     __syncthreads();
@@ -1036,20 +1031,17 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
         float acc[RG_U];
 #pragma unroll
         for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
-        const float* hp = Hs + cb * hstride + x;
-        if (nvalid == RG_U) {
-          for (int q = fb; q <= lb; ++q) {
-            const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
-            const float* hq = hp + q * xp;
+        const float* hp = Hs + grp * hgroup + x * RG_U;
+        for (int q = fb; q <= lb; ++q) {
+          const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
+          const float4* hq = reinterpret_cast<const float4*>(hp + q * extx * RG_U);
 #pragma unroll
-            for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, hq[u * hstride], acc[u]);
-          }
-        } else {
-          for (int q = fb; q <= lb; ++q) {
-            const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
-#pragma unroll
-            for (int u = 0; u < RG_U; ++u)
-              if (u < nvalid) acc[u] = fmaf(w, hp[u * hstride + q * xp], acc[u]);
+          for (int v = 0; v < RG_U / 4; ++v) {
+            const float4 h = hq[v];
+            acc[4 * v] = fmaf(w, h.x, acc[4 * v]);
+            acc[4 * v + 1] = fmaf(w, h.y, acc[4 * v + 1]);
+            acc[4 * v + 2] = fmaf(w, h.z, acc[4 * v + 2]);
+            acc[4 * v + 3] = fmaf(w, h.w, acc[4 * v + 3]);
           }
         }
         if (fb > lb) continue;  // a tile row no bin touches carries no gradient
