@@ -30,6 +30,9 @@
 namespace {
 
 constexpr int RT_THREADS = 256;
+#ifndef RP_ROI_IMPL_DEFAULT
+#define RP_ROI_IMPL_DEFAULT 3  // forward kernel: 3 = tile walk, 4 = banded, 5 = merged taps
+#endif
 constexpr int RT_U1 = 4;  // channels per thread, phase 1
 constexpr int RT_U2 = 2;  // channels per thread, phase 2
 constexpr int RT_CC_CAP = 32;  // max channels per chunk (bounds the out tile)
@@ -967,7 +970,7 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 
   for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
     const int cc = min(cc_max, c_end - c_begin - c0);
-    float* Hs = d_s + ((cc_max * P + 3) & ~3);  // [group][PH][extx][RG_U]: a thread's channels are 32 bytes
+    float* Hs = d_s + ((cc_max * P + 3) & ~3);  // [group][RG_U/4 planes][PH][extx][4 channels]
     {
       const float* src = dout_k + (size_t)c0 * P;
       const int nfl = cc * P;
@@ -1011,10 +1014,12 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           }
         }
         // channels past nvalid hold zeros: the group is stored whole (two 16-byte stores)
-        float4* hp = reinterpret_cast<float4*>(Hs + grp * hgroup + (ph * extx + x) * RG_U);
+        // H is kept as RG_U/4 planes of 4 channels: consecutive lanes (x) are 16 bytes apart in a
+        // plane, which keeps the 16-byte shared accesses conflict-free (32-byte strides are 2-way)
+        float4* hp = reinterpret_cast<float4*>(Hs + grp * hgroup) + ph * extx + x;
 #pragma unroll
         for (int v = 0; v < RG_U / 4; ++v)
-          hp[v] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
+          hp[v * nA] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
       }
     }
     __syncthreads();
@@ -1031,13 +1036,13 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
         float acc[RG_U];
 #pragma unroll
         for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
-        const float* hp = Hs + grp * hgroup + x * RG_U;
+        const float4* hp = reinterpret_cast<const float4*>(Hs + grp * hgroup) + x;
         for (int q = fb; q <= lb; ++q) {
           const float w = wyf[q * RG_TAPS + (y - pl->ay.start[q])];
-          const float4* hq = reinterpret_cast<const float4*>(hp + q * extx * RG_U);
+          const float4* hq = hp + q * extx;
 #pragma unroll
           for (int v = 0; v < RG_U / 4; ++v) {
-            const float4 h = hq[v];
+            const float4 h = hq[v * nA];
             acc[4 * v] = fmaf(w, h.x, acc[4 * v]);
             acc[4 * v + 1] = fmaf(w, h.y, acc[4 * v + 1]);
             acc[4 * v + 2] = fmaf(w, h.z, acc[4 * v + 2]);
@@ -1058,6 +1063,169 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 #pragma unroll
           for (int u = 0; u < RG_U; ++u)
             if (u < nvalid) atomicAdd(gp + (size_t)u * HW, (inv != 0.f) ? acc[u] * inv : acc[u] / fcount);
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// forward kernel, merged-tap form (v5): the same per-axis plan as the gather backward (RgAxis:
+// every pooled bin reads a short run of consecutive tile rows with merged weights).  CTA = (RoI,
+// channel slice); per chunk of cc channels (whole groups of RG_U):
+//   stage   the RoI's tile [cc][exty][extx] global -> shared, 4-byte cp.async; a thread keeps its
+//           tile positions and only steps the channel
+//   y-pass  thread = (ph, x) x RG_U channels: V[ph][x][c8] = sum_j wy[ph][j] * T[c][sy+j][x]
+//   x-pass  thread = (ph, pw) x RG_U channels: out = sum_j wx[pw][j] * V[ph][sx+j][c8] / count;
+//           V is channel-minor (two 16-byte loads per tap), consecutive threads write consecutive
+//           output floats of a channel plane (streaming stores).
+// Weights, starts and lengths are fetched once for RG_U channels.  RoIs without a short-tap form
+// (rare with a fixed sampling grid) are evaluated in reference order by the same CTA.
+// ------------------------------------------------------------------------------------------
+#ifndef RGF_MINB
+#define RGF_MINB 4
+#endif
+__global__ void __launch_bounds__(RT_THREADS, RGF_MINB)
+rg_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   float* __restrict__ out, int c_per_cta, int buf_floats, int cc_cap) {
+  extern __shared__ __align__(16) unsigned char rt_smem[];
+  RgAxes* pl = reinterpret_cast<RgAxes*>(rt_smem);
+  float* T = reinterpret_cast<float*>(rt_smem + ((sizeof(RgAxes) + 15) / 16) * 16);
+  __shared__ int fin[2];
+
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x;
+  const int c_begin = blockIdx.y * c_per_cta;
+  const int c_end = min(C, c_begin + c_per_cta);
+  if (c_begin >= c_end) return;
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  float* out_k = out + ((size_t)k * C + c_begin) * P;
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) {
+    rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+    return;
+  }
+  const int H = lv.H[level], W = lv.W[level];
+  const size_t HW = (size_t)H * W;
+  const float* feat_b = lv.feat[level] + ((size_t)b * C + c_begin) * HW;
+  const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
+  const int banded = rg_build_axes(pl, fin, g, PH, PW, H, W);
+  int cc_max = 0, exty = 0, extx = 0;
+  if (banded) {
+    exty = pl->ay.ext;
+    extx = pl->ax.ext;
+    if (exty == 0 || extx == 0) {  // every sample lies outside the map
+      rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
+      return;
+    }
+    cc_max = (buf_floats - 4) / (exty * extx + PH * extx);
+    if (cc_max > cc_cap) cc_max = cc_cap;
+    cc_max &= ~(RG_U - 1);
+  }
+  if (cc_max < RG_U) {  // no short-tap form, or the tile does not fit: reference order (rare)
+    const int total = (c_end - c_begin) * P;
+    for (int i = tid; i < total; i += blockDim.x) {
+      const int c = i / P;
+      const int rem = i - c * P;
+      const int ph = rem / PW, pw = rem - ph * PW;
+      out_k[i] = rt_direct_output(feat_b + (size_t)c * HW, H, W, g, ph, pw);
+    }
+    return;
+  }
+  const int count = g.gh * g.gw;
+  const float inv = rt_exact_inv(count);
+  const float fcount = (float)count;
+  const float* wyf = &pl->ay.w[0][0];
+  const float* wxf = &pl->ax.w[0][0];
+  const int nT = exty * extx, nV = PH * extx;
+  const uint32_t mx = rt_magic((uint32_t)extx), mpw = rt_magic((uint32_t)PW);
+  const float* tile_g = feat_b + (size_t)pl->ay.lo0 * W + pl->ax.lo0;
+  float* V = T + ((cc_max * nT + 3) & ~3);  // [group][RG_U/4 planes][PH][extx][4 channels]
+  const int vgroup = nV * RG_U;
+
+  for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
+    const int cc = min(cc_max, c_end - c_begin - c0);
+    const int ngrp = (cc + RG_U - 1) / RG_U;
+    // ---- stage -------------------------------------------------------------------------------
+    for (int pos = tid; pos < nT; pos += blockDim.x) {
+      const int y = (int)rt_div((uint32_t)pos, (uint32_t)extx, mx);
+      const int x = pos - y * extx;
+      const float* src = tile_g + (size_t)c0 * HW + (size_t)y * W + x;
+      uint32_t dst = rp_smem_addr(T + pos);
+      for (int c = 0; c < cc; ++c) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        src += HW;
+        dst += (uint32_t)nT * 4u;
+      }
+    }
+    if (cc < ngrp * RG_U)  // the last group's missing channels read as zeros
+      for (int i = cc * nT + tid; i < ngrp * RG_U * nT; i += blockDim.x) T[i] = 0.f;
+    rt_cp_async_wait_all();
+    __syncthreads();
+    // ---- y-pass ------------------------------------------------------------------------------
+    for (int grp = 0; grp < ngrp; ++grp) {
+      for (int rem = tid; rem < nV; rem += blockDim.x) {
+        const int ph = (int)rt_div((uint32_t)rem, (uint32_t)extx, mx);
+        const int x = rem - ph * extx;
+        const int ly = pl->ay.len[ph];
+        const float* tp = T + (grp * RG_U * exty + pl->ay.start[ph]) * extx + x;
+        const float* wp = wyf + ph * RG_TAPS;
+        float acc[RG_U];
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
+        for (int j = 0; j < ly; ++j) {
+          const float w = wp[j];
+          const float* tq = tp + j * extx;
+#pragma unroll
+          for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, tq[u * nT], acc[u]);
+        }
+        float4* vp = reinterpret_cast<float4*>(V + grp * vgroup) + rem;  // planes of 4 channels
+#pragma unroll
+        for (int v = 0; v < RG_U / 4; ++v)
+          vp[v * nV] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
+      }
+    }
+    __syncthreads();
+    // ---- x-pass ------------------------------------------------------------------------------
+    for (int grp = 0; grp < ngrp; ++grp) {
+      const int cb = grp * RG_U;
+      const int nvalid = min(RG_U, cc - cb);
+      float* ob = out_k + (size_t)(c0 + cb) * P;
+      for (int i = tid; i < P; i += blockDim.x) {
+        const int ph = (int)rt_div((uint32_t)i, (uint32_t)PW, mpw);
+        const int pw = i - ph * PW;
+        const int lx = pl->ax.len[pw];
+        const float4* vq = reinterpret_cast<const float4*>(V + grp * vgroup) + ph * extx + pl->ax.start[pw];
+        const float* wp = wxf + pw * RG_TAPS;
+        float acc[RG_U];
+#pragma unroll
+        for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
+        for (int j = 0; j < lx; ++j) {
+          const float w = wp[j];
+#pragma unroll
+          for (int v = 0; v < RG_U / 4; ++v) {
+            const float4 h = vq[v * nV + j];
+            acc[4 * v] = fmaf(w, h.x, acc[4 * v]);
+            acc[4 * v + 1] = fmaf(w, h.y, acc[4 * v + 1]);
+            acc[4 * v + 2] = fmaf(w, h.z, acc[4 * v + 2]);
+            acc[4 * v + 3] = fmaf(w, h.w, acc[4 * v + 3]);
+          }
+        }
+        float* op = ob + i;
+        if (nvalid == RG_U && inv != 0.f) {
+#pragma unroll
+          for (int u = 0; u < RG_U; ++u) {
+            __stcs(op, acc[u] * inv);
+            op += P;
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < RG_U; ++u)
+            if (u < nvalid) __stcs(op + (size_t)u * P, (inv != 0.f) ? acc[u] * inv : acc[u] / fcount);
         }
       }
     }
@@ -1396,7 +1564,27 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   if (mode != 0) return RP_E_ARG;
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
-  if (rp_env_int("RP_ROI_IMPL", 3) == 4 && PW <= 128) {
+  if (rp_env_int("RP_ROI_IMPL", RP_ROI_IMPL_DEFAULT) == 5 && sampling_ratio > 0 &&
+      (int)sampling_ratio <= RB_MAXG && PH <= RB_MAXP && PW <= RB_MAXP) {
+    // merged-tap kernel (fixed sampling grid); RoIs without a short-tap form: reference order
+    int threads = rp_env_int("RP_ROI_G_THREADS", 256) & ~31;
+    if (threads < 64) threads = 64;
+    if (threads > RT_THREADS) threads = RT_THREADS;
+    int gfloats = rp_env_int("RP_ROI_G_FLOATS", 12288) & ~3;
+    if (gfloats < 2048) gfloats = 2048;
+    int gcc = rp_env_int("RP_ROI_G_CC", 32) & ~(RG_U - 1);
+    if (gcc < RG_U) gcc = RG_U;
+    const size_t gsmem = rp_align_up(sizeof(RgAxes), 16) + sizeof(float) * (size_t)gfloats;
+    if (gsmem > 227 * 1024) return RP_E_LIMIT;
+    RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)gsmem));
+    dim3 grid((unsigned)K, (unsigned)l.csplit);
+    rg_pool_fwd_kernel<<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
+                                                     out, l.c_per_cta, gfloats, gcc);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
+  if (rp_env_int("RP_ROI_IMPL", RP_ROI_IMPL_DEFAULT) == 4 && PW <= 128) {
     // banded kernel; RoIs without a band form run the v3 body inside the same CTA
     const int cfg = rp_env_int("RP_ROI_BAND_CFG", 0);  // 0: 128 thr x5, 1: 128 x8, 2: 256 x4, 3: 256 x3
     const int nt = cfg >= 2 ? 256 : 128;

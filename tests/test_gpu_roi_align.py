@@ -166,10 +166,11 @@ def test_full_size_properties():
     assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), abs(rhs), 1.0) * 10
 
 
-@pytest.mark.parametrize("impl", ["3", "4"])
+@pytest.mark.parametrize("impl", ["3", "4", "5"])
 @pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
 def test_forward_kernel_variants(impl, P, sr, monkeypatch):
-    """Both forward kernels (RP_ROI_IMPL=3: column walk; =4: banded, v3 body as its fallback)
+    """The forward kernels (RP_ROI_IMPL=3: column walk; =4: banded, v3 body as its fallback; =5:
+    merged taps, reference-order fallback; adaptive sampling always takes the column walk)
     against the oracle, on aligned (W % 4 == 0), 8-byte (W = 42) and odd-width maps."""
     monkeypatch.setenv("RP_ROI_IMPL", impl)
     rng = np.random.default_rng(11)
@@ -183,8 +184,9 @@ def test_forward_kernel_variants(impl, P, sr, monkeypatch):
         _close(out, exp)
 
 
-def test_banded_pooler_multi_level(monkeypatch):
-    monkeypatch.setenv("RP_ROI_IMPL", "4")
+@pytest.mark.parametrize("impl", ["4", "5"])
+def test_banded_pooler_multi_level(impl, monkeypatch):
+    monkeypatch.setenv("RP_ROI_IMPL", impl)
     N, C = 2, 24
     feats = synth.fpn_features(N, C)
     rois = synth.rois_for_images(N, 200)
@@ -193,6 +195,23 @@ def test_banded_pooler_multi_level(monkeypatch):
         exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, P, 2)
         out = rp.pooler_forward([T(f) for f in feats], synth.FPN_SCALES, T(rois), T(lv), P, 2)
         _close(out.cpu().numpy(), exp)
+
+
+def test_backward_kernels_agree_with_oracle_on_wide_bins(monkeypatch):
+    """Gather backward (default) and the sweep kernel on RoIs whose bins are wider than the
+    short-tap form allows (reference-order fallback inside the gather kernel), plus adaptive
+    sampling (sweep kernel in a second launch)."""
+    rng = np.random.default_rng(3)
+    feat_shape = (2, 6, 60, 90)
+    rois = _rois(rng, 40, 2)
+    rois[:8, 1:] = np.array([0.0, 0.0, 1400.0, 940.0], np.float32)  # 87 x 59 px at 1/16: 29 px bins at 3x2
+    for P, sr in [((2, 3), 2), ((7, 7), 2), ((7, 7), 0)]:
+        d = rng.standard_normal((rois.shape[0], feat_shape[1]) + P).astype(np.float32)
+        exp = oracle.roi_align_backward(d, rois, feat_shape, 1 / 16, sr)
+        for impl in ("2", "1"):
+            monkeypatch.setenv("RP_ROI_BWD_IMPL", impl)
+            got = rp.roi_align_backward(T(d), T(rois), feat_shape, 1 / 16, sr).cpu().numpy()
+            np.testing.assert_allclose(got, exp, rtol=1e-5, atol=1e-5 * max(1.0, np.abs(exp).max()))
 
 
 def test_pooler_execute_host_pipeline():
