@@ -158,29 +158,36 @@ bp_candidates_kernel(const float* __restrict__ prob, const float* __restrict__ r
   const float xmax = im_wh[2 * b] - 1.0f, ymax = im_wh[2 * b + 1] - 1.0f;
   const int code_col = agnostic ? reg_cols - 4 : 4 * j;
   int base = 0;
-  for (int i0 = r0; i0 < r1 && base < limit; i0 += 32) {
-    const int i = i0 + lane;
-    float p = 0.0f;
-    bool ok = false;
-    if (i < r1) {
-      p = prob[(size_t)i * C + j];
-      ok = p > thr;
+  // four 32-row steps per trip: the strided probability loads of a trip are all in flight before the
+  // first ballot (a problem is one warp walking ~1000 rows: latency, not bandwidth)
+  for (int i0 = r0; i0 < r1 && base < limit; i0 += 128) {
+    float pv[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int i = i0 + 32 * t + lane;
+      pv[t] = (i < r1) ? prob[(size_t)i * C + j] : -1.0f;
     }
-    const unsigned m = __ballot_sync(0xffffffffu, ok);
-    const int pos = base + __popc(m & ((1u << lane) - 1u));
-    if (ok && pos < limit) {
-      const float4 d = *reinterpret_cast<const float4*>(reg + (size_t)i * reg_cols + code_col);
-      const float4 a = *reinterpret_cast<const float4*>(proposals + (size_t)i * 4);
-      float4 o = bp_decode_one(a, d, wx, wy, ww, wh, clip);
-      o.x = fminf(fmaxf(o.x, 0.f), xmax);  // clip_to_image(remove_empty=False), :80
-      o.y = fminf(fmaxf(o.y, 0.f), ymax);
-      o.z = fminf(fmaxf(o.z, 0.f), xmax);
-      o.w = fminf(fmaxf(o.w, 0.f), ymax);
-      *reinterpret_cast<float4*>(cand_boxes + (size_t)(off + pos) * 4) = o;
-      cand_scores[off + pos] = p;
-      cand_row[off + pos] = i - r0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int i = i0 + 32 * t + lane;
+      const float p = pv[t];
+      const bool ok = (i < r1) && (p > thr);
+      const unsigned m = __ballot_sync(0xffffffffu, ok);
+      const int pos = base + __popc(m & ((1u << lane) - 1u));
+      if (ok && pos < limit) {
+        const float4 d = *reinterpret_cast<const float4*>(reg + (size_t)i * reg_cols + code_col);
+        const float4 a = *reinterpret_cast<const float4*>(proposals + (size_t)i * 4);
+        float4 o = bp_decode_one(a, d, wx, wy, ww, wh, clip);
+        o.x = fminf(fmaxf(o.x, 0.f), xmax);  // clip_to_image(remove_empty=False), :80
+        o.y = fminf(fmaxf(o.y, 0.f), ymax);
+        o.z = fminf(fmaxf(o.z, 0.f), xmax);
+        o.w = fminf(fmaxf(o.w, 0.f), ymax);
+        *reinterpret_cast<float4*>(cand_boxes + (size_t)(off + pos) * 4) = o;
+        cand_scores[off + pos] = p;
+        cand_row[off + pos] = i - r0;
+      }
+      base += __popc(m);
     }
-    base += __popc(m);
   }
 }
 
