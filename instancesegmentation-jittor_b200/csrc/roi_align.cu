@@ -1086,6 +1086,7 @@ rg_pool_bwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 #ifndef RGF_MINB
 #define RGF_MINB 4
 #endif
+template <bool DIRECT>  // DIRECT: no staged tile, the y-pass reads the feature map through L1
 __global__ void __launch_bounds__(RT_THREADS, RGF_MINB)
 rg_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
@@ -1122,7 +1123,7 @@ rg_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
       rt_zero_fill(out_k, (size_t)(c_end - c_begin) * P);
       return;
     }
-    cc_max = (buf_floats - 4) / (exty * extx + PH * extx);
+    cc_max = (buf_floats - 4) / ((DIRECT ? 0 : exty * extx) + PH * extx);
     if (cc_max > cc_cap) cc_max = cc_cap;
     cc_max &= ~(RG_U - 1);
   }
@@ -1144,44 +1145,59 @@ rg_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int nT = exty * extx, nV = PH * extx;
   const uint32_t mx = rt_magic((uint32_t)extx), mpw = rt_magic((uint32_t)PW);
   const float* tile_g = feat_b + (size_t)pl->ay.lo0 * W + pl->ax.lo0;
-  float* V = T + ((cc_max * nT + 3) & ~3);  // [group][RG_U/4 planes][PH][extx][4 channels]
+  float* V = T + (DIRECT ? 0 : ((cc_max * nT + 3) & ~3));  // [group][RG_U/4 planes][PH][extx][4 channels]
   const int vgroup = nV * RG_U;
 
   for (int c0 = 0; c0 < c_end - c_begin; c0 += cc_max) {
     const int cc = min(cc_max, c_end - c_begin - c0);
     const int ngrp = (cc + RG_U - 1) / RG_U;
     // ---- stage -------------------------------------------------------------------------------
-    for (int pos = tid; pos < nT; pos += blockDim.x) {
-      const int y = (int)rt_div((uint32_t)pos, (uint32_t)extx, mx);
-      const int x = pos - y * extx;
-      const float* src = tile_g + (size_t)c0 * HW + (size_t)y * W + x;
-      uint32_t dst = rp_smem_addr(T + pos);
-      for (int c = 0; c < cc; ++c) {
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-        src += HW;
-        dst += (uint32_t)nT * 4u;
+    if (!DIRECT) {
+      for (int pos = tid; pos < nT; pos += blockDim.x) {
+        const int y = (int)rt_div((uint32_t)pos, (uint32_t)extx, mx);
+        const int x = pos - y * extx;
+        const float* src = tile_g + (size_t)c0 * HW + (size_t)y * W + x;
+        uint32_t dst = rp_smem_addr(T + pos);
+        for (int c = 0; c < cc; ++c) {
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+          src += HW;
+          dst += (uint32_t)nT * 4u;
+        }
       }
+      if (cc < ngrp * RG_U)  // the last group's missing channels read as zeros
+        for (int i = cc * nT + tid; i < ngrp * RG_U * nT; i += blockDim.x) T[i] = 0.f;
+      rt_cp_async_wait_all();
+      __syncthreads();
     }
-    if (cc < ngrp * RG_U)  // the last group's missing channels read as zeros
-      for (int i = cc * nT + tid; i < ngrp * RG_U * nT; i += blockDim.x) T[i] = 0.f;
-    rt_cp_async_wait_all();
-    __syncthreads();
     // ---- y-pass ------------------------------------------------------------------------------
     for (int grp = 0; grp < ngrp; ++grp) {
       for (int rem = tid; rem < nV; rem += blockDim.x) {
         const int ph = (int)rt_div((uint32_t)rem, (uint32_t)extx, mx);
         const int x = rem - ph * extx;
         const int ly = pl->ay.len[ph];
-        const float* tp = T + (grp * RG_U * exty + pl->ay.start[ph]) * extx + x;
         const float* wp = wyf + ph * RG_TAPS;
         float acc[RG_U];
 #pragma unroll
         for (int u = 0; u < RG_U; ++u) acc[u] = 0.f;
-        for (int j = 0; j < ly; ++j) {
-          const float w = wp[j];
-          const float* tq = tp + j * extx;
+        if (DIRECT) {
+          const int cb = grp * RG_U;
+          const int nvalid = min(RG_U, cc - cb);
+          const float* gp = tile_g + (size_t)(c0 + cb) * HW + (size_t)pl->ay.start[ph] * W + x;
+          for (int j = 0; j < ly; ++j) {
+            const float w = wp[j];
+            const float* gq = gp + (size_t)j * W;
 #pragma unroll
-          for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, tq[u * nT], acc[u]);
+            for (int u = 0; u < RG_U; ++u)
+              if (u < nvalid) acc[u] = fmaf(w, __ldg(gq + (size_t)u * HW), acc[u]);
+          }
+        } else {
+          const float* tp = T + (grp * RG_U * exty + pl->ay.start[ph]) * extx + x;
+          for (int j = 0; j < ly; ++j) {
+            const float w = wp[j];
+            const float* tq = tp + j * extx;
+#pragma unroll
+            for (int u = 0; u < RG_U; ++u) acc[u] = fmaf(w, tq[u * nT], acc[u]);
+          }
         }
         float4* vp = reinterpret_cast<float4*>(V + grp * vgroup) + rem;  // planes of 4 channels
 #pragma unroll
@@ -1576,11 +1592,18 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     if (gcc < RG_U) gcc = RG_U;
     const size_t gsmem = rp_align_up(sizeof(RgAxes), 16) + sizeof(float) * (size_t)gfloats;
     if (gsmem > 227 * 1024) return RP_E_LIMIT;
-    RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)gsmem));
     dim3 grid((unsigned)K, (unsigned)l.csplit);
-    rg_pool_fwd_kernel<<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
-                                                     out, l.c_per_cta, gfloats, gcc);
+    if (rp_env_int("RP_ROI_G_DIRECT", 0)) {
+      RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+      rg_pool_fwd_kernel<true><<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                             sampling_ratio, out, l.c_per_cta, gfloats, gcc);
+    } else {
+      RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel<false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+      rg_pool_fwd_kernel<false><<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW,
+                                                              sampling_ratio, out, l.c_per_cta, gfloats, gcc);
+    }
     RP_LAUNCH_CHECK();
     return RP_OK;
   }
