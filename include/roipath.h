@@ -305,6 +305,13 @@ RP_API int rp_box_post(const float* class_logits, const float* box_regression, c
  *   probs [num_center,num_pixel] = exp(-|e_p - e_c|^2 * sigma) inside each centre's box, 0
  *   elsewhere (the launch zero-fills, :60).  Limits: dim <= 128, num_center <= 65535.
  * ------------------------------------------------------------------------------------ */
+/* rp_box_masks: boxes_to_masks det/structures/boxlist_ops.py:237-261 (crop = 0: indicator of the
+ *   box grown by 1 px + padding * size, upper clamp w / h) and crop_by_box :262-281 (crop = 1:
+ *   upper clamp w-1 / h-1, masks_out = masks_in * indicator).  boxes [n,4]; indicator [n,h,w]
+ *   uint8 (may be NULL when masks_out is given); masks_in / masks_out [n,h,w] float or NULL. */
+RP_API int rp_box_masks(const float* boxes, int n, int h, int w, float padding, int crop,
+                 const float* masks_in, float* masks_out, uint8_t* indicator, void* stream);
+
 RP_API int rp_boxlist_iou(const float* boxes1, int N, const float* boxes2, int M, float* out,
                    void* stream);
 

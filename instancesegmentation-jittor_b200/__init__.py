@@ -17,7 +17,7 @@ from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_f
 from .box_head import PostProcessor, box_post, make_roi_box_post_processor
 from .rpn import (BoxCoder, RPNPostProcessor, box_decode, make_rpn_postprocessor, rpn_pre_nms,
                   rpn_pre_nms_levels, rpn_select_levels)
-from .structures import (BoxList, boxlist_iou, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
+from .structures import (BoxList, boxes_to_masks, crop_by_box, boxlist_iou, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
                          remove_small_boxes)
 from .yolact import (Detect, crop, decode, detect_prefilter, fast_nms_batched, mask_assemble, postprocess,
                      sanitize_coordinates)

@@ -52,6 +52,7 @@ SIGNATURES = {
     "rp_box_post_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rp_box_post": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _d, _i, _f, _f, _f, _f,
                          _f, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _sz, _vp]),
+    "rp_box_masks": (_i, [_vp, _i, _i, _i, _f, _i, _vp, _vp, _vp, _vp]),
     "rp_boxlist_iou": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "rp_roi_pool_forward": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _f, _vp, _vp, _vp]),
     "rp_roi_pool_backward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),

@@ -116,6 +116,42 @@ mask_prob_kernel(const float* __restrict__ embed_pixel, const float* __restrict_
   }
 }
 
+
+// ---- EmbedMask box masks --------------------------------------------------------------------
+// boxes_to_masks (boxlist_ops.py:237-261) and crop_by_box (:262-281): a padded-box indicator per
+// (instance, pixel); crop_by_box also multiplies a float mask by it.  The two differ in the order
+// of the padding arithmetic and in the upper clamp (w / h against w-1 / h-1); `crop` selects.
+// CTA = (256-pixel run, instance): rows are written in plane order (coalesced bytes / floats).
+__global__ void __launch_bounds__(256)
+box_mask_kernel(const float* __restrict__ boxes, int h, int w, float padding, int crop,
+                const float* __restrict__ masks_in, float* __restrict__ masks_out,
+                uint8_t* __restrict__ ind_out) {
+  const int n = blockIdx.y;
+  const float* bx = boxes + (size_t)n * 4;
+  const float bw = bx[2] - bx[0], bh = bx[3] - bx[1];
+  float x1, x2, y1, y2;
+  if (crop) {
+    x1 = fmaxf(bx[0] - bw * padding - 1.0f, 0.0f);
+    x2 = fminf(bx[2] + bw * padding + 1.0f, (float)(w - 1));
+    y1 = fmaxf(bx[1] - bh * padding - 1.0f, 0.0f);
+    y2 = fminf(bx[3] + bh * padding + 1.0f, (float)(h - 1));
+  } else {
+    x1 = fmaxf(bx[0] - 1.0f - bw * padding, 0.0f);
+    x2 = fminf(bx[2] + 1.0f + bw * padding, (float)w);
+    y1 = fmaxf(bx[1] - 1.0f - bh * padding, 0.0f);
+    y2 = fminf(bx[3] + 1.0f + bh * padding, (float)h);
+  }
+  const size_t plane = (size_t)h * w;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / w), c = (int)(i - (size_t)r * w);
+    const bool in = ((float)c >= x1) && ((float)c < x2) && ((float)r >= y1) && ((float)r < y2);
+    const size_t o = (size_t)n * plane + i;
+    if (ind_out) ind_out[o] = in ? 1 : 0;
+    if (masks_out) masks_out[o] = masks_in[o] * (in ? 1.0f : 0.0f);
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -171,6 +207,21 @@ int rp_mask_prob(const float* embed_pixel, const float* embed_center, const floa
   RP_CUDA_TRY(cudaMemsetAsync(probs, 0, sizeof(float) * (size_t)num_pixel * num_center, st));  // :60
   mask_prob_kernel<<<dim3(32, (unsigned)num_center), 256, 0, st>>>(
       embed_pixel, embed_center, sigma_center, boxes, box_areas, num_pixel, mask_width, dim, probs);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_box_masks(const float* boxes, int n, int h, int w, float padding, int crop,
+                 const float* masks_in, float* masks_out, uint8_t* indicator, void* stream) {
+  if (n == 0) return RP_OK;
+  if (!boxes || n < 0 || h < 1 || w < 1 || n > 65535) return RP_E_ARG;
+  if (!indicator && !masks_out) return RP_E_ARG;
+  if (masks_out && !masks_in) return RP_E_ARG;
+  const size_t plane = (size_t)h * w;
+  unsigned gx = (unsigned)((plane + 255) / 256);
+  if (gx > 4096) gx = 4096;
+  box_mask_kernel<<<dim3(gx, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(boxes, h, w, padding, crop ? 1 : 0,
+                                                                         masks_in, masks_out, indicator);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

@@ -201,6 +201,33 @@ def boxlist_iou(boxlist1, boxlist2):
     return out
 
 
+def _box_masks(boxes, h, w, padding, crop, masks=None):
+    boxes = _lib.as_f32(boxes, "boxes")
+    n = int(boxes.shape[0])
+    dev = boxes.device
+    ind = torch.empty((n, int(h), int(w)), dtype=torch.uint8, device=dev)
+    out = None
+    if masks is not None:
+        masks = _lib.as_f32(masks, "masks")
+        out = torch.empty_like(masks)
+    rc = _lib.lib().rp_box_masks(_lib.dptr(boxes), n, int(h), int(w), float(padding), int(crop),
+                                 _lib.dptr(masks), _lib.dptr(out), _lib.dptr(ind),
+                                 _lib.stream_ptr(dev))
+    _lib.check(rc, "rp_box_masks")
+    return out, ind.bool()
+
+
+def boxes_to_masks(boxes, h, w, padding=0.0):
+    """boxlist_ops.py:237-261: [n,h,w] bool indicator of every box grown by 1 px + padding * size."""
+    return _box_masks(boxes, h, w, padding, 0)[1]
+
+
+def crop_by_box(masks, box, padding=0.0):
+    """boxlist_ops.py:262-281: (masks * indicator, indicator)."""
+    n, h, w = masks.shape
+    return _box_masks(box, h, w, padding, 1, masks)
+
+
 def cat_boxlist(bboxes):
     """boxlist_ops.py:127-152."""
     assert isinstance(bboxes, (list, tuple)) and len(bboxes) > 0

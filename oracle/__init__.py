@@ -328,6 +328,21 @@ def mask_prob(embed_pixel, embed_center, sigma_center, boxes, box_areas, mask_wi
     return out
 
 
+def box_masks(boxes, h, w, padding=0.0, crop=False, masks=None):
+    boxes, bp = _f(boxes)
+    n = boxes.shape[0]
+    ind = np.zeros((n, h, w), np.uint8)
+    mi = mo = None
+    mip = mop = None
+    if masks is not None:
+        mi, mip = _f(masks)
+        mo = np.zeros_like(mi)
+        mop = mo.ctypes.data_as(_f32p)
+    lib().orc_box_masks(bp, n, int(h), int(w), ctypes.c_float(padding), int(bool(crop)), mip, mop,
+                        ind.ctypes.data_as(_u8p))
+    return mo, ind
+
+
 # --------------------------------------------------------------------------- Yolact
 def yolact_decode(loc, priors):
     loc, lp = _f(loc)

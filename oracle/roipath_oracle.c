@@ -1097,6 +1097,35 @@ ORC_API void orc_mask_prob(const float* ep, const float* ec, const float* sigma,
   }
 }
 
+/* det/structures/boxlist_ops.py:237-261 boxes_to_masks (crop = 0) and :262-281 crop_by_box
+ * (crop = 1), in the written operand order; indicator [n,h,w] uint8, masks_out = masks_in * ind. */
+ORC_API void orc_box_masks(const float* boxes, int n, int h, int w, float padding, int crop,
+                           const float* masks_in, float* masks_out, uint8_t* ind) {
+  for (int i = 0; i < n; ++i) {
+    const float* b = boxes + (size_t)i * 4;
+    const float bw = b[2] - b[0], bh = b[3] - b[1];
+    float x1, x2, y1, y2;
+    if (crop) {
+      x1 = fmaxf(b[0] - bw * padding - 1.0f, 0.0f);
+      x2 = fminf(b[2] + bw * padding + 1.0f, (float)(w - 1));
+      y1 = fmaxf(b[1] - bh * padding - 1.0f, 0.0f);
+      y2 = fminf(b[3] + bh * padding + 1.0f, (float)(h - 1));
+    } else {
+      x1 = fmaxf(b[0] - 1.0f - bw * padding, 0.0f);
+      x2 = fminf(b[2] + 1.0f + bw * padding, (float)w);
+      y1 = fmaxf(b[1] - 1.0f - bh * padding, 0.0f);
+      y2 = fminf(b[3] + 1.0f + bh * padding, (float)h);
+    }
+    for (int r = 0; r < h; ++r)
+      for (int c = 0; c < w; ++c) {
+        const size_t o = ((size_t)i * h + r) * w + c;
+        const int in = ((float)c >= x1) && ((float)c < x2) && ((float)r >= y1) && ((float)r < y2);
+        if (ind) ind[o] = (uint8_t)in;
+        if (masks_out) masks_out[o] = masks_in[o] * (in ? 1.0f : 0.0f);
+      }
+  }
+}
+
 /* ------------------------------------------------------------------------- */
 /* helpers exported for tests                                                 */
 /* ------------------------------------------------------------------------- */

@@ -28,7 +28,7 @@ def test_header_declares_the_whole_path():
                  "rp_box_decode", "rp_rpn_pre_nms", "rp_rpn_pre_nms_workspace_bytes",
                  "rp_rpn_pre_nms_levels", "rp_rpn_select_levels", "rp_box_post",
                  "rp_yolact_prefilter", "rp_boxlist_iou", "rp_roi_pool_forward", "rp_roi_pool_backward",
-                 "rp_mask_prob"):
+                 "rp_mask_prob", "rp_box_masks"):
         assert must in names
 
 
@@ -81,6 +81,7 @@ def test_argument_errors_need_no_gpu():
     assert L.rp_yolact_prefilter_workspace_bytes(64, 19248, 65536) >= 64 * 19248 + 4 * 65536
     assert L.rp_yolact_prefilter(None, None, None, None, 64, 19248, 81, 32, 0.05, 65536, None, None,
                                  None, None, None, None, None, 0, None) == -1
+    assert L.rp_box_masks(None, 3, 10, 10, 0.0, 0, None, None, None, None) == -1
     assert L.rp_boxlist_iou(None, 5, None, 5, None, None) == -1
     assert L.rp_boxlist_iou(None, 0, None, 5, None, None) == 0
     assert L.rp_roi_pool_forward(None, 1, 1, 4, 4, None, 3, 7, 7, 1.0, None, None, None) == -1

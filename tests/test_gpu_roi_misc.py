@@ -54,3 +54,28 @@ def test_mask_prob_matches_oracle(n_center, h, w, dim):
     got = rp.mask_prob_cuda(T(ep), T(ec), T(sg), T(bx), T(ar), int(ar.sum()), mw)
     np.testing.assert_array_equal(got.cpu().numpy(), oracle.mask_prob(ep, ec, sg, bx, ar, mw))
     assert rp.mask_prob_cuda(T(ep), T(ec[:0]), T(sg[:0]), T(bx[:0]), T(ar[:0]), 0, mw).numel() == 0
+
+
+@pytest.mark.parametrize("h,w,padding", [(100, 136, 0.0), (37, 53, 0.1), (8, 8, 0.5)])
+def test_box_masks_match_oracle(h, w, padding):
+    rng = np.random.default_rng(h)
+    n = 9
+    x1 = rng.uniform(-5, w - 2, n); y1 = rng.uniform(-5, h - 2, n)
+    boxes = np.stack([x1, y1, x1 + rng.uniform(0, w, n), y1 + rng.uniform(0, h, n)], 1).astype(np.float32)
+    boxes[0] = (3.0, 2.0, 3.0, 2.0)
+    got = rp.boxes_to_masks(T(boxes), h, w, padding)
+    assert got.dtype == torch.bool
+    np.testing.assert_array_equal(got.cpu().numpy().astype(np.uint8), oracle.box_masks(boxes, h, w, padding)[1])
+    masks = rng.uniform(0, 1, (n, h, w)).astype(np.float32)
+    out, crop = rp.crop_by_box(T(masks), T(boxes), padding)
+    o_ref, c_ref = oracle.box_masks(boxes, h, w, padding, crop=True, masks=masks)
+    np.testing.assert_array_equal(crop.cpu().numpy().astype(np.uint8), c_ref)
+    np.testing.assert_array_equal(out.cpu().numpy(), o_ref)
+    # the numpy form of boxlist_ops.py:237-261
+    b = boxes
+    bw, bh = b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]
+    X1 = np.clip(b[:, 0] - 1 - bw * np.float32(padding), 0, None); X2 = np.clip(b[:, 2] + 1 + bw * np.float32(padding), None, w)
+    Y1 = np.clip(b[:, 1] - 1 - bh * np.float32(padding), 0, None); Y2 = np.clip(b[:, 3] + 1 + bh * np.float32(padding), None, h)
+    cols = np.arange(w, dtype=np.float32)[None, None, :]; rows = np.arange(h, dtype=np.float32)[None, :, None]
+    ref = (cols >= X1[:, None, None]) & (cols < X2[:, None, None]) & (rows >= Y1[:, None, None]) & (rows < Y2[:, None, None])
+    np.testing.assert_array_equal(got.cpu().numpy(), ref)
