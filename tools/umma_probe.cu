@@ -1,0 +1,242 @@
+// Probe of the sm_100a building blocks the tensor-core Pooler forward uses (one process, three tests):
+//   1. tcgen05.mma kind::tf32, M=128 N=16, A and B K-major SWIZZLE_128B in shared memory, 3xTF32 split
+//      (hi*hi + lo*hi + hi*lo), accumulator in TMEM, read back with tcgen05.ld 32x32b.x16
+//   2. the same with a raw (unsplit) A: tells whether the tensor core truncates or rounds fp32 -> tf32
+//   3. TMA tensor load with PERMUTED dimensions (x, plane, y): a box (KP, 8 planes, RB rows) lands as
+//      [row][plane][x] in shared memory
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o umma_probe tools/umma_probe.cu
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define CK(x)                                                                  \
+  do {                                                                         \
+    cudaError_t e_ = (x);                                                      \
+    if (e_ != cudaSuccess) {                                                   \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return 1;                                                                \
+    }                                                                          \
+  } while (0)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ bool mbar_wait_bounded(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done && spin < (1u << 22); ++spin)
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
+
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);  // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                   // LBO (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;         // SBO: 8 rows x 128 bytes
+  d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
+  return d;
+}
+
+// byte offset of (row, k-float) inside a K-major SWIZZLE_128B tile with 32 floats per row
+__device__ __forceinline__ uint32_t sw128_off(int row, int k) {
+  return (uint32_t)(row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2)));
+}
+
+// mode 0: 3xTF32 split; mode 1: raw A and raw B in one MMA per k-step
+__global__ void __launch_bounds__(128) umma_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                  float* __restrict__ D, int K, int mode, int* status) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  unsigned char* a_hi = smem;            // 128 x 128 B
+  unsigned char* a_lo = smem + 16384;
+  unsigned char* b_hi = smem + 32768;    // 16 x 128 B
+  unsigned char* b_lo = smem + 32768 + 2048;
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 32;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // operands -> swizzled shared memory
+  for (int i = tid; i < 128 * 32; i += 128) {
+    const int r = i >> 5, k = i & 31;
+    float v = k < K ? A[r * K + k] : 0.f;
+    float hi = mode == 0 ? __uint_as_float(__float_as_uint(v) & 0xFFFFE000u) : v;
+    float lo = v - hi;
+    *reinterpret_cast<float*>(a_hi + sw128_off(r, k)) = hi;
+    *reinterpret_cast<float*>(a_lo + sw128_off(r, k)) = lo;
+  }
+  for (int i = tid; i < 16 * 32; i += 128) {
+    const int r = i >> 5, k = i & 31;
+    float v = k < K ? B[r * K + k] : 0.f;
+    float hi = mode == 0 ? __uint_as_float(__float_as_uint(v) & 0xFFFFE000u) : v;
+    float lo = v - hi;
+    *reinterpret_cast<float*>(b_hi + sw128_off(r, k)) = hi;
+    *reinterpret_cast<float*>(b_lo + sw128_off(r, k)) = lo;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_base_s;
+
+  if (tid == 0) {
+    // idesc: D fp32 (1<<4), A tf32 (2<<7), B tf32 (2<<10), K-major both, N>>3 at 17, M>>4 at 24
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+    const uint64_t dah = make_desc_sw128(smem_u32(a_hi)), dal = make_desc_sw128(smem_u32(a_lo));
+    const uint64_t dbh = make_desc_sw128(smem_u32(b_hi)), dbl = make_desc_sw128(smem_u32(b_lo));
+    uint32_t acc = 0;
+    for (int ks = 0; ks < K / 8; ++ks) {
+      const uint64_t adv = (uint64_t)(ks * 2);  // 32 bytes per k-step, 16-byte units
+#define MMA(DA, DB)                                                                              \
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"                                      \
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem),     \
+               "l"((DA) + adv), "l"((DB) + adv), "r"(idesc), "r"(acc)                           \
+               : "memory");                                                                     \
+  acc = 1;
+      MMA(dah, dbh)
+      if (mode == 0) {
+        MMA(dal, dbh)
+        MMA(dah, dbl)
+      }
+#undef MMA
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+  }
+  const bool ok = mbar_wait_bounded(smem_u32(&bar), 0);
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (!ok) {
+    if (tid == 0) *status = 1;
+  } else {
+    uint32_t r[16];
+    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    const int row = warp * 32 + lane;
+    for (int j = 0; j < 16; ++j) D[row * 16 + j] = __uint_as_float(r[j]);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" ::"r"(tmem) : "memory");
+}
+
+// ---- TMA with permuted dimensions ----------------------------------------------------------------
+typedef CUresult (*enc_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                           const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                           CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+__global__ void tma_kernel(const CUtensorMap* __restrict__ tm, int bytes, int x, int p, int y, float* out, int n) {
+  __shared__ __align__(1024) unsigned char base[32768];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t bar_s = smem_u32(&bar);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(smem_u32(base)), "l"(tm), "r"(x), "r"(p), "r"(y), "r"(bar_s) : "memory");
+  }
+  const bool ok = mbar_wait_bounded(bar_s, 0);
+  __syncthreads();
+  const float* f = (const float*)base;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = ok ? f[i] : -12345.f;
+}
+
+static float tf32_trunc(float v) { uint32_t u; memcpy(&u, &v, 4); u &= 0xFFFFE000u; memcpy(&v, &u, 4); return v; }
+static float tf32_round(float v) { uint32_t u; memcpy(&u, &v, 4); u += 0x1000u; u &= 0xFFFFE000u; memcpy(&v, &u, 4); return v; }
+
+int main() {
+  int rc = 0;
+  // ---------------- tests 1 and 2: UMMA ----------------
+  for (int K = 32; K >= 16; K -= 8) {
+    float *hA = (float*)malloc(128 * K * 4), *hB = (float*)malloc(16 * K * 4), *hD = (float*)malloc(128 * 16 * 4);
+    srand(7 + K);
+    for (int i = 0; i < 128 * K; ++i) hA[i] = (float)rand() / RAND_MAX * 4.f - 2.f;
+    for (int i = 0; i < 16 * K; ++i) hB[i] = (float)rand() / RAND_MAX;
+    float *dA, *dB, *dD; int* dS;
+    CK(cudaMalloc(&dA, 128 * K * 4)); CK(cudaMalloc(&dB, 16 * K * 4)); CK(cudaMalloc(&dD, 128 * 16 * 4)); CK(cudaMalloc(&dS, 4));
+    CK(cudaMemcpy(dA, hA, 128 * K * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dB, hB, 16 * K * 4, cudaMemcpyHostToDevice));
+    const int smem = 32768 + 4096 + 1024;
+    CK(cudaFuncSetAttribute(umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    for (int mode = 0; mode < 2; ++mode) {
+      CK(cudaMemset(dD, 0xff, 128 * 16 * 4)); CK(cudaMemset(dS, 0, 4));
+      umma_kernel<<<1, 128, smem>>>(dA, dB, dD, K, mode, dS);
+      CK(cudaDeviceSynchronize());
+      int st; CK(cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(hD, dD, 128 * 16 * 4, cudaMemcpyDeviceToHost));
+      double e_exact = 0, e_trunc = 0, e_round = 0, mag = 0;
+      for (int r = 0; r < 128; ++r)
+        for (int n = 0; n < 16; ++n) {
+          double ex = 0, tr = 0, ro = 0;
+          for (int k = 0; k < K; ++k) {
+            ex += (double)hA[r * K + k] * hB[n * K + k];
+            tr += (double)tf32_trunc(hA[r * K + k]) * tf32_trunc(hB[n * K + k]);
+            ro += (double)tf32_round(hA[r * K + k]) * tf32_round(hB[n * K + k]);
+          }
+          const double g = hD[r * 16 + n];
+          e_exact = fmax(e_exact, fabs(g - ex)); e_trunc = fmax(e_trunc, fabs(g - tr)); e_round = fmax(e_round, fabs(g - ro));
+          mag = fmax(mag, fabs(ex));
+        }
+      printf("UMMA K=%d mode=%d status=%d: max|err| vs exact %.3e, vs trunc-model %.3e, vs round-model %.3e (|ref|max %.2f) D[0..3]=%g %g %g %g\n",
+             K, mode, st, e_exact, e_trunc, e_round, mag, hD[0], hD[1], hD[2], hD[3]);
+      if (mode == 0 && !(e_exact < 2e-5 * mag)) { printf("  FAIL: 3xTF32 not within 2e-5\n"); rc = 2; }
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dS); free(hA); free(hB); free(hD);
+  }
+  // ---------------- test 3: TMA (x, plane, y) ----------------
+  {
+    const int W = 84, H = 50, P = 32;
+    float* h = (float*)malloc(sizeof(float) * W * H * P);
+    for (int i = 0; i < W * H * P; ++i) h[i] = (float)i;
+    float *d, *o; CK(cudaMalloc(&d, sizeof(float) * W * H * P)); CK(cudaMalloc(&o, 32768));
+    CK(cudaMemcpy(d, h, sizeof(float) * W * H * P, cudaMemcpyHostToDevice));
+    void* pf = nullptr; cudaDriverEntryPointQueryResult q;
+    CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &pf, cudaEnableDefault, &q));
+    enc_fn enc = (enc_fn)pf;
+    const int KP = 24, RB = 4, X = 64, PL = 8, Y = 48;  // x box runs past W (84): columns 84..87 must read 0; rows 50, 51 too
+    CUtensorMap m; memset(&m, 0, sizeof(m));
+    cuuint64_t gd[3] = {W, P, H}; cuuint64_t gs[2] = {(cuuint64_t)W * H * 4, (cuuint64_t)W * 4};
+    cuuint32_t box[3] = {KP, 8, RB}; cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, d, gd, gs, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    printf("TMA permuted encode -> %d\n", (int)r);
+    if (r == CUDA_SUCCESS) {
+      CUtensorMap* dm; CK(cudaMalloc(&dm, sizeof(m))); CK(cudaMemcpy(dm, &m, sizeof(m), cudaMemcpyHostToDevice));
+      const int n = KP * 8 * RB;
+      tma_kernel<<<1, 128>>>(dm, n * 4, X, PL, Y, o, n);
+      CK(cudaDeviceSynchronize());
+      float* res = (float*)malloc(n * 4); CK(cudaMemcpy(res, o, n * 4, cudaMemcpyDeviceToHost));
+      int bad = 0;
+      for (int y = 0; y < RB; ++y) for (int c = 0; c < 8; ++c) for (int x = 0; x < KP; ++x) {
+        const int gx = X + x, gy = Y + y, gp = PL + c;
+        const float exp = (gx < W && gy < H) ? (float)((gp * H + gy) * W + gx) : 0.f;
+        const float got = res[(y * 8 + c) * KP + x];
+        if (got != exp) { if (bad < 5) printf("  mismatch y%d c%d x%d: got %g expect %g\n", y, c, x, got, exp); ++bad; }
+      }
+      printf("TMA permuted (x,plane,y) box lands [y][plane][x], OOB zero: %s (%d mismatches)\n", bad ? "FAIL" : "PASS", bad);
+      if (bad) rc = 3;
+    } else rc = 3;
+  }
+  printf(rc ? "PROBE FAIL %d\n" : "PROBE PASS\n", rc);
+  return rc;
+}
