@@ -45,6 +45,11 @@ extern "C" {
 RP_API int rp_version(void);
 /* Compute capability the kernels were compiled for (100 for sm_100a). */
 RP_API int rp_built_for_sm(void);
+/* Diagnostic.  The warp-specialised Pooler forward never waits unboundedly: a barrier that does not
+ * complete makes the kernel trap (a CUDA error, not a hang).  With RP_RX_DEBUG=1 in the environment
+ * every warp records {1, block, wait code, parity, counter} in a host-mapped buffer before the trap;
+ * this copies the first n ints (8 per warp, 16 warps) to out and returns 1, or 0 when nothing was set up. */
+RP_API int rp_debug_rx_timeouts(int* out, int n);
 
 /* ------------------------------------------------------------------------------------
  * ROIAlign (legacy / non-aligned), forward and backward.
@@ -279,7 +284,9 @@ RP_API int rp_rpn_select_levels(const float* boxes, const float* scores, const i
  *   out_boxes [N*out_cap,4], out_scores, out_labels (int32 class), out_rows (int32 proposal
  *   row relative to row_offsets[b]; may be NULL), class-major, descending score inside a
  *   class; out_count[b] is the full count (it can exceed detections_per_img on ties).
- * Limits: nms_thresh > 0; N*(C-1) <= 65535.
+ * nms_thresh <= 0 skips NMS (boxlist_nms returns its input, boxlist_ops.py:24-25): every candidate
+ * is kept in nonzero() order; the score threshold and the detections_per_img cut still apply.
+ * Limits: N*(C-1) <= 65535.
  * ------------------------------------------------------------------------------------ */
 RP_API size_t rp_box_post_workspace_bytes(int R, int C, int N, int r_max, int cand_cap);
 

@@ -24,6 +24,7 @@ _vp, _i, _f, _d, _sz = _c.c_void_p, _c.c_int, _c.c_float, _c.c_double, _c.c_size
 SIGNATURES = {
     "rp_version": (_i, []),
     "rp_built_for_sm": (_i, []),
+    "rp_debug_rx_timeouts": (_i, [_vp, _i]),
     "rp_roi_align_forward": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _f, _f, _vp, _i, _vp]),
     "rp_roi_align_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _vp]),
     "rp_level_map": (_i, [_vp, _i, _i, _i, _f, _i, _f, _vp, _vp]),
@@ -92,6 +93,8 @@ def lib():
         fn.argtypes = args
     if L.rp_version() != 1:
         raise RoiPathError("libroipath_b200.so ABI version mismatch")
+    if L.rp_built_for_sm() != 100:
+        raise RoiPathError("libroipath_b200.so was not built for sm_100a (built for sm_%d)" % L.rp_built_for_sm())
     _lib = L
     return _lib
 
@@ -139,10 +142,17 @@ _ws_cache = {}
 
 
 def workspace(nbytes, device, tag="default"):
-    """A per-(device, tag) scratch buffer that only grows; reused across calls on a stream."""
-    key = (str(device), tag)
+    """A scratch buffer per (device index, tag, current stream) that only grows.  Keyed on the
+    stream so that two streams never share keys / bit words; a buffer that is replaced by a
+    larger one is handed back to the allocator only after the work queued on its stream."""
+    dev = torch.device(device)
+    index = dev.index if dev.index is not None else torch.cuda.current_device()
+    stream = torch.cuda.current_stream(index)
+    key = (index, tag, stream.cuda_stream)
     buf = _ws_cache.get(key)
     if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        if buf is not None:
+            buf.record_stream(stream)
+        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=torch.device("cuda", index))
         _ws_cache[key] = buf
     return buf

@@ -291,6 +291,17 @@ struct BpWorkspace {
   size_t nms_bytes, total;
 };
 
+// nms_thresh <= 0: boxlist_nms returns its input unchanged (boxlist_ops.py:24-25), i.e. every
+// candidate of the segment is kept in candidate (= nonzero()) order.
+__global__ void bp_identity_keep_kernel(const int* __restrict__ seg_off, int S, int* __restrict__ keep,
+                                        int* __restrict__ n_keep) {
+  const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (s >= S) return;
+  const int o = seg_off[s], n = seg_off[s + 1] - o;
+  for (int i = lane; i < n; i += 32) keep[o + i] = i;
+  if (lane == 0) n_keep[s] = n;
+}
+
 BpWorkspace bp_carve(void* base, int R, int C, int N, int r_max, int cand_cap, bool need_prob) {
   BpWorkspace w;
   size_t off = 0;
@@ -331,7 +342,7 @@ int rp_box_post(const float* class_logits, const float* box_regression, const fl
                 float* out_scores, int* out_labels, int* out_rows, int* out_count, int out_cap,
                 int* n_cand, void* workspace, size_t workspace_bytes, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  if (R < 1 || C < 2 || N < 1 || r_max < 1 || cand_cap < 1 || out_cap < 1 || !(nms_thresh > 0))
+  if (R < 1 || C < 2 || N < 1 || r_max < 1 || cand_cap < 1 || out_cap < 1 || nms_thresh != nms_thresh)
     return RP_E_ARG;
   if (!class_logits || !box_regression || !proposals || !row_offsets || !im_wh || !out_boxes ||
       !out_scores || !out_labels || !out_count || !n_cand || !workspace)
@@ -358,9 +369,14 @@ int rp_box_post(const float* class_logits, const float* box_regression, const fl
       w.cand_scores, w.cand_row);
   RP_LAUNCH_CHECK();
   const int n_max = r_max < cand_cap ? r_max : cand_cap;
-  const int rc = rp_nms_batched(w.cand_boxes, w.cand_scores, nullptr, w.seg_off, S, cand_cap, n_max,
-                                nms_thresh, -1, 0, w.keep, w.n_keep, w.nms, w.nms_bytes, stream);
-  if (rc) return rc;
+  if (nms_thresh > 0) {
+    const int rc = rp_nms_batched(w.cand_boxes, w.cand_scores, nullptr, w.seg_off, S, cand_cap, n_max,
+                                  nms_thresh, -1, 0, w.keep, w.n_keep, w.nms, w.nms_bytes, stream);
+    if (rc) return rc;
+  } else {
+    bp_identity_keep_kernel<<<(S + wpb - 1) / wpb, BP_THREADS, 0, st>>>(w.seg_off, S, w.keep, w.n_keep);
+    RP_LAUNCH_CHECK();
+  }
   bp_finish_kernel<<<N, BP_THREADS, (size_t)C * sizeof(int), st>>>(
       w.cand_boxes, w.cand_scores, w.cand_row, w.seg_off, w.keep, w.n_keep, C, detections_per_img,
       out_cap, out_boxes, out_scores, out_labels, out_rows, out_count);

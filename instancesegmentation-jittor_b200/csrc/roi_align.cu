@@ -25,6 +25,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "roi_levels.h"
 #include "roi_tile.h"
 
 namespace {
@@ -36,15 +37,6 @@ constexpr int RT_THREADS = 256;
 constexpr int RT_U1 = 4;  // channels per thread, phase 1
 constexpr int RT_U2 = 2;  // channels per thread, phase 2
 constexpr int RT_CC_CAP = 32;  // max channels per chunk (bounds the out tile)
-
-struct RtLevels {
-  const float* feat[RP_MAX_LEVELS];
-  float* grad[RP_MAX_LEVELS];
-  int H[RP_MAX_LEVELS];
-  int W[RP_MAX_LEVELS];
-  float scale[RP_MAX_LEVELS];
-  int L;
-};
 
 __device__ __forceinline__ void rt_zero_fill(float* dst, size_t n) {
   for (size_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = 0.f;
@@ -1579,6 +1571,11 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     return RP_OK;
   }
   if (mode != 0) return RP_E_ARG;
+  if (rp_env_int("RP_ROI_IMPL", RP_ROI_IMPL_DEFAULT) == 6) {
+    // tensor-core kernel (roi_fwd_tc.cu); 1 = configuration not eligible, use the SIMT kernels
+    const int rc = rx_forward(lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
+    if (rc != 1) return rc;
+  }
   const RtLaunch l = rt_plan_launch(K, C, PH, PW);
   if (rp_env_int("RP_ROI_IMPL", RP_ROI_IMPL_DEFAULT) == 5 && sampling_ratio > 0 &&
       (int)sampling_ratio <= RB_MAXG && PH <= RB_MAXP && PW <= RB_MAXP) {

@@ -1,0 +1,765 @@
+// roi_fwd_tc.cu -- ROIAlign / Pooler forward on the sm_100a tensor cores ("rx" kernel).
+//
+// Reference being replaced: det/layers/roi_align.py:116-169 (RoIAlignForward, one thread per output,
+// 16 scalar gathers) behind det/modeling/poolers.py:123-156.
+//
+// The separable form  out[c,ph,pw] = 1/(gh*gw) * sum_y sum_x Ay[ph,y] * Ax[pw,x] * F[c,y,x]
+// (roi_tile.h) is evaluated as
+//   y-pass (SIMT)   V[(c,ph)][x] = sum_y Ay[ph,y] * F[c,y,x]      4-row bands, one 16-byte strip per thread
+//   x-pass (tcgen05) D[(c,ph)][pw] = sum_x V[(c,ph)][x] * Ax'[pw,x]  M=128 (8 channels x 16 bins), N=16, K<=64
+// with the x-pass in 3xTF32 (V_hi*Ax_hi + V_lo*Ax_hi + V_hi*Ax_lo; the tensor core truncates fp32 to
+// tf32, measured with tools/umma_probe.cu), fp32 accumulation in TMEM: ~3e-7 relative error.
+//
+// One persistent CTA per SM, 16 warps with fixed roles, everything connected by mbarriers:
+//   warp 0      TMA producer: per sub-chunk (<= 8 channels x R rows x <= 32 columns of the RoI's tile)
+//               a few cp.async.bulk.tensor boxes; the tensor maps are (x, plane, y) so that a box lands
+//               [row][channel][x]: the 16-byte strips of one row of all channels are one contiguous,
+//               conflict-free run for the y-pass
+//   warp 1      MMA issuer (one lane): per V tile 3 MMAs per 8 columns, tcgen05.commit frees the V slot
+//               and publishes the accumulator
+//   warp 2      planner: per RoI the y band plan (4 merged weights per bin, rotated to the register
+//               ring) and the dense x-weight matrix Ax' (hi / lo, K-major SWIZZLE_128B, 1/(gh*gw) folded in)
+//   warps 4-7   epilogue: tcgen05.ld (one accumulator row = 16 pw per lane) -> packed [c][ph][pw] rows in
+//               shared memory -> one cp.async.bulk store of 8 channels x PH x PW floats (contiguous in out)
+//   warps 8-15  y-pass: thread = strip; ring of 4 rows; every finished bin is split into tf32 hi / lo
+//               and stored as the K-major SWIZZLE_128B A operand
+// The input tile never passes through the LSU on its way in (TMA), the x-pass and the V read-back are
+// gone from the LSU / FMA pipes, and the output leaves through the bulk-copy engine.
+// RoIs without a band form, wider than 64 columns or taller than the tile slot are evaluated in the
+// reference's operand order by the epilogue warps (same CTA, same launch).
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "roi_levels.h"
+#include "roi_tile.h"
+
+namespace {
+
+constexpr int RX_THREADS = 512;
+constexpr int RX_W_TMA = 0, RX_W_MMA = 1, RX_W_PLAN = 2, RX_W_FREE = 3, RX_W_EPI0 = 4, RX_W_Y0 = 8;
+constexpr int RX_NY = 8;               // y-pass warps
+constexpr int RX_S = 5;                // tile slots
+constexpr int RX_SLOT = 16384;         // bytes per tile slot
+constexpr int RX_SV = 3;               // V slots (hi + lo, 32 KB each)
+constexpr int RX_SD = 4;               // accumulator tiles in TMEM (16 columns each)
+constexpr int RX_NP = 2;               // plans in flight
+constexpr int RX_CS = 128;             // channels per work item (RoI x channel slice)
+constexpr int RX_RMAX = 64;            // tile rows
+constexpr int RX_OSTAGE = 8 * 16 * 16 * 4;  // out stage: 8 channels x <= 16x16 floats
+constexpr int RX_NMAP = 36;            // tensor maps per level: 4 widths x 3 row counts x 3 channel counts
+constexpr int RX_PLAN_ARRIVALS = 1 + RX_NY + 1 + 4 + 1;
+
+struct RxMeta {
+  int kind;  // 0 tensor-core path, 1 reference-order fallback, 2 zero fill
+  int level, R, nq, nkh, cs, y0, x0a, plane0, nmt;
+  int H, W, nch;
+  float* out;          // &out[(k*C + c_begin) * P]
+  const float* featb;  // &feat[level][(b*C + c_begin) * H*W]
+  RtGeom g;
+  RbF4 wrot[16];
+  uint32_t mw[RX_RMAX / 4 + 2];
+};
+
+constexpr int RX_MAXL = 5;  // levels with tensor maps (kernel parameter space: 23 KB)
+struct RxMaps {
+  CUtensorMap m[RX_MAXL][RX_NMAP];
+};
+
+struct RxBars {
+  uint64_t plan_full[RX_NP], plan_empty[RX_NP];
+  uint64_t tile_full[RX_S], tile_empty[RX_S];
+  uint64_t v_full[RX_SV], v_empty[RX_SV];
+  uint64_t d_full[RX_SD], d_empty[RX_SD];
+  // software sequence numbers for the hand-offs that several warps wait on out of order (an mbarrier
+  // parity cannot tell phase k from phase k + 2): sub-chunks issued by the TMA warp, V tiles whose
+  // MMAs have completed
+  uint32_t issued, v_freed;
+};
+
+// shared-memory layout (offsets from a 1024-byte aligned base)
+constexpr int RX_OFF_V = 0;
+constexpr int RX_OFF_B = RX_OFF_V + RX_SV * 32768;
+constexpr int RX_OFF_TILE = RX_OFF_B + RX_NP * 8192;
+constexpr int RX_OFF_OST = RX_OFF_TILE + RX_S * RX_SLOT;
+constexpr int RX_OFF_META = RX_OFF_OST + 2 * RX_OSTAGE;
+constexpr int RX_OFF_AY = RX_OFF_META + RX_NP * 1024;
+constexpr int RX_OFF_BARS = RX_OFF_AY + 1024;
+constexpr int RX_SMEM = RX_OFF_BARS + 512 + 1024;  // + alignment slack
+static_assert(sizeof(RxMeta) <= 1024, "RxMeta");
+static_assert(sizeof(RbAxis) <= 1024, "RbAxis");
+static_assert(sizeof(RxBars) <= 512, "RxBars");
+static_assert(RX_SMEM <= 227 * 1024, "shared memory");
+
+// Bounded wait.  On a timeout the warp records (block, code, parity, counter) in the host-mapped
+// diagnostic buffer (when one was passed), gives the other warps time to record theirs, and traps:
+// a kernel that cannot make progress fails loudly instead of hanging the GPU.
+__device__ int* rx_dbg = nullptr;
+__device__ __noinline__ void rx_timeout(uint32_t code, uint32_t parity, uint32_t counter) {
+  int* d = rx_dbg;
+  if (d) {
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) {
+      d[8 * w + 1] = (int)blockIdx.x;
+      d[8 * w + 2] = (int)code;
+      d[8 * w + 3] = (int)parity;
+      d[8 * w + 4] = (int)counter;
+      d[8 * w + 0] = 1;
+      __threadfence_system();
+    }
+    for (int i = 0; i < 2000; ++i) __nanosleep(100000);
+  }
+  __trap();
+}
+__device__ __forceinline__ void rx_wait(uint64_t* bar, uint32_t parity, uint32_t code = 0, uint32_t counter = 0) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(rp_smem_addr(bar)), "r"(parity)
+        : "memory");
+    if (spin > (1u << 20)) rx_timeout(code, parity, counter);
+  }
+}
+__device__ __forceinline__ void rx_publish(uint32_t* ctr, uint32_t v) {
+  asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(rp_smem_addr(ctr)), "r"(v) : "memory");
+}
+// wait until *ctr >= target (sequence numbers: compared modulo 2^32)
+__device__ __forceinline__ void rx_wait_ge(uint32_t* ctr, uint32_t target, uint32_t code, uint32_t counter) {
+  for (uint32_t spin = 0;; ++spin) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(rp_smem_addr(ctr)) : "memory");
+    if ((int32_t)(v - target) >= 0) return;
+    if (spin > (1u << 22)) rx_timeout(code, target, counter);
+  }
+}
+__device__ __forceinline__ void rx_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rp_smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void rx_arrive_n(uint64_t* bar, uint32_t n) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(rp_smem_addr(bar)), "r"(n) : "memory");
+}
+__device__ __forceinline__ void rx_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   rp_smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ uint64_t rx_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// byte offset of (row, k) in a K-major SWIZZLE_128B tile of 32 floats per row
+__device__ __forceinline__ uint32_t rx_sw128(int row, int k) {
+  return (uint32_t)(row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2)));
+}
+// exact floor(j / d) for j * d < 2^32, with m = rx_magic(d), d >= 2
+__device__ __forceinline__ uint32_t rx_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
+__device__ __forceinline__ float rx_tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+
+// ---- planner ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, RbAxis* ay, int lane,
+                                              const RtLevels& lv, int N, int C,
+                                              const float* __restrict__ rois,
+                                              const int* __restrict__ levels, int k, int c_begin, int PH,
+                                              int PW, float sampling_ratio, float* __restrict__ out) {
+  const int P = PH * PW;
+  const float* roi = rois + (size_t)k * 5;
+  const int level = levels ? levels[k] : 0;
+  const int b = (int)roi[0];
+  const int nch = min(RX_CS, C - c_begin);
+  int kind = 0;
+  if (level < 0 || level >= lv.L || b < 0 || b >= N) kind = 2;
+  const int lvl = kind == 2 ? 0 : level;
+  const int H = lv.H[lvl], W = lv.W[lvl];
+  RtGeom g = rt_geom_fwd(roi, lv.scale[lvl], sampling_ratio, PH, PW);
+  if (kind == 0 && !(rb_axis_candidate(g.bh, g.gh, PH, H) && g.gw >= 1 && g.gw <= RB_MAXG && W >= 4)) kind = 1;
+
+  // y axis: band plan (one bin per lane)
+  int oky = 1;
+  if (kind == 0 && lane < PH) oky = rb_build_bin(ay, lane, g.sh, g.bh, g.gh, H);
+  if (!__all_sync(0xffffffffu, oky)) kind = kind == 0 ? 1 : kind;
+  __syncwarp();
+  int R = 4;
+  if (kind == 0) {
+    int fin = 1;
+    if (lane == 0) fin = rb_finish_axis(ay, PH);
+    fin = __shfl_sync(0xffffffffu, fin, 0);
+    __syncwarp();
+    R = ay->ext;
+    if (!fin || R > RX_RMAX) kind = 1;
+  }
+  // x axis: extent of the valid taps
+  int xmin = 0x7fffffff, xmax = -1;
+  if (kind == 0 && lane < PW) {
+    for (int i = 0; i < g.gw; ++i) {
+      int lo, hi;
+      float wlo, whi;
+      if (rt_axis_tap(g.sw, g.bw, lane, i, g.gw, W, &lo, &hi, &wlo, &whi)) {
+        xmin = min(xmin, lo);
+        xmax = max(xmax, hi);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    xmin = min(xmin, __shfl_xor_sync(0xffffffffu, xmin, o));
+    xmax = max(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+  }
+  int x0a = 0, Kp = 8;
+  if (kind == 0) {
+    if (xmax < 0) {
+      kind = 2;  // no x sample inside the map: the output is zero
+    } else {
+      x0a = xmin & ~3;
+      Kp = (xmax - x0a + 1 + 7) & ~7;
+      if (Kp > 64) kind = 1;
+    }
+  }
+  int cs = 8;
+  if (kind == 0) {
+    // channels per sub-chunk: a sub-chunk is one warp's y-pass and must fit a tile slot; 8 channels
+    // only for narrow tiles (<= 4 strips: 32 items), so that wider tiles put two warps on a V tile
+    const int Re = (R + 1) & ~1, Kh = min(Kp, 32);
+    if (Kh <= 16 && Re * Kh * 8 * 4 <= RX_SLOT)
+      cs = 8;
+    else if (Re * Kh * 4 * 4 <= RX_SLOT)
+      cs = 4;
+    else if (Re * Kh * 2 * 4 <= RX_SLOT)
+      cs = 2;
+    else
+      kind = 1;
+  }
+  if (kind == 0) {
+    const int nkh = Kp > 32 ? 2 : 1;
+    // y: weights rotated to the ring (slot = tile row & 3), bins completed per tile row
+    if (lane < PH) {
+      const int rot = ay->start[lane] & 3;
+      const RbF4 w = ay->w[lane];
+      RbF4 r;
+      r.x = rot == 0 ? w.x : (rot == 1 ? w.w : (rot == 2 ? w.z : w.y));
+      r.y = rot == 0 ? w.y : (rot == 1 ? w.x : (rot == 2 ? w.w : w.z));
+      r.z = rot == 0 ? w.z : (rot == 1 ? w.y : (rot == 2 ? w.x : w.w));
+      r.w = rot == 0 ? w.w : (rot == 1 ? w.z : (rot == 2 ? w.y : w.x));
+      m->wrot[lane] = r;
+    }
+    if (lane < RX_RMAX / 4 + 2) {
+      uint32_t word = 0;
+      for (int bn = 0; bn < PH; ++bn) {
+        const int r = ay->start[bn] + 3;
+        if ((r >> 2) == lane) word += 1u << (8 * (r & 3));
+      }
+      m->mw[lane] = word;
+    }
+    // x: dense weights, accumulated in full precision in the "hi" planes, then split
+    float4* bz = reinterpret_cast<float4*>(bmat);
+    for (int i = lane; i < nkh * 4096 / 16; i += 32) {  // hi and lo planes of the used K halves
+      const int kh = i >> 8, j = i & 255;
+      bz[kh * 256 + j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncwarp();
+    if (lane < PW) {
+      for (int i = 0; i < g.gw; ++i) {
+        int lo, hi;
+        float wlo, whi;
+        if (rt_axis_tap(g.sw, g.bw, lane, i, g.gw, W, &lo, &hi, &wlo, &whi)) {
+          const int c0 = lo - x0a, c1 = hi - x0a;
+          float* p0 = reinterpret_cast<float*>(bmat + (c0 >> 5) * 4096 + rx_sw128(lane, c0 & 31));
+          *p0 += wlo;
+          float* p1 = reinterpret_cast<float*>(bmat + (c1 >> 5) * 4096 + rx_sw128(lane, c1 & 31));
+          *p1 += whi;
+        }
+      }
+    }
+    __syncwarp();
+    const float inv = 1.0f / (float)(g.gh * g.gw);
+    for (int i = lane; i < nkh * 512; i += 32) {  // 16 rows x 32 floats per half
+      const int kh = i >> 9, e = i & 511;
+      float* ph_ = reinterpret_cast<float*>(bmat + kh * 4096) + e;
+      const float v = *ph_ * inv;
+      const float hi = rx_tf32_hi(v);
+      *ph_ = hi;
+      ph_[512] = v - hi;  // lo plane: +2048 bytes
+    }
+    if (lane == 0) {
+      m->nkh = nkh;
+      m->nq = Kp >> 2;
+      m->cs = cs;
+      m->R = R;
+      m->y0 = ay->lo0;
+      m->x0a = x0a;
+    }
+  }
+  if (lane == 0) {
+    m->kind = kind;
+    m->level = lvl;
+    m->plane0 = b * C + c_begin;
+    m->nmt = nch >> 3;
+    m->nch = nch;
+    m->H = H;
+    m->W = W;
+    m->out = out + ((size_t)k * C + c_begin) * P;
+    m->featb = kind == 2 ? nullptr : lv.feat[lvl] + ((size_t)b * C + c_begin) * H * W;
+    m->g = g;
+  }
+  rp_fence_proxy_async_smem();
+  __syncwarp();
+}
+
+// ---- y-pass of one sub-chunk by one warp -----------------------------------------------------------
+// tile: [R rows][cs channels][nqh strips] RbF4; V rows (c, ph) at vbase + ((cbase + c) * 16 + ph) * 128.
+__device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, int cs, int nqh,
+                                         const uint32_t* __restrict__ mw, const RbF4* __restrict__ wrot,
+                                         unsigned char* vhi, int cbase, int lane) {
+  const int nitems = cs * nqh;
+  const uint32_t magic = rx_magic((uint32_t)nqh);
+  for (int u = lane; u < nitems; u += 32) {
+    const int c = (int)__umulhi((uint32_t)u, magic);
+    const int s = u - c * nqh;
+    const RbF4* rows = tile + u;
+    unsigned char* vrow = vhi + (size_t)((cbase + c) * 16) * 128;
+    const RbF4* wr = wrot;
+    int ph = 0;
+    RbF4 W0, W1, W2, W3;
+    W0.x = W0.y = W0.z = W0.w = 0.f;
+    W1 = W0;
+    W2 = W0;
+    W3 = W0;
+#define RX_BINS(cnt)                                                                             \
+  for (uint32_t m_ = (cnt); m_ != 0; --m_) {                                                    \
+    const RbF4 w_ = *wr++;                                                                      \
+    float4 a_;                                                                                  \
+    a_.x = fmaf(w_.w, W3.x, fmaf(w_.z, W2.x, fmaf(w_.y, W1.x, w_.x * W0.x)));                   \
+    a_.y = fmaf(w_.w, W3.y, fmaf(w_.z, W2.y, fmaf(w_.y, W1.y, w_.x * W0.y)));                   \
+    a_.z = fmaf(w_.w, W3.z, fmaf(w_.z, W2.z, fmaf(w_.y, W1.z, w_.x * W0.z)));                   \
+    a_.w = fmaf(w_.w, W3.w, fmaf(w_.z, W2.w, fmaf(w_.y, W1.w, w_.x * W0.w)));                   \
+    float4 h_;                                                                                  \
+    h_.x = rx_tf32_hi(a_.x);                                                                    \
+    h_.y = rx_tf32_hi(a_.y);                                                                    \
+    h_.z = rx_tf32_hi(a_.z);                                                                    \
+    h_.w = rx_tf32_hi(a_.w);                                                                    \
+    unsigned char* d_ = vrow + ph * 128 + ((s ^ (ph & 7)) << 4);                                \
+    *reinterpret_cast<float4*>(d_) = h_;                                                        \
+    *reinterpret_cast<float4*>(d_ + 16384) =                                                    \
+        make_float4(a_.x - h_.x, a_.y - h_.y, a_.z - h_.z, a_.w - h_.w);                        \
+    ++ph;                                                                                       \
+  }
+    for (int r = 0; r < R; r += 4) {
+      const uint32_t mword = mw[r >> 2];
+      W0 = rows[0];
+      RX_BINS(mword & 0xffu)
+      if (r + 1 < R) W1 = rows[nitems];
+      RX_BINS((mword >> 8) & 0xffu)
+      if (r + 2 < R) W2 = rows[2 * nitems];
+      RX_BINS((mword >> 16) & 0xffu)
+      if (r + 3 < R) W3 = rows[3 * nitems];
+      RX_BINS(mword >> 24)
+      rows += 4 * nitems;
+    }
+#undef RX_BINS
+  }
+}
+
+__global__ void __launch_bounds__(RX_THREADS, 1)
+rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                   const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
+                   float* __restrict__ out, const __grid_constant__ RxMaps maps, int n_items) {
+  extern __shared__ unsigned char rx_smem_raw[];
+  unsigned char* smem = rx_smem_raw + ((1024u - (rp_smem_addr(rx_smem_raw) & 1023u)) & 1023u);
+  RxBars* bars = reinterpret_cast<RxBars*>(smem + RX_OFF_BARS);
+  __shared__ uint32_t tmem_base_s;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int P = PH * PW;
+
+  if (tid == 0) {
+    for (int i = 0; i < RX_NP; ++i) {
+      rp_mbar_init(&bars->plan_full[i], 1);
+      rp_mbar_init(&bars->plan_empty[i], RX_PLAN_ARRIVALS);
+    }
+    for (int i = 0; i < RX_S; ++i) {
+      rp_mbar_init(&bars->tile_full[i], 1);
+      rp_mbar_init(&bars->tile_empty[i], 1);
+    }
+    for (int i = 0; i < RX_SV; ++i) {
+      rp_mbar_init(&bars->v_full[i], 8);
+      rp_mbar_init(&bars->v_empty[i], 1);
+    }
+    for (int i = 0; i < RX_SD; ++i) {
+      rp_mbar_init(&bars->d_full[i], 1);
+      rp_mbar_init(&bars->d_empty[i], 4);
+    }
+    bars->issued = 0;
+    bars->v_freed = 0;
+  }
+  if (warp == RX_W_MMA) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(
+                     rp_smem_addr(&tmem_base_s))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_base_s;
+
+#define RX_ITEM_LOOP for (int it = blockIdx.x, p = 0; it < n_items; it += gridDim.x, ++p)
+#define RX_META()                                                     \
+  const int ps = p % RX_NP;                                           \
+  rx_wait(&bars->plan_full[ps], (uint32_t)(p / RX_NP) & 1u, 1, p);    \
+  const RxMeta* M = reinterpret_cast<const RxMeta*>(smem + RX_OFF_META + ps * 1024);
+
+  if (warp == RX_W_PLAN) {
+    // ===== planner =====
+    RbAxis* ay = reinterpret_cast<RbAxis*>(smem + RX_OFF_AY);
+    RX_ITEM_LOOP {
+      const int ps = p % RX_NP;
+      rx_wait(&bars->plan_empty[ps], ((uint32_t)(p / RX_NP) & 1u) ^ 1u, 2, p);
+      const int sl = it / K, k = it - sl * K;
+      rx_build_plan(reinterpret_cast<RxMeta*>(smem + RX_OFF_META + ps * 1024), smem + RX_OFF_B + ps * 8192,
+                    ay, lane, lv, N, C, rois, levels, k, sl * RX_CS, PH, PW, sampling_ratio, out);
+      if (lane == 0) rx_arrive(&bars->plan_full[ps]);
+    }
+  } else if (warp == RX_W_TMA) {
+    // ===== TMA producer =====
+    uint32_t q = 0;
+    RX_ITEM_LOOP {
+      RX_META()
+      if (M->kind == 0) {
+        const int R = M->R, cs = M->cs, nkh = M->nkh, nq = M->nq, nsc = 8 / cs;
+        const int Re = (R + 1) & ~1, n8 = Re >> 3, rem = Re & 7;
+        const int nbox = n8 + ((rem & 4) ? 1 : 0) + ((rem & 2) ? 1 : 0);
+        // this lane's box: row offset and row-count index (0: 8 rows, 1: 4, 2: 2)
+        int brow = lane * 8, bri = 0;
+        if (lane >= n8) {
+          brow = n8 * 8;
+          if ((rem & 4) && lane == n8) {
+            bri = 1;
+          } else {
+            bri = 2;
+            brow += rem & 4;
+          }
+        }
+        const CUtensorMap* lmaps = maps.m[M->level];
+        for (int mt = 0; mt < M->nmt; ++mt)
+          for (int kh = 0; kh < nkh; ++kh) {
+            const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
+            const int wi = (nqh >> 1) - 1;  // box width 8, 16, 24, 32 floats
+            const CUtensorMap* tm = lmaps + (wi * 3 + bri) * 3 + (cs == 8 ? 0 : (cs == 4 ? 1 : 2));
+            const uint32_t row_bytes = (uint32_t)(cs * nqh * 16);
+            for (int sc = 0; sc < nsc; ++sc, ++q) {
+              const int ts = q % RX_S;
+              rx_wait(&bars->tile_empty[ts], ((q / RX_S) & 1u) ^ 1u, 3, q);
+              if (lane == 0) rp_mbar_arrive_expect_tx(&bars->tile_full[ts], (uint32_t)Re * row_bytes);
+              __syncwarp();
+              if (lane < nbox)
+                rp_tma_load_3d(smem + RX_OFF_TILE + ts * RX_SLOT + (uint32_t)brow * row_bytes, tm,
+                               M->x0a + 32 * kh, M->plane0 + mt * 8 + sc * cs, M->y0 + brow,
+                               &bars->tile_full[ts]);
+              __syncwarp();
+              if (lane == 0) rx_publish(&bars->issued, q + 1);
+            }
+          }
+      }
+      __syncwarp();
+      if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
+    }
+  } else if (warp == RX_W_MMA) {
+    // ===== MMA issuer =====
+    uint32_t v = 0, d = 0;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+    RX_ITEM_LOOP {
+      RX_META()
+      if (M->kind == 0) {
+        const int nkh = M->nkh, nq = M->nq;
+        const uint32_t b_s = rp_smem_addr(smem + RX_OFF_B + ps * 8192);
+        for (int mt = 0; mt < M->nmt; ++mt, ++d) {
+          const int ds = d % RX_SD;
+          rx_wait(&bars->d_empty[ds], ((d / RX_SD) & 1u) ^ 1u, 4, d);
+          for (int kh = 0; kh < nkh; ++kh, ++v) {
+            const int vs = v % RX_SV;
+            rx_wait(&bars->v_full[vs], (v / RX_SV) & 1u, 5, v);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (lane == 0) {
+              const int nks = (kh == 0 ? min(nq, 8) : nq - 8) >> 1;
+              const uint32_t a_s = rp_smem_addr(smem + RX_OFF_V + vs * 32768);
+              const uint64_t dah = rx_desc_sw128(a_s), dal = rx_desc_sw128(a_s + 16384);
+              const uint64_t dbh = rx_desc_sw128(b_s + kh * 4096), dbl = rx_desc_sw128(b_s + kh * 4096 + 2048);
+              const uint32_t dtm = tmem + (uint32_t)(ds * 16);
+              uint32_t acc = kh ? 1u : 0u;
+              for (int ks = 0; ks < nks; ++ks) {
+                const uint64_t adv = (uint64_t)(ks * 2);
+#define RX_MMA(DA, DB)                                                                        \
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"                                   \
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(dtm),   \
+               "l"((DA) + adv), "l"((DB) + adv), "r"(idesc), "r"(acc)                        \
+               : "memory");                                                                  \
+  acc = 1u;
+                RX_MMA(dah, dbh)
+                RX_MMA(dal, dbh)
+                RX_MMA(dah, dbl)
+#undef RX_MMA
+              }
+              rx_commit(&bars->v_empty[vs]);
+              if (kh == nkh - 1) rx_commit(&bars->d_full[ds]);
+            }
+            __syncwarp();
+          }
+        }
+        if (lane == 0) rx_commit(&bars->plan_empty[ps]);  // arrives once the MMAs have read the B planes
+      } else {
+        if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
+      }
+      __syncwarp();
+    }
+  } else if (warp == RX_W_FREE) {
+    // ===== V-slot release: the only waiter of v_empty, in order; publishes the count of finished V tiles
+    uint32_t v = 0;
+    RX_ITEM_LOOP {
+      RX_META()
+      if (M->kind == 0) {
+        const int nv = M->nmt * M->nkh;
+        for (int i = 0; i < nv; ++i, ++v) {
+          rx_wait(&bars->v_empty[v % RX_SV], (v / RX_SV) & 1u, 7, v);
+          if (lane == 0) rx_publish(&bars->v_freed, v + 1u);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
+    }
+  } else if (warp >= RX_W_EPI0 && warp < RX_W_EPI0 + 4) {
+    // ===== epilogue =====
+    const int quad = warp & 3, etid = tid - RX_W_EPI0 * 32;
+    uint32_t d = 0, ob = 0;
+    RX_ITEM_LOOP {
+      RX_META()
+      if (M->kind == 0) {
+        float* outp = M->out;
+        for (int mt = 0; mt < M->nmt; ++mt, ++d) {
+          const int ds = d % RX_SD;
+          rx_wait(&bars->d_full[ds], (d / RX_SD) & 1u, 6, d);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          uint32_t r[16];
+          const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ds * 16);
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+              "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+                "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+                "=r"(r[14]), "=r"(r[15])
+              : "r"(taddr)
+              : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) rx_arrive(&bars->d_empty[ds]);
+          // the stage buffer was last read by the bulk store issued two tiles ago
+          if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          unsigned char* stage = smem + RX_OFF_OST + ob * RX_OSTAGE;
+          const int row = quad * 32 + lane, c = row >> 4, ph = row & 15;
+          if (ph < PH) {
+            float* dst = reinterpret_cast<float*>(stage) + c * P + ph * PW;
+            if ((PW & 1) == 0) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (2 * j < PW)
+                  *reinterpret_cast<float2*>(dst + 2 * j) =
+                      make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < PW) dst[j] = __uint_as_float(r[j]);
+            }
+          }
+          rp_fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (etid == 0) rp_bulk_store(outp + (size_t)mt * 8 * P, stage, (uint32_t)(8 * P * 4));
+          ob ^= 1u;
+        }
+      } else if (M->kind == 1) {
+        const int total = M->nch * P, H = M->H, W = M->W;
+        const size_t HW = (size_t)H * W;
+        const RtGeom g = M->g;
+        for (int i = etid; i < total; i += 128) {
+          const int c = i / P, rem = i - c * P;
+          const int ph = rem / PW, pw = rem - ph * PW;
+          M->out[i] = rt_direct_output(M->featb + (size_t)c * HW, H, W, g, ph, pw);
+        }
+      } else {
+        const int total = M->nch * P;
+        for (int i = etid; i < total; i += 128) M->out[i] = 0.f;
+      }
+      __syncwarp();
+      if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
+    }
+    if (etid == 0) rp_bulk_wait_all();
+  } else if (warp >= RX_W_Y0) {
+    // ===== y-pass =====
+    const int yw = warp - RX_W_Y0;
+    uint32_t q = 0, v = 0;
+    RX_ITEM_LOOP {
+      RX_META()
+      if (M->kind == 0) {
+        const int R = M->R, cs = M->cs, nkh = M->nkh, nq = M->nq, nsc = 8 / cs;
+        for (int mt = 0; mt < M->nmt; ++mt)
+          for (int kh = 0; kh < nkh; ++kh, ++v) {
+            const int vs = v % RX_SV;
+            const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
+            for (int sc = 0; sc < nsc; ++sc, ++q) {
+              if ((int)(q % RX_NY) != yw) continue;
+              const int ts = q % RX_S;
+              rx_wait_ge(&bars->v_freed, v + 1u - (uint32_t)RX_SV, 7, v);  // the MMAs of tile v - SV are done
+              rx_wait_ge(&bars->issued, q + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
+              rx_wait(&bars->tile_full[ts], (q / RX_S) & 1u, 8, q);
+              rx_ypass(reinterpret_cast<const RbF4*>(smem + RX_OFF_TILE + ts * RX_SLOT), R, cs, nqh, M->mw,
+                       M->wrot, smem + RX_OFF_V + vs * 32768, sc * cs, lane);
+              rp_fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                rx_arrive(&bars->tile_empty[ts]);
+                rx_arrive_n(&bars->v_full[vs], (uint32_t)cs);
+              }
+            }
+          }
+      }
+      __syncwarp();
+      if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
+    }
+  }
+#undef RX_ITEM_LOOP
+#undef RX_META
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == RX_W_MMA)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+}
+
+// ---- host: tensor maps (x, plane, y) per level, kept in device memory ------------------------------
+typedef CUresult (*rx_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                 CUtensorMapFloatOOBfill);
+
+rx_encode_fn rx_encoder() {
+  static rx_encode_fn fn = []() -> rx_encode_fn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    return reinterpret_cast<rx_encode_fn>(p);
+  }();
+  return fn;
+}
+
+struct RxMapEntry {
+  const float* ptr;
+  long long planes;
+  int H, W, ok;
+  unsigned long long stamp;
+  CUtensorMap m[RX_NMAP];
+};
+
+// Fills maps->m[l] for level l; a small host cache keeps repeated calls on the same tensors free of
+// encoding (36 cuTensorMapEncodeTiled calls per level otherwise).  Returns 0 on failure.
+int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H, int W) {
+  static std::mutex mu;
+  static RxMapEntry cache[32];
+  static unsigned long long clock_ = 0;
+  rx_encode_fn enc = rx_encoder();
+  if (!enc) return 0;
+  std::lock_guard<std::mutex> lock(mu);
+  int victim = 0;
+  for (int i = 0; i < 32; ++i) {
+    RxMapEntry& e = cache[i];
+    if (e.ok && e.ptr == ptr && e.planes == planes && e.H == H && e.W == W) {
+      e.stamp = ++clock_;
+      memcpy(maps->m[l], e.m, sizeof(e.m));
+      return 1;
+    }
+    if (e.stamp < cache[victim].stamp) victim = i;
+  }
+  RxMapEntry& e = cache[victim];
+  e.ok = 0;
+  static const int rows_of[3] = {8, 4, 2};
+  const cuuint64_t gdim[3] = {(cuuint64_t)W, (cuuint64_t)planes, (cuuint64_t)H};
+  const cuuint64_t gstride[2] = {(cuuint64_t)H * W * 4, (cuuint64_t)W * 4};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  for (int wi = 0; wi < 4; ++wi)
+    for (int ri = 0; ri < 3; ++ri)
+      for (int ci = 0; ci < 3; ++ci) {
+        const cuuint32_t box[3] = {(cuuint32_t)(8 * (wi + 1)), (cuuint32_t)(8 >> ci), (cuuint32_t)rows_of[ri]};
+        const CUresult r = enc(&e.m[(wi * 3 + ri) * 3 + ci], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                               const_cast<float*>(ptr), gdim, gstride, box, estride,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return 0;
+      }
+  e.ptr = ptr;
+  e.planes = planes;
+  e.H = H;
+  e.W = W;
+  e.ok = 1;
+  e.stamp = ++clock_;
+  memcpy(maps->m[l], e.m, sizeof(e.m));
+  return 1;
+}
+
+}  // namespace
+
+static int* rx_dbg_host_ptr = nullptr;
+// diagnostic (RP_RX_DEBUG=1): per warp {set, block, wait code, parity, counter} of the last barrier timeout
+extern "C" RP_API int rp_debug_rx_timeouts(int* out, int n) {
+  if (!rx_dbg_host_ptr || !out) return 0;
+  for (int i = 0; i < n && i < 1024; ++i) out[i] = rx_dbg_host_ptr[i];
+  return 1;
+}
+
+int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K, int PH,
+               int PW, float sampling_ratio, float* out, cudaStream_t st) {
+  // eligibility: fixed sampling grid, bins fit 16 accumulator rows / columns, whole 8-channel groups,
+  // every level a legal TMA tensor (16-byte aligned rows and base)
+  if (!(sampling_ratio > 0) || (int)sampling_ratio > RB_MAXG || PH > 16 || PW > 16 || (C & 7)) return 1;
+  const long long planes = (long long)N * C;
+  if (planes > 0x7fffffffLL) return 1;
+  for (int l = 0; l < lv.L; ++l)
+    if ((lv.W[l] & 3) || (reinterpret_cast<uintptr_t>(lv.feat[l]) & 15) || lv.H[l] < 1 || lv.W[l] < 4) return 1;
+  if (lv.L > RX_MAXL) return 1;
+  static RxMaps maps;  // 15 KB: filled under the lock below, copied into the launch by value
+  static std::mutex launch_mu;
+  std::lock_guard<std::mutex> lock(launch_mu);
+  for (int l = 0; l < lv.L; ++l)
+    if (!rx_level_maps(&maps, l, lv.feat[l], planes, lv.H[l], lv.W[l])) return 1;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(rx_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RX_SMEM);
+  });
+  if (attr_err != cudaSuccess) return (int)attr_err;
+  static int* dbg_host = nullptr;
+  if (!dbg_host && rp_env_int("RP_RX_DEBUG", 0)) {
+    int* dev = nullptr;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&dbg_host), 4096, cudaHostAllocMapped) == cudaSuccess &&
+        cudaHostGetDevicePointer(reinterpret_cast<void**>(&dev), dbg_host, 0) == cudaSuccess) {
+      memset(dbg_host, 0, 4096);
+      cudaMemcpyToSymbol(rx_dbg, &dev, sizeof(dev));
+      rx_dbg_host_ptr = dbg_host;
+    }
+  }
+  const int nsl = (C + RX_CS - 1) / RX_CS;
+  const long long n_items = (long long)K * nsl;
+  if (n_items > 0x7fffffffLL) return RP_E_LIMIT;
+  const int grid = (int)(n_items < RP_NUM_SMS ? n_items : RP_NUM_SMS);
+  rx_pool_fwd_kernel<<<grid, RX_THREADS, RX_SMEM, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
+                                                       out, maps, (int)n_items);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}

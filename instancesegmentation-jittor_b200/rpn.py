@@ -200,7 +200,6 @@ class RPNPostProcessor(torch.nn.Module):
             fpn_post_nms_top_n = post_nms_top_n
         self.fpn_post_nms_top_n = fpn_post_nms_top_n
         self.fpn_post_nms_per_batch = fpn_post_nms_per_batch
-        self._anchor_cache = {}
 
     def is_training(self):
         return self.training
@@ -212,16 +211,10 @@ class RPNPostProcessor(torch.nn.Module):
         return [cat_boxlist((p, g)) for p, g in zip(proposals, gt_boxes)]
 
     def _stack_anchors(self, anchors):
-        """list[BoxList] of one level -> [N, H*W*A, 4].  Anchors depend only on the padded batch
-        shape, so the stacked tensor is reused while the per-image tensors stay the same objects."""
-        key = tuple((a.bbox.data_ptr(), int(a.bbox.shape[0])) for a in anchors)
-        hit = self._anchor_cache.get(key)
-        if hit is None:
-            if len(self._anchor_cache) > 64:
-                self._anchor_cache.clear()
-            hit = torch.stack([a.bbox for a in anchors], dim=0).to(_F32).contiguous()
-            self._anchor_cache[key] = hit
-        return hit
+        """list[BoxList] of one level -> [N, H*W*A, 4].  The reference builds new anchor tensors on
+        every forward (anchor_generator.py grid_anchors), so nothing is cached by address here: one
+        stack per level is a single small launch."""
+        return torch.stack([a.bbox for a in anchors], dim=0).to(_F32).contiguous()
 
     # ---- device part: nothing here waits for the GPU
     def _launch(self, anchors_by_level, objectness, box_regression):

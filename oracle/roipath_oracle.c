@@ -960,7 +960,13 @@ ORC_API int orc_box_post_image(const float* logits, const float* reg, const floa
       ++nc;
     }
     if (nc == 0) continue;
-    const int nk = orc_nms(cb, cs, nc, nms_thresh, NULL, -1, keep);
+    int nk;
+    if (nms_thresh > 0) {
+      nk = orc_nms(cb, cs, nc, nms_thresh, NULL, -1, keep);
+    } else { /* det/structures/boxlist_ops.py:24-25: the boxlist is returned unchanged */
+      nk = nc;
+      for (int q = 0; q < nc; ++q) keep[q] = q;
+    }
     for (int q = 0; q < nk; ++q) {
       memcpy(out_boxes + (size_t)m * 4, cb + (size_t)keep[q] * 4, sizeof(float) * 4);
       out_scores[m] = cs[keep[q]];

@@ -48,7 +48,8 @@ def test_post_processor_matches_oracle(n_images, per_image, C, ties):
     _check(res, lg, reg, pr, counts, wh)
 
 
-@pytest.mark.parametrize("dets,thresh,nms", [(0, 0.05, 0.5), (10, 0.3, 0.3), (100, 0.0, 0.7), (5, 0.9999, 0.5)])
+@pytest.mark.parametrize("dets,thresh,nms", [(0, 0.05, 0.5), (10, 0.3, 0.3), (100, 0.0, 0.7), (5, 0.9999, 0.5),
+                                             (100, 0.05, 0.0), (0, 0.2, -1.0)])  # nms <= 0: NMS skipped
 def test_parameters(dets, thresh, nms):
     lg, reg, pr, counts, wh = synth.box_head_batch(2, 400, num_classes=21, seed=4, ties=True)
     post = rp.PostProcessor(thresh, nms, dets)
@@ -109,6 +110,6 @@ def test_errors_are_loud():
     with pytest.raises(ValueError):
         rp.box_post(T(lg), T(reg[:, :8]), T(pr), offs, T(wh), 20, 0.05, 0.5, 100)
     with pytest.raises(ValueError):
-        rp.box_post(T(lg), T(reg), T(pr), offs, T(wh), 20, 0.05, 0.0, 100)  # nms_thresh must be > 0
+        rp.box_post(T(lg), T(reg), T(pr), offs, T(wh), 20, 0.05, float("nan"), 100)
     with pytest.raises(Exception):
         rp.box_post(torch.from_numpy(lg), T(reg), T(pr), offs, T(wh), 20, 0.05, 0.5, 100)
