@@ -231,133 +231,6 @@ def time_steps(fn, steps, stream_sync, barrier):
     return e0.elapsed_time(e1)  # ms
 
 
-def extras(rp, torch, dev):
-    """The other figures of the compound metric, each timed with CUDA events (median of 10)."""
-    out = {}
-
-    def med(fn, n=10, warm=3):
-        for _ in range(warm):
-            fn()
-        ts = []
-        for _ in range(n):
-            torch.cuda.synchronize()
-            a = torch.cuda.Event(enable_timing=True)
-            b = torch.cuda.Event(enable_timing=True)
-            a.record()
-            fn()
-            b.record()
-            torch.cuda.synchronize()
-            ts.append(a.elapsed_time(b))
-        return float(np.median(ts))
-
-    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    # --- Pooler backward, train shape of BASELINE configs[2]: 16 images x 512 RoIs (7x7, box head)
-    #     and 2048 positives (14x14, mask head); bytes = dout read + every level gradient written
-    shapes = synth.fpn_shapes(IMAGES_PER_GPU, CHANNELS)
-    rois_b = T(synth.rois_for_images(IMAGES_PER_GPU, 512))
-    lv_b = rp.LevelMapper(2, 5).map_rois(rois_b)
-    grad_bytes = sum(int(np.prod(sh)) for sh in shapes) * 4
-    for res, k in ((7, int(rois_b.shape[0])), (14, 2048)):
-        d = torch.randn((k, CHANNELS, res, res), device=dev)
-        ms = med(lambda: rp.pooler_backward(d, rois_b[:k], lv_b[:k], shapes, synth.FPN_SCALES, SAMPLING), n=5)
-        out["pooler_bwd_%dx%d_ms" % (res, res)] = ms
-        out["pooler_bwd_%dx%d_gbs" % (res, res)] = (d.numel() * 4 + grad_bytes) / (ms * 1e-3) / 1e9
-        del d
-    # --- NMS sweep, batch 8 (BASELINE configs[1]); thr 0.7
-    for n in (2000, 5000, 10000, 20000):
-        B = 8
-        bs, ss = zip(*[synth.nms_boxes(n, 7 + i)[:2] for i in range(B)])
-        boxes, scores = T(np.concatenate(bs)), T(np.concatenate(ss))
-        offs = T((np.arange(B + 1) * n).astype(np.int32))
-        for mk in (-1, 1000):
-            ms = med(lambda: rp.nms_batched(boxes, scores, offs, 0.7, max_keep=mk, n_max=n))
-            out["nms_ms_per_image_n%d_max%d" % (n, mk)] = ms / B
-        if n == 20000:
-            b1, s1 = T(bs[0]), T(ss[0])
-            o1 = T(np.array([0, n], np.int32))
-            out["nms_ms_single_image_n20000"] = med(lambda: rp.nms_batched(b1, s1, o1, 0.7, n_max=n))
-        del boxes, scores
-    # --- Yolact post (FastNMS + assembly at 550x550), batch 64 (BASELINE configs[3])
-    priors = synth.yolact_priors()
-    B = 64
-    base = []
-    for i in range(4):  # decode + conf filter prepare the inputs; they are outside the timed op
-        loc, conf, mask, proto = synth.yolact_image(100 + i, priors)
-        boxes = rp.decode(T(loc), T(priors)).cpu().numpy()
-        fg = np.ascontiguousarray(conf[:, 1:].T)
-        kp = np.nonzero(fg.max(0) > np.float32(0.05))[0]
-        base.append((boxes[kp], mask[kp], np.ascontiguousarray(fg[:, kp]), proto))
-    cands = [base[i % 4] for i in range(B)]
-    offs_np = np.concatenate([[0], np.cumsum([c[0].shape[0] for c in cands])]).astype(np.int32)
-    yb, yc = T(np.concatenate([c[0] for c in cands])), T(np.concatenate([c[1] for c in cands]))
-    ys = T(np.concatenate([c[2] for c in cands], 1))
-    yp = T(np.stack([c[3] for c in cands]))
-    yo = T(offs_np)
-    masks_buf = torch.empty((B * 100, 550, 550), dtype=torch.uint8, device=dev)
-    slot_off = T((np.arange(B + 1) * 100).astype(np.int32))
-
-    def yolact_post():
-        r = rp.fast_nms_batched(yb, yc, ys, yo, 0.5, 200, 100, n_max=int(np.diff(offs_np).max()))
-        # padded layout: every image owns 100 detection slots (unused slots hold zero boxes)
-        rp.mask_assemble(yp, r["mask"].reshape(B * 100, -1), r["box"].reshape(B * 100, 4), 550, 550,
-                         True, det_offsets=slot_off, out=masks_buf)
-
-    ms = med(yolact_post, n=5, warm=2)
-    out["yolact_post_images_per_s"] = B / (ms * 1e-3)
-    out["yolact_post_ms_per_batch64"] = ms
-    r = rp.fast_nms_batched(yb, yc, ys, yo, 0.5, 200, 100)
-    out["yolact_fast_nms_ms_per_batch64"] = med(lambda: rp.fast_nms_batched(yb, yc, ys, yo, 0.5, 200, 100))
-    cf, bx = r["mask"].reshape(B * 100, -1), r["box"].reshape(B * 100, 4)
-    ms_a = med(lambda: rp.mask_assemble(yp, cf, bx, 550, 550, True, det_offsets=slot_off, out=masks_buf), n=5, warm=2)
-    out["mask_assemble_ms_per_batch64"] = ms_a
-    out["mask_assemble_gbs"] = (B * (138 * 138 * 32 * 4 + 100 * 32 * 4 + 1600) + B * 100 * 550 * 550) / (ms_a * 1e-3) / 1e9
-    del masks_buf, yp
-    # --- Yolact Detect pre-stage (SURVEY 8(f) rank 3) from the raw head outputs, batch 64:
-    #     decode + class-max + conf filter + gathers over the 399 MB conf tensor
-    raw = [synth.yolact_image(100 + i, priors) for i in range(4)]
-    loc64 = T(np.stack([raw[i % 4][0] for i in range(B)]))
-    conf64 = T(np.stack([raw[i % 4][1] for i in range(B)]))
-    mask64 = T(np.stack([raw[i % 4][2] for i in range(B)]))
-    pri_t = T(priors)
-    ms_f = med(lambda: rp.detect_prefilter(loc64, conf64, mask64, pri_t, 0.05), n=5, warm=2)
-    out["yolact_prefilter_ms_per_batch64"] = ms_f
-    out["yolact_prefilter_gbs"] = (conf64.numel() + loc64.numel()) * 4 / (ms_f * 1e-3) / 1e9
-    del loc64, conf64, mask64
-    # --- paste-back, 100 instances at 1333x800 (BASELINE configs[4], one image per launch)
-    pm, pb = synth.paste_inputs(100, 200)
-    pmt, pbt = T(pm), T(pb)
-    pout = torch.empty((100, 800, 1333), dtype=torch.uint8, device=dev)
-    ms_p = med(lambda: rp.paste_masks(pmt, pbt, 800, 1333, out=pout))
-    out["paste_ms_per_image_100inst"] = ms_p
-    out["paste_gbs"] = (100 * 28 * 28 * 4 + 100 * 800 * 1333) / (ms_p * 1e-3) / 1e9
-    # --- RPN proposal stage (SURVEY 8(f) rank 1): 5 FPN levels of 8 images at 800 x 1344, test
-    #     configuration (pre/post/fpn top-n 1000, thr 0.7): pre-NMS + NMS + per-image selection,
-    #     device part (no host read) and the whole RPNPostProcessor.execute (BoxLists out)
-    N, A = 8, 3
-    lv = [synth.rpn_level(N, A, H, W, st, seed=100 + st)
-          for H, W, st in ((200, 336, 4), (100, 168, 8), (50, 84, 16), (25, 42, 32), (13, 21, 64))]
-    im_wh = lv[0][3]
-    anchors = [[rp.BoxList(T(l[0][b]), (int(im_wh[b, 0]), int(im_wh[b, 1]))) for l in lv] for b in range(N)]
-    objs, regs, ancs, wh = [T(l[1]) for l in lv], [T(l[2]) for l in lv], [T(l[0]) for l in lv], T(im_wh)
-    post = rp.RPNPostProcessor(1000, 1000, 0.7, 0, fpn_post_nms_top_n=1000)
-    post.eval()
-
-    def rpn_device():
-        bx, sc, _, off, ks = rp.rpn_pre_nms_levels(objs, regs, ancs, wh, 1000, 0.0)
-        keep, nk = rp.nms_batched(bx, sc, off, 0.7, max_keep=1000, n_max=max(ks))
-        rp.rpn_select_levels(bx, sc, off, keep, nk, len(lv), N, 1000)
-
-    out["rpn_post_device_ms_per_batch8"] = med(rpn_device)
-    out["rpn_post_execute_ms_per_batch8"] = med(lambda: post(anchors, objs, regs))
-    # --- box-head post-processor (SURVEY 8(f) rank 2): 8 images x 1000 proposals x 81 classes
-    lg, reg, pr, counts, bwh = synth.box_head_batch(8, 1000, seed=3)
-    lgt, regt, prt, bwht = T(lg), T(reg), T(pr), T(bwh)
-    boffs = T(np.concatenate([[0], np.cumsum(counts)]).astype(np.int32))
-    out["box_post_device_ms_per_batch8"] = med(
-        lambda: rp.box_post(lgt, regt, prt, boffs, bwht, 1000, 0.05, 0.5, 100))
-    return out
-
-
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -393,7 +266,7 @@ def run_gpu_arm(args):
         levels = mapper.map_rois(rois)
         rp.pooler_forward(feats, synth.FPN_SCALES, rois, levels, (RES, RES), SAMPLING, out=out)
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(args.warmup):
         step()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -434,14 +307,51 @@ def run_gpu_arm(args):
         n_e2e = max(1, min(args.steps, 3))
         ms_e2e = time_steps(e2e_step, n_e2e, None, barrier)
         te = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+        per_rank = [te.clone() for _ in range(world)]
         if world > 1:
+            dist.all_gather(per_rank, te)
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         h2d = int(sum(hf.numel() * 4 for hf in h_feats) + h_rois[:, 1:].numel() * 4)
         d2h = int(h_out.numel() * 4)
+
+        # host ceiling: the same pinned H2D + D2H bytes on two streams with NO kernel, all ranks at once
+        d_out_tmp = out
+        s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+        def copies_only():
+            with torch.cuda.stream(s_in):
+                for hf, f in zip(h_feats, feats):
+                    f.copy_(hf, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                h_out.copy_(d_out_tmp, non_blocking=True)
+            torch.cuda.current_stream(dev).wait_stream(s_in)
+            torch.cuda.current_stream(dev).wait_stream(s_out)
+
+        copies_only()
+        torch.cuda.synchronize()
+        ms_copy = time_steps(copies_only, n_e2e, None, barrier)
+        tc = torch.tensor([ms_copy], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tc, op=dist.ReduceOp.MAX)
         e2e = {"value": world * K * n_e2e / (float(te.item()) * 1e-3), "unit": "RoIs/s",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": n_e2e}
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": n_e2e,
+               "per_rank_rois_per_s": [K * n_e2e / (float(t.item()) * 1e-3) for t in per_rank],
+               "host_ceiling": {
+                   "what": "the same pinned H2D + D2H bytes per rank on two streams, no kernel, all ranks "
+                           "at once (max over ranks)",
+                   "rois_per_s": world * K * n_e2e / (float(tc.item()) * 1e-3),
+                   "aggregate_gbs": world * (h2d + d2h) * n_e2e / (float(tc.item()) * 1e-3) / 1e9}}
         del h_feats, h_out
 
+    # ---- the other figures of the compound metric, sharded by image over the ranks (every N)
+    extra = None
+    cores = len(os.sched_getaffinity(0))
+    if not args.no_extras:
+        import bench_extras
+        try:
+            extra = bench_extras.run(rp, torch, dist, dev, rank, world, IMAGES_PER_GPU, cores)
+        except Exception as ex:  # the headline line must still be printed
+            extra = {"error": repr(ex)}
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -472,26 +382,36 @@ def run_gpu_arm(args):
                 "level_histogram": np.bincount(lv_np, minlength=4).tolist()}
 
     # ---- CPU baseline on this box's host cores (bounded sample)
-    cores = len(os.sched_getaffinity(0))
     cf, cr, cl = cpu_sample(1)
     dt, kind, cpu_out = cpu_pooler(cf, cr, cl, cores)
     dt2, _, _ = cpu_pooler(cf, cr, cl, cores)
     dt = min(dt, dt2)
     cpu_baseline = {"value": cr.shape[0] / dt, "unit": "RoIs/s", "cores": cores, "kind": kind,
                     "sample": "1 image x %d RoIs of the same workload, best of 2" % ROIS_PER_IMAGE}
+    # ---- parity at the headline configuration: the GPU path on the CPU arm's own inputs (1 image x
+    #      1000 RoIs x 256 channels x 14x14) against the CPU arm's output (reference kernel text when
+    #      kind == "reference"); north_star bar: 1e-5 relative in fp32
+    g_feats = [torch.from_numpy(f).to(dev) for f in cf]
+    g_rois = torch.from_numpy(cr).to(dev)
+    g_out = rp.pooler_forward(g_feats, synth.FPN_SCALES, g_rois, mapper.map_rois(g_rois), (RES, RES), SAMPLING)
+    g_np = g_out.cpu().numpy()
+    err = np.abs(g_np - cpu_out)
+    tol = 1e-5 * np.abs(cpu_out) + 1e-5
+    parity = {"against": kind, "n": int(err.size), "max_abs": float(err.max()),
+              "max_rel": float((err / np.maximum(np.abs(cpu_out), 1e-3)).max()),
+              "violations": int((err > tol).sum()), "tol": "1e-5*|ref| + 1e-5",
+              "levels_equal": bool(np.array_equal(mapper.map_rois(g_rois).cpu().numpy(), cl))}
+    del g_feats, g_out
 
     line = {
         "metric": METRIC, "value": value, "unit": "RoIs/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+        "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(world), "roofline": roofline, "cpu_baseline": cpu_baseline,
-        "e2e": e2e, "gpu_launches": 2 * args.steps, "clocks": clocks,
+        "parity": parity, "e2e": e2e, "gpu_launches": 2 * args.steps, "clocks": clocks,
     }
-    if not args.no_extras and world == 1:
-        try:
-            line["extra"] = extras(rp, torch, dev)
-        except Exception as ex:  # the headline line must still be printed
-            line["extra"] = {"error": repr(ex)}
+    if extra is not None:
+        line["extra"] = extra
     print(json.dumps(line))
     if world > 1:
         dist.barrier()

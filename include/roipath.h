@@ -208,6 +208,39 @@ RP_API int rp_paste_masks(const float* masks, const float* boxes, int n, int M, 
                    float thresh, int padding, uint8_t* out, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * Yolact lincomb mask loss, forward + backward in one launch (the training twin of
+ * rp_mask_assemble).
+ * Replaces, per image: yol/layers/modules/multibox_loss.py:616-660 -- pred = sigmoid(proto @ coef^T),
+ *           crop(pred, boxes) (box_utils.py:355-378, padding 1; boxes NULL = mask_proto_crop off),
+ *           binary_cross_entropy(clamp(pred,0,1), mask_t) (:8-9), per-instance sum times scale[i]
+ *           (scale NULL = 1; with mask_proto_normalize_emulate_roi_pooling the caller passes
+ *           H*W / (gt_w*W) / (gt_h*H), :645-649) -- and the autograd backward of sum_i loss[i].
+ *   proto [H,W,D], coef [n,D], mask_t [H,W,n] (0/1 targets), boxes [n,4] relative xyxy, scale [n]
+ *   -> loss [n], d_proto [H,W,D] (fully written), d_coef [n,D].
+ * Limits: D in {8,16,32,64}; n*(D+134) floats of shared memory (n <= ~280 at D = 32).
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_lincomb_mask_loss(const float* proto, const float* coef, const float* mask_t,
+                                const float* boxes, const float* scale, int H, int W, int D, int n,
+                                float* loss, float* d_proto, float* d_coef, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Pose2Seg paste-back (BASELINE configs[4] names Pose2Seg).
+ * Replaces: warpAffine(predmap, H_e2e, width, height) Pose2Seg.jittor/modeling/build_model.py:31-43 =
+ *           cv2.warpAffine(predmap, H_e2e[0:2], (width, height), WARP_INVERSE_MAP + INTER_LINEAR,
+ *           BORDER_CONSTANT)[:, :, channel] > 0.5, bit for bit (OpenCV's 10-bit fixed-point source
+ *           coordinates and 32x32 bilinear weight table).
+ *   pred [n,h,w,C] float (HWC, as the seg head's softmax output), M [n,6] DOUBLE row-major 2x3
+ *   (output pixel -> source), out [n,height,width] uint8 (0/1).
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_affine_paste(const float* pred, const double* M, int n, int h, int w, int C, int channel,
+                           int width, int height, uint8_t* out, void* stream);
+
+/* Bit-packing of binary masks for the final gather of kept detections (the one exchange of the
+ * image-sharded path; the reference is single-process and has no counterpart).
+ *   masks [m, npix] uint8 (0 / non-zero) -> out [m, ceil(npix/8)] uint8, pixel i in bit (i & 7) of byte i >> 3. */
+RP_API int rp_pack_mask_bits(const uint8_t* masks, long long m, long long npix, uint8_t* out, void* stream);
+
+/* ------------------------------------------------------------------------------------
  * RPN proposal stage in front of the NMS (the caller of rp_nms_batched).
  * Replaces: BoxCoder.decode det/modeling/box_coder.py:53-94 (rp_box_decode), and in
  *           RPNPostProcessor.forward_for_single_feature_map det/modeling/rpn/inference.py:83-117

@@ -204,4 +204,49 @@ RP_HD float rp_float_ge(double d) {
   return f;
 }
 
+/* ---- cv2.warpAffine(flags = WARP_INVERSE_MAP + INTER_LINEAR, borderMode = BORDER_CONSTANT, 0) for
+ * float32 images, as Pose2Seg.jittor/modeling/build_model.py:31-43 calls it.  OpenCV (imgwarp.cpp,
+ * warpAffine / remapBilinear) evaluates the source coordinate in 10-bit fixed point
+ *   X = (cvRound((M[1]*y + M[2]) * 1024) + 16 + cvRound(M[0]*x * 1024)) >> 5       (same for Y with M[3..5])
+ * so that X >> 5 is the integer source column (saturated to int16) and X & 31 indexes a table of 32x32
+ * bilinear weights  w = {(1-fy)(1-fx), (1-fy)fx, fy(1-fx), fy*fx},  f = i * (1/32) in float; the value is
+ * S00*w0 + S01*w1 + S10*w2 + S11*w3 in float, taps outside the image read 0. */
+RP_HD int rp_cv_round(double v) {
+#if defined(__CUDA_ARCH__)
+  return __double2int_rn(v);
+#else
+  return (int)lrint(v);
+#endif
+}
+
+RP_HD int rp_sat_short(int v) { return v < -32768 ? -32768 : (v > 32767 ? 32767 : v); }
+
+RP_HD void rp_warp_affine_coord(const double* M, int x, int y, int* sx, int* sy, int* fx, int* fy) {
+  const int X0 = rp_cv_round((M[1] * (double)y + M[2]) * 1024.0) + 16;
+  const int Y0 = rp_cv_round((M[4] * (double)y + M[5]) * 1024.0) + 16;
+  const int X = (X0 + rp_cv_round(M[0] * (double)x * 1024.0)) >> 5;
+  const int Y = (Y0 + rp_cv_round(M[3] * (double)x * 1024.0)) >> 5;
+  *sx = rp_sat_short(X >> 5);
+  *sy = rp_sat_short(Y >> 5);
+  *fx = X & 31;
+  *fy = Y & 31;
+}
+
+/* channel c of an interleaved [h, w, C] float image */
+RP_HD float rp_warp_affine_sample(const float* src, int h, int w, int C, int c, int sx, int sy, int fx,
+                                  int fy) {
+  if (sx >= w || sx + 1 < 0 || sy >= h || sy + 1 < 0) return 0.0f;
+  const float scale = 1.0f / 32.0f;
+  const float x = (float)fx * scale, y = (float)fy * scale;
+  const float x0 = 1.0f - x, y0 = 1.0f - y;
+  const float w0 = y0 * x0, w1 = y0 * x, w2 = y * x0, w3 = y * x;
+  const int okx0 = sx >= 0 && sx < w, okx1 = sx + 1 >= 0 && sx + 1 < w;
+  const int oky0 = sy >= 0 && sy < h, oky1 = sy + 1 >= 0 && sy + 1 < h;
+  const float v0 = (okx0 && oky0) ? src[((size_t)sy * w + sx) * C + c] : 0.0f;
+  const float v1 = (okx1 && oky0) ? src[((size_t)sy * w + sx + 1) * C + c] : 0.0f;
+  const float v2 = (okx0 && oky1) ? src[((size_t)(sy + 1) * w + sx) * C + c] : 0.0f;
+  const float v3 = (okx1 && oky1) ? src[((size_t)(sy + 1) * w + sx + 1) * C + c] : 0.0f;
+  return v0 * w0 + v1 * w1 + v2 * w2 + v3 * w3;
+}
+
 #endif /* ROIPATH_MATH_H_ */

@@ -10,6 +10,7 @@ from .layers import (ROIAlign, ROIPool, cython_nms, mask_prob_cuda, ml_nms, nms,
                      roi_pool,
                      roi_align_backward, roi_align_forward)
 from . import parallel
+from .pose2seg import affine_paste, warpAffine
 from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_in_image,
                      paste_masks)
 from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_format,
@@ -19,7 +20,8 @@ from .rpn import (BoxCoder, RPNPostProcessor, box_decode, make_rpn_postprocessor
                   rpn_pre_nms_levels, rpn_select_levels)
 from .structures import (BoxList, boxes_to_masks, crop_by_box, boxlist_iou, boxlist_ml_nms, boxlist_nms, boxlist_nms_batched, cat_boxlist,
                          remove_small_boxes)
-from .yolact import (Detect, crop, decode, detect_prefilter, fast_nms_batched, mask_assemble, postprocess,
+from .yolact import (Detect, crop, decode, detect_prefilter, fast_nms_batched, lincomb_mask_loss,
+                     lincomb_mask_loss_raw, mask_assemble, postprocess,
                      sanitize_coordinates)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -40,6 +40,9 @@ SIGNATURES = {
     "rp_mask_assemble": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "rp_mask_select_sigmoid": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "rp_paste_masks": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _vp]),
+    "rp_lincomb_mask_loss": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "rp_affine_paste": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "rp_pack_mask_bits": (_i, [_vp, _c.c_longlong, _c.c_longlong, _vp, _vp]),
     "rp_box_decode": (_i, [_vp, _vp, _i, _i, _f, _f, _f, _f, _f, _vp, _vp]),
     "rp_rpn_pre_nms_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rp_rpn_pre_nms": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _f, _f, _f, _f,

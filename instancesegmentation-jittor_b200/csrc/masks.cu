@@ -489,7 +489,49 @@ paste_masks_flat_kernel(const float* __restrict__ masks, const float* __restrict
   }
 }
 
+// ---- bit-packing of binary masks for the final gather (parallel.gather_detections) ----------------
+// masks [m, npix] uint8 (0 / non-zero) -> bits [m, ceil(npix / 8)], pixel i of a mask in bit (i & 7) of
+// byte i >> 3.  One thread per 32 pixels: eight 4-byte loads (rows of 4-byte multiples) or 32 byte
+// loads, one 4-byte / up to four 1-byte stores.  HBM bound: npix bytes in, npix / 8 out.
+__global__ void __launch_bounds__(256)
+pack_mask_bits_kernel(const uint8_t* __restrict__ masks, long long m, long long npix,
+                      uint8_t* __restrict__ out) {
+  const long long words = (npix + 31) >> 5;   // 32-pixel groups per mask
+  const long long obytes = (npix + 7) >> 3;   // output bytes per mask
+  const bool vec = (npix & 3) == 0 && (reinterpret_cast<uintptr_t>(masks) & 3) == 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m * words;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / words, w = i - r * words;
+    const uint8_t* src = masks + r * npix + (w << 5);
+    const long long left = npix - (w << 5);
+    uint32_t bits = 0;
+    if (vec && left >= 32) {
+      const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t v = __ldcs(s4 + j);
+        bits |= ((v & 0xffu) ? 1u : 0u) << (4 * j);
+        bits |= ((v & 0xff00u) ? 1u : 0u) << (4 * j + 1);
+        bits |= ((v & 0xff0000u) ? 1u : 0u) << (4 * j + 2);
+        bits |= ((v & 0xff000000u) ? 1u : 0u) << (4 * j + 3);
+      }
+    } else {
+      const int n = left < 32 ? (int)left : 32;
+      for (int j = 0; j < n; ++j) bits |= (src[j] ? 1u : 0u) << j;
+    }
+    uint8_t* dst = out + r * obytes + (w << 2);
+    const long long bleft = obytes - (w << 2);
+    if (bleft >= 4 && ((reinterpret_cast<uintptr_t>(dst) & 3) == 0)) {
+      *reinterpret_cast<uint32_t*>(dst) = bits;
+    } else {
+      const int nb = bleft < 4 ? (int)bleft : 4;
+      for (int j = 0; j < nb; ++j) dst[j] = (uint8_t)(bits >> (8 * j));
+    }
+  }
+}
+
 }  // namespace
+
 
 extern "C" {
 
@@ -582,6 +624,17 @@ int rp_paste_masks(const float* masks, const float* boxes, int n, int M, int im_
   dim3 grid((unsigned)((im_h + PM_ROWS - 1) / PM_ROWS), (unsigned)n);
   paste_masks_kernel<<<grid, PM_THREADS, 0, (cudaStream_t)stream>>>(masks, boxes, M, im_h, im_w,
                                                                      thresh, padding, scale, out);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_pack_mask_bits(const uint8_t* masks, long long m, long long npix, uint8_t* out, void* stream) {
+  if (m == 0 || npix == 0) return RP_OK;
+  if (!masks || !out || m < 0 || npix < 0) return RP_E_ARG;
+  const long long groups = m * ((npix + 31) >> 5);
+  long long blocks = (groups + 255) / 256;
+  if (blocks > (long long)RP_NUM_SMS * 32) blocks = (long long)RP_NUM_SMS * 32;
+  pack_mask_bits_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(masks, m, npix, out);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

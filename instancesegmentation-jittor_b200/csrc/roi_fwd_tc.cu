@@ -37,19 +37,19 @@
 
 namespace {
 
-constexpr int RX_THREADS = 512;
+constexpr int RX_THREADS = 1024;
 constexpr int RX_W_TMA = 0, RX_W_MMA = 1, RX_W_PLAN = 2, RX_W_FREE = 3, RX_W_EPI0 = 4, RX_W_Y0 = 8;
-constexpr int RX_NY = 8;               // y-pass warps
-constexpr int RX_S = 5;                // tile slots
-constexpr int RX_SLOT = 16384;         // bytes per tile slot
-constexpr int RX_SV = 3;               // V slots (hi + lo, 32 KB each)
+constexpr int RX_NY = 24;              // y-pass warps
+constexpr int RX_S = 4;                // tile slots
+constexpr int RX_SLOT = 14336;         // bytes per tile slot
+constexpr int RX_SV = 4;               // V slots (hi + lo, 32 KB each)
 constexpr int RX_SD = 4;               // accumulator tiles in TMEM (16 columns each)
 constexpr int RX_NP = 2;               // plans in flight
 constexpr int RX_CS = 128;             // channels per work item (RoI x channel slice)
 constexpr int RX_RMAX = 64;            // tile rows
-constexpr int RX_OSTAGE = 8 * 16 * 16 * 4;  // out stage: 8 channels x <= 16x16 floats
+constexpr int RX_OSTAGE = 8 * 16 * 16 * 4;  // out stage: 8 channels x <= 16x16 floats (one buffer)
 constexpr int RX_NMAP = 36;            // tensor maps per level: 4 widths x 3 row counts x 3 channel counts
-constexpr int RX_PLAN_ARRIVALS = 1 + RX_NY + 1 + 4 + 1;
+constexpr int RX_PLAN_ARRIVALS = 1 + RX_NY + 1 + 4 + 1;  // TMA, y-pass warps, MMA, epilogue warps, V release
 
 struct RxMeta {
   int kind;  // 0 tensor-core path, 1 reference-order fallback, 2 zero fill
@@ -58,8 +58,10 @@ struct RxMeta {
   float* out;          // &out[(k*C + c_begin) * P]
   const float* featb;  // &feat[level][(b*C + c_begin) * H*W]
   RtGeom g;
+  // the bins of a RoI are cut into nseg row segments, each walked by its own warp
+  int nseg, seg_b0[3], seg_r0[2], seg_rows[2];
   RbF4 wrot[16];
-  uint32_t mw[RX_RMAX / 4 + 2];
+  uint32_t mw[2][RX_RMAX / 4 + 2];
 };
 
 constexpr int RX_MAXL = 5;  // levels with tensor maps (kernel parameter space: 23 KB)
@@ -83,7 +85,7 @@ constexpr int RX_OFF_V = 0;
 constexpr int RX_OFF_B = RX_OFF_V + RX_SV * 32768;
 constexpr int RX_OFF_TILE = RX_OFF_B + RX_NP * 8192;
 constexpr int RX_OFF_OST = RX_OFF_TILE + RX_S * RX_SLOT;
-constexpr int RX_OFF_META = RX_OFF_OST + 2 * RX_OSTAGE;
+constexpr int RX_OFF_META = RX_OFF_OST + RX_OSTAGE;
 constexpr int RX_OFF_AY = RX_OFF_META + RX_NP * 1024;
 constexpr int RX_OFF_BARS = RX_OFF_AY + 1024;
 constexpr int RX_SMEM = RX_OFF_BARS + 512 + 1024;  // + alignment slack
@@ -112,7 +114,20 @@ __device__ __noinline__ void rx_timeout(uint32_t code, uint32_t parity, uint32_t
   }
   __trap();
 }
+#ifdef RX_PROFILE
+#define RX_PROF_T0 const long long rx_t0_ = clock64();
+#define RX_PROF_ADD(code) rx_prof_acc[(code)] += clock64() - rx_t0_;
+__device__ long long* rx_prof_ptr() {
+  __shared__ long long acc[32][12];  // [warp][wait code]; index 0: whole role loop, 10: work, 11: units
+  return acc[threadIdx.x >> 5];
+}
+#define rx_prof_acc (rx_prof_ptr())
+#else
+#define RX_PROF_T0
+#define RX_PROF_ADD(code)
+#endif
 __device__ __forceinline__ void rx_wait(uint64_t* bar, uint32_t parity, uint32_t code = 0, uint32_t counter = 0) {
+  RX_PROF_T0
   uint32_t done = 0;
   for (uint32_t spin = 0; !done; ++spin) {
     asm volatile(
@@ -126,16 +141,26 @@ __device__ __forceinline__ void rx_wait(uint64_t* bar, uint32_t parity, uint32_t
         : "memory");
     if (spin > (1u << 20)) rx_timeout(code, parity, counter);
   }
+#ifdef RX_PROFILE
+  if ((threadIdx.x & 31) == 0) { RX_PROF_ADD(code) }
+#endif
 }
 __device__ __forceinline__ void rx_publish(uint32_t* ctr, uint32_t v) {
   asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(rp_smem_addr(ctr)), "r"(v) : "memory");
 }
 // wait until *ctr >= target (sequence numbers: compared modulo 2^32)
 __device__ __forceinline__ void rx_wait_ge(uint32_t* ctr, uint32_t target, uint32_t code, uint32_t counter) {
+  RX_PROF_T0
   for (uint32_t spin = 0;; ++spin) {
     uint32_t v;
     asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(rp_smem_addr(ctr)) : "memory");
-    if ((int32_t)(v - target) >= 0) return;
+    if ((int32_t)(v - target) >= 0) {
+#ifdef RX_PROFILE
+      if ((threadIdx.x & 31) == 0) { RX_PROF_ADD(code) }
+#endif
+      return;
+    }
+    __nanosleep(40);  // polling warps must not load the shared-memory pipe the working warps live on
     if (spin > (1u << 22)) rx_timeout(code, target, counter);
   }
 }
@@ -237,9 +262,14 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
   }
   if (kind == 0) {
     const int nkh = Kp > 32 ? 2 : 1;
-    // y: weights rotated to the ring (slot = tile row & 3), bins completed per tile row
+    // y: segments, weights rotated to the ring of the bin's segment (slot = segment row & 3), bins
+    // completed per segment row
+    const int nseg = PH >= 4 ? 2 : 1;
+    const int b_mid = nseg == 2 ? PH / 2 : PH;
+    const int r0_1 = nseg == 2 ? ay->start[b_mid] : 0;
     if (lane < PH) {
-      const int rot = ay->start[lane] & 3;
+      const int r0 = lane >= b_mid ? r0_1 : 0;
+      const int rot = (ay->start[lane] - r0) & 3;
       const RbF4 w = ay->w[lane];
       RbF4 r;
       r.x = rot == 0 ? w.x : (rot == 1 ? w.w : (rot == 2 ? w.z : w.y));
@@ -249,12 +279,25 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
       m->wrot[lane] = r;
     }
     if (lane < RX_RMAX / 4 + 2) {
-      uint32_t word = 0;
-      for (int bn = 0; bn < PH; ++bn) {
-        const int r = ay->start[bn] + 3;
-        if ((r >> 2) == lane) word += 1u << (8 * (r & 3));
+      for (int sg = 0; sg < nseg; ++sg) {
+        const int bb0 = sg ? b_mid : 0, bb1 = sg ? PH : b_mid, r0 = sg ? r0_1 : 0;
+        uint32_t word = 0;
+        for (int bn = bb0; bn < bb1; ++bn) {
+          const int r = ay->start[bn] - r0 + 3;
+          if ((r >> 2) == lane) word += 1u << (8 * (r & 3));
+        }
+        m->mw[sg][lane] = word;
       }
-      m->mw[lane] = word;
+    }
+    if (lane == 0) {
+      m->nseg = nseg;
+      m->seg_b0[0] = 0;
+      m->seg_b0[1] = b_mid;
+      m->seg_b0[2] = PH;
+      m->seg_r0[0] = 0;
+      m->seg_r0[1] = r0_1;
+      m->seg_rows[0] = ay->start[b_mid - 1] + 4;
+      m->seg_rows[1] = nseg == 2 ? ay->start[PH - 1] + 4 - r0_1 : 0;
     }
     // x: dense weights, accumulated in full precision in the "hi" planes, then split
     float4* bz = reinterpret_cast<float4*>(bmat);
@@ -315,7 +358,7 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
 // tile: [R rows][cs channels][nqh strips] RbF4; V rows (c, ph) at vbase + ((cbase + c) * 16 + ph) * 128.
 __device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, int cs, int nqh,
                                          const uint32_t* __restrict__ mw, const RbF4* __restrict__ wrot,
-                                         unsigned char* vhi, int cbase, int lane) {
+                                         int ph0, unsigned char* vhi, int cbase, int lane) {
   const int nitems = cs * nqh;
   const uint32_t magic = rx_magic((uint32_t)nqh);
   for (int u = lane; u < nitems; u += 32) {
@@ -323,8 +366,8 @@ __device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, i
     const int s = u - c * nqh;
     const RbF4* rows = tile + u;
     unsigned char* vrow = vhi + (size_t)((cbase + c) * 16) * 128;
-    const RbF4* wr = wrot;
-    int ph = 0;
+    const RbF4* wr = wrot + ph0;
+    int ph = ph0;
     RbF4 W0, W1, W2, W3;
     W0.x = W0.y = W0.z = W0.w = 0.f;
     W1 = W0;
@@ -384,10 +427,10 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     for (int i = 0; i < RX_S; ++i) {
       rp_mbar_init(&bars->tile_full[i], 1);
-      rp_mbar_init(&bars->tile_empty[i], 1);
+      rp_mbar_init(&bars->tile_empty[i], 2);
     }
     for (int i = 0; i < RX_SV; ++i) {
-      rp_mbar_init(&bars->v_full[i], 8);
+      rp_mbar_init(&bars->v_full[i], 16);
       rp_mbar_init(&bars->v_empty[i], 1);
     }
     for (int i = 0; i < RX_SD; ++i) {
@@ -407,6 +450,11 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = tmem_base_s;
+#ifdef RX_PROFILE
+  if (lane < 12) rx_prof_acc[lane] = 0;
+  __syncwarp();
+  const long long rx_role_t0 = clock64();
+#endif
 
 #define RX_ITEM_LOOP for (int it = blockIdx.x, p = 0; it < n_items; it += gridDim.x, ++p)
 #define RX_META()                                                     \
@@ -421,8 +469,17 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
       const int ps = p % RX_NP;
       rx_wait(&bars->plan_empty[ps], ((uint32_t)(p / RX_NP) & 1u) ^ 1u, 2, p);
       const int sl = it / K, k = it - sl * K;
+#ifdef RX_PROFILE
+      const long long pl_t0 = clock64();
+#endif
       rx_build_plan(reinterpret_cast<RxMeta*>(smem + RX_OFF_META + ps * 1024), smem + RX_OFF_B + ps * 8192,
                     ay, lane, lv, N, C, rois, levels, k, sl * RX_CS, PH, PW, sampling_ratio, out);
+#ifdef RX_PROFILE
+      if (lane == 0) {
+        rx_prof_acc[10] += clock64() - pl_t0;
+        rx_prof_acc[11] += 1;
+      }
+#endif
       if (lane == 0) rx_arrive(&bars->plan_full[ps]);
     }
   } else if (warp == RX_W_TMA) {
@@ -535,7 +592,9 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   } else if (warp >= RX_W_EPI0 && warp < RX_W_EPI0 + 4) {
     // ===== epilogue =====
     const int quad = warp & 3, etid = tid - RX_W_EPI0 * 32;
-    uint32_t d = 0, ob = 0;
+    uint64_t evict_first;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(evict_first));
+    uint32_t d = 0;
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
@@ -558,10 +617,10 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) rx_arrive(&bars->d_empty[ds]);
-          // the stage buffer was last read by the bulk store issued two tiles ago
-          if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          // the stage buffer was last read by the bulk store of the previous tile
+          if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          unsigned char* stage = smem + RX_OFF_OST + ob * RX_OSTAGE;
+          unsigned char* stage = smem + RX_OFF_OST;
           const int row = quad * 32 + lane, c = row >> 4, ph = row & 15;
           if (ph < PH) {
             float* dst = reinterpret_cast<float*>(stage) + c * P + ph * PW;
@@ -579,8 +638,15 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           }
           rp_fence_proxy_async_smem();
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (etid == 0) rp_bulk_store(outp + (size_t)mt * 8 * P, stage, (uint32_t)(8 * P * 4));
-          ob ^= 1u;
+          if (etid == 0) {
+            // the output is written once and never read here: evict-first keeps the feature planes in L2
+            asm volatile(
+                "cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(
+                    outp + (size_t)mt * 8 * P),
+                "r"(rp_smem_addr(stage)), "r"((uint32_t)(8 * P * 4)), "l"(evict_first)
+                : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
         }
       } else if (M->kind == 1) {
         const int total = M->nch * P, H = M->H, W = M->W;
@@ -602,31 +668,47 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   } else if (warp >= RX_W_Y0) {
     // ===== y-pass =====
     const int yw = warp - RX_W_Y0;
-    uint32_t q = 0, v = 0;
+    uint32_t q0 = 0, v0 = 0, u0 = 0;  // sub-chunks, V tiles, work units (sub-chunk x segment) before this item
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
-        const int R = M->R, cs = M->cs, nkh = M->nkh, nq = M->nq, nsc = 8 / cs;
-        for (int mt = 0; mt < M->nmt; ++mt)
-          for (int kh = 0; kh < nkh; ++kh, ++v) {
-            const int vs = v % RX_SV;
-            const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
-            for (int sc = 0; sc < nsc; ++sc, ++q) {
-              if ((int)(q % RX_NY) != yw) continue;
-              const int ts = q % RX_S;
-              rx_wait_ge(&bars->v_freed, v + 1u - (uint32_t)RX_SV, 7, v);  // the MMAs of tile v - SV are done
-              rx_wait_ge(&bars->issued, q + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
-              rx_wait(&bars->tile_full[ts], (q / RX_S) & 1u, 8, q);
-              rx_ypass(reinterpret_cast<const RbF4*>(smem + RX_OFF_TILE + ts * RX_SLOT), R, cs, nqh, M->mw,
-                       M->wrot, smem + RX_OFF_V + vs * 32768, sc * cs, lane);
-              rp_fence_proxy_async_smem();
-              __syncwarp();
-              if (lane == 0) {
-                rx_arrive(&bars->tile_empty[ts]);
-                rx_arrive_n(&bars->v_full[vs], (uint32_t)cs);
-              }
-            }
+        // unit j of the item = (((mt * nkh + kh) * nsc + sc) * nseg + sg); nkh, nsc, nseg are powers of
+        // two, so this warp's units (u0 + j == yw mod NY) are decoded with shifts, not walked
+        const int cs = M->cs, nkh = M->nkh, nq = M->nq, nseg = M->nseg;
+        const int lseg = nseg >> 1, lsc = cs == 8 ? 0 : (cs == 4 ? 1 : 2), lkh = nkh >> 1;
+        const int nunits = M->nmt << (lkh + lsc + lseg);
+        for (int j = (int)((uint32_t)(yw + RX_NY) - u0 % RX_NY) % RX_NY; j < nunits; j += RX_NY) {
+          const int sg = j & (nseg - 1);
+          const int qi = j >> lseg, sc = qi & ((1 << lsc) - 1);
+          const int vi = qi >> lsc, kh = vi & (nkh - 1);
+          const uint32_t q = q0 + (uint32_t)qi, v = v0 + (uint32_t)vi;
+          const int vs = v % RX_SV, ts = q % RX_S;
+          const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
+          rx_wait_ge(&bars->v_freed, v + 1u - (uint32_t)RX_SV, 7, v);  // the MMAs of tile v - SV are done
+          rx_wait_ge(&bars->issued, q + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
+          rx_wait(&bars->tile_full[ts], (q / RX_S) & 1u, 8, q);
+#ifdef RX_PROFILE
+          const long long yp_t0 = clock64();
+#endif
+          rx_ypass(reinterpret_cast<const RbF4*>(smem + RX_OFF_TILE + ts * RX_SLOT) + M->seg_r0[sg] * cs * nqh,
+                   M->seg_rows[sg], cs, nqh, M->mw[sg], M->wrot, M->seg_b0[sg], smem + RX_OFF_V + vs * 32768,
+                   sc * cs, lane);
+          rp_fence_proxy_async_smem();
+          __syncwarp();
+#ifdef RX_PROFILE
+          if (lane == 0) {
+            rx_prof_acc[10] += clock64() - yp_t0;
+            rx_prof_acc[11] += 1;
           }
+#endif
+          if (lane == 0) {
+            rx_arrive_n(&bars->tile_empty[ts], (uint32_t)(2 / nseg));
+            rx_arrive_n(&bars->v_full[vs], (uint32_t)(cs * 2 / nseg));
+          }
+        }
+        u0 += (uint32_t)nunits;
+        q0 += (uint32_t)(nunits >> lseg);
+        v0 += (uint32_t)(M->nmt << lkh);
       }
       __syncwarp();
       if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
@@ -634,10 +716,29 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   }
 #undef RX_ITEM_LOOP
 #undef RX_META
+#ifdef RX_PROFILE
+  if (lane == 0) rx_prof_acc[0] = clock64() - rx_role_t0;
+  __syncwarp();
+  if (blockIdx.x == 0 && rx_dbg && lane < 12)
+    reinterpret_cast<long long*>(rx_dbg + 256)[warp * 12 + lane] = rx_prof_acc[lane];
+#endif
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == RX_W_MMA)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+}
+
+// Rows of `W` floats -> rows of `pitch` floats (pitch % 4 == 0, zero padded): a level whose rows are not
+// 16-byte multiples (P5 of an 800 x 1344 batch is 25 x 42) cannot be a TMA tensor as it lies; it is
+// re-pitched into a stream-ordered scratch buffer first (a few MB; the big levels never need it).
+__global__ void rx_repitch_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t rows, int W,
+                                  int pitch) {
+  const size_t total = rows * (size_t)pitch;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = i / (size_t)pitch;
+    const int x = (int)(i - r * (size_t)pitch);
+    dst[i] = x < W ? src[r * (size_t)W + x] : 0.f;
+  }
 }
 
 // ---- host: tensor maps (x, plane, y) per level, kept in device memory ------------------------------
@@ -663,14 +764,14 @@ rx_encode_fn rx_encoder() {
 struct RxMapEntry {
   const float* ptr;
   long long planes;
-  int H, W, ok;
+  int H, W, pitch, ok;
   unsigned long long stamp;
   CUtensorMap m[RX_NMAP];
 };
 
 // Fills maps->m[l] for level l; a small host cache keeps repeated calls on the same tensors free of
 // encoding (36 cuTensorMapEncodeTiled calls per level otherwise).  Returns 0 on failure.
-int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H, int W) {
+int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H, int W, int pitch) {
   static std::mutex mu;
   static RxMapEntry cache[32];
   static unsigned long long clock_ = 0;
@@ -680,7 +781,7 @@ int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H
   int victim = 0;
   for (int i = 0; i < 32; ++i) {
     RxMapEntry& e = cache[i];
-    if (e.ok && e.ptr == ptr && e.planes == planes && e.H == H && e.W == W) {
+    if (e.ok && e.ptr == ptr && e.planes == planes && e.H == H && e.W == W && e.pitch == pitch) {
       e.stamp = ++clock_;
       memcpy(maps->m[l], e.m, sizeof(e.m));
       return 1;
@@ -691,7 +792,7 @@ int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H
   e.ok = 0;
   static const int rows_of[3] = {8, 4, 2};
   const cuuint64_t gdim[3] = {(cuuint64_t)W, (cuuint64_t)planes, (cuuint64_t)H};
-  const cuuint64_t gstride[2] = {(cuuint64_t)H * W * 4, (cuuint64_t)W * 4};
+  const cuuint64_t gstride[2] = {(cuuint64_t)H * pitch * 4, (cuuint64_t)pitch * 4};
   const cuuint32_t estride[3] = {1, 1, 1};
   for (int wi = 0; wi < 4; ++wi)
     for (int ri = 0; ri < 3; ++ri)
@@ -700,13 +801,14 @@ int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H
         const CUresult r = enc(&e.m[(wi * 3 + ri) * 3 + ci], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
                                const_cast<float*>(ptr), gdim, gstride, box, estride,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                               CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return 0;
       }
   e.ptr = ptr;
   e.planes = planes;
   e.H = H;
   e.W = W;
+  e.pitch = pitch;
   e.ok = 1;
   e.stamp = ++clock_;
   memcpy(maps->m[l], e.m, sizeof(e.m));
@@ -725,25 +827,53 @@ extern "C" RP_API int rp_debug_rx_timeouts(int* out, int n) {
 
 int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K, int PH,
                int PW, float sampling_ratio, float* out, cudaStream_t st) {
-  // eligibility: fixed sampling grid, bins fit 16 accumulator rows / columns, whole 8-channel groups,
-  // every level a legal TMA tensor (16-byte aligned rows and base)
+  // eligibility: fixed sampling grid, bins fit 16 accumulator rows / columns, whole 8-channel groups;
+  // a level whose rows or base are not 16-byte aligned is re-pitched into a scratch copy for the TMA
   if (!(sampling_ratio > 0) || (int)sampling_ratio > RB_MAXG || PH > 16 || PW > 16 || (C & 7)) return 1;
   const long long planes = (long long)N * C;
   if (planes > 0x7fffffffLL) return 1;
-  for (int l = 0; l < lv.L; ++l)
-    if ((lv.W[l] & 3) || (reinterpret_cast<uintptr_t>(lv.feat[l]) & 15) || lv.H[l] < 1 || lv.W[l] < 4) return 1;
   if (lv.L > RX_MAXL) return 1;
-  static RxMaps maps;  // 15 KB: filled under the lock below, copied into the launch by value
-  static std::mutex launch_mu;
-  std::lock_guard<std::mutex> lock(launch_mu);
   for (int l = 0; l < lv.L; ++l)
-    if (!rx_level_maps(&maps, l, lv.feat[l], planes, lv.H[l], lv.W[l])) return 1;
+    if (lv.H[l] < 1 || lv.W[l] < 4 || (reinterpret_cast<uintptr_t>(lv.feat[l]) & 3)) return 1;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     attr_err = cudaFuncSetAttribute(rx_pool_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RX_SMEM);
   });
   if (attr_err != cudaSuccess) return (int)attr_err;
+  const int nsl = (C + RX_CS - 1) / RX_CS;
+  const long long n_items = (long long)K * nsl;
+  if (n_items > 0x7fffffffLL) return RP_E_LIMIT;
+  static RxMaps maps;  // 23 KB: filled under the lock below, copied into the launch by value
+  static std::mutex launch_mu;
+  std::lock_guard<std::mutex> lock(launch_mu);
+  float* scratch[RX_MAXL] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  auto release = [&]() {
+    for (int l = 0; l < RX_MAXL; ++l)
+      if (scratch[l]) (void)cudaFreeAsync(scratch[l], st);
+  };
+  for (int l = 0; l < lv.L; ++l) {
+    const float* ptr = lv.feat[l];
+    int pitch = lv.W[l];
+    if ((lv.W[l] & 3) || (reinterpret_cast<uintptr_t>(ptr) & 15)) {
+      pitch = (lv.W[l] + 3) & ~3;
+      const size_t rows = (size_t)planes * lv.H[l];
+      if (cudaMallocAsync(reinterpret_cast<void**>(&scratch[l]), rows * pitch * sizeof(float), st) != cudaSuccess) {
+        (void)cudaGetLastError();
+        scratch[l] = nullptr;
+        release();
+        return 1;
+      }
+      size_t blocks = (rows * pitch + 255) / 256;
+      if (blocks > (size_t)RP_NUM_SMS * 16) blocks = (size_t)RP_NUM_SMS * 16;
+      rx_repitch_kernel<<<(unsigned)blocks, 256, 0, st>>>(ptr, scratch[l], rows, lv.W[l], pitch);
+      ptr = scratch[l];
+    }
+    if (!rx_level_maps(&maps, l, ptr, planes, lv.H[l], lv.W[l], pitch)) {
+      release();
+      return 1;
+    }
+  }
   static int* dbg_host = nullptr;
   if (!dbg_host && rp_env_int("RP_RX_DEBUG", 0)) {
     int* dev = nullptr;
@@ -754,12 +884,11 @@ int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
       rx_dbg_host_ptr = dbg_host;
     }
   }
-  const int nsl = (C + RX_CS - 1) / RX_CS;
-  const long long n_items = (long long)K * nsl;
-  if (n_items > 0x7fffffffLL) return RP_E_LIMIT;
   const int grid = (int)(n_items < RP_NUM_SMS ? n_items : RP_NUM_SMS);
   rx_pool_fwd_kernel<<<grid, RX_THREADS, RX_SMEM, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
                                                        out, maps, (int)n_items);
-  RP_LAUNCH_CHECK();
+  const cudaError_t launch_err = cudaGetLastError();
+  release();
+  if (launch_err != cudaSuccess) return (int)launch_err;
   return RP_OK;
 }

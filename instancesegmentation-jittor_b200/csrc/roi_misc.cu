@@ -152,6 +152,45 @@ box_mask_kernel(const float* __restrict__ boxes, int h, int w, float padding, in
   }
 }
 
+// ---- Pose2Seg paste-back: cv2.warpAffine(WARP_INVERSE_MAP + INTER_LINEAR) + "> 0.5" -----------------
+// Pose2Seg.jittor/modeling/build_model.py:31-43.  One thread per 4 output pixels of one instance; the
+// source map (64 x 64 x 2 floats = 32 KB) stays in L1/L2; OpenCV's fixed-point coordinates and weight
+// table (include/roipath_math.h, shared with the oracle, which is pinned against cv2 itself).
+// HBM-bound on the output: width*height bytes per instance, written as 4-byte words.
+__global__ void __launch_bounds__(256)
+affine_paste_kernel(const float* __restrict__ pred, const double* __restrict__ M, int h, int w, int C, int c,
+                    int width, int height, uint8_t* __restrict__ out) {
+  const int i = blockIdx.y;
+  const float* src = pred + (size_t)i * h * w * C;
+  double m[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) m[k] = M[6 * (size_t)i + k];
+  const size_t plane = (size_t)width * height;
+  uint8_t* dst = out + (size_t)i * plane;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(dst) & 3) == 0);
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g * 4 < plane; g += (size_t)gridDim.x * blockDim.x) {
+    uint32_t packed = 0;
+    const size_t p0 = g * 4;
+    const int nv = plane - p0 < 4 ? (int)(plane - p0) : 4;
+    int y = (int)(p0 / width), x = (int)(p0 - (size_t)y * width);
+    for (int j = 0; j < nv; ++j) {
+      int sx, sy, fx, fy;
+      rp_warp_affine_coord(m, x, y, &sx, &sy, &fx, &fy);
+      const float v = rp_warp_affine_sample(src, h, w, C, c, sx, sy, fx, fy);
+      packed |= (v > 0.5f ? 1u : 0u) << (8 * j);
+      if (++x == width) {
+        x = 0;
+        ++y;
+      }
+    }
+    if (aligned && nv == 4) {
+      __stcs(reinterpret_cast<uint32_t*>(dst + p0), packed);
+    } else {
+      for (int j = 0; j < nv; ++j) dst[p0 + j] = (uint8_t)(packed >> (8 * j));
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -222,6 +261,22 @@ int rp_box_masks(const float* boxes, int n, int h, int w, float padding, int cro
   if (gx > 4096) gx = 4096;
   box_mask_kernel<<<dim3(gx, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(boxes, h, w, padding, crop ? 1 : 0,
                                                                          masks_in, masks_out, indicator);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_affine_paste(const float* pred, const double* M, int n, int h, int w, int C, int channel, int width,
+                    int height, uint8_t* out, void* stream) {
+  if (n == 0) return RP_OK;
+  if (!pred || !M || !out || n < 0 || h < 1 || w < 1 || C < 1 || channel < 0 || channel >= C || width < 1 ||
+      height < 1)
+    return RP_E_ARG;
+  if (n > 65535 || h > 32767 || w > 32767) return RP_E_LIMIT;
+  const size_t groups = ((size_t)width * height + 3) / 4;
+  unsigned gx = (unsigned)((groups + 255) / 256);
+  if (gx > 2048) gx = 2048;
+  affine_paste_kernel<<<dim3(gx, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(pred, M, h, w, C, channel, width,
+                                                                              height, out);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

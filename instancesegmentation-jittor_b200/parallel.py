@@ -28,8 +28,21 @@ def rebase_rois(rois, begin):
 
 
 def pack_masks(masks_u8):
-    """uint8 0/1 masks [m, H, W] -> bit-packed uint8 [m, ceil(H*W/8)] (LSB first)."""
+    """uint8 0/1 masks [m, H, W] -> bit-packed uint8 [m, ceil(H*W/8)] (LSB first).  CUDA tensors go
+    through rp_pack_mask_bits (one pass, npix bytes in, npix/8 out); the torch form below only
+    serves CPU tensors (the gloo tests of the gather logic)."""
     m = masks_u8.shape[0]
+    if masks_u8.is_cuda:
+        import ctypes
+        from . import _lib
+        src = masks_u8.to(torch.uint8).contiguous()
+        npix = int(src[0].numel()) if m else 0
+        out = torch.empty((m, (npix + 7) // 8), dtype=torch.uint8, device=src.device)
+        if m and npix:
+            rc = _lib.lib().rp_pack_mask_bits(ctypes.c_void_p(src.data_ptr()), m, npix,
+                                              ctypes.c_void_p(out.data_ptr()), _lib.stream_ptr(src.device))
+            _lib.check(rc, "rp_pack_mask_bits")
+        return out
     flat = masks_u8.reshape(m, -1).to(torch.uint8)
     pad = (-flat.shape[1]) % 8
     if pad:

@@ -331,3 +331,67 @@ def postprocess(det_output, w, h, batch_idx=0, interpolation_mode="bilinear",
     masks, iboxes = mask_assemble(dets["proto"], coeff.contiguous(), boxes.contiguous(), h, w,
                                   crop_masks)
     return classes, scores, iboxes, masks.bool()
+
+
+# ------------------------------------------------------------------------------------------------
+# lincomb mask loss (training twin of the assembly; multibox_loss.py:616-660)
+# ------------------------------------------------------------------------------------------------
+def lincomb_mask_loss_raw(proto, coef, mask_t, boxes=None, scale=None):
+    """One launch: per-instance losses [n] and the gradients of their sum (d_proto [H,W,D],
+    d_coef [n,D]).  proto [H,W,D], coef [n,D], mask_t [H,W,n], boxes [n,4] relative xyxy or None
+    (no crop), scale [n] or None."""
+    proto = _lib.as_f32(proto, "proto")
+    H, W, D = (int(v) for v in proto.shape)
+    n = int(coef.shape[0])
+    dev = proto.device
+    loss = torch.empty((n,), dtype=_F32, device=dev)
+    d_proto = torch.empty((H, W, D), dtype=_F32, device=dev)
+    d_coef = torch.empty((n, D), dtype=_F32, device=dev)
+    if n:
+        coef = _lib.as_f32(coef, "coef")
+        mask_t = _lib.as_f32(mask_t, "mask_t")
+        if tuple(mask_t.shape) != (H, W, n) or tuple(coef.shape) != (n, D):
+            raise ValueError("mask_t must be [H,W,n] and coef [n,D]")
+        boxes = _lib.as_f32(boxes, "boxes") if boxes is not None else None
+        scale = _lib.as_f32(scale, "scale") if scale is not None else None
+    rc = _lib.lib().rp_lincomb_mask_loss(
+        _lib.dptr(proto, _F32), _lib.dptr(coef, _F32) if n else None, _lib.dptr(mask_t, _F32) if n else None,
+        _lib.dptr(boxes, _F32) if n else None, _lib.dptr(scale, _F32) if n else None, H, W, D, n,
+        _lib.dptr(loss, _F32), _lib.dptr(d_proto, _F32), _lib.dptr(d_coef, _F32), _lib.stream_ptr(dev))
+    _lib.check(rc, "rp_lincomb_mask_loss")
+    return loss, d_proto, d_coef
+
+
+class _LincombMaskLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, proto, coef, mask_t, boxes, scale):
+        loss, d_proto, d_coef = lincomb_mask_loss_raw(proto.detach(), coef.detach(), mask_t, boxes, scale)
+        ctx.save_for_backward(d_proto, d_coef)
+        ctx.mark_non_differentiable(loss)
+        return loss.sum(), loss
+
+    @staticmethod
+    def backward(ctx, g_total, _g_per_instance):
+        d_proto, d_coef = ctx.saved_tensors
+        return g_total * d_proto, g_total * d_coef, None, None, None
+
+
+def lincomb_mask_loss(proto, coef, mask_t, boxes=None, normalize_emulate_roi_pooling=False, weight=1.0):
+    """The per-image body of MultiBoxLoss.lincomb_mask_loss (multibox_loss.py:616-660) for the
+    sigmoid activation: returns (sum of the per-instance losses -- differentiable w.r.t. proto and
+    coef --, per-instance losses).  boxes = pos_gt_box_t (relative xyxy) when mask_proto_crop;
+    normalize_emulate_roi_pooling divides instance i by gt_w*gt_h (in mask pixels) and multiplies by
+    H*W when cropping (:645-649); `weight` folds old_num_pos/num_pos (:652-653)."""
+    H, W = int(proto.shape[0]), int(proto.shape[1])
+    n = int(coef.shape[0])
+    scale = None
+    if normalize_emulate_roi_pooling or weight != 1.0:
+        scale = torch.full((n,), float(weight), dtype=_F32, device=proto.device)
+        if normalize_emulate_roi_pooling:
+            if boxes is None:
+                raise ValueError("normalize_emulate_roi_pooling needs the gt boxes")
+            w_roi = float(H * W)  # mask_proto_crop is on whenever boxes are given
+            gw = (boxes[:, 2] - boxes[:, 0]).to(_F32) * W
+            gh = (boxes[:, 3] - boxes[:, 1]).to(_F32) * H
+            scale = scale / gw / gh * w_roi
+    return _LincombMaskLoss.apply(proto, coef, mask_t, boxes, scale)

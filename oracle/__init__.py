@@ -459,3 +459,36 @@ def expf(x):
 
 def sigmoidf(x):
     return float(lib().orc_sigmoidf(ctypes.c_float(x)))
+
+
+def lincomb_mask_loss(proto, coef, mask_t, boxes=None, scale=None):
+    """Returns (loss [n], d_proto [H,W,D], d_coef [n,D]) of sum_i loss[i]."""
+    proto, pp = _f(proto)
+    coef, cp = _f(coef)
+    mask_t, mp = _f(mask_t)
+    H, W, D = proto.shape
+    n = coef.shape[0]
+    bp = sp = None
+    if boxes is not None:
+        boxes, bp = _f(boxes)
+    if scale is not None:
+        scale, sp = _f(scale)
+    loss = np.zeros((n,), np.float32)
+    dpr = np.zeros((H, W, D), np.float32)
+    dco = np.zeros((n, D), np.float32)
+    lib().orc_lincomb_mask_loss(pp, cp, mp, bp, sp, H, W, D, n, loss.ctypes.data_as(_f32p),
+                                dpr.ctypes.data_as(_f32p), dco.ctypes.data_as(_f32p))
+    return loss, dpr, dco
+
+
+def affine_paste(pred, M, width, height, channel=1, return_values=False):
+    """pred [n,h,w,C] float32, M [n,2,3] float64 (dst -> src) -> u8 [n,height,width] (value > 0.5)."""
+    pred, pp = _f(pred)
+    M = np.ascontiguousarray(M, np.float64).reshape(-1, 6)
+    n, h, w, C = pred.shape
+    out = np.zeros((n, height, width), np.uint8)
+    vals = np.zeros((n, height, width), np.float32) if return_values else None
+    lib().orc_affine_paste(pp, M.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), n, h, w, C, int(channel),
+                           int(width), int(height), out.ctypes.data_as(_u8p),
+                           vals.ctypes.data_as(_f32p) if return_values else None)
+    return (out, vals) if return_values else out

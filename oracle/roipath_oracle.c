@@ -1143,3 +1143,82 @@ ORC_API float orc_iou_plus1(const float* a, const float* b) {
   return rp_iou_plus1(a[0], a[1], a[2], a[3], rp_area_plus1(a[0], a[1], a[2], a[3]), b[0], b[1],
                       b[2], b[3], rp_area_plus1(b[0], b[1], b[2], b[3]));
 }
+
+/* yol/layers/modules/multibox_loss.py:616-660 (lincomb_mask_loss, sigmoid activation), per image:
+ *   pred = sigmoid(proto @ coef^T) (:616-618); crop(pred, boxes) when boxes != NULL (box_utils.py:355-378);
+ *   bce = -(t*log(max(p,1e-20)) + (1-t)*log(max(1-p,1e-20))), p = clamp(pred,0,1) (:8-9,:632);
+ *   loss[i] = scale[i] * sum_{y,x} bce[y,x,i]  (scale NULL = 1; :645-653 are folded into scale by the caller)
+ * and the gradients of sum_i loss[i] w.r.t. proto [H,W,D] and coef [n,D] (what autograd produces:
+ * the max(.,1e-20) clamps pass no gradient below the clamp, the crop zeroes it outside the box).
+ * Sums are accumulated in double (the checker should be the more exact side). */
+ORC_API void orc_lincomb_mask_loss(const float* proto, const float* coef, const float* mask_t,
+                                   const float* boxes, const float* scale, int H, int W, int D, int n,
+                                   float* loss, float* d_proto, float* d_coef) {
+  double* lacc = (double*)calloc((size_t)(n > 0 ? n : 1), sizeof(double));
+  double* dc = (double*)calloc((size_t)(n > 0 ? n : 1) * D, sizeof(double));
+  float* cb = (float*)malloc(sizeof(float) * 4 * (size_t)(n > 0 ? n : 1));
+  for (int i = 0; i < n; ++i) {
+    float x1 = 0.f, x2 = (float)W, y1 = 0.f, y2 = (float)H;
+    if (boxes) {
+      orc_sanitize(boxes[4 * i], boxes[4 * i + 2], W, 1, &x1, &x2);
+      orc_sanitize(boxes[4 * i + 1], boxes[4 * i + 3], H, 1, &y1, &y2);
+    }
+    cb[4 * i] = x1; cb[4 * i + 1] = x2; cb[4 * i + 2] = y1; cb[4 * i + 3] = y2;
+  }
+  for (int y = 0; y < H; ++y)
+    for (int x = 0; x < W; ++x) {
+      const size_t pix = (size_t)y * W + x;
+      const float* pr = proto + pix * D;
+      double* dp = (double*)calloc((size_t)D, sizeof(double));
+      for (int i = 0; i < n; ++i) {
+        const float* c = coef + (size_t)i * D;
+        float z = 0.f;
+        for (int k = 0; k < D; ++k) z = fmaf(pr[k], c[k], z);
+        const float t = mask_t[pix * n + i];
+        const int inside = (float)x >= cb[4 * i] && (float)x < cb[4 * i + 1] && (float)y >= cb[4 * i + 2] &&
+                           (float)y < cb[4 * i + 3];
+        const float p = inside ? 1.0f / (1.0f + expf(-z)) : 0.f;
+        const float q = 1.0f - p;
+        const float bce = -(t * logf(p > 1e-20f ? p : 1e-20f) + (1.0f - t) * logf(q > 1e-20f ? q : 1e-20f));
+        const float s = scale ? scale[i] : 1.0f;
+        lacc[i] += (double)s * (double)bce;
+        if (inside) {
+          const float gpos = p > 1e-20f ? -t * q : 0.f;
+          const float gneg = q > 1e-20f ? (1.0f - t) * p : 0.f;
+          const double g = (double)s * (double)(gpos + gneg);
+          for (int k = 0; k < D; ++k) {
+            dp[k] += g * c[k];
+            dc[(size_t)i * D + k] += g * pr[k];
+          }
+        }
+      }
+      for (int k = 0; k < D; ++k) d_proto[pix * D + k] = (float)dp[k];
+      free(dp);
+    }
+  for (int i = 0; i < n; ++i) loss[i] = (float)lacc[i];
+  for (size_t i = 0; i < (size_t)n * D; ++i) d_coef[i] = (float)dc[i];
+  free(lacc); free(dc); free(cb);
+}
+
+/* Pose2Seg.jittor/modeling/build_model.py:31-43 (warpAffine): cv2.warpAffine(predmap, H_e2e[0:2],
+ * (width, height), WARP_INVERSE_MAP + INTER_LINEAR, BORDER_CONSTANT), channel `c` of the result,
+ * > 0.5 -> 1 else 0.  pred [n,h,w,C] float; M [n,6] double (dst -> src); out [n,height,width] u8;
+ * val_out (optional) receives the interpolated float values.  Arithmetic: include/roipath_math.h
+ * (OpenCV's 10-bit fixed-point coordinates and 32x32 weight table); pinned against cv2 itself in
+ * tests/test_oracle_golden.py. */
+ORC_API void orc_affine_paste(const float* pred, const double* M, int n, int h, int w, int C, int c,
+                              int width, int height, uint8_t* out, float* val_out) {
+  for (int i = 0; i < n; ++i) {
+    const float* src = pred + (size_t)i * h * w * C;
+    const double* Mi = M + 6 * (size_t)i;
+    for (int y = 0; y < height; ++y)
+      for (int x = 0; x < width; ++x) {
+        int sx, sy, fx, fy;
+        rp_warp_affine_coord(Mi, x, y, &sx, &sy, &fx, &fy);
+        const float v = rp_warp_affine_sample(src, h, w, C, c, sx, sy, fx, fy);
+        const size_t o = ((size_t)i * height + y) * width + x;
+        out[o] = v > 0.5f ? 1 : 0;
+        if (val_out) val_out[o] = v;
+      }
+  }
+}

@@ -94,3 +94,59 @@ def test_full_size_properties():
     outside = (xs < (b[:, 0] - 40).view(-1, 1, 1)) | (xs > (b[:, 2] + 40).view(-1, 1, 1)) | \
               (ys < (b[:, 1] - 40).view(-1, 1, 1)) | (ys > (b[:, 3] + 40).view(-1, 1, 1))
     assert int((out.bool() & outside).sum()) == 0
+
+
+@pytest.mark.parametrize("shape", [(3, 550, 550), (5, 9, 13), (2, 800, 1333), (1, 1, 7), (4, 16, 64)])
+def test_pack_mask_bits_matches_numpy(shape):
+    # rp_pack_mask_bits (the final gather's payload) against numpy.packbits, LSB first
+    rng = np.random.default_rng(shape[1])
+    m = (rng.random(shape) > 0.6).astype(np.uint8)
+    got = rp.parallel.pack_masks(T(m)).cpu().numpy()
+    exp = np.packbits(m.reshape(shape[0], -1), axis=1, bitorder="little")
+    np.testing.assert_array_equal(got, exp)
+    back = rp.parallel.unpack_masks(T(exp), shape[1], shape[2]).cpu().numpy()
+    np.testing.assert_array_equal(back, m)
+
+
+@pytest.mark.parametrize("n,H,W,crop,scaled", [(9, 23, 31, True, True), (100, 138, 138, True, True),
+                                               (37, 138, 138, False, False), (1, 5, 7, True, False),
+                                               (0, 20, 20, True, False)])
+def test_lincomb_mask_loss_matches_oracle(n, H, W, crop, scaled):
+    # rp_lincomb_mask_loss (multibox_loss.py:616-660 forward + backward) against the oracle, 1e-5
+    rng = np.random.default_rng(n + H)
+    D = 32
+    proto = np.maximum(rng.standard_normal((H, W, D)), 0).astype(np.float32)
+    coef = np.tanh(rng.standard_normal((n, D))).astype(np.float32)
+    mask_t = (rng.random((H, W, n)) > 0.6).astype(np.float32)
+    c = rng.uniform(0.2, 0.8, (n, 2))
+    wh = rng.uniform(0.1, 0.5, (n, 2))
+    boxes = np.concatenate([c - wh / 2, c + wh / 2], 1).astype(np.float32)
+    scale = None
+    if scaled:
+        scale = (H * W / ((boxes[:, 2] - boxes[:, 0]) * W) / ((boxes[:, 3] - boxes[:, 1]) * H)).astype(np.float32)
+    bx = boxes if crop else None
+    loss, dp, dc = rp.lincomb_mask_loss_raw(T(proto), T(coef), T(mask_t), T(bx) if bx is not None else None,
+                                            T(scale) if scale is not None else None)
+    if n == 0:
+        assert loss.numel() == 0 and float(dp.abs().max()) == 0.0
+        return
+    el, edp, edc = oracle.lincomb_mask_loss(proto, coef, mask_t, bx, scale)
+    np.testing.assert_allclose(loss.cpu().numpy(), el, rtol=1e-5)
+    np.testing.assert_allclose(dp.cpu().numpy(), edp, rtol=1e-5, atol=1e-5 * np.abs(edp).max())
+    np.testing.assert_allclose(dc.cpu().numpy(), edc, rtol=1e-5, atol=1e-5 * np.abs(edc).max())
+
+
+def test_lincomb_mask_loss_autograd():
+    # the autograd wrapper: gradients of 0.5 * total reach proto and coef scaled by the upstream factor
+    rng = np.random.default_rng(0)
+    proto = torch.from_numpy(np.maximum(rng.standard_normal((20, 24, 32)), 0).astype(np.float32)).to(DEV).requires_grad_(True)
+    coef = torch.from_numpy(np.tanh(rng.standard_normal((6, 32))).astype(np.float32)).to(DEV).requires_grad_(True)
+    mask_t = T((rng.random((20, 24, 6)) > 0.5).astype(np.float32))
+    boxes = T(np.tile(np.array([[0.1, 0.2, 0.8, 0.9]], np.float32), (6, 1)))
+    total, per = rp.lincomb_mask_loss(proto, coef, mask_t, boxes, normalize_emulate_roi_pooling=True)
+    (0.5 * total).backward()
+    _, dp, dc = rp.lincomb_mask_loss_raw(proto.detach(), coef.detach(), mask_t, boxes,
+                                         torch.full((6,), 20 * 24 / (0.7 * 24) / (0.7 * 20), device=DEV))
+    torch.testing.assert_close(proto.grad, 0.5 * dp, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(coef.grad, 0.5 * dc, rtol=1e-5, atol=1e-5)
+    assert abs(float(total) - float(per.sum())) <= 1e-5 * abs(float(total))

@@ -79,3 +79,26 @@ def test_box_masks_match_oracle(h, w, padding):
     cols = np.arange(w, dtype=np.float32)[None, None, :]; rows = np.arange(h, dtype=np.float32)[None, :, None]
     ref = (cols >= X1[:, None, None]) & (cols < X2[:, None, None]) & (rows >= Y1[:, None, None]) & (rows < Y2[:, None, None])
     np.testing.assert_array_equal(got.cpu().numpy(), ref)
+
+
+def test_affine_paste_bit_exact():
+    # rp_affine_paste against the oracle (pinned to cv2.warpAffine in tests/test_oracle_golden.py) and,
+    # when cv2 is importable on the box, against cv2 itself
+    from tests.test_oracle_golden import _affine_cases
+    rng = np.random.default_rng(5)
+    n, width, height = 16, 333, 250
+    e = np.exp(rng.standard_normal((n, 64, 64, 2)).astype(np.float32))
+    pred = (e / e.sum(-1, keepdims=True)).astype(np.float32)
+    M = _affine_cases(rng, n)
+    got = rp.affine_paste(T(pred), M, width, height).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.affine_paste(pred, M, width, height))
+    one = rp.warpAffine(T(pred[3]), np.vstack([M[3], [0, 0, 1]]), width, height).cpu().numpy()
+    np.testing.assert_array_equal(one, got[3])
+    try:
+        import cv2
+    except ImportError:
+        return
+    for i in range(n):
+        ref = cv2.warpAffine(pred[i], M[i], (width, height), borderMode=cv2.BORDER_CONSTANT,
+                             flags=cv2.WARP_INVERSE_MAP + cv2.INTER_LINEAR)[:, :, 1]
+        np.testing.assert_array_equal(got[i], (ref > 0.5).astype(np.uint8))

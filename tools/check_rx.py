@@ -30,6 +30,24 @@ def dump_timeouts():
                 print("  warp %2d block %3d waits on %-10s parity %d counter %d" % (w, e[1], names.get(e[2], e[2]), e[3], e[4]))
 
 
+def dump_profile():
+    """RX_PROFILE build: cycles per warp of block 0 spent in each wait (lane 0), whole loop, work."""
+    import ctypes
+    buf = (ctypes.c_int * 1024)()
+    if not rp.lib().rp_debug_rx_timeouts(buf, 1024):
+        return
+    a = np.frombuffer(buf, dtype=np.int32).copy()[256:256 + 32 * 12 * 2].view(np.int64).reshape(32, 12)
+    if not a.any():
+        return
+    roles = {0: "TMA", 1: "MMA", 2: "PLAN", 3: "FREE", 4: "EPI", 5: "EPI", 6: "EPI", 7: "EPI"}
+    names = ["total", "plan_full", "plan_empty", "tile_empty", "d_empty", "v_full", "d_full", "v_freed",
+             "tile_full", "issued", "work", "units"]
+    print("  warp role  " + " ".join("%10s" % n for n in names))
+    for w in range(32):
+        if a[w, 0]:
+            print("  %4d %-5s " % (w, roles.get(w, "Y")) + " ".join("%10d" % v for v in a[w]))
+
+
 def run(impl, fn):
     os.environ["RP_ROI_IMPL"] = str(impl)
     try:
@@ -124,5 +142,7 @@ for res in (14, 7):
         e1.record()
         torch.cuda.synchronize()
         print("  impl %d %dx%d: %.3f ms" % (impl, res, res, e0.elapsed_time(e1) / reps))
+        if impl == 6:
+            dump_profile()
 print("ALL OK" if ok else "SOME FAILED")
 sys.exit(0 if ok else 1)

@@ -136,6 +136,132 @@ __global__ void __launch_bounds__(128) umma_kernel(const float* __restrict__ A, 
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" ::"r"(tmem) : "memory");
 }
 
+
+// ---- test 4: K = 16 operands in 64-byte rows: SWIZZLE_64B (layout 4, SBO 512) and the interleaved
+// no-swizzle layout (layout 0): core matrices of 8 rows x 16 bytes, LBO between k-cores, SBO between
+// 8-row groups (padded strides to keep the y-pass stores conflict-free) ----------------------------
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo >> 4) << 16;
+  d |= (uint64_t)(sbo >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+
+// variant 0: SWIZZLE_64B; variant 1: interleaved, LBO = 128 rows-groups... (lbo, sbo given); swap = 1 exchanges
+// the LBO / SBO fields (to find out which is which)
+__global__ void __launch_bounds__(128) umma16_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                    float* __restrict__ D, int variant, uint32_t lbo, uint32_t sbo,
+                                                    int swap, int* status) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  unsigned char* a_s = smem;             // up to 16 KB
+  unsigned char* b_s = smem + 16384;     // up to 2 KB
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 32;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  const int K = 16;
+  auto off = [&](int r, int k, uint32_t sb, uint32_t lb) -> uint32_t {
+    if (variant == 0) return (uint32_t)(r * 64 + ((((k >> 2) ^ ((r >> 1) & 3)) << 4) | ((k & 3) << 2)));
+    return (uint32_t)((r >> 3) * sb + (k >> 2) * lb + (r & 7) * 16 + (k & 3) * 4);
+  };
+  const uint32_t b_sbo = variant == 0 ? 512 : 4 * 128, b_lbo = 128;   // B: dense interleaved / SW64
+  for (int i = tid; i < 128 * K; i += 128) {
+    const int r = i / K, k = i % K;
+    *reinterpret_cast<float*>(a_s + off(r, k, sbo, lbo)) = A[r * K + k];
+  }
+  for (int i = tid; i < 16 * K; i += 128) {
+    const int r = i / K, k = i % K;
+    *reinterpret_cast<float*>(b_s + off(r, k, b_sbo, b_lbo)) = B[r * K + k];
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_base_s;
+  if (tid == 0) {
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+    uint32_t acc = 0;
+    for (int ks = 0; ks < K / 8; ++ks) {
+      uint64_t da, db;
+      if (variant == 0) {
+        da = make_desc(smem_u32(a_s) + ks * 32, 16, 512, 4);
+        db = make_desc(smem_u32(b_s) + ks * 32, 16, 512, 4);
+      } else {
+        // a k-step covers 2 k-cores: advance the start address by 2 * LBO
+        const uint32_t fa = swap ? sbo : lbo, fb = swap ? lbo : sbo;
+        const uint32_t ga = swap ? b_sbo : b_lbo, gb = swap ? b_lbo : b_sbo;
+        da = make_desc(smem_u32(a_s) + ks * 2 * lbo, fa, fb, 0);
+        db = make_desc(smem_u32(b_s) + ks * 2 * b_lbo, ga, gb, 0);
+      }
+      asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+                   "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem), "l"(da), "l"(db),
+                   "r"(idesc), "r"(acc)
+                   : "memory");
+      acc = 1;
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+  }
+  const bool ok = mbar_wait_bounded(smem_u32(&bar), 0);
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (!ok) {
+    if (tid == 0) *status = 1;
+  } else {
+    uint32_t r[16];
+    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    const int row = warp * 32 + lane;
+    for (int j = 0; j < 16; ++j) D[row * 16 + j] = __uint_as_float(r[j]);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" ::"r"(tmem) : "memory");
+}
+
+static int run_umma16(int variant, uint32_t lbo, uint32_t sbo, int swap, const char* tag) {
+  const int K = 16;
+  float *hA = (float*)malloc(128 * K * 4), *hB = (float*)malloc(16 * K * 4), *hD = (float*)malloc(128 * 16 * 4);
+  srand(99);
+  for (int i = 0; i < 128 * K; ++i) hA[i] = (float)(rand() % 64 - 32) / 8.f;   // exactly representable in tf32
+  for (int i = 0; i < 16 * K; ++i) hB[i] = (float)(rand() % 32) / 32.f;
+  float *dA, *dB, *dD; int* dS;
+  CK(cudaMalloc(&dA, 128 * K * 4)); CK(cudaMalloc(&dB, 16 * K * 4)); CK(cudaMalloc(&dD, 128 * 16 * 4)); CK(cudaMalloc(&dS, 4));
+  CK(cudaMemcpy(dA, hA, 128 * K * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dB, hB, 16 * K * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dD, 0xff, 128 * 16 * 4)); CK(cudaMemset(dS, 0, 4));
+  const int smem = 16384 + 16 * 1024 + 1024;
+  CK(cudaFuncSetAttribute(umma16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  umma16_kernel<<<1, 128, smem>>>(dA, dB, dD, variant, lbo, sbo, swap, dS);
+  CK(cudaDeviceSynchronize());
+  int st; CK(cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hD, dD, 128 * 16 * 4, cudaMemcpyDeviceToHost));
+  double err = 0;
+  for (int r = 0; r < 128; ++r) for (int n = 0; n < 16; ++n) {
+    double ex = 0; for (int k = 0; k < K; ++k) ex += (double)hA[r * K + k] * hB[n * K + k];
+    err = fmax(err, fabs(hD[r * 16 + n] - ex));
+  }
+  printf("UMMA16 %s (variant %d lbo %u sbo %u swap %d) status %d: max|err| %.3e %s\n", tag, variant, lbo, sbo, swap, st, err,
+         err < 1e-4 ? "PASS" : "FAIL");
+  cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dS); free(hA); free(hB); free(hD);
+  return err < 1e-4 ? 0 : 1;
+}
+
 // ---- TMA with permuted dimensions ----------------------------------------------------------------
 typedef CUresult (*enc_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                            const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -237,6 +363,12 @@ int main() {
       if (bad) rc = 3;
     } else rc = 3;
   }
+  // ---------------- test 4: K = 16 layouts ----------------
+  run_umma16(0, 0, 0, 0, "SWIZZLE_64B");
+  run_umma16(1, 128, 512, 0, "interleaved dense  lbo=128 sbo=512");
+  run_umma16(1, 128, 512, 1, "interleaved dense  swapped fields");
+  run_umma16(1, 144, 608, 0, "interleaved padded lbo=144 sbo=608");
+  run_umma16(1, 144, 608, 1, "interleaved padded swapped fields");
   printf(rc ? "PROBE FAIL %d\n" : "PROBE PASS\n", rc);
   return rc;
 }
