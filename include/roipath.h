@@ -45,6 +45,9 @@ extern "C" {
 RP_API int rp_version(void);
 /* Compute capability the kernels were compiled for (100 for sm_100a). */
 RP_API int rp_built_for_sm(void);
+/* The RP_* tuning knobs (environment variables) are read once per process, at their first use;
+ * rp_reload_env() forgets the values read so far (tests and tuning tools). */
+RP_API void rp_reload_env(void);
 /* Diagnostic.  The warp-specialised Pooler forward never waits unboundedly: a barrier that does not
  * complete makes the kernel trap (a CUDA error, not a hang).  With RP_RX_DEBUG=1 in the environment
  * every warp records {1, block, wait code, parity, counter} in a host-mapped buffer before the trap;
@@ -234,6 +237,24 @@ RP_API int rp_lincomb_mask_loss(const float* proto, const float* coef, const flo
  * ------------------------------------------------------------------------------------ */
 RP_API int rp_affine_paste(const float* pred, const double* M, int n, int h, int w, int C, int channel,
                            int width, int height, uint8_t* out, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * EmbedMask mask stage.
+ * Replaces, per image: compute_mask_prob + the box-mask product of forward_for_mask,
+ *           det/modeling/rpn/embed_mask/inference.py:153-169,193-197 (boxes / stride, int cast, +-2
+ *           growth, clamp; layers/mask_prob.py:36-57; boxlist_ops.py:237-261 boxes_to_masks), and the
+ *           post_process_masks branch :199-202 (bilinear upsample by the stride, > mask_th, crop).
+ *   rp_embed_masks: pixel_embed [dim,m_h,m_w], proposal_embed [n,dim], proposal_margin [n],
+ *                   boxes [n,4] xyxy in image pixels -> masks [n,m_h,m_w] float (fully written).
+ *   rp_resize_threshold: masks [n,h,w] float -> out [n,crop_h,crop_w] uint8 = (bilinear resize to
+ *                   (H,W), align_corners=False) > thresh, rows < crop_h, columns < crop_w.
+ * Limits: dim <= 128, n <= 65535.
+ * ------------------------------------------------------------------------------------ */
+RP_API int rp_embed_masks(const float* pixel_embed, const float* proposal_embed, const float* proposal_margin,
+                          const float* boxes, float stride, int n, int dim, int m_h, int m_w, float* masks,
+                          void* stream);
+RP_API int rp_resize_threshold(const float* masks, int n, int h, int w, int H, int W, float thresh,
+                               int crop_h, int crop_w, uint8_t* out, void* stream);
 
 /* Bit-packing of binary masks for the final gather of kept detections (the one exchange of the
  * image-sharded path; the reference is single-process and has no counterpart).

@@ -5,12 +5,13 @@ Everything here calls libroipath_b200.so through ctypes (include/roipath.h); the
 torch-op or CPU fallback and nothing under oracle/ is ever imported.
 """
 from . import _lib
-from ._lib import RoiPathError, lib
+from ._lib import RoiPathError, lib, reload_env
 from .layers import (ROIAlign, ROIPool, cython_nms, mask_prob_cuda, ml_nms, nms, nms_batched, roi_align,
                      roi_pool,
                      roi_align_backward, roi_align_forward)
 from . import parallel
 from .pose2seg import affine_paste, warpAffine
+from .embed_mask import EmbedMaskMaskStage, embed_masks, resize_threshold
 from .masker import (Masker, MaskPostProcessor, mask_select_sigmoid, paste_mask_in_image,
                      paste_masks)
 from .poolers import (LevelMapper, LevelMapperwithArea, Pooler, convert_to_roi_format,

@@ -25,6 +25,7 @@ SIGNATURES = {
     "rp_version": (_i, []),
     "rp_built_for_sm": (_i, []),
     "rp_debug_rx_timeouts": (_i, [_vp, _i]),
+    "rp_reload_env": (None, []),
     "rp_roi_align_forward": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _f, _f, _vp, _i, _vp]),
     "rp_roi_align_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _vp]),
     "rp_level_map": (_i, [_vp, _i, _i, _i, _f, _i, _f, _vp, _vp]),
@@ -42,6 +43,8 @@ SIGNATURES = {
     "rp_paste_masks": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _vp]),
     "rp_lincomb_mask_loss": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "rp_affine_paste": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "rp_embed_masks": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp, _vp]),
+    "rp_resize_threshold": (_i, [_vp, _i, _i, _i, _i, _i, _f, _i, _i, _vp, _vp]),
     "rp_pack_mask_bits": (_i, [_vp, _c.c_longlong, _c.c_longlong, _vp, _vp]),
     "rp_box_decode": (_i, [_vp, _vp, _i, _i, _f, _f, _f, _f, _f, _vp, _vp]),
     "rp_rpn_pre_nms_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
@@ -100,6 +103,11 @@ def lib():
         raise RoiPathError("libroipath_b200.so was not built for sm_100a (built for sm_%d)" % L.rp_built_for_sm())
     _lib = L
     return _lib
+
+
+def reload_env():
+    """Make the library re-read its RP_* knobs (they are read once per process otherwise)."""
+    lib().rp_reload_env()
 
 
 _ERR = {-1: "invalid argument", -2: "workspace too small", -3: "size exceeds a documented limit"}

@@ -25,10 +25,25 @@
     if (rp_err__ != cudaSuccess) return (int)rp_err__; \
   } while (0)
 
-static inline int rp_env_int(const char* name, int dflt) {
-  const char* s = getenv(name);
-  return (s && *s) ? atoi(s) : dflt;
-}
+// Tuning knobs (RP_* environment variables): read ONCE per process, at their first use, into a table in
+// capi.cu, so that the library's behaviour cannot change under a running program; rp_reload_env()
+// (C ABI; tests and tuning tools) drops the table.  A knob that is not set costs one table lookup.
+int rp_env_int(const char* name, int dflt);
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) only when this call site needs more than it has
+// already set on the current device (once per kernel in the steady state, not once per launch).
+#define RP_SET_MAX_SMEM(kernel, bytes)                                                              \
+  do {                                                                                              \
+    static int rp_smem_set__[16] = {0};                                                             \
+    int rp_dev__ = 0;                                                                               \
+    (void)cudaGetDevice(&rp_dev__);                                                                 \
+    rp_dev__ &= 15;                                                                                 \
+    if ((int)(bytes) > rp_smem_set__[rp_dev__]) {                                                   \
+      RP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                                       (int)(bytes)));                                              \
+      rp_smem_set__[rp_dev__] = (int)(bytes);                                                       \
+    }                                                                                               \
+  } while (0)
 
 static inline size_t rp_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

@@ -163,8 +163,7 @@ int rp_lincomb_mask_loss(const float* proto, const float* coef, const float* mas
   const int grid = (H * W + LM_PIX - 1) / LM_PIX;
 #define LM_LAUNCH(D_)                                                                              \
   do {                                                                                             \
-    RP_CUDA_TRY(cudaFuncSetAttribute(lincomb_loss_kernel<D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                     (int)smem));                                                  \
+    RP_SET_MAX_SMEM(lincomb_loss_kernel<D_>, smem);                                                 \
     lincomb_loss_kernel<D_><<<grid, LM_THREADS, smem, st>>>(proto, coef, mask_t, boxes, scale, H, W, n, \
                                                             loss, d_proto, d_coef);                \
   } while (0)

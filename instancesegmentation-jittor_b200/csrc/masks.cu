@@ -563,8 +563,7 @@ int rp_mask_assemble(const float* proto, const float* coeff, const float* boxes,
     RP_LAUNCH_CHECK();
   } else {
     if (smem > 48 * 1024)
-      RP_CUDA_TRY(cudaFuncSetAttribute(mask_assemble_kernel,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      RP_SET_MAX_SMEM(mask_assemble_kernel, smem);
     const int tiles_x = (out_w + MA_TW - 1) / MA_TW, tiles_y = (out_h + MA_TH - 1) / MA_TH;
     dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)B);
     // With cropping most (detection, tile) pairs lie outside the crop box: zero-fill the whole

@@ -472,8 +472,7 @@ int nms_run_bands(const NmsBand& p, int B, int n_max, int max_keep, int ascendin
   const int ndiag = p.bw * groups;
   const size_t smem = sizeof(uint64_t) * ((size_t)p.BR * p.bw + 2 * (size_t)p.bw) +
                       sizeof(int) * ((size_t)p.bw + 2);
-  RP_CUDA_TRY(cudaFuncSetAttribute(nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)smem));
+  RP_SET_MAX_SMEM(nms_resolve_kernel, smem);
   const int rthreads = p.BR >= 1024 ? 1024 : (p.BR < 128 ? 128 : p.BR);
   nms_diag_kernel<GE, LABELS><<<dim3((unsigned)ndiag, (unsigned)B), 256, 0, st>>>(p, 0);
   RP_LAUNCH_CHECK();

@@ -1520,8 +1520,7 @@ template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
                   cudaStream_t st) {
-  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_fwd_kernel<U>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)l.smem_fwd));
+  RP_SET_MAX_SMEM(rt_pool_fwd_kernel<U>, l.smem_fwd);
   dim3 grid((unsigned)K, (unsigned)l.csplit);
   rt_pool_fwd_kernel<U><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
       lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
@@ -1591,13 +1590,11 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     if (gsmem > 227 * 1024) return RP_E_LIMIT;
     dim3 grid((unsigned)K, (unsigned)l.csplit);
     if (rp_env_int("RP_ROI_G_DIRECT", 0)) {
-      RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel<true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+      RP_SET_MAX_SMEM(rg_pool_fwd_kernel<true>, gsmem);
       rg_pool_fwd_kernel<true><<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW,
                                                              sampling_ratio, out, l.c_per_cta, gfloats, gcc);
     } else {
-      RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_fwd_kernel<false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+      RP_SET_MAX_SMEM(rg_pool_fwd_kernel<false>, gsmem);
       rg_pool_fwd_kernel<false><<<grid, threads, gsmem, st>>>(lv, N, C, rois, levels, K, PH, PW,
                                                               sampling_ratio, out, l.c_per_cta, gfloats, gcc);
     }
@@ -1628,8 +1625,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
         rb_level_maps(&maps, i, lv.feat[i], (long long)N * C, lv.H[i], lv.W[i]);
 #define RB_LAUNCH(NT_, MB_)                                                                      \
   do {                                                                                           \
-    RP_CUDA_TRY(cudaFuncSetAttribute(rb_pool_fwd_kernel<NT_, MB_>,                               \
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem));        \
+    RP_SET_MAX_SMEM((rb_pool_fwd_kernel<NT_, MB_>), smem);                                       \
     rb_pool_fwd_kernel<NT_, MB_><<<grid, NT_, smem, st>>>(lv, N, C, rois, levels, K, PH, PW,     \
                                                           sampling_ratio, out, l.c_per_cta,      \
                                                           (smem - 128) / 4, gpb, gw, nbuf, maps); \
@@ -1684,8 +1680,7 @@ int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* 
     if (gcc < 4) gcc = 4;
     const size_t gsmem = rp_align_up(sizeof(RgAxes), 16) + sizeof(float) * (size_t)gfloats;
     if (gsmem > 227 * 1024) return RP_E_LIMIT;
-    RP_CUDA_TRY(cudaFuncSetAttribute(rg_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)gsmem));
+    RP_SET_MAX_SMEM(rg_pool_bwd_kernel, gsmem);
     // with a fixed sampling grid <= RB_MAXG only bins wider than ~6 feature pixels lack a short-tap
     // form: too rare for a second launch, the gather kernel scatters them in reference order itself
     const int one_launch = sampling_ratio > 0 && (int)sampling_ratio <= RB_MAXG &&
@@ -1695,8 +1690,7 @@ int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* 
     RP_LAUNCH_CHECK();
     if (one_launch) return RP_OK;
   }
-  RP_CUDA_TRY(cudaFuncSetAttribute(rt_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)l.smem));
+  RP_SET_MAX_SMEM(rt_pool_bwd_kernel, l.smem);
   rt_pool_bwd_kernel<<<grid, l.bwd_threads, l.smem, st>>>(lv, N, C, rois, levels, K, PH, PW,
                                                           sampling_ratio, dout, l.c_per_cta,
                                                           l.vs_floats, l.bwd_cc, gather);

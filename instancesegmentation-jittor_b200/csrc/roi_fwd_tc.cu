@@ -5,24 +5,31 @@
 //
 // The separable form  out[c,ph,pw] = 1/(gh*gw) * sum_y sum_x Ay[ph,y] * Ax[pw,x] * F[c,y,x]
 // (roi_tile.h) is evaluated as
-//   y-pass (SIMT)   V[(c,ph)][x] = sum_y Ay[ph,y] * F[c,y,x]      4-row bands, one 16-byte strip per thread
-//   x-pass (tcgen05) D[(c,ph)][pw] = sum_x V[(c,ph)][x] * Ax'[pw,x]  M=128 (8 channels x 16 bins), N=16, K<=64
+//   y-pass (SIMT)    V[(ph,c)][x] = sum_y Ay[ph,y] * F[c,y,x]      4-row bands, one 16-byte strip per thread
+//   x-pass (tcgen05) D[(ph,c)][pw] = sum_x V[(ph,c)][x] * Ax'[pw,x]  M=128 (16 bins x 8 channels), N=16
 // with the x-pass in 3xTF32 (V_hi*Ax_hi + V_lo*Ax_hi + V_hi*Ax_lo; the tensor core truncates fp32 to
 // tf32, measured with tools/umma_probe.cu), fp32 accumulation in TMEM: ~3e-7 relative error.
 //
-// One persistent CTA per SM, 16 warps with fixed roles, everything connected by mbarriers:
-//   warp 0      TMA producer: per sub-chunk (<= 8 channels x R rows x <= 32 columns of the RoI's tile)
-//               a few cp.async.bulk.tensor boxes; the tensor maps are (x, plane, y) so that a box lands
+// The RoI's tile is processed in column blocks of 16 ("K quarters", up to 4): a V tile is 128 rows x
+// 64 bytes (K-major SWIZZLE_64B, hi and lo planes: 16 KB), the accumulator collects the quarters.
+// V rows are ordered (ph, c): the 8 channels x 4 strips a warp stores for one bin are one whole
+// 512-byte swizzle atom (conflict-free), and the epilogue's packed [c][ph][pw] stores are conflict-free too.
+//
+// One persistent CTA per SM, 32 warps with fixed roles, connected by mbarriers:
+//   warp 0      TMA producer: per sub-chunk (<= 8 channels x R rows x 16 columns) a few
+//               cp.async.bulk.tensor boxes; the tensor maps are (x, plane, y) so that a box lands
 //               [row][channel][x]: the 16-byte strips of one row of all channels are one contiguous,
-//               conflict-free run for the y-pass
-//   warp 1      MMA issuer (one lane): per V tile 3 MMAs per 8 columns, tcgen05.commit frees the V slot
-//               and publishes the accumulator
-//   warp 2      planner: per RoI the y band plan (4 merged weights per bin, rotated to the register
-//               ring) and the dense x-weight matrix Ax' (hi / lo, K-major SWIZZLE_128B, 1/(gh*gw) folded in)
+//               conflict-free 512-byte run for the y-pass
+//   warp 1      MMA issuer (one lane): per V tile 3 MMAs per 8 columns; tcgen05.commit frees the V slot
+//               and, after the last quarter, publishes the accumulator
+//   warps 2-3   planners (even / odd work items): the y band plan (4 merged weights per bin, rotated to
+//               the register ring, per row segment) and the dense x-weight matrices Ax' (hi / lo per
+//               quarter, K-major SWIZZLE_64B, 1/(gh*gw) folded in)
 //   warps 4-7   epilogue: tcgen05.ld (one accumulator row = 16 pw per lane) -> packed [c][ph][pw] rows in
 //               shared memory -> one cp.async.bulk store of 8 channels x PH x PW floats (contiguous in out)
-//   warps 8-15  y-pass: thread = strip; ring of 4 rows; every finished bin is split into tf32 hi / lo
-//               and stored as the K-major SWIZZLE_128B A operand
+//   warp 8      V-slot release: turns MMA completions into a sequence number the y-pass warps can test
+//   warps 9-31  y-pass: unit = (sub-chunk, row segment) = one warp pass of <= 32 strips; ring of 4 rows;
+//               every finished bin is split into tf32 hi / lo and stored into the A operand
 // The input tile never passes through the LSU on its way in (TMA), the x-pass and the V read-back are
 // gone from the LSU / FMA pipes, and the output leaves through the bulk-copy engine.
 // RoIs without a band form, wider than 64 columns or taller than the tile slot are evaluated in the
@@ -38,22 +45,23 @@
 namespace {
 
 constexpr int RX_THREADS = 1024;
-constexpr int RX_W_TMA = 0, RX_W_MMA = 1, RX_W_PLAN = 2, RX_W_FREE = 3, RX_W_EPI0 = 4, RX_W_Y0 = 8;
-constexpr int RX_NY = 24;              // y-pass warps
-constexpr int RX_S = 4;                // tile slots
-constexpr int RX_SLOT = 14336;         // bytes per tile slot
-constexpr int RX_SV = 4;               // V slots (hi + lo, 32 KB each)
+constexpr int RX_W_TMA = 0, RX_W_MMA = 1, RX_W_PLAN = 2, RX_W_EPI0 = 4, RX_W_FREE = 8, RX_W_Y0 = 9;
+constexpr int RX_NY = 23;              // y-pass warps
+constexpr int RX_S = 7;                // tile slots
+constexpr int RX_SLOT = 14336;         // bytes per tile slot: 8 channels x 28 rows x 16 columns
+constexpr int RX_SV = 5;               // V slots
+constexpr int RX_VBYTES = 16384;       // V tile: hi plane (128 rows x 64 B) + lo plane
 constexpr int RX_SD = 4;               // accumulator tiles in TMEM (16 columns each)
-constexpr int RX_NP = 2;               // plans in flight
+constexpr int RX_NP = 2;               // plans in flight (one per planner warp)
 constexpr int RX_CS = 128;             // channels per work item (RoI x channel slice)
 constexpr int RX_RMAX = 64;            // tile rows
 constexpr int RX_OSTAGE = 8 * 16 * 16 * 4;  // out stage: 8 channels x <= 16x16 floats (one buffer)
-constexpr int RX_NMAP = 36;            // tensor maps per level: 4 widths x 3 row counts x 3 channel counts
+constexpr int RX_NMAP = 18;            // tensor maps per level: 2 widths x 3 row counts x 3 channel counts
 constexpr int RX_PLAN_ARRIVALS = 1 + RX_NY + 1 + 4 + 1;  // TMA, y-pass warps, MMA, epilogue warps, V release
 
 struct RxMeta {
   int kind;  // 0 tensor-core path, 1 reference-order fallback, 2 zero fill
-  int level, R, nq, nkh, cs, y0, x0a, plane0, nmt;
+  int level, R, nq, nkq, cs, y0, x0a, plane0, nmt;  // nq: 16-byte strips per tile row, nkq: 16-column quarters
   int H, W, nch;
   float* out;          // &out[(k*C + c_begin) * P]
   const float* featb;  // &feat[level][(b*C + c_begin) * H*W]
@@ -64,7 +72,7 @@ struct RxMeta {
   uint32_t mw[2][RX_RMAX / 4 + 2];
 };
 
-constexpr int RX_MAXL = 5;  // levels with tensor maps (kernel parameter space: 23 KB)
+constexpr int RX_MAXL = 5;  // levels with tensor maps (kernel parameter space: 11.5 KB)
 struct RxMaps {
   CUtensorMap m[RX_MAXL][RX_NMAP];
 };
@@ -82,12 +90,12 @@ struct RxBars {
 
 // shared-memory layout (offsets from a 1024-byte aligned base)
 constexpr int RX_OFF_V = 0;
-constexpr int RX_OFF_B = RX_OFF_V + RX_SV * 32768;
+constexpr int RX_OFF_B = RX_OFF_V + RX_SV * RX_VBYTES;
 constexpr int RX_OFF_TILE = RX_OFF_B + RX_NP * 8192;
 constexpr int RX_OFF_OST = RX_OFF_TILE + RX_S * RX_SLOT;
 constexpr int RX_OFF_META = RX_OFF_OST + RX_OSTAGE;
 constexpr int RX_OFF_AY = RX_OFF_META + RX_NP * 1024;
-constexpr int RX_OFF_BARS = RX_OFF_AY + 1024;
+constexpr int RX_OFF_BARS = RX_OFF_AY + RX_NP * 1024;
 constexpr int RX_SMEM = RX_OFF_BARS + 512 + 1024;  // + alignment slack
 static_assert(sizeof(RxMeta) <= 1024, "RxMeta");
 static_assert(sizeof(RbAxis) <= 1024, "RbAxis");
@@ -160,7 +168,7 @@ __device__ __forceinline__ void rx_wait_ge(uint32_t* ctr, uint32_t target, uint3
 #endif
       return;
     }
-    __nanosleep(40);  // polling warps must not load the shared-memory pipe the working warps live on
+    __nanosleep(spin < 4 ? 64 : 256);  // polling warps must not take the issue slots / the LSU of the working warps
     if (spin > (1u << 22)) rx_timeout(code, target, counter);
   }
 }
@@ -175,13 +183,15 @@ __device__ __forceinline__ void rx_commit(uint64_t* bar) {
                    rp_smem_addr(bar))
                : "memory");
 }
-__device__ __forceinline__ uint64_t rx_desc_sw128(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
-         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+// K-major SWIZZLE_64B operand of 16 floats per row (validated by tools/umma_probe.cu): layout type 4,
+// stride between 8-row groups 512 bytes; a k-step of 8 floats advances the start address by 32 bytes
+__device__ __forceinline__ uint64_t rx_desc_sw64(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
 }
-// byte offset of (row, k) in a K-major SWIZZLE_128B tile of 32 floats per row
-__device__ __forceinline__ uint32_t rx_sw128(int row, int k) {
-  return (uint32_t)(row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2)));
+// byte offset of (row, k) in that tile: the 16-byte chunk index is XORed with bits 1-2 of the row
+__device__ __forceinline__ uint32_t rx_sw64(int row, int k) {
+  return (uint32_t)(row * 64 + ((((k >> 2) ^ ((row >> 1) & 3)) << 4) | ((k & 3) << 2)));
 }
 // exact floor(j / d) for j * d < 2^32, with m = rx_magic(d), d >= 2
 __device__ __forceinline__ uint32_t rx_magic(uint32_t d) { return 0xffffffffu / d + 1u; }
@@ -248,20 +258,19 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
   }
   int cs = 8;
   if (kind == 0) {
-    // channels per sub-chunk: a sub-chunk is one warp's y-pass and must fit a tile slot; 8 channels
-    // only for narrow tiles (<= 4 strips: 32 items), so that wider tiles put two warps on a V tile
-    const int Re = (R + 1) & ~1, Kh = min(Kp, 32);
-    if (Kh <= 16 && Re * Kh * 8 * 4 <= RX_SLOT)
+    // channels per sub-chunk (one 16-column quarter of cs channels must fit a tile slot)
+    const int Re = (R + 1) & ~1;
+    if (Re * 16 * 8 * 4 <= RX_SLOT)
       cs = 8;
-    else if (Re * Kh * 4 * 4 <= RX_SLOT)
+    else if (Re * 16 * 4 * 4 <= RX_SLOT)
       cs = 4;
-    else if (Re * Kh * 2 * 4 <= RX_SLOT)
+    else if (Re * 16 * 2 * 4 <= RX_SLOT)
       cs = 2;
     else
       kind = 1;
   }
   if (kind == 0) {
-    const int nkh = Kp > 32 ? 2 : 1;
+    const int nkq = (Kp + 15) >> 4;
     // y: segments, weights rotated to the ring of the bin's segment (slot = segment row & 3), bins
     // completed per segment row
     const int nseg = PH >= 4 ? 2 : 1;
@@ -299,12 +308,10 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
       m->seg_rows[0] = ay->start[b_mid - 1] + 4;
       m->seg_rows[1] = nseg == 2 ? ay->start[PH - 1] + 4 - r0_1 : 0;
     }
-    // x: dense weights, accumulated in full precision in the "hi" planes, then split
+    // x: dense weights per quarter [16 pw rows][16 columns], hi plane at +0 and lo plane at +1024 of
+    // the quarter's 2 KB; accumulated in full precision in the hi planes, then split
     float4* bz = reinterpret_cast<float4*>(bmat);
-    for (int i = lane; i < nkh * 4096 / 16; i += 32) {  // hi and lo planes of the used K halves
-      const int kh = i >> 8, j = i & 255;
-      bz[kh * 256 + j] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    for (int i = lane; i < nkq * 128; i += 32) bz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
     if (lane < PW) {
       for (int i = 0; i < g.gw; ++i) {
@@ -312,25 +319,25 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
         float wlo, whi;
         if (rt_axis_tap(g.sw, g.bw, lane, i, g.gw, W, &lo, &hi, &wlo, &whi)) {
           const int c0 = lo - x0a, c1 = hi - x0a;
-          float* p0 = reinterpret_cast<float*>(bmat + (c0 >> 5) * 4096 + rx_sw128(lane, c0 & 31));
+          float* p0 = reinterpret_cast<float*>(bmat + (c0 >> 4) * 2048 + rx_sw64(lane, c0 & 15));
           *p0 += wlo;
-          float* p1 = reinterpret_cast<float*>(bmat + (c1 >> 5) * 4096 + rx_sw128(lane, c1 & 31));
+          float* p1 = reinterpret_cast<float*>(bmat + (c1 >> 4) * 2048 + rx_sw64(lane, c1 & 15));
           *p1 += whi;
         }
       }
     }
     __syncwarp();
     const float inv = 1.0f / (float)(g.gh * g.gw);
-    for (int i = lane; i < nkh * 512; i += 32) {  // 16 rows x 32 floats per half
-      const int kh = i >> 9, e = i & 511;
-      float* ph_ = reinterpret_cast<float*>(bmat + kh * 4096) + e;
+    for (int i = lane; i < nkq * 256; i += 32) {  // 16 rows x 16 floats per quarter
+      const int kq = i >> 8, e = i & 255;
+      float* ph_ = reinterpret_cast<float*>(bmat + kq * 2048) + e;
       const float v = *ph_ * inv;
       const float hi = rx_tf32_hi(v);
       *ph_ = hi;
-      ph_[512] = v - hi;  // lo plane: +2048 bytes
+      ph_[256] = v - hi;  // lo plane: +1024 bytes
     }
     if (lane == 0) {
-      m->nkh = nkh;
+      m->nkq = nkq;
       m->nq = Kp >> 2;
       m->cs = cs;
       m->R = R;
@@ -354,25 +361,27 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
   __syncwarp();
 }
 
-// ---- y-pass of one sub-chunk by one warp -----------------------------------------------------------
-// tile: [R rows][cs channels][nqh strips] RbF4; V rows (c, ph) at vbase + ((cbase + c) * 16 + ph) * 128.
+// ---- y-pass of one unit (sub-chunk x row segment) by one warp ---------------------------------------
+// tile: [rows][cs channels][nqh strips] RbF4 (nqh <= 4, so cs * nqh <= 32: one item per lane);
+// V row of (ph, channel c) is ph * 8 + c: 64 bytes, 16-byte chunk s at (s ^ ((row >> 1) & 3)).
 __device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, int cs, int nqh,
                                          const uint32_t* __restrict__ mw, const RbF4* __restrict__ wrot,
                                          int ph0, unsigned char* vhi, int cbase, int lane) {
   const int nitems = cs * nqh;
-  const uint32_t magic = rx_magic((uint32_t)nqh);
-  for (int u = lane; u < nitems; u += 32) {
-    const int c = (int)__umulhi((uint32_t)u, magic);
-    const int s = u - c * nqh;
-    const RbF4* rows = tile + u;
-    unsigned char* vrow = vhi + (size_t)((cbase + c) * 16) * 128;
-    const RbF4* wr = wrot + ph0;
-    int ph = ph0;
-    RbF4 W0, W1, W2, W3;
-    W0.x = W0.y = W0.z = W0.w = 0.f;
-    W1 = W0;
-    W2 = W0;
-    W3 = W0;
+  if (lane >= nitems) return;
+  const int c = nqh == 4 ? lane >> 2 : lane >> 1;
+  const int s = lane - c * nqh;
+  const int ch = cbase + c;
+  const RbF4* rows = tile + lane;
+  // byte offset of row (ph, ch), chunk s:  (ph*8 + ch)*64 + ((s ^ ((ph*8 + ch) >> 1 & 3)) << 4); ph*8 is a
+  // multiple of 8, so the XOR term depends on ch only
+  unsigned char* vdst = vhi + ch * 64 + ((s ^ ((ch >> 1) & 3)) << 4) + ph0 * 512;
+  const RbF4* wr = wrot + ph0;
+  RbF4 W0, W1, W2, W3;
+  W0.x = W0.y = W0.z = W0.w = 0.f;
+  W1 = W0;
+  W2 = W0;
+  W3 = W0;
 #define RX_BINS(cnt)                                                                             \
   for (uint32_t m_ = (cnt); m_ != 0; --m_) {                                                    \
     const RbF4 w_ = *wr++;                                                                      \
@@ -386,26 +395,24 @@ __device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, i
     h_.y = rx_tf32_hi(a_.y);                                                                    \
     h_.z = rx_tf32_hi(a_.z);                                                                    \
     h_.w = rx_tf32_hi(a_.w);                                                                    \
-    unsigned char* d_ = vrow + ph * 128 + ((s ^ (ph & 7)) << 4);                                \
-    *reinterpret_cast<float4*>(d_) = h_;                                                        \
-    *reinterpret_cast<float4*>(d_ + 16384) =                                                    \
+    *reinterpret_cast<float4*>(vdst) = h_;                                                      \
+    *reinterpret_cast<float4*>(vdst + 8192) =                                                   \
         make_float4(a_.x - h_.x, a_.y - h_.y, a_.z - h_.z, a_.w - h_.w);                        \
-    ++ph;                                                                                       \
+    vdst += 512;                                                                                \
   }
-    for (int r = 0; r < R; r += 4) {
-      const uint32_t mword = mw[r >> 2];
-      W0 = rows[0];
-      RX_BINS(mword & 0xffu)
-      if (r + 1 < R) W1 = rows[nitems];
-      RX_BINS((mword >> 8) & 0xffu)
-      if (r + 2 < R) W2 = rows[2 * nitems];
-      RX_BINS((mword >> 16) & 0xffu)
-      if (r + 3 < R) W3 = rows[3 * nitems];
-      RX_BINS(mword >> 24)
-      rows += 4 * nitems;
-    }
+  for (int r = 0; r < R; r += 4) {
+    const uint32_t mword = mw[r >> 2];
+    W0 = rows[0];
+    RX_BINS(mword & 0xffu)
+    if (r + 1 < R) W1 = rows[nitems];
+    RX_BINS((mword >> 8) & 0xffu)
+    if (r + 2 < R) W2 = rows[2 * nitems];
+    RX_BINS((mword >> 16) & 0xffu)
+    if (r + 3 < R) W3 = rows[3 * nitems];
+    RX_BINS(mword >> 24)
+    rows += 4 * nitems;
+  }
 #undef RX_BINS
-  }
 }
 
 __global__ void __launch_bounds__(RX_THREADS, 1)
@@ -462,11 +469,13 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   rx_wait(&bars->plan_full[ps], (uint32_t)(p / RX_NP) & 1u, 1, p);    \
   const RxMeta* M = reinterpret_cast<const RxMeta*>(smem + RX_OFF_META + ps * 1024);
 
-  if (warp == RX_W_PLAN) {
-    // ===== planner =====
-    RbAxis* ay = reinterpret_cast<RbAxis*>(smem + RX_OFF_AY);
+  if (warp == RX_W_PLAN || warp == RX_W_PLAN + 1) {
+    // ===== planners: warp RX_W_PLAN builds the even work items (plan slot 0), the next warp the odd ones
+    const int pw_ = warp - RX_W_PLAN;
+    RbAxis* ay = reinterpret_cast<RbAxis*>(smem + RX_OFF_AY + pw_ * 1024);
     RX_ITEM_LOOP {
       const int ps = p % RX_NP;
+      if (ps != pw_) continue;
       rx_wait(&bars->plan_empty[ps], ((uint32_t)(p / RX_NP) & 1u) ^ 1u, 2, p);
       const int sl = it / K, k = it - sl * K;
 #ifdef RX_PROFILE
@@ -488,7 +497,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
-        const int R = M->R, cs = M->cs, nkh = M->nkh, nq = M->nq, nsc = 8 / cs;
+        const int R = M->R, cs = M->cs, nkq = M->nkq, nq = M->nq, nsc = 8 / cs;
         const int Re = (R + 1) & ~1, n8 = Re >> 3, rem = Re & 7;
         const int nbox = n8 + ((rem & 4) ? 1 : 0) + ((rem & 2) ? 1 : 0);
         // this lane's box: row offset and row-count index (0: 8 rows, 1: 4, 2: 2)
@@ -503,11 +512,11 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           }
         }
         const CUtensorMap* lmaps = maps.m[M->level];
+        const int ci = cs == 8 ? 0 : (cs == 4 ? 1 : 2);
         for (int mt = 0; mt < M->nmt; ++mt)
-          for (int kh = 0; kh < nkh; ++kh) {
-            const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
-            const int wi = (nqh >> 1) - 1;  // box width 8, 16, 24, 32 floats
-            const CUtensorMap* tm = lmaps + (wi * 3 + bri) * 3 + (cs == 8 ? 0 : (cs == 4 ? 1 : 2));
+          for (int kq = 0; kq < nkq; ++kq) {
+            const int nqh = min(4, nq - 4 * kq);  // 2 or 4 strips: box width 8 or 16 floats
+            const CUtensorMap* tm = lmaps + (((nqh >> 1) - 1) * 3 + bri) * 3 + ci;
             const uint32_t row_bytes = (uint32_t)(cs * nqh * 16);
             for (int sc = 0; sc < nsc; ++sc, ++q) {
               const int ts = q % RX_S;
@@ -516,7 +525,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
               __syncwarp();
               if (lane < nbox)
                 rp_tma_load_3d(smem + RX_OFF_TILE + ts * RX_SLOT + (uint32_t)brow * row_bytes, tm,
-                               M->x0a + 32 * kh, M->plane0 + mt * 8 + sc * cs, M->y0 + brow,
+                               M->x0a + 16 * kq, M->plane0 + mt * 8 + sc * cs, M->y0 + brow,
                                &bars->tile_full[ts]);
               __syncwarp();
               if (lane == 0) rx_publish(&bars->issued, q + 1);
@@ -533,22 +542,25 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
-        const int nkh = M->nkh, nq = M->nq;
+        const int nkq = M->nkq, nq = M->nq;
         const uint32_t b_s = rp_smem_addr(smem + RX_OFF_B + ps * 8192);
         for (int mt = 0; mt < M->nmt; ++mt, ++d) {
           const int ds = d % RX_SD;
           rx_wait(&bars->d_empty[ds], ((d / RX_SD) & 1u) ^ 1u, 4, d);
-          for (int kh = 0; kh < nkh; ++kh, ++v) {
+          for (int kq = 0; kq < nkq; ++kq, ++v) {
             const int vs = v % RX_SV;
             rx_wait(&bars->v_full[vs], (v / RX_SV) & 1u, 5, v);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (lane == 0) {
-              const int nks = (kh == 0 ? min(nq, 8) : nq - 8) >> 1;
-              const uint32_t a_s = rp_smem_addr(smem + RX_OFF_V + vs * 32768);
-              const uint64_t dah = rx_desc_sw128(a_s), dal = rx_desc_sw128(a_s + 16384);
-              const uint64_t dbh = rx_desc_sw128(b_s + kh * 4096), dbl = rx_desc_sw128(b_s + kh * 4096 + 2048);
+#ifdef RX_PROFILE
+              const long long mm_t0 = clock64();
+#endif
+              const int nks = min(4, nq - 4 * kq) >> 1;
+              const uint32_t a_s = rp_smem_addr(smem + RX_OFF_V + vs * RX_VBYTES);
+              const uint64_t dah = rx_desc_sw64(a_s), dal = rx_desc_sw64(a_s + 8192);
+              const uint64_t dbh = rx_desc_sw64(b_s + kq * 2048), dbl = rx_desc_sw64(b_s + kq * 2048 + 1024);
               const uint32_t dtm = tmem + (uint32_t)(ds * 16);
-              uint32_t acc = kh ? 1u : 0u;
+              uint32_t acc = kq ? 1u : 0u;
               for (int ks = 0; ks < nks; ++ks) {
                 const uint64_t adv = (uint64_t)(ks * 2);
 #define RX_MMA(DA, DB)                                                                        \
@@ -562,8 +574,16 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                 RX_MMA(dah, dbl)
 #undef RX_MMA
               }
+#ifdef RX_PROFILE
+              const long long mm_t1 = clock64();
+#endif
               rx_commit(&bars->v_empty[vs]);
-              if (kh == nkh - 1) rx_commit(&bars->d_full[ds]);
+              if (kq == nkq - 1) rx_commit(&bars->d_full[ds]);
+#ifdef RX_PROFILE
+              rx_prof_acc[10] += mm_t1 - mm_t0;
+              rx_prof_acc[9] += clock64() - mm_t1;
+              rx_prof_acc[11] += 1;
+#endif
             }
             __syncwarp();
           }
@@ -580,7 +600,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
-        const int nv = M->nmt * M->nkh;
+        const int nv = M->nmt * M->nkq;
         for (int i = 0; i < nv; ++i, ++v) {
           rx_wait(&bars->v_empty[v % RX_SV], (v / RX_SV) & 1u, 7, v);
           if (lane == 0) rx_publish(&bars->v_freed, v + 1u);
@@ -621,7 +641,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           asm volatile("bar.sync 1, 128;" ::: "memory");
           unsigned char* stage = smem + RX_OFF_OST;
-          const int row = quad * 32 + lane, c = row >> 4, ph = row & 15;
+          const int row = quad * 32 + lane, ph = row >> 3, c = row & 7;  // V / accumulator rows are (ph, c)
           if (ph < PH) {
             float* dst = reinterpret_cast<float*>(stage) + c * P + ph * PW;
             if ((PW & 1) == 0) {
@@ -672,18 +692,19 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
-        // unit j of the item = (((mt * nkh + kh) * nsc + sc) * nseg + sg); nkh, nsc, nseg are powers of
-        // two, so this warp's units (u0 + j == yw mod NY) are decoded with shifts, not walked
-        const int cs = M->cs, nkh = M->nkh, nq = M->nq, nseg = M->nseg;
-        const int lseg = nseg >> 1, lsc = cs == 8 ? 0 : (cs == 4 ? 1 : 2), lkh = nkh >> 1;
-        const int nunits = M->nmt << (lkh + lsc + lseg);
+        // unit j of the item = ((tile * nsc + sc) * nseg + sg), tile = mt * nkq + kq; nsc and nseg are
+        // powers of two: this warp's units (u0 + j == yw mod NY) are decoded, not walked
+        const int cs = M->cs, nkq = M->nkq, nq = M->nq, nseg = M->nseg;
+        const int lseg = nseg >> 1, lsc = cs == 8 ? 0 : (cs == 4 ? 1 : 2);
+        const int ntiles = M->nmt * nkq;
+        const int nunits = ntiles << (lsc + lseg);
         for (int j = (int)((uint32_t)(yw + RX_NY) - u0 % RX_NY) % RX_NY; j < nunits; j += RX_NY) {
           const int sg = j & (nseg - 1);
           const int qi = j >> lseg, sc = qi & ((1 << lsc) - 1);
-          const int vi = qi >> lsc, kh = vi & (nkh - 1);
+          const int vi = qi >> lsc, kq = vi % nkq;
           const uint32_t q = q0 + (uint32_t)qi, v = v0 + (uint32_t)vi;
           const int vs = v % RX_SV, ts = q % RX_S;
-          const int nqh = kh == 0 ? min(nq, 8) : nq - 8;
+          const int nqh = min(4, nq - 4 * kq);
           rx_wait_ge(&bars->v_freed, v + 1u - (uint32_t)RX_SV, 7, v);  // the MMAs of tile v - SV are done
           rx_wait_ge(&bars->issued, q + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
           rx_wait(&bars->tile_full[ts], (q / RX_S) & 1u, 8, q);
@@ -691,7 +712,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           const long long yp_t0 = clock64();
 #endif
           rx_ypass(reinterpret_cast<const RbF4*>(smem + RX_OFF_TILE + ts * RX_SLOT) + M->seg_r0[sg] * cs * nqh,
-                   M->seg_rows[sg], cs, nqh, M->mw[sg], M->wrot, M->seg_b0[sg], smem + RX_OFF_V + vs * 32768,
+                   M->seg_rows[sg], cs, nqh, M->mw[sg], M->wrot, M->seg_b0[sg], smem + RX_OFF_V + vs * RX_VBYTES,
                    sc * cs, lane);
           rp_fence_proxy_async_smem();
           __syncwarp();
@@ -708,7 +729,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
         }
         u0 += (uint32_t)nunits;
         q0 += (uint32_t)(nunits >> lseg);
-        v0 += (uint32_t)(M->nmt << lkh);
+        v0 += (uint32_t)ntiles;
       }
       __syncwarp();
       if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
@@ -770,7 +791,7 @@ struct RxMapEntry {
 };
 
 // Fills maps->m[l] for level l; a small host cache keeps repeated calls on the same tensors free of
-// encoding (36 cuTensorMapEncodeTiled calls per level otherwise).  Returns 0 on failure.
+// encoding (18 cuTensorMapEncodeTiled calls per level otherwise).  Returns 0 on failure.
 int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H, int W, int pitch) {
   static std::mutex mu;
   static RxMapEntry cache[32];
@@ -794,7 +815,7 @@ int rx_level_maps(RxMaps* maps, int l, const float* ptr, long long planes, int H
   const cuuint64_t gdim[3] = {(cuuint64_t)W, (cuuint64_t)planes, (cuuint64_t)H};
   const cuuint64_t gstride[2] = {(cuuint64_t)H * pitch * 4, (cuuint64_t)pitch * 4};
   const cuuint32_t estride[3] = {1, 1, 1};
-  for (int wi = 0; wi < 4; ++wi)
+  for (int wi = 0; wi < 2; ++wi)
     for (int ri = 0; ri < 3; ++ri)
       for (int ci = 0; ci < 3; ++ci) {
         const cuuint32_t box[3] = {(cuuint32_t)(8 * (wi + 1)), (cuuint32_t)(8 >> ci), (cuuint32_t)rows_of[ri]};
@@ -844,7 +865,7 @@ int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   const int nsl = (C + RX_CS - 1) / RX_CS;
   const long long n_items = (long long)K * nsl;
   if (n_items > 0x7fffffffLL) return RP_E_LIMIT;
-  static RxMaps maps;  // 23 KB: filled under the lock below, copied into the launch by value
+  static RxMaps maps;  // 11.5 KB: filled under the lock below, copied into the launch by value
   static std::mutex launch_mu;
   std::lock_guard<std::mutex> lock(launch_mu);
   float* scratch[RX_MAXL] = {nullptr, nullptr, nullptr, nullptr, nullptr};

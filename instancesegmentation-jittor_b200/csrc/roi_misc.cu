@@ -191,6 +191,85 @@ affine_paste_kernel(const float* __restrict__ pred, const double* __restrict__ M
   }
 }
 
+// ---- EmbedMask mask stage, fused -------------------------------------------------
+// det/modeling/rpn/embed_mask/inference.py:153-169 (compute_mask_prob) and :193-197 (forward_for_mask):
+//   mask_boxes = boxes / stride; b = int(mask_boxes) grown by 2 and clamped to the map (:157-161);
+//   prob[n][pixel] = exp(-|e_pixel - e_center|^2 * margin) inside b, 0 elsewhere (layers/mask_prob.py:36-57);
+//   masks = prob * boxes_to_masks(mask_boxes, m_h, m_w)   (boxlist_ops.py:237-261, padding 0).
+// The reference transposes pixel_embed to [HW, dim] first and makes three passes over n x HW floats;
+// here pixel_embed stays [dim, m_h, m_w] (lanes along x read each embedding plane coalesced), the
+// output is zero-filled once and only the grown box of each instance is visited.
+__global__ void __launch_bounds__(256)
+embed_masks_kernel(const float* __restrict__ pixel_embed, const float* __restrict__ embed_center,
+                   const float* __restrict__ margin, const float* __restrict__ boxes, float inv_stride_num,
+                   float stride, int dim, int m_h, int m_w, float* __restrict__ masks) {
+  __shared__ float ec[MP_MAXDIM];
+  const int n = blockIdx.y;
+  for (int d = threadIdx.x; d < dim; d += blockDim.x) ec[d] = embed_center[(size_t)n * dim + d];
+  __syncthreads();
+  (void)inv_stride_num;
+  const float fx1 = boxes[4 * n] / stride, fy1 = boxes[4 * n + 1] / stride;
+  const float fx2 = boxes[4 * n + 2] / stride, fy2 = boxes[4 * n + 3] / stride;
+  // int() truncation, +-2, clamps (:157-161)
+  int x1 = (int)fx1 - 2, y1 = (int)fy1 - 2, x2 = (int)fx2 + 2, y2 = (int)fy2 + 2;
+  x1 = x1 < 0 ? 0 : x1;
+  y1 = y1 < 0 ? 0 : y1;
+  x2 = x2 > m_w ? m_w : x2;
+  y2 = y2 > m_h ? m_h : y2;
+  const int bw = x2 - x1, bh = y2 - y1;
+  if (bw <= 0 || bh <= 0) return;
+  // boxes_to_masks indicator on the float mask boxes
+  const float ix1 = fmaxf(fx1 - 1.0f, 0.0f), ix2 = fminf(fx2 + 1.0f, (float)m_w);
+  const float iy1 = fmaxf(fy1 - 1.0f, 0.0f), iy2 = fminf(fy2 + 1.0f, (float)m_h);
+  const float sg = margin[n];
+  const size_t HW = (size_t)m_h * m_w;
+  const int area = bw * bh;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < area; q += gridDim.x * blockDim.x) {
+    const int yy = q / bw, x = q - yy * bw + x1, y = yy + y1;
+    const size_t pid = (size_t)y * m_w + x;
+    float norm2 = 0.0f;
+    for (int d = 0; d < dim; ++d) {
+      const float t = pixel_embed[(size_t)d * HW + pid] - ec[d];
+      norm2 = norm2 + t * t;
+    }
+    const bool in = ((float)x >= ix1) && ((float)x < ix2) && ((float)y >= iy1) && ((float)y < iy2);
+    masks[(size_t)n * HW + pid] = rp_expf(-norm2 * sg) * (in ? 1.0f : 0.0f);
+  }
+}
+
+// masks [n,h,w] float -> bilinear x (H/h, W/w), align_corners=False -> > thresh -> [:crop_h, :crop_w] as
+// uint8 (inference.py:199-202: nn.interpolate(scale_factor=stride) > mask_th, cropped to the input size).
+// One thread per 4 output pixels; HBM-bound on the output bytes.
+__global__ void __launch_bounds__(256)
+resize_threshold_kernel(const float* __restrict__ masks, int h, int w, int H, int W, float thresh, int crop_h,
+                        int crop_w, uint8_t* __restrict__ out) {
+  const int n = blockIdx.y;
+  const float* img = masks + (size_t)n * h * w;
+  const float sy = (float)h / (float)H, sx = (float)w / (float)W;
+  const size_t plane = (size_t)crop_h * crop_w;
+  uint8_t* dst = out + (size_t)n * plane;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g * 4 < plane; g += (size_t)gridDim.x * blockDim.x) {
+    const size_t p0 = g * 4;
+    const int nv = plane - p0 < 4 ? (int)(plane - p0) : 4;
+    int Y = (int)(p0 / crop_w), X = (int)(p0 - (size_t)Y * crop_w);
+    for (int j = 0; j < nv; ++j) {
+      const float fy = rp_resize_src(Y, sy), fx = rp_resize_src(X, sx);
+      int y0 = (int)fy, x0 = (int)fx;
+      if (y0 > h - 1) y0 = h - 1;
+      if (x0 > w - 1) x0 = w - 1;
+      const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+      const float h1 = fy - (float)y0, h0 = 1.0f - h1, w1 = fx - (float)x0, w0 = 1.0f - w1;
+      const float top = w0 * img[y0 * w + x0] + w1 * img[y0 * w + x1];
+      const float bot = w0 * img[y1 * w + x0] + w1 * img[y1 * w + x1];
+      dst[p0 + j] = (h0 * top + h1 * bot) > thresh ? 1 : 0;
+      if (++X == crop_w) {
+        X = 0;
+        ++Y;
+      }
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -277,6 +356,38 @@ int rp_affine_paste(const float* pred, const double* M, int n, int h, int w, int
   if (gx > 2048) gx = 2048;
   affine_paste_kernel<<<dim3(gx, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(pred, M, h, w, C, channel, width,
                                                                               height, out);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_embed_masks(const float* pixel_embed, const float* proposal_embed, const float* proposal_margin,
+                   const float* boxes, float stride, int n, int dim, int m_h, int m_w, float* masks,
+                   void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) return RP_OK;
+  if (!pixel_embed || !proposal_embed || !proposal_margin || !boxes || !masks || n < 0 || dim < 1 || m_h < 1 ||
+      m_w < 1 || !(stride > 0))
+    return RP_E_ARG;
+  if (dim > MP_MAXDIM || n > 65535) return RP_E_LIMIT;
+  RP_CUDA_TRY(cudaMemsetAsync(masks, 0, sizeof(float) * (size_t)n * m_h * m_w, st));
+  embed_masks_kernel<<<dim3(16, (unsigned)n), 256, 0, st>>>(pixel_embed, proposal_embed, proposal_margin, boxes,
+                                                            0.f, stride, dim, m_h, m_w, masks);
+  RP_LAUNCH_CHECK();
+  return RP_OK;
+}
+
+int rp_resize_threshold(const float* masks, int n, int h, int w, int H, int W, float thresh, int crop_h,
+                        int crop_w, uint8_t* out, void* stream) {
+  if (n == 0) return RP_OK;
+  if (!masks || !out || n < 0 || h < 1 || w < 1 || H < 1 || W < 1 || crop_h < 1 || crop_w < 1 || crop_h > H ||
+      crop_w > W)
+    return RP_E_ARG;
+  if (n > 65535) return RP_E_LIMIT;
+  const size_t groups = ((size_t)crop_h * crop_w + 3) / 4;
+  unsigned gx = (unsigned)((groups + 255) / 256);
+  if (gx > 2048) gx = 2048;
+  resize_threshold_kernel<<<dim3(gx, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(masks, h, w, H, W, thresh,
+                                                                                  crop_h, crop_w, out);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

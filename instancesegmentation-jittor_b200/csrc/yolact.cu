@@ -631,8 +631,7 @@ int rp_yolact_prefilter(const float* loc, const float* conf, const float* mask, 
   const dim3 grid((unsigned)nchunks, (unsigned)B);
   const size_t flag_smem = (size_t)YP_CHUNK * NC * sizeof(float);
   if (flag_smem > 200 * 1024) return RP_E_LIMIT;  // NC <= 200 classes
-  RP_CUDA_TRY(cudaFuncSetAttribute(yp_flag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)flag_smem));
+  RP_SET_MAX_SMEM(yp_flag_kernel, flag_smem);
   yp_flag_kernel<<<grid, YP_CHUNK, flag_smem, st>>>(conf, P, NC, conf_thresh, w.flags, w.chunk_count);
   RP_LAUNCH_CHECK();
   yp_scan_kernel<<<1, FN_MAX_TOPK, 0, st>>>(w.chunk_count, B, nchunks, cand_cap, w.chunk_off,

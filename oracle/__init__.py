@@ -492,3 +492,30 @@ def affine_paste(pred, M, width, height, channel=1, return_values=False):
                            int(width), int(height), out.ctypes.data_as(_u8p),
                            vals.ctypes.data_as(_f32p) if return_values else None)
     return (out, vals) if return_values else out
+
+
+def embed_masks(pixel_embed, proposal_embed, proposal_margin, boxes, stride):
+    """det/modeling/rpn/embed_mask/inference.py:153-169 + :193-197 composed from the restated pieces:
+    pixel_embed [dim,m_h,m_w], boxes [n,4] image pixels -> masks [n,m_h,m_w] float."""
+    pe = np.ascontiguousarray(pixel_embed, np.float32)
+    dim, m_h, m_w = pe.shape
+    n = proposal_embed.shape[0]
+    mask_boxes = (np.asarray(boxes, np.float32) / np.float32(stride)).astype(np.float32)
+    ib = mask_boxes.astype(np.int32)  # .int(): truncation toward zero
+    ib[:, 0] = np.maximum(ib[:, 0] - 2, 0)
+    ib[:, 1] = np.maximum(ib[:, 1] - 2, 0)
+    ib[:, 2] = np.minimum(ib[:, 2] + 2, m_w)
+    ib[:, 3] = np.minimum(ib[:, 3] + 2, m_h)
+    areas = ((ib[:, 2] - ib[:, 0]) * (ib[:, 3] - ib[:, 1])).astype(np.int32)
+    ep = np.ascontiguousarray(pe.reshape(dim, m_h * m_w).T)
+    prob = mask_prob(ep, proposal_embed, proposal_margin, ib, areas, m_w).reshape(n, m_h, m_w)
+    _, ind = box_masks(mask_boxes, m_h, m_w, 0.0, crop=False)
+    return (prob * ind.astype(np.float32)).astype(np.float32)
+
+
+def resize_threshold(masks, H, W, thresh, crop_h, crop_w):
+    """inference.py:199-202: bilinear resize (align_corners=False) > thresh, cropped."""
+    out = np.zeros((masks.shape[0], crop_h, crop_w), np.uint8)
+    for i in range(masks.shape[0]):
+        out[i] = (bilinear_resize(masks[i], H, W) > np.float32(thresh))[:crop_h, :crop_w]
+    return out

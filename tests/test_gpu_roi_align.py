@@ -173,9 +173,11 @@ def test_forward_kernel_variants(impl, P, sr, monkeypatch):
     merged taps, reference-order fallback; adaptive sampling always takes the column walk)
     against the oracle, on aligned (W % 4 == 0), 8-byte (W = 42) and odd-width maps."""
     monkeypatch.setenv("RP_ROI_IMPL", impl)
+    rp.reload_env()
     rng = np.random.default_rng(11)
     for (H, W), C, cpc in [((50, 84), 37, "16"), ((25, 42), 8, "64"), ((13, 19), 5, "64"), ((3, 9), 4, "64")]:
         monkeypatch.setenv("RP_ROI_CPC", cpc)
+        rp.reload_env()
         feat = rng.standard_normal((2, C, H, W)).astype(np.float32)
         rois = _rois(rng, 90, 2)
         rois[:, 1:] *= np.float32(W * 16 / 1344)
@@ -187,6 +189,7 @@ def test_forward_kernel_variants(impl, P, sr, monkeypatch):
 @pytest.mark.parametrize("impl", ["4", "5"])
 def test_banded_pooler_multi_level(impl, monkeypatch):
     monkeypatch.setenv("RP_ROI_IMPL", impl)
+    rp.reload_env()
     N, C = 2, 24
     feats = synth.fpn_features(N, C)
     rois = synth.rois_for_images(N, 200)
@@ -210,6 +213,7 @@ def test_backward_kernels_agree_with_oracle_on_wide_bins(monkeypatch):
         exp = oracle.roi_align_backward(d, rois, feat_shape, 1 / 16, sr)
         for impl in ("2", "1"):
             monkeypatch.setenv("RP_ROI_BWD_IMPL", impl)
+            rp.reload_env()
             got = rp.roi_align_backward(T(d), T(rois), feat_shape, 1 / 16, sr).cpu().numpy()
             np.testing.assert_allclose(got, exp, rtol=1e-5, atol=1e-5 * max(1.0, np.abs(exp).max()))
 

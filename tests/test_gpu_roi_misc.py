@@ -102,3 +102,34 @@ def test_affine_paste_bit_exact():
         ref = cv2.warpAffine(pred[i], M[i], (width, height), borderMode=cv2.BORDER_CONSTANT,
                              flags=cv2.WARP_INVERSE_MAP + cv2.INTER_LINEAR)[:, :, 1]
         np.testing.assert_array_equal(got[i], (ref > 0.5).astype(np.uint8))
+
+
+def test_embed_mask_stage_matches_oracle():
+    # rp_embed_masks / rp_resize_threshold against the composed oracle (inference.py:153-202)
+    rng = np.random.default_rng(9)
+    dim, m_h, m_w, n, stride = 32, 100, 136, 24, 4.0
+    pe = (rng.standard_normal((dim, m_h, m_w)) * 0.3).astype(np.float32)
+    ce = (rng.standard_normal((n, dim)) * 0.3).astype(np.float32)
+    mg = rng.uniform(0.05, 2.0, n).astype(np.float32)
+    bx = synth.proposals(n, 3, img_w=int(m_w * stride), img_h=int(m_h * stride), smin=20, smax=300, adversarial=False)
+    bx[0] = (0, 0, m_w * stride - 1, m_h * stride - 1)
+    bx[1] = (50.5, 60.25, 50.9, 60.75)       # sub-pixel box
+    bx[2] = (-30, -20, 40, 50)               # partly outside
+    exp = oracle.embed_masks(pe, ce, mg, bx, stride)
+    got = rp.embed_masks(T(pe), T(ce), T(mg), T(bx), stride)
+    np.testing.assert_array_equal(got.cpu().numpy(), exp)
+    # the unfused mirror of compute_mask_prob + boxes_to_masks gives the same product
+    stage = rp.EmbedMaskMaskStage(8, 2, 0.5, True)
+    prob = stage.compute_mask_prob(T(pe), T(ce), T(mg), T(bx) / stride)
+    twin = prob * rp.boxes_to_masks(T(bx) / stride, m_h, m_w).float()
+    np.testing.assert_array_equal(twin.cpu().numpy(), exp)
+    in_h, in_w = 390, 540
+    up = rp.resize_threshold(got, stride, 0.5, in_h, in_w).cpu().numpy()
+    np.testing.assert_array_equal(up, oracle.resize_threshold(exp, int(m_h * stride), int(m_w * stride), 0.5, in_h, in_w))
+    bl = rp.BoxList(T(bx), (in_w, in_h))
+    bl.add_field("proposal_embed", T(ce))
+    bl.add_field("proposal_margin", T(mg))
+    bl.add_field("labels", torch.ones(n, device=DEV))
+    bl.add_field("scores", torch.ones(n, device=DEV))
+    res = stage.forward_for_mask([bl], T(pe)[None])
+    np.testing.assert_array_equal(res[0].get_field("mask").cpu().numpy().astype(np.uint8), up)

@@ -39,7 +39,7 @@ def dump_profile():
     a = np.frombuffer(buf, dtype=np.int32).copy()[256:256 + 32 * 12 * 2].view(np.int64).reshape(32, 12)
     if not a.any():
         return
-    roles = {0: "TMA", 1: "MMA", 2: "PLAN", 3: "FREE", 4: "EPI", 5: "EPI", 6: "EPI", 7: "EPI"}
+    roles = {0: "TMA", 1: "MMA", 2: "PLAN", 3: "PLAN", 4: "EPI", 5: "EPI", 6: "EPI", 7: "EPI", 8: "FREE"}
     names = ["total", "plan_full", "plan_empty", "tile_empty", "d_empty", "v_full", "d_full", "v_freed",
              "tile_full", "issued", "work", "units"]
     print("  warp role  " + " ".join("%10s" % n for n in names))
@@ -50,6 +50,7 @@ def dump_profile():
 
 def run(impl, fn):
     os.environ["RP_ROI_IMPL"] = str(impl)
+    rp.reload_env()
     try:
         out = fn()
         torch.cuda.synchronize()
@@ -131,6 +132,7 @@ for res in (14, 7):
     ok &= bad == 0
     for impl, o in ((3, o3), (6, o6)):
         os.environ["RP_ROI_IMPL"] = str(impl)
+        rp.reload_env()
         fn = lambda: rp.pooler_forward(feats, synth.FPN_SCALES, rois, levels, (res, res), 2, out=o)
         for _ in range(3):
             fn()
