@@ -179,6 +179,7 @@ def gather_run(rp, torch, dist, dev, rank, world, keep):
            "payload_bytes_this_rank": int(m * (8 + 8 + 4 + 16) + m * ((550 * 550 + 7) // 8)),
            "pack_masks_ms": pack_ms, "pack_masks_gbs": mk.numel() * 1.125 / (pack_ms * 1e-3) / 1e9 if m else None}
     if world > 1:
+        rp.parallel.gather_detections(ids, cls, sc, bx, mk)  # warm-up: NCCL sets its channels up lazily
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()

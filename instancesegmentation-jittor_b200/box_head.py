@@ -188,6 +188,33 @@ class PostProcessor(torch.nn.Module):
         return result
 
 
+    def filter_results_v2(self, boxlist, num_classes):
+        """inference.py:198-243: ONE multi-label NMS over every (row, class) above the threshold, then
+        the detections_per_img highest scores (topk, sorted).  Kept as the reference has it, including
+        its indexing: the box of candidate (row, label) is boxes[row, label - 1] (:218, the column index
+        of scores[:, 1:] is used unshifted).  boxlist_ml_nms already returns descending scores (stable),
+        so topk(k) is its first k rows."""
+        boxes = boxlist.bbox.reshape(-1, num_classes, 4)
+        scores = boxlist.get_field("scores").reshape(-1, num_classes)[:, 1:]
+        inds = (scores > self.score_thresh).nonzero()
+        labels = inds[:, 1] + 1
+        sc = scores[inds[:, 0], inds[:, 1]].contiguous()
+        bx = boxes[inds[:, 0], inds[:, 1], :].reshape(-1, 4).contiguous()
+        if bx.shape[0] > 0 and self.nms > 0:
+            keep = layers.ml_nms(bx, sc, labels.float(), self.nms)
+            bx, sc, labels = bx[keep], sc[keep], labels[keep]
+        if bx.shape[0] > self.detections_per_img > 0:
+            if not self.nms > 0:  # no NMS ran: order by score first
+                order = torch.sort(sc, descending=True, stable=True)[1]
+                bx, sc, labels = bx[order], sc[order], labels[order]
+            k = self.detections_per_img
+            bx, sc, labels = bx[:k], sc[:k], labels[:k]
+        result = BoxList(bx, boxlist.size, mode="xyxy")
+        result.add_field("scores", sc)
+        result.add_field("labels", labels)
+        return result
+
+
 def make_roi_box_post_processor(cfg):
     """inference.py:244-266; cfg is any object with the MODEL.* / TEST.* attributes."""
     rh = cfg.MODEL.ROI_HEADS

@@ -108,6 +108,277 @@ __global__ void rpn_keys_kernel(const __grid_constant__ RpnLevels lv, uint64_t* 
   vals[o] = e;
 }
 
+
+// ---- per-problem top-k without a sort of all anchors -------------------------------------------
+// topk(pre_nms_top_n, sorted=True) of every (level, image) (rpn/inference.py:83-111) as a byte-wise
+// radix SELECT spread over the whole GPU, then a small sort of the k survivors per problem:
+//   rs_keys     coalesced walk of the NCHW objectness tensors: 32-bit key (descending sigmoid bits) written
+//               at the element's flattened (h, w, a) position + histogram of the top byte (shared-memory
+//               histogram per 1024-element chunk, flushed with a few global atomics)
+//   rs_hist x3  every chunk first derives, from the previous pass's histogram, which bin holds the k-th key
+//               of its problem (all chunks of a problem compute the same thing), then histograms the next byte
+//               of the keys that match the prefix so far
+//   rs_ties     the k-th key T is known: per chunk, how many keys equal T (ties are taken in ascending
+//               flattened index = ascending position)
+//   rs_collect  keys < T go to the problem's list through an atomic cursor; a chunk takes its ties only while
+//               (ties in earlier chunks + rank inside the chunk) < needed
+//   rs_sort     one CTA per problem: bitonic sort of (key << 32 | index) in shared memory, indices out
+// Replaces the 64-bit cub::DeviceRadixSort over all L*N*A*H*W anchors of the batch (38 % of the stage's
+// device time in round 1: 5 onesweep passes over 2.15 M pairs).
+constexpr int RS_CAP = 4096;     // pre_nms_top_n handled here; larger values keep the sort path
+constexpr int RS_CHUNK = 1024;   // elements per CTA (256 threads x 4)
+
+struct RsPlan {
+  int chunk_base[RP_MAX_LEVELS + 1];  // prefix of N * chunks_per_problem[l]
+  int cpp[RP_MAX_LEVELS];             // chunks per problem of level l
+  uint32_t* keys;                     // [n_elems] in flattened order
+  int* hist;                          // [4][S][256]
+  int* state;                         // [4][S][2]: prefix, remaining rank after the pass
+  int* tie_cnt;                       // [n_chunks]
+  int* cursor;                        // [S]
+  unsigned long long* list;           // [S][RS_CAP]
+};
+
+struct RsWhere {
+  int l, b, j, s, per, base;  // level, image, chunk inside the problem, problem id, elements, first element
+};
+
+__device__ __forceinline__ RsWhere rs_where(const RpnLevels& lv, const RsPlan& pl, int chunk) {
+  RsWhere w;
+  int l = 0;
+  while (l + 1 < lv.L && chunk >= pl.chunk_base[l + 1]) ++l;
+  const int r = chunk - pl.chunk_base[l];
+  w.l = l;
+  w.b = r / pl.cpp[l];
+  w.j = r - w.b * pl.cpp[l];
+  w.s = l * lv.N + w.b;
+  w.per = lv.A[l] * lv.HW[l];
+  w.base = lv.elem_base[l] + w.b * w.per;
+  return w;
+}
+
+// The bin of `hist` (256 counts) that holds the rank-th smallest (1-based) value, and how many values
+// lie in lower bins; evaluated by the whole CTA (256 threads), result in every thread.
+__device__ __forceinline__ void rs_pick(const int* __restrict__ hist, int rank, int* s_scan, int* bin,
+                                        int* before, int* count) {
+  const int t = threadIdx.x;
+  const int v = hist[t];
+  // inclusive scan over 256 threads
+  int inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, inc, d);
+    if ((t & 31) >= d) inc += u;
+  }
+  if ((t & 31) == 31) s_scan[t >> 5] = inc;
+  __syncthreads();
+  int wbase = 0;
+  for (int w = 0; w < (t >> 5); ++w) wbase += s_scan[w];
+  inc += wbase;
+  const int exc = inc - v;
+  __syncthreads();
+  if (exc < rank && inc >= rank) {
+    s_scan[8] = t;
+    s_scan[9] = exc;
+    s_scan[10] = v;
+  }
+  __syncthreads();
+  *bin = s_scan[8];
+  *before = s_scan[9];
+  *count = s_scan[10];
+  __syncthreads();
+}
+
+// prefix / remaining rank of problem s after passes 3 .. pass+1 (recomputed by every chunk; chunk 0 stores it)
+__device__ __forceinline__ void rs_state(const RpnLevels& lv, const RsPlan& pl, const RsWhere& w, int S, int pass,
+                                         int* s_scan, uint32_t* prefix, int* rank, int* last_count) {
+  uint32_t pre = 0;
+  int kk = lv.k[w.l], cnt = 0;
+  if (pass < 3) {
+    if (pass < 2) {  // state after the pass before the previous one was stored by chunk 0 of that launch
+      pre = (uint32_t)pl.state[((pass + 2) * S + w.s) * 2];
+      kk = pl.state[((pass + 2) * S + w.s) * 2 + 1];
+    }
+    int bin, before;
+    rs_pick(pl.hist + ((size_t)(pass + 1) * S + w.s) * 256, kk, s_scan, &bin, &before, &cnt);
+    pre |= (uint32_t)bin << (8 * (pass + 1));
+    kk -= before;
+    if (w.j == 0 && threadIdx.x == 0) {
+      pl.state[((pass + 1) * S + w.s) * 2] = (int)pre;
+      pl.state[((pass + 1) * S + w.s) * 2 + 1] = kk;
+    }
+  }
+  *prefix = pre;
+  *rank = kk;
+  *last_count = cnt;
+}
+
+__global__ void __launch_bounds__(256)
+rs_keys_kernel(const __grid_constant__ RpnLevels lv, const __grid_constant__ RsPlan pl, int S) {
+  __shared__ int hist[256];
+  const RsWhere w = rs_where(lv, pl, blockIdx.x);
+  hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int A = lv.A[w.l], HW = lv.HW[w.l];
+  const float* obj_b = lv.obj[w.l] + (size_t)w.b * w.per;
+#pragma unroll
+  for (int q = 0; q < RS_CHUNK / 256; ++q) {
+    const int i = w.j * RS_CHUNK + q * 256 + threadIdx.x;  // memory order (a, hw)
+    if (i < w.per) {
+      const int a = i / HW, hw = i - a * HW;
+      const uint32_t key = rpn_desc_bits(rp_sigmoidf(obj_b[i]));
+      pl.keys[w.base + hw * A + a] = key;
+      atomicAdd(&hist[key >> 24], 1);
+    }
+  }
+  __syncthreads();
+  const int v = hist[threadIdx.x];
+  if (v) atomicAdd(&pl.hist[((size_t)3 * S + w.s) * 256 + threadIdx.x], v);
+}
+
+__global__ void __launch_bounds__(256)
+rs_hist_kernel(const __grid_constant__ RpnLevels lv, const __grid_constant__ RsPlan pl, int S, int pass) {
+  __shared__ int hist[256];
+  __shared__ int s_scan[12];
+  const RsWhere w = rs_where(lv, pl, blockIdx.x);
+  uint32_t prefix;
+  int rank, cnt;
+  rs_state(lv, pl, w, S, pass, s_scan, &prefix, &rank, &cnt);
+  hist[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t mask = 0xffffffffu << (8 * (pass + 1));
+  const int sh = 8 * pass;
+#pragma unroll
+  for (int q = 0; q < RS_CHUNK / 256; ++q) {
+    const int e = w.j * RS_CHUNK + q * 256 + threadIdx.x;
+    if (e < w.per) {
+      const uint32_t key = pl.keys[w.base + e];
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> sh) & 255u], 1);
+    }
+  }
+  __syncthreads();
+  const int v = hist[threadIdx.x];
+  if (v) atomicAdd(&pl.hist[((size_t)pass * S + w.s) * 256 + threadIdx.x], v);
+}
+
+// pass == -1 in rs_state terms: all four bytes known after this derivation
+__device__ __forceinline__ void rs_final(const RpnLevels& lv, const RsPlan& pl, const RsWhere& w, int S, int* s_scan,
+                                         uint32_t* T, int* need, int* equal) {
+  uint32_t pre = (uint32_t)pl.state[(1 * S + w.s) * 2];
+  int kk = pl.state[(1 * S + w.s) * 2 + 1];
+  int bin, before, cnt;
+  rs_pick(pl.hist + ((size_t)0 * S + w.s) * 256, kk, s_scan, &bin, &before, &cnt);
+  *T = pre | (uint32_t)bin;
+  *need = kk - before;
+  *equal = cnt;
+}
+
+__global__ void __launch_bounds__(256)
+rs_ties_kernel(const __grid_constant__ RpnLevels lv, const __grid_constant__ RsPlan pl, int S) {
+  __shared__ int s_scan[12];
+  __shared__ int s_n;
+  const RsWhere w = rs_where(lv, pl, blockIdx.x);
+  uint32_t T;
+  int need, equal;
+  rs_final(lv, pl, w, S, s_scan, &T, &need, &equal);
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
+  int n = 0;
+#pragma unroll
+  for (int q = 0; q < RS_CHUNK / 256; ++q) {
+    const int e = w.j * RS_CHUNK + q * 256 + threadIdx.x;
+    if (e < w.per && pl.keys[w.base + e] == T) ++n;
+  }
+  if (n) atomicAdd(&s_n, n);
+  __syncthreads();
+  if (threadIdx.x == 0) pl.tie_cnt[blockIdx.x] = s_n;
+}
+
+__global__ void __launch_bounds__(256)
+rs_collect_kernel(const __grid_constant__ RpnLevels lv, const __grid_constant__ RsPlan pl, int S) {
+  __shared__ int s_scan[12];
+  __shared__ int s_w[8];
+  const RsWhere w = rs_where(lv, pl, blockIdx.x);
+  uint32_t T;
+  int need, equal;
+  rs_final(lv, pl, w, S, s_scan, &T, &need, &equal);
+  // ties in the earlier chunks of this problem
+  int earlier = 0;
+  {
+    const int c0 = blockIdx.x - w.j;
+    int part = 0;
+    for (int c = threadIdx.x; c < w.j; c += 256) part += pl.tie_cnt[c0 + c];
+#pragma unroll
+    for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = part;
+    __syncthreads();
+    for (int i = 0; i < 8; ++i) earlier += s_w[i];
+    __syncthreads();
+  }
+  unsigned long long* list = pl.list + (size_t)w.s * RS_CAP;
+  // the chunk's elements in ascending position: thread t takes positions 4t .. 4t+3
+  const int e0 = w.j * RS_CHUNK + threadIdx.x * 4;
+  uint32_t key[4];
+  int tie = 0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    key[q] = (e0 + q < w.per) ? pl.keys[w.base + e0 + q] : 0xffffffffu;
+    if (e0 + q < w.per && key[q] == T) ++tie;
+  }
+  // exclusive scan of the tie counts over the CTA
+  int inc = tie;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, inc, d);
+    if ((threadIdx.x & 31) >= d) inc += u;
+  }
+  if ((threadIdx.x & 31) == 31) s_w[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  int rank = earlier + inc - tie;
+  for (int i = 0; i < (threadIdx.x >> 5); ++i) rank += s_w[i];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (e0 + q >= w.per) continue;
+    bool take = key[q] < T;
+    if (key[q] == T) {
+      take = rank < need;
+      ++rank;
+    }
+    if (take) {
+      const int pos = atomicAdd(&pl.cursor[w.s], 1);
+      if (pos < RS_CAP) list[pos] = ((unsigned long long)key[q] << 32) | (uint32_t)(e0 + q);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+rs_sort_kernel(const __grid_constant__ RpnLevels lv, const __grid_constant__ RsPlan pl, int* __restrict__ vals_out) {
+  __shared__ unsigned long long list[RS_CAP];
+  const int s = blockIdx.x;
+  const int l = s / lv.N, b = s - l * lv.N;
+  const int k = lv.k[l], per = lv.A[l] * lv.HW[l];
+  int np2 = 1;
+  while (np2 < k) np2 <<= 1;
+  const unsigned long long* src = pl.list + (size_t)s * RS_CAP;
+  for (int i = threadIdx.x; i < np2; i += 1024) list[i] = i < k ? src[i] : ~0ull;
+  __syncthreads();
+  for (int size = 2; size <= np2; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = threadIdx.x; t < (np2 >> 1); t += 1024) {
+        const int lo = ((t / stride) * stride * 2) + (t % stride), hi = lo + stride;
+        const bool up = ((lo & size) == 0);
+        const unsigned long long x = list[lo], y = list[hi];
+        if ((x > y) == up) {
+          list[lo] = y;
+          list[hi] = x;
+        }
+      }
+      __syncthreads();
+    }
+  int* dst = vals_out + lv.elem_base[l] + (size_t)b * per;
+  for (int j = threadIdx.x; j < k; j += 1024) dst[j] = (int)(uint32_t)(list[j] & 0xffffffffull);
+}
+
 template <int T>
 __device__ __forceinline__ int rpn_block_excl_scan(int v, int* warp_sums, int* total) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -446,10 +717,43 @@ int rp_rpn_pre_nms_levels(const float* const* objectness, const float* const* bo
   const int n_elems = lv.elem_base[L];
   RpnWorkspace w = rpn_carve(workspace, (size_t)n_elems, (size_t)lv.slot_base[L], S);
   if (w.total > workspace_bytes) return RP_E_WORKSPACE;
-  rpn_keys_kernel<<<(unsigned)((n_elems + 255) / 256), 256, 0, st>>>(lv, w.keys_in, w.vals_in);
-  RP_LAUNCH_CHECK();
-  RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out, w.vals_in,
-                                              w.vals_out, n_elems, 0, 32 + rpn_bits((size_t)S), st));
+  RsPlan pl;
+  int n_chunks = 0;
+  for (int l = 0; l < RP_MAX_LEVELS; ++l) pl.cpp[l] = 0;
+  for (int l = 0; l < L; ++l) {
+    pl.chunk_base[l] = n_chunks;
+    pl.cpp[l] = (lv.A[l] * lv.HW[l] + RS_CHUNK - 1) / RS_CHUNK;
+    n_chunks += N * pl.cpp[l];
+  }
+  for (int l = L; l <= RP_MAX_LEVELS; ++l) pl.chunk_base[l] = n_chunks;
+  // scratch carved from the sort path's key buffers (8 bytes per element each)
+  const size_t small_bytes = rp_align_up(sizeof(int) * ((size_t)4 * S * 256 + (size_t)4 * S * 2 + S), 256);
+  const size_t need_in = rp_align_up((size_t)n_elems * 4, 256) + small_bytes + rp_align_up(4 * (size_t)n_chunks, 256);
+  const size_t need_out = sizeof(unsigned long long) * (size_t)S * RS_CAP;
+  if (kmax <= RS_CAP && need_in <= 8 * (size_t)n_elems && need_out <= 8 * (size_t)n_elems &&
+      rp_env_int("RP_RPN_SELECT", 1)) {
+    // per-problem radix select + small sort (no pass over all anchors of the batch with 64-bit keys)
+    char* base = reinterpret_cast<char*>(w.keys_in);
+    pl.keys = reinterpret_cast<uint32_t*>(base);
+    char* small = base + rp_align_up((size_t)n_elems * 4, 256);
+    pl.hist = reinterpret_cast<int*>(small);
+    pl.state = pl.hist + (size_t)4 * S * 256;
+    pl.cursor = pl.state + (size_t)4 * S * 2;
+    pl.tie_cnt = reinterpret_cast<int*>(small + small_bytes);
+    pl.list = reinterpret_cast<unsigned long long*>(w.keys_out);
+    RP_CUDA_TRY(cudaMemsetAsync(small, 0, small_bytes, st));
+    rs_keys_kernel<<<n_chunks, 256, 0, st>>>(lv, pl, S);
+    for (int pass = 2; pass >= 0; --pass) rs_hist_kernel<<<n_chunks, 256, 0, st>>>(lv, pl, S, pass);
+    rs_ties_kernel<<<n_chunks, 256, 0, st>>>(lv, pl, S);
+    rs_collect_kernel<<<n_chunks, 256, 0, st>>>(lv, pl, S);
+    rs_sort_kernel<<<S, 1024, 0, st>>>(lv, pl, w.vals_out);
+    RP_LAUNCH_CHECK();
+  } else {
+    rpn_keys_kernel<<<(unsigned)((n_elems + 255) / 256), 256, 0, st>>>(lv, w.keys_in, w.vals_in);
+    RP_LAUNCH_CHECK();
+    RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out, w.vals_in,
+                                                w.vals_out, n_elems, 0, 32 + rpn_bits((size_t)S), st));
+  }
   rpn_decode_kernel<<<S, RPN_THREADS, 0, st>>>(lv, im_wh, w.vals_out, min_size, wx, wy, ww, wh,
                                                bbox_xform_clip, w.pad_boxes, w.pad_scores,
                                                w.pad_index, w.counts);

@@ -113,3 +113,22 @@ def test_errors_are_loud():
         rp.box_post(T(lg), T(reg), T(pr), offs, T(wh), 20, 0.05, float("nan"), 100)
     with pytest.raises(Exception):
         rp.box_post(torch.from_numpy(lg), T(reg), T(pr), offs, T(wh), 20, 0.05, 0.5, 100)
+
+
+def test_filter_results_v2_matches_numpy_restatement():
+    # inference.py:198-243: one ml_nms over all (row, class) candidates + topk; box column = label - 1
+    lg, reg, pr, counts, wh = synth.box_head_batch(1, 400, num_classes=21, seed=12, ties=True)
+    C = 21
+    post = rp.PostProcessor(0.05, 0.5, 30)
+    prob = oracle.softmax_rows(lg)
+    dec = rp.box_decode(T(reg), T(pr), (10.0, 10.0, 5.0, 5.0))
+    bl = post.prepare_boxlist(dec, T(prob), (int(wh[0, 0]), int(wh[0, 1]))).clip_to_image(remove_empty=False)
+    got = post.filter_results_v2(bl, C)
+    boxes = bl.bbox.cpu().numpy().reshape(-1, C, 4)
+    sc = prob[:, 1:]
+    r, c = np.nonzero(sc > np.float32(0.05))
+    cb, cs, cl = boxes[r, c], sc[r, c], (c + 1).astype(np.float32)
+    keep = oracle.ml_nms(cb, cs, cl, 0.5)[:30]
+    np.testing.assert_array_equal(got.bbox.cpu().numpy(), cb[keep])
+    np.testing.assert_array_equal(got.get_field("scores").cpu().numpy(), cs[keep])
+    np.testing.assert_array_equal(got.get_field("labels").cpu().numpy(), (c + 1)[keep])

@@ -185,3 +185,38 @@ def test_errors_are_loud():
         rp.rpn_pre_nms(T(obj), T(reg[:, :8]), T(anchors), T(im_wh), 100, 0)
     with pytest.raises(Exception):
         rp.rpn_pre_nms(obj, reg, anchors, im_wh, 100, 0)  # numpy / CPU input: no fallback
+
+
+def test_sort_path_and_select_path_agree(monkeypatch):
+    # RP_RPN_SELECT=0 keeps the whole-batch radix sort; the default per-problem radix select must
+    # give the same candidates in the same order (massive ties: logits quantised to 1/4)
+    N, A, H, W, stride = 2, 3, 100, 168, 8
+    anchors, obj, reg, im_wh = synth.rpn_level(N, A, H, W, stride, seed=5, ties=True)
+    obj[0, :, :40] = 3.0  # one huge plateau of equal scores: the cut falls inside it
+    outs = []
+    for sel in ("1", "0"):
+        monkeypatch.setenv("RP_RPN_SELECT", sel)
+        rp.reload_env()
+        b, s, i, o, k = rp.rpn_pre_nms(T(obj), T(reg), T(anchors), T(im_wh), 1000, 0.0)
+        outs.append((b.cpu().numpy(), s.cpu().numpy(), i.cpu().numpy(), o.cpu().numpy()))
+    monkeypatch.delenv("RP_RPN_SELECT")
+    rp.reload_env()
+    for x, y in zip(*outs):
+        np.testing.assert_array_equal(x, y)
+    ref = oracle.rpn_pre_nms(obj, reg, anchors, im_wh, 1000, 0.0)
+    np.testing.assert_array_equal(outs[0][2][: len(ref[0][2])], ref[0][2])
+
+
+def test_anchors_are_not_cached_by_address():
+    # a landscape batch followed by a portrait batch with the same anchor count must be
+    # decoded against its own anchors (the reference builds new anchor tensors on every forward)
+    post = rp.RPNPostProcessor(pre_nms_top_n=200, post_nms_top_n=50, nms_thresh=0.7, min_size=0)
+    res = []
+    for (H, W, seed) in ((20, 30, 1), (30, 20, 2)):
+        anchors, obj, reg, im_wh = synth.rpn_level(1, 3, H, W, 16, seed=seed)
+        a_t = T(anchors)  # same size both times: the allocator hands back the same address
+        out = post.forward_for_single_feature_map(_anchor_lists(anchors, im_wh), T(obj), T(reg))
+        ref = _oracle_level(obj, reg, anchors, im_wh, 200, 0.0, 0.7, 50)
+        np.testing.assert_array_equal(out[0].bbox.cpu().numpy(), ref[0][0])
+        res.append(out)
+        del a_t
