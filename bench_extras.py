@@ -59,6 +59,16 @@ def local_times(rp, torch, dev, rank, world, images_per_gpu):
         ms["pooler_bwd_%dx%d" % (res, res)] = med(
             lambda: rp.pooler_backward(d, rois_b[:k], lv_b[:k], shapes, synth.FPN_SCALES, SAMPLING), n=5)
         del d
+    # --- Pooler forward on torch.channels_last feature maps (the NHWC entry), same workload as the headline
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    feats_cl = [torch.randn(s_, device=dev, generator=gen).contiguous(memory_format=torch.channels_last)
+                for s_ in shapes]
+    rois_f = T(synth.rois_for_images(images_per_gpu, 1000))
+    lv_f = rp.LevelMapper(2, 5).map_rois(rois_f)
+    out_f = torch.empty((rois_f.shape[0], CHANNELS, 14, 14), device=dev)
+    ms["pooler_fwd_nhwc_14x14"] = med(
+        lambda: rp.pooler_forward(feats_cl, synth.FPN_SCALES, rois_f, lv_f, (14, 14), SAMPLING, out=out_f), n=5)
+    del feats_cl, out_f
     # --- NMS sweep, batch 8 sharded by image (BASELINE configs[1]); thr 0.7
     b0, b1 = shard(NMS_BATCH)
     nb = max(1, b1 - b0)
@@ -248,6 +258,8 @@ def derive(ms, world, images_per_gpu, keep):
         t = ms["pooler_bwd_%dx%d" % (res, res)]
         out["pooler_bwd_%dx%d_ms" % (res, res)] = t
         out["pooler_bwd_%dx%d_gbs_per_gpu" % (res, res)] = (k * CHANNELS * res * res * 4 + grad_bytes) / (t * 1e-3) / 1e9
+    out["pooler_fwd_nhwc_14x14_ms"] = ms["pooler_fwd_nhwc_14x14"]
+    out["pooler_fwd_nhwc_layout"] = "features torch.channels_last [N,H,W,C] fp32, output [K,C,14,14]"
     per_rank = -(-NMS_BATCH // world)
     for n in (2000, 5000, 10000, 20000):
         for mk in (-1, 1000):

@@ -98,6 +98,18 @@ RP_API int rp_pooler_backward(const float* dout, const float* rois, const int* l
                        int PH, int PW, float sampling_ratio, float* const* grads, int mode,
                        void* stream);
 
+/* Channels-last entries (north_star: "NHWC-aware bilinear gathers"; the reference's layout is NCHW,
+ * det/layers/roi_align.py:116-169, so these are an ADDITIONAL path for channels-last backbones):
+ * feat / feats[l] are [N, H_l, W_l, C] fp32, every tap is one 16-byte load of 4 channels; the output
+ * stays [K, C, PH, PW].  Same semantics and tolerance as mode 0 of the NCHW entries. */
+RP_API int rp_roi_align_forward_nhwc(const float* feat, int N, int C, int H, int W, const float* rois,
+                                     int K, int PH, int PW, float spatial_scale, float sampling_ratio,
+                                     float* out, void* stream);
+RP_API int rp_pooler_forward_nhwc(const float* const* feats, const int* H, const int* W,
+                                  const float* scales, int L, int N, int C, const float* rois,
+                                  const int* levels, int K, int PH, int PW, float sampling_ratio,
+                                  float* out, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Greedy NMS family.
  * Replaces: nms(dets, scores, thr) det/layers/nms.py:12-14 (-> jittor.nms),

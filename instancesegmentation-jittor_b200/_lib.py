@@ -28,6 +28,8 @@ SIGNATURES = {
     "rp_reload_env": (None, []),
     "rp_roi_align_forward": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _f, _f, _vp, _i, _vp]),
     "rp_roi_align_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _vp]),
+    "rp_roi_align_forward_nhwc": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _f, _f, _vp, _vp]),
+    "rp_pooler_forward_nhwc": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _vp]),
     "rp_level_map": (_i, [_vp, _i, _i, _i, _f, _i, _f, _vp, _vp]),
     "rp_level_map_area": (_i, [_vp, _vp, _i, _i, _i, _f, _vp, _vp]),
     "rp_pooler_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _f, _vp, _i, _vp]),

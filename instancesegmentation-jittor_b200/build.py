@@ -18,7 +18,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libroipath_b200.so")
-SOURCES = ["roi_align.cu", "roi_fwd_tc.cu", "nms.cu", "yolact.cu", "masks.cu", "mask_loss.cu", "rpn.cu", "box_post.cu", "roi_misc.cu", "capi.cu"]
+SOURCES = ["roi_align.cu", "roi_fwd_tc.cu", "roi_nhwc.cu", "nms.cu", "yolact.cu", "masks.cu", "mask_loss.cu", "rpn.cu", "box_post.cu", "roi_misc.cu", "capi.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -1774,4 +1774,27 @@ int rp_pooler_backward(const float* dout, const float* rois, const int* levels, 
                      (cudaStream_t)stream);
 }
 
+int rp_roi_align_forward_nhwc(const float* feat, int N, int C, int H, int W, const float* rois, int K,
+                              int PH, int PW, float spatial_scale, float sampling_ratio, float* out,
+                              void* stream) {
+  if (K == 0) return RP_OK;
+  if (!feat) return RP_E_ARG;
+  RtLevels lv;
+  const float* feats[1] = {feat};
+  int rc = rt_fill_levels(&lv, feats, nullptr, &H, &W, &spatial_scale, 1);
+  if (rc) return rc;
+  return rn_forward_nhwc(lv, N, C, rois, nullptr, K, PH, PW, sampling_ratio, out, (cudaStream_t)stream);
+}
+
+int rp_pooler_forward_nhwc(const float* const* feats, const int* H, const int* W, const float* scales,
+                           int L, int N, int C, const float* rois, const int* levels, int K, int PH,
+                           int PW, float sampling_ratio, float* out, void* stream) {
+  if (K == 0) return RP_OK;
+  if (!feats || (L > 1 && !levels)) return RP_E_ARG;
+  RtLevels lv;
+  int rc = rt_fill_levels(&lv, feats, nullptr, H, W, scales, L);
+  if (rc) return rc;
+  return rn_forward_nhwc(lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, (cudaStream_t)stream);
+}
+
 }  // extern "C"

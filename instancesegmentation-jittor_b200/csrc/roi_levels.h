@@ -16,3 +16,7 @@ struct RtLevels {
 // kernel instead), or an error code.
 int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K, int PH,
                int PW, float sampling_ratio, float* out, cudaStream_t st);
+
+// roi_nhwc.cu: channels-last forward (features [N,H,W,C]); output [K,C,PH,PW].
+int rn_forward_nhwc(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K, int PH,
+                    int PW, float sampling_ratio, float* out, cudaStream_t st);

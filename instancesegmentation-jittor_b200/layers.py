@@ -30,6 +30,16 @@ def roi_align_forward(input, rois, output_size, spatial_scale, sampling_ratio, m
         out = torch.empty((K, C, PH, PW), dtype=_F32, device=input.device)
     if K == 0:  # roi_align.py:304-305
         return out
+    if (input.ndim == 4 and not input.is_contiguous()
+            and input.is_contiguous(memory_format=torch.channels_last) and mode == 0):
+        # torch.channels_last input: the NHWC entry (16-byte taps of 4 channels), output stays [K,C,PH,PW]
+        import ctypes
+        rc = _lib.lib().rp_roi_align_forward_nhwc(
+            ctypes.c_void_p(input.data_ptr()), N, C, H, W, _lib.dptr(rois, _F32, "rois"), K, PH, PW,
+            float(spatial_scale), float(sampling_ratio), _lib.dptr(out, _F32, "out"),
+            _lib.stream_ptr(input.device))
+        _lib.check(rc, "rp_roi_align_forward_nhwc")
+        return out
     rc = _lib.lib().rp_roi_align_forward(
         _lib.dptr(input, _F32, "input"), N, C, H, W, _lib.dptr(rois, _F32, "rois"), K, PH, PW,
         float(spatial_scale), float(sampling_ratio), _lib.dptr(out, _F32, "out"), int(mode),

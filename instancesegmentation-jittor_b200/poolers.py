@@ -83,6 +83,12 @@ class LevelMapperwithArea(object):
         return _level_map_area(rois, img_area, self.k_min, self.k_max, self.eps)
 
 
+def _is_channels_last(t):
+    """A [N,C,H,W] tensor whose memory is [N,H,W,C] (torch.channels_last) and not also NCHW-contiguous."""
+    return (t.ndim == 4 and t.is_cuda and t.dtype == _F32 and not t.is_contiguous()
+            and t.is_contiguous(memory_format=torch.channels_last))
+
+
 def _host_arrays(feats, scales):
     L = len(feats)
     ptrs = (ctypes.c_void_p * L)(*[f.data_ptr() for f in feats])
@@ -98,8 +104,10 @@ def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, mod
     L = len(feats)
     if L < 1 or L > _lib.RP_MAX_LEVELS:
         raise ValueError("between 1 and %d levels" % _lib.RP_MAX_LEVELS)
-    for f in feats:
-        _lib.dptr(f, _F32, "feature map")
+    nhwc = all(_is_channels_last(f) for f in feats)
+    if not nhwc:
+        for f in feats:
+            _lib.dptr(f, _F32, "feature map")
     N, C = int(feats[0].shape[0]), int(feats[0].shape[1])
     PH, PW = (output_size if isinstance(output_size, (tuple, list)) else (output_size, output_size))
     K = int(rois.shape[0])
@@ -108,6 +116,15 @@ def pooler_forward(feats, scales, rois, levels, output_size, sampling_ratio, mod
     if K == 0:
         return out
     ptrs, Hs, Ws, sc = _host_arrays(feats, scales)
+    if nhwc:  # torch.channels_last feature maps: [N,H,W,C] in memory, 16-byte taps of 4 channels
+        if mode != 0:
+            raise ValueError("mode 1 (reference operand order) exists for NCHW feature maps only")
+        rc = _lib.lib().rp_pooler_forward_nhwc(
+            ptrs, Hs, Ws, sc, L, N, C, _lib.dptr(rois, _F32, "rois"), _lib.dptr(levels, _I32, "levels"),
+            K, int(PH), int(PW), float(sampling_ratio), _lib.dptr(out, _F32, "out"),
+            _lib.stream_ptr(rois.device))
+        _lib.check(rc, "rp_pooler_forward_nhwc")
+        return out
     rc = _lib.lib().rp_pooler_forward(
         ptrs, Hs, Ws, sc, L, N, C, _lib.dptr(rois, _F32, "rois"), _lib.dptr(levels, _I32, "levels"),
         K, int(PH), int(PW), float(sampling_ratio), _lib.dptr(out, _F32, "out"), int(mode),

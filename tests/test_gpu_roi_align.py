@@ -237,3 +237,29 @@ def test_pooler_execute_host_pipeline():
     # second call reuses the staging buffers
     out2 = pooler.execute_host(h_feats, boxes_host)
     np.testing.assert_array_equal(out2.numpy(), ref.cpu().numpy())
+
+
+@pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
+@pytest.mark.parametrize("C", [37, 64])
+def test_channels_last_entry_matches_oracle(P, sr, C):
+    # torch.channels_last feature maps take the NHWC kernels (16-byte taps); same oracle, same bar
+    rng = np.random.default_rng(2)
+    N = 2
+    feat = rng.standard_normal((N, C, 50, 84)).astype(np.float32)
+    rois = _rois(rng, 150, N)
+    exp = oracle.roi_align_forward(feat, rois, P, 1 / 16, sr)
+    x = T(feat).contiguous(memory_format=torch.channels_last)
+    assert not x.is_contiguous()
+    got = rp.roi_align_forward(x, T(rois), P, 1 / 16, sr).cpu().numpy()
+    _close(got, exp)
+
+
+def test_channels_last_pooler_matches_oracle():
+    N, C = 2, 40
+    feats = synth.fpn_features(N, C)
+    rois = synth.rois_for_images(N, 200)
+    lv = oracle.level_map(rois[:, 1:], 2, 5)
+    exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, (14, 14), 2)
+    xs = [T(f).contiguous(memory_format=torch.channels_last) for f in feats]
+    got = rp.pooler_forward(xs, synth.FPN_SCALES, T(rois), T(lv), (14, 14), 2).cpu().numpy()
+    _close(got, exp)
