@@ -370,11 +370,19 @@ def run_gpu_arm(args):
     out_bytes = 4 * K * CHANNELS * RES * RES
     alg_bytes = out_bytes + 20 * K + 4 * U
     achieved = alg_bytes / (ms_kernel * 1e-3) / 1e9
-    traffic = None
+    # the kernel the forward call launches: the SIMT column walk by default, the tensor-core kernel when
+    # RP_ROI_IMPL=6 is set; `traffic` is that kernel's ncu DRAM bytes per launch (same workload), taken
+    # from the round's capture listed in profiles/roofline_traffic.json -- null without a capture
+    impl = os.environ.get("RP_ROI_IMPL", "3")
+    kernel_name = {"3": "rt_pool_fwd_kernel", "4": "rb_pool_fwd_kernel", "5": "rg_pool_fwd_kernel",
+                   "6": "rx_pool_fwd_kernel"}.get(impl, "rt_pool_fwd_kernel")
+    traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get("rt_pool_fwd_kernel_dram_bytes_per_launch")
-    roofline = {"bound": "hbm", "kernel": "rt_pool_fwd_kernel", "achieved": achieved, "peak": peak,
+        tj = json.load(open(tpath))
+        traffic = tj.get(kernel_name + "_dram_bytes_per_launch")
+        traffic_src = tj.get(kernel_name + "_capture")
+    roofline = {"bound": "hbm", "kernel": kernel_name, "traffic_source": traffic_src, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "output_bytes_per_launch": out_bytes,
                 "distinct_feature_bytes": 4 * U, "kernel_ms": ms_kernel,

@@ -418,7 +418,7 @@ __device__ __forceinline__ void rx_ypass(const RbF4* __restrict__ tile, int R, i
 __global__ void __launch_bounds__(RX_THREADS, 1)
 rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, const __grid_constant__ RxMaps maps, int n_items) {
+                   float* __restrict__ out, const __grid_constant__ RxMaps maps, int n_items, int ablate) {
   extern __shared__ unsigned char rx_smem_raw[];
   unsigned char* smem = rx_smem_raw + ((1024u - (rp_smem_addr(rx_smem_raw) & 1023u)) & 1023u);
   RxBars* bars = reinterpret_cast<RxBars*>(smem + RX_OFF_BARS);
@@ -570,8 +570,10 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                : "memory");                                                                  \
   acc = 1u;
                 RX_MMA(dah, dbh)
-                RX_MMA(dal, dbh)
-                RX_MMA(dah, dbl)
+                if (!(ablate & 1)) {  // timing ablation (RP_RX_ABLATE bit 0): hi*hi only, wrong results
+                  RX_MMA(dal, dbh)
+                  RX_MMA(dah, dbl)
+                }
 #undef RX_MMA
               }
 #ifdef RX_PROFILE
@@ -711,6 +713,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 #ifdef RX_PROFILE
           const long long yp_t0 = clock64();
 #endif
+          if (!(ablate & 2))  // timing ablation (RP_RX_ABLATE bit 1): no y-pass at all, wrong results
           rx_ypass(reinterpret_cast<const RbF4*>(smem + RX_OFF_TILE + ts * RX_SLOT) + M->seg_r0[sg] * cs * nqh,
                    M->seg_rows[sg], cs, nqh, M->mw[sg], M->wrot, M->seg_b0[sg], smem + RX_OFF_V + vs * RX_VBYTES,
                    sc * cs, lane);
@@ -907,7 +910,7 @@ int rx_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   const int grid = (int)(n_items < RP_NUM_SMS ? n_items : RP_NUM_SMS);
   rx_pool_fwd_kernel<<<grid, RX_THREADS, RX_SMEM, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
-                                                       out, maps, (int)n_items);
+                                                       out, maps, (int)n_items, rp_env_int("RP_RX_ABLATE", 0));
   const cudaError_t launch_err = cudaGetLastError();
   release();
   if (launch_err != cudaSuccess) return (int)launch_err;

@@ -166,11 +166,12 @@ def test_full_size_properties():
     assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), abs(rhs), 1.0) * 10
 
 
-@pytest.mark.parametrize("impl", ["3", "4", "5"])
+@pytest.mark.parametrize("impl", ["3", "4", "5", "6"])
 @pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
 def test_forward_kernel_variants(impl, P, sr, monkeypatch):
     """The forward kernels (RP_ROI_IMPL=3: column walk; =4: banded, v3 body as its fallback; =5:
-    merged taps, reference-order fallback; adaptive sampling always takes the column walk)
+    merged taps, reference-order fallback; =6: tensor-core kernel for whole 8-channel groups and a fixed
+    sampling grid, the SIMT kernel otherwise; adaptive sampling always takes the column walk)
     against the oracle, on aligned (W % 4 == 0), 8-byte (W = 42) and odd-width maps."""
     monkeypatch.setenv("RP_ROI_IMPL", impl)
     rp.reload_env()
@@ -186,7 +187,7 @@ def test_forward_kernel_variants(impl, P, sr, monkeypatch):
         _close(out, exp)
 
 
-@pytest.mark.parametrize("impl", ["4", "5"])
+@pytest.mark.parametrize("impl", ["4", "5", "6"])
 def test_banded_pooler_multi_level(impl, monkeypatch):
     monkeypatch.setenv("RP_ROI_IMPL", impl)
     rp.reload_env()
