@@ -33,6 +33,39 @@ int rp_env_int(const char* name, int dflt) {
   return v == INT32_MIN ? dflt : v;
 }
 
+namespace {
+struct RpSmemEntry {
+  const void* kernel;
+  int device, bytes;
+};
+std::mutex smem_mu;
+RpSmemEntry smem_set[128];
+int n_smem = 0;
+}  // namespace
+
+int rp_smem_ensure(const void* kernel, int bytes) {
+  if (bytes <= 0) return 0;  // (static + dynamic may exceed the 48 KB default even when dynamic alone does not)
+  int dev = 0;
+  (void)cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(smem_mu);
+  RpSmemEntry* e = nullptr;
+  for (int i = 0; i < n_smem; ++i)
+    if (smem_set[i].kernel == kernel && smem_set[i].device == dev) e = &smem_set[i];
+  if (e && e->bytes >= bytes) return 0;
+  const cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (rc != cudaSuccess) {
+    (void)cudaGetLastError();
+    return (int)rc;
+  }
+  if (!e && n_smem < 128) {
+    e = &smem_set[n_smem++];
+    e->kernel = kernel;
+    e->device = dev;
+  }
+  if (e) e->bytes = bytes;
+  return 0;
+}
+
 extern "C" {
 
 int rp_version(void) { return RP_ABI_VERSION; }

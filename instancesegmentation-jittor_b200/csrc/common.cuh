@@ -30,19 +30,14 @@
 // (C ABI; tests and tuning tools) drops the table.  A knob that is not set costs one table lookup.
 int rp_env_int(const char* name, int dflt);
 
-// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) only when this call site needs more than it has
-// already set on the current device (once per kernel in the steady state, not once per launch).
-#define RP_SET_MAX_SMEM(kernel, bytes)                                                              \
-  do {                                                                                              \
-    static int rp_smem_set__[16] = {0};                                                             \
-    int rp_dev__ = 0;                                                                               \
-    (void)cudaGetDevice(&rp_dev__);                                                                 \
-    rp_dev__ &= 15;                                                                                 \
-    if ((int)(bytes) > rp_smem_set__[rp_dev__]) {                                                   \
-      RP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
-                                       (int)(bytes)));                                              \
-      rp_smem_set__[rp_dev__] = (int)(bytes);                                                       \
-    }                                                                                               \
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) only when the kernel needs more than has already been
+// set for it on the current device (once per kernel in the steady state, not once per launch).  Keyed by
+// the kernel's address (capi.cu), not by call site: several call sites may launch the same kernel.
+int rp_smem_ensure(const void* kernel, int bytes);  // 0 or a cudaError_t
+#define RP_SET_MAX_SMEM(kernel, bytes)                                                 \
+  do {                                                                                 \
+    const int rp_rc__ = rp_smem_ensure(reinterpret_cast<const void*>(kernel), (int)(bytes)); \
+    if (rp_rc__) return rp_rc__;                                                        \
   } while (0)
 
 static inline size_t rp_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

@@ -76,14 +76,17 @@ lincomb_loss_kernel(const float* __restrict__ proto, const float* __restrict__ c
   }
   __syncthreads();
 
-  if (tid < npix) {
-    const int pix = p0 + tid;
+  {
+    // every thread runs the loop (the warp reduction below needs whole warps); threads past the last
+    // pixel of the map work on a clamped pixel and contribute nothing
+    const bool active = tid < npix;
+    const int pix = active ? p0 + tid : p0;
     const int y = pix / W, x = pix - y * W;
     const float fx = (float)x, fy = (float)y;
     float pr[D], dp[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) {
-      pr[k] = proto_s[tid * (D + 1) + k];
+      pr[k] = proto_s[(active ? tid : 0) * (D + 1) + k];
       dp[k] = 0.f;
     }
     const float* mt = mask_t + (size_t)pix * n;
@@ -99,20 +102,26 @@ lincomb_loss_kernel(const float* __restrict__ proto, const float* __restrict__ c
       const float q = 1.0f - p;
       const float bce = -(t * logf(fmaxf(p, 1e-20f)) + (1.0f - t) * logf(fmaxf(q, 1e-20f)));
       const float s = scale_s[i];
-      atomicAdd(&lsum_s[i], s * bce);
+      {  // one shared atomic per warp, not per thread (all lanes hit the same word)
+        float part = active ? s * bce : 0.f;
+#pragma unroll
+        for (int d_ = 16; d_; d_ >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d_);
+        if ((tid & 31) == 0) atomicAdd(&lsum_s[i], part);
+      }
       float g = 0.f;
-      if (inside) {
+      if (inside && active) {
         const float gpos = p > 1e-20f ? -t * q : 0.f;           // d/dz of -t log p
         const float gneg = q > 1e-20f ? (1.0f - t) * p : 0.f;   // d/dz of -(1-t) log(1-p)
         g = s * (gpos + gneg);
       }
-      g_s[tid * gp + i] = g;
+      if (active) g_s[tid * gp + i] = g;
 #pragma unroll
       for (int k = 0; k < D; ++k) dp[k] = fmaf(g, c[k], dp[k]);
     }
     float* dpo = d_proto + (size_t)pix * D;
 #pragma unroll
-    for (int k = 0; k < D; ++k) proto_s[tid * (D + 1) + k] = dp[k];  // staged for a coalesced write
+    for (int k = 0; k < D; ++k)
+      if (active) proto_s[tid * (D + 1) + k] = dp[k];  // staged for a coalesced write
     (void)dpo;
   }
   __syncthreads();

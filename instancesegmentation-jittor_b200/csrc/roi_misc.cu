@@ -173,14 +173,19 @@ affine_paste_kernel(const float* __restrict__ pred, const double* __restrict__ M
     const size_t p0 = g * 4;
     const int nv = plane - p0 < 4 ? (int)(plane - p0) : 4;
     int y = (int)(p0 / width), x = (int)(p0 - (size_t)y * width);
+    // rp_warp_affine_coord with its per-row terms (X0, Y0) hoisted: they change only when the row does
+    int X0 = rp_cv_round((m[1] * (double)y + m[2]) * 1024.0) + 16;
+    int Y0 = rp_cv_round((m[4] * (double)y + m[5]) * 1024.0) + 16;
     for (int j = 0; j < nv; ++j) {
-      int sx, sy, fx, fy;
-      rp_warp_affine_coord(m, x, y, &sx, &sy, &fx, &fy);
-      const float v = rp_warp_affine_sample(src, h, w, C, c, sx, sy, fx, fy);
+      const int X = (X0 + rp_cv_round(m[0] * (double)x * 1024.0)) >> 5;
+      const int Y = (Y0 + rp_cv_round(m[3] * (double)x * 1024.0)) >> 5;
+      const float v = rp_warp_affine_sample(src, h, w, C, c, rp_sat_short(X >> 5), rp_sat_short(Y >> 5), X & 31, Y & 31);
       packed |= (v > 0.5f ? 1u : 0u) << (8 * j);
       if (++x == width) {
         x = 0;
         ++y;
+        X0 = rp_cv_round((m[1] * (double)y + m[2]) * 1024.0) + 16;
+        Y0 = rp_cv_round((m[4] * (double)y + m[5]) * 1024.0) + 16;
       }
     }
     if (aligned && nv == 4) {
@@ -248,10 +253,12 @@ resize_threshold_kernel(const float* __restrict__ masks, int h, int w, int H, in
   const float sy = (float)h / (float)H, sx = (float)w / (float)W;
   const size_t plane = (size_t)crop_h * crop_w;
   uint8_t* dst = out + (size_t)n * plane;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(dst) & 3) == 0);
   for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g * 4 < plane; g += (size_t)gridDim.x * blockDim.x) {
     const size_t p0 = g * 4;
     const int nv = plane - p0 < 4 ? (int)(plane - p0) : 4;
     int Y = (int)(p0 / crop_w), X = (int)(p0 - (size_t)Y * crop_w);
+    uint32_t packed = 0;
     for (int j = 0; j < nv; ++j) {
       const float fy = rp_resize_src(Y, sy), fx = rp_resize_src(X, sx);
       int y0 = (int)fy, x0 = (int)fx;
@@ -261,11 +268,16 @@ resize_threshold_kernel(const float* __restrict__ masks, int h, int w, int H, in
       const float h1 = fy - (float)y0, h0 = 1.0f - h1, w1 = fx - (float)x0, w0 = 1.0f - w1;
       const float top = w0 * img[y0 * w + x0] + w1 * img[y0 * w + x1];
       const float bot = w0 * img[y1 * w + x0] + w1 * img[y1 * w + x1];
-      dst[p0 + j] = (h0 * top + h1 * bot) > thresh ? 1 : 0;
+      packed |= ((h0 * top + h1 * bot) > thresh ? 1u : 0u) << (8 * j);
       if (++X == crop_w) {
         X = 0;
         ++Y;
       }
+    }
+    if (aligned && nv == 4) {
+      __stcs(reinterpret_cast<uint32_t*>(dst + p0), packed);
+    } else {
+      for (int j = 0; j < nv; ++j) dst[p0 + j] = (uint8_t)(packed >> (8 * j));
     }
   }
 }
