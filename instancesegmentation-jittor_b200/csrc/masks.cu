@@ -70,6 +70,7 @@ __device__ __forceinline__ void mk_store4(uint8_t* p, uint32_t packed, int n_val
 // Yolact mask assembly
 // --------------------------------------------------------------------------------------
 constexpr int MA_THREADS = 256;
+constexpr int MA_LIST = 128;  // detections per tile kept in the shared list (more: the plain loop)
 constexpr int MA_TW = 128;  // output tile width  (32 threads x 4 pixels)
 constexpr int MA_TH = 32;   // output tile height (8 thread rows x 4 rows)
 #ifndef MA_MINB
@@ -99,19 +100,35 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
   const MkTap ty0 = mk_tap(Y0, sy, ph), ty1 = mk_tap(Y1, sy, ph);
   const MkTap tx0 = mk_tap(X0, sx, pw), tx1 = mk_tap(X1, sx, pw);
   const int fy0 = ty0.i0, fy1 = ty1.i1, fx0 = tx0.i0, fx1 = tx1.i1;
+  // detections whose crop box reaches this tile (round 2: 30 % of the kernel's instructions were every
+  // thread re-deriving every detection's crop box): listed once per CTA with their sanitized boxes
+  __shared__ int s_list[MA_LIST];
+  __shared__ float4 s_box[MA_LIST];
+  __shared__ int s_nlist;
+  bool use_list = false;
   if (prefilled && crop) {
     // the output was zero-filled by the caller: a tile no detection's crop box reaches has
     // nothing to write and does not even stage the prototypes
-    int any = 0;
+    if (tid == 0) s_nlist = 0;
+    __syncthreads();
     for (int j = j0 + tid; j < j1; j += MA_THREADS) {
       const float* bxj = boxes + (size_t)j * 4;
       float cx1, cx2, cy1, cy2;
       mk_sanitize(bxj[0], bxj[2], pw, 1, &cx1, &cx2);
       mk_sanitize(bxj[1], bxj[3], ph, 1, &cy1, &cy2);
-      any |= !(!((float)fx1 >= cx1) || !((float)fx0 < cx2) || !((float)fy1 >= cy1) || !((float)fy0 < cy2));
+      if (!(!((float)fx1 >= cx1) || !((float)fx0 < cx2) || !((float)fy1 >= cy1) || !((float)fy0 < cy2))) {
+        const int pos = atomicAdd(&s_nlist, 1);
+        if (pos < MA_LIST) {
+          s_list[pos] = j;
+          s_box[pos] = make_float4(cx1, cx2, cy1, cy2);
+        }
+      }
     }
-    if (!__syncthreads_or(any)) return;
+    __syncthreads();
+    if (s_nlist == 0) return;
+    use_list = s_nlist <= MA_LIST;
   }
+  const int n_iter = use_list ? s_nlist : j1 - j0;
   const int frows = fy1 - fy0 + 1, fcols = fx1 - fx0 + 1;
   const int npix = frows * fcols;
   const int pixp = (fp_rows_max * fp_cols_max) | 1;  // odd pitch: conflict-free k-major staging
@@ -137,15 +154,28 @@ mask_assemble_kernel(const float* __restrict__ proto, const float* __restrict__ 
   }
   __syncthreads();
 
-  for (int j = j0; j < j1; ++j) {
-    const float* bxj = boxes + (size_t)j * 4;
+  for (int it = 0; it < n_iter; ++it) {
+    int j;
     float cx1, cx2, cy1, cy2;
-    mk_sanitize(bxj[0], bxj[2], pw, 1, &cx1, &cx2);
-    mk_sanitize(bxj[1], bxj[3], ph, 1, &cy1, &cy2);
+    bool empty;
+    if (use_list) {
+      j = s_list[it];
+      const float4 bx4 = s_box[it];
+      cx1 = bx4.x;
+      cx2 = bx4.y;
+      cy1 = bx4.z;
+      cy2 = bx4.w;
+      empty = false;
+    } else {
+      j = j0 + it;
+      const float* bxj = boxes + (size_t)j * 4;
+      mk_sanitize(bxj[0], bxj[2], pw, 1, &cx1, &cx2);
+      mk_sanitize(bxj[1], bxj[3], ph, 1, &cy1, &cy2);
+      // no prototype pixel of the footprint inside the crop box => the whole tile is zero
+      empty = crop && (!((float)fx1 >= cx1) || !((float)fx0 < cx2) || !((float)fy1 >= cy1) ||
+                       !((float)fy0 < cy2));
+    }
     uint8_t* out_j = out_masks + (size_t)j * out_h * out_w;
-    // no prototype pixel of the footprint inside the crop box => the whole tile is zero
-    const bool empty = crop && (!((float)fx1 >= cx1) || !((float)fx0 < cx2) ||
-                                !((float)fy1 >= cy1) || !((float)fy0 < cy2));
     if (!empty) {
       if (tid < D) coef_s[tid] = coeff[(size_t)j * D + tid];
       __syncthreads();
