@@ -406,7 +406,7 @@ def run_gpu_arm(args):
     err = np.abs(g_np - cpu_out)
     tol = 1e-5 * np.abs(cpu_out) + 1e-5
     parity = {"against": kind, "n": int(err.size), "max_abs": float(err.max()),
-              "max_rel": float((err / np.maximum(np.abs(cpu_out), 1e-3)).max()),
+              "max_rel_where_abs_ref_ge_0.1": float((err / np.abs(cpu_out))[np.abs(cpu_out) >= 0.1].max()),
               "violations": int((err > tol).sum()), "tol": "1e-5*|ref| + 1e-5",
               "levels_equal": bool(np.array_equal(mapper.map_rois(g_rois).cpu().numpy(), cl))}
     del g_feats, g_out

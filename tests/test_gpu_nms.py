@@ -144,3 +144,41 @@ def test_n_total_and_n_max_may_be_upper_bounds():
         ref = oracle.nms(bs[i], ss[i], 0.5)
         assert n_keep[i] == len(ref)
         np.testing.assert_array_equal(keep[offs[i]: offs[i] + n_keep[i]], ref)
+
+
+def test_iou_comparator_on_exact_threshold_pairs():
+    """Exhaustive family of INTEGER-coordinate box pairs (legacy +1 areas): box A = 10 x 10 at the origin
+    against every box B inside [0, 12]^2 -- 8281 two-box problems whose IoU values are small exact
+    rationals, many of them EXACTLY 0.3, 0.5, 0.25, 1/3 or within one ulp of a threshold.  The
+    reference compares (double)iou_f32 > thr (det/layers/nms.py:23,34): float32(30/100) > 0.3 holds,
+    0.5 > 0.5 does not.  The kernel's comparator (fminf/fmaxf, division-free pre-filter, t_cmp =
+    float_le(thr)) must agree with the oracle's compare-and-select on every one of them."""
+    bs = []
+    for x1 in range(13):
+        for x2 in range(x1, 13):
+            for y1 in range(13):
+                for y2 in range(y1, 13):
+                    bs.append((x1, y1, x2, y2))
+    B = len(bs)
+    boxes = np.zeros((B, 2, 4), np.float32)
+    boxes[:, 0] = (0, 0, 9, 9)
+    boxes[:, 1] = np.asarray(bs, np.float32)
+    scores = np.tile(np.array([0.9, 0.5], np.float32), (B, 1))
+    offs = (np.arange(B + 1) * 2).astype(np.int32)
+    flat_b, flat_s = boxes.reshape(-1, 4), scores.reshape(-1)
+    # the family does contain exact-threshold pairs
+    inter = (np.minimum(9, boxes[:, 1, 2]) - boxes[:, 1, 0] + 1).clip(0) * (np.minimum(9, boxes[:, 1, 3]) - boxes[:, 1, 1] + 1).clip(0)
+    area_b = (boxes[:, 1, 2] - boxes[:, 1, 0] + 1) * (boxes[:, 1, 3] - boxes[:, 1, 1] + 1)
+    iou = inter / (100 + area_b - inter)
+    for thr in (0.3, 0.5, 0.25):
+        assert (np.abs(iou - thr) < 1e-7).sum() >= 3
+    for thr in (0.3, 0.5, 0.7, 0.25, 1 / 3, 0.1, 0.9):
+        keep, nk = rp.nms_batched(T(flat_b), T(flat_s), T(offs), thr, n_max=2)
+        nk = nk.cpu().numpy()
+        exp = np.array([len(oracle.nms(boxes[i], scores[i], thr)) for i in range(B)])
+        bad = np.nonzero(nk != exp)[0]
+        assert bad.size == 0, "thr %r: %d pairs disagree, first B=%s iou=%r" % (thr, bad.size, bs[bad[0]], iou[bad[0]])
+        # the cython variant's comparator: iou >= float(thr)
+        keep, nk = rp.nms_batched(T(flat_b), T(flat_s), T(offs), thr, n_max=2, flags=1)  # RP_NMS_GE
+        exp_ge = np.array([len(oracle.cython_nms(np.concatenate([boxes[i], scores[i][:, None]], 1), thr)) for i in range(B)])
+        assert np.array_equal(nk.cpu().numpy(), exp_ge)
