@@ -16,20 +16,23 @@
 // 512-byte swizzle atom (conflict-free), and the epilogue's packed [c][ph][pw] stores are conflict-free too.
 //
 // One persistent CTA per SM, 32 warps with fixed roles, connected by mbarriers:
-//   warp 0      TMA producer: per sub-chunk (<= 8 channels x R rows x 16 columns) a few
-//               cp.async.bulk.tensor boxes; the tensor maps are (x, plane, y) so that a box lands
-//               [row][channel][x]: the 16-byte strips of one row of all channels are one contiguous,
-//               conflict-free 512-byte run for the y-pass
-//   warp 1      MMA issuer (one lane): per V tile 3 MMAs per 8 columns; tcgen05.commit frees the V slot
-//               and, after the last quarter, publishes the accumulator
+//   warps 0-1   TMA producers (sub-chunk q belongs to producer q % 2): per sub-chunk (<= 8 channels x R
+//               rows x 16 columns) a few cp.async.bulk.tensor boxes; the tensor maps are (x, plane, y) so
+//               that a box lands [row][channel][x]: the 16-byte strips of one row of all channels are one
+//               contiguous, conflict-free 512-byte run for the y-pass.  Warp 1 also owns the TMEM allocation
 //   warps 2-3   planners (even / odd work items): the y band plan (4 merged weights per bin, rotated to
 //               the register ring, per row segment) and the dense x-weight matrices Ax' (hi / lo per
 //               quarter, K-major SWIZZLE_64B, 1/(gh*gw) folded in)
-//   warps 4-7   epilogue: tcgen05.ld (one accumulator row = 16 pw per lane) -> packed [c][ph][pw] rows in
-//               shared memory -> one cp.async.bulk store of 8 channels x PH x PW floats (contiguous in out)
+//   warps 4-7   epilogue: tcgen05.ld (one accumulator row = 16 pw per lane), tcgen05.st of zeros (the next
+//               user of the accumulator always accumulates, so K quarters may arrive in any order) ->
+//               packed [c][ph][pw] rows in shared memory -> one cp.async.bulk store of 8 channels x PH x PW
+//               floats (contiguous in out)
 //   warp 8      V-slot release: turns MMA completions into a sequence number the y-pass warps can test
 //   warps 9-31  y-pass: unit = (sub-chunk, row segment) = one warp pass of <= 32 strips; ring of 4 rows;
-//               every finished bin is split into tf32 hi / lo and stored into the A operand
+//               every finished bin is split into tf32 hi / lo and stored into the A operand.  The warp
+//               whose unit completes a V tile (shared atomic count of the units written) issues that
+//               tile's MMAs (one lane; 3 per 8 columns), tcgen05.commit frees the V slot and arrives on the
+//               accumulator barrier -- there is no dedicated MMA warp
 // The input tile never passes through the LSU on its way in (TMA), the x-pass and the V read-back are
 // gone from the LSU / FMA pipes, and the output leaves through the bulk-copy engine.
 // RoIs without a band form, wider than 64 columns or taller than the tile slot are evaluated in the
@@ -47,9 +50,9 @@ namespace {
 constexpr int RX_THREADS = 1024;
 constexpr int RX_W_TMA = 0, RX_W_MMA = 1, RX_W_PLAN = 2, RX_W_EPI0 = 4, RX_W_FREE = 8, RX_W_Y0 = 9;
 constexpr int RX_NY = 23;              // y-pass warps
-constexpr int RX_S = 7;                // tile slots
+constexpr int RX_S = 6;                // tile slots
 constexpr int RX_SLOT = 14336;         // bytes per tile slot: 8 channels x 28 rows x 16 columns
-constexpr int RX_SV = 5;               // V slots
+constexpr int RX_SV = 6;               // V slots
 constexpr int RX_VBYTES = 16384;       // V tile: hi plane (128 rows x 64 B) + lo plane
 constexpr int RX_SD = 4;               // accumulator tiles in TMEM (16 columns each)
 constexpr int RX_NP = 2;               // plans in flight (one per planner warp)
@@ -57,7 +60,9 @@ constexpr int RX_CS = 128;             // channels per work item (RoI x channel 
 constexpr int RX_RMAX = 64;            // tile rows
 constexpr int RX_OSTAGE = 8 * 16 * 16 * 4;  // out stage: 8 channels x <= 16x16 floats (one buffer)
 constexpr int RX_NMAP = 18;            // tensor maps per level: 2 widths x 3 row counts x 3 channel counts
-constexpr int RX_PLAN_ARRIVALS = 1 + RX_NY + 1 + 4 + 1;  // TMA, y-pass warps, MMA, epilogue warps, V release
+constexpr int RX_NPROD = 2;             // TMA producer warps (warps 0, 1): sub-chunk q belongs to producer q % 2
+constexpr int RX_PLAN_ARRIVALS = RX_NPROD + RX_NY + 4 + 1;  // TMA warps, y-pass warps, epilogue warps, V release
+static_assert(RX_S % RX_NPROD == 0, "each producer owns whole tile slots");
 
 struct RxMeta {
   int kind;  // 0 tensor-core path, 1 reference-order fallback, 2 zero fill
@@ -67,9 +72,9 @@ struct RxMeta {
   const float* featb;  // &feat[level][(b*C + c_begin) * H*W]
   RtGeom g;
   // the bins of a RoI are cut into nseg row segments, each walked by its own warp
-  int nseg, seg_b0[3], seg_r0[2], seg_rows[2];
+  int nseg, lseg, seg_b0[5], seg_r0[4], seg_rows[4];
   RbF4 wrot[16];
-  uint32_t mw[2][RX_RMAX / 4 + 2];
+  uint32_t mw[4][RX_RMAX / 4 + 2];
 };
 
 constexpr int RX_MAXL = 5;  // levels with tensor maps (kernel parameter space: 11.5 KB)
@@ -85,7 +90,8 @@ struct RxBars {
   // software sequence numbers for the hand-offs that several warps wait on out of order (an mbarrier
   // parity cannot tell phase k from phase k + 2): sub-chunks issued by the TMA warp, V tiles whose
   // MMAs have completed
-  uint32_t issued, v_freed;
+  uint32_t issued[2], v_freed, d_freed;
+  uint32_t vcount[RX_SV];  // channel-segments written into each V slot (32 = complete)
 };
 
 // shared-memory layout (offsets from a 1024-byte aligned base)
@@ -273,11 +279,16 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
     const int nkq = (Kp + 15) >> 4;
     // y: segments, weights rotated to the ring of the bin's segment (slot = segment row & 3), bins
     // completed per segment row
-    const int nseg = PH >= 4 ? 2 : 1;
-    const int b_mid = nseg == 2 ? PH / 2 : PH;
-    const int r0_1 = nseg == 2 ? ay->start[b_mid] : 0;
+    const int nseg = PH >= 8 ? 4 : (PH >= 4 ? 2 : 1);
+    // segment sg covers bins [sg*PH/nseg, (sg+1)*PH/nseg) and the tile rows its bands touch
+    auto seg_of = [&](int bin) {
+      int sg = 0;
+      while (sg + 1 < nseg && bin >= ((sg + 1) * PH) / nseg) ++sg;
+      return sg;
+    };
     if (lane < PH) {
-      const int r0 = lane >= b_mid ? r0_1 : 0;
+      const int sg = seg_of(lane);
+      const int r0 = ay->start[(sg * PH) / nseg];
       const int rot = (ay->start[lane] - r0) & 3;
       const RbF4 w = ay->w[lane];
       RbF4 r;
@@ -289,7 +300,7 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
     }
     if (lane < RX_RMAX / 4 + 2) {
       for (int sg = 0; sg < nseg; ++sg) {
-        const int bb0 = sg ? b_mid : 0, bb1 = sg ? PH : b_mid, r0 = sg ? r0_1 : 0;
+        const int bb0 = (sg * PH) / nseg, bb1 = ((sg + 1) * PH) / nseg, r0 = ay->start[bb0];
         uint32_t word = 0;
         for (int bn = bb0; bn < bb1; ++bn) {
           const int r = ay->start[bn] - r0 + 3;
@@ -300,13 +311,14 @@ __device__ __forceinline__ void rx_build_plan(RxMeta* m, unsigned char* bmat, Rb
     }
     if (lane == 0) {
       m->nseg = nseg;
-      m->seg_b0[0] = 0;
-      m->seg_b0[1] = b_mid;
-      m->seg_b0[2] = PH;
-      m->seg_r0[0] = 0;
-      m->seg_r0[1] = r0_1;
-      m->seg_rows[0] = ay->start[b_mid - 1] + 4;
-      m->seg_rows[1] = nseg == 2 ? ay->start[PH - 1] + 4 - r0_1 : 0;
+      m->lseg = nseg == 4 ? 2 : (nseg == 2 ? 1 : 0);
+      for (int sg = 0; sg < nseg; ++sg) {
+        const int bb0 = (sg * PH) / nseg, bb1 = ((sg + 1) * PH) / nseg;
+        m->seg_b0[sg] = bb0;
+        m->seg_r0[sg] = ay->start[bb0];
+        m->seg_rows[sg] = ay->start[bb1 - 1] + 4 - ay->start[bb0];
+      }
+      m->seg_b0[nseg] = PH;
     }
     // x: dense weights per quarter [16 pw rows][16 columns], hi plane at +0 and lo plane at +1024 of
     // the quarter's 2 KB; accumulated in full precision in the hi planes, then split
@@ -434,18 +446,20 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
     for (int i = 0; i < RX_S; ++i) {
       rp_mbar_init(&bars->tile_full[i], 1);
-      rp_mbar_init(&bars->tile_empty[i], 2);
+      rp_mbar_init(&bars->tile_empty[i], 4);
     }
     for (int i = 0; i < RX_SV; ++i) {
-      rp_mbar_init(&bars->v_full[i], 16);
+      rp_mbar_init(&bars->v_full[i], 1);  // unused since the last y-pass warp of a tile issues its MMAs
       rp_mbar_init(&bars->v_empty[i], 1);
+      bars->vcount[i] = 0;
     }
     for (int i = 0; i < RX_SD; ++i) {
-      rp_mbar_init(&bars->d_full[i], 1);
+      rp_mbar_init(&bars->d_full[i], 4);  // one commit per K quarter (+ 4 - nkq plain arrivals)
       rp_mbar_init(&bars->d_empty[i], 4);
     }
-    bars->issued = 0;
+    bars->issued[0] = bars->issued[1] = 0;
     bars->v_freed = 0;
+    bars->d_freed = 0;
   }
   if (warp == RX_W_MMA) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(
@@ -491,8 +505,8 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 #endif
       if (lane == 0) rx_arrive(&bars->plan_full[ps]);
     }
-  } else if (warp == RX_W_TMA) {
-    // ===== TMA producer =====
+  } else if (warp < RX_NPROD) {
+    // ===== TMA producers: warp w issues the sub-chunks q == w (mod RX_NPROD) into the slots it owns =====
     uint32_t q = 0;
     RX_ITEM_LOOP {
       RX_META()
@@ -519,6 +533,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
             const CUtensorMap* tm = lmaps + (((nqh >> 1) - 1) * 3 + bri) * 3 + ci;
             const uint32_t row_bytes = (uint32_t)(cs * nqh * 16);
             for (int sc = 0; sc < nsc; ++sc, ++q) {
+              if ((int)(q % RX_NPROD) != warp) continue;
               const int ts = q % RX_S;
               rx_wait(&bars->tile_empty[ts], ((q / RX_S) & 1u) ^ 1u, 3, q);
               if (lane == 0) rp_mbar_arrive_expect_tx(&bars->tile_full[ts], (uint32_t)Re * row_bytes);
@@ -528,73 +543,12 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                                M->x0a + 16 * kq, M->plane0 + mt * 8 + sc * cs, M->y0 + brow,
                                &bars->tile_full[ts]);
               __syncwarp();
-              if (lane == 0) rx_publish(&bars->issued, q + 1);
+              if (lane == 0) rx_publish(&bars->issued[q % RX_NPROD], q / RX_NPROD + 1);
             }
           }
       }
       __syncwarp();
       if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
-    }
-  } else if (warp == RX_W_MMA) {
-    // ===== MMA issuer =====
-    uint32_t v = 0, d = 0;
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
-    RX_ITEM_LOOP {
-      RX_META()
-      if (M->kind == 0) {
-        const int nkq = M->nkq, nq = M->nq;
-        const uint32_t b_s = rp_smem_addr(smem + RX_OFF_B + ps * 8192);
-        for (int mt = 0; mt < M->nmt; ++mt, ++d) {
-          const int ds = d % RX_SD;
-          rx_wait(&bars->d_empty[ds], ((d / RX_SD) & 1u) ^ 1u, 4, d);
-          for (int kq = 0; kq < nkq; ++kq, ++v) {
-            const int vs = v % RX_SV;
-            rx_wait(&bars->v_full[vs], (v / RX_SV) & 1u, 5, v);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (lane == 0) {
-#ifdef RX_PROFILE
-              const long long mm_t0 = clock64();
-#endif
-              const int nks = min(4, nq - 4 * kq) >> 1;
-              const uint32_t a_s = rp_smem_addr(smem + RX_OFF_V + vs * RX_VBYTES);
-              const uint64_t dah = rx_desc_sw64(a_s), dal = rx_desc_sw64(a_s + 8192);
-              const uint64_t dbh = rx_desc_sw64(b_s + kq * 2048), dbl = rx_desc_sw64(b_s + kq * 2048 + 1024);
-              const uint32_t dtm = tmem + (uint32_t)(ds * 16);
-              uint32_t acc = kq ? 1u : 0u;
-              for (int ks = 0; ks < nks; ++ks) {
-                const uint64_t adv = (uint64_t)(ks * 2);
-#define RX_MMA(DA, DB)                                                                        \
-  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"                                   \
-               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(dtm),   \
-               "l"((DA) + adv), "l"((DB) + adv), "r"(idesc), "r"(acc)                        \
-               : "memory");                                                                  \
-  acc = 1u;
-                RX_MMA(dah, dbh)
-                if (!(ablate & 1)) {  // timing ablation (RP_RX_ABLATE bit 0): hi*hi only, wrong results
-                  RX_MMA(dal, dbh)
-                  RX_MMA(dah, dbl)
-                }
-#undef RX_MMA
-              }
-#ifdef RX_PROFILE
-              const long long mm_t1 = clock64();
-#endif
-              rx_commit(&bars->v_empty[vs]);
-              if (kq == nkq - 1) rx_commit(&bars->d_full[ds]);
-#ifdef RX_PROFILE
-              rx_prof_acc[10] += mm_t1 - mm_t0;
-              rx_prof_acc[9] += clock64() - mm_t1;
-              rx_prof_acc[11] += 1;
-#endif
-            }
-            __syncwarp();
-          }
-        }
-        if (lane == 0) rx_commit(&bars->plan_empty[ps]);  // arrives once the MMAs have read the B planes
-      } else {
-        if (lane == 0) rx_arrive(&bars->plan_empty[ps]);
-      }
-      __syncwarp();
     }
   } else if (warp == RX_W_FREE) {
     // ===== V-slot release: the only waiter of v_empty, in order; publishes the count of finished V tiles
@@ -617,6 +571,19 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     uint64_t evict_first;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(evict_first));
     uint32_t d = 0;
+    // accumulators start at zero and are zeroed again after every drain: the K quarters of a tile are
+    // issued by whichever y-pass warp finishes each quarter last, in any order, always accumulating
+    for (int i = 0; i < RX_SD; ++i) {
+      const uint32_t za = tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)(i * 16);
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(za),
+          "r"(0u)
+          : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (etid == 0) rx_publish(&bars->d_freed, (uint32_t)RX_SD);  // tiles 0 .. SD-1 may be issued
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
@@ -636,12 +603,17 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
               : "r"(taddr)
               : "memory");
           asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          asm volatile(
+              "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(
+                  taddr),
+              "r"(0u)
+              : "memory");
+          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          __syncwarp();
-          if (lane == 0) rx_arrive(&bars->d_empty[ds]);
           // the stage buffer was last read by the bulk store of the previous tile
           if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (etid == 0) rx_publish(&bars->d_freed, d + 1u + (uint32_t)RX_SD);  // slot ds is drained and zero
           unsigned char* stage = smem + RX_OFF_OST;
           const int row = quad * 32 + lane, ph = row >> 3, c = row & 7;  // V / accumulator rows are (ph, c)
           if (ph < PH) {
@@ -690,15 +662,17 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   } else if (warp >= RX_W_Y0) {
     // ===== y-pass =====
     const int yw = warp - RX_W_Y0;
-    uint32_t q0 = 0, v0 = 0, u0 = 0;  // sub-chunks, V tiles, work units (sub-chunk x segment) before this item
+    uint32_t q0 = 0, v0 = 0, u0 = 0, d0 = 0;  // sub-chunks, V tiles, work units, accumulator tiles before this item
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
     RX_ITEM_LOOP {
       RX_META()
       if (M->kind == 0) {
         // unit j of the item = ((tile * nsc + sc) * nseg + sg), tile = mt * nkq + kq; nsc and nseg are
         // powers of two: this warp's units (u0 + j == yw mod NY) are decoded, not walked
         const int cs = M->cs, nkq = M->nkq, nq = M->nq, nseg = M->nseg;
-        const int lseg = nseg >> 1, lsc = cs == 8 ? 0 : (cs == 4 ? 1 : 2);
+        const int lseg = M->lseg, lsc = cs == 8 ? 0 : (cs == 4 ? 1 : 2);
         const int ntiles = M->nmt * nkq;
+        const uint32_t b_s = rp_smem_addr(smem + RX_OFF_B + ps * 8192);
         const int nunits = ntiles << (lsc + lseg);
         for (int j = (int)((uint32_t)(yw + RX_NY) - u0 % RX_NY) % RX_NY; j < nunits; j += RX_NY) {
           const int sg = j & (nseg - 1);
@@ -708,7 +682,7 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
           const int vs = v % RX_SV, ts = q % RX_S;
           const int nqh = min(4, nq - 4 * kq);
           rx_wait_ge(&bars->v_freed, v + 1u - (uint32_t)RX_SV, 7, v);  // the MMAs of tile v - SV are done
-          rx_wait_ge(&bars->issued, q + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
+          rx_wait_ge(&bars->issued[q % RX_NPROD], q / RX_NPROD + 1u, 9, q);  // the slot's barrier is in the phase of sub-chunk q
           rx_wait(&bars->tile_full[ts], (q / RX_S) & 1u, 8, q);
 #ifdef RX_PROFILE
           const long long yp_t0 = clock64();
@@ -725,11 +699,55 @@ rx_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
             rx_prof_acc[11] += 1;
           }
 #endif
+          // hand the tile slot back; count this unit's channel-segments into the V slot (32 = the tile
+          // is complete): the warp that completes it issues the tile's MMAs itself
+          uint32_t done = 0;
           if (lane == 0) {
-            rx_arrive_n(&bars->tile_empty[ts], (uint32_t)(2 / nseg));
-            rx_arrive_n(&bars->v_full[vs], (uint32_t)(cs * 2 / nseg));
+            rx_arrive_n(&bars->tile_empty[ts], (uint32_t)(4 >> lseg));
+            const uint32_t add = (uint32_t)(cs * (4 >> lseg));
+            uint32_t old;
+            asm volatile("atom.add.acq_rel.cta.shared::cta.u32 %0, [%1], %2;"
+                         : "=r"(old)
+                         : "r"(rp_smem_addr(&bars->vcount[vs])), "r"(add)
+                         : "memory");
+            done = old + add;
+          }
+          done = __shfl_sync(0xffffffffu, done, 0);
+          if (done == 32u) {
+            const int mt = vi / nkq;
+            const uint32_t d = d0 + (uint32_t)mt;
+            const int ds = d % RX_SD;
+            rx_wait_ge(&bars->d_freed, d + 1u, 4, d);  // accumulator slot drained and zeroed
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (lane == 0) {
+              bars->vcount[vs] = 0;
+              const int nks = nqh >> 1;
+              const uint32_t a_s = rp_smem_addr(smem + RX_OFF_V + vs * RX_VBYTES);
+              const uint64_t dah = rx_desc_sw64(a_s), dal = rx_desc_sw64(a_s + 8192);
+              const uint64_t dbh = rx_desc_sw64(b_s + kq * 2048), dbl = rx_desc_sw64(b_s + kq * 2048 + 1024);
+              const uint32_t dtm = tmem + (uint32_t)(ds * 16);
+              for (int ks = 0; ks < nks; ++ks) {
+                const uint64_t adv = (uint64_t)(ks * 2);
+#define RX_MMA(DA, DB)                                                                        \
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"                                   \
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(dtm),   \
+               "l"((DA) + adv), "l"((DB) + adv), "r"(idesc), "r"(1u)                         \
+               : "memory");
+                RX_MMA(dah, dbh)
+                if (!(ablate & 1)) {  // timing ablation (RP_RX_ABLATE bit 0): hi*hi only, wrong results
+                  RX_MMA(dal, dbh)
+                  RX_MMA(dah, dbl)
+                }
+#undef RX_MMA
+              }
+              rx_commit(&bars->v_empty[vs]);
+              rx_commit(&bars->d_full[ds]);  // 4 arrivals complete the accumulator: one commit per quarter ...
+              if (kq == 0 && nkq < 4) rx_arrive_n(&bars->d_full[ds], (uint32_t)(4 - nkq));  // ... and the rest here
+            }
+            __syncwarp();
           }
         }
+        d0 += (uint32_t)M->nmt;
         u0 += (uint32_t)nunits;
         q0 += (uint32_t)(nunits >> lseg);
         v0 += (uint32_t)ntiles;

@@ -39,7 +39,7 @@ def dump_profile():
     a = np.frombuffer(buf, dtype=np.int32).copy()[256:256 + 32 * 12 * 2].view(np.int64).reshape(32, 12)
     if not a.any():
         return
-    roles = {0: "TMA", 1: "MMA", 2: "PLAN", 3: "PLAN", 4: "EPI", 5: "EPI", 6: "EPI", 7: "EPI", 8: "FREE"}
+    roles = {0: "TMA", 1: "TMA", 2: "PLAN", 3: "PLAN", 4: "EPI", 5: "EPI", 6: "EPI", 7: "EPI", 8: "FREE"}
     names = ["total", "plan_full", "plan_empty", "tile_empty", "d_empty", "v_full", "d_full", "v_freed",
              "tile_full", "issued", "work", "units"]
     print("  warp role  " + " ".join("%10s" % n for n in names))
