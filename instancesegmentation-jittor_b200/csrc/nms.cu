@@ -23,6 +23,8 @@
 //              ascending index for the cython variant), n_keep, truncation at max_keep.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -49,15 +51,20 @@ __device__ __forceinline__ int nms_find_segment(const int* __restrict__ offsets,
   return lo;
 }
 
+// zero8 / n_zero8: the scan state of this call (removed bits, counters), cleared here instead of by a
+// separate memset launch when it is small enough for the grid.
 __global__ void nms_keys_kernel(const float* __restrict__ scores, const int* __restrict__ offsets,
                                 int B, int n_total, int ties_high_first,
-                                uint64_t* __restrict__ keys, int* __restrict__ vals) {
+                                uint64_t* __restrict__ keys, int* __restrict__ vals,
+                                uint64_t* __restrict__ zero8, int n_zero8) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < n_zero8) zero8[p] = 0ull;
   if (p >= n_total) return;
   if (p >= offsets[B]) {
     // n_total may be an upper bound of offsets[B] (a device-side count the host never reads,
-    // e.g. the output of rp_rpn_pre_nms): the slack rows sort behind the last problem
-    keys[p] = ((uint64_t)(uint32_t)B << 32);
+    // e.g. the output of rp_rpn_pre_nms): the slack rows sort behind the last problem (and, with
+    // the low word all ones, behind every score when only the low 32 bits are sorted: B == 1)
+    keys[p] = ((uint64_t)(uint32_t)B << 32) | 0xffffffffull;
     vals[p] = p;
     return;
   }
@@ -97,8 +104,25 @@ __global__ void nms_gather_kernel(const float* __restrict__ boxes, const float* 
 // Only pairs (kept box, later alive box) and the diagonal blocks are ever evaluated -- with the
 // usual 70-95 % suppression that is a fraction of the n(n-1)/2 pairs of a full bit matrix, and
 // no n x n/64 matrix is materialised.
+// The diagonal block is stored "who can suppress me": row j, word w holds the HIGHER-ranked boxes
+// w*64 .. w*64+63 of the band that overlap box j (lower triangle; IoU is symmetric), word-major
+// (D[w][j]) so that both the tile writes and the per-box reads of the resolve step are coalesced.
 // ------------------------------------------------------------------------------------------
 constexpr int NMS_BAND_MAX = 1024;
+
+#ifdef NMS_PROFILE
+// cycle stamps of CTA 0, thread 0 in band 3 of the one-launch kernel (tools/run_nms_single.py)
+__device__ long long nms_prof[32];
+__device__ int nms_prof_on;
+#define NMS_STAMP(i)                                                        \
+  do {                                                                      \
+    if (nms_prof_on && blockIdx.x == 0 && threadIdx.x == 0) nms_prof[i] = clock64(); \
+  } while (0)
+#else
+#define NMS_STAMP(i) \
+  do {               \
+  } while (0)
+#endif
 
 // the reference's IoU test (det/layers/nms.py:28-34), exact: pairs with inter < t_lo * union
 // are rejected without a division, the rest take the IEEE division the oracle takes.
@@ -131,7 +155,7 @@ struct NmsBand {
   const int* offsets;
   const int* sorted_vals;
   uint64_t* removed;      // [B][wmax]
-  uint64_t* D;            // [B][BR][bw]  diagonal block of the current band (upper triangle)
+  uint64_t* D;            // [B][bw][BR]  diagonal block of the current band (lower triangle)
   NmsBox* kbox;           // [B][BR]      boxes the current band kept
   float* karea;
   float* klabel;
@@ -142,219 +166,654 @@ struct NmsBand {
   float t_cmp, t_lo;
 };
 
-// Diagonal block of `band`: CTA = 64 rows x 4 column tiles (as thread = (tile j, row r)).
+// One 64 x 64 tile (row block rb, column block cb <= rb) of the diagonal block of `band` per CTA;
+// thread = (row r, column sub-range q): 64 / (blockDim / 64) pair tests each, the sub-ranges of a row
+// are merged through a shared word.  bw (bw + 1) / 2 tiles per problem.
 template <bool GE, bool LABELS>
-__device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int band, int blk,
-                                              NmsBox* cbox, float* carea, float* clabel) {
+__device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int band, int tile,
+                                              NmsBox* cbox, float* carea, float* clabel,
+                                              unsigned long long* wordS) {
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
   const int base = band * p.BR;
   if (base >= n) return;
-  const int groups = (p.bw + 3) >> 2;
-  const int rb = blk / groups, cb0 = (blk - rb * groups) * 4;
-  if (rb >= p.bw || cb0 + 3 < rb) return;
+  int rb = 0;
+  while (tile >= rb + 1) {
+    tile -= rb + 1;
+    ++rb;
+  }
+  const int cb = tile;
+  if (rb >= p.bw || base + rb * 64 >= n) return;
   const int tid = threadIdx.x;
-  {
-    const int c = base + cb0 * 64 + tid;
-    if (cb0 * 64 + tid < p.BR && c < n) {
+  if (tid < 64) {
+    const int c = base + cb * 64 + tid;  // c < n: the column block is not after the row block
+    if (c < n) {
       cbox[tid] = p.sboxes[off + c];
       carea[tid] = p.sarea[off + c];
       if (LABELS) clabel[tid] = p.slabel[off + c];
     }
+    wordS[tid] = 0ull;
   }
   __syncthreads();
-  const int j = tid >> 6, r = tid & 63;
-  const int cb = cb0 + j;
+  const int nq = blockDim.x >> 6, cw = 64 / nq;
+  const int r = tid & 63, q = tid >> 6;
   const int rrow = rb * 64 + r;  // row inside the band
   const int row = base + rrow;
-  if (cb >= p.bw || cb < rb || row >= n) return;
-  const NmsBox a = p.sboxes[off + row];
-  const float aarea = p.sarea[off + row];
-  float alabel = 0.f;
-  if (LABELS) alabel = p.slabel[off + row];
-  int ncol = n - (base + cb * 64);
-  ncol = ncol > 64 ? 64 : ncol;
-  uint64_t up = 0;
-  const NmsBox* cbx = cbox + j * 64;
-  const float* car = carea + j * 64;
-  const float* clb = clabel + j * 64;
-  for (int c = (cb == rb) ? r + 1 : 0; c < ncol; ++c) {  // strict upper triangle
-    bool sup = nms_pair<GE>(a, aarea, cbx[c], car[c], p.t_cmp, p.t_lo);
-    if (LABELS) sup = sup && (alabel == clb[c]);
-    if (sup) up |= (1ull << c);
+  if (row < n) {
+    const NmsBox a = p.sboxes[off + row];
+    const float aarea = p.sarea[off + row];
+    float alabel = 0.f;
+    if (LABELS) alabel = p.slabel[off + row];
+    // columns of strictly higher rank only
+    const int cend = min((q + 1) * cw, (cb == rb) ? r : 64);
+    uint64_t bits = 0;
+    for (int c = q * cw; c < cend; ++c) {
+      bool sup = nms_pair<GE>(cbox[c], carea[c], a, aarea, p.t_cmp, p.t_lo);
+      if (LABELS) sup = sup && (alabel == clabel[c]);
+      if (sup) bits |= (1ull << c);
+    }
+    if (bits) atomicOr(&wordS[r], (unsigned long long)bits);
   }
-  p.D[((size_t)seg * p.BR + rrow) * p.bw + cb] = up;
+  __syncthreads();
+  if (tid < 64 && base + rb * 64 + tid < n)
+    p.D[((size_t)seg * p.bw + cb) * p.BR + rb * 64 + tid] = wordS[tid];
 }
 
 template <bool GE, bool LABELS>
 __global__ void __launch_bounds__(256)
 nms_diag_kernel(NmsBand p, int band) {
-  __shared__ NmsBox cbox[256];
-  __shared__ float carea[256];
-  __shared__ float clabel[256];
-  nms_diag_part<GE, LABELS>(p, blockIdx.y, band, blockIdx.x, cbox, carea, clabel);
+  __shared__ NmsBox cbox[64];
+  __shared__ float carea[64];
+  __shared__ float clabel[64];
+  __shared__ unsigned long long wordS[64];
+  nms_diag_part<GE, LABELS>(p, blockIdx.y, band, blockIdx.x, cbox, carea, clabel, wordS);
 }
 
-// Blocks [0, nsup): 64 later boxes each against the boxes band `band` kept.
-// Blocks [nsup, ...): diagonal block of band + 1.
+// Blocks [0, nsup): 64 later boxes each against the boxes band `band` kept, 16 threads per box (the
+// kept list of a full band is 1024 boxes: 64 tests per thread, early exit on the first hit).
+// Blocks [nsup, ...): the tiles of the diagonal block of band + 1.
+constexpr int NMS_SUP_PARTS = 16;
+constexpr int NMS_SUP_THREADS = 64 * NMS_SUP_PARTS;
+
+struct NmsSupSmem {
+  NmsBox kb[NMS_BAND_MAX];
+  float ka[NMS_BAND_MAX];
+  float kl[NMS_BAND_MAX];
+  unsigned long long s_new;
+  unsigned long long wordS[64];
+  unsigned long long s_new4[4];
+  unsigned bcast;
+};
+
+// Work item x of problem seg in the suppress step of `band` (the CTA returns together).
+// The still-alive boxes of the 64-box word are compacted and each gets P = 16, 32 or 64 threads
+// (as many as 1024 threads allow), which split the kept list between them.  `cached` names the
+// problem whose kept list is already in shared memory (-1: none; a CTA of the one-launch kernel
+// works through several words of the same problem).
 template <bool GE, bool LABELS>
-__global__ void __launch_bounds__(256)
-nms_suppress_kernel(NmsBand p, int band, int nsup) {
-  __shared__ NmsBox kb[NMS_BAND_MAX];
-  __shared__ float ka[NMS_BAND_MAX];
-  __shared__ float kl[LABELS ? NMS_BAND_MAX : 1];
-  __shared__ unsigned long long s_new;
-  const int seg = blockIdx.y;
+__device__ __forceinline__ void nms_suppress_body(const NmsBand& p, int seg, int band, int x, int nsup,
+                                                  NmsSupSmem& sm, int& cached) {
   const int tid = threadIdx.x;
-  if ((int)blockIdx.x >= nsup) {
-    nms_diag_part<GE, LABELS>(p, seg, band + 1, blockIdx.x - nsup, kb, ka, kl);
+  if (x >= nsup) {
+    nms_diag_part<GE, LABELS>(p, seg, band + 1, x - nsup, sm.kb, sm.ka, sm.kl, sm.wordS);
+    cached = -1;  // the tile used the kept-list buffers
     return;
   }
-  if (p.done[seg]) return;
+  const int wj = (band + 1) * p.bw + x;
+  const int done = p.done[seg];
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
-  const int wj = (band + 1) * p.bw + blockIdx.x;
-  if (wj * 64 >= n) return;
   const int kc = p.kcount[seg];
-  if (kc == 0) return;
-  for (int i = tid; i < kc; i += 256) {
-    kb[i] = p.kbox[(size_t)seg * p.BR + i];
-    ka[i] = p.karea[(size_t)seg * p.BR + i];
-    if (LABELS) kl[i] = p.klabel[(size_t)seg * p.BR + i];
-  }
-  if (tid == 0) s_new = 0ull;
-  __syncthreads();
-  const int jj = tid & 63, part = tid >> 6;
-  const int j = wj * 64 + jj;
   const uint64_t word = p.removed[(size_t)seg * p.wmax + wj];
-  if (j < n && !((word >> jj) & 1ull)) {
+  if (done || wj * 64 >= n || kc == 0) return;
+  const int nv = min(64, n - wj * 64);
+  const uint64_t alive = ~word & (nv == 64 ? ~0ull : ((1ull << nv) - 1ull));
+  const int na = __popcll(alive);
+  if (na == 0) return;
+  if (cached != seg) {
+    for (int i = tid; i < kc; i += NMS_SUP_THREADS) {
+      sm.kb[i] = p.kbox[(size_t)seg * p.BR + i];
+      sm.ka[i] = p.karea[(size_t)seg * p.BR + i];
+      if (LABELS) sm.kl[i] = p.klabel[(size_t)seg * p.BR + i];
+    }
+    cached = seg;
+  }
+  if (tid == 0) sm.s_new = 0ull;
+  __syncthreads();
+  const int lp = na <= 16 ? 6 : (na <= 32 ? 5 : 4);  // log2 of the threads per alive box
+  const int P = 1 << lp;
+  const int slot = tid >> lp, part = tid & (P - 1);
+  if (slot < na) {
+    const uint32_t lo = (uint32_t)alive, hi = (uint32_t)(alive >> 32);
+    const int cl = __popc(lo);
+    const int jj = slot < cl ? (int)__fns(lo, 0, slot + 1) : 32 + (int)__fns(hi, 0, slot - cl + 1);
+    const int j = wj * 64 + jj;
     const NmsBox q = p.sboxes[off + j];
     const float qarea = p.sarea[off + j];
     float qlabel = 0.f;
     if (LABELS) qlabel = p.slabel[off + j];
     bool hit = false;
-    for (int i = part; i < kc && !hit; i += 4) {
-      bool sup = nms_pair<GE>(kb[i], ka[i], q, qarea, p.t_cmp, p.t_lo);
-      if (LABELS) sup = sup && (kl[i] == qlabel);
+    for (int i = part; i < kc && !hit; i += P) {
+      bool sup = nms_pair<GE>(sm.kb[i], sm.ka[i], q, qarea, p.t_cmp, p.t_lo);
+      if (LABELS) sup = sup && (sm.kl[i] == qlabel);
       hit = sup;
     }
-    if (hit) atomicOr(&s_new, 1ull << jj);
+    if (hit) atomicOr(&sm.s_new, 1ull << jj);
   }
   __syncthreads();
-  if (tid == 0 && s_new) p.removed[(size_t)seg * p.wmax + wj] = word | s_new;
+  if (tid == 0 && sm.s_new) p.removed[(size_t)seg * p.wmax + wj] = word | sm.s_new;
 }
 
-// Greedy NMS inside band `band`, one CTA per problem.
-__global__ void __launch_bounds__(1024)
-nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __restrict__ keep,
-                   uint8_t* __restrict__ flags) {
-  extern __shared__ __align__(16) uint64_t nr_smem[];
-  uint64_t* Ds = nr_smem;               // [BR][bw]
-  uint64_t* rem = Ds + p.BR * p.bw;     // [bw]
-  uint64_t* keptm = rem + p.bw;         // [bw]
-  int* cbase = reinterpret_cast<int*>(keptm + p.bw);  // [bw + 1]
-  const int seg = blockIdx.x;
+// Up to 4 words of ONE problem in one pass (dataflow workers): the alive boxes of all words are
+// compacted together and share the 1024 threads, P = 1024 / alive threads per box (at most 64).
+// Does not look at done[seg] (the resolver may be writing it): the caller knows from R.
+template <bool GE, bool LABELS>
+__device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, const int (&wl)[4], int nw,
+                                                   NmsSupSmem& sm, int& cached) {
   const int tid = threadIdx.x;
-  if (tid == 0) p.kcount[seg] = 0;
-  if (p.done[seg]) return;
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
-  const int base = band * p.BR;
-  if (base >= n) return;
-  const int rows = min(p.BR, n - base);
-  const int chunks = (rows + 63) >> 6;
-  {
-    const uint64_t* Dg = p.D + (size_t)seg * p.BR * p.bw;
-    if ((p.bw & 1) == 0) {  // 16-byte copies (rows * bw is even, both bases 16-byte aligned)
-      const uint4* g4 = reinterpret_cast<const uint4*>(Dg);
-      uint4* s4 = reinterpret_cast<uint4*>(Ds);
-      const int n4 = (rows * p.bw) >> 1;
-#pragma unroll 8
-      for (int i = tid; i < n4; i += blockDim.x) s4[i] = g4[i];
-    } else {
-      for (int i = tid; i < rows * p.bw; i += blockDim.x) Ds[i] = Dg[i];
+  const int kc = p.kcount[seg];
+  uint64_t word[4], alive[4];
+  int pre[5];
+  pre[0] = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    word[k] = 0ull;
+    alive[k] = 0ull;
+    if (k < nw && wl[k] * 64 < n) {
+      word[k] = p.removed[(size_t)seg * p.wmax + wl[k]];
+      const int nv = min(64, n - wl[k] * 64);
+      alive[k] = ~word[k] & (nv == 64 ? ~0ull : ((1ull << nv) - 1ull));
     }
-    if (tid < p.bw) {
-      rem[tid] = p.removed[(size_t)seg * p.wmax + band * p.bw + tid];
-      keptm[tid] = 0ull;
+    pre[k + 1] = pre[k] + __popcll(alive[k]);
+  }
+  const int na = pre[4];
+  if (kc == 0 || na == 0) return;
+  if (cached != seg) {
+    for (int i = tid; i < kc; i += NMS_SUP_THREADS) {
+      sm.kb[i] = p.kbox[(size_t)seg * p.BR + i];
+      sm.ka[i] = p.karea[(size_t)seg * p.BR + i];
+      if (LABELS) sm.kl[i] = p.klabel[(size_t)seg * p.BR + i];
+    }
+    cached = seg;
+  }
+  if (tid < 4) sm.s_new4[tid] = 0ull;
+  __syncthreads();
+  int P = NMS_SUP_THREADS / na;
+  if (P > 64) P = 64;
+  const int slot = tid / P, part = tid - slot * P;
+  if (slot < na) {
+    int k = 0;
+#pragma unroll
+    for (int t = 1; t < 4; ++t)
+      if (slot >= pre[t]) k = t;
+    uint64_t a = alive[0];
+    int wk = wl[0], ls = slot;
+#pragma unroll
+    for (int t = 1; t < 4; ++t)
+      if (k == t) {
+        a = alive[t];
+        wk = wl[t];
+        ls = slot - pre[t];
+      }
+    const uint32_t lo = (uint32_t)a, hi = (uint32_t)(a >> 32);
+    const int cl = __popc(lo);
+    const int jj = ls < cl ? (int)__fns(lo, 0, ls + 1) : 32 + (int)__fns(hi, 0, ls - cl + 1);
+    const int j = wk * 64 + jj;
+    const NmsBox q = p.sboxes[off + j];
+    const float qarea = p.sarea[off + j];
+    float qlabel = 0.f;
+    if (LABELS) qlabel = p.slabel[off + j];
+    bool hit = false;
+    for (int i = part; i < kc && !hit; i += P) {
+      bool sup = nms_pair<GE>(sm.kb[i], sm.ka[i], q, qarea, p.t_cmp, p.t_lo);
+      if (LABELS) sup = sup && (sm.kl[i] == qlabel);
+      hit = sup;
+    }
+    if (hit) atomicOr(&sm.s_new4[k], 1ull << jj);
+  }
+  __syncthreads();
+  if (tid < nw && sm.s_new4[tid]) {
+    uint64_t wv = word[0];
+    int wk = wl[0];
+#pragma unroll
+    for (int t = 1; t < 4; ++t)
+      if (tid == t) {
+        wv = word[t];
+        wk = wl[t];
+      }
+    p.removed[(size_t)seg * p.wmax + wk] = wv | sm.s_new4[tid];
+  }
+}
+
+template <bool GE, bool LABELS>
+__global__ void __launch_bounds__(NMS_SUP_THREADS)
+nms_suppress_kernel(NmsBand p, int band, int nsup) {
+  __shared__ NmsSupSmem sm;
+  int cached = -1;
+  nms_suppress_body<GE, LABELS>(p, blockIdx.y, band, blockIdx.x, nsup, sm, cached);
+}
+
+// Greedy NMS inside band `band`, one CTA per problem, one THREAD per box, as a band-wide fixpoint.
+// Thread j holds row j of the diagonal block in registers (the higher-ranked boxes of the band that
+// overlap box j).  Two bit sets over the band live in shared memory: kept and undecided.  Per round
+//   box j is suppressed  once a KEPT higher-ranked box overlaps it,
+//   box j is kept        once no UNDECIDED higher-ranked box overlaps it (and no kept one does);
+// the highest-ranked undecided box is always decided, so the loop ends, and the number of rounds is
+// the longest alternating chain of overlaps in the band (a handful), not the number of kept boxes.
+// The greedy result is unique, so this is the reference's sequential loop (det/layers/nms.py:13-45).
+constexpr int NMS_RES_WORDS = NMS_BAND_MAX / 64;
+struct NmsResSmem {
+  __align__(8) uint32_t keptS[2][NMS_BAND_MAX / 32];
+  __align__(8) uint32_t undecS[2][NMS_BAND_MAX / 32];
+  int wsum[NMS_BAND_MAX / 32];
+};
+
+// blockDim >= BR, a multiple of 32 (threads past the band idle along)
+struct NmsNoWait {
+  __device__ __forceinline__ void operator()() const {}
+};
+
+// `wait` (called by the whole CTA) returns once the removed bits of this band are final; everything
+// before it -- the diagonal rows, the boxes' own records -- is fetched while the suppress step of the
+// previous band may still be running (one-launch dataflow kernel)
+template <class Wait>
+__device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int band, int max_keep,
+                                                 int ascending, int* __restrict__ keep,
+                                                 uint8_t* __restrict__ flags, NmsResSmem& sm,
+                                                 const Wait& wait) {
+  uint32_t (*keptS)[NMS_BAND_MAX / 32] = sm.keptS;
+  uint32_t (*undecS)[NMS_BAND_MAX / 32] = sm.undecS;
+  int* wsum = sm.wsum;
+  const int tid = threadIdx.x;
+  // independent loads first: one L2 round trip, not four
+  const int done = p.done[seg];
+  const int off = p.offsets[seg];
+  const int n = p.offsets[seg + 1] - off;
+  const int count0 = p.count[seg];
+  const int base = band * p.BR;
+  if (done || base >= n) {  // (the dataflow kernel never gets here: its resolver stops first)
+    if (tid == 0) p.kcount[seg] = 0;
+    return;
+  }
+  const int rows = min(p.BR, n - base);
+  const int lane = tid & 31, warp = tid >> 5;
+  const int cj = tid >> 6;  // the box's 64-rank chunk: only words 0..cj of its row can be set
+  const bool live = tid < rows;
+  uint64_t T[NMS_RES_WORDS];
+  {
+    const uint64_t* col = p.D + (size_t)seg * p.bw * p.BR + tid;
+#pragma unroll
+    for (int w = 0; w < NMS_RES_WORDS; ++w) T[w] = (live && w <= cj) ? col[(size_t)w * p.BR] : 0ull;
+  }
+  // the box's own record, for the outputs (fetched now, used after the fixpoint)
+  int my_e = 0;
+  NmsBox my_box{0.f, 0.f, 0.f, 0.f};
+  float my_area = 0.f, my_label = 0.f;
+  if (live) {
+    const int rank = off + base + tid;
+    my_e = p.sorted_vals[rank] - off;
+    my_box = p.sboxes[rank];
+    my_area = p.sarea[rank];
+    if (p.slabel) my_label = p.slabel[rank];
+  }
+  NMS_STAMP(10);
+  wait();
+  bool my_undec = false, my_kept = false;
+  if (live) {
+    const uint64_t rem = p.removed[(size_t)seg * p.wmax + band * p.bw + cj];
+    my_undec = !((rem >> (tid & 63)) & 1ull);
+  }
+  {
+    const unsigned ub = __ballot_sync(0xffffffffu, my_undec);
+    if (lane == 0) {
+      undecS[0][warp] = ub;
+      keptS[0][warp] = 0u;
     }
   }
   __syncthreads();
-  const int count0 = p.count[seg];
-  if (tid < 32) {
-    const int l = tid;
-    int count = count0;
-    for (int c = 0; c < chunks; ++c) {
-      const int nrow = min(64, rows - c * 64);
-      const uint64_t valid = (nrow == 64) ? ~0ull : ((1ull << nrow) - 1ull);
-      // Greedy rule as a warp-parallel fixpoint.  Lane l holds the diagonal-block rows of boxes
-      // l and l+32 (bits = the lower-scored boxes of the chunk each one overlaps).  A box is
-      // suppressed once a KEPT higher-scored box overlaps it, and kept once no undecided
-      // higher-scored box overlaps it; the lowest undecided box is always decided, and chains
-      // of overlapping boxes inside 64 ranks are short.
-      uint64_t undec = ~rem[c] & valid;
-      uint64_t kept = 0ull;
-      const uint64_t r0 = (l < nrow) ? Ds[(c * 64 + l) * p.bw + c] : 0ull;
-      const uint64_t r1 = (l + 32 < nrow) ? Ds[(c * 64 + 32 + l) * p.bw + c] : 0ull;
-      while (undec) {
-        const uint64_t ks = (((kept >> l) & 1ull) ? r0 : 0ull) | (((kept >> (l + 32)) & 1ull) ? r1 : 0ull);
-        const uint64_t us = (((undec >> l) & 1ull) ? r0 : 0ull) | (((undec >> (l + 32)) & 1ull) ? r1 : 0ull);
-        const uint64_t sup = nms_warp_or64(ks);  // overlapped by a kept box
-        const uint64_t pot = nms_warp_or64(us);  // overlapped by an undecided box
-        const uint64_t ns = undec & sup;
-        const uint64_t nk = undec & ~sup & ~pot;
-        kept |= nk;
-        undec &= ~(nk | ns);
-      }
-      bool stop = false;
-      if (max_keep > 0) {
-        const int allowed = max_keep - count;
-        while (__popcll(kept) > allowed) kept &= ~(1ull << (63 - __clzll((long long)kept)));
-        stop = (count + __popcll(kept) >= max_keep);
-      }
-      if (l == 0) {
-        keptm[c] = kept;
-        cbase[c] = count - count0;
-      }
-      count += __popcll(kept);
-      if (stop) break;
-      // removed bits of the later chunks of this band: OR of the kept rows, word by word
-      {
-        const bool k0 = (kept >> l) & 1ull, k1 = (kept >> (l + 32)) & 1ull;
-        const uint64_t* d0 = Ds + (c * 64 + l) * p.bw;
-        const uint64_t* d1 = Ds + (c * 64 + 32 + l) * p.bw;
-        for (int w = c + 1; w < chunks; ++w) {
-          const uint64_t v = (k0 ? d0[w] : 0ull) | (k1 ? d1[w] : 0ull);
-          const uint64_t o = nms_warp_or64(v);
-          if (l == 0) rem[w] |= o;
+  NMS_STAMP(11);
+  int cur = 0;
+  for (int round = 0;; ++round) {
+    const unsigned ub = undecS[cur][warp];
+    bool nk = false, ns = false;
+    if (ub) {
+      const uint64_t* k64 = reinterpret_cast<const uint64_t*>(keptS[cur]);
+      const uint64_t* u64 = reinterpret_cast<const uint64_t*>(undecS[cur]);
+      uint64_t supd = 0ull, potd = 0ull;
+      if (round == 0) {  // nothing is kept yet
+#pragma unroll
+        for (int w = 0; w < NMS_RES_WORDS; ++w)
+          if (w <= cj) potd |= T[w] & u64[w];
+      } else {
+#pragma unroll
+        for (int w = 0; w < NMS_RES_WORDS; ++w) {
+          if (w <= cj) {  // warp-uniform
+            supd |= T[w] & k64[w];
+            potd |= T[w] & u64[w];
+          }
         }
       }
-      __syncwarp();
+      if (my_undec) {
+        ns = supd != 0ull;
+        nk = !ns && potd == 0ull;
+      }
     }
-    if (l == 0) {
-      cbase[p.bw] = count - count0;
-      p.kcount[seg] = count - count0;
-      p.count[seg] = count;
-      if (max_keep > 0 && count >= max_keep) p.done[seg] = 1;
+    const unsigned bk = __ballot_sync(0xffffffffu, nk);
+    const unsigned bs = __ballot_sync(0xffffffffu, ns);
+    if (nk) my_kept = true;
+    if (nk || ns) my_undec = false;
+    const unsigned nub = ub & ~(bk | bs);
+    if (lane == 0) {
+      keptS[cur ^ 1][warp] = keptS[cur][warp] | bk;
+      undecS[cur ^ 1][warp] = nub;
+    }
+    cur ^= 1;
+    if (!__syncthreads_or(nub != 0u)) break;
+  }
+  NMS_STAMP(12);
+  // positions in rank order, the max_keep cap, outputs
+  const unsigned kb = keptS[cur][warp];
+  if (lane == 0) wsum[warp] = __popc(kb);
+  __syncthreads();
+  const int nwarps = blockDim.x >> 5;
+  const int wc = lane < nwarps ? wsum[lane] : 0;
+  const int before = (int)__reduce_add_sync(0xffffffffu, (unsigned)(lane < warp ? wc : 0));
+  int total = (int)__reduce_add_sync(0xffffffffu, (unsigned)wc);
+  const int allowed = max_keep > 0 ? max_keep - count0 : 0x7fffffff;
+  if (total > allowed) total = allowed;
+  if (tid == 0) {
+    p.kcount[seg] = total;
+    p.count[seg] = count0 + total;
+    if (max_keep > 0 && count0 + total >= max_keep) p.done[seg] = 1;
+  }
+  if (my_kept) {
+    const int pos = before + __popc(kb & ((1u << lane) - 1u));
+    if (pos < allowed) {
+      if (ascending)
+        flags[off + my_e] = 1;
+      else
+        keep[off + count0 + pos] = my_e;
+      p.kbox[(size_t)seg * p.BR + pos] = my_box;
+      p.karea[(size_t)seg * p.BR + pos] = my_area;
+      if (p.slabel) p.klabel[(size_t)seg * p.BR + pos] = my_label;
     }
   }
+}
+
+__global__ void __launch_bounds__(NMS_BAND_MAX)
+nms_resolve_kernel(NmsBand p, int band, int max_keep, int ascending, int* __restrict__ keep,
+                   uint8_t* __restrict__ flags) {
+  __shared__ NmsResSmem sm;
+  nms_resolve_body(p, blockIdx.x, band, max_keep, ascending, keep, flags, sm, NmsNoWait());
+}
+
+// ------------------------------------------------------------------------------------------
+// All bands in ONE cooperative launch (one CTA per SM, 1024 threads): per band the problems are
+// resolved by the first B CTAs, a grid barrier, the suppress / next-diagonal work items are spread
+// over the grid, a grid barrier.  Replaces 2 launches per band (each ~3 us of launch + drain on an
+// otherwise idle GPU) by two ~1 us barriers; the single-image n = 20000 case has 20 bands.
+// The barrier is a monotonic arrival counter in the (zeroed) workspace; the launch is cooperative,
+// so all CTAs are resident, and the wait is bounded (trap instead of a hang).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void nms_grid_barrier(unsigned* bar, unsigned target) {
   __syncthreads();
-  // emit: keep list in rank order, and the band's kept boxes for the suppress launch
-  for (int t = tid; t < rows; t += blockDim.x) {
-    const int c = t >> 6, bit = t & 63;
-    const uint64_t kept = keptm[c];
-    if ((kept >> bit) & 1ull) {
-      const int pos = cbase[c] + __popcll(kept & ((1ull << bit) - 1ull));
-      const int rank = off + base + t;
-      const int e = p.sorted_vals[rank] - off;
-      if (ascending)
-        flags[off + e] = 1;
-      else
-        keep[off + count0 + pos] = e;
-      p.kbox[(size_t)seg * p.BR + pos] = p.sboxes[rank];
-      p.karea[(size_t)seg * p.BR + pos] = p.sarea[rank];
-      if (p.slabel) p.klabel[(size_t)seg * p.BR + pos] = p.slabel[rank];
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1u);
+    unsigned spins = 0;
+    while (*reinterpret_cast<volatile unsigned*>(bar) < target) {
+      if (++spins > (1u << 23)) __trap();  // seconds: a resident grid never gets here
     }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+union NmsFusedSmem {
+  NmsResSmem res;
+  NmsSupSmem sup;
+};
+
+template <bool GE, bool LABELS>
+__global__ void __launch_bounds__(NMS_BAND_MAX)
+nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* __restrict__ keep,
+                 uint8_t* __restrict__ flags, int* __restrict__ n_keep, unsigned* __restrict__ bar) {
+  __shared__ NmsFusedSmem sm;
+  const unsigned G = gridDim.x;
+  unsigned phase = 0;
+  const int ndiag = p.bw * (p.bw + 1) / 2;
+  // diagonal block of band 0
+  for (int it = blockIdx.x; it < B * ndiag; it += G) {
+    const int seg = it / ndiag;
+    nms_diag_part<GE, LABELS>(p, seg, 0, it - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl, sm.sup.wordS);
+    __syncthreads();
+  }
+  nms_grid_barrier(bar, ++phase * G);
+  for (int b = 0; b < bands; ++b) {
+#ifdef NMS_PROFILE
+    if (threadIdx.x == 0 && blockIdx.x == 0) nms_prof_on = (b == 3);
+    __syncthreads();
+#endif
+    NMS_STAMP(0);
+    for (int seg = blockIdx.x; seg < B; seg += G) {
+      nms_resolve_body(p, seg, b, max_keep, ascending, keep, flags, sm.res, NmsNoWait());
+      __syncthreads();
+      if (b + 1 == bands && !ascending && threadIdx.x == 0) n_keep[seg] = p.count[seg];
+    }
+    if (b + 1 == bands) break;
+    NMS_STAMP(1);
+    nms_grid_barrier(bar, ++phase * G);
+    NMS_STAMP(2);
+    const int nsup = p.wmax - (b + 1) * p.bw;
+    const int per = nsup + ndiag;
+    int cached = -1;  // the resolve step of this CTA (if any) used the shared memory
+    for (int it = blockIdx.x; it < B * per; it += G) {
+      const int seg = it / per;
+      nms_suppress_body<GE, LABELS>(p, seg, b, it - seg * per, nsup, sm.sup, cached);
+      __syncthreads();
+    }
+    NMS_STAMP(3);
+    nms_grid_barrier(bar, ++phase * G);
+    NMS_STAMP(4);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Few problems, many bands (one image of 20000 proposals = 20 bands): the two grid barriers per band
+// of nms_bands_kernel leave 147 CTAs idle while one resolves.  The dataflow kernel gives every
+// problem its own resolver CTA and lets the other CTAs (workers) own the removed words and diagonal
+// tiles statically (word (problem, w) -> worker (problem * wmax + w) mod NW, so the updates of a word
+// are ordered by program order).  Monotonic counters connect them:
+//   R[s]   bands of problem s resolved          (resolver -> workers: kept list of band b is ready)
+//   Dc[par][s]  diagonal tiles finished, bands of parity par   (workers -> resolver)
+//   Uc[s]       "urgent" word items finished: the words of band b+1 in the suppress step of band b
+//   Fc[par][s]  word items finished, steps of parity par (the kept-list and diagonal buffers are
+//               double buffered; a buffer is reused two bands later, once its step has drained)
+// (Dc and Fc are kept per parity because a fast worker may already count items of step b+1 while a
+// slow one is still inside step b: a single running total could reach its target early.)
+// The resolver of band b+1 waits only for the 16 urgent words of step b, which their owners process
+// first; the rest of step b overlaps with the resolve of band b+1.  The launch is cooperative (all
+// CTAs resident), every wait is bounded.
+// ------------------------------------------------------------------------------------------
+struct NmsFlow {
+  unsigned *R, *Uc, *Dc[2], *Fc[2];
+  uint64_t* D[2];
+  NmsBox* kbox[2];
+  float *karea[2], *klabel[2];
+  int* kcount[2];
+};
+
+__device__ __forceinline__ void nms_wait_ge(const unsigned* ctr, unsigned target) {
+  if (threadIdx.x == 0) {
+    unsigned spins = 0, v;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+      if (v >= target) break;
+      if (++spins > (1u << 23)) __trap();  // seconds: a resident grid never gets here
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+// the same, handing the value seen to the whole CTA (through `slot`, free again after the next barrier)
+__device__ __forceinline__ unsigned nms_wait_ge_value(const unsigned* ctr, unsigned target, unsigned* slot) {
+  if (threadIdx.x == 0) {
+    unsigned spins = 0, v;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+      if (v >= target) break;
+      if (++spins > (1u << 23)) __trap();
+    }
+    __threadfence();
+    *slot = v;
+  }
+  __syncthreads();
+  const unsigned v = *slot;
+  __syncthreads();
+  return v;
+}
+// after the CTA's writes: counter a (and b, if given) += the given amounts
+__device__ __forceinline__ void nms_signal_add2(unsigned* a, unsigned na, unsigned* b, unsigned nb) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (na) atomicAdd(a, na);
+    if (nb) atomicAdd(b, nb);
+  }
+}
+// after the CTA's writes
+__device__ __forceinline__ void nms_signal_add(unsigned* ctr) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(ctr, 1u);
+  }
+}
+__device__ __forceinline__ void nms_signal_max(unsigned* ctr, unsigned v) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicMax(ctr, v);
+  }
+}
+
+struct NmsFlowWait {
+  const unsigned *uc, *fc;
+  unsigned ut, ft;
+  int band;
+  __device__ __forceinline__ void operator()() const {
+    if (band >= 1) nms_wait_ge(uc, ut);
+    if (band >= 2) nms_wait_ge(fc, ft);
+  }
+};
+
+template <bool GE, bool LABELS>
+__global__ void __launch_bounds__(NMS_BAND_MAX)
+nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascending,
+                int* __restrict__ keep, uint8_t* __restrict__ flags, int* __restrict__ n_keep) {
+  __shared__ NmsFusedSmem sm;
+  const int G = gridDim.x, NW = G - B;
+  const int ndiag = p.bw * (p.bw + 1) / 2;
+  {  // diagonal block of band 0: all CTAs
+    NmsBand q = p;
+    q.D = f.D[0];
+    for (int it = blockIdx.x; it < B * ndiag; it += G) {
+      const int seg = it / ndiag;
+      nms_diag_part<GE, LABELS>(q, seg, 0, it - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl, sm.sup.wordS);
+      nms_signal_add(&f.Dc[0][seg]);
+    }
+    __syncthreads();
+  }
+  if ((int)blockIdx.x < B) {
+    // ---- resolver of problem seg
+    const int seg = blockIdx.x;
+    const int n = p.offsets[seg + 1] - p.offsets[seg];
+    unsigned ut = 0, fsum[2] = {0u, 0u};  // urgent items of steps < b; word items of the steps of each parity
+    for (int b = 0; b < bands; ++b) {
+      const int par = b & 1;
+      NmsBand q = p;
+      q.D = f.D[par];
+      q.kbox = f.kbox[par];
+      q.karea = f.karea[par];
+      q.klabel = f.klabel[par];
+      q.kcount = f.kcount[par];
+#ifdef NMS_PROFILE
+      if (threadIdx.x == 0 && blockIdx.x == 0) nms_prof_on = (b == 3);
+      __syncthreads();
+#endif
+      nms_wait_ge(&f.Dc[par][seg], (unsigned)((b / 2 + 1) * ndiag));
+      NmsFlowWait wait{&f.Uc[seg], &f.Fc[par][seg], ut, fsum[par], b};
+      NMS_STAMP(0);
+      nms_resolve_body(q, seg, b, max_keep, ascending, keep, flags, sm.res, wait);
+      __syncthreads();
+      NMS_STAMP(1);
+      const bool capped = p.done[seg] != 0;
+      const bool last = (b + 1 == bands) || capped || (b + 1) * p.BR >= n;
+      // R = bands: all bands resolved; bands + 1: the keep cap was reached, later steps are void
+      nms_signal_max(&f.R[seg], (unsigned)(capped ? bands + 1 : (last ? bands : b + 1)));
+      if (last) break;
+      const int items = p.wmax - (b + 1) * p.bw;  // word items of step b (> 0: the problem goes on)
+      ut += (unsigned)(items < p.bw ? items : p.bw);
+      fsum[par] += (unsigned)items;
+    }
+    __syncthreads();
+    if (!ascending && threadIdx.x == 0) n_keep[seg] = p.count[seg];
+    return;
+  }
+  // ---- worker v
+  const int v = blockIdx.x - B;
+  unsigned capped_mask = 0u;
+  const unsigned all_mask = (B >= 32) ? 0xffffffffu : ((1u << B) - 1u);
+  for (int b = 0; b + 1 < bands; ++b) {
+    {  // tiles of band b+1, into the buffer band b-1 used
+      NmsBand q = p;
+      q.D = f.D[(b + 1) & 1];
+      for (int gt = v; gt < B * ndiag; gt += NW) {
+        const int seg = gt / ndiag;
+        if ((capped_mask >> seg) & 1u) continue;
+        if (b >= 1 && nms_wait_ge_value(&f.R[seg], (unsigned)b, &sm.sup.bcast) > (unsigned)bands) {
+          capped_mask |= 1u << seg;
+          continue;
+        }
+        nms_diag_part<GE, LABELS>(q, seg, b + 1, gt - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl,
+                                  sm.sup.wordS);
+        nms_signal_add(&f.Dc[(b + 1) & 1][seg]);
+      }
+      __syncthreads();
+    }
+    const int par = b & 1;
+    NmsBand q = p;
+    q.kbox = f.kbox[par];
+    q.karea = f.karea[par];
+    q.klabel = f.klabel[par];
+    q.kcount = f.kcount[par];
+    const int w0 = (b + 1) * p.bw;
+    const int w1 = w0 + p.bw < p.wmax ? w0 + p.bw : p.wmax;
+    int cached = -1;
+    for (int sweep = 0; sweep < 2; ++sweep) {  // the words of band b+1 first
+      const int lo = sweep ? w1 : w0, hi = sweep ? p.wmax : w1;
+      for (int seg = 0; seg < B; ++seg) {
+        if ((capped_mask >> seg) & 1u) continue;
+        const int r = (int)(((long long)seg * p.wmax + lo) % NW);
+        int w = lo + (v - r + NW) % NW;
+        while (w < hi) {
+          int wl[4] = {0, 0, 0, 0};
+          int nw = 0;
+          for (; nw < 4 && w < hi; ++nw, w += NW) wl[nw] = w;
+          const unsigned rv = nms_wait_ge_value(&f.R[seg], (unsigned)(b + 1), &sm.sup.bcast);
+          if (rv > (unsigned)bands) {  // cap reached: nobody will read these words again
+            capped_mask |= 1u << seg;
+            break;
+          }
+          nms_suppress_multi<GE, LABELS>(q, seg, wl, nw, sm.sup, cached);
+          nms_signal_add2(&f.Uc[seg], sweep == 0 ? (unsigned)nw : 0u, &f.Fc[par][seg], (unsigned)nw);
+        }
+      }
+    }
+    if (capped_mask == all_mask) return;  // (uniform: every thread sees the same R values)
+    __syncthreads();
   }
 }
 
@@ -397,6 +856,8 @@ nms_finish_kernel(const int* __restrict__ offsets, const int* __restrict__ count
   if (tid == 0) n_keep[b] = s_base;
 }
 
+constexpr int NMS_FLOW_MAXB = 16;  // problems the dataflow kernel takes (one resolver CTA each)
+
 struct NmsWorkspace {
   uint64_t *keys_in, *keys_out;
   int *vals_in, *vals_out;
@@ -408,6 +869,12 @@ struct NmsWorkspace {
   // banded scan state; [zero_begin, zero_begin + zero_bytes) is cleared at the start of a call
   uint64_t* removed;
   int *count, *done, *kcount;
+  unsigned* bar;  // grid-barrier arrival counter of the one-launch path
+  unsigned* flow_ctr;  // [6][B] counters of the dataflow kernel
+  int* kcount2;
+  uint64_t* D2;
+  NmsBox* kbox2;
+  float *karea2, *klabel2;
   char* zero_begin;
   size_t zero_bytes;
   uint64_t* D;
@@ -454,35 +921,109 @@ NmsWorkspace nms_carve(void* base, int n_total, int n_max, int B) {
   w.count = (int*)take(nb * 4);
   w.done = (int*)take(nb * 4);
   w.kcount = (int*)take(nb * 4);
+  w.bar = (unsigned*)take(256);
+  w.flow_ctr = (unsigned*)take(nb * 24);
+  w.kcount2 = (int*)take(nb * 4);
   w.zero_begin = base ? (char*)base + z0 : nullptr;
   w.zero_bytes = o - z0;
   w.D = (uint64_t*)take(nb * (size_t)w.BR * w.bw * 8);
   w.kbox = (NmsBox*)take(nb * (size_t)w.BR * sizeof(NmsBox));
   w.karea = (float*)take(nb * (size_t)w.BR * 4);
   w.klabel = (float*)take(nb * (size_t)w.BR * 4);
+  // second buffer set of the dataflow kernel (few problems, many bands)
+  const size_t nf = nb <= NMS_FLOW_MAXB ? nb : 0;
+  w.D2 = (uint64_t*)take(nf * (size_t)w.BR * w.bw * 8);
+  w.kbox2 = (NmsBox*)take(nf * (size_t)w.BR * sizeof(NmsBox));
+  w.karea2 = (float*)take(nf * (size_t)w.BR * 4);
+  w.klabel2 = (float*)take(nf * (size_t)w.BR * 4);
   w.total = o;
   return w;
 }
 
+// cooperative-launch capacity (CTAs of 1024 threads, at most one per SM) of a one-launch kernel
+int nms_coop_capacity(const void* kernel, int slot) {
+  static std::mutex mu;
+  static int cap[8][64];
+  static bool known[8][64];
+  int dev = 0;
+  (void)cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || slot < 0 || slot >= 8) return 0;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!known[slot][dev]) {
+    int coop = 0, sms = 0, occ = 0;
+    (void)cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    (void)cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, NMS_BAND_MAX, 0) != cudaSuccess) {
+      (void)cudaGetLastError();
+      occ = 0;
+    }
+    cap[slot][dev] = (coop && occ >= 1) ? sms : 0;  // one CTA per SM: synchronisation is the cost
+    known[slot][dev] = true;
+  }
+  return cap[slot][dev];
+}
+
+// *need_finish = 0 when n_keep has been written already
 template <bool GE, bool LABELS>
-int nms_run_bands(const NmsBand& p, int B, int n_max, int max_keep, int ascending, int* keep,
-                  uint8_t* flags, cudaStream_t st) {
+int nms_run_bands(const NmsBand& p, const NmsWorkspace& w, int B, int n_max, int max_keep, int ascending,
+                  int* keep, uint8_t* flags, int* n_keep, int* need_finish, cudaStream_t st) {
   const int bands = (n_max + p.BR - 1) / p.BR;
-  const int groups = (p.bw + 3) / 4;
-  const int ndiag = p.bw * groups;
-  const size_t smem = sizeof(uint64_t) * ((size_t)p.BR * p.bw + 2 * (size_t)p.bw) +
-                      sizeof(int) * ((size_t)p.bw + 2);
-  RP_SET_MAX_SMEM(nms_resolve_kernel, smem);
-  const int rthreads = p.BR >= 1024 ? 1024 : (p.BR < 128 ? 128 : p.BR);
+  const int ndiag = p.bw * (p.bw + 1) / 2;  // lower-triangle tiles of a diagonal block
+  const int slot = (GE ? 1 : 0) + (LABELS ? 2 : 0);
+  *need_finish = 1;
+  if (bands >= 2 && B <= NMS_FLOW_MAXB && rp_env_int("RP_NMS_FUSED", 1) && rp_env_int("RP_NMS_FLOW", 1)) {
+    const int cap = nms_coop_capacity((const void*)nms_flow_kernel<GE, LABELS>, 4 + slot);
+    if (cap >= B + 64) {
+      NmsBand pc = p;
+      NmsFlow f;
+      f.R = w.flow_ctr;
+      f.Uc = w.flow_ctr + B;
+      f.Dc[0] = w.flow_ctr + 2 * B;
+      f.Dc[1] = w.flow_ctr + 3 * B;
+      f.Fc[0] = w.flow_ctr + 4 * B;
+      f.Fc[1] = w.flow_ctr + 5 * B;
+      f.D[0] = w.D;
+      f.D[1] = w.D2;
+      f.kbox[0] = w.kbox;
+      f.kbox[1] = w.kbox2;
+      f.karea[0] = w.karea;
+      f.karea[1] = w.karea2;
+      f.klabel[0] = w.klabel;
+      f.klabel[1] = w.klabel2;
+      f.kcount[0] = w.kcount;
+      f.kcount[1] = w.kcount2;
+      int B_ = B, bands_ = bands, mk = max_keep, asc = ascending;
+      void* args[] = {&pc, &f, &B_, &bands_, &mk, &asc, &keep, &flags, &n_keep};
+      RP_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)nms_flow_kernel<GE, LABELS>, dim3((unsigned)cap),
+                                              dim3(NMS_BAND_MAX), args, 0, st));
+      *need_finish = ascending ? 1 : 0;
+      return RP_OK;
+    }
+  }
+  const int cap = rp_env_int("RP_NMS_FUSED", 1) ? nms_coop_capacity((const void*)nms_bands_kernel<GE, LABELS>, slot) : 0;
+  if (cap > 0) {
+    long long items = (long long)B * ndiag;
+    if (bands > 1) items = (long long)B * (p.wmax - p.bw + ndiag);
+    if (items < B) items = B;
+    const int G = (int)(items < cap ? items : cap);
+    NmsBand pc = p;
+    unsigned* bar = w.bar;
+    int B_ = B, bands_ = bands, mk = max_keep, asc = ascending;
+    void* args[] = {&pc, &B_, &bands_, &mk, &asc, &keep, &flags, &n_keep, &bar};
+    RP_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)nms_bands_kernel<GE, LABELS>, dim3((unsigned)G),
+                                            dim3(NMS_BAND_MAX), args, 0, st));
+    *need_finish = ascending ? 1 : 0;
+    return RP_OK;
+  }
   nms_diag_kernel<GE, LABELS><<<dim3((unsigned)ndiag, (unsigned)B), 256, 0, st>>>(p, 0);
   RP_LAUNCH_CHECK();
   for (int b = 0; b < bands; ++b) {
-    nms_resolve_kernel<<<B, rthreads, smem, st>>>(p, b, max_keep, ascending, keep, flags);
+    nms_resolve_kernel<<<B, p.BR, 0, st>>>(p, b, max_keep, ascending, keep, flags);
     RP_LAUNCH_CHECK();
     if (b + 1 < bands) {
       const int nsup = p.wmax - (b + 1) * p.bw;
-      nms_suppress_kernel<GE, LABELS><<<dim3((unsigned)(nsup + ndiag), (unsigned)B), 256, 0, st>>>(
-          p, b, nsup);
+      nms_suppress_kernel<GE, LABELS>
+          <<<dim3((unsigned)(nsup + ndiag), (unsigned)B), NMS_SUP_THREADS, 0, st>>>(p, b, nsup);
       RP_LAUNCH_CHECK();
     }
   }
@@ -492,6 +1033,12 @@ int nms_run_bands(const NmsBand& p, int B, int n_max, int max_keep, int ascendin
 }  // namespace
 
 extern "C" {
+
+#ifdef NMS_PROFILE
+__attribute__((visibility("default"))) int rp_debug_nms_prof(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, nms_prof, sizeof(long long) * 32);
+}
+#endif
 
 size_t rp_nms_workspace_bytes(int n_total, int n_max, int B) {
   if (n_total < 0 || n_max < 0 || B < 1) return 0;
@@ -524,18 +1071,24 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
     t_lo = -INFINITY;  // never reject early: every pair takes the exact division
   const int T = 256;
   const int nb = (n_total + T - 1) / T;
+  const bool zero_in_keys = (w.zero_bytes % 8 == 0) && (w.zero_bytes / 8 <= (size_t)nb * T);
   nms_keys_kernel<<<nb, T, 0, st>>>(scores, offsets, B, n_total,
-                                    (flags & RP_NMS_TIES_HIGH_FIRST) ? 1 : 0, w.keys_in, w.vals_in);
+                                    (flags & RP_NMS_TIES_HIGH_FIRST) ? 1 : 0, w.keys_in, w.vals_in,
+                                    reinterpret_cast<uint64_t*>(w.zero_begin),
+                                    zero_in_keys ? (int)(w.zero_bytes / 8) : 0);
   RP_LAUNCH_CHECK();
-  int seg_bits = 1;
-  while ((1 << seg_bits) < B + 1) ++seg_bits;  // B problems + the slack id B
+  int seg_bits = 0;  // one problem: its rows and the slack rows differ in the low word already
+  if (B > 1) {
+    seg_bits = 1;
+    while ((1 << seg_bits) < B + 1) ++seg_bits;  // B problems + the slack id B
+  }
   RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
                                               w.vals_in, w.vals_out, n_total, 0, 32 + seg_bits,
                                               st));
   nms_gather_kernel<<<nb, T, 0, st>>>(boxes, labels, w.vals_out, n_total, w.sboxes, w.sarea,
                                       w.slabel);
   RP_LAUNCH_CHECK();
-  RP_CUDA_TRY(cudaMemsetAsync(w.zero_begin, 0, w.zero_bytes, st));
+  if (!zero_in_keys) RP_CUDA_TRY(cudaMemsetAsync(w.zero_begin, 0, w.zero_bytes, st));
   if (ascending) RP_CUDA_TRY(cudaMemsetAsync(w.flags, 0, (size_t)n_total, st));
   if (B > 65535) return RP_E_LIMIT;
   NmsBand p;
@@ -557,16 +1110,17 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
   p.bw = w.bw;
   p.t_cmp = t_cmp;
   p.t_lo = t_lo;
-  int rc;
+  int rc, need_finish = 1;
   if (labels)
-    rc = ge ? nms_run_bands<true, true>(p, B, n_max, max_keep, ascending, keep, w.flags, st)
-            : nms_run_bands<false, true>(p, B, n_max, max_keep, ascending, keep, w.flags, st);
+    rc = ge ? nms_run_bands<true, true>(p, w, B, n_max, max_keep, ascending, keep, w.flags, n_keep, &need_finish, st)
+            : nms_run_bands<false, true>(p, w, B, n_max, max_keep, ascending, keep, w.flags, n_keep, &need_finish, st);
   else
-    rc = ge ? nms_run_bands<true, false>(p, B, n_max, max_keep, ascending, keep, w.flags, st)
-            : nms_run_bands<false, false>(p, B, n_max, max_keep, ascending, keep, w.flags, st);
+    rc = ge ? nms_run_bands<true, false>(p, w, B, n_max, max_keep, ascending, keep, w.flags, n_keep, &need_finish, st)
+            : nms_run_bands<false, false>(p, w, B, n_max, max_keep, ascending, keep, w.flags, n_keep, &need_finish, st);
   if (rc) return rc;
-  nms_finish_kernel<<<B, NMS_SCAN_THREADS, 0, st>>>(offsets, w.count, ascending, w.flags, keep,
-                                                    n_keep);
+  if (need_finish)
+    nms_finish_kernel<<<B, NMS_SCAN_THREADS, 0, st>>>(offsets, w.count, ascending, w.flags, keep,
+                                                      n_keep);
   RP_LAUNCH_CHECK();
   return RP_OK;
 }

@@ -182,3 +182,48 @@ def test_iou_comparator_on_exact_threshold_pairs():
         keep, nk = rp.nms_batched(T(flat_b), T(flat_s), T(offs), thr, n_max=2, flags=1)  # RP_NMS_GE
         exp_ge = np.array([len(oracle.cython_nms(np.concatenate([boxes[i], scores[i][:, None]], 1), thr)) for i in range(B)])
         assert np.array_equal(nk.cpu().numpy(), exp_ge)
+
+
+def _chain_boxes(n, step):
+    # box i = box 0 shifted by i * step pixels: every box overlaps its neighbours only, so the greedy
+    # result alternates along one long dependency chain (the worst case of the band fixpoint)
+    x = (np.arange(n) * step).astype(np.float32)
+    b = np.stack([x, np.zeros(n, np.float32), x + 99.0, np.full(n, 49.0, np.float32)], 1)
+    s = np.linspace(1.0, 0.1, n).astype(np.float32)
+    return b, s
+
+
+@pytest.mark.parametrize("fused", ["1", "0"])
+def test_one_launch_and_per_band_launch_paths(monkeypatch, fused):
+    # RP_NMS_FUSED=1 (default): all bands in one cooperative launch with grid barriers;
+    # RP_NMS_FUSED=0: one resolve + one suppress launch per band.  Same results, bit for bit.
+    monkeypatch.setenv("RP_NMS_FUSED", fused)
+    rp.reload_env()
+    try:
+        b, s, _ = synth.nms_boxes(5000, 11, tie_heavy=True)
+        for thr, mk in ((0.7, -1), (0.5, 300), (0.3, -1)):
+            keep, nk = rp.nms_batched(T(b), T(s), T(np.array([0, 5000], np.int32)), thr, max_keep=mk)
+            np.testing.assert_array_equal(keep.cpu().numpy()[: int(nk[0])], oracle.nms(b, s, thr, max_keep=mk))
+        # ragged batch with labels, problems of 1 .. 3 bands
+        lens = [2500, 0, 1100, 64, 3000]
+        bs, ss, ls = zip(*[synth.nms_boxes(max(n, 1), 60 + i) for i, n in enumerate(lens)])
+        bs = [x[:n] for x, n in zip(bs, lens)]
+        ss = [x[:n] for x, n in zip(ss, lens)]
+        ls = [x[:n] for x, n in zip(ls, lens)]
+        offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        keep, nk = rp.nms_batched(T(np.concatenate(bs)), T(np.concatenate(ss)), T(offs), 0.5,
+                                  labels=T(np.concatenate(ls).astype(np.float32)), max_keep=200)
+        keep, nk = keep.cpu().numpy(), nk.cpu().numpy()
+        for i, n in enumerate(lens):
+            ref = oracle.nms(bs[i], ss[i], 0.5, labels=ls[i], max_keep=200) if n else np.zeros(0, np.int32)
+            np.testing.assert_array_equal(keep[offs[i]: offs[i] + nk[i]], ref)
+        # one dependency chain through 3 bands: hundreds of fixpoint rounds per band
+        cb, cs = _chain_boxes(2500, 20.0)
+        for thr in (0.5, 0.3):
+            keep = rp.nms(T(cb), T(cs), thr).cpu().numpy()
+            np.testing.assert_array_equal(keep, oracle.nms(cb, cs, thr))
+        dets = np.concatenate([cb, cs[:, None]], 1)
+        np.testing.assert_array_equal(rp.cython_nms(T(dets), 0.5).cpu().numpy(), oracle.cython_nms(dets, 0.5))
+    finally:
+        monkeypatch.delenv("RP_NMS_FUSED")
+        rp.reload_env()
