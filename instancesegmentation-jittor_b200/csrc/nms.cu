@@ -166,26 +166,32 @@ struct NmsBand {
   float t_cmp, t_lo;
 };
 
-// One 64 x 64 tile (row block rb, column block cb <= rb) of the diagonal block of `band` per CTA;
-// thread = (row r, column sub-range q): 64 / (blockDim / 64) pair tests each, the sub-ranges of a row
-// are merged through a shared word.  bw (bw + 1) / 2 tiles per problem.
+// 64 x 64 tiles (row block rb, column block cb <= rb) of the diagonal block of `band`: every group of
+// 256 threads of the CTA takes one tile (t_first + group * t_step, `count` tiles in all, count <=
+// blockDim / 256); thread = (row r, column quarter q), 16 pair tests, the quarters of a row are merged
+// through a shared word.  bw (bw + 1) / 2 tiles per problem.  The whole CTA must call this together.
+// Shared arrays: 64 entries per group.
 template <bool GE, bool LABELS>
-__device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int band, int tile,
-                                              NmsBox* cbox, float* carea, float* clabel,
-                                              unsigned long long* wordS) {
+__device__ __forceinline__ void nms_diag_tiles(const NmsBand& p, int seg, int band, int t_first,
+                                               int t_step, int count, NmsBox* cbox, float* carea,
+                                               float* clabel, unsigned long long* wordS) {
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
   const int base = band * p.BR;
-  if (base >= n) return;
+  const int g = threadIdx.x >> 8, tid = threadIdx.x & 255;
+  int tile = t_first + g * t_step;
   int rb = 0;
   while (tile >= rb + 1) {
     tile -= rb + 1;
     ++rb;
   }
   const int cb = tile;
-  if (rb >= p.bw || base + rb * 64 >= n) return;
-  const int tid = threadIdx.x;
-  if (tid < 64) {
+  const bool valid = g < count && base < n && rb < p.bw && base + rb * 64 < n;
+  cbox += g * 64;
+  carea += g * 64;
+  clabel += g * 64;
+  wordS += g * 64;
+  if (valid && tid < 64) {
     const int c = base + cb * 64 + tid;  // c < n: the column block is not after the row block
     if (c < n) {
       cbox[tid] = p.sboxes[off + c];
@@ -195,19 +201,17 @@ __device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int ban
     wordS[tid] = 0ull;
   }
   __syncthreads();
-  const int nq = blockDim.x >> 6, cw = 64 / nq;
   const int r = tid & 63, q = tid >> 6;
-  const int rrow = rb * 64 + r;  // row inside the band
-  const int row = base + rrow;
-  if (row < n) {
+  const int row = base + rb * 64 + r;
+  if (valid && row < n) {
     const NmsBox a = p.sboxes[off + row];
     const float aarea = p.sarea[off + row];
     float alabel = 0.f;
     if (LABELS) alabel = p.slabel[off + row];
     // columns of strictly higher rank only
-    const int cend = min((q + 1) * cw, (cb == rb) ? r : 64);
+    const int cend = min((q + 1) * 16, (cb == rb) ? r : 64);
     uint64_t bits = 0;
-    for (int c = q * cw; c < cend; ++c) {
+    for (int c = q * 16; c < cend; ++c) {
       bool sup = nms_pair<GE>(cbox[c], carea[c], a, aarea, p.t_cmp, p.t_lo);
       if (LABELS) sup = sup && (alabel == clabel[c]);
       if (sup) bits |= (1ull << c);
@@ -215,7 +219,7 @@ __device__ __forceinline__ void nms_diag_part(const NmsBand& p, int seg, int ban
     if (bits) atomicOr(&wordS[r], (unsigned long long)bits);
   }
   __syncthreads();
-  if (tid < 64 && base + rb * 64 + tid < n)
+  if (valid && tid < 64 && base + rb * 64 + tid < n)
     p.D[((size_t)seg * p.bw + cb) * p.BR + rb * 64 + tid] = wordS[tid];
 }
 
@@ -226,7 +230,7 @@ nms_diag_kernel(NmsBand p, int band) {
   __shared__ float carea[64];
   __shared__ float clabel[64];
   __shared__ unsigned long long wordS[64];
-  nms_diag_part<GE, LABELS>(p, blockIdx.y, band, blockIdx.x, cbox, carea, clabel, wordS);
+  nms_diag_tiles<GE, LABELS>(p, blockIdx.y, band, blockIdx.x, 1, 1, cbox, carea, clabel, wordS);
 }
 
 // Blocks [0, nsup): 64 later boxes each against the boxes band `band` kept, 16 threads per box (the
@@ -240,10 +244,13 @@ struct NmsSupSmem {
   float ka[NMS_BAND_MAX];
   float kl[NMS_BAND_MAX];
   unsigned long long s_new;
-  unsigned long long wordS[64];
-  unsigned long long s_new4[4];
+  unsigned long long wordS[256];
   unsigned bcast;
+  // multi-word pass
+  unsigned long long mw_word[16], mw_alive[16], mw_new[16];
+  int mw_pre[17];
 };
+constexpr int NMS_MW = 16;  // words per multi-word pass
 
 // Work item x of problem seg in the suppress step of `band` (the CTA returns together).
 // The still-alive boxes of the 64-box word are compacted and each gets P = 16, 32 or 64 threads
@@ -255,8 +262,8 @@ __device__ __forceinline__ void nms_suppress_body(const NmsBand& p, int seg, int
                                                   NmsSupSmem& sm, int& cached) {
   const int tid = threadIdx.x;
   if (x >= nsup) {
-    nms_diag_part<GE, LABELS>(p, seg, band + 1, x - nsup, sm.kb, sm.ka, sm.kl, sm.wordS);
-    cached = -1;  // the tile used the kept-list buffers
+    nms_diag_tiles<GE, LABELS>(p, seg, band + 1, (x - nsup) * 4, 1, 4, sm.kb, sm.ka, sm.kl, sm.wordS);
+    cached = -1;  // the tiles used the kept-list buffers
     return;
   }
   const int wj = (band + 1) * p.bw + x;
@@ -304,31 +311,41 @@ __device__ __forceinline__ void nms_suppress_body(const NmsBand& p, int seg, int
   if (tid == 0 && sm.s_new) p.removed[(size_t)seg * p.wmax + wj] = word | sm.s_new;
 }
 
-// Up to 4 words of ONE problem in one pass (dataflow workers): the alive boxes of all words are
-// compacted together and share the 1024 threads, P = 1024 / alive threads per box (at most 64).
-// Does not look at done[seg] (the resolver may be writing it): the caller knows from R.
+// Up to NMS_MW words (w_first, w_first + w_step, ...) of ONE problem in one pass: the alive boxes of
+// all words are compacted together and share the 1024 threads, P = 1024 / alive threads per box (at
+// most 64), which split the kept list between them.  One set of round trips per pass instead of per
+// word.  Does not look at done[seg] (in the dataflow kernel the resolver may be writing it).
 template <bool GE, bool LABELS>
-__device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, const int (&wl)[4], int nw,
-                                                   NmsSupSmem& sm, int& cached) {
+__device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, int w_first, int w_step,
+                                                   int nw, NmsSupSmem& sm, int& cached) {
   const int tid = threadIdx.x;
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
   const int kc = p.kcount[seg];
-  uint64_t word[4], alive[4];
-  int pre[5];
-  pre[0] = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    word[k] = 0ull;
-    alive[k] = 0ull;
-    if (k < nw && wl[k] * 64 < n) {
-      word[k] = p.removed[(size_t)seg * p.wmax + wl[k]];
-      const int nv = min(64, n - wl[k] * 64);
-      alive[k] = ~word[k] & (nv == 64 ? ~0ull : ((1ull << nv) - 1ull));
+  if (tid < 32) {
+    uint64_t word = 0ull, alive = 0ull;
+    const int wk = w_first + tid * w_step;
+    if (tid < nw && wk * 64 < n) {
+      word = p.removed[(size_t)seg * p.wmax + wk];
+      const int nv = min(64, n - wk * 64);
+      alive = ~word & (nv == 64 ? ~0ull : ((1ull << nv) - 1ull));
     }
-    pre[k + 1] = pre[k] + __popcll(alive[k]);
+    int c = __popcll(alive);
+#pragma unroll
+    for (int d = 1; d < NMS_MW; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, c, d);
+      if (tid >= d) c += t;
+    }
+    if (tid < NMS_MW) {
+      sm.mw_word[tid] = word;
+      sm.mw_alive[tid] = alive;
+      sm.mw_new[tid] = 0ull;
+      sm.mw_pre[tid + 1] = c;
+    }
+    if (tid == 0) sm.mw_pre[0] = 0;
   }
-  const int na = pre[4];
+  __syncthreads();
+  const int na = sm.mw_pre[NMS_MW];
   if (kc == 0 || na == 0) return;
   if (cached != seg) {
     for (int i = tid; i < kc; i += NMS_SUP_THREADS) {
@@ -337,30 +354,24 @@ __device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, co
       if (LABELS) sm.kl[i] = p.klabel[(size_t)seg * p.BR + i];
     }
     cached = seg;
+    __syncthreads();
   }
-  if (tid < 4) sm.s_new4[tid] = 0ull;
-  __syncthreads();
   int P = NMS_SUP_THREADS / na;
   if (P > 64) P = 64;
+  if (P < 1) P = 1;
+  // na > 1024 (16 words, all alive) cannot happen: 16 x 64 = 1024 boxes at most
   const int slot = tid / P, part = tid - slot * P;
   if (slot < na) {
     int k = 0;
 #pragma unroll
-    for (int t = 1; t < 4; ++t)
-      if (slot >= pre[t]) k = t;
-    uint64_t a = alive[0];
-    int wk = wl[0], ls = slot;
-#pragma unroll
-    for (int t = 1; t < 4; ++t)
-      if (k == t) {
-        a = alive[t];
-        wk = wl[t];
-        ls = slot - pre[t];
-      }
+    for (int d = NMS_MW / 2; d; d >>= 1)
+      if (sm.mw_pre[k + d] <= slot) k += d;
+    const uint64_t a = sm.mw_alive[k];
+    const int ls = slot - sm.mw_pre[k];
     const uint32_t lo = (uint32_t)a, hi = (uint32_t)(a >> 32);
     const int cl = __popc(lo);
     const int jj = ls < cl ? (int)__fns(lo, 0, ls + 1) : 32 + (int)__fns(hi, 0, ls - cl + 1);
-    const int j = wk * 64 + jj;
+    const int j = (w_first + k * w_step) * 64 + jj;
     const NmsBox q = p.sboxes[off + j];
     const float qarea = p.sarea[off + j];
     float qlabel = 0.f;
@@ -371,20 +382,11 @@ __device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, co
       if (LABELS) sup = sup && (sm.kl[i] == qlabel);
       hit = sup;
     }
-    if (hit) atomicOr(&sm.s_new4[k], 1ull << jj);
+    if (hit) atomicOr(&sm.mw_new[k], 1ull << jj);
   }
   __syncthreads();
-  if (tid < nw && sm.s_new4[tid]) {
-    uint64_t wv = word[0];
-    int wk = wl[0];
-#pragma unroll
-    for (int t = 1; t < 4; ++t)
-      if (tid == t) {
-        wv = word[t];
-        wk = wl[t];
-      }
-    p.removed[(size_t)seg * p.wmax + wk] = wv | sm.s_new4[tid];
-  }
+  if (tid < nw && sm.mw_new[tid])
+    p.removed[(size_t)seg * p.wmax + w_first + tid * w_step] = sm.mw_word[tid] | sm.mw_new[tid];
 }
 
 template <bool GE, bool LABELS>
@@ -576,19 +578,29 @@ union NmsFusedSmem {
   NmsSupSmem sup;
 };
 
+// CTA c works for problem c % B (B <= grid) as member c / B of that problem's group, or for the
+// problems c, c + grid, ... alone: a CTA keeps one kept list in shared memory per step.
 template <bool GE, bool LABELS>
 __global__ void __launch_bounds__(NMS_BAND_MAX)
 nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* __restrict__ keep,
                  uint8_t* __restrict__ flags, int* __restrict__ n_keep, unsigned* __restrict__ bar) {
   __shared__ NmsFusedSmem sm;
-  const unsigned G = gridDim.x;
+  const int G = (int)gridDim.x, c = (int)blockIdx.x;
   unsigned phase = 0;
   const int ndiag = p.bw * (p.bw + 1) / 2;
+  const bool grouped = B <= G;
+  const int seg0 = grouped ? c % B : c;
+  const int seg_step = grouped ? B : G;            // (grouped: the loop below runs once)
+  const int rnk = grouped ? c / B : 0;             // member of the problem's group
+  const int cnt = grouped ? (G - seg0 + B - 1) / B : 1;
   // diagonal block of band 0
-  for (int it = blockIdx.x; it < B * ndiag; it += G) {
-    const int seg = it / ndiag;
-    nms_diag_part<GE, LABELS>(p, seg, 0, it - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl, sm.sup.wordS);
-    __syncthreads();
+  for (int seg = seg0; seg < B; seg += seg_step) {
+    for (int t = rnk; t < ndiag; t += 4 * cnt) {
+      nms_diag_tiles<GE, LABELS>(p, seg, 0, t, cnt, (ndiag - t + cnt - 1) / cnt, sm.sup.kb, sm.sup.ka,
+                                 sm.sup.kl, sm.sup.wordS);
+      __syncthreads();
+    }
+    if (grouped) break;
   }
   nms_grid_barrier(bar, ++phase * G);
   for (int b = 0; b < bands; ++b) {
@@ -597,26 +609,50 @@ nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* 
     __syncthreads();
 #endif
     NMS_STAMP(0);
-    for (int seg = blockIdx.x; seg < B; seg += G) {
+    for (int seg = c; seg < B; seg += G) {
       nms_resolve_body(p, seg, b, max_keep, ascending, keep, flags, sm.res, NmsNoWait());
       __syncthreads();
-      if (b + 1 == bands && !ascending && threadIdx.x == 0) n_keep[seg] = p.count[seg];
     }
     if (b + 1 == bands) break;
     NMS_STAMP(1);
     nms_grid_barrier(bar, ++phase * G);
     NMS_STAMP(2);
-    const int nsup = p.wmax - (b + 1) * p.bw;
-    const int per = nsup + ndiag;
-    int cached = -1;  // the resolve step of this CTA (if any) used the shared memory
-    for (int it = blockIdx.x; it < B * per; it += G) {
-      const int seg = it / per;
-      nms_suppress_body<GE, LABELS>(p, seg, b, it - seg * per, nsup, sm.sup, cached);
-      __syncthreads();
+    {
+      // all problems capped or out of boxes: nothing left to do (the flags are stable until the
+      // next resolve step, so the whole grid takes this exit together)
+      int open_problems = 0;
+      for (int seg = (int)threadIdx.x; seg < B; seg += (int)blockDim.x) {
+        const int n = p.offsets[seg + 1] - p.offsets[seg];
+        if (!p.done[seg] && (b + 1) * p.BR < n) open_problems = 1;
+      }
+      if (!__syncthreads_or(open_problems)) break;
+    }
+    const int w0 = (b + 1) * p.bw;
+    for (int seg = seg0; seg < B; seg += seg_step) {
+      for (int t = rnk; t < ndiag; t += 4 * cnt) {
+        nms_diag_tiles<GE, LABELS>(p, seg, b + 1, t, cnt, (ndiag - t + cnt - 1) / cnt, sm.sup.kb,
+                                   sm.sup.ka, sm.sup.kl, sm.sup.wordS);
+        __syncthreads();
+      }
+      if (!p.done[seg]) {
+        int cached = -1;  // the tiles used the kept-list buffers
+        for (int w = w0 + rnk; w < p.wmax; w += cnt * NMS_MW) {
+          int nw = (p.wmax - w + cnt - 1) / cnt;
+          if (nw > NMS_MW) nw = NMS_MW;
+          nms_suppress_multi<GE, LABELS>(p, seg, w, cnt, nw, sm.sup, cached);
+          __syncthreads();
+        }
+      }
+      if (grouped) break;
     }
     NMS_STAMP(3);
     nms_grid_barrier(bar, ++phase * G);
     NMS_STAMP(4);
+  }
+  if (!ascending) {
+    __syncthreads();
+    for (int seg = c; seg < B; seg += G)
+      if (threadIdx.x == 0) n_keep[seg] = p.count[seg];
   }
 }
 
@@ -721,7 +757,7 @@ nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascend
     q.D = f.D[0];
     for (int it = blockIdx.x; it < B * ndiag; it += G) {
       const int seg = it / ndiag;
-      nms_diag_part<GE, LABELS>(q, seg, 0, it - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl, sm.sup.wordS);
+      nms_diag_tiles<GE, LABELS>(q, seg, 0, it - seg * ndiag, 1, 1, sm.sup.kb, sm.sup.ka, sm.sup.kl, sm.sup.wordS);
       nms_signal_add(&f.Dc[0][seg]);
     }
     __syncthreads();
@@ -777,8 +813,8 @@ nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascend
           capped_mask |= 1u << seg;
           continue;
         }
-        nms_diag_part<GE, LABELS>(q, seg, b + 1, gt - seg * ndiag, sm.sup.kb, sm.sup.ka, sm.sup.kl,
-                                  sm.sup.wordS);
+        nms_diag_tiles<GE, LABELS>(q, seg, b + 1, gt - seg * ndiag, 1, 1, sm.sup.kb, sm.sup.ka, sm.sup.kl,
+                                   sm.sup.wordS);
         nms_signal_add(&f.Dc[(b + 1) & 1][seg]);
       }
       __syncthreads();
@@ -799,16 +835,16 @@ nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascend
         const int r = (int)(((long long)seg * p.wmax + lo) % NW);
         int w = lo + (v - r + NW) % NW;
         while (w < hi) {
-          int wl[4] = {0, 0, 0, 0};
-          int nw = 0;
-          for (; nw < 4 && w < hi; ++nw, w += NW) wl[nw] = w;
+          int nw = (hi - w + NW - 1) / NW;
+          if (nw > NMS_MW) nw = NMS_MW;
           const unsigned rv = nms_wait_ge_value(&f.R[seg], (unsigned)(b + 1), &sm.sup.bcast);
           if (rv > (unsigned)bands) {  // cap reached: nobody will read these words again
             capped_mask |= 1u << seg;
             break;
           }
-          nms_suppress_multi<GE, LABELS>(q, seg, wl, nw, sm.sup, cached);
+          nms_suppress_multi<GE, LABELS>(q, seg, w, NW, nw, sm.sup, cached);
           nms_signal_add2(&f.Uc[seg], sweep == 0 ? (unsigned)nw : 0u, &f.Fc[par][seg], (unsigned)nw);
+          w += nw * NW;
         }
       }
     }
@@ -971,7 +1007,10 @@ int nms_run_bands(const NmsBand& p, const NmsWorkspace& w, int B, int n_max, int
   const int ndiag = p.bw * (p.bw + 1) / 2;  // lower-triangle tiles of a diagonal block
   const int slot = (GE ? 1 : 0) + (LABELS ? 2 : 0);
   *need_finish = 1;
-  if (bands >= 2 && B <= NMS_FLOW_MAXB && rp_env_int("RP_NMS_FUSED", 1) && rp_env_int("RP_NMS_FLOW", 1)) {
+  // dataflow kernel: latency-bound shapes (few words per band step in all); else grid barriers
+  const int flow_words = rp_env_int("RP_NMS_FLOW_WORDS", 400);
+  if (bands >= 2 && B <= NMS_FLOW_MAXB && (long long)B * p.wmax <= flow_words &&
+      rp_env_int("RP_NMS_FUSED", 1) && rp_env_int("RP_NMS_FLOW", 1)) {
     const int cap = nms_coop_capacity((const void*)nms_flow_kernel<GE, LABELS>, 4 + slot);
     if (cap >= B + 64) {
       NmsBand pc = p;
@@ -1023,7 +1062,7 @@ int nms_run_bands(const NmsBand& p, const NmsWorkspace& w, int B, int n_max, int
     if (b + 1 < bands) {
       const int nsup = p.wmax - (b + 1) * p.bw;
       nms_suppress_kernel<GE, LABELS>
-          <<<dim3((unsigned)(nsup + ndiag), (unsigned)B), NMS_SUP_THREADS, 0, st>>>(p, b, nsup);
+          <<<dim3((unsigned)(nsup + (ndiag + 3) / 4), (unsigned)B), NMS_SUP_THREADS, 0, st>>>(p, b, nsup);
       RP_LAUNCH_CHECK();
     }
   }

@@ -193,11 +193,19 @@ def _chain_boxes(n, step):
     return b, s
 
 
-@pytest.mark.parametrize("fused", ["1", "0"])
-def test_one_launch_and_per_band_launch_paths(monkeypatch, fused):
-    # RP_NMS_FUSED=1 (default): all bands in one cooperative launch with grid barriers;
-    # RP_NMS_FUSED=0: one resolve + one suppress launch per band.  Same results, bit for bit.
-    monkeypatch.setenv("RP_NMS_FUSED", fused)
+_NMS_MODES = {
+    "default": {},                                        # dataflow kernel for few words, else grid barriers
+    "dataflow": {"RP_NMS_FLOW_WORDS": "1000000"},         # dataflow kernel for every batch of <= 16 problems
+    "barriers": {"RP_NMS_FLOW": "0"},                     # one cooperative launch, grid barriers
+    "launches": {"RP_NMS_FUSED": "0"},                    # one resolve + one suppress launch per band
+}
+
+
+@pytest.mark.parametrize("mode", sorted(_NMS_MODES))
+def test_one_launch_and_per_band_launch_paths(monkeypatch, mode):
+    # The band loop has three drivers; all must give the oracle's keeps, bit for bit.
+    for k, v in _NMS_MODES[mode].items():
+        monkeypatch.setenv(k, v)
     rp.reload_env()
     try:
         b, s, _ = synth.nms_boxes(5000, 11, tie_heavy=True)
@@ -224,6 +232,14 @@ def test_one_launch_and_per_band_launch_paths(monkeypatch, fused):
             np.testing.assert_array_equal(keep, oracle.nms(cb, cs, thr))
         dets = np.concatenate([cb, cs[:, None]], 1)
         np.testing.assert_array_equal(rp.cython_nms(T(dets), 0.5).cpu().numpy(), oracle.cython_nms(dets, 0.5))
+        # 20 problems (more than the dataflow kernel takes), two bands each
+        bs, ss = zip(*[synth.nms_boxes(1500, 90 + i)[:2] for i in range(20)])
+        offs = (np.arange(21) * 1500).astype(np.int32)
+        keep, nk = rp.nms_batched(T(np.concatenate(bs)), T(np.concatenate(ss)), T(offs), 0.6, n_max=1500)
+        keep, nk = keep.cpu().numpy(), nk.cpu().numpy()
+        for i in (0, 7, 19):
+            np.testing.assert_array_equal(keep[offs[i]: offs[i] + nk[i]], oracle.nms(bs[i], ss[i], 0.6))
     finally:
-        monkeypatch.delenv("RP_NMS_FUSED")
+        for k in _NMS_MODES[mode]:
+            monkeypatch.delenv(k)
         rp.reload_env()

@@ -45,3 +45,22 @@ for n in (2000, 5000, 20000):
         print("n=%d max_keep=%d kept=%d  median %.4f ms  min %.4f ms" % (n, mk, int(nk[0]), float(np.median(ts)), min(ts)))
         if n >= 5000:
             stamps()
+
+# batch of 8 images (BASELINE configs[1]): ms per image
+for n in (5000, 20000):
+    bs, ss = zip(*[synth.nms_boxes(n, 7 + i)[:2] for i in range(8)])
+    b8 = torch.from_numpy(np.concatenate(bs)).to(dev)
+    s8 = torch.from_numpy(np.concatenate(ss)).to(dev)
+    o8 = torch.from_numpy((np.arange(9) * n).astype(np.int32)).to(dev)
+    for mk in (-1, 1000):
+        for _ in range(3):
+            rp.nms_batched(b8, s8, o8, 0.7, max_keep=mk, n_max=n)
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rp.nms_batched(b8, s8, o8, 0.7, max_keep=mk, n_max=n)
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        print("batch 8 x n=%d max_keep=%d  median %.4f ms = %.4f ms/image" % (n, mk, float(np.median(ts)), float(np.median(ts)) / 8))
