@@ -314,14 +314,20 @@ __device__ __forceinline__ void nms_suppress_body(const NmsBand& p, int seg, int
 // Up to NMS_MW words (w_first, w_first + w_step, ...) of ONE problem in one pass: the alive boxes of
 // all words are compacted together and share the 1024 threads, P = 1024 / alive threads per box (at
 // most 64), which split the kept list between them.  One set of round trips per pass instead of per
-// word.  Does not look at done[seg] (in the dataflow kernel the resolver may be writing it).
-template <bool GE, bool LABELS>
-__device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, int w_first, int w_step,
-                                                   int nw, NmsSupSmem& sm, int& cached) {
+// word.  Everything that does not depend on the kept list of the current band -- the words, the
+// compaction, the candidates' own boxes -- is fetched BEFORE `wait()` (dataflow kernel: the resolver
+// may still be running); wait() returns true when the problem needs no further work (CTA-uniform).
+// Does not look at done[seg] itself.  Returns wait()'s verdict.
+struct NmsGoOn {
+  __device__ __forceinline__ bool operator()() const { return false; }
+};
+
+template <bool GE, bool LABELS, class Wait>
+__device__ __forceinline__ bool nms_suppress_multi(const NmsBand& p, int seg, int w_first, int w_step,
+                                                   int nw, NmsSupSmem& sm, int& cached, const Wait& wait) {
   const int tid = threadIdx.x;
   const int off = p.offsets[seg];
   const int n = p.offsets[seg + 1] - off;
-  const int kc = p.kcount[seg];
   if (tid < 32) {
     uint64_t word = 0ull, alive = 0ull;
     const int wk = w_first + tid * w_step;
@@ -345,24 +351,15 @@ __device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, in
     if (tid == 0) sm.mw_pre[0] = 0;
   }
   __syncthreads();
-  const int na = sm.mw_pre[NMS_MW];
-  if (kc == 0 || na == 0) return;
-  if (cached != seg) {
-    for (int i = tid; i < kc; i += NMS_SUP_THREADS) {
-      sm.kb[i] = p.kbox[(size_t)seg * p.BR + i];
-      sm.ka[i] = p.karea[(size_t)seg * p.BR + i];
-      if (LABELS) sm.kl[i] = p.klabel[(size_t)seg * p.BR + i];
-    }
-    cached = seg;
-    __syncthreads();
-  }
+  const int na = sm.mw_pre[NMS_MW];  // <= 1024: 16 words x 64 boxes
+  if (na == 0) return false;
   int P = NMS_SUP_THREADS / na;
   if (P > 64) P = 64;
-  if (P < 1) P = 1;
-  // na > 1024 (16 words, all alive) cannot happen: 16 x 64 = 1024 boxes at most
   const int slot = tid / P, part = tid - slot * P;
+  int k = 0, jj = 0;
+  NmsBox q{0.f, 0.f, 0.f, 0.f};
+  float qarea = 0.f, qlabel = 0.f;
   if (slot < na) {
-    int k = 0;
 #pragma unroll
     for (int d = NMS_MW / 2; d; d >>= 1)
       if (sm.mw_pre[k + d] <= slot) k += d;
@@ -370,12 +367,25 @@ __device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, in
     const int ls = slot - sm.mw_pre[k];
     const uint32_t lo = (uint32_t)a, hi = (uint32_t)(a >> 32);
     const int cl = __popc(lo);
-    const int jj = ls < cl ? (int)__fns(lo, 0, ls + 1) : 32 + (int)__fns(hi, 0, ls - cl + 1);
+    jj = ls < cl ? (int)__fns(lo, 0, ls + 1) : 32 + (int)__fns(hi, 0, ls - cl + 1);
     const int j = (w_first + k * w_step) * 64 + jj;
-    const NmsBox q = p.sboxes[off + j];
-    const float qarea = p.sarea[off + j];
-    float qlabel = 0.f;
+    q = p.sboxes[off + j];
+    qarea = p.sarea[off + j];
     if (LABELS) qlabel = p.slabel[off + j];
+  }
+  if (wait()) return true;
+  const int kc = p.kcount[seg];
+  if (cached != seg) {
+    // the whole buffer, without waiting for kc (entries past kc are never read)
+    for (int i = tid; i < p.BR; i += NMS_SUP_THREADS) {
+      sm.kb[i] = p.kbox[(size_t)seg * p.BR + i];
+      sm.ka[i] = p.karea[(size_t)seg * p.BR + i];
+      if (LABELS) sm.kl[i] = p.klabel[(size_t)seg * p.BR + i];
+    }
+    cached = seg;
+    __syncthreads();
+  }
+  if (slot < na) {
     bool hit = false;
     for (int i = part; i < kc && !hit; i += P) {
       bool sup = nms_pair<GE>(sm.kb[i], sm.ka[i], q, qarea, p.t_cmp, p.t_lo);
@@ -387,6 +397,7 @@ __device__ __forceinline__ void nms_suppress_multi(const NmsBand& p, int seg, in
   __syncthreads();
   if (tid < nw && sm.mw_new[tid])
     p.removed[(size_t)seg * p.wmax + w_first + tid * w_step] = sm.mw_word[tid] | sm.mw_new[tid];
+  return false;
 }
 
 template <bool GE, bool LABELS>
@@ -406,10 +417,13 @@ nms_suppress_kernel(NmsBand p, int band, int nsup) {
 // the longest alternating chain of overlaps in the band (a handful), not the number of kept boxes.
 // The greedy result is unique, so this is the reference's sequential loop (det/layers/nms.py:13-45).
 constexpr int NMS_RES_WORDS = NMS_BAND_MAX / 64;
+constexpr int NMS_RES_COMPACT = 256;  // undecided boxes at which the rounds switch to a compacted set
 struct NmsResSmem {
   __align__(8) uint32_t keptS[2][NMS_BAND_MAX / 32];
   __align__(8) uint32_t undecS[2][NMS_BAND_MAX / 32];
   int wsum[NMS_BAND_MAX / 32];
+  uint64_t rows[NMS_RES_WORDS][NMS_RES_COMPACT];  // diagonal rows of the compacted boxes, word-major
+  short ids[NMS_RES_COMPACT];
 };
 
 // blockDim >= BR, a multiple of 32 (threads past the band idle along)
@@ -420,8 +434,9 @@ struct NmsNoWait {
 // `wait` (called by the whole CTA) returns once the removed bits of this band are final; everything
 // before it -- the diagonal rows, the boxes' own records -- is fetched while the suppress step of the
 // previous band may still be running (one-launch dataflow kernel)
+// Returns (CTA-uniform) whether the keep cap of the problem has been reached.
 template <class Wait>
-__device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int band, int max_keep,
+__device__ __forceinline__ bool nms_resolve_body(const NmsBand& p, int seg, int band, int max_keep,
                                                  int ascending, int* __restrict__ keep,
                                                  uint8_t* __restrict__ flags, NmsResSmem& sm,
                                                  const Wait& wait) {
@@ -437,7 +452,7 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
   const int base = band * p.BR;
   if (done || base >= n) {  // (the dataflow kernel never gets here: its resolver stops first)
     if (tid == 0) p.kcount[seg] = 0;
-    return;
+    return done != 0;
   }
   const int rows = min(p.BR, n - base);
   const int lane = tid & 31, warp = tid >> 5;
@@ -462,7 +477,7 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
   }
   NMS_STAMP(10);
   wait();
-  bool my_undec = false, my_kept = false;
+  bool my_undec = false;
   if (live) {
     const uint64_t rem = p.removed[(size_t)seg * p.wmax + band * p.bw + cj];
     my_undec = !((rem >> (tid & 63)) & 1ull);
@@ -476,7 +491,12 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
   }
   __syncthreads();
   NMS_STAMP(11);
+  // Rounds over all boxes (thread = box, double-buffered bit sets written by ballots) until at most
+  // NMS_RES_COMPACT boxes are undecided; then those boxes (typically a quarter of the band after the
+  // first round, scattered over all warps) are moved to the first threads, diagonal rows and all, and
+  // the remaining rounds keep only a few warps busy (bit sets updated with shared atomics).
   int cur = 0;
+  int left;
   for (int round = 0;; ++round) {
     const unsigned ub = undecS[cur][warp];
     bool nk = false, ns = false;
@@ -504,15 +524,83 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
     }
     const unsigned bk = __ballot_sync(0xffffffffu, nk);
     const unsigned bs = __ballot_sync(0xffffffffu, ns);
-    if (nk) my_kept = true;
     if (nk || ns) my_undec = false;
     const unsigned nub = ub & ~(bk | bs);
     if (lane == 0) {
       keptS[cur ^ 1][warp] = keptS[cur][warp] | bk;
       undecS[cur ^ 1][warp] = nub;
+      wsum[warp] = __popc(nub);
     }
     cur ^= 1;
-    if (!__syncthreads_or(nub != 0u)) break;
+    left = __syncthreads_count(my_undec);
+    if (left <= NMS_RES_COMPACT) break;
+  }
+  NMS_STAMP(13);
+#ifdef NMS_PROFILE
+  if (nms_prof_on && blockIdx.x == 0 && threadIdx.x == 0) nms_prof[20] = left;
+#endif
+  if (left > 0) {
+    // compaction: slot = rank of the box among the undecided ones
+    {
+      const unsigned ub = undecS[cur][warp];
+      const int nwarps_ = blockDim.x >> 5;
+      const int wc = lane < nwarps_ ? wsum[lane] : 0;
+      const int before = (int)__reduce_add_sync(0xffffffffu, (unsigned)(lane < warp ? wc : 0));
+      if (my_undec) {
+        const int sl = before + __popc(ub & ((1u << lane) - 1u));
+        sm.ids[sl] = (short)tid;
+#pragma unroll
+        for (int w = 0; w < NMS_RES_WORDS; ++w) sm.rows[w][sl] = T[w];
+      }
+    }
+    __syncthreads();
+    const bool mine = tid < left;
+    int myj = 0;
+    unsigned nzw = 0u;  // words of the box's row that have any bit: a handful of the 16
+    if (mine) {
+      myj = sm.ids[tid];
+#pragma unroll
+      for (int w = 0; w < NMS_RES_WORDS; ++w) nzw |= (sm.rows[w][tid] != 0ull) ? (1u << w) : 0u;
+    }
+    my_undec = mine;
+    NMS_STAMP(14);
+    const uint64_t* k64 = reinterpret_cast<const uint64_t*>(keptS[cur]);
+    const uint64_t* u64 = reinterpret_cast<const uint64_t*>(undecS[cur]);
+    if (warp * 32 < left) {
+      // only the warps that hold compacted boxes take part: named barrier 1 over those threads.
+      // Few warps run here, so a round costs its instruction count: rows are read back from shared
+      // memory word by word, non-empty words only.
+      const unsigned nthr = (unsigned)((left + 31) & ~31);
+      for (;;) {
+        bool nk = false, ns = false;
+        if (my_undec) {
+          uint64_t supd = 0ull, potd = 0ull;
+          for (unsigned m = nzw; m; m &= m - 1u) {
+            const int w = __ffs(m) - 1;
+            const uint64_t t = sm.rows[w][tid];
+            supd |= t & k64[w];
+            potd |= t & u64[w];
+          }
+          ns = supd != 0ull;
+          nk = !ns && potd == 0ull;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");  // every box has read this round's sets
+        if (nk) atomicOr(&keptS[cur][myj >> 5], 1u << (myj & 31));
+        if (nk || ns) {
+          atomicAnd(&undecS[cur][myj >> 5], ~(1u << (myj & 31)));
+          my_undec = false;
+        }
+        unsigned more;
+        asm volatile(
+            "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\tbar.red.or.pred q, 1, %2, p;\n\t"
+            "selp.u32 %0, 1, 0, q;\n\t}"
+            : "=r"(more)
+            : "r"((unsigned)my_undec), "r"(nthr)
+            : "memory");
+        if (!more) break;
+      }
+    }
+    __syncthreads();
   }
   NMS_STAMP(12);
   // positions in rank order, the max_keep cap, outputs
@@ -530,7 +618,7 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
     p.count[seg] = count0 + total;
     if (max_keep > 0 && count0 + total >= max_keep) p.done[seg] = 1;
   }
-  if (my_kept) {
+  if ((kb >> lane) & 1u) {
     const int pos = before + __popc(kb & ((1u << lane) - 1u));
     if (pos < allowed) {
       if (ascending)
@@ -542,6 +630,7 @@ __device__ __forceinline__ void nms_resolve_body(const NmsBand& p, int seg, int 
       if (p.slabel) p.klabel[(size_t)seg * p.BR + pos] = my_label;
     }
   }
+  return max_keep > 0 && count0 + total >= max_keep;
 }
 
 __global__ void __launch_bounds__(NMS_BAND_MAX)
@@ -639,7 +728,7 @@ nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* 
         for (int w = w0 + rnk; w < p.wmax; w += cnt * NMS_MW) {
           int nw = (p.wmax - w + cnt - 1) / cnt;
           if (nw > NMS_MW) nw = NMS_MW;
-          nms_suppress_multi<GE, LABELS>(p, seg, w, cnt, nw, sm.sup, cached);
+          (void)nms_suppress_multi<GE, LABELS>(p, seg, w, cnt, nw, sm.sup, cached, NmsGoOn());
           __syncthreads();
         }
       }
@@ -735,6 +824,16 @@ __device__ __forceinline__ void nms_signal_max(unsigned* ctr, unsigned v) {
   }
 }
 
+// worker side: the kept list of the band is ready; true = the problem has reached its keep cap
+struct NmsFlowWaitR {
+  const unsigned* r;
+  unsigned target, bands;
+  unsigned* slot;
+  __device__ __forceinline__ bool operator()() const {
+    return nms_wait_ge_value(r, target, slot) > bands;
+  }
+};
+
 struct NmsFlowWait {
   const unsigned *uc, *fc;
   unsigned ut, ft;
@@ -782,13 +881,12 @@ nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascend
       nms_wait_ge(&f.Dc[par][seg], (unsigned)((b / 2 + 1) * ndiag));
       NmsFlowWait wait{&f.Uc[seg], &f.Fc[par][seg], ut, fsum[par], b};
       NMS_STAMP(0);
-      nms_resolve_body(q, seg, b, max_keep, ascending, keep, flags, sm.res, wait);
-      __syncthreads();
+      const bool capped = nms_resolve_body(q, seg, b, max_keep, ascending, keep, flags, sm.res, wait);
       NMS_STAMP(1);
-      const bool capped = p.done[seg] != 0;
       const bool last = (b + 1 == bands) || capped || (b + 1) * p.BR >= n;
       // R = bands: all bands resolved; bands + 1: the keep cap was reached, later steps are void
       nms_signal_max(&f.R[seg], (unsigned)(capped ? bands + 1 : (last ? bands : b + 1)));
+      NMS_STAMP(5);
       if (last) break;
       const int items = p.wmax - (b + 1) * p.bw;  // word items of step b (> 0: the problem goes on)
       ut += (unsigned)(items < p.bw ? items : p.bw);
@@ -837,12 +935,11 @@ nms_flow_kernel(NmsBand p, NmsFlow f, int B, int bands, int max_keep, int ascend
         while (w < hi) {
           int nw = (hi - w + NW - 1) / NW;
           if (nw > NMS_MW) nw = NMS_MW;
-          const unsigned rv = nms_wait_ge_value(&f.R[seg], (unsigned)(b + 1), &sm.sup.bcast);
-          if (rv > (unsigned)bands) {  // cap reached: nobody will read these words again
-            capped_mask |= 1u << seg;
+          NmsFlowWaitR waitR{&f.R[seg], (unsigned)(b + 1), (unsigned)bands, &sm.sup.bcast};
+          if (nms_suppress_multi<GE, LABELS>(q, seg, w, NW, nw, sm.sup, cached, waitR)) {
+            capped_mask |= 1u << seg;  // cap reached: nobody will read these words again
             break;
           }
-          nms_suppress_multi<GE, LABELS>(q, seg, w, NW, nw, sm.sup, cached);
           nms_signal_add2(&f.Uc[seg], sweep == 0 ? (unsigned)nw : 0u, &f.Fc[par][seg], (unsigned)nw);
           w += nw * NW;
         }

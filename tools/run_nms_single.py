@@ -21,8 +21,10 @@ def stamps():
     torch.cuda.synchronize()
     h.rp_debug_nms_prof(buf)
     v = list(buf)
-    print("   band 3, CTA 0: resolve %d (prologue %d, load %d, fixpoint %d, emit %d)  barrier %d  suppress %d  barrier %d cycles"
-          % (v[1] - v[0], v[10] - v[0], v[11] - v[10], v[12] - v[11], v[1] - v[12], v[2] - v[1], v[3] - v[2], v[4] - v[3]))
+    print("   band 3, CTA 0: resolve %d (prologue %d, wait+load %d, fixpoint %d, emit %d)  then: barrier %d  suppress %d  barrier %d | signal %d cycles"
+          % (v[1] - v[0], v[10] - v[0], v[11] - v[10], v[12] - v[11], v[1] - v[12], v[2] - v[1], v[3] - v[2], v[4] - v[3], v[5] - v[1]))
+    print("      fixpoint: all-box rounds %d, compaction %d, compact rounds %d cycles; %d boxes compacted"
+          % (v[13] - v[11], v[14] - v[13], v[12] - v[14], v[20]))
 
 
 dev = torch.device("cuda:0")
