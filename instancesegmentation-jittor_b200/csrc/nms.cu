@@ -223,6 +223,16 @@ __device__ __forceinline__ void nms_diag_tiles(const NmsBand& p, int seg, int ba
     p.D[((size_t)seg * p.bw + cb) * p.BR + rb * 64 + tid] = wordS[tid];
 }
 
+// tiles of the diagonal block of `band` that hold any box of problem seg (tiles are numbered row block
+// by row block, so these are the first ones)
+__device__ __forceinline__ int nms_tiles_needed(const NmsBand& p, int seg, int band) {
+  const int n = p.offsets[seg + 1] - p.offsets[seg];
+  const int rows = min(p.BR, n - band * p.BR);
+  if (rows <= 0) return 0;
+  const int nrb = (rows + 63) >> 6;
+  return nrb * (nrb + 1) / 2;
+}
+
 template <bool GE, bool LABELS>
 __global__ void __launch_bounds__(256)
 nms_diag_kernel(NmsBand p, int band) {
@@ -684,8 +694,9 @@ nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* 
   const int cnt = grouped ? (G - seg0 + B - 1) / B : 1;
   // diagonal block of band 0
   for (int seg = seg0; seg < B; seg += seg_step) {
-    for (int t = rnk; t < ndiag; t += 4 * cnt) {
-      nms_diag_tiles<GE, LABELS>(p, seg, 0, t, cnt, (ndiag - t + cnt - 1) / cnt, sm.sup.kb, sm.sup.ka,
+    const int nt = nms_tiles_needed(p, seg, 0);
+    for (int t = rnk; t < nt; t += 4 * cnt) {
+      nms_diag_tiles<GE, LABELS>(p, seg, 0, t, cnt, (nt - t + cnt - 1) / cnt, sm.sup.kb, sm.sup.ka,
                                  sm.sup.kl, sm.sup.wordS);
       __syncthreads();
     }
@@ -718,15 +729,18 @@ nms_bands_kernel(NmsBand p, int B, int bands, int max_keep, int ascending, int* 
     }
     const int w0 = (b + 1) * p.bw;
     for (int seg = seg0; seg < B; seg += seg_step) {
-      for (int t = rnk; t < ndiag; t += 4 * cnt) {
-        nms_diag_tiles<GE, LABELS>(p, seg, b + 1, t, cnt, (ndiag - t + cnt - 1) / cnt, sm.sup.kb,
+      const int nt = p.done[seg] ? 0 : nms_tiles_needed(p, seg, b + 1);
+      for (int t = rnk; t < nt; t += 4 * cnt) {
+        nms_diag_tiles<GE, LABELS>(p, seg, b + 1, t, cnt, (nt - t + cnt - 1) / cnt, sm.sup.kb,
                                    sm.sup.ka, sm.sup.kl, sm.sup.wordS);
         __syncthreads();
       }
       if (!p.done[seg]) {
         int cached = -1;  // the tiles used the kept-list buffers
-        for (int w = w0 + rnk; w < p.wmax; w += cnt * NMS_MW) {
-          int nw = (p.wmax - w + cnt - 1) / cnt;
+        const int n_seg = p.offsets[seg + 1] - p.offsets[seg];
+        const int wlim = min(p.wmax, (n_seg + 63) >> 6);  // the problem's own words
+        for (int w = w0 + rnk; w < wlim; w += cnt * NMS_MW) {
+          int nw = (wlim - w + cnt - 1) / cnt;
           if (nw > NMS_MW) nw = NMS_MW;
           (void)nms_suppress_multi<GE, LABELS>(p, seg, w, cnt, nw, sm.sup, cached, NmsGoOn());
           __syncthreads();
