@@ -158,7 +158,8 @@ def local_times(rp, torch, dev, rank, world, images_per_gpu):
 
     def rpn_device():
         bx_, sc_, _, off_, ks = rp.rpn_pre_nms_levels(objs, regs, ancs, wh, 1000, 0.0)
-        kp_, nk_ = rp.nms_batched(bx_, sc_, off_, 0.7, max_keep=1000, n_max=max(ks))
+        kp_, nk_ = rp.nms_batched(bx_, sc_, off_, 0.7, max_keep=1000, n_max=max(ks),
+                                  flags=rp.package._lib.RP_NMS_PRESORTED)  # as RPNPostProcessor._launch does
         rp.rpn_select_levels(bx_, sc_, off_, kp_, nk_, len(lv), N, 1000)
 
     ms["rpn_post_device"] = med(rpn_device)

@@ -131,11 +131,17 @@ RP_API int rp_pooler_forward_nhwc(const float* const* feats, const int* H, const
  *        RP_NMS_ASCENDING        return each keep list sorted by ascending index (:74)
  *        RP_NMS_TIES_HIGH_FIRST  equal scores: higher index first (argsort()[::-1], :35)
  *        RP_NMS_CYTHON           all three: the yol/utils/cython_nms.pyx contract
+ *        RP_NMS_PRESORTED        the caller guarantees that the scores of every problem are
+ *                                non-increasing (the stable argsort is then the identity and is
+ *                                skipped: rp_rpn_pre_nms emits its candidates in that order).
+ *                                Not with RP_NMS_TIES_HIGH_FIRST.  An input that breaks the promise
+ *                                is processed in the given order (greedy NMS in input order).
  * ------------------------------------------------------------------------------------ */
 #define RP_NMS_GE 1
 #define RP_NMS_ASCENDING 2
 #define RP_NMS_TIES_HIGH_FIRST 4
 #define RP_NMS_CYTHON (RP_NMS_GE | RP_NMS_ASCENDING | RP_NMS_TIES_HIGH_FIRST)
+#define RP_NMS_PRESORTED 8
 
 RP_API size_t rp_nms_workspace_bytes(int n_total, int n_max, int B);
 

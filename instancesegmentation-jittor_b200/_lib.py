@@ -16,6 +16,7 @@ RP_NMS_GE = 1
 RP_NMS_ASCENDING = 2
 RP_NMS_TIES_HIGH_FIRST = 4
 RP_NMS_CYTHON = RP_NMS_GE | RP_NMS_ASCENDING | RP_NMS_TIES_HIGH_FIRST
+RP_NMS_PRESORTED = 8
 
 _c = ctypes
 _vp, _i, _f, _d, _sz = _c.c_void_p, _c.c_int, _c.c_float, _c.c_double, _c.c_size_t

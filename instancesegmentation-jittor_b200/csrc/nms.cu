@@ -76,6 +76,14 @@ __global__ void nms_keys_kernel(const float* __restrict__ scores, const int* __r
   vals[p] = e;
 }
 
+// RP_NMS_PRESORTED: rank order = input order; also clears the scan state
+__global__ void nms_iota_kernel(int n_total, int* __restrict__ vals, uint64_t* __restrict__ zero8,
+                                int n_zero8) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < n_zero8) zero8[p] = 0ull;
+  if (p < n_total) vals[p] = p;
+}
+
 struct __align__(16) NmsBox {
   float x1, y1, x2, y2;
 };
@@ -1222,19 +1230,26 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
   const int T = 256;
   const int nb = (n_total + T - 1) / T;
   const bool zero_in_keys = (w.zero_bytes % 8 == 0) && (w.zero_bytes / 8 <= (size_t)nb * T);
-  nms_keys_kernel<<<nb, T, 0, st>>>(scores, offsets, B, n_total,
-                                    (flags & RP_NMS_TIES_HIGH_FIRST) ? 1 : 0, w.keys_in, w.vals_in,
-                                    reinterpret_cast<uint64_t*>(w.zero_begin),
-                                    zero_in_keys ? (int)(w.zero_bytes / 8) : 0);
-  RP_LAUNCH_CHECK();
-  int seg_bits = 0;  // one problem: its rows and the slack rows differ in the low word already
-  if (B > 1) {
-    seg_bits = 1;
-    while ((1 << seg_bits) < B + 1) ++seg_bits;  // B problems + the slack id B
+  if (flags & RP_NMS_PRESORTED) {
+    if (flags & RP_NMS_TIES_HIGH_FIRST) return RP_E_ARG;
+    nms_iota_kernel<<<nb, T, 0, st>>>(n_total, w.vals_out, reinterpret_cast<uint64_t*>(w.zero_begin),
+                                      zero_in_keys ? (int)(w.zero_bytes / 8) : 0);
+    RP_LAUNCH_CHECK();
+  } else {
+    nms_keys_kernel<<<nb, T, 0, st>>>(scores, offsets, B, n_total,
+                                      (flags & RP_NMS_TIES_HIGH_FIRST) ? 1 : 0, w.keys_in, w.vals_in,
+                                      reinterpret_cast<uint64_t*>(w.zero_begin),
+                                      zero_in_keys ? (int)(w.zero_bytes / 8) : 0);
+    RP_LAUNCH_CHECK();
+    int seg_bits = 0;  // one problem: its rows and the slack rows differ in the low word already
+    if (B > 1) {
+      seg_bits = 1;
+      while ((1 << seg_bits) < B + 1) ++seg_bits;  // B problems + the slack id B
+    }
+    RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
+                                                w.vals_in, w.vals_out, n_total, 0, 32 + seg_bits,
+                                                st));
   }
-  RP_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.cub_temp, w.cub_bytes, w.keys_in, w.keys_out,
-                                              w.vals_in, w.vals_out, n_total, 0, 32 + seg_bits,
-                                              st));
   nms_gather_kernel<<<nb, T, 0, st>>>(boxes, labels, w.vals_out, n_total, w.sboxes, w.sarea,
                                       w.slabel);
   RP_LAUNCH_CHECK();

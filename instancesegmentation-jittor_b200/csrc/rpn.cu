@@ -567,6 +567,150 @@ __global__ void rpn_sel_emit_kernel(const float* __restrict__ boxes, const float
   out_scores[o] = scores[src];
 }
 
+// The same selection in ONE launch, one CTA per image.  Every survivor of the image (all levels, in
+// cat_boxlist order) gets the key (descending-score bits << 32 | position): a total order whose first
+// top_n elements are what the stable radix sort of the whole batch puts first.  The CTA finds the
+// top_n-th smallest key by an 8-pass radix select (shared histograms), collects the keys up to it and
+// sorts just those with a bitonic network (<= 4096 keys; the source row is looked up by position
+// afterwards, so only keys move).  Keys and source rows of up to RSEL_CAP survivors are cached in
+// shared memory; a larger image recomputes them from global memory in every pass (slow, correct).
+constexpr int RSEL_CAP = 8192;
+constexpr int RSEL_TOP = 4096;
+constexpr int RSEL_THREADS = 1024;
+
+struct RselImage {
+  const float* scores;
+  const int *offsets, *keep;
+  const int* lvl_start;  // shared
+  int L, N, b;
+  __device__ __forceinline__ int src_at(int pos) const {
+    int l = 0;  // last level whose start is <= pos (empty levels share a start: take the last)
+    for (int q = 1; q < L; ++q)
+      if (lvl_start[q] <= pos) l = q;
+    const int s = l * N + b;
+    return offsets[s] + keep[offsets[s] + (pos - lvl_start[l])];
+  }
+  __device__ __forceinline__ uint64_t key_at(int pos) const {
+    return ((uint64_t)rpn_desc_bits(scores[src_at(pos)]) << 32) | (uint32_t)pos;
+  }
+};
+
+__global__ void __launch_bounds__(RSEL_THREADS)
+rpn_sel_image_kernel(const float* __restrict__ boxes, const float* __restrict__ scores,
+                     const int* __restrict__ offsets, const int* __restrict__ keep,
+                     const int* __restrict__ n_keep, int L, int N, int top_n,
+                     float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                     int* __restrict__ out_count) {
+  extern __shared__ __align__(16) unsigned char rsel_smem[];
+  uint64_t* sk = reinterpret_cast<uint64_t*>(rsel_smem);   // [RSEL_CAP] keys by position
+  uint64_t* sel = sk + RSEL_CAP;                           // [RSEL_TOP] selected keys
+  int* sv = reinterpret_cast<int*>(sel + RSEL_TOP);        // [RSEL_CAP] source rows by position
+  __shared__ int lvl_start[RP_MAX_LEVELS + 1];
+  __shared__ int hist[256];
+  __shared__ int s_digit, s_k, s_nsel;
+  const int b = blockIdx.x, tid = threadIdx.x;
+  if (tid == 0) {
+    int p = 0;
+    for (int l = 0; l < L; ++l) {
+      lvl_start[l] = p;
+      p += n_keep[l * N + b];
+    }
+    lvl_start[L] = p;
+    s_nsel = 0;
+  }
+  __syncthreads();
+  const int cnt = lvl_start[L];
+  const RselImage im{scores, offsets, keep, lvl_start, L, N, b};
+  const bool cached = cnt <= RSEL_CAP;
+  if (cached) {
+    for (int pos = tid; pos < cnt; pos += RSEL_THREADS) {
+      const int src = im.src_at(pos);
+      sv[pos] = src;
+      sk[pos] = ((uint64_t)rpn_desc_bits(scores[src]) << 32) | (uint32_t)pos;
+    }
+    __syncthreads();
+  }
+  const int n_out = min(cnt, top_n);
+  uint64_t kth = ~0ull;  // every key is <= kth
+  if (cnt > top_n) {
+    // radix select of the top_n-th smallest key, most significant byte first
+    uint64_t prefix = 0ull;
+    int k = top_n;  // rank (1-based) among the keys that match the prefix
+    for (int shift = 56; shift >= 0; shift -= 8) {
+      if (tid < 256) hist[tid] = 0;
+      __syncthreads();
+      const uint64_t mask = shift == 56 ? 0ull : (~0ull << (shift + 8));
+      for (int pos = tid; pos < cnt; pos += RSEL_THREADS) {
+        const uint64_t key = cached ? sk[pos] : im.key_at(pos);
+        if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
+      }
+      __syncthreads();
+      if (tid < 32) {
+        // 8 bins per lane: find the digit whose cumulative count reaches k
+        int c[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          c[i] = hist[tid * 8 + i];
+          sum += c[i];
+        }
+        int incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, d);
+          if (tid >= d) incl += t;
+        }
+        const int excl = incl - sum;
+        if (excl < k && k <= incl) {
+          int run = excl;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (run < k && k <= run + c[i]) {
+              s_digit = tid * 8 + i;
+              s_k = k - run;
+            }
+            run += c[i];
+          }
+        }
+      }
+      __syncthreads();
+      prefix |= (uint64_t)s_digit << shift;
+      k = s_k;
+    }
+    kth = prefix;
+  }
+  // collect the keys up to kth (exactly n_out of them: keys are unique), sort, emit
+  for (int pos = tid; pos < cnt; pos += RSEL_THREADS) {
+    const uint64_t key = cached ? sk[pos] : im.key_at(pos);
+    if (key <= kth) sel[atomicAdd(&s_nsel, 1)] = key;
+  }
+  int P2 = 32;
+  while (P2 < n_out) P2 <<= 1;
+  __syncthreads();
+  for (int i = n_out + tid; i < P2; i += RSEL_THREADS) sel[i] = ~0ull;
+  __syncthreads();
+  for (int k = 2; k <= P2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < (P2 >> 1); i += RSEL_THREADS) {
+        const int lo = ((i / j) * (j << 1)) + (i & (j - 1)), hi = lo + j;
+        const uint64_t a = sel[lo], c = sel[hi];
+        if ((a > c) == ((lo & k) == 0)) {
+          sel[lo] = c;
+          sel[hi] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  if (tid == 0) out_count[b] = n_out;
+  for (int j = tid; j < n_out; j += RSEL_THREADS) {
+    const int pos = (int)(uint32_t)sel[j];
+    const int src = cached ? sv[pos] : im.src_at(pos);
+    const size_t o = (size_t)b * top_n + j;
+    *reinterpret_cast<float4*>(out_boxes + o * 4) = *reinterpret_cast<const float4*>(boxes + (size_t)src * 4);
+    out_scores[o] = scores[src];
+  }
+}
+
 size_t rpn_cub_bytes(size_t n) {
   size_t bytes = 0;
   cub::DeviceRadixSort::SortPairs((void*)nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
@@ -796,6 +940,14 @@ int rp_rpn_select_levels(const float* boxes, const float* scores, const int* off
     return RP_E_ARG;
   if (((reinterpret_cast<uintptr_t>(boxes) | reinterpret_cast<uintptr_t>(out_boxes)) & 15) != 0)
     return RP_E_ARG;
+  if (L <= RP_MAX_LEVELS && top_n <= RSEL_TOP && rp_env_int("RP_RPN_SEL_FUSED", 1)) {
+    const size_t smem = (size_t)RSEL_CAP * (sizeof(uint64_t) + sizeof(int)) + (size_t)RSEL_TOP * sizeof(uint64_t);
+    RP_SET_MAX_SMEM(rpn_sel_image_kernel, smem);
+    rpn_sel_image_kernel<<<N, RSEL_THREADS, smem, st>>>(boxes, scores, offsets, keep, n_keep, L, N, top_n,
+                                                        out_boxes, out_scores, out_count);
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
   RpnSelWorkspace w = rpn_sel_carve(workspace, (size_t)n_cap, L, N);
   if (w.total > workspace_bytes) return RP_E_WORKSPACE;
   rpn_sel_scan_kernel<<<1, RPN_THREADS, 0, st>>>(n_keep, L, N, w.img_off, w.seg_pos);

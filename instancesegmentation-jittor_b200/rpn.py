@@ -232,9 +232,12 @@ class RPNPostProcessor(torch.nn.Module):
             bc.weights, bc.bbox_xform_clip)
         keep = n_keep = None
         if self.nms_thresh > 0:  # boxlist_nms returns its input otherwise (boxlist_ops.py:24-25)
+            # the candidates of every (level, image) come out of the top-k in descending score order
+            # (ties by ascending anchor index), i.e. as the reference's argsort would leave them
             keep, n_keep = layers.nms_batched(
                 boxes, scores, offsets, self.nms_thresh, None,
-                max_keep=self.post_nms_top_n if self.post_nms_top_n > 0 else -1, n_max=max(ks))
+                max_keep=self.post_nms_top_n if self.post_nms_top_n > 0 else -1, n_max=max(ks),
+                flags=_lib.RP_NMS_PRESORTED)
         return dict(boxes=boxes, scores=scores, offsets=offsets, keep=keep, n_keep=n_keep,
                     shapes=shapes, N=N, L=L)
 

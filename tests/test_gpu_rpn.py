@@ -220,3 +220,45 @@ def test_anchors_are_not_cached_by_address():
         np.testing.assert_array_equal(out[0].bbox.cpu().numpy(), ref[0][0])
         res.append(out)
         del a_t
+
+
+def test_select_levels_one_launch_kernel_rounds_and_radix_path(monkeypatch):
+    # rp_rpn_select_levels: per image the survivors of all levels, stable-sorted by descending score,
+    # first top_n.  20 000 survivors per image (more than the 8192 the one-launch kernel sorts at a time:
+    # it works in rounds), tie-heavy scores; RP_RPN_SEL_FUSED=0 is the whole-batch radix sort.
+    rng = np.random.default_rng(5)
+    L, N, per = 4, 3, 6000
+    S = L * N
+    lens = rng.integers(per - 2000, per + 1, S)
+    lens[5] = 0
+    offs = np.concatenate([[0], np.cumsum(np.full(S, per))]).astype(np.int32)  # padded segments
+    n_tot = int(offs[-1])
+    boxes = rng.uniform(0, 500, (n_tot, 4)).astype(np.float32)
+    scores = (np.floor(rng.uniform(0, 1, n_tot) * 512) / 512).astype(np.float32)
+    keep = np.zeros(n_tot, np.int32)
+    n_keep = np.zeros(S, np.int32)
+    for s in range(S):
+        k = rng.permutation(lens[s])[: max(0, lens[s] - 100)].astype(np.int32)
+        keep[offs[s]: offs[s] + len(k)] = k
+        n_keep[s] = len(k)
+    for top in (1000, 2000):
+        ref_b, ref_s = [], []
+        for b in range(N):
+            src = np.concatenate([offs[l * N + b] + keep[offs[l * N + b]: offs[l * N + b] + n_keep[l * N + b]]
+                                  for l in range(L)])
+            order = np.argsort(-scores[src], kind="stable")[:top]
+            ref_b.append(boxes[src[order]])
+            ref_s.append(scores[src[order]])
+        for fused in ("1", "0"):
+            monkeypatch.setenv("RP_RPN_SEL_FUSED", fused)
+            rp.reload_env()
+            try:
+                ob, osc, cnt = rp.rpn_select_levels(T(boxes), T(scores), T(offs), T(keep), T(n_keep), L, N, top)
+            finally:
+                monkeypatch.delenv("RP_RPN_SEL_FUSED")
+                rp.reload_env()
+            ob, osc, cnt = ob.cpu().numpy(), osc.cpu().numpy(), cnt.cpu().numpy()
+            for b in range(N):
+                assert cnt[b] == len(ref_s[b])
+                np.testing.assert_array_equal(osc[b, : cnt[b]], ref_s[b])
+                np.testing.assert_array_equal(ob[b, : cnt[b]], ref_b[b])

@@ -22,7 +22,8 @@ objs, regs, ancs, wh = [T(l[1]) for l in lv], [T(l[2]) for l in lv], [T(l[0]) fo
 
 def step():
     bx, sc, _, off, ks = rp.rpn_pre_nms_levels(objs, regs, ancs, wh, top_n, 0.0)
-    keep, nk = rp.nms_batched(bx, sc, off, 0.7, max_keep=top_n, n_max=max(ks))
+    keep, nk = rp.nms_batched(bx, sc, off, 0.7, max_keep=top_n, n_max=max(ks),
+                              flags=rp.package._lib.RP_NMS_PRESORTED)  # as RPNPostProcessor calls it
     return rp.rpn_select_levels(bx, sc, off, keep, nk, len(lv), N, top_n)
 
 
