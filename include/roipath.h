@@ -308,6 +308,8 @@ RP_API int rp_pack_mask_bits(const uint8_t* masks, long long m, long long npix, 
  *   descending score, equal scores in (level, keep rank) order = the cat_boxlist order :143-144.
  *   n_cap = rows of boxes / scores / keep.  out_boxes [N*top_n,4], out_scores [N*top_n]: image
  *   b owns rows [b*top_n, b*top_n + out_count[b]).
+ *   One launch (one CTA per image: radix select + sort of the selected keys) for top_n <= 4096,
+ *   else a stable radix sort of the whole batch in the workspace; identical results.
  * ------------------------------------------------------------------------------------ */
 RP_API int rp_box_decode(const float* rel_codes, const float* boxes, int n, int K, float wx,
                   float wy, float ww, float wh, float bbox_xform_clip, float* out, void* stream);
