@@ -371,7 +371,10 @@ __device__ __forceinline__ bool nms_suppress_multi(const NmsBand& p, int seg, in
   }
   __syncthreads();
   const int na = sm.mw_pre[NMS_MW];  // <= 1024: 16 words x 64 boxes
-  if (na == 0) return false;
+  // Nothing alive: no work, but the caller's "done" signal must still come after the band's resolve
+  // (the dataflow counters are running totals: an item of a later step that reports early would let
+  // the resolver's wait for an earlier step pass before that step's words are final).
+  if (na == 0) return wait();
   int P = NMS_SUP_THREADS / na;
   if (P > 64) P = 64;
   const int slot = tid / P, part = tid - slot * P;

@@ -243,3 +243,43 @@ def test_one_launch_and_per_band_launch_paths(monkeypatch, mode):
         for k in _NMS_MODES[mode]:
             monkeypatch.delenv(k)
         rp.reload_env()
+
+
+@pytest.mark.parametrize("mode", ["default", "dataflow", "barriers"])
+def test_random_batches_stress(monkeypatch, mode):
+    # the one-launch drivers synchronise CTAs through counters in global memory: many random shapes
+    # (ragged, empty, 1-6 bands, with and without labels / caps), each launched several times in a row
+    for k, v in _NMS_MODES[mode].items():
+        monkeypatch.setenv(k, v)
+    rp.reload_env()
+    try:
+        rng = np.random.default_rng(1234)
+        for case in range(14):
+            B = int(rng.integers(1, 14))
+            lens = [int(rng.choice([0, 1, 63, 64, 65, 300, 1024, 1025, 1500, 2500, 4000, 6000])) for _ in range(B)]
+            if case % 4 == 0:
+                lens = [int(x) for x in rng.integers(0, 1200, B)]
+            parts = [synth.nms_boxes(max(n, 1), 1000 + 31 * case + i, tie_heavy=bool(i & 1)) for i, n in enumerate(lens)]
+            bs = [p[0][:n] for p, n in zip(parts, lens)]
+            ss = [p[1][:n] for p, n in zip(parts, lens)]
+            ls = [(p[2][:n] % 3).astype(np.float32) for p, n in zip(parts, lens)]
+            offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+            if int(offs[-1]) == 0:
+                continue
+            thr = float(rng.choice([0.3, 0.5, 0.7]))
+            mk = int(rng.choice([-1, -1, 50, 700]))
+            use_labels = bool(case % 3 == 1)
+            bt, st, ot = T(np.concatenate(bs)), T(np.concatenate(ss)), T(offs)
+            lt = T(np.concatenate(ls)) if use_labels else None
+            refs = [oracle.nms(bs[i], ss[i], thr, labels=ls[i] if use_labels else None, max_keep=mk)
+                    if lens[i] else np.zeros(0, np.int32) for i in range(B)]
+            for rep in range(3):
+                keep, nk = rp.nms_batched(bt, st, ot, thr, labels=lt, max_keep=mk)
+                keep, nk = keep.cpu().numpy(), nk.cpu().numpy()
+                for i in range(B):
+                    np.testing.assert_array_equal(keep[offs[i]: offs[i] + nk[i]], refs[i],
+                                                  err_msg="case %d rep %d problem %d lens %s" % (case, rep, i, lens))
+    finally:
+        for k in _NMS_MODES[mode]:
+            monkeypatch.delenv(k)
+        rp.reload_env()
