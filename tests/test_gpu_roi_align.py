@@ -241,9 +241,12 @@ def test_pooler_execute_host_pipeline():
 
 
 @pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
-@pytest.mark.parametrize("C", [37, 64])
+@pytest.mark.parametrize("C", [37, 64, 8, 100])
 def test_channels_last_entry_matches_oracle(P, sr, C):
-    # torch.channels_last feature maps take the NHWC kernels (16-byte taps); same oracle, same bar
+    # torch.channels_last feature maps take the NHWC kernels; same oracle, same bar.  C % 4 == 0 with
+    # sampling_ratio 2 is the separable kernel (the RoIs span tiles that fit 32, 16, 8 and 4 channels
+    # per chunk and tiles that do not fit at all: reference-order path; C = 100: a last chunk of 4
+    # channels; pooled width 7: 8 column lanes), everything else the gather kernel (16-byte taps)
     rng = np.random.default_rng(2)
     N = 2
     feat = rng.standard_normal((N, C, 50, 84)).astype(np.float32)

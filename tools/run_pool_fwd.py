@@ -16,6 +16,8 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 dev = torch.device("cuda", 0)
 gen = torch.Generator(device=dev).manual_seed(1234)
 feats = [torch.randn(s, device=dev, generator=gen) for s in synth.fpn_shapes(images, 256)]
+if os.environ.get("LAYOUT", "nchw") == "nhwc":  # torch.channels_last: the NHWC entry
+    feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
 rois = torch.from_numpy(synth.rois_for_images(images, 1000)).to(dev)
 levels = rp.LevelMapper(2, 5).map_rois(rois)
 out = torch.empty((rois.shape[0], 256, res, res), device=dev)
@@ -29,4 +31,4 @@ for _ in range(reps):
     fn()
 e1.record()
 torch.cuda.synchronize()
-print("pooler fwd %dx%d, %d RoIs: %.3f ms" % (res, res, rois.shape[0], e0.elapsed_time(e1) / reps))
+print("pooler fwd %s %dx%d, %d RoIs: %.3f ms" % (os.environ.get("LAYOUT", "nchw"), res, res, rois.shape[0], e0.elapsed_time(e1) / reps))
