@@ -150,6 +150,22 @@ RP_API int rp_nms_batched(const float* boxes, const float* scores, const float* 
                    int flags, int* keep, int* n_keep, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/* rp_nms_batched_static: rp_nms_batched without a workspace argument, for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO
+ * counterpart in the reference.  The workspace is
+ * a fixed array of rp_nms_static_capacity_bytes() = 4 MiB of device memory that every GPU which loads
+ * the library holds until the process exits; the call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  Shapes whose rp_nms_workspace_bytes(n_total, n_max, B) exceeds the
+ * capacity return RP_E_LIMIT (one image of 20 000 boxes needs 1.3 MiB, 8 x 1000 boxes 2.8 MiB).
+ * All calls share the array: calls that may overlap on the GPU (different streams or host threads)
+ * race; serialise them.  The array keeps the previous call's contents, the call clears what must
+ * start at zero.  Same arguments, results and error codes as rp_nms_batched otherwise. */
+RP_API size_t rp_nms_static_capacity_bytes(void);
+
+RP_API int rp_nms_batched_static(const float* boxes, const float* scores, const float* labels,
+                          const int* offsets, int B, int n_total, int n_max, double thr,
+                          int max_keep, int flags, int* keep, int* n_keep, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Yolact: box decode, detection pre-filter, FastNMS.
  * Replaces: decode(loc, priors) yol/layers/box_utils.py:272-316;

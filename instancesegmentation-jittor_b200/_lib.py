@@ -37,6 +37,8 @@ SIGNATURES = {
     "rp_pooler_backward": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _i, _vp]),
     "rp_nms_workspace_bytes": (_sz, [_i, _i, _i]),
     "rp_nms_batched": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _d, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "rp_nms_static_capacity_bytes": (_sz, []),
+    "rp_nms_batched_static": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _d, _i, _i, _vp, _vp, _vp]),
     "rp_yolact_decode": (_i, [_vp, _vp, _i, _vp, _vp]),
     "rp_fast_nms_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rp_fast_nms_batched": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _i, _i, _i, _f, _i,

@@ -1297,3 +1297,65 @@ int rp_nms_batched(const float* boxes, const float* scores, const float* labels,
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// rp_nms_batched_static: rp_nms_batched for callers that may not allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The workspace is a fixed array in device memory that every GPU
+// which loads the library holds until the process exits.  In host code the array's NAME is only a
+// host-side stand-in, not a device address: the address is fetched once per device, with that device
+// current, by cudaGetSymbolAddress and handed to the kernels as an ordinary pointer.
+// All calls share the array: calls that overlap on the GPU (two streams, two host threads) race.
+// The array keeps the previous call's contents; rp_nms_batched clears the part that must start at
+// zero (removed bits, counters, barrier words) at the start of every call, on the stream.
+// ------------------------------------------------------------------------------------------
+#define RP_NMS_STATIC_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char nms_static_scratch[RP_NMS_STATIC_BYTES];
+
+namespace {
+// device address of nms_static_scratch on the current device (nullptr + *rc on failure)
+void* nms_static_ptr(int* rc) {
+  static std::mutex mu;
+  static void* ptr[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    (void)cudaGetLastError();
+    *rc = e != cudaSuccess ? (int)e : RP_E_LIMIT;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, nms_static_scratch);
+    if (e != cudaSuccess || !p) {
+      (void)cudaGetLastError();
+      *rc = e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+      return nullptr;
+    }
+    ptr[dev] = p;
+  }
+  *rc = RP_OK;
+  return ptr[dev];
+}
+}  // namespace
+
+extern "C" {
+
+size_t rp_nms_static_capacity_bytes(void) { return (size_t)RP_NMS_STATIC_BYTES; }
+
+int rp_nms_batched_static(const float* boxes, const float* scores, const float* labels,
+                          const int* offsets, int B, int n_total, int n_max, double thr, int max_keep,
+                          int flags, int* keep, int* n_keep, void* stream) {
+  if (B < 1 || n_total < 0 || n_max < 0) return RP_E_ARG;
+  // the same sizing rule as rp_nms_workspace_bytes; too large for the fixed array: RP_E_LIMIT
+  const size_t need = nms_carve(nullptr, n_total, n_max, B).total;
+  if (need > (size_t)RP_NMS_STATIC_BYTES) return RP_E_LIMIT;
+  int rc = RP_OK;
+  void* ws = nms_static_ptr(&rc);
+  if (!ws) return rc;
+  return rp_nms_batched(boxes, scores, labels, offsets, B, n_total, n_max, thr, max_keep, flags, keep,
+                        n_keep, ws, (size_t)RP_NMS_STATIC_BYTES, stream);
+}
+
+}  // extern "C"
