@@ -189,9 +189,127 @@ struct FwdGlobalSink {
   }
 };
 
+// rt_fwd_item_fsm (roi_tile.h) with the address arithmetic done by hand: the same operations on the
+// same values in the same order (bit-identical results), but
+//   * tile and sample-table accesses are ld.shared with 32-bit addresses: ONE add per (row, channel,
+//     tap pair) instead of the 64-bit index * 4 + base the generic-pointer form compiles to,
+//   * the U output pointers are kept as running 64-bit pointers (one add per emitted row each).
+// ncu on the generic form: IMAD 19 % and LEA / IADD3 5 % of the instruction stream were addresses.
+__device__ __forceinline__ float rt_lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float rt_lds_f32_4(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+4];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ RtYSample rt_lds_sample(uint32_t a) {
+  RtYSample e;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(e.wlo), "=f"(e.whi), "=r"(e.row), "=r"(e.flags)
+               : "r"(a));
+  return e;
+}
+
+template <int U>
+__device__ __forceinline__ void rt_fwd_item_fsm_s(uint32_t tile_a, uint32_t ustride4, int nvalid,
+                                                  uint32_t ytab_a, const RtW* xw, const short* xo_t,
+                                                  int gy, uint32_t tw4, int pw, int b0, int b1,
+                                                  float* optr, int cstride, int PW, float inv) {
+  if (b0 >= b1) return;
+  const RtW w0 = xw[pw * 2], w1 = xw[pw * 2 + 1];
+  uint32_t st = ytab_a + (uint32_t)(b0 * gy) * 16u;
+  int bins_left = b1 - b0;
+  /* the first sample of a segment: its row pair is computed from scratch, flags ignored */
+  RtYSample e = rt_lds_sample(st);
+  st += 16u;
+  uint32_t a0[U], a1[U];
+  float* op[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint32_t b = tile_a + (u < nvalid ? (uint32_t)u * ustride4 : 0u) + (uint32_t)e.row * tw4;
+    a0[u] = b + 4u * (uint32_t)xo_t[pw * 2];
+    a1[u] = b + 4u * (uint32_t)xo_t[pw * 2 + 1];
+    op[u] = optr + (size_t)u * cstride;
+  }
+  float Ta[U], Tb[U], acc[U];
+#define RS_XROW(T)                                                                            \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                             \
+    T[u] = fmaf(w1.hi, rt_lds_f32_4(a1[u]),                                                   \
+                fmaf(w1.lo, rt_lds_f32(a1[u]),                                                \
+                     fmaf(w0.hi, rt_lds_f32_4(a0[u]), fmaf(w0.lo, rt_lds_f32(a0[u]), 0.f)))); \
+    a0[u] += tw4;                                                                             \
+    a1[u] += tw4;                                                                             \
+  }
+#define RS_JUMP(LO, HI)                                      \
+  {                                                          \
+    const uint32_t skip = (uint32_t)(e.flags >> 8) * tw4;    \
+    _Pragma("unroll") for (int u = 0; u < U; ++u) {          \
+      a0[u] += skip;                                         \
+      a1[u] += skip;                                         \
+    }                                                        \
+    RS_XROW(LO)                                              \
+    RS_XROW(HI)                                              \
+  }
+#define RS_YFMA(LO, HI)                                      \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) acc[u] =     \
+      fmaf(e.whi, HI[u], fmaf(e.wlo, LO[u], acc[u]));
+#define RS_EMIT()                                            \
+  if (e.flags & RT_F_EMIT) {                                  \
+    _Pragma("unroll") for (int u = 0; u < U; ++u) {          \
+      if (u < nvalid) __stcs(op[u], acc[u] * inv);           \
+      op[u] += PW;                                           \
+      acc[u] = 0.f;                                          \
+    }                                                        \
+    if (--bins_left == 0) return;                            \
+  }
+  RS_XROW(Ta)
+  RS_XROW(Tb)
+#pragma unroll
+  for (int u = 0; u < U; ++u) acc[u] = 0.f;
+  RS_YFMA(Ta, Tb)
+  RS_EMIT()
+  for (;;) {
+    /* state A: Ta = lo row, Tb = hi row */
+    for (;;) {
+      e = rt_lds_sample(st);
+      st += 16u;
+      if (e.flags & RT_F_ADV) {
+        RS_XROW(Ta) /* Ta becomes the new hi row */
+        RS_YFMA(Tb, Ta)
+        RS_EMIT()
+        break;
+      }
+      if (e.flags & RT_F_JUMP) RS_JUMP(Ta, Tb)
+      RS_YFMA(Ta, Tb)
+      RS_EMIT()
+    }
+    /* state B: Tb = lo row, Ta = hi row */
+    for (;;) {
+      e = rt_lds_sample(st);
+      st += 16u;
+      if (e.flags & RT_F_ADV) {
+        RS_XROW(Tb)
+        RS_YFMA(Ta, Tb)
+        RS_EMIT()
+        break;
+      }
+      if (e.flags & RT_F_JUMP) RS_JUMP(Tb, Ta)
+      RS_YFMA(Tb, Ta)
+      RS_EMIT()
+    }
+  }
+#undef RS_XROW
+#undef RS_JUMP
+#undef RS_YFMA
+#undef RS_EMIT
+}
+
 // The v3 evaluation of one (RoI, channel slice) by the whole CTA; any CTA size that is a multiple
 // of gw.  Also the fallback of the banded kernel below for RoIs without a band form.
-template <int U>
+template <int U, bool LEAN = false>
 __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const RtLevels& lv, int N,
                                                 int C, const float* __restrict__ rois,
                                                 const int* __restrict__ levels, int PH, int PW,
@@ -349,7 +467,11 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                               nvalid, inv};
         const float* tile_g = tile + cg * chp;
         const int ustride = tp.ncg * chp;
-        if (g.gw == 2)
+        if (g.gw == 2 && LEAN)
+          rt_fwd_item_fsm_s<U>(tile_s + 4u * (uint32_t)(cg * chp), 4u * (uint32_t)ustride, nvalid,
+                               rp_smem_addr(ytab), xw_s, xo_s, g.gh, 4u * (uint32_t)twa, pw, b0, b1,
+                               out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW, inv);
+        else if (g.gw == 2)
           rt_fwd_item_fsm<U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, twa, pw, b0, b1, sink);
         else
           rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink);
@@ -362,13 +484,13 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
 constexpr int RT3_TABLE_BYTES =
     sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX;
 
-template <int U>
+template <int U, bool LEAN>
 __global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
                    float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
-  rt3_roi_forward<U>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
+  rt3_roi_forward<U, LEAN>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
                      tile_floats, gpb, gw);
 }
 
@@ -1520,10 +1642,16 @@ template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
                   cudaStream_t st) {
-  RP_SET_MAX_SMEM(rt_pool_fwd_kernel<U>, l.smem_fwd);
   dim3 grid((unsigned)K, (unsigned)l.csplit);
-  rt_pool_fwd_kernel<U><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-      lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
+  if (rp_env_int("RP_ROI_LEAN", 1)) {  // hand-written shared-memory addressing in the sample walk
+    RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, true>), l.smem_fwd);
+    rt_pool_fwd_kernel<U, true><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
+  } else {
+    RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, false>), l.smem_fwd);
+    rt_pool_fwd_kernel<U, false><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
+  }
   RP_LAUNCH_CHECK();
   return RP_OK;
 }
