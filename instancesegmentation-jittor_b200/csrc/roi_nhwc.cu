@@ -13,6 +13,11 @@
 // contiguous in `out` and leaves through a shared-memory stage as full 128-byte lines.
 // LSU-bound (16 vector loads per output quad); no staging of the feature tile is needed because
 // neighbouring bins hit the same lines in L1.
+#include <cuda.h>
+
+#include <cstring>
+#include <mutex>
+
 #include "common.cuh"
 #include "roi_levels.h"
 #include "roi_tile.h"
@@ -195,16 +200,34 @@ __device__ __forceinline__ void rn2_direct(const float* feat_b, int H, int W, in
   }
 }
 
-__global__ void __launch_bounds__(RN2_THREADS, 4)
-rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
-                         const int* __restrict__ levels, int PH, int PW, float sampling_ratio,
-                         float* __restrict__ out, int c_per_cta, int tile_bytes) {
-  extern __shared__ __align__(16) unsigned char rn2_smem[];
+// TMA variant ("rn3"): the tile of a chunk is one cp.async.bulk.tensor box per tile row -- the map
+// (c, x, y) of a channels-last tensor needs no permutation to land [row][x][channels] -- issued by the
+// lanes of warp 0, completion on an mbarrier; two tile buffers, the boxes of chunk i + 2 are issued as
+// soon as chunk i has been walked, so the copy of the next chunk runs under the walk of this one.  No
+// staging instructions at all (the cp.async form spends 20 % of its instruction stream on them) -- and
+// no faster: 1.95 ms against 1.94 ms at 14x14, 1.36 against 0.96 ms at 7x7 (short walks do not cover the
+// latency of a box per row), so it is opt-in (RP_NHWC_TMA=1).  Box
+// widths are fixed per tensor map: RN3_NW widths x 4 channel counts per level; the tile row pitch is
+// the box width (columns past the RoI's tile are fetched and never read; past the map: zero fill).
+constexpr int RN3_NW = 6, RN3_NCG = 4, RN3_MAXL = 5;
+__device__ __constant__ int rn3_widths[RN3_NW] = {8, 16, 24, 32, 48, 64};
+static const int rn3_widths_h[RN3_NW] = {8, 16, 24, 32, 48, 64};
+struct Rn3Maps {
+  CUtensorMap m[RN3_MAXL][RN3_NW][RN3_NCG];  // [level][width][32, 16, 8, 4 channels]
+};
+
+template <bool TMA>
+__device__ __forceinline__ void rn2_body(unsigned char* rn2_smem, const RtLevels& lv, int N, int C,
+                                         const float* __restrict__ rois, const int* __restrict__ levels,
+                                         int PH, int PW, float sampling_ratio, float* __restrict__ out,
+                                         int c_per_cta, int tile_bytes, const Rn3Maps* maps) {
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rn2_smem);
   RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
   short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
-  const uint32_t tile_a = rp_smem_addr(rn2_smem) + (uint32_t)((RN2_TABLE_BYTES + 15) & ~15);
+  // tile buffer(s): 128-byte aligned (TMA destination)
+  const uint32_t tile_a = (rp_smem_addr(rn2_smem) + (uint32_t)RN2_TABLE_BYTES + 127u) & ~127u;
   __shared__ int s_ext[4];  // y: min lo, max lo ; x: min lo, max lo
+  __shared__ __align__(8) uint64_t s_full[2];
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
   const int c_begin = blockIdx.y * c_per_cta;
@@ -260,11 +283,17 @@ rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ ro
     return;
   }
   const int R = yl - y0 + 2, tw = xl - x0 + 2;  // the hi tap of every sample is lo + 1
-  int CG = 0;
-  if (fits)
-    for (int cg = 32; cg >= 4; cg >>= 1)
-      if ((size_t)R * tw * cg * 4 <= (size_t)tile_bytes) {
+  int CG = 0, cgi = 0, wi = 0;
+  int twp = tw;  // tile row pitch in columns
+  if (TMA) {
+    while (wi < RN3_NW && rn3_widths[wi] < tw) ++wi;
+    twp = wi < RN3_NW ? rn3_widths[wi] : 0;
+  }
+  if (fits && twp > 0)
+    for (int cg = 32, i = 0; cg >= 4; cg >>= 1, ++i)
+      if ((size_t)R * twp * cg * 4 <= (size_t)tile_bytes) {
         CG = cg;
+        cgi = i;
         break;
       }
   if (CG == 0) {
@@ -303,7 +332,7 @@ rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ ro
   const int b0 = active ? seg * PH / nseg : 0;
   const int b1 = active ? (seg + 1) * PH / nseg : 0;
   const float inv = 1.0f / (float)(g.gh * g.gw);
-  const uint32_t row4 = (uint32_t)(tw * nq) * 16u;  // bytes per tile row
+  const uint32_t row4 = (uint32_t)(twp * nq) * 16u;  // bytes per tile row
   const uint32_t xstep = (uint32_t)nq * 16u;        // bytes per tile column
   RtW w0{0.f, 0.f}, w1{0.f, 0.f};
   uint32_t xoff0 = 0, xoff1 = 0;
@@ -321,37 +350,73 @@ rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ ro
   const int n_xy = R * tw;
   const uint32_t sa_step = (uint32_t)(step * nq) * 16u;
 
-  for (int c0 = 0; c0 < nch; c0 += CG) {
+  // ---- TMA: boxes of one chunk = one per tile row, issued by the lanes of warp 0
+  const int nchunk = (nch + CG - 1) / CG;
+  const uint32_t chunk_bytes = (uint32_t)(R * twp * CG * 4);
+  const CUtensorMap* tm = TMA ? &maps->m[level][wi][cgi] : nullptr;
+  const int ty0 = b * H + y0;
+  auto issue = [&](int ci) {
+    if (tid < 32) {
+      const uint32_t bar = rp_smem_addr(&s_full[ci & 1]);
+      const uint32_t dst = tile_a + (uint32_t)(ci & 1) * (uint32_t)tile_bytes;
+      if (tid == 0)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(chunk_bytes)
+                     : "memory");
+      __syncwarp();
+      for (int r = tid; r < R; r += 32)
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst + (uint32_t)r * row4),
+            "l"(tm), "r"(c_begin + ci * CG), "r"(x0), "r"(ty0 + r), "r"(bar)
+            : "memory");
+    }
+  };
+  if (TMA) {
+    if (tid == 0) {
+      rp_mbar_init(&s_full[0], 1);
+      rp_mbar_init(&s_full[1], 1);
+    }
+    __syncthreads();
+    issue(0);
+    if (nchunk > 1) issue(1);
+  }
+
+  for (int c0 = 0, ci = 0; c0 < nch; c0 += CG, ++ci) {
     const int cc = min(CG, nch - c0);  // multiple of 4
-    if (4 * q < cc) {
-      // (every tile column lies inside the map: the last one is the hi tap of the last valid sample.)
-      // The address of every copy is formed from (y, x) on its own: a running pointer is 4 instructions
-      // shorter per copy but chains the copies of a thread behind each other, and this loop lives on
-      // the number of copies in flight (measured: 2.24 ms against 2.14).
-      const float* src = feat_b + ((size_t)y0 * W + x0) * C + c0 + 4 * q;
-      int y = sy0, x = sx0;
-      uint32_t sa = tile_a + (uint32_t)(idx0 * nq + q) * 16u;
-      for (int i = idx0; i < n_xy; i += step) {
-        const float* gp = src + ((size_t)y * W + x) * C;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gp) : "memory");
-        sa += sa_step;
-        x += sdx;
-        y += sdy;
-        if (x >= tw) {
-          x -= tw;
-          ++y;
+    const uint32_t tile_c = tile_a + (TMA ? (uint32_t)(ci & 1) * (uint32_t)tile_bytes : 0u);
+    if (TMA) {
+      rp_mbar_wait_bounded(&s_full[ci & 1], (uint32_t)((ci >> 1) & 1));
+    } else {
+      if (4 * q < cc) {
+        // (every tile column lies inside the map: the last one is the hi tap of the last valid sample.)
+        // The address of every copy is formed from (y, x) on its own: a running pointer is 4
+        // instructions shorter per copy but chains the copies of a thread behind each other, and this
+        // loop lives on the number of copies in flight (measured: 2.24 ms against 2.14).
+        const float* src = feat_b + ((size_t)y0 * W + x0) * C + c0 + 4 * q;
+        int y = sy0, x = sx0;
+        uint32_t sa = tile_a + (uint32_t)(idx0 * nq + q) * 16u;
+        for (int i = idx0; i < n_xy; i += step) {
+          const float* gp = src + ((size_t)y * W + x) * C;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gp) : "memory");
+          sa += sa_step;
+          x += sdx;
+          y += sdy;
+          if (x >= tw) {
+            x -= tw;
+            ++y;
+          }
         }
       }
+      asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+      __syncthreads();
     }
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
     if (b0 < b1 && 4 * q < cc) {
       uint32_t st = rp_smem_addr(ytab) + (uint32_t)(b0 * g.gh) * 16u;
       int bins_left = b1 - b0;
       RtYSample e = rn2_lds_sample(st);
       st += 16u;
-      uint32_t a0 = tile_a + (uint32_t)e.row * row4 + xoff0;
-      uint32_t a1 = tile_a + (uint32_t)e.row * row4 + xoff1;
+      uint32_t a0 = tile_c + (uint32_t)e.row * row4 + xoff0;
+      uint32_t a1 = tile_c + (uint32_t)e.row * row4 + xoff1;
       float* op = out_k + (size_t)(c0 + 4 * q) * P + b0 * PW + pwl;
       float4 Ta, Tb, acc;
 #define RN2_XROW(T)                                                                        \
@@ -427,8 +492,97 @@ rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ ro
 #undef RN2_EMIT
     }
   item_done:
-    __syncthreads();  // the tile is overwritten by the next chunk
+    __syncthreads();  // the tile is overwritten by the next chunk (TMA: by the chunk after the next)
+    if (TMA && ci + 2 < nchunk) issue(ci + 2);
   }
+}
+
+__global__ void __launch_bounds__(RN2_THREADS, 4)
+rn2_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                         const int* __restrict__ levels, int PH, int PW, float sampling_ratio,
+                         float* __restrict__ out, int c_per_cta, int tile_bytes) {
+  extern __shared__ __align__(128) unsigned char rn2_smem[];
+  rn2_body<false>(rn2_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta, tile_bytes,
+                  nullptr);
+}
+
+__global__ void __launch_bounds__(RN2_THREADS, 4)
+rn3_pool_fwd_nhwc_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
+                         const int* __restrict__ levels, int PH, int PW, float sampling_ratio,
+                         float* __restrict__ out, int c_per_cta, int tile_bytes,
+                         const __grid_constant__ Rn3Maps maps) {
+  extern __shared__ __align__(128) unsigned char rn2_smem[];
+  rn2_body<true>(rn2_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta, tile_bytes,
+                 &maps);
+}
+
+// ---- host: tensor maps (c, x, y) of the channels-last levels -----------------------------------
+typedef CUresult (*rn3_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+rn3_encode_fn rn3_encoder() {
+  static rn3_encode_fn fn = []() -> rn3_encode_fn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    return reinterpret_cast<rn3_encode_fn>(p);
+  }();
+  return fn;
+}
+
+struct Rn3Entry {
+  const float* ptr;
+  long long rows;  // N * H
+  int W, C, ok;
+  unsigned long long stamp;
+  CUtensorMap m[RN3_NW][RN3_NCG];
+};
+
+// Fills maps->m[l]; a small host cache keeps repeated calls on the same tensors free of encoding.
+int rn3_level_maps(Rn3Maps* maps, int l, const float* ptr, long long rows, int W, int C) {
+  static std::mutex mu;
+  static Rn3Entry cache[32];
+  static unsigned long long clock_ = 0;
+  rn3_encode_fn enc = rn3_encoder();
+  if (!enc) return 0;
+  std::lock_guard<std::mutex> lock(mu);
+  int victim = 0;
+  for (int i = 0; i < 32; ++i) {
+    Rn3Entry& e = cache[i];
+    if (e.ok && e.ptr == ptr && e.rows == rows && e.W == W && e.C == C) {
+      e.stamp = ++clock_;
+      memcpy(maps->m[l], e.m, sizeof(e.m));
+      return 1;
+    }
+    if (e.stamp < cache[victim].stamp) victim = i;
+  }
+  Rn3Entry& e = cache[victim];
+  e.ok = 0;
+  const cuuint64_t gdim[3] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)rows};
+  const cuuint64_t gstride[2] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  for (int wi = 0; wi < RN3_NW; ++wi)
+    for (int ci = 0; ci < RN3_NCG; ++ci) {
+      const cuuint32_t box[3] = {(cuuint32_t)(32 >> ci), (cuuint32_t)rn3_widths_h[wi], 1u};
+      const CUresult r = enc(&e.m[wi][ci], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr), gdim,
+                             gstride, box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) return 0;
+    }
+  e.ptr = ptr;
+  e.rows = rows;
+  e.W = W;
+  e.C = C;
+  e.ok = 1;
+  e.stamp = ++clock_;
+  memcpy(maps->m[l], e.m, sizeof(e.m));
+  return 1;
 }
 
 }  // namespace
@@ -442,12 +596,33 @@ int rn_forward_nhwc(const RtLevels& lv, int N, int C, const float* rois, const i
   for (int l = 0; l < lv.L && sep; ++l)
     if ((reinterpret_cast<uintptr_t>(lv.feat[l]) & 15) != 0) sep = false;
   if (sep) {
-    const int tile_bytes = rp_env_int("RP_NHWC_TILE_KB", 48) * 1024;
+    const int tile_bytes = rp_env_int("RP_NHWC_TILE_KB", 40) * 1024;
     const int c_per_cta = rp_env_int("RP_NHWC_CPC", 128);
-    const size_t smem2 = ((RN2_TABLE_BYTES + 15) & ~15) + (size_t)tile_bytes;
+    const size_t smem2 = (size_t)RN2_TABLE_BYTES + 128 + (size_t)tile_bytes;
     if (tile_bytes < 1024 || smem2 > 200 * 1024 || c_per_cta < 4 || (c_per_cta & 3)) return RP_E_ARG;
-    RP_SET_MAX_SMEM(rn2_pool_fwd_nhwc_kernel, smem2);
     dim3 grid2((unsigned)K, (unsigned)((C + c_per_cta - 1) / c_per_cta));
+    if (rp_env_int("RP_NHWC_TMA", 0) && lv.L <= RN3_MAXL) {
+      // opt-in: two tile buffers filled by TMA (measured: no faster than cp.async);
+      // falls through to the cp.async kernel if a map cannot be made
+      const int buf_bytes = rp_env_int("RP_NHWC_TMA_KB", 32) * 1024;
+      const size_t smem3 = (size_t)RN2_TABLE_BYTES + 128 + 2 * (size_t)buf_bytes;
+      static Rn3Maps maps;  // (guarded: filled and passed by value under the lock)
+      static std::mutex maps_mu;
+      bool ok = buf_bytes >= 1024 && smem3 <= 200 * 1024;
+      std::unique_lock<std::mutex> lock(maps_mu);
+      for (int l = 0; l < lv.L && ok; ++l)
+        ok = rn3_level_maps(&maps, l, lv.feat[l], (long long)N * lv.H[l], lv.W[l], C) != 0;
+      if (ok) {
+        RP_SET_MAX_SMEM(rn3_pool_fwd_nhwc_kernel, smem3);
+        rn3_pool_fwd_nhwc_kernel<<<grid2, RN2_THREADS, smem3, st>>>(lv, N, C, rois, levels, PH, PW,
+                                                                     sampling_ratio, out, c_per_cta, buf_bytes,
+                                                                     maps);
+        lock.unlock();
+        RP_LAUNCH_CHECK();
+        return RP_OK;
+      }
+    }
+    RP_SET_MAX_SMEM(rn2_pool_fwd_nhwc_kernel, smem2);
     rn2_pool_fwd_nhwc_kernel<<<grid2, RN2_THREADS, smem2, st>>>(lv, N, C, rois, levels, PH, PW, sampling_ratio,
                                                                  out, c_per_cta, tile_bytes);
     RP_LAUNCH_CHECK();

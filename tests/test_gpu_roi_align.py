@@ -267,3 +267,28 @@ def test_channels_last_pooler_matches_oracle():
     xs = [T(f).contiguous(memory_format=torch.channels_last) for f in feats]
     got = rp.pooler_forward(xs, synth.FPN_SCALES, T(rois), T(lv), (14, 14), 2).cpu().numpy()
     _close(got, exp)
+
+
+def test_channels_last_tma_variant_matches_oracle(monkeypatch):
+    # RP_NHWC_TMA=1: the tile of every chunk arrives by cp.async.bulk.tensor boxes into two buffers
+    monkeypatch.setenv("RP_NHWC_TMA", "1")
+    rp.reload_env()
+    try:
+        N, C = 2, 72
+        feats = synth.fpn_features(N, C)
+        rois = synth.rois_for_images(N, 300)
+        lv = oracle.level_map(rois[:, 1:], 2, 5)
+        xs = [T(f).contiguous(memory_format=torch.channels_last) for f in feats]
+        for P in ((14, 14), (7, 7)):
+            exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, P, 2)
+            got = rp.pooler_forward(xs, synth.FPN_SCALES, T(rois), T(lv), P, 2).cpu().numpy()
+            _close(got, exp)
+        rng = np.random.default_rng(4)
+        feat = rng.standard_normal((N, 64, 50, 84)).astype(np.float32)
+        r2 = _rois(rng, 150, N)  # includes RoIs wider than every box width and outside the map
+        exp = oracle.roi_align_forward(feat, r2, (14, 14), 1 / 16, 2)
+        x = T(feat).contiguous(memory_format=torch.channels_last)
+        _close(rp.roi_align_forward(x, T(r2), (14, 14), 1 / 16, 2).cpu().numpy(), exp)
+    finally:
+        monkeypatch.delenv("RP_NHWC_TMA")
+        rp.reload_env()
