@@ -450,7 +450,7 @@ constexpr int PF_CHUNK = 16384;
 __global__ void __launch_bounds__(PM_THREADS)
 paste_masks_flat_kernel(const float* __restrict__ masks, const float* __restrict__ boxes, int M,
                         int im_h, int im_w, float thresh, int padding, float scale,
-                        uint8_t* __restrict__ out) {
+                        uint8_t* __restrict__ out, int sub, int chunk) {
   __shared__ float pad_s[PM_MAXP * PM_MAXP];
   const int tid = threadIdx.x;
   const int i = blockIdx.y;
@@ -470,52 +470,68 @@ paste_masks_flat_kernel(const float* __restrict__ masks, const float* __restrict
   const int x_0 = max(bx0, 0), x_1 = min(min(bx1 + 1, im_w), bx0 + w);
   const int y_0 = max(by0, 0), y_1 = min(min(by1 + 1, im_h), by0 + h);
   const int plane = im_h * im_w;
-  const int f0 = blockIdx.x * PF_CHUNK;
-  const int f1 = min(plane, f0 + PF_CHUNK);
   uint8_t* out_i = out + (size_t)i * plane;
-  const int Yfirst = f0 / im_w, Ylast = (f1 - 1) / im_w;
-  const bool touches = (Yfirst < y_1) && (Ylast >= y_0) && (x_0 < x_1);
-  if (!touches) {
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) __stcs(reinterpret_cast<uint4*>(out_i + f), z);
-    return;
-  }
-  for (int t = tid; t < P * P; t += PM_THREADS) {
-    const int py = t / P, px = t - py * P;
-    const int my = py - padding, mx = px - padding;
-    pad_s[t] = (my >= 0 && my < M && mx >= 0 && mx < M) ? __ldg(masks + ((size_t)i * M + my) * M + mx) : 0.f;
-  }
-  __syncthreads();
   const float sy = (float)P / (float)h, sx = (float)P / (float)w;
-  for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) {
-    int Y = f / im_w;
-    int X = f - Y * im_w;
-    uint32_t word[4] = {0u, 0u, 0u, 0u};
-    // rows of this 16-byte group: Y (and Y + 1 when the group wraps)
-    if ((Y < y_1 && Y >= y_0 && X < x_1 && X + 15 >= x_0) || (X + 15 >= im_w && Y + 1 < y_1 && Y + 1 >= y_0)) {
-      MkTap yt = mk_tap(Y - by0, sy, P);
-      bool row_in = Y >= y_0 && Y < y_1;
+  bool staged = false;
+  // `sub` consecutive chunks per CTA: the box arithmetic above (a dependent global load) is paid once
+  // per `sub * PF_CHUNK` bytes, and a launch has few enough CTAs to be resident at once
+  for (int cb = 0; cb < sub; ++cb) {
+    const int f0 = (blockIdx.x * sub + cb) * chunk;
+    if (f0 >= plane) break;
+    const int f1 = min(plane, f0 + chunk);
+    const int Yfirst = f0 / im_w, Ylast = (f1 - 1) / im_w;
+    const bool touches = (Yfirst < y_1) && (Ylast >= y_0) && (x_0 < x_1);
+    if (!touches) {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) __stcs(reinterpret_cast<uint4*>(out_i + f), z);
+      continue;
+    }
+    if (!staged) {  // (CTA-uniform)
+      for (int t = tid; t < P * P; t += PM_THREADS) {
+        const int py = t / P, px = t - py * P;
+        const int my = py - padding, mx = px - padding;
+        pad_s[t] = (my >= 0 && my < M && mx >= 0 && mx < M) ? __ldg(masks + ((size_t)i * M + my) * M + mx) : 0.f;
+      }
+      __syncthreads();
+      staged = true;
+    }
+    // zero the whole chunk at fill speed, then (after a barrier: same bytes, other threads) write the
+    // box pixels of the chunk's rows, spread evenly over the threads in groups of 4 pixels -- only
+    // 1-2 % of an image lies inside a box, and a thread that met a box while walking its own 16-byte
+    // groups used to hold the whole CTA back
+    {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      for (int f = f0 + tid * 16; f < f1; f += PM_THREADS * 16) __stcs(reinterpret_cast<uint4*>(out_i + f), z);
+    }
+    __syncthreads();
+    const int Ya = max(y_0, Yfirst), Yb = min(y_1 - 1, Ylast);
+    const int gpr = (x_1 - x_0 + 3) >> 2;  // groups per row
+    for (int t = tid; t < (Yb - Ya + 1) * gpr; t += PM_THREADS) {
+      const int ry = t / gpr, g = t - ry * gpr;
+      const int Y = Ya + ry, X0 = x_0 + 4 * g;
+      const MkTap yt = mk_tap(Y - by0, sy, P);
+      const float* r0 = pad_s + yt.i0 * P;
+      const float* r1 = pad_s + yt.i1 * P;
+      const int fb = Y * im_w + X0;
+      uint32_t packed = 0u;
 #pragma unroll
-      for (int q = 0; q < 16; ++q) {
-        if (row_in && X >= x_0 && X < x_1) {
+      for (int q = 0; q < 4; ++q) {
+        const int X = X0 + q;
+        if (X < x_1 && fb + q >= f0 && fb + q < f1) {
           const MkTap xt = mk_tap(X - bx0, sx, P);
-          const float* r0 = pad_s + yt.i0 * P;
-          const float* r1 = pad_s + yt.i1 * P;
           const float top = xt.w0 * r0[xt.i0] + xt.w1 * r0[xt.i1];
           const float bot = xt.w0 * r1[xt.i0] + xt.w1 * r1[xt.i1];
           const float v = yt.w0 * top + yt.w1 * bot;
           const bool on = (thresh >= 0.f) ? (v > thresh) : ((v * 255.0f) != 0.0f);
-          if (on) word[q >> 2] |= 1u << (8 * (q & 3));
-        }
-        if (++X == im_w) {
-          X = 0;
-          ++Y;
-          row_in = Y >= y_0 && Y < y_1;
-          if (row_in) yt = mk_tap(Y - by0, sy, P);
+          if (on) packed |= 1u << (8 * q);
         }
       }
+      if (packed) {  // (pixels that are off, or outside the chunk, are zero already / not ours)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if ((packed >> (8 * q)) & 1u) out_i[fb + q] = (uint8_t)1;
+      }
     }
-    __stcs(reinterpret_cast<uint4*>(out_i + f), make_uint4(word[0], word[1], word[2], word[3]));
   }
 }
 
@@ -644,9 +660,14 @@ int rp_paste_masks(const float* masks, const float* boxes, int n, int M, int im_
   const long long plane = (long long)im_h * im_w;
   if ((plane & 15) == 0 && im_w >= 16 && plane < 0x7fff0000LL && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
       rp_env_int("RP_PASTE_FLAT", 1)) {
-    dim3 grid((unsigned)((plane + PF_CHUNK - 1) / PF_CHUNK), (unsigned)n);
+    int sub = rp_env_int("RP_PASTE_SUB", 1);
+    if (sub < 1) sub = 1;
+    int chunk = rp_env_int("RP_PASTE_CHUNK", PF_CHUNK);
+    if (chunk < 4096 || (chunk & 4095)) chunk = PF_CHUNK;  // whole passes of 256 threads x 16 bytes
+    const long long per_cta = (long long)chunk * sub;
+    dim3 grid((unsigned)((plane + per_cta - 1) / per_cta), (unsigned)n);
     paste_masks_flat_kernel<<<grid, PM_THREADS, 0, (cudaStream_t)stream>>>(masks, boxes, M, im_h, im_w,
-                                                                            thresh, padding, scale, out);
+                                                                            thresh, padding, scale, out, sub, chunk);
     RP_LAUNCH_CHECK();
     return RP_OK;
   }
