@@ -484,6 +484,8 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
 constexpr int RT3_TABLE_BYTES =
     sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX;
 
+#include "roi_fwd_mma.cuh"  // rm_pool_fwd_kernel: both passes on the warp-level tensor path
+
 template <int U, bool LEAN>
 __global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
@@ -1769,6 +1771,26 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     return RP_OK;
   }
   if (l.smem_fwd > 227 * 1024) return RP_E_LIMIT;
+  if (rp_env_int("RP_ROI_IMPL", RP_ROI_IMPL_DEFAULT) == 7 && PH <= 16 && PW <= 16 &&
+      l.threads_fwd == RM_THREADS) {
+    // chained-MMA kernel (roi_fwd_mma.cuh); tiles it does not take run the tile-walk body in the same CTA
+    const size_t smem = RM_SMEM_BYTES > l.smem_fwd ? RM_SMEM_BYTES : l.smem_fwd;
+    int cpc = rp_env_int("RP_ROI_MMA_CPC", 128);
+    if (cpc < 8) cpc = 8;
+    if (cpc > C) cpc = C;
+    dim3 grid((unsigned)K, (unsigned)((C + cpc - 1) / cpc));
+    if (rp_env_int("RP_ROI_MMA_MODE", 0) == 0) {  // 0: bf16 correction product, 1: 3xTF32
+      RP_SET_MAX_SMEM(rm_pool_fwd_kernel<0>, smem);
+      rm_pool_fwd_kernel<0><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
+                                                             out, cpc, l.tile_floats, l.gpb, l.gw);
+    } else {
+      RP_SET_MAX_SMEM(rm_pool_fwd_kernel<1>, smem);
+      rm_pool_fwd_kernel<1><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
+                                                             out, cpc, l.tile_floats, l.gpb, l.gw);
+    }
+    RP_LAUNCH_CHECK();
+    return RP_OK;
+  }
   switch (l.U) {
     case 1: return rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
     case 4: return rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
