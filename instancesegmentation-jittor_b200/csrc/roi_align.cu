@@ -1782,11 +1782,11 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     if (rp_env_int("RP_ROI_MMA_MODE", 0) == 0) {  // 0: bf16 correction product, 1: 3xTF32
       RP_SET_MAX_SMEM(rm_pool_fwd_kernel<0>, smem);
       rm_pool_fwd_kernel<0><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
-                                                             out, cpc, l.tile_floats, l.gpb, l.gw);
+                                                             out, cpc, l.tile_floats, l.gpb, l.gw, rp_env_int("RP_ROI_MMA_ABLATE", 0));
     } else {
       RP_SET_MAX_SMEM(rm_pool_fwd_kernel<1>, smem);
       rm_pool_fwd_kernel<1><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
-                                                             out, cpc, l.tile_floats, l.gpb, l.gw);
+                                                             out, cpc, l.tile_floats, l.gpb, l.gw, rp_env_int("RP_ROI_MMA_ABLATE", 0));
     }
     RP_LAUNCH_CHECK();
     return RP_OK;

@@ -37,12 +37,15 @@
 // difference for NON-FINITE feature values: a dense product spreads an Inf / NaN inside the
 // tile to every bin of its row / column block, the reference only to the bins that sample it.
 
+// row pitch (floats) of a staged tile of KX column blocks: 8 or 24 mod 32, >= 8 * KX
+#define RM_PITCH(KX) ((KX) == 1 ? 8 : ((KX) <= 3 ? 24 : ((KX) <= 5 ? 40 : 56)))
 constexpr int RM_WARPS = 8;
 constexpr int RM_THREADS = RM_WARPS * 32;
-constexpr int RM_KMAX = 4;                   // 8-row / 8-column blocks per tile axis
-constexpr int RM_WARP_FLOATS = 2560;         // private staging ring of one warp (10 KB)
-constexpr int RM_WY_PITCH = 36, RM_WX_PITCH = 20;  // fragment loads of a warp hit distinct banks
-constexpr int RM_W_FLOATS = 16 * RM_WY_PITCH + 32 * RM_WX_PITCH;  // Wy[16][36] | Wx[32][20]
+constexpr int RM_KMAX = 6;                   // 8-row / 8-column blocks per tile axis
+constexpr int RM_WARP_FLOATS = 3072;         // private staging ring of one warp (12 KB)
+constexpr int RM_WY_PITCH = RM_KMAX * 8 + 4, RM_WX_PITCH = 20;  // fragment loads of a warp hit distinct banks
+constexpr int RM_W_FLOATS = 16 * RM_WY_PITCH + RM_KMAX * 8 * RM_WX_PITCH;  // Wy[16][52] | Wx[48][20]
+constexpr int RM_BFRAG_U4 = RM_KMAX * 2 * 32;  // x-product B fragments: [column block][pw block][lane] x 16 bytes
 
 __device__ __forceinline__ void rm_mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                             uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -149,9 +152,22 @@ struct RmRoi {
   int nch, R, W, vecw, P, PW;
   uint32_t chp4;     // channel-buffer pitch in bytes
   int nst;           // ring depth
+  int ablate;        // timing experiments (results wrong): 1 = stage the first channels only, 2 = no stores
   uint32_t ring;     // this warp's ring (shared address)           [per warp]
-  uint32_t wy, wx;   // shared addresses of Wy[16][36], Wx[32][20]
+  uint32_t wy;       // shared address of Wy[16][RM_WY_PITCH]
+  uint32_t bfrag;    // shared address of the x-product B fragments (this lane's slot of pair 0)
+  uint32_t band;     // bit xb*2+pb: the (column block, pw block) pair has a nonzero weight
 };
+
+// Channels a warp works on at once.  Two (for tiles small enough for four ring buffers and a second set
+// of accumulators: KY <= 4 && 4 * KY * 8 * RM_PITCH(KX) <= RM_WARP_FLOATS) was measured SLOWER on the
+// headline workload (2.33 against 2.13 ms), so one; the loop is written for any U.
+#ifndef RM_UNROLL2
+#define RM_UNROLL2 0
+#endif
+__host__ __device__ constexpr int rm_unroll(int KY, int KX) {
+  return (RM_UNROLL2 && KY <= 4 && 4 * KY * 8 * RM_PITCH(KX) <= RM_WARP_FLOATS) ? 2 : 1;
+}
 
 // The steady state of one warp for a tile of KY x KX blocks.
 template <int MODE, int KY, int KX>
@@ -187,22 +203,9 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
       ab[yb][3] = __float_as_uint(l11);
     }
   }
-  // x-product B = Wx (8 x 8 per (column block, pw block)): k-slot q <-> column 2q, slot q+4 <->
-  // column 2q+1 of the block (the order the y-product's accumulator holds them); n = g.
-  uint32_t bh[KX][2][2], bb[KX][2][2];
-  uint32_t band = 0;  // bit xb*2+pb: the block has a nonzero weight
-#pragma unroll
-  for (int xb = 0; xb < KX; ++xb)
-#pragma unroll
-    for (int pb = 0; pb < 2; ++pb) {
-      const uint32_t base = r.wx + 4u * (uint32_t)((xb * 8 + 2 * q) * RM_WX_PITCH + pb * 8 + g);
-      const float w0 = rm_lds(base), w1 = rm_lds(base + 4u * RM_WX_PITCH);
-      float l0, l1;
-      rm_split<0>(w0, bh[xb][pb][0], l0);
-      rm_split<0>(w1, bh[xb][pb][1], l1);
-      rm_corr_b<MODE>(w0, w1, l0, l1, bb[xb][pb]);
-      if (__any_sync(0xffffffffu, w0 != 0.f || w1 != 0.f)) band |= 1u << (xb * 2 + pb);
-    }
+  // x-product B = Wx: built once per CTA in shared memory (rm_build_bfrags), one 16-byte load per
+  // (column block, pw block) pair inside the band.
+  const uint32_t band = r.band;
 
   // ---- output addressing: (ph, pw) = (g | g+8, pb*8 + 2q | +1) ------------------------------
   const int PW = r.PW;
@@ -219,20 +222,26 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
       if (ph < PH && pw + 1 < PW) okm |= 2u << (2 * (pb * 2 + h));
     }
 
-  // ---- channel ring ---------------------------------------------------------------------------
-  constexpr uint32_t pitch4 = 4u * (KX == 1 ? 8 : (KX <= 3 ? 24 : 40));
-  const int nst = r.nst;
+  // ---- channel ring: U channels per iteration (independent instruction streams for the scheduler) ----
+  constexpr uint32_t pitch4 = 4u * RM_PITCH(KX);
+  constexpr int U = rm_unroll(KY, KX);
+  const int nst = r.nst;  // ring slots of U buffers each
   const int nmine = (r.nch - warp + RM_WARPS - 1) / RM_WARPS;  // channels warp, warp + 8, ...
+  const int niter = (nmine + U - 1) / U;
   const float* gnext = r.src + (size_t)warp * r.HW;  // next channel to stage
   const size_t cstep = (size_t)RM_WARPS * r.HW;
-  const uint32_t ring_end = r.ring + (uint32_t)nst * r.chp4;
+  const uint32_t ring_end = r.ring + (uint32_t)(nst * U) * r.chp4;
   uint32_t snext = r.ring;  // buffer of the next channel to stage
-  int staged = 0;
-  for (; staged < nst - 1; ++staged) {
-    if (staged < nmine) rm_stage_any(r.vecw, snext, gnext, st);
+  int staged = 0;           // channels staged so far
+  for (int sl = 0; sl < nst - 1; ++sl) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (staged < nmine) rm_stage_any(r.vecw, snext, gnext, st);
+      ++staged;
+      gnext += cstep;
+      snext += r.chp4;
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    gnext += cstep;
-    snext += r.chp4;
   }
   // B-fragment addresses inside a buffer: rows q and q+4 of the row block, column g of the column block
   const uint32_t frag = 4u * (uint32_t)g + (uint32_t)q * pitch4;
@@ -240,13 +249,17 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
   const uint32_t scur_end = ring_end + frag;
   float* optr = r.out + (size_t)warp * r.P;
   const size_t ostep = (size_t)RM_WARPS * r.P;
+  int left = nmine;  // channels not yet computed
 #pragma unroll 1
-  for (int i = 0; i < nmine; ++i) {
-    if (staged < nmine) rm_stage_any(r.vecw, snext, gnext, st);
+  for (int i = 0; i < niter; ++i) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (staged < nmine && !(r.ablate & 1)) rm_stage_any(r.vecw, snext, gnext, st);
+      ++staged;
+      gnext += cstep;
+      snext += r.chp4;
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    ++staged;
-    gnext += cstep;
-    snext += r.chp4;
     if (snext == ring_end) snext = r.ring;
     if (nst == 2)
       asm volatile("cp.async.wait_group 1;" ::: "memory");
@@ -256,69 +269,95 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
       asm volatile("cp.async.wait_group 3;" ::: "memory");
     __syncwarp();
     const uint32_t t0 = scur;
-    scur += r.chp4;
+    scur += (uint32_t)U * r.chp4;
     if (scur == scur_end) scur = r.ring + frag;
 
-    float o[2][4];
+    float o[U][2][4];
 #pragma unroll
-    for (int pb = 0; pb < 2; ++pb)
+    for (int u = 0; u < U; ++u)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) o[pb][e] = 0.f;
+      for (int pb = 0; pb < 2; ++pb)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[u][pb][e] = 0.f;
 #pragma unroll
     for (int xb = 0; xb < KX; ++xb) {
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      float v[U][4];
 #pragma unroll
-      for (int yb = 0; yb < KY; ++yb) {
-        const uint32_t a = t0 + 32u * xb + (uint32_t)(yb * 8) * pitch4;
-        const float e0 = rm_lds(a), e1 = rm_lds(a + 4u * pitch4);
-        uint32_t th[2], tc[2];
-        float l0, l1;
-        rm_split<MODE>(e0, th[0], l0);
-        rm_split<MODE>(e1, th[1], l1);
-        rm_corr_b<MODE>(e0, e1, l0, l1, tc);
-        rm_block<MODE>(v, ah[yb], ab[yb], th, tc);
-      }
-      // v = V[ph = g | g+8][column 2q | 2q+1 of block xb] -> A operand of the x-product
-      // (tf32 fragment order a0..a3 = v0, v2, v1, v3)
-      uint32_t vh[4], vc[4];
-      float vl[4];
-      rm_split<MODE>(v[0], vh[0], vl[0]);
-      rm_split<MODE>(v[2], vh[1], vl[1]);
-      rm_split<MODE>(v[1], vh[2], vl[2]);
-      rm_split<MODE>(v[3], vh[3], vl[3]);
-      if (MODE == 0) {
-        vc[0] = rm_pack_bf16(vl[0], vl[2]);
-        vc[1] = rm_pack_bf16(vl[1], vl[3]);
-        vc[2] = rm_pack_bf16(v[0], v[1]);
-        vc[3] = rm_pack_bf16(v[2], v[3]);
-      } else {
+      for (int u = 0; u < U; ++u) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) vc[e] = __float_as_uint(vl[e]);
-      }
+        for (int e = 0; e < 4; ++e) v[u][e] = 0.f;
 #pragma unroll
-      for (int pb = 0; pb < 2; ++pb)
-        if (band & (1u << (xb * 2 + pb))) rm_block<MODE>(o[pb], vh, vc, bh[xb][pb], bb[xb][pb]);
-    }
-    float* p0 = optr + ooff0;
-    float* p1 = optr + ooff1;
-    if (pair) {
-      if (okm & 0x01u) asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" ::"l"(p0), "f"(o[0][0]), "f"(o[0][1]) : "memory");
-      if (okm & 0x04u) asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" ::"l"(p1), "f"(o[0][2]), "f"(o[0][3]) : "memory");
-      if (okm & 0x10u) asm volatile("st.global.cs.v2.f32 [%0+32], {%1, %2};" ::"l"(p0), "f"(o[1][0]), "f"(o[1][1]) : "memory");
-      if (okm & 0x40u) asm volatile("st.global.cs.v2.f32 [%0+32], {%1, %2};" ::"l"(p1), "f"(o[1][2]), "f"(o[1][3]) : "memory");
-    } else {
-#pragma unroll
-      for (int pb = 0; pb < 2; ++pb)
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          float* p = (h ? p1 : p0) + 8 * pb;
-          const int sh = 2 * (pb * 2 + h);
-          if (okm & (1u << sh)) asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(o[pb][2 * h]) : "memory");
-          if (okm & (2u << sh)) asm volatile("st.global.cs.f32 [%0+4], %1;" ::"l"(p), "f"(o[pb][2 * h + 1]) : "memory");
+        for (int yb = 0; yb < KY; ++yb) {
+          const uint32_t a = t0 + (uint32_t)u * r.chp4 + 32u * xb + (uint32_t)(yb * 8) * pitch4;
+          const float e0 = rm_lds(a), e1 = rm_lds(a + 4u * pitch4);
+          uint32_t th[2], tc[2];
+          float l0, l1;
+          rm_split<MODE>(e0, th[0], l0);
+          rm_split<MODE>(e1, th[1], l1);
+          rm_corr_b<MODE>(e0, e1, l0, l1, tc);
+          rm_block<MODE>(v[u], ah[yb], ab[yb], th, tc);
         }
+      }
+      // the B fragments of this column block (shared by the U channels)
+      uint32_t bh[2][2], bc[2][2];
+#pragma unroll
+      for (int pb = 0; pb < 2; ++pb)
+        if (band & (1u << (xb * 2 + pb)))
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(bh[pb][0]), "=r"(bh[pb][1]), "=r"(bc[pb][0]), "=r"(bc[pb][1])
+                       : "r"(r.bfrag + 512u * (uint32_t)(xb * 2 + pb)));
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        // v = V[ph = g | g+8][column 2q | 2q+1 of block xb] -> A operand of the x-product
+        // (tf32 fragment order a0..a3 = v0, v2, v1, v3)
+        uint32_t vh[4], vc[4];
+        float vl[4];
+        rm_split<MODE>(v[u][0], vh[0], vl[0]);
+        rm_split<MODE>(v[u][2], vh[1], vl[1]);
+        rm_split<MODE>(v[u][1], vh[2], vl[2]);
+        rm_split<MODE>(v[u][3], vh[3], vl[3]);
+        if (MODE == 0) {
+          vc[0] = rm_pack_bf16(vl[0], vl[2]);
+          vc[1] = rm_pack_bf16(vl[1], vl[3]);
+          vc[2] = rm_pack_bf16(v[u][0], v[u][1]);
+          vc[3] = rm_pack_bf16(v[u][2], v[u][3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) vc[e] = __float_as_uint(vl[e]);
+        }
+#pragma unroll
+        for (int pb = 0; pb < 2; ++pb)
+          if (band & (1u << (xb * 2 + pb))) rm_block<MODE>(o[u][pb], vh, vc, bh[pb], bc[pb]);
+      }
     }
-    optr += ostep;
-    __syncwarp();  // every lane is done reading the buffer that the next iteration's copies overwrite
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (u < left) {
+        float* p0 = optr + ooff0;
+        float* p1 = optr + ooff1;
+        if (r.ablate & 2) {
+          if (o[u][0][0] + o[u][0][1] + o[u][0][2] + o[u][0][3] + o[u][1][0] + o[u][1][1] + o[u][1][2] + o[u][1][3] == 12345.678f) *p0 = 0.f;
+        } else if (pair) {
+          if (okm & 0x01u) asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" ::"l"(p0), "f"(o[u][0][0]), "f"(o[u][0][1]) : "memory");
+          if (okm & 0x04u) asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" ::"l"(p1), "f"(o[u][0][2]), "f"(o[u][0][3]) : "memory");
+          if (okm & 0x10u) asm volatile("st.global.cs.v2.f32 [%0+32], {%1, %2};" ::"l"(p0), "f"(o[u][1][0]), "f"(o[u][1][1]) : "memory");
+          if (okm & 0x40u) asm volatile("st.global.cs.v2.f32 [%0+32], {%1, %2};" ::"l"(p1), "f"(o[u][1][2]), "f"(o[u][1][3]) : "memory");
+        } else {
+#pragma unroll
+          for (int pb = 0; pb < 2; ++pb)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float* p = (h ? p1 : p0) + 8 * pb;
+              const int sh = 2 * (pb * 2 + h);
+              if (okm & (1u << sh)) asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(o[u][pb][2 * h]) : "memory");
+              if (okm & (2u << sh)) asm volatile("st.global.cs.f32 [%0+4], %1;" ::"l"(p), "f"(o[u][pb][2 * h + 1]) : "memory");
+            }
+        }
+      }
+      optr += ostep;
+    }
+    left -= U;
+    __syncwarp();  // every lane is done reading the buffers that the next iteration's copies overwrite
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
@@ -329,7 +368,30 @@ __device__ __forceinline__ void rm_dispatch_kx(int KX, const RmRoi& r, const RmS
     case 1: rm_channels<MODE, KY, 1>(r, st); break;
     case 2: rm_channels<MODE, KY, 2>(r, st); break;
     case 3: rm_channels<MODE, KY, 3>(r, st); break;
-    default: rm_channels<MODE, KY, 4>(r, st); break;
+    case 4: rm_channels<MODE, KY, 4>(r, st); break;
+    case 5: rm_channels<MODE, KY, 5>(r, st); break;
+    default: rm_channels<MODE, KY, 6>(r, st); break;
+  }
+}
+
+// The x-product B fragments of every (column block, pw block) pair, written once per CTA: pair p is
+// built by warp p % 8; k-slot q <-> column 2q, slot q+4 <-> column 2q+1 of the block (the order the
+// y-product's accumulator holds them); n = g.  Returns nothing; *band_s collects the nonzero pairs.
+template <int MODE>
+__device__ __forceinline__ void rm_build_bfrags(const float* wx, uint4* bfrag, int KX, int* band_s) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, q = lane & 3;
+  for (int p = warp; p < 2 * KX; p += RM_WARPS) {
+    const int xb = p >> 1, pb = p & 1;
+    const float* w = wx + (xb * 8 + 2 * q) * RM_WX_PITCH + pb * 8 + g;
+    const float w0 = w[0], w1 = w[RM_WX_PITCH];
+    uint32_t bh[2], bc[2];
+    float l0, l1;
+    rm_split<0>(w0, bh[0], l0);
+    rm_split<0>(w1, bh[1], l1);
+    rm_corr_b<MODE>(w0, w1, l0, l1, bc);
+    bfrag[p * 32 + lane] = make_uint4(bh[0], bh[1], bc[0], bc[1]);
+    if (__any_sync(0xffffffffu, w0 != 0.f || w1 != 0.f) && lane == 0) atomicOr(band_s, 1 << p);
   }
 }
 
@@ -337,15 +399,16 @@ template <int MODE>
 __global__ void __launch_bounds__(RM_THREADS, 2)
 rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int ablate) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   // layout: [tile-walk tables: ytab | xw | xo] [Wy | Wx] [8 warp rings]
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
   RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
   short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
   float* wmat = reinterpret_cast<float*>(rt_smem + RT3_TABLE_BYTES);
-  float* rings = wmat + RM_W_FLOATS;
-  __shared__ int s_ext[4];
+  uint4* bfrag = reinterpret_cast<uint4*>(wmat + RM_W_FLOATS);
+  float* rings = reinterpret_cast<float*>(bfrag + RM_BFRAG_U4);
+  __shared__ int s_ext[5];  // y: min lo, max lo; x: min lo, max lo; band bits
 
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
@@ -373,6 +436,7 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   for (int i = tid; i < RM_W_FLOATS / 4; i += RM_THREADS)
     reinterpret_cast<float4*>(wmat)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
+  if (tid == 4) s_ext[4] = 0;
   __syncthreads();
   if (fits) {
     for (int s = tid; s < SY + SX; s += RM_THREADS) {
@@ -412,7 +476,9 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   const int xa0 = x0 & ~(vecw - 1);
   const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
   const int KY = (R + 7) >> 3, KX = (twa + 7) >> 3;
-  if (!fits || KY > RM_KMAX || KX > RM_KMAX) {
+  const int pitch = RM_PITCH(KX);
+  const int chp = KY * 8 * pitch;
+  if (!fits || KY > RM_KMAX || KX > RM_KMAX || 2 * chp > RM_WARP_FLOATS || twa / vecw > 32) {
     __syncthreads();  // the tile-walk body rebuilds its tables over the same shared memory
     rt3_roi_forward<2, true>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
                              tile_floats, gpb, gw);
@@ -443,6 +509,8 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     }
   }
   __syncthreads();
+  rm_build_bfrags<MODE>(wmat + 16 * RM_WY_PITCH, bfrag, KX, &s_ext[4]);
+  __syncthreads();
 
   RmRoi r;
   r.src = lv.feat[level] + ((size_t)b * C + c_begin) * HW + (size_t)y0 * W + xa0;
@@ -454,19 +522,20 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   r.vecw = vecw;
   r.P = P;
   r.PW = PW;
-  const int pitch = KX == 1 ? 8 : (KX <= 3 ? 24 : 40);
-  const int chp = KY * 8 * pitch;
+  r.ablate = ablate;
+  r.band = (uint32_t)s_ext[4];
   r.chp4 = 4u * (uint32_t)chp;
-  int nst = RM_WARP_FLOATS / chp;
+  const int U = rm_unroll(KY, KX);
+  int nst = RM_WARP_FLOATS / (chp * U);  // ring slots of U buffers
   r.nst = nst > 4 ? 4 : nst;
   r.ring = rp_smem_addr(rings + (tid >> 5) * RM_WARP_FLOATS);
   r.wy = rp_smem_addr(wmat);
-  r.wx = rp_smem_addr(wmat + 16 * RM_WY_PITCH);
+  r.bfrag = rp_smem_addr(bfrag + (tid & 31));
 
   RmStage st;
   {
     const int lane = tid & 31;
-    const int vpr = twa / vecw;  // <= 32: twa <= 32
+    const int vpr = twa / vecw;  // <= 32 (checked above)
     const int rpw = 32 / vpr;
     const int vrow = lane / vpr;
     const int col = (lane - vrow * vpr) * vecw;
@@ -478,10 +547,10 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     // the rows / columns that pad the tile to whole blocks live in the last row / column block of
     // every ring buffer: zero them once (the copies never write them)
     const int RP = KY * 8, CP = KX * 8;
-    for (int bf = 0; bf < r.nst; ++bf) {
+    for (int bf = 0; bf < r.nst * U; ++bf) {
       float* bp = rings + (tid >> 5) * RM_WARP_FLOATS + bf * chp;
-      if (lane < CP)
-        for (int row = R; row < RP; ++row) bp[row * pitch + lane] = 0.f;
+      for (int c = lane; c < CP; c += 32)
+        for (int row = R; row < RP; ++row) bp[row * pitch + c] = 0.f;
       if (twa < CP) {
         const int c = twa + (lane & 7);
         if (c < CP)
@@ -494,9 +563,13 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     case 1: rm_dispatch_kx<MODE, 1>(KX, r, st); break;
     case 2: rm_dispatch_kx<MODE, 2>(KX, r, st); break;
     case 3: rm_dispatch_kx<MODE, 3>(KX, r, st); break;
-    default: rm_dispatch_kx<MODE, 4>(KX, r, st); break;
+    case 4: rm_dispatch_kx<MODE, 4>(KX, r, st); break;
+    case 5: rm_dispatch_kx<MODE, 5>(KX, r, st); break;
+    default: rm_dispatch_kx<MODE, 6>(KX, r, st); break;
   }
 }
 
-constexpr size_t RM_SMEM_BYTES =
-    RT3_TABLE_BYTES + sizeof(float) * (size_t)(RM_W_FLOATS + RM_WARPS * RM_WARP_FLOATS);
+constexpr size_t RM_SMEM_BYTES = RT3_TABLE_BYTES + sizeof(float) * (size_t)RM_W_FLOATS +
+                                 sizeof(uint4) * (size_t)RM_BFRAG_U4 +
+                                 sizeof(float) * (size_t)(RM_WARPS * RM_WARP_FLOATS);
+static_assert(2 * (RM_SMEM_BYTES + 1024) <= 233472, "two CTAs per SM");

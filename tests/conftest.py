@@ -17,3 +17,14 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(autouse=True)
+def _knobs_follow_the_environment():
+    """Tests that set RP_* knobs (monkeypatch + reload_env) must not leak them: the library reads its
+    knob table once, so after every test that loaded it the table is re-read from the restored
+    environment (this fixture is set up first, hence torn down after monkeypatch)."""
+    yield
+    mod = sys.modules.get("instancesegmentation_jittor_b200._lib")
+    if mod is not None and getattr(mod, "_lib", None) is not None:
+        mod.reload_env()

@@ -166,12 +166,13 @@ def test_full_size_properties():
     assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), abs(rhs), 1.0) * 10
 
 
-@pytest.mark.parametrize("impl", ["3", "4", "5", "6"])
+@pytest.mark.parametrize("impl", ["3", "4", "5", "6", "7"])
 @pytest.mark.parametrize("P,sr", [((14, 14), 2), ((7, 7), 2), ((14, 14), 0), ((3, 5), 3)])
 def test_forward_kernel_variants(impl, P, sr, monkeypatch):
     """The forward kernels (RP_ROI_IMPL=3: column walk; =4: banded, v3 body as its fallback; =5:
     merged taps, reference-order fallback; =6: tensor-core kernel for whole 8-channel groups and a fixed
-    sampling grid, the SIMT kernel otherwise; adaptive sampling always takes the column walk)
+    sampling grid, the SIMT kernel otherwise; =7: two chained warp-level matrix products, column walk for
+    tiles above 48 rows / columns; adaptive sampling always takes the column walk except in 7)
     against the oracle, on aligned (W % 4 == 0), 8-byte (W = 42) and odd-width maps."""
     monkeypatch.setenv("RP_ROI_IMPL", impl)
     rp.reload_env()
@@ -187,7 +188,7 @@ def test_forward_kernel_variants(impl, P, sr, monkeypatch):
         _close(out, exp)
 
 
-@pytest.mark.parametrize("impl", ["4", "5", "6"])
+@pytest.mark.parametrize("impl", ["4", "5", "6", "7"])
 def test_banded_pooler_multi_level(impl, monkeypatch):
     monkeypatch.setenv("RP_ROI_IMPL", impl)
     rp.reload_env()
@@ -292,3 +293,28 @@ def test_channels_last_tma_variant_matches_oracle(monkeypatch):
     finally:
         monkeypatch.delenv("RP_NHWC_TMA")
         rp.reload_env()
+
+
+@pytest.mark.parametrize("mode", ["0", "1"])
+def test_chained_mma_forward_modes(mode, monkeypatch):
+    """RP_ROI_IMPL=7 (roi_fwd_mma.cuh) in both precision modes (0: tf32 + one bf16 correction product,
+    1: 3xTF32), with channel slices that leave warps with uneven channel counts, on every tile class
+    (1..6 blocks per axis, wider tiles take the column walk) and with adaptive sampling."""
+    monkeypatch.setenv("RP_ROI_IMPL", "7")
+    monkeypatch.setenv("RP_ROI_MMA_MODE", mode)
+    rng = np.random.default_rng(5)
+    for cpc, C, (H, W) in [("8", 13, (100, 168)), ("24", 37, (50, 84)), ("256", 20, (25, 42))]:
+        monkeypatch.setenv("RP_ROI_MMA_CPC", cpc)
+        rp.reload_env()
+        feat = rng.standard_normal((2, C, H, W)).astype(np.float32)
+        K = 120
+        rois = np.zeros((K, 5), np.float32)
+        rois[:, 0] = rng.integers(0, 2, K)
+        side = np.exp(rng.uniform(np.log(4), np.log(60 * 16), (K, 2)))  # 0.25 .. 60 feature pixels
+        ctr = rng.uniform(0, 1, (K, 2)) * [W * 16, H * 16]
+        rois[:, 1:3] = ctr - side / 2
+        rois[:, 3:5] = ctr + side / 2
+        for P, sr in [((14, 14), 2), ((7, 7), 2), ((16, 16), 1), ((14, 14), 0), ((5, 9), 3)]:
+            exp = oracle.roi_align_forward(feat, rois, P, 1 / 16, sr)
+            out = rp.roi_align(T(feat), T(rois), P, 1 / 16, sr).cpu().numpy()
+            _close(out, exp)
