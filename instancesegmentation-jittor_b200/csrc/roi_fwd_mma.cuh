@@ -21,21 +21,30 @@
 // ~8 significant bits).  Dropped term lo.lo ~ 2^-22; observed error against the oracle ~1e-6
 // relative (tests: 1e-5 * |ref| + 1e-5).  Two HMMA per 16 x 8 x 8 block instead of three.
 //
-// CTA = (RoI, channel slice), 8 warps.  Set-up (whole CTA): the sample tables of the tile-walk
-// kernel, the two dense weight matrices in shared memory, then every thread pulls its constant
-// fragments into registers (Wy: A operand of the y-product, Wx: B operand of the x-product).
-// Steady state (per warp, no CTA barrier): a warp owns channels w, w + 8, ...; its lanes stage
-// the channel's tile [KY*8 rows][pitch] with cp.async into a private ring of 2-4 buffers
-// (pitch = 8 or 24 mod 32 floats: the B-fragment loads of a warp hit 32 distinct banks),
-// for every 8-column block: y-product over the KY row blocks, split, x-product into the two
-// pw blocks whose band covers the column block; finally 8-byte streaming stores.
-// Rows / columns that pad the tile to whole 8 x 8 blocks are zero-filled once and never
-// written again (they meet zero weights, but 0 x garbage could be NaN).
+// CTA = (RoI, channel slice), 8 warps, 2 CTAs per SM (126 registers: the Wy fragments of up to 6 row
+// blocks stay in registers).  Set-up (whole CTA): the sample tables of the tile-walk kernel, the two
+// dense weight matrices in shared memory, the x-product B fragments of every (column block, pw block)
+// pair in fragment order in shared memory (one 16-byte load per use), the y-product A fragments in
+// registers.  Steady state (per warp, no CTA barrier): a warp owns channels w, w + 8, ...; the
+// channel's tile [KY*8 rows][pitch] arrives in a private ring of 2-4 buffers (pitch = 8 or 24 mod 32
+// floats: the B-fragment loads of a warp hit 32 distinct banks) either as ONE TMA box per channel
+// (cp.async.bulk.tensor.3d on the warp's mbarrier; levels whose rows are 16-byte multiples; rows and
+// columns beyond the map arrive as zeros) or through cp.async copies of the lanes (other levels; the
+// rows / columns that pad the tile to whole 8 x 8 blocks are zero-filled once); for every 8-column
+// block: y-product over the KY row blocks, split, x-product into the pw blocks whose band covers the
+// column block; finally 8-byte streaming stores.
 //
-// Not taken (evaluated by the tile-walk body in the same launch): tiles above 32 rows or 32
-// (aligned) columns, PH or PW above 16, sample lattices above RT_SMAX.  One semantic
-// difference for NON-FINITE feature values: a dense product spreads an Inf / NaN inside the
-// tile to every bin of its row / column block, the reference only to the bins that sample it.
+// Not taken (evaluated by the tile-walk body in the same launch): tiles above 48 rows or 48 (aligned)
+// columns or whose double buffer exceeds the ring, PH or PW above 16, sample lattices above RT_SMAX.
+// One semantic difference for NON-FINITE feature values: a dense product spreads an Inf / NaN inside
+// the staged box to every bin of its row / column block, the reference only to the bins that sample it.
+//
+// Measured (B200, headline workload 16 x 1000 RoIs, 14x14x256; DESIGN.md 4.1, profiles/ncu_rm_fwd_r02.txt):
+// 2.08 ms (MODE 0) / 2.30 ms (MODE 1) against 2.20 ms for the tile-walk kernel, max error against the
+// oracle 7.0e-6 (MODE 0) / 2.4e-6 (MODE 1) where the tile walk has 7e-7.  The tensor pipe is 28 % busy
+// and removing the HMMAs altogether changes the time by 4 %: splitting and packing the operands
+// (VIADD, LOP3, FADD, F2FP: 140 warp instructions per (RoI, channel) of 307) costs more issue slots than
+// the FFMA + LDS of the tile walk it replaces (122).  Opt-in; not the default.
 
 // row pitch (floats) of a staged tile of KX column blocks: 8 or 24 mod 32, >= 8 * KX
 #define RM_PITCH(KX) ((KX) == 1 ? 8 : ((KX) <= 3 ? 24 : ((KX) <= 5 ? 40 : 56)))
@@ -45,7 +54,18 @@ constexpr int RM_KMAX = 6;                   // 8-row / 8-column blocks per tile
 constexpr int RM_WARP_FLOATS = 3072;         // private staging ring of one warp (12 KB)
 constexpr int RM_WY_PITCH = RM_KMAX * 8 + 4, RM_WX_PITCH = 20;  // fragment loads of a warp hit distinct banks
 constexpr int RM_W_FLOATS = 16 * RM_WY_PITCH + RM_KMAX * 8 * RM_WX_PITCH;  // Wy[16][52] | Wx[48][20]
-constexpr int RM_BFRAG_U4 = RM_KMAX * 2 * 32;  // x-product B fragments: [column block][pw block][lane] x 16 bytes
+constexpr int RM_BFRAG_U4 = RM_KMAX * 2 * 32;
+// TMA descriptors (host-encoded, roi_align.cu rm_level_maps): per level the 3-D tensor (W, H, N*C
+// planes) with one box per (row pitch class, row blocks): pitch x 8*KY x 1 plane, dense in shared
+// memory, so the box IS the [KY*8][pitch] buffer the fragments are read from; out-of-range rows and
+// columns arrive as zeros (no pad zeroing), in-range ones beyond the tile meet zero weights.
+constexpr int RM_TMA_LEVELS = 5;
+constexpr int RM_NPITCH = 4;
+struct RmMaps {
+  CUtensorMap m[RM_TMA_LEVELS][RM_NPITCH][RM_KMAX];
+  int ok[RM_TMA_LEVELS];
+};
+#define RM_PITCH_CLASS(KX) ((KX) == 1 ? 0 : ((KX) <= 3 ? 1 : ((KX) <= 5 ? 2 : 3)))  // x-product B fragments: [column block][pw block][lane] x 16 bytes
 
 __device__ __forceinline__ void rm_mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                             uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -98,6 +118,29 @@ __device__ __forceinline__ void rm_block(float (&d)[4], const uint32_t (&ah)[4],
   } else {
     rm_mma_tf32(d, ac[0], ac[1], ac[2], ac[3], bh[0], bh[1]);  // lo(A) . hi(B)
     rm_mma_tf32(d, ah[0], ah[1], ah[2], ah[3], bc[0], bc[1]);  // hi(A) . lo(B)
+  }
+}
+__device__ __forceinline__ void rm_tma_issue(uint32_t dst, const void* tmap, int x, int y, int z, uint32_t bar,
+                                             uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void rm_mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > (1u << 22)) __trap();  // a copy that never lands must not hang the GPU
   }
 }
 __device__ __forceinline__ float rm_lds(uint32_t a) {
@@ -157,6 +200,9 @@ struct RmRoi {
   uint32_t wy;       // shared address of Wy[16][RM_WY_PITCH]
   uint32_t bfrag;    // shared address of the x-product B fragments (this lane's slot of pair 0)
   uint32_t band;     // bit xb*2+pb: the (column block, pw block) pair has a nonzero weight
+  const void* tmap;  // TMA descriptor of this tile class, or nullptr: cp.async staging
+  int tx, ty, tz;    // box origin: column, row, plane of this warp's first channel
+  uint32_t bars;     // this warp's mbarriers, one per ring buffer (shared address)           [per warp]
 };
 
 // Channels a warp works on at once.  Two (for tiles small enough for four ring buffers and a second set
@@ -233,15 +279,28 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
   const uint32_t ring_end = r.ring + (uint32_t)(nst * U) * r.chp4;
   uint32_t snext = r.ring;  // buffer of the next channel to stage
   int staged = 0;           // channels staged so far
+  const bool tma = r.tmap != nullptr;
+  int znext = r.tz;           // plane of the next channel to stage (TMA)
+  uint32_t bnext = r.bars;    // its mbarrier
+  uint32_t bcur = r.bars;     // mbarrier of the next buffer to consume
+  const uint32_t bars_end = r.bars + 8u * (uint32_t)(nst * U);
+  uint32_t phase = 0;         // parity to wait for on bcur (flips every trip round the ring)
   for (int sl = 0; sl < nst - 1; ++sl) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      if (staged < nmine) rm_stage_any(r.vecw, snext, gnext, st);
+      if (staged < nmine) {
+        if (!tma)
+          rm_stage_any(r.vecw, snext, gnext, st);
+        else if (lane == 0)
+          rm_tma_issue(snext, r.tmap, r.tx, r.ty, znext, bnext, r.chp4);
+      }
       ++staged;
       gnext += cstep;
       snext += r.chp4;
+      znext += RM_WARPS;
+      bnext += 8u;
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (!tma) asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // B-fragment addresses inside a buffer: rows q and q+4 of the row block, column g of the column block
   const uint32_t frag = 4u * (uint32_t)g + (uint32_t)q * pitch4;
@@ -254,20 +313,41 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
   for (int i = 0; i < niter; ++i) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      if (staged < nmine && !(r.ablate & 1)) rm_stage_any(r.vecw, snext, gnext, st);
+      if (staged < nmine && !(r.ablate & 1)) {
+        if (!tma)
+          rm_stage_any(r.vecw, snext, gnext, st);
+        else if (lane == 0)
+          rm_tma_issue(snext, r.tmap, r.tx, r.ty, znext, bnext, r.chp4);
+      }
       ++staged;
       gnext += cstep;
       snext += r.chp4;
+      znext += RM_WARPS;
+      bnext += 8u;
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    if (snext == ring_end) snext = r.ring;
-    if (nst == 2)
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    else if (nst == 3)
-      asm volatile("cp.async.wait_group 2;" ::: "memory");
-    else
-      asm volatile("cp.async.wait_group 3;" ::: "memory");
-    __syncwarp();
+    if (snext == ring_end) {
+      snext = r.ring;
+      bnext = r.bars;
+    }
+    if (!tma) {
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      if (nst == 2)
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      else if (nst == 3)
+        asm volatile("cp.async.wait_group 2;" ::: "memory");
+      else
+        asm volatile("cp.async.wait_group 3;" ::: "memory");
+      __syncwarp();
+    } else if (!(r.ablate & 1) || i < nst - 1) {
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (u < left) rm_mbar_wait(bcur + 8u * u, phase);
+    }
+    bcur += 8u * U;
+    if (bcur == bars_end) {
+      bcur = r.bars;
+      phase ^= 1u;
+    }
     const uint32_t t0 = scur;
     scur += (uint32_t)U * r.chp4;
     if (scur == scur_end) scur = r.ring + frag;
@@ -359,7 +439,7 @@ __device__ __forceinline__ void rm_channels(const RmRoi& r, const RmStage& st) {
     left -= U;
     __syncwarp();  // every lane is done reading the buffers that the next iteration's copies overwrite
   }
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (!tma) asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 template <int MODE, int KY>
@@ -399,7 +479,8 @@ template <int MODE>
 __global__ void __launch_bounds__(RM_THREADS, 2)
 rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int ablate) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int ablate,
+                   const __grid_constant__ RmMaps maps) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   // layout: [tile-walk tables: ytab | xw | xo] [Wy | Wx] [8 warp rings]
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
@@ -408,7 +489,9 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   float* wmat = reinterpret_cast<float*>(rt_smem + RT3_TABLE_BYTES);
   uint4* bfrag = reinterpret_cast<uint4*>(wmat + RM_W_FLOATS);
   float* rings = reinterpret_cast<float*>(bfrag + RM_BFRAG_U4);
+  rings += ((128u - (rp_smem_addr(rings) & 127u)) & 127u) >> 2;  // TMA boxes land on 128-byte boundaries
   __shared__ int s_ext[5];  // y: min lo, max lo; x: min lo, max lo; band bits
+  __shared__ __align__(8) uint64_t s_bar[RM_WARPS][4];  // per warp: one mbarrier per ring buffer (TMA staging)
 
   const int tid = threadIdx.x;
   const int k = blockIdx.x;
@@ -524,10 +607,21 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
   r.PW = PW;
   r.ablate = ablate;
   r.band = (uint32_t)s_ext[4];
+  const bool tma = level < RM_TMA_LEVELS && maps.ok[level] && !(ablate & 4);
+  r.tmap = tma ? (const void*)&maps.m[level][RM_PITCH_CLASS(KX)][KY - 1] : nullptr;
+  r.tx = xa0;
+  r.ty = y0;
+  r.tz = b * C + c_begin + (tid >> 5);
+  r.bars = rp_smem_addr(&s_bar[tid >> 5][0]);
+  if (tma && (tid & 31) == 0) {
+    for (int i = 0; i < 4; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(r.bars + 8u * i) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   r.chp4 = 4u * (uint32_t)chp;
   const int U = rm_unroll(KY, KX);
   int nst = RM_WARP_FLOATS / (chp * U);  // ring slots of U buffers
-  r.nst = nst > 4 ? 4 : nst;
+  r.nst = nst > 4 / U ? 4 / U : nst;  // at most 4 buffers (and mbarriers) per warp
   r.ring = rp_smem_addr(rings + (tid >> 5) * RM_WARP_FLOATS);
   r.wy = rp_smem_addr(wmat);
   r.bfrag = rp_smem_addr(bfrag + (tid & 31));
@@ -547,7 +641,7 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
     // the rows / columns that pad the tile to whole blocks live in the last row / column block of
     // every ring buffer: zero them once (the copies never write them)
     const int RP = KY * 8, CP = KX * 8;
-    for (int bf = 0; bf < r.nst * U; ++bf) {
+    for (int bf = 0; bf < (tma ? 0 : r.nst * U); ++bf) {
       float* bp = rings + (tid >> 5) * RM_WARP_FLOATS + bf * chp;
       for (int c = lane; c < CP; c += 32)
         for (int row = R; row < RP; ++row) bp[row * pitch + c] = 0.f;
@@ -571,5 +665,5 @@ rm_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
 
 constexpr size_t RM_SMEM_BYTES = RT3_TABLE_BYTES + sizeof(float) * (size_t)RM_W_FLOATS +
                                  sizeof(uint4) * (size_t)RM_BFRAG_U4 +
-                                 sizeof(float) * (size_t)(RM_WARPS * RM_WARP_FLOATS);
-static_assert(2 * (RM_SMEM_BYTES + 1024) <= 233472, "two CTAs per SM");
+                                 sizeof(float) * (size_t)(RM_WARPS * RM_WARP_FLOATS) + 128;
+static_assert(2 * (RM_SMEM_BYTES + 512 + 1024) <= 233472, "two CTAs per SM");
