@@ -1,8 +1,12 @@
 """b200-roi-path: the RoI / NMS / mask hot path of Jittor/InstanceSegmentation-jittor,
 hand-written for B200 (sm_100a) behind the reference's Python call signatures.
 
-Everything here calls libroipath_b200.so through ctypes (include/roipath.h); there is no
-torch-op or CPU fallback and nothing under oracle/ is ever imported.
+Every operator of the path calls libroipath_b200.so through ctypes (include/roipath.h); no kernel has
+a torch-op or CPU fallback (a missing library raises RoiPathError) and nothing under oracle/ is ever
+imported.  torch supplies device memory, streams and, on four non-default configuration branches that
+no benchmark touches, the index glue AROUND the CUDA NMS (`Detect.traditional_nms`,
+`PostProcessor._decode_only` / `filter_results` / `filter_results_v2` on already decoded BoxLists, the
+training branch of `RPNPostProcessor.select_over_all_levels`: nonzero / stable sort / softmax on the device).
 """
 from . import _lib
 from ._lib import RoiPathError, lib, reload_env
