@@ -86,10 +86,12 @@ __device__ __forceinline__ void rm_mma_bf16(float (&d)[4], uint32_t a0, uint32_t
 //         core does to a raw fp32 operand), corrections as two more tf32 m16n8k8 (classic 3xTF32,
 //         three HMMA per block, no packing).  lo is exact in both.  The tensor core ignores the low
 //         13 bits of a tf32 operand, so hi is passed unmasked.
+// MODE 2: ONE tf32 product, no split (~1e-3 relative: NOT within the 1e-5 bar; a measurement of what the
+//         fp32 emulation costs, never selected unless RP_ROI_MMA_MODE=2 is set explicitly).
 template <int MODE>
 __device__ __forceinline__ void rm_split(float x, uint32_t& hi, float& lo) {
   hi = MODE == 0 ? __float_as_uint(x) + 0x1000u : __float_as_uint(x);
-  lo = x - __uint_as_float(hi & 0xffffe000u);
+  lo = MODE == 2 ? 0.f : x - __uint_as_float(hi & 0xffffe000u);
 }
 // {lower 16 bits = bf16(a), upper 16 bits = bf16(b)}
 __device__ __forceinline__ uint32_t rm_pack_bf16(float a, float b) {
@@ -103,6 +105,8 @@ __device__ __forceinline__ void rm_corr_b(float x0, float x1, float l0, float l1
   if (MODE == 0) {
     c[0] = rm_pack_bf16(x0, x1);  // k-slots 2q, 2q+1: meet lo(A)
     c[1] = rm_pack_bf16(l0, l1);  // k-slots 2q+8, 2q+9: meet A
+  } else if (MODE == 2) {
+    c[0] = c[1] = 0u;
   } else {
     c[0] = __float_as_uint(l0);
     c[1] = __float_as_uint(l1);
@@ -115,7 +119,7 @@ __device__ __forceinline__ void rm_block(float (&d)[4], const uint32_t (&ah)[4],
   rm_mma_tf32(d, ah[0], ah[1], ah[2], ah[3], bh[0], bh[1]);
   if (MODE == 0) {
     rm_mma_bf16(d, ac[0], ac[1], ac[2], ac[3], bc[0], bc[1]);
-  } else {
+  } else if (MODE == 1) {
     rm_mma_tf32(d, ac[0], ac[1], ac[2], ac[3], bh[0], bh[1]);  // lo(A) . hi(B)
     rm_mma_tf32(d, ah[0], ah[1], ah[2], ah[3], bc[0], bc[1]);  // hi(A) . lo(B)
   }

@@ -84,7 +84,7 @@ for res in (14, 7):
     exp = oracle.pooler_forward(fe, synth.FPN_SCALES, rois[sub].cpu().numpy(), levels[sub].cpu().numpy(), (res, res), 2)
     a = run(3, fn).clone()
     print("headline %dx%d  impl 3: %.3f ms" % (res, res, timeit(fn)))
-    for mode in ("0", "1"):
+    for mode in ("0", "1", "2"):
         for cpc in ("128", "256"):
             os.environ["RP_ROI_MMA_MODE"] = mode
             os.environ["RP_ROI_MMA_CPC"] = cpc
@@ -93,5 +93,6 @@ for res in (14, 7):
             ms = timeit(fn)
             print("  impl 7 mode %s cpc %s: %.3f ms   vs impl 3: max|diff| %.3e  max diff/(|ref|+1) %.3e"
                   % (mode, cpc, ms, float(d.max()), float((d / (a.abs() + 1)).max())))
-        fails += report("  mode %s first 64 RoIs vs oracle" % mode, b[sub].cpu().numpy(), exp)
+        bad = report("  mode %s first 64 RoIs vs oracle" % mode, b[sub].cpu().numpy(), exp)
+        fails += bad if mode != "2" else 0  # mode 2 (single tf32 product) is a measurement, not a product path
 sys.exit(1 if fails else 0)
