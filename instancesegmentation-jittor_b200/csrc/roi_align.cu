@@ -1843,10 +1843,12 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
       RP_SET_MAX_SMEM(rm_pool_fwd_kernel<0>, smem);
       rm_pool_fwd_kernel<0><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
                                                              out, cpc, l.tile_floats, l.gpb, l.gw, rp_env_int("RP_ROI_MMA_ABLATE", 0), maps);
-    } else if (rp_env_int("RP_ROI_MMA_MODE", 0) == 2) {  // single tf32 product (~1e-3): measurement only
+#ifdef RM_WITH_MODE2  // build with RP_EXTRA_NVCC=-DRM_WITH_MODE2: single tf32 product (~1e-3), measurement only
+    } else if (rp_env_int("RP_ROI_MMA_MODE", 0) == 2) {
       RP_SET_MAX_SMEM(rm_pool_fwd_kernel<2>, smem);
       rm_pool_fwd_kernel<2><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,
                                                              out, cpc, l.tile_floats, l.gpb, l.gw, rp_env_int("RP_ROI_MMA_ABLATE", 0), maps);
+#endif
     } else {
       RP_SET_MAX_SMEM(rm_pool_fwd_kernel<1>, smem);
       rm_pool_fwd_kernel<1><<<grid, RM_THREADS, smem, st>>>(lv, N, C, rois, levels, K, PH, PW, sampling_ratio,

@@ -84,7 +84,7 @@ for res in (14, 7):
     exp = oracle.pooler_forward(fe, synth.FPN_SCALES, rois[sub].cpu().numpy(), levels[sub].cpu().numpy(), (res, res), 2)
     a = run(3, fn).clone()
     print("headline %dx%d  impl 3: %.3f ms" % (res, res, timeit(fn)))
-    for mode in ("0", "1", "2"):
+    for mode in ("0", "1") + (("2",) if os.environ.get("RM_WITH_MODE2") else ()):  # mode 2 needs a -DRM_WITH_MODE2 build
         for cpc in ("128", "256"):
             os.environ["RP_ROI_MMA_MODE"] = mode
             os.environ["RP_ROI_MMA_CPC"] = cpc
