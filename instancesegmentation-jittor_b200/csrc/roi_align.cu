@@ -189,6 +189,16 @@ struct FwdGlobalSink {
   }
 };
 
+#ifndef RT_ST_POLICY
+#define RT_ST_POLICY 0  // output stores of the sample walk: 0 = streaming (.cs), 1 = plain, 2 = .cg (measured: see DESIGN 4.1)
+#endif
+#if RT_ST_POLICY == 0
+#define RT_ST_OUT(p, v) __stcs(p, v)
+#elif RT_ST_POLICY == 1
+#define RT_ST_OUT(p, v) (*(p) = (v))
+#else
+#define RT_ST_OUT(p, v) __stcg(p, v)
+#endif
 // rt_fwd_item_fsm (roi_tile.h) with the address arithmetic done by hand: the same operations on the
 // same values in the same order (bit-identical results), but
 //   * tile and sample-table accesses are ld.shared with 32-bit addresses: ONE add per (row, channel,
@@ -259,7 +269,7 @@ __device__ __forceinline__ void rt_fwd_item_fsm_s(uint32_t tile_a, uint32_t ustr
 #define RS_EMIT()                                            \
   if (e.flags & RT_F_EMIT) {                                  \
     _Pragma("unroll") for (int u = 0; u < U; ++u) {          \
-      if (u < nvalid) __stcs(op[u], acc[u] * inv);           \
+      if (u < nvalid) RT_ST_OUT(op[u], acc[u] * inv);        \
       op[u] += PW;                                           \
       acc[u] = 0.f;                                          \
     }                                                        \
