@@ -34,6 +34,9 @@ constexpr int RT_THREADS = 256;
 #ifndef RP_ROI_IMPL_DEFAULT
 #define RP_ROI_IMPL_DEFAULT 3  // forward kernel: 3 = tile walk, 4 = banded, 5 = merged taps
 #endif
+#ifndef RP_ROI_PLANES_DEFAULT
+#define RP_ROI_PLANES_DEFAULT 0  // whole-plane kernel for the coarse levels (roi_fwd_plane.cuh)
+#endif
 constexpr int RT_U1 = 4;  // channels per thread, phase 1
 constexpr int RT_U2 = 2;  // channels per thread, phase 2
 constexpr int RT_CC_CAP = 32;  // max channels per chunk (bounds the out tile)
@@ -196,8 +199,10 @@ struct FwdGlobalSink {
 #define RT_ST_OUT(p, v) __stcs(p, v)
 #elif RT_ST_POLICY == 1
 #define RT_ST_OUT(p, v) (*(p) = (v))
-#else
+#elif RT_ST_POLICY == 2
 #define RT_ST_OUT(p, v) __stcg(p, v)
+#else  // 3: timing experiment, results wrong: the value is computed but (practically) never stored
+#define RT_ST_OUT(p, v) do { const float rt_v_ = (v); if (rt_v_ == 12345.678f) *(p) = rt_v_; } while (0)
 #endif
 // rt_fwd_item_fsm (roi_tile.h) with the address arithmetic done by hand: the same operations on the
 // same values in the same order (bit-identical results), but
@@ -324,8 +329,12 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                                                 int C, const float* __restrict__ rois,
                                                 const int* __restrict__ levels, int PH, int PW,
                                                 float sampling_ratio, float* __restrict__ out,
-                                                int c_per_cta, int tile_floats, int gpb, int gw) {
+                                                int c_per_cta, int tile_floats, int gpb, int gw,
+                                                int nbuf = 1) {
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
+  // nbuf == 2: the tile buffer is cut into two halves and the copies of chunk i+1 are issued before
+  // chunk i is walked, so they fly under the walk (a timing ablation put the exposed copies at 0.6 of
+  // the kernel's 2.2 ms: DESIGN.md 4.1); a RoI whose tile does not fit a half keeps the single buffer
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
   RtW* xw_s = reinterpret_cast<RtW*>(ytab + RT_SMAX);
   short* xo_s = reinterpret_cast<short*>(xw_s + RT_SMAX);
@@ -400,7 +409,18 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   const int twa = ((xl + 1) / vecw - xa0 / vecw + 1) * vecw;
   RtTilePlan tp;
   tp.cc = 0;
-  if (fits) tp = rt_plan_tile(R, twa, tile_floats, gpb, gw, U, nch, PH);
+  int nbufs = 1, buf_floats = tile_floats;
+  if (fits && nbuf == 2) {
+    const int half = (tile_floats / 2) & ~31;
+    tp = rt_plan_tile(R, twa, half, gpb, gw, U, nch, PH);
+    if (tp.cc >= 1 && tp.cc < nch) {  // more than one chunk: worth the second buffer
+      nbufs = 2;
+      buf_floats = half;
+    } else {
+      tp.cc = 0;
+    }
+  }
+  if (fits && nbufs == 1) tp = rt_plan_tile(R, twa, tile_floats, gpb, gw, U, nch, PH);
   if (tp.cc < 1) {
     // RoI too large for the tile buffer (or a degenerate map): reference-order evaluation
     const int total = nch * P;
@@ -451,34 +471,64 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   const RbStageLane sl = rb_stage_lane(vecw, vw, twa, W, 0x7fffffff);
   const uint32_t tile_s = rp_smem_addr(tile);
 
-  for (int c0 = 0; c0 < nch; c0 += tp.cc) {
+  // copies of the chunk that starts at channel c0 into buffer b
+  auto stage_chunk = [&](int c0, int b) {
     const int cc = min(tp.cc, nch - c0);
     const float* src = src0 + (size_t)c0 * HW;
+    float* tb = tile + b * buf_floats;
+    const uint32_t tb_s = tile_s + 4u * (uint32_t)(b * buf_floats);
     if (lane_stage) {
       if (vecw == 4)
-        rb_stage_tile<4>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+        rb_stage_tile<4>(tb_s, src, cc, R, twa, W, HW, chp, sl);
       else if (vecw == 2)
-        rb_stage_tile<2>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+        rb_stage_tile<2>(tb_s, src, cc, R, twa, W, HW, chp, sl);
       else
-        rb_stage_tile<1>(tile_s, src, cc, R, twa, W, HW, chp, sl);
+        rb_stage_tile<1>(tb_s, src, cc, R, twa, W, HW, chp, sl);
     } else if (vecw == 4)
-      rt_stage_tile<4>(tile, src, cc, R, vw, magicV, W, HW, chp);
+      rt_stage_tile<4>(tb, src, cc, R, vw, magicV, W, HW, chp);
     else if (vecw == 2)
-      rt_stage_tile<2>(tile, src, cc, R, vw, magicV, W, HW, chp);
+      rt_stage_tile<2>(tb, src, cc, R, vw, magicV, W, HW, chp);
     else
-      rt_stage_tile<1>(tile, src, cc, R, vw, magicV, W, HW, chp);
-    rt_cp_async_wait_all();
+      rt_stage_tile<1>(tb, src, cc, R, vw, magicV, W, HW, chp);
+  };
+  if (nbufs == 2) {
+    stage_chunk(0, 0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  int ib = 0;
+  for (int c0 = 0; c0 < nch; c0 += tp.cc) {
+    const int cc = min(tp.cc, nch - c0);
+    if (nbufs == 2) {
+      const bool more = c0 + tp.cc < nch;
+#ifdef RT3_ABLATE_NOSTAGE
+      if (false)
+#endif
+      if (more) stage_chunk(c0 + tp.cc, ib ^ 1);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      if (more)
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      else
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    } else {
+#ifdef RT3_ABLATE_NOSTAGE  // timing experiment, results wrong: only the first chunk of a CTA is staged
+      if (c0 == 0)
+#endif
+      stage_chunk(c0, 0);
+      rt_cp_async_wait_all();
+    }
     __syncthreads();
+    const float* tile_b = tile + ib * buf_floats;
+    const uint32_t tile_bs = tile_s + 4u * (uint32_t)(ib * buf_floats);
     if (b0 < b1) {
       int nvalid = (cc - cg + tp.ncg - 1) >> ncg_shift;
       if (nvalid > U) nvalid = U;
       if (nvalid > 0) {
         FwdGlobalSink<U> sink{out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW,
                               nvalid, inv};
-        const float* tile_g = tile + cg * chp;
+        const float* tile_g = tile_b + cg * chp;
         const int ustride = tp.ncg * chp;
         if (g.gw == 2 && LEAN)
-          rt_fwd_item_fsm_s<U>(tile_s + 4u * (uint32_t)(cg * chp), 4u * (uint32_t)ustride, nvalid,
+          rt_fwd_item_fsm_s<U>(tile_bs + 4u * (uint32_t)(cg * chp), 4u * (uint32_t)ustride, nvalid,
                                rp_smem_addr(ytab), xw_s, xo_s, g.gh, 4u * (uint32_t)twa, pw, b0, b1,
                                out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW, inv);
         else if (g.gw == 2)
@@ -487,7 +537,8 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
           rt_fwd_item<0, U>(tile_g, ustride, nvalid, ytab, xw_s, xo_s, g.gh, g.gw, twa, pw, b0, b1, sink);
       }
     }
-    __syncthreads();  // the tile is overwritten by the next chunk
+    __syncthreads();  // the buffer is overwritten by the copies issued in the next iteration
+    if (nbufs == 2) ib ^= 1;
   }
 }
 
@@ -495,15 +546,18 @@ constexpr int RT3_TABLE_BYTES =
     sizeof(RtYSample) * RT_SMAX + sizeof(RtW) * RT_SMAX + sizeof(short) * RT_SMAX;
 
 #include "roi_fwd_mma.cuh"  // rm_pool_fwd_kernel: both passes on the warp-level tensor path
+#include "roi_fwd_plane.cuh"  // rp_plane_fwd_kernel: whole planes of the coarse levels staged once
 
 template <int U, bool LEAN>
 __global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
-                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw) {
+                   float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int nbuf,
+                   const int* __restrict__ skip) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
+  if (skip && skip[blockIdx.x] >= 0) return;  // taken by the whole-plane kernel (roi_fwd_plane.cuh)
   rt3_roi_forward<U, LEAN>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
-                     tile_floats, gpb, gw);
+                     tile_floats, gpb, gw, nbuf);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1708,16 +1762,17 @@ void rm_level_maps(RmMaps* maps, int l, const float* ptr, long long planes, int 
 template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
-                  cudaStream_t st) {
+                  cudaStream_t st, const int* skip = nullptr) {
   dim3 grid((unsigned)K, (unsigned)l.csplit);
+  const int nbuf = rp_env_int("RP_ROI_DBUF", 0) ? 2 : 1;  // two half-size tile buffers: copies under the walk
   if (rp_env_int("RP_ROI_LEAN", 1)) {  // hand-written shared-memory addressing in the sample walk
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, true>), l.smem_fwd);
     rt_pool_fwd_kernel<U, true><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip);
   } else {
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, false>), l.smem_fwd);
     rt_pool_fwd_kernel<U, false><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw);
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip);
   }
   RP_LAUNCH_CHECK();
   return RP_OK;
@@ -1867,11 +1922,48 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     RP_LAUNCH_CHECK();
     return RP_OK;
   }
-  switch (l.U) {
-    case 1: return rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
-    case 4: return rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
-    default: return rt_launch_fwd<2>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st);
+  // Whole-plane kernel for the coarse levels (roi_fwd_plane.cuh): their RoIs leave the column walk.
+  const int* skip = nullptr;
+  void* scratch = nullptr;
+  if (rp_env_int("RP_ROI_PLANES", RP_ROI_PLANES_DEFAULT) && sampling_ratio == 2.0f && PH <= 16 && PW <= 16) {
+    int max_groups = 0;
+    for (int i = 0; i < lv.L; ++i) {
+      const long long hw = (long long)lv.H[i] * lv.W[i];
+      if (lv.H[i] < 2 || lv.W[i] < 2 || hw > RP_PLANE_MAX) continue;
+      int cg = (int)(RP_PLANE_FLOATS / hw);
+      if (cg > C) cg = C;
+      cg &= ~1;
+      if (cg < 2) cg = C >= 2 ? 2 : 1;
+      const int groups = (C + cg - 1) / cg;
+      if (groups > max_groups) max_groups = groups;
+    }
+    if (max_groups > 0 && (long long)N * max_groups <= 0x7fffffffLL) {
+      const size_t tb = rp_align_up(sizeof(RpTab) * (size_t)K, 256);
+      if (cudaMallocAsync(&scratch, tb + sizeof(int) * (size_t)K, st) != cudaSuccess) {
+        (void)cudaGetLastError();
+        scratch = nullptr;  // no scratch: the column walk takes every RoI
+      } else {
+        RpTab* tabs = reinterpret_cast<RpTab*>(scratch);
+        int* key = reinterpret_cast<int*>(reinterpret_cast<char*>(scratch) + tb);
+        rp_tables_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(lv, N, rois, levels, K, PH, PW, sampling_ratio,
+                                                                  tabs, key);
+        RP_LAUNCH_CHECK();
+        RP_SET_MAX_SMEM(rp_plane_fwd_kernel, RP_SMEM_BYTES);
+        rp_plane_fwd_kernel<<<dim3((unsigned)(N * max_groups), (unsigned)lv.L), RP_THREADS, RP_SMEM_BYTES, st>>>(
+            lv, N, C, key, tabs, K, PH, PW, out, max_groups);
+        RP_LAUNCH_CHECK();
+        skip = key;
+      }
+    }
   }
+  int rc;
+  switch (l.U) {
+    case 1: rc = rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
+    case 4: rc = rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
+    default: rc = rt_launch_fwd<2>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
+  }
+  if (scratch) (void)cudaFreeAsync(scratch, st);
+  return rc;
 }
 
 int rt_backward(const RtLevels& lv, int N, int C, const float* rois, const int* levels, int K,
