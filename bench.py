@@ -375,7 +375,10 @@ def run_gpu_arm(args):
     # from the round's capture listed in profiles/roofline_traffic.json -- null without a capture
     impl = os.environ.get("RP_ROI_IMPL", "3")
     kernel_name = {"3": "rt_pool_fwd_kernel", "4": "rb_pool_fwd_kernel", "5": "rg_pool_fwd_kernel",
-                   "6": "rx_pool_fwd_kernel"}.get(impl, "rt_pool_fwd_kernel")
+                   "6": "rx_pool_fwd_kernel", "7": "rm_pool_fwd_kernel"}.get(impl, "rt_pool_fwd_kernel")
+    planes = impl == "3" and os.environ.get("RP_ROI_PLANES", "1") != "0"
+    if planes:  # the call is three launches: sample tables, whole-plane kernel (coarse levels), column walk
+        kernel_name = "rt_pool_fwd_kernel+rp_plane_fwd_kernel"
     traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
@@ -416,7 +419,7 @@ def run_gpu_arm(args):
         "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(world), "roofline": roofline, "cpu_baseline": cpu_baseline,
-        "parity": parity, "e2e": e2e, "gpu_launches": 2 * args.steps, "clocks": clocks,
+        "parity": parity, "e2e": e2e, "gpu_launches": (4 if planes else 2) * args.steps, "clocks": clocks,
     }
     if extra is not None:
         line["extra"] = extra

@@ -34,8 +34,11 @@ constexpr int RT_THREADS = 256;
 #ifndef RP_ROI_IMPL_DEFAULT
 #define RP_ROI_IMPL_DEFAULT 3  // forward kernel: 3 = tile walk, 4 = banded, 5 = merged taps
 #endif
+#ifndef RP_ROI_TAP3_DEFAULT
+#define RP_ROI_TAP3_DEFAULT 1  // three-tap rows in the sample walk (merged x weights): 2.24 -> 2.11 ms
+#endif
 #ifndef RP_ROI_PLANES_DEFAULT
-#define RP_ROI_PLANES_DEFAULT 0  // whole-plane kernel for the coarse levels (roi_fwd_plane.cuh)
+#define RP_ROI_PLANES_DEFAULT 1  // whole-plane kernel for the coarse levels (roi_fwd_plane.cuh): 2.11 -> 1.98 ms
 #endif
 constexpr int RT_U1 = 4;  // channels per thread, phase 1
 constexpr int RT_U2 = 2;  // channels per thread, phase 2
@@ -228,13 +231,24 @@ __device__ __forceinline__ RtYSample rt_lds_sample(uint32_t a) {
   return e;
 }
 
-template <int U>
+// TAP3: the two x-samples of every output column of this RoI lie in the same or in adjacent tile
+// columns (rt_x_tap3: true for every bin of at most 2 feature pixels), so a row needs 3 loads and 3 FMAs
+// per channel with merged weights instead of 4 + 4 (reassociation only, ~1e-7 relative); the third
+// load repeats column lo+1 with weight 0 when both samples share a column pair.
+template <int U, bool TAP3 = false>
 __device__ __forceinline__ void rt_fwd_item_fsm_s(uint32_t tile_a, uint32_t ustride4, int nvalid,
                                                   uint32_t ytab_a, const RtW* xw, const short* xo_t,
                                                   int gy, uint32_t tw4, int pw, int b0, int b1,
                                                   float* optr, int cstride, int PW, float inv) {
   if (b0 >= b1) return;
-  const RtW w0 = xw[pw * 2], w1 = xw[pw * 2 + 1];
+  RtW w0 = xw[pw * 2], w1 = xw[pw * 2 + 1];
+  float w3a = 0.f, w3b = 0.f, w3c = 0.f;
+  if (TAP3) {
+    const bool same = xo_t[pw * 2 + 1] == xo_t[pw * 2];
+    w3a = same ? w0.lo + w1.lo : w0.lo;
+    w3b = same ? w0.hi + w1.hi : w0.hi + w1.lo;
+    w3c = same ? 0.f : w1.hi;
+  }
   uint32_t st = ytab_a + (uint32_t)(b0 * gy) * 16u;
   int bins_left = b1 - b0;
   /* the first sample of a segment: its row pair is computed from scratch, flags ignored */
@@ -246,17 +260,21 @@ __device__ __forceinline__ void rt_fwd_item_fsm_s(uint32_t tile_a, uint32_t ustr
   for (int u = 0; u < U; ++u) {
     const uint32_t b = tile_a + (u < nvalid ? (uint32_t)u * ustride4 : 0u) + (uint32_t)e.row * tw4;
     a0[u] = b + 4u * (uint32_t)xo_t[pw * 2];
-    a1[u] = b + 4u * (uint32_t)xo_t[pw * 2 + 1];
+    a1[u] = b + 4u * (uint32_t)xo_t[pw * 2 + 1];  // TAP3: its +4 is the third column (lo+2, or lo+1 again)
     op[u] = optr + (size_t)u * cstride;
   }
   float Ta[U], Tb[U], acc[U];
-#define RS_XROW(T)                                                                            \
-  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                             \
-    T[u] = fmaf(w1.hi, rt_lds_f32_4(a1[u]),                                                   \
-                fmaf(w1.lo, rt_lds_f32(a1[u]),                                                \
-                     fmaf(w0.hi, rt_lds_f32_4(a0[u]), fmaf(w0.lo, rt_lds_f32(a0[u]), 0.f)))); \
-    a0[u] += tw4;                                                                             \
-    a1[u] += tw4;                                                                             \
+#define RS_XROW(T)                                                                              \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                               \
+    if (TAP3)                                                                                   \
+      T[u] = fmaf(w3c, rt_lds_f32_4(a1[u]),                                                     \
+                  fmaf(w3b, rt_lds_f32_4(a0[u]), fmaf(w3a, rt_lds_f32(a0[u]), 0.f)));           \
+    else                                                                                        \
+      T[u] = fmaf(w1.hi, rt_lds_f32_4(a1[u]),                                                   \
+                  fmaf(w1.lo, rt_lds_f32(a1[u]),                                                \
+                       fmaf(w0.hi, rt_lds_f32_4(a0[u]), fmaf(w0.lo, rt_lds_f32(a0[u]), 0.f)))); \
+    a0[u] += tw4;                                                                               \
+    a1[u] += tw4;                                                                               \
   }
 #define RS_JUMP(LO, HI)                                      \
   {                                                          \
@@ -332,7 +350,8 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                                                 int c_per_cta, int tile_floats, int gpb, int gw,
                                                 int nbuf = 1) {
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
-  // nbuf == 2: the tile buffer is cut into two halves and the copies of chunk i+1 are issued before
+  // nbuf bit 4: three-tap rows where the RoI allows them.
+  // (nbuf & 3) == 2: the tile buffer is cut into two halves and the copies of chunk i+1 are issued before
   // chunk i is walked, so they fly under the walk (a timing ablation put the exposed copies at 0.6 of
   // the kernel's 2.2 ms: DESIGN.md 4.1); a RoI whose tile does not fit a half keeps the single buffer
   RtYSample* ytab = reinterpret_cast<RtYSample*>(rt_smem);
@@ -410,7 +429,7 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   RtTilePlan tp;
   tp.cc = 0;
   int nbufs = 1, buf_floats = tile_floats;
-  if (fits && nbuf == 2) {
+  if (fits && (nbuf & 3) == 2) {
     const int half = (tile_floats / 2) & ~31;
     tp = rt_plan_tile(R, twa, half, gpb, gw, U, nch, PH);
     if (tp.cc >= 1 && tp.cc < nch) {  // more than one chunk: worth the second buffer
@@ -450,7 +469,14 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
     const int prev = s ? ytab[s - 1].row : cur;
     ytab[s].flags = rt_ysample_flags(cur, prev, ytab[s].flags & RT_F_EMIT);
   }
-  __syncthreads();
+  // three-tap rows (rt_fwd_item_fsm_s<U, true>): every output column's two x-samples in the same or in
+  // adjacent tile columns -- CTA-uniform, decided here
+  int x3ok = 1;
+  if (tid < PW && g.gw == 2) {
+    const int d = xo_s[2 * tid + 1] - xo_s[2 * tid];
+    x3ok = (d == 0) || (d == 1);
+  }
+  const bool tap3 = __syncthreads_and(x3ok) && g.gw == 2 && (nbuf & 16);
 
   // ---- this thread's item: (pw, channel group cg, segment seg) -------------------------------
   const int chp = tp.chp;
@@ -527,7 +553,11 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                               nvalid, inv};
         const float* tile_g = tile_b + cg * chp;
         const int ustride = tp.ncg * chp;
-        if (g.gw == 2 && LEAN)
+        if (g.gw == 2 && LEAN && tap3)
+          rt_fwd_item_fsm_s<U, true>(tile_bs + 4u * (uint32_t)(cg * chp), 4u * (uint32_t)ustride, nvalid,
+                                     rp_smem_addr(ytab), xw_s, xo_s, g.gh, 4u * (uint32_t)twa, pw, b0, b1,
+                                     out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW, inv);
+        else if (g.gw == 2 && LEAN)
           rt_fwd_item_fsm_s<U>(tile_bs + 4u * (uint32_t)(cg * chp), 4u * (uint32_t)ustride, nvalid,
                                rp_smem_addr(ytab), xw_s, xo_s, g.gh, 4u * (uint32_t)twa, pw, b0, b1,
                                out_k + (size_t)(c0 + cg) * P + b0 * PW + pw, tp.ncg * P, PW, inv);
@@ -1764,7 +1794,8 @@ int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const flo
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
                   cudaStream_t st, const int* skip = nullptr) {
   dim3 grid((unsigned)K, (unsigned)l.csplit);
-  const int nbuf = rp_env_int("RP_ROI_DBUF", 0) ? 2 : 1;  // two half-size tile buffers: copies under the walk
+  const int nbuf = (rp_env_int("RP_ROI_DBUF", 0) ? 2 : 1)     // two half-size tile buffers: copies under the walk
+                   | (rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT) ? 16 : 0);  // three-tap rows
   if (rp_env_int("RP_ROI_LEAN", 1)) {  // hand-written shared-memory addressing in the sample walk
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, true>), l.smem_fwd);
     rt_pool_fwd_kernel<U, true><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
@@ -1925,7 +1956,8 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   // Whole-plane kernel for the coarse levels (roi_fwd_plane.cuh): their RoIs leave the column walk.
   const int* skip = nullptr;
   void* scratch = nullptr;
-  if (rp_env_int("RP_ROI_PLANES", RP_ROI_PLANES_DEFAULT) && sampling_ratio == 2.0f && PH <= 16 && PW <= 16) {
+  if (rp_env_int("RP_ROI_PLANES", RP_ROI_PLANES_DEFAULT) && sampling_ratio == 2.0f && PH <= 16 && PW <= 16 &&
+      K <= 262144) {  // 848 bytes of tables per RoI in stream-ordered scratch
     int max_groups = 0;
     for (int i = 0; i < lv.L; ++i) {
       const long long hw = (long long)lv.H[i] * lv.W[i];
@@ -1949,8 +1981,12 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
                                                                   tabs, key);
         RP_LAUNCH_CHECK();
         RP_SET_MAX_SMEM(rp_plane_fwd_kernel, RP_SMEM_BYTES);
-        rp_plane_fwd_kernel<<<dim3((unsigned)(N * max_groups), (unsigned)lv.L), RP_THREADS, RP_SMEM_BYTES, st>>>(
-            lv, N, C, key, tabs, K, PH, PW, out, max_groups);
+        // enough CTAs for two waves of the 2 x 148 resident ones: with few images the RoIs of one
+        // (level, image) are dealt to up to 8 CTAs
+        int slices = 1;
+        while (slices < 8 && (long long)N * max_groups * slices < 4 * RP_NUM_SMS) slices *= 2;
+        rp_plane_fwd_kernel<<<dim3((unsigned)(N * max_groups), (unsigned)lv.L, (unsigned)slices), RP_THREADS, RP_SMEM_BYTES, st>>>(
+            lv, N, C, key, tabs, K, PH, PW, out, max_groups, rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT));
         RP_LAUNCH_CHECK();
         skip = key;
       }

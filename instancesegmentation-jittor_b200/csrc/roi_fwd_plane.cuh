@@ -34,7 +34,7 @@ struct __align__(16) RpTab {
   RtYSample y[RP_NS];  // absolute plane row of the lo tap, weights, walk flags
   RtW xw[RP_NS];
   short xo[RP_NS];     // absolute plane column of the lo tap
-  int meta[4];         // [0]: 1 walk, 0 every output is zero
+  int meta[4];         // [0]: 1 walk, 0 every output is zero; [1]: three-tap rows allowed
 };
 static_assert(sizeof(RpTab) % 16 == 0, "RpTab is copied in 16-byte pieces");
 
@@ -96,15 +96,20 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
     t->xw[lane] = w;
     t->xo[lane] = (short)xcol;
   }
+  // three-tap rows: the two x-samples of every column in the same or in adjacent plane columns
+  const int xnext = __shfl_down_sync(0xffffffffu, xcol, 1);
+  const int d = xnext - xcol;
+  const int x3 = __all_sync(0xffffffffu, (lane >= SX) || (lane & 1) || d == 0 || d == 1);
   if (lane == 0) {
     t->meta[0] = 1;
+    t->meta[1] = x3;
     key[k] = level * N + b;
   }
 }
 
 __global__ void __launch_bounds__(RP_THREADS, 2)
 rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, const RpTab* __restrict__ tabs,
-                    int K, int PH, int PW, float* __restrict__ out, int max_groups) {
+                    int K, int PH, int PW, float* __restrict__ out, int max_groups, int tap3) {
   extern __shared__ __align__(16) unsigned char rp_smem[];
   // layout: planes[RP_PLANE_FLOATS] | tables[2 * RP_WARPS] | list[RP_LIST]
   float* planes = reinterpret_cast<float*>(rp_smem);
@@ -153,7 +158,9 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
     const int end = min(K, base + RP_LIST);
     for (int kb = base; kb < end; kb += RP_THREADS) {
       const int k = kb + tid;
-      const bool hit = k < end && key[k] == mykey;
+      // gridDim.z > 1 (few images): RoI k belongs to the CTA with blockIdx.z == k % gridDim.z (the list
+      // order depends on warp timing, so the deal is by RoI index, not by list position)
+      const bool hit = k < end && key[k] == mykey && (k % (int)gridDim.z) == (int)blockIdx.z;
       const unsigned m = __ballot_sync(0xffffffffu, hit);
       if (m) {
         int pos = 0;
@@ -189,10 +196,17 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
         for (int j = lane; j < nch * P; j += 32) out_k[j] = 0.f;
       } else if (active) {
         const uint32_t ytab_s = rp_smem_addr(tb->y);
-        for (int c = 2 * half; c < nch; c += 4)
-          rt_fwd_item_fsm_s<2>(planes_s + 4u * (uint32_t)(c * HW), 4u * (uint32_t)HW, min(2, nch - c), ytab_s,
-                               tb->xw, tb->xo, 2, 4u * (uint32_t)W, pw, 0, PH,
-                               out_k + (size_t)c * P + pw, P, PW, 0.25f);
+        if (tap3 && tb->meta[1]) {
+          for (int c = 2 * half; c < nch; c += 4)
+            rt_fwd_item_fsm_s<2, true>(planes_s + 4u * (uint32_t)(c * HW), 4u * (uint32_t)HW, min(2, nch - c),
+                                       ytab_s, tb->xw, tb->xo, 2, 4u * (uint32_t)W, pw, 0, PH,
+                                       out_k + (size_t)c * P + pw, P, PW, 0.25f);
+        } else {
+          for (int c = 2 * half; c < nch; c += 4)
+            rt_fwd_item_fsm_s<2>(planes_s + 4u * (uint32_t)(c * HW), 4u * (uint32_t)HW, min(2, nch - c), ytab_s,
+                                 tb->xw, tb->xo, 2, 4u * (uint32_t)W, pw, 0, PH,
+                                 out_k + (size_t)c * P + pw, P, PW, 0.25f);
+        }
       }
       __syncwarp();  // the slot is refilled two RoIs later
     }
