@@ -37,6 +37,9 @@ constexpr int RT_THREADS = 256;
 #ifndef RP_ROI_TAP3_DEFAULT
 #define RP_ROI_TAP3_DEFAULT 1  // three-tap rows in the sample walk (merged x weights): 2.24 -> 2.11 ms
 #endif
+#ifndef RP_ROI_YMERGE_DEFAULT
+#define RP_ROI_YMERGE_DEFAULT 1  // merged y-samples in the walk table: 1.995 -> 1.93 ms
+#endif
 #ifndef RP_ROI_PLANES_DEFAULT
 #define RP_ROI_PLANES_DEFAULT 1  // whole-plane kernel for the coarse levels (roi_fwd_plane.cuh): 2.11 -> 1.98 ms
 #endif
@@ -351,6 +354,7 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                                                 int nbuf = 1) {
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
   // nbuf bit 4: three-tap rows where the RoI allows them.
+  // nbuf bit 5: y-merge (below).
   // (nbuf & 3) == 2: the tile buffer is cut into two halves and the copies of chunk i+1 are issued before
   // chunk i is walked, so they fly under the walk (a timing ablation put the exposed copies at 0.6 of
   // the kernel's 2.2 ms: DESIGN.md 4.1); a RoI whose tile does not fit a half keeps the single buffer
@@ -461,6 +465,29 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
       const int lo = xo_s[t];
       xo_s[t] = (short)(lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0));
     }
+  }
+  __syncthreads();
+  // y-merge: when the two y-samples of a bin share a row pair their weights are added and the bin keeps
+  // ONE table entry (every second bin on the fine level: fewer entries, loads and FMAs in the walk;
+  // reassociation only).  Only when every item walks its whole column (one segment: the walk then starts
+  // at entry 0 and stops on the bin count, so no per-bin start index is needed).
+  if ((nbuf & 32) && LEAN && g.gh == 2 && g.gw == 2 && tp.nseg == 1 && SY <= 32 && tid < 32) {
+    const int t = tid;
+    RtYSample e = ytab[t < SY ? t : 0];
+    const int rown = __shfl_down_sync(0xffffffffu, e.row, 1);
+    const float wlon = __shfl_down_sync(0xffffffffu, e.wlo, 1), whin = __shfl_down_sync(0xffffffffu, e.whi, 1);
+    const int m = (t < SY) && !(t & 1) && (rown == e.row);  // decided on the bin's first sample
+    const int mprev = __shfl_up_sync(0xffffffffu, m, 1);
+    const bool keep = (t < SY) && !((t & 1) && mprev);
+    if (m) {
+      e.wlo += wlon;
+      e.whi += whin;
+    }
+    e.flags = ((t & 1) || m) ? RT_F_EMIT : 0;  // last entry of its bin
+    const unsigned km = __ballot_sync(0xffffffffu, keep);
+    const int pos = __popc(km & ((1u << t) - 1u));
+    __syncwarp();
+    if (keep) ytab[pos] = e;
   }
   __syncthreads();
   // how the live row pair moves before each y-sample (rows are final now)
@@ -1795,7 +1822,8 @@ int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const flo
                   cudaStream_t st, const int* skip = nullptr) {
   dim3 grid((unsigned)K, (unsigned)l.csplit);
   const int nbuf = (rp_env_int("RP_ROI_DBUF", 0) ? 2 : 1)     // two half-size tile buffers: copies under the walk
-                   | (rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT) ? 16 : 0);  // three-tap rows
+                   | (rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT) ? 16 : 0)   // three-tap rows
+                   | (rp_env_int("RP_ROI_YMERGE", RP_ROI_YMERGE_DEFAULT) ? 32 : 0);  // one entry per bin where both y-samples share a row pair
   if (rp_env_int("RP_ROI_LEAN", 1)) {  // hand-written shared-memory addressing in the sample walk
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, true>), l.smem_fwd);
     rt_pool_fwd_kernel<U, true><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
@@ -1978,7 +2006,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
         RpTab* tabs = reinterpret_cast<RpTab*>(scratch);
         int* key = reinterpret_cast<int*>(reinterpret_cast<char*>(scratch) + tb);
         rp_tables_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(lv, N, rois, levels, K, PH, PW, sampling_ratio,
-                                                                  tabs, key);
+                                                                  tabs, key, rp_env_int("RP_ROI_YMERGE", RP_ROI_YMERGE_DEFAULT));
         RP_LAUNCH_CHECK();
         RP_SET_MAX_SMEM(rp_plane_fwd_kernel, RP_SMEM_BYTES);
         // enough CTAs for two waves of the 2 x 148 resident ones: with few images the RoIs of one

@@ -46,7 +46,8 @@ __device__ __forceinline__ bool rp_level_planar(const RtLevels& lv, int level) {
 // One warp per RoI.
 __global__ void __launch_bounds__(256)
 rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* __restrict__ levels, int K,
-                 int PH, int PW, float sampling_ratio, RpTab* __restrict__ tabs, int* __restrict__ key) {
+                 int PH, int PW, float sampling_ratio, RpTab* __restrict__ tabs, int* __restrict__ key,
+                 int ymerge) {
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (k >= K) return;
@@ -80,14 +81,26 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
   // out-of-range samples carry zero weights and park on the nearest row / column that has a sample
   const int yrow = (lane < SY) ? (yok ? ylo : (ylo == -1 ? y0 : yl)) : yl;
   const int xcol = xok ? xlo : (xlo == -1 ? x0 : xl);
-  const int prev = __shfl_up_sync(0xffffffffu, yrow, 1);
-  if (lane < SY) {
-    RtYSample e;
-    e.wlo = ywl;
-    e.whi = ywh;
-    e.row = yrow;
-    e.flags = rt_ysample_flags(yrow, lane ? prev : yrow, lane & 1);
-    t->y[lane] = e;
+  {
+    // y-merge (see rt3_roi_forward): the two samples of a bin that share a row pair become one entry
+    const int rown = __shfl_down_sync(0xffffffffu, yrow, 1);
+    const float wlon = __shfl_down_sync(0xffffffffu, ywl, 1), whin = __shfl_down_sync(0xffffffffu, ywh, 1);
+    const int m = ymerge && (lane < SY) && !(lane & 1) && (rown == yrow);
+    const int mprev = __shfl_up_sync(0xffffffffu, m, 1);
+    const bool keep = (lane < SY) && !((lane & 1) && mprev);
+    const unsigned km = __ballot_sync(0xffffffffu, keep);
+    const int pos = __popc(km & ((1u << lane) - 1u));
+    // row of the entry before this one in the compacted sequence
+    const int src = pos > 0 ? (int)__fns(km, 0, pos) : lane;
+    const int prev = __shfl_sync(0xffffffffu, yrow, src);
+    if (keep) {
+      RtYSample e;
+      e.wlo = m ? ywl + wlon : ywl;
+      e.whi = m ? ywh + whin : ywh;
+      e.row = yrow;
+      e.flags = rt_ysample_flags(yrow, pos ? prev : yrow, (lane & 1) || m);
+      t->y[pos] = e;
+    }
   }
   if (lane < SX) {
     RtW w;
