@@ -318,3 +318,28 @@ def test_chained_mma_forward_modes(mode, monkeypatch):
             exp = oracle.roi_align_forward(feat, rois, P, 1 / 16, sr)
             out = rp.roi_align(T(feat), T(rois), P, 1 / 16, sr).cpu().numpy()
             _close(out, exp)
+
+
+@pytest.mark.parametrize("knobs", [{"RP_ROI_PLANES": "0"}, {"RP_ROI_TAP3": "0"}, {"RP_ROI_YMERGE": "0"},
+                                   {"RP_ROI_PLANES": "0", "RP_ROI_TAP3": "0", "RP_ROI_YMERGE": "0"},
+                                   {"RP_ROI_DBUF": "1"}, {"RP_ROI_DBUF": "1", "RP_ROI_PLANES": "0"}])
+def test_default_forward_with_each_step_switched_off(knobs, monkeypatch):
+    """The default forward call = column walk with three-tap rows and merged y-samples + the whole-plane
+    kernel on the coarse levels.  Every step has a switch; with any of them off (and with the opt-in
+    double-buffered chunk loop on) the call must still match the oracle: on the FPN pyramid (plane kernel
+    takes P4 / P5 there), on one image (its RoIs are dealt to several CTAs) and on RoIs with bins wider
+    than 2 feature pixels (no three-tap rows), 14x14 and 7x7."""
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    rp.reload_env()
+    for N, per in [(3, 150), (1, 300)]:
+        C = 20
+        feats = synth.fpn_features(N, C)
+        rois = synth.rois_for_images(N, per)
+        rois[::7, 3] += 300.0  # wide bins on every level
+        rois[::11, 4] += 250.0
+        lv = oracle.level_map(rois[:, 1:], 2, 5)
+        for P in [(14, 14), (7, 7)]:
+            exp = oracle.pooler_forward(feats, synth.FPN_SCALES, rois, lv, P, 2)
+            out = rp.pooler_forward([T(f) for f in feats], synth.FPN_SCALES, T(rois), T(lv), P, 2)
+            _close(out.cpu().numpy(), exp)
