@@ -1999,14 +1999,24 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
     }
     if (max_groups > 0 && (long long)N * max_groups <= 0x7fffffffLL) {
       const size_t tb = rp_align_up(sizeof(RpTab) * (size_t)K, 256);
-      if (cudaMallocAsync(&scratch, tb + sizeof(int) * (size_t)K, st) != cudaSuccess) {
+      const size_t kb = rp_align_up(sizeof(int) * (size_t)K, 256);
+      const int nkeys = lv.L * N;
+      const size_t nwin = ((size_t)K + RP_LIST - 1) / RP_LIST;
+      const size_t wb = (nwin * nkeys <= (1u << 20)) ? sizeof(int) * nwin * nkeys : 0;  // window counts (optional)
+      if (cudaMallocAsync(&scratch, tb + kb + wb, st) != cudaSuccess) {
         (void)cudaGetLastError();
         scratch = nullptr;  // no scratch: the column walk takes every RoI
       } else {
         RpTab* tabs = reinterpret_cast<RpTab*>(scratch);
         int* key = reinterpret_cast<int*>(reinterpret_cast<char*>(scratch) + tb);
+        int* wcnt = wb ? reinterpret_cast<int*>(reinterpret_cast<char*>(scratch) + tb + kb) : nullptr;
+        if (wcnt && cudaMemsetAsync(wcnt, 0, wb, st) != cudaSuccess) {
+          (void)cudaGetLastError();
+          wcnt = nullptr;  // without the counts the plane kernel visits every window
+        }
         rp_tables_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(lv, N, rois, levels, K, PH, PW, sampling_ratio,
-                                                                  tabs, key, rp_env_int("RP_ROI_YMERGE", RP_ROI_YMERGE_DEFAULT));
+                                                                  tabs, key, rp_env_int("RP_ROI_YMERGE", RP_ROI_YMERGE_DEFAULT),
+                                                                  wcnt, nkeys);
         RP_LAUNCH_CHECK();
         RP_SET_MAX_SMEM(rp_plane_fwd_kernel, RP_SMEM_BYTES);
         // enough CTAs for two waves of the 2 x 148 resident ones: with few images the RoIs of one
@@ -2014,7 +2024,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
         int slices = 1;
         while (slices < 8 && (long long)N * max_groups * slices < 4 * RP_NUM_SMS) slices *= 2;
         rp_plane_fwd_kernel<<<dim3((unsigned)(N * max_groups), (unsigned)lv.L, (unsigned)slices), RP_THREADS, RP_SMEM_BYTES, st>>>(
-            lv, N, C, key, tabs, K, PH, PW, out, max_groups, rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT));
+            lv, N, C, key, tabs, K, PH, PW, out, max_groups, rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT), wcnt, nkeys);
         RP_LAUNCH_CHECK();
         skip = key;
       }

@@ -47,7 +47,7 @@ __device__ __forceinline__ bool rp_level_planar(const RtLevels& lv, int level) {
 __global__ void __launch_bounds__(256)
 rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* __restrict__ levels, int K,
                  int PH, int PW, float sampling_ratio, RpTab* __restrict__ tabs, int* __restrict__ key,
-                 int ymerge) {
+                 int ymerge, int* __restrict__ wcnt, int nkeys) {
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (k >= K) return;
@@ -71,6 +71,9 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
   const int yl = __reduce_max_sync(0xffffffffu, yok ? ylo : -1);
   const int x0 = __reduce_min_sync(0xffffffffu, xok ? xlo : 0x7fffffff);
   const int xl = __reduce_max_sync(0xffffffffu, xok ? xlo : -1);
+  // wcnt[window][key]: how many RoIs of each (level, image) the window of RP_LIST keys holds, so that the
+  // plane kernel only visits the windows that concern it
+  if (lane == 0 && wcnt) atomicAdd(&wcnt[(size_t)(k / RP_LIST) * nkeys + level * N + b], 1);
   if (yl < 0 || xl < 0) {  // no sample inside the map on some axis: zeros (roi_align.py:20)
     if (lane == 0) {
       t->meta[0] = 0;
@@ -122,7 +125,8 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
 
 __global__ void __launch_bounds__(RP_THREADS, 2)
 rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, const RpTab* __restrict__ tabs,
-                    int K, int PH, int PW, float* __restrict__ out, int max_groups, int tap3) {
+                    int K, int PH, int PW, float* __restrict__ out, int max_groups, int tap3,
+                    const int* __restrict__ wcnt, int nkeys) {
   extern __shared__ __align__(16) unsigned char rp_smem[];
   // layout: planes[RP_PLANE_FLOATS] | tables[2 * RP_WARPS] | list[RP_LIST]
   float* planes = reinterpret_cast<float*>(rp_smem);
@@ -164,8 +168,10 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
   const bool active = pw < PW;
   RpTab* slot = slots + 2 * warp;  // two slots per warp
 
+  bool landed = false;
   for (int base = 0; base < K; base += RP_LIST) {
     // ---- the RoIs of this (level, image) among the next RP_LIST keys ----------------------------
+    if (wcnt && wcnt[(size_t)(base / RP_LIST) * nkeys + mykey] == 0) continue;  // CTA-uniform
     if (tid == 0) s_n = 0;
     __syncthreads();
     const int end = min(K, base + RP_LIST);
@@ -182,7 +188,8 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
         if (hit) list[pos] = k;
       }
     }
-    if (base == 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (!landed) asm volatile("cp.async.wait_group 0;" ::: "memory");  // the planes
+    landed = true;
     __syncthreads();
     const int cnt = s_n;
     // ---- warps on their own from here -------------------------------------------------------
@@ -226,6 +233,7 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();  // the list is rebuilt by the next round
   }
+  if (!landed) asm volatile("cp.async.wait_group 0;" ::: "memory");  // no RoI of this (level, image): drain the copies
 }
 
 constexpr size_t RP_SMEM_BYTES =
