@@ -1816,6 +1816,39 @@ void rm_level_maps(RmMaps* maps, int l, const float* ptr, long long planes, int 
   }
 }
 
+// Stream-ordered scratch of the forward call from a pool of this library's own (one per device) that
+// keeps its memory across synchronisations: the default pool trims to zero at every sync, which turned
+// the per-call allocation into a 0.1 ms driver call in the bench's step loop.
+cudaError_t rt_scratch_alloc(void** p, size_t bytes, cudaStream_t st) {
+  static std::mutex mu;
+  static cudaMemPool_t pools[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaMallocAsync(p, bytes, st);
+  cudaMemPool_t pool;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!pools[dev]) {
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      e = cudaMemPoolCreate(&pools[dev], &props);
+      if (e != cudaSuccess) {
+        pools[dev] = nullptr;
+        (void)cudaGetLastError();
+        return cudaMallocAsync(p, bytes, st);
+      }
+      unsigned long long keep = ~0ull;
+      (void)cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    pool = pools[dev];
+  }
+  return cudaMallocFromPoolAsync(p, bytes, pool, st);
+}
+
 template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
@@ -2003,7 +2036,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
       const int nkeys = lv.L * N;
       const size_t nwin = ((size_t)K + RP_LIST - 1) / RP_LIST;
       const size_t wb = (nwin * nkeys <= (1u << 20)) ? sizeof(int) * nwin * nkeys : 0;  // window counts (optional)
-      if (cudaMallocAsync(&scratch, tb + kb + wb, st) != cudaSuccess) {
+      if (rt_scratch_alloc(&scratch, tb + kb + wb, st) != cudaSuccess) {
         (void)cudaGetLastError();
         scratch = nullptr;  // no scratch: the column walk takes every RoI
       } else {
