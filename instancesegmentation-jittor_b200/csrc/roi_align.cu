@@ -37,6 +37,9 @@ constexpr int RT_THREADS = 256;
 #ifndef RP_ROI_TAP3_DEFAULT
 #define RP_ROI_TAP3_DEFAULT 1  // three-tap rows in the sample walk (merged x weights): 2.24 -> 2.11 ms
 #endif
+#ifndef RP_ROI_WALK_TABS_DEFAULT
+#define RP_ROI_WALK_TABS_DEFAULT 0  // the column walk reads the tables kernel's sample tables
+#endif
 #ifndef RP_ROI_YMERGE_DEFAULT
 #define RP_ROI_YMERGE_DEFAULT 1  // merged y-samples in the walk table: 1.995 -> 1.93 ms
 #endif
@@ -343,6 +346,18 @@ __device__ __forceinline__ void rt_fwd_item_fsm_s(uint32_t tile_a, uint32_t ustr
 #undef RS_EMIT
 }
 
+// Sample tables of one RoI as rp_tables_kernel (roi_fwd_plane.cuh) leaves them in global memory: the values
+// rt3_roi_forward builds itself, with ABSOLUTE map rows / columns, out-of-range samples already parked.
+constexpr int RP_NS = 32;  // samples per axis (bins * 2 <= 32)
+struct __align__(16) RpTab {
+  RtYSample y[RP_NS];  // absolute row of the lo tap, weights, walk flags
+  RtW xw[RP_NS];
+  short xo[RP_NS];     // absolute column of the lo tap
+  int meta[4];         // [0]: 1 tables valid, 0 every output is zero, 2 not built; [1]: three-tap rows allowed;
+                       // [2]: first | last << 16 row that holds a lo tap; [3]: the same for columns
+};
+static_assert(sizeof(RpTab) % 16 == 0, "RpTab is copied in 16-byte pieces");
+
 // The v3 evaluation of one (RoI, channel slice) by the whole CTA; any CTA size that is a multiple
 // of gw.  Also the fallback of the banded kernel below for RoIs without a band form.
 template <int U, bool LEAN = false>
@@ -351,7 +366,7 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
                                                 const int* __restrict__ levels, int PH, int PW,
                                                 float sampling_ratio, float* __restrict__ out,
                                                 int c_per_cta, int tile_floats, int gpb, int gw,
-                                                int nbuf = 1) {
+                                                int nbuf = 1, const RpTab* __restrict__ tabs = nullptr) {
   // layout: ytab[RT_SMAX] | xw[RT_SMAX] | xo[RT_SMAX] | tile[tile_floats]
   // nbuf bit 4: three-tap rows where the RoI allows them.
   // nbuf bit 5: y-merge (below).
@@ -387,37 +402,59 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   const int SY = PH * g.gh, SX = PW * g.gw;
   const bool fits = (SY <= RT_SMAX) && (SX <= RT_SMAX) && SY > 0 && SX > 0 && H >= 2 && W >= 2;
 
-  // ---- tables: taps of every y- and x-sample in parallel, extents by shared atomics ---------
-  if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
-  __syncthreads();
-  if (fits) {
-    for (int s = tid; s < SY + SX; s += nthreads) {
-      const bool isy = s < SY;
-      const int t = isy ? s : s - SY;
-      const int grid = isy ? g.gh : g.gw;
-      const int p = t / grid, i = t - p * grid;
-      int lo = 0;
-      float wlo = 0.f, whi = 0.f;
-      const int ok = isy ? rt_axis_tap_pair(g.sh, g.bh, p, i, grid, H, &lo, &wlo, &whi)
-                         : rt_axis_tap_pair(g.sw, g.bw, p, i, grid, W, &lo, &wlo, &whi);
-      if (ok) {
-        atomicMin(&s_ext[isy ? 0 : 2], lo);
-        atomicMax(&s_ext[isy ? 1 : 3], lo);
-      }
-      if (isy) {
-        ytab[t].wlo = wlo;
-        ytab[t].whi = whi;
-        ytab[t].row = lo;
-        ytab[t].flags = (i == grid - 1) ? RT_F_EMIT : 0;
-      } else {
-        xw_s[t].lo = wlo;
-        xw_s[t].hi = whi;
-        xo_s[t] = (short)lo;
+  // ---- tables: read from rp_tables_kernel's copy when there is one (one warp built them once per RoI),
+  //      else taps of every y- and x-sample in parallel, extents by shared atomics ------------------
+  const RpTab* tb = tabs ? tabs + k : nullptr;
+  const bool from_tabs = tb && fits && g.gh == 2 && g.gw == 2 && SY <= RP_NS && SX <= RP_NS && tb->meta[0] != 2;
+  int y0, yl, x0, xl;
+  if (from_tabs) {
+    if (tid < 32) {
+      if (tid < SY) ytab[tid] = tb->y[tid];
+    } else if (tid < 64) {
+      const int t = tid - 32;
+      if (t < SX) {
+        xw_s[t] = tb->xw[t];
+        xo_s[t] = tb->xo[t];
       }
     }
+    const int valid = tb->meta[0], m2 = tb->meta[2], m3 = tb->meta[3];
+    y0 = m2 & 0xffff;
+    yl = valid ? (m2 >> 16) : -1;
+    x0 = m3 & 0xffff;
+    xl = valid ? (m3 >> 16) : -1;
+    __syncthreads();
+  } else {
+    if (tid < 4) s_ext[tid] = (tid & 1) ? -1 : 0x7fffffff;
+    __syncthreads();
+    if (fits) {
+      for (int s = tid; s < SY + SX; s += nthreads) {
+        const bool isy = s < SY;
+        const int t = isy ? s : s - SY;
+        const int grid = isy ? g.gh : g.gw;
+        const int p = t / grid, i = t - p * grid;
+        int lo = 0;
+        float wlo = 0.f, whi = 0.f;
+        const int ok = isy ? rt_axis_tap_pair(g.sh, g.bh, p, i, grid, H, &lo, &wlo, &whi)
+                           : rt_axis_tap_pair(g.sw, g.bw, p, i, grid, W, &lo, &wlo, &whi);
+        if (ok) {
+          atomicMin(&s_ext[isy ? 0 : 2], lo);
+          atomicMax(&s_ext[isy ? 1 : 3], lo);
+        }
+        if (isy) {
+          ytab[t].wlo = wlo;
+          ytab[t].whi = whi;
+          ytab[t].row = lo;
+          ytab[t].flags = (i == grid - 1) ? RT_F_EMIT : 0;
+        } else {
+          xw_s[t].lo = wlo;
+          xw_s[t].hi = whi;
+          xo_s[t] = (short)lo;
+        }
+      }
+    }
+    __syncthreads();
+    y0 = s_ext[0], yl = s_ext[1], x0 = s_ext[2], xl = s_ext[3];
   }
-  __syncthreads();
-  const int y0 = s_ext[0], yl = s_ext[1], x0 = s_ext[2], xl = s_ext[3];
   if (fits && (yl < 0 || xl < 0)) {  // no sample inside the map on some axis
     rt_zero_fill(out_k, (size_t)nch * P);
     return;
@@ -459,11 +496,11 @@ __device__ __forceinline__ void rt3_roi_forward(unsigned char* rt_smem, const Rt
   for (int s = tid; s < SY + SX; s += nthreads) {
     if (s < SY) {
       const int lo = ytab[s].row;
-      ytab[s].row = lo >= 0 ? lo - y0 : (lo == -1 ? 0 : yl - y0);
+      ytab[s].row = from_tabs ? lo - y0 : (lo >= 0 ? lo - y0 : (lo == -1 ? 0 : yl - y0));
     } else {
       const int t = s - SY;
       const int lo = xo_s[t];
-      xo_s[t] = (short)(lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0));
+      xo_s[t] = (short)(from_tabs ? lo - xa0 : (lo >= 0 ? lo - xa0 : (lo == -1 ? x0 - xa0 : xl - xa0)));
     }
   }
   __syncthreads();
@@ -610,11 +647,11 @@ __global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
                    float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int nbuf,
-                   const int* __restrict__ skip) {
+                   const int* __restrict__ skip, const RpTab* __restrict__ tabs) {
   extern __shared__ __align__(16) unsigned char rt_smem[];
   if (skip && skip[blockIdx.x] >= 0) return;  // taken by the whole-plane kernel (roi_fwd_plane.cuh)
   rt3_roi_forward<U, LEAN>(rt_smem, lv, N, C, rois, levels, PH, PW, sampling_ratio, out, c_per_cta,
-                     tile_floats, gpb, gw, nbuf);
+                     tile_floats, gpb, gw, nbuf, tabs);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1852,7 +1889,7 @@ cudaError_t rt_scratch_alloc(void** p, size_t bytes, cudaStream_t st) {
 template <int U>
 int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const float* rois,
                   const int* levels, int K, int PH, int PW, float sampling_ratio, float* out,
-                  cudaStream_t st, const int* skip = nullptr) {
+                  cudaStream_t st, const int* skip = nullptr, const RpTab* tabs = nullptr) {
   dim3 grid((unsigned)K, (unsigned)l.csplit);
   const int nbuf = (rp_env_int("RP_ROI_DBUF", 0) ? 2 : 1)     // two half-size tile buffers: copies under the walk
                    | (rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT) ? 16 : 0)   // three-tap rows
@@ -1860,11 +1897,11 @@ int rt_launch_fwd(const RtLaunch& l, const RtLevels& lv, int N, int C, const flo
   if (rp_env_int("RP_ROI_LEAN", 1)) {  // hand-written shared-memory addressing in the sample walk
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, true>), l.smem_fwd);
     rt_pool_fwd_kernel<U, true><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip);
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip, tabs);
   } else {
     RP_SET_MAX_SMEM((rt_pool_fwd_kernel<U, false>), l.smem_fwd);
     rt_pool_fwd_kernel<U, false><<<grid, l.threads_fwd, l.smem_fwd, st>>>(
-        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip);
+        lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, l.c_per_cta, l.tile_floats, l.gpb, l.gw, nbuf, skip, tabs);
   }
   RP_LAUNCH_CHECK();
   return RP_OK;
@@ -2016,6 +2053,7 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
   }
   // Whole-plane kernel for the coarse levels (roi_fwd_plane.cuh): their RoIs leave the column walk.
   const int* skip = nullptr;
+  const RpTab* wtabs = nullptr;  // sample tables the column walk reads instead of building its own
   void* scratch = nullptr;
   if (rp_env_int("RP_ROI_PLANES", RP_ROI_PLANES_DEFAULT) && sampling_ratio == 2.0f && PH <= 16 && PW <= 16 &&
       K <= 262144) {  // 848 bytes of tables per RoI in stream-ordered scratch
@@ -2060,14 +2098,15 @@ int rt_forward(const RtLevels& lv, int N, int C, const float* rois, const int* l
             lv, N, C, key, tabs, K, PH, PW, out, max_groups, rp_env_int("RP_ROI_TAP3", RP_ROI_TAP3_DEFAULT), wcnt, nkeys);
         RP_LAUNCH_CHECK();
         skip = key;
+        if (rp_env_int("RP_ROI_WALK_TABS", RP_ROI_WALK_TABS_DEFAULT)) wtabs = tabs;
       }
     }
   }
   int rc;
   switch (l.U) {
-    case 1: rc = rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
-    case 4: rc = rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
-    default: rc = rt_launch_fwd<2>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip); break;
+    case 1: rc = rt_launch_fwd<1>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip, wtabs); break;
+    case 4: rc = rt_launch_fwd<4>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip, wtabs); break;
+    default: rc = rt_launch_fwd<2>(l, lv, N, C, rois, levels, K, PH, PW, sampling_ratio, out, st, skip, wtabs); break;
   }
   if (scratch) (void)cudaFreeAsync(scratch, st);
   return rc;

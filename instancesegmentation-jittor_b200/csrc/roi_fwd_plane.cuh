@@ -27,16 +27,8 @@ constexpr int RP_WARPS = 16;
 constexpr int RP_THREADS = RP_WARPS * 32;
 constexpr int RP_PLANE_FLOATS = 16896;  // plane buffer of a CTA (66 KB): CG = RP_PLANE_FLOATS / (H * W) channels
 constexpr int RP_PLANE_MAX = RP_PLANE_FLOATS / 2;  // a plane must allow a channel pair
-constexpr int RP_NS = 32;               // samples per axis (PH * 2 <= 32)
 constexpr int RP_LIST = 1024;           // RoIs of one (level, image) handled per round
-
-struct __align__(16) RpTab {
-  RtYSample y[RP_NS];  // absolute plane row of the lo tap, weights, walk flags
-  RtW xw[RP_NS];
-  short xo[RP_NS];     // absolute plane column of the lo tap
-  int meta[4];         // [0]: 1 walk, 0 every output is zero; [1]: three-tap rows allowed
-};
-static_assert(sizeof(RpTab) % 16 == 0, "RpTab is copied in 16-byte pieces");
+// RpTab (the per-RoI sample tables) is defined in roi_align.cu, next to rt3_roi_forward, which reads it too.
 
 __device__ __forceinline__ bool rp_level_planar(const RtLevels& lv, int level) {
   return level >= 0 && level < lv.L && lv.H[level] >= 2 && lv.W[level] >= 2 &&
@@ -54,14 +46,19 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
   const float* roi = rois + (size_t)k * 5;
   const int level = levels ? levels[k] : 0;
   const int b = (int)roi[0];
-  if (!rp_level_planar(lv, level) || b < 0 || b >= N) {
-    if (lane == 0) key[k] = -1;
+  RpTab* t = tabs + k;
+  if (level < 0 || level >= lv.L || b < 0 || b >= N || lv.H[level] < 2 || lv.W[level] < 2) {
+    if (lane == 0) {
+      key[k] = -1;
+      t->meta[0] = 2;  // no tables: the column walk decides on its own
+    }
     return;
   }
+  const bool planar = rp_level_planar(lv, level);  // whole-plane kernel; else only the tables are used
+  ymerge = ymerge && planar;  // the column walk merges itself, where its items walk whole columns
   const int H = lv.H[level], W = lv.W[level];
   const RtGeom g = rt_geom_fwd(roi, lv.scale[level], sampling_ratio, PH, PW);
   const int SY = PH * 2, SX = PW * 2;  // the launcher guarantees sampling_ratio == 2
-  RpTab* t = tabs + k;
   // lane s < SY: y-sample s; every lane also x-sample s (SX <= 32)
   int ylo = 0, xlo = 0;
   float ywl = 0.f, ywh = 0.f, xwl = 0.f, xwh = 0.f;
@@ -73,11 +70,13 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
   const int xl = __reduce_max_sync(0xffffffffu, xok ? xlo : -1);
   // wcnt[window][key]: how many RoIs of each (level, image) the window of RP_LIST keys holds, so that the
   // plane kernel only visits the windows that concern it
-  if (lane == 0 && wcnt) atomicAdd(&wcnt[(size_t)(k / RP_LIST) * nkeys + level * N + b], 1);
+  if (lane == 0 && wcnt && planar) atomicAdd(&wcnt[(size_t)(k / RP_LIST) * nkeys + level * N + b], 1);
   if (yl < 0 || xl < 0) {  // no sample inside the map on some axis: zeros (roi_align.py:20)
     if (lane == 0) {
       t->meta[0] = 0;
-      key[k] = level * N + b;
+      t->meta[2] = 0;
+      t->meta[3] = 0;
+      key[k] = planar ? level * N + b : -1;
     }
     return;
   }
@@ -119,7 +118,9 @@ rp_tables_kernel(RtLevels lv, int N, const float* __restrict__ rois, const int* 
   if (lane == 0) {
     t->meta[0] = 1;
     t->meta[1] = x3;
-    key[k] = level * N + b;
+    t->meta[2] = y0 | (yl << 16);
+    t->meta[3] = x0 | (xl << 16);
+    key[k] = planar ? level * N + b : -1;
   }
 }
 
