@@ -642,8 +642,11 @@ constexpr int RT3_TABLE_BYTES =
 #include "roi_fwd_mma.cuh"  // rm_pool_fwd_kernel: both passes on the warp-level tensor path
 #include "roi_fwd_plane.cuh"  // rp_plane_fwd_kernel: whole planes of the coarse levels staged once
 
+#ifndef RT3_MINB
+#define RT3_MINB 4  // resident CTAs per SM the column-walk kernel is compiled for (64 registers)
+#endif
 template <int U, bool LEAN>
-__global__ void __launch_bounds__(RT3_MAX_THREADS, 4)
+__global__ void __launch_bounds__(RT3_MAX_THREADS, RT3_MINB)
 rt_pool_fwd_kernel(RtLevels lv, int N, int C, const float* __restrict__ rois,
                    const int* __restrict__ levels, int K, int PH, int PW, float sampling_ratio,
                    float* __restrict__ out, int c_per_cta, int tile_floats, int gpb, int gw, int nbuf,
