@@ -134,6 +134,7 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
   RpTab* slots = reinterpret_cast<RpTab*>(planes + RP_PLANE_FLOATS);
   int* list = reinterpret_cast<int*>(slots + 2 * RP_WARPS);
   __shared__ int s_n;
+  __shared__ __align__(8) uint64_t s_bar;  // completion of the planes' bulk copy
 
   const int level = blockIdx.y;
   if (!rp_level_planar(lv, level)) return;
@@ -151,17 +152,28 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
   const int P = PH * PW;
   const int mykey = level * N + n;
 
-  // ---- the planes of this CTA's channels: one contiguous run of the NCHW map ------------------
+  // ---- the planes of this CTA's channels: one contiguous run of the NCHW map, fetched by ONE TMA bulk
+  //      copy (cp.async.bulk on an mbarrier, SASS UBLKCP) when the run is 16-byte aligned and a multiple of
+  //      16 bytes (P4: 4 x 50 x 84, P5: 16 x 25 x 42 floats = 67 200 bytes both), else by cp.async ----------
   const float* src = lv.feat[level] + ((size_t)n * C + c0) * HW;
   const int total = nch * HW;
   const bool v16 = ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
-  const int n16 = v16 ? (total >> 2) : 0;
+  const bool bulk = v16 && (total & 3) == 0 && total * 4 < (1 << 20);
   const uint32_t planes_s = rp_smem_addr(planes);
-  for (int i = tid; i < n16; i += RP_THREADS)
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(planes_s + 16u * (uint32_t)i), "l"(src + 4 * i) : "memory");
-  for (int i = 4 * n16 + tid; i < total; i += RP_THREADS)
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(planes_s + 4u * (uint32_t)i), "l"(src + i) : "memory");
-  asm volatile("cp.async.commit_group;" ::: "memory");
+  if (bulk) {
+    if (tid == 0) {
+      rp_mbar_init(&s_bar, 1);
+      rp_mbar_arrive_expect_tx(&s_bar, (uint32_t)total * 4u);
+      rp_bulk_load(planes, src, (uint32_t)total * 4u, &s_bar);
+    }
+  } else {
+    const int n16 = v16 ? (total >> 2) : 0;
+    for (int i = tid; i < n16; i += RP_THREADS)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(planes_s + 16u * (uint32_t)i), "l"(src + 4 * i) : "memory");
+    for (int i = 4 * n16 + tid; i < total; i += RP_THREADS)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(planes_s + 4u * (uint32_t)i), "l"(src + i) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
 
   // lanes: 16 per channel pair (PW <= 16 of them walk a column each); the two halves of a warp take
   // different channel pairs of the SAME RoI, so both run the same sample sequence (no divergence)
@@ -189,9 +201,10 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
         if (hit) list[pos] = k;
       }
     }
-    if (!landed) asm volatile("cp.async.wait_group 0;" ::: "memory");  // the planes
+    if (!landed && !bulk) asm volatile("cp.async.wait_group 0;" ::: "memory");  // the planes
+    __syncthreads();  // the list is complete; s_bar is initialised for every thread
+    if (!landed && bulk) rp_mbar_wait_bounded(&s_bar, 0);
     landed = true;
-    __syncthreads();
     const int cnt = s_n;
     // ---- warps on their own from here -------------------------------------------------------
     // tables of the warp's first RoI, then always one RoI ahead (two slots per warp)
@@ -234,7 +247,12 @@ rp_plane_fwd_kernel(RtLevels lv, int N, int C, const int* __restrict__ key, cons
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();  // the list is rebuilt by the next round
   }
-  if (!landed) asm volatile("cp.async.wait_group 0;" ::: "memory");  // no RoI of this (level, image): drain the copies
+  // no RoI of this (level, image): drain the copies before the CTA's shared memory is given away
+  if (!landed && !bulk) asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (!landed && bulk) {
+    __syncthreads();
+    rp_mbar_wait_bounded(&s_bar, 0);
+  }
 }
 
 constexpr size_t RP_SMEM_BYTES =
